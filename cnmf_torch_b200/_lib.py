@@ -1,0 +1,103 @@
+"""ctypes binding of libcnmf_b200.so (the C ABI declared in include/cnmf_b200.h).
+
+There is no fallback: if the library has not been built (``python -m cnmf_torch_b200.build``)
+importing this module's ``lib()`` raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+_PKG = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_PKG, "lib", "libcnmf_b200.so")
+
+ALGO_MU, ALGO_HALS = 0, 1
+IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05 = 0, 1, 2
+MAX_KP = 32
+
+ERR_INVALID, ERR_CUDA, ERR_WORKSPACE, ERR_UNSUPPORTED = -1, -2, -3, -4
+
+i32, i64, f32, f64, vp = C.c_int32, C.c_int64, C.c_float, C.c_double, C.c_void_p
+
+
+class FrobProblem(C.Structure):
+    """Mirror of ``cnmf_b200_frob_problem``."""
+    _fields_ = [
+        ("n_cells", i64), ("n_genes", i64),
+        ("X", vp), ("ldx", i64), ("Xt", vp), ("ldxt", i64),
+        ("R", i32), ("K", i32), ("Kp", i32), ("algo", i32), ("impl", i32), ("reserved", i32),
+        ("Wall", vp), ("ldw", i64), ("Ht", vp), ("ldh", i64),
+        ("gramW", vp), ("gramH", vp), ("active", vp),
+        ("l1_H", f32), ("l2_H", f32), ("l1_W", f32), ("l2_W", f32), ("eps", f32), ("pad0", f32),
+        ("normX2", f64), ("err2", vp), ("workspace", vp), ("workspace_bytes", i64),
+    ]
+
+
+class CsrProblem(C.Structure):
+    """Mirror of ``cnmf_b200_kl_problem``."""
+    _fields_ = [
+        ("n_cells", i64), ("n_genes", i64), ("nnz", i64),
+        ("row_ptr", vp), ("col_idx", vp), ("val", vp),
+        ("t_row_ptr", vp), ("t_col_idx", vp), ("t_val", vp),
+        ("R", i32), ("K", i32), ("Kp", i32), ("reserved", i32),
+        ("Hr", vp), ("Wt", vp),
+        ("active", vp),
+        ("l1_H", f32), ("l2_H", f32), ("l1_W", f32), ("l2_W", f32), ("eps", f32), ("pad0", f32),
+        ("sumX", f64), ("xlogx", f64), ("err2", vp), ("workspace", vp), ("workspace_bytes", i64),
+    ]
+
+
+# name -> (restype, argtypes).  Every symbol include/cnmf_b200.h declares must be listed here;
+# tests/test_abi.py checks the header against this table and the built library.
+SIGNATURES = {
+    "cnmf_b200_abi_version": (i32, []),
+    "cnmf_b200_last_error": (C.c_char_p, []),
+    "cnmf_b200_last_launch_count": (i64, []),
+    "cnmf_b200_sumsq_workspace_bytes": (i64, []),
+    "cnmf_b200_sumsq": (i32, [vp, i64, i64, i64, vp, vp, vp]),
+    "cnmf_b200_gram_workspace_bytes": (i64, [i32, i32, i64]),
+    "cnmf_b200_gram": (i32, [vp, i64, i32, i32, i64, vp, vp, vp]),
+    "cnmf_b200_gemm_nt": (i32, [vp, i64, i64, vp, i64, i64, i64, vp, i64, vp]),
+    "cnmf_b200_row_update_blocks": (i64, [i64]),
+    "cnmf_b200_row_update": (i32, [vp, i64, vp, i64, vp, vp, i64, i32, i32, i32, f32, f32, f32, vp, vp]),
+    "cnmf_b200_frob_workspace_bytes": (i64, [C.POINTER(FrobProblem)]),
+    "cnmf_b200_frob_prepare": (i32, [C.POINTER(FrobProblem), vp]),
+    "cnmf_b200_frob_iterate": (i32, [C.POINTER(FrobProblem), i32, vp]),
+    "cnmf_b200_frob_objective": (i32, [C.POINTER(FrobProblem), vp]),
+}
+
+_LIB = None
+
+
+class Cnmfb200Error(RuntimeError):
+    pass
+
+
+def lib() -> C.CDLL:
+    """Load the shared library once; raise loudly if it is absent."""
+    global _LIB
+    if _LIB is None:
+        if not os.path.exists(LIB_PATH):
+            raise Cnmfb200Error(
+                f"{LIB_PATH} is missing: build it with `python -m cnmf_torch_b200.build` "
+                "(nvcc, sm_100a). There is no CPU or PyTorch fallback for this path.")
+        handle = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(handle, name)
+            fn.restype = res
+            fn.argtypes = args
+        _LIB = handle
+    return _LIB
+
+
+def check(rc: int, what: str = "") -> int:
+    """Raise on a negative return code, with the library's own message."""
+    if rc < 0:
+        msg = lib().cnmf_b200_last_error().decode(errors="replace")
+        raise Cnmfb200Error(f"{what or 'libcnmf_b200'} failed (rc={rc}): {msg}")
+    return rc
+
+
+def ptr(t) -> int:
+    """Device pointer of a torch tensor (or None -> NULL)."""
+    return None if t is None else t.data_ptr()

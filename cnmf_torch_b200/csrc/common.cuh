@@ -1,0 +1,120 @@
+// Shared host/device helpers for libcnmf_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/cnmf_b200.h"
+
+namespace cnmf {
+
+// thread-local error text + launch counter (defined in abi.cu)
+void set_error(const char* fmt, ...);
+void count_launch(int64_t n = 1);
+void reset_launch_count();
+
+#define CNMF_CHECK_ARG(cond, ...)                \
+  do {                                           \
+    if (!(cond)) {                               \
+      cnmf::set_error(__VA_ARGS__);              \
+      return CNMF_B200_ERR_INVALID;              \
+    }                                            \
+  } while (0)
+
+#define CNMF_CUDA(call)                                                                    \
+  do {                                                                                     \
+    cudaError_t _e = (call);                                                               \
+    if (_e != cudaSuccess) {                                                               \
+      cnmf::set_error("%s failed: %s (%s:%d)", #call, cudaGetErrorString(_e), __FILE__,    \
+                      __LINE__);                                                           \
+      return CNMF_B200_ERR_CUDA;                                                           \
+    }                                                                                      \
+  } while (0)
+
+#define CNMF_LAUNCH_CHECK()                                                                \
+  do {                                                                                     \
+    cudaError_t _e = cudaGetLastError();                                                   \
+    if (_e != cudaSuccess) {                                                               \
+      cnmf::set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, \
+                      __LINE__);                                                           \
+      return CNMF_B200_ERR_CUDA;                                                           \
+    }                                                                                      \
+    cnmf::count_launch();                                                                  \
+  } while (0)
+
+#define CNMF_TRY(call)          \
+  do {                          \
+    int _rc = (call);           \
+    if (_rc != 0) return _rc;   \
+  } while (0)
+
+static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
+static inline int64_t align_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
+static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }
+
+// Dispatch a runtime Kp in {4,8,...,32} to a compile-time constant.
+#define CNMF_DISPATCH_KP(kp, ...)                          \
+  switch (kp) {                                            \
+    case 4:  { constexpr int KP = 4;  __VA_ARGS__; } break; \
+    case 8:  { constexpr int KP = 8;  __VA_ARGS__; } break; \
+    case 12: { constexpr int KP = 12; __VA_ARGS__; } break; \
+    case 16: { constexpr int KP = 16; __VA_ARGS__; } break; \
+    case 20: { constexpr int KP = 20; __VA_ARGS__; } break; \
+    case 24: { constexpr int KP = 24; __VA_ARGS__; } break; \
+    case 28: { constexpr int KP = 28; __VA_ARGS__; } break; \
+    case 32: { constexpr int KP = 32; __VA_ARGS__; } break; \
+    default:                                               \
+      cnmf::set_error("Kp=%d unsupported (multiple of 4, <= 32)", (int)(kp)); \
+      return CNMF_B200_ERR_INVALID;                        \
+  }
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// The per-row update shared by the SIMT row-update kernel and the tcgen05 epilogue.
+// p[k]  : (Y F^T)[row, r*KP + k]     s[k] : state[row, r*KP + k] (in/out)
+// gram  : KP x KP Gram of the fixed factor (shared memory; read as broadcast)
+// MU   : cnmf.py:358-372   HALS : sklearn _cdnmf_fast.pyx column sweep restated
+template <int KP, int ALGO>
+__device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
+                                           const float* __restrict__ gram, float l1, float l2,
+                                           float eps) {
+  if (ALGO == CNMF_B200_ALGO_MU) {
+    float out[KP];
+#pragma unroll
+    for (int k = 0; k < KP; ++k) {
+      float denom = 0.f;
+#pragma unroll
+      for (int j = 0; j < KP; ++j) denom = fmaf(s[j], gram[j * KP + k], denom);
+      denom = fmaf(l2, s[k], denom);
+      float numer = l1 > 0.f ? fmaxf(p[k] - l1, 0.f) : p[k];
+      float rate = denom < eps ? 0.f : __fdiv_rn(numer, denom);
+      out[k] = s[k] * rate;
+    }
+#pragma unroll
+    for (int k = 0; k < KP; ++k) s[k] = out[k];
+  } else {
+#pragma unroll
+    for (int k = 0; k < KP; ++k) {
+      float d = gram[k * KP + k] + l2;
+      float dot = 0.f;
+#pragma unroll
+      for (int j = 0; j < KP; ++j) dot = fmaf(s[j], gram[j * KP + k], dot);
+      float g = p[k] - dot - l1;
+      float v = fmaxf(s[k] + __fdiv_rn(g, d), 0.f);
+      s[k] = (d < eps) ? 0.f : v;
+    }
+  }
+}
+#endif
+
+}  // namespace cnmf

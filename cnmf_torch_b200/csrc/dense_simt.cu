@@ -1,0 +1,408 @@
+// Dense Frobenius engine, CUDA-core (fp32 FFMA) kernels: the semantic baseline that the
+// tcgen05 path is checked against, plus the small kernels both paths share (Gram, sum of
+// squares, objective combine).  See include/cnmf_b200.h for the reference lines replaced.
+#include "common.cuh"
+
+namespace cnmf {
+
+// ---------------------------------------------------------------------------------------------
+// sum of squares (fp64 accumulate), two stages, deterministic
+// ---------------------------------------------------------------------------------------------
+constexpr int SUMSQ_BLOCKS = 1024;
+
+__global__ void __launch_bounds__(256) sumsq_partial_kernel(const float* __restrict__ x, int64_t rows,
+                                                            int64_t cols, int64_t ld,
+                                                            double* __restrict__ partial) {
+  double acc = 0.0;
+  const int64_t total = rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (int64_t)gridDim.x * blockDim.x) {
+    int64_t r = i / cols, c = i - r * cols;
+    float v = x[r * ld + c];
+    acc += (double)v * (double)v;
+  }
+  __shared__ double red[8];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    partial[blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(32) sumsq_final_kernel(const double* __restrict__ partial, int n,
+                                                         double* __restrict__ out) {
+  // fixed-order tree: lane-strided partial sums then a shuffle tree
+  double acc = 0.0;
+  for (int i = threadIdx.x; i < n; i += 32) acc += partial[i];
+  acc = warp_sum(acc);
+  if (threadIdx.x == 0) out[0] = acc;
+}
+
+// ---------------------------------------------------------------------------------------------
+// Gram of every replicate block: gram[r] = F_r F_r^T
+// ---------------------------------------------------------------------------------------------
+constexpr int GRAM_TILE = 64;      // columns staged per step
+constexpr int GRAM_THREADS = 256;
+constexpr int GRAM_SPLIT_LEN = 2048;  // columns per CTA (multiple of GRAM_TILE)
+
+static inline int gram_splits(int64_t L) { return (int)ceil_div(L, GRAM_SPLIT_LEN); }
+
+template <int KP>
+__global__ void __launch_bounds__(GRAM_THREADS) gram_partial_kernel(const float* __restrict__ F,
+                                                                    int64_t ld, int64_t L,
+                                                                    float* __restrict__ partial,
+                                                                    int nsplit) {
+  constexpr int NP = KP * KP;
+  constexpr int NSL = (GRAM_THREADS / NP) > 0 ? (GRAM_THREADS / NP) : 1;  // column slices
+  constexpr int OPT = (NP * NSL + GRAM_THREADS - 1) / GRAM_THREADS;       // outputs per thread
+  __shared__ float tile[KP][GRAM_TILE + 1];
+  __shared__ float red[NSL][NP];
+  const int r = blockIdx.y, split = blockIdx.x;
+  const float* Fr = F + (int64_t)r * KP * ld;
+  const int64_t l_begin = (int64_t)split * GRAM_SPLIT_LEN;
+  const int64_t l_end = min(L, l_begin + (int64_t)GRAM_SPLIT_LEN);
+
+  float acc[OPT];
+#pragma unroll
+  for (int i = 0; i < OPT; ++i) acc[i] = 0.f;
+
+  for (int64_t l0 = l_begin; l0 < l_end; l0 += GRAM_TILE) {
+    for (int i = threadIdx.x; i < KP * GRAM_TILE; i += GRAM_THREADS) {
+      int a = i / GRAM_TILE, c = i - a * GRAM_TILE;
+      int64_t l = l0 + c;
+      tile[a][c] = (l < l_end) ? Fr[(int64_t)a * ld + l] : 0.f;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int i = 0; i < OPT; ++i) {
+      int o = threadIdx.x + i * GRAM_THREADS;
+      if (o < NP * NSL) {
+        int pair = o % NP, sl = o / NP;
+        int a = pair / KP, b = pair - a * KP;
+        float t = acc[i];
+        for (int c = sl; c < GRAM_TILE; c += NSL) t = fmaf(tile[a][c], tile[b][c], t);
+        acc[i] = t;
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < OPT; ++i) {
+    int o = threadIdx.x + i * GRAM_THREADS;
+    if (o < NP * NSL) red[o / NP][o % NP] = acc[i];
+  }
+  __syncthreads();
+  for (int pair = threadIdx.x; pair < NP; pair += GRAM_THREADS) {
+    float t = 0.f;
+#pragma unroll
+    for (int sl = 0; sl < NSL; ++sl) t += red[sl][pair];
+    partial[((int64_t)r * nsplit + split) * NP + pair] = t;
+  }
+}
+
+__global__ void gram_final_kernel(const float* __restrict__ partial, int nsplit, int np,
+                                  float* __restrict__ gram, int64_t total) {
+  int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // over R*np
+  if (i >= total) return;
+  int64_t r = i / np;
+  int pair = (int)(i - r * np);
+  // fp64 combine of the split partials, fixed order
+  double t = 0.0;
+  for (int s = 0; s < nsplit; ++s) t += (double)partial[(r * nsplit + s) * np + pair];
+  gram[i] = (float)t;
+}
+
+// ---------------------------------------------------------------------------------------------
+// C = A B^T, fp32, 128x128x16 tiles, 8x8 per thread
+// ---------------------------------------------------------------------------------------------
+constexpr int GM = 128, GN = 128, GK = 16;
+
+__global__ void __launch_bounds__(256) gemm_nt_kernel(const float* __restrict__ A, int64_t lda,
+                                                      int64_t M, const float* __restrict__ B,
+                                                      int64_t ldb, int64_t N, int64_t Kd,
+                                                      float* __restrict__ C, int64_t ldc) {
+  __shared__ __align__(16) float As[GK][GM + 4];
+  __shared__ __align__(16) float Bs[GK][GN + 4];
+  const int tid = threadIdx.x;
+  const int tx = tid & 15, ty = tid >> 4;  // 16 x 16 threads, 8x8 each
+  const int64_t m0 = (int64_t)blockIdx.y * GM, n0 = (int64_t)blockIdx.x * GN;
+
+  float acc[8][8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[i][j] = 0.f;
+
+  // each thread stages 2 float4 of A and 2 of B per k-step: row = idx/4, k-quad = idx%4
+  for (int64_t k0 = 0; k0 < Kd; k0 += GK) {
+#pragma unroll
+    for (int h = 0; h < 2; ++h) {
+      int idx = tid + h * 256;
+      int row = idx >> 2, kq = (idx & 3) * 4;
+      int64_t k = k0 + kq;
+      float4 va = make_float4(0.f, 0.f, 0.f, 0.f), vb = va;
+      if (m0 + row < M) {
+        const float* pa = A + (m0 + row) * lda + k;
+        if (k + 3 < Kd) va = *reinterpret_cast<const float4*>(pa);
+        else {
+          if (k < Kd) va.x = pa[0];
+          if (k + 1 < Kd) va.y = pa[1];
+          if (k + 2 < Kd) va.z = pa[2];
+        }
+      }
+      if (n0 + row < N) {
+        const float* pb = B + (n0 + row) * ldb + k;
+        if (k + 3 < Kd) vb = *reinterpret_cast<const float4*>(pb);
+        else {
+          if (k < Kd) vb.x = pb[0];
+          if (k + 1 < Kd) vb.y = pb[1];
+          if (k + 2 < Kd) vb.z = pb[2];
+        }
+      }
+      As[kq + 0][row] = va.x; As[kq + 1][row] = va.y; As[kq + 2][row] = va.z; As[kq + 3][row] = va.w;
+      Bs[kq + 0][row] = vb.x; Bs[kq + 1][row] = vb.y; Bs[kq + 2][row] = vb.z; Bs[kq + 3][row] = vb.w;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < GK; ++kk) {
+      float a[8], b[8];
+      *reinterpret_cast<float4*>(&a[0]) = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+      *reinterpret_cast<float4*>(&a[4]) = *reinterpret_cast<const float4*>(&As[kk][64 + ty * 4]);
+      *reinterpret_cast<float4*>(&b[0]) = *reinterpret_cast<const float4*>(&Bs[kk][tx * 4]);
+      *reinterpret_cast<float4*>(&b[4]) = *reinterpret_cast<const float4*>(&Bs[kk][64 + tx * 4]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    int64_t m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+    if (m >= M) continue;
+#pragma unroll
+    for (int jh = 0; jh < 2; ++jh) {
+      int64_t n = n0 + jh * 64 + tx * 4;
+      float* pc = C + m * ldc + n;
+      if (n + 3 < N) {
+        *reinterpret_cast<float4*>(pc) =
+            make_float4(acc[i][jh * 4 + 0], acc[i][jh * 4 + 1], acc[i][jh * 4 + 2], acc[i][jh * 4 + 3]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (n + j < N) pc[j] = acc[i][jh * 4 + j];
+      }
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Row update (state and Pt both [R*KP x M]: consecutive threads = consecutive m => coalesced)
+// ---------------------------------------------------------------------------------------------
+constexpr int RU_THREADS = 128;
+constexpr int RU_REPS = 4;  // replicates per CTA
+
+template <int KP, int ALGO>
+__global__ void __launch_bounds__(RU_THREADS) row_update_kernel(
+    const float* __restrict__ Pt, int64_t ldp, float* __restrict__ state, int64_t lds,
+    const float* __restrict__ gram, const uint8_t* __restrict__ active, int64_t M, int R, float l1,
+    float l2, float eps, double* __restrict__ partials) {
+  __shared__ float sgram[RU_REPS][KP * KP];
+  __shared__ double red[RU_THREADS / 32][2];
+  const int r0 = blockIdx.y * RU_REPS;
+  for (int i = threadIdx.x; i < RU_REPS * KP * KP; i += RU_THREADS) {
+    int rr = i / (KP * KP);
+    sgram[rr][i - rr * KP * KP] = (r0 + rr < R) ? gram[(int64_t)(r0 + rr) * KP * KP + (i - rr * KP * KP)] : 0.f;
+  }
+  __syncthreads();
+  const int64_t m = (int64_t)blockIdx.x * RU_THREADS + threadIdx.x;
+  const bool in = m < M;
+  for (int rr = 0; rr < RU_REPS; ++rr) {
+    const int r = r0 + rr;
+    if (r >= R) break;
+    const bool act = active == nullptr || active[r] != 0;
+    float cross = 0.f, ssum = 0.f;
+    if (in) {
+      float p[KP], s[KP];
+      const int64_t base = (int64_t)r * KP;
+#pragma unroll
+      for (int k = 0; k < KP; ++k) {
+        p[k] = Pt[(base + k) * ldp + m];
+        s[k] = state[(base + k) * lds + m];
+      }
+      if (act) {
+        update_row<KP, ALGO>(p, s, sgram[rr], l1, l2, eps);
+#pragma unroll
+        for (int k = 0; k < KP; ++k) state[(base + k) * lds + m] = s[k];
+      }
+#pragma unroll
+      for (int k = 0; k < KP; ++k) {
+        cross = fmaf(s[k], p[k], cross);
+        ssum += s[k];
+      }
+    }
+    double dc = warp_sum((double)cross), dsum = warp_sum((double)ssum);
+    if ((threadIdx.x & 31) == 0) {
+      red[threadIdx.x >> 5][0] = dc;
+      red[threadIdx.x >> 5][1] = dsum;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      double c = 0.0, s2 = 0.0;
+      for (int w = 0; w < RU_THREADS / 32; ++w) {
+        c += red[w][0];
+        s2 += red[w][1];
+      }
+      partials[((int64_t)blockIdx.x * R + r) * 2 + 0] = c;
+      partials[((int64_t)blockIdx.x * R + r) * 2 + 1] = s2;
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Objective combine: err2[r] = ||X||^2 - 2 cross_r + <gramW_r, gramH_r> + regularisation, fp64
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) frob_objective_kernel(
+    double normX2, const double* __restrict__ partW, int nblkW, const double* __restrict__ partH,
+    int nblkH, const float* __restrict__ gramW, const float* __restrict__ gramH, int R, int Kp,
+    float l1_H, float l2_H, float l1_W, float l2_W, double* __restrict__ err2) {
+  const int r = blockIdx.x;
+  const int lane = threadIdx.x;
+  double cross = 0.0, sumW = 0.0, sumH = 0.0;
+  for (int b = lane; b < nblkW; b += 32) {
+    cross += partW[((int64_t)b * R + r) * 2 + 0];
+    sumW += partW[((int64_t)b * R + r) * 2 + 1];
+  }
+  for (int b = lane; b < nblkH; b += 32) sumH += partH[((int64_t)b * R + r) * 2 + 1];
+  double tr = 0.0, trW = 0.0, trH = 0.0;
+  const int np = Kp * Kp;
+  for (int i = lane; i < np; i += 32) {
+    double gw = gramW[(int64_t)r * np + i], gh = gramH[(int64_t)r * np + i];
+    tr += gw * gh;
+    if (i / Kp == i % Kp) {
+      trW += gw;
+      trH += gh;
+    }
+  }
+  cross = warp_sum(cross); sumW = warp_sum(sumW); sumH = warp_sum(sumH);
+  tr = warp_sum(tr); trW = warp_sum(trW); trH = warp_sum(trH);
+  if (lane == 0) {
+    double v = normX2 - 2.0 * cross + tr;
+    v += 2.0 * ((double)l1_H * sumH + (double)l1_W * sumW) + (double)l2_H * trH + (double)l2_W * trW;
+    err2[r] = v;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// host-side launchers
+// ---------------------------------------------------------------------------------------------
+int launch_gram(const float* F, int64_t ld, int R, int Kp, int64_t L, float* gram, void* ws,
+                cudaStream_t st) {
+  const int ns = gram_splits(L);
+  float* partial = reinterpret_cast<float*>(ws);
+  dim3 grid(ns, R);
+  CNMF_DISPATCH_KP(Kp, (gram_partial_kernel<KP><<<grid, GRAM_THREADS, 0, st>>>(F, ld, L, partial, ns)));
+  CNMF_LAUNCH_CHECK();
+  const int64_t total = (int64_t)R * Kp * Kp;
+  gram_final_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, st>>>(partial, ns, Kp * Kp, gram, total);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, int64_t ldb, int64_t N,
+                   int64_t Kd, float* C, int64_t ldc, cudaStream_t st) {
+  dim3 grid((unsigned)ceil_div(N, GN), (unsigned)ceil_div(M, GM));
+  gemm_nt_kernel<<<grid, 256, 0, st>>>(A, lda, M, B, ldb, N, Kd, C, ldc);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_row_update(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
+                      const uint8_t* active, int64_t M, int R, int Kp, int algo, float l1, float l2,
+                      float eps, double* partials, cudaStream_t st) {
+  dim3 grid((unsigned)ceil_div(M, RU_THREADS), (unsigned)ceil_div(R, RU_REPS));
+  if (algo == CNMF_B200_ALGO_MU) {
+    CNMF_DISPATCH_KP(Kp, (row_update_kernel<KP, CNMF_B200_ALGO_MU><<<grid, RU_THREADS, 0, st>>>(
+                             Pt, ldp, state, lds, gram, active, M, R, l1, l2, eps, partials)));
+  } else if (algo == CNMF_B200_ALGO_HALS) {
+    CNMF_DISPATCH_KP(Kp, (row_update_kernel<KP, CNMF_B200_ALGO_HALS><<<grid, RU_THREADS, 0, st>>>(
+                             Pt, ldp, state, lds, gram, active, M, R, l1, l2, eps, partials)));
+  } else {
+    set_error("unknown algo %d", algo);
+    return CNMF_B200_ERR_INVALID;
+  }
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_frob_objective(double normX2, const double* partW, int nblkW, const double* partH,
+                          int nblkH, const float* gramW, const float* gramH, int R, int Kp, float l1_H,
+                          float l2_H, float l1_W, float l2_W, double* err2, cudaStream_t st) {
+  frob_objective_kernel<<<R, 32, 0, st>>>(normX2, partW, nblkW, partH, nblkH, gramW, gramH, R, Kp,
+                                          l1_H, l2_H, l1_W, l2_W, err2);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+}  // namespace cnmf
+
+using namespace cnmf;
+
+extern "C" {
+
+int64_t cnmf_b200_sumsq_workspace_bytes(void) { return SUMSQ_BLOCKS * (int64_t)sizeof(double); }
+
+int cnmf_b200_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld, double* out,
+                    void* workspace, void* stream) {
+  CNMF_CHECK_ARG(x && out && workspace, "sumsq: null pointer");
+  CNMF_CHECK_ARG(rows >= 0 && cols >= 0 && ld >= cols, "sumsq: bad shape %lld x %lld ld %lld",
+                 (long long)rows, (long long)cols, (long long)ld);
+  cudaStream_t st = (cudaStream_t)stream;
+  double* partial = reinterpret_cast<double*>(workspace);
+  sumsq_partial_kernel<<<SUMSQ_BLOCKS, 256, 0, st>>>(x, rows, cols, ld, partial);
+  CNMF_LAUNCH_CHECK();
+  sumsq_final_kernel<<<1, 32, 0, st>>>(partial, SUMSQ_BLOCKS, out);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int64_t cnmf_b200_gram_workspace_bytes(int32_t R, int32_t Kp, int64_t L) {
+  return (int64_t)R * gram_splits(L) * Kp * Kp * (int64_t)sizeof(float);
+}
+
+int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
+                   void* workspace, void* stream) {
+  CNMF_CHECK_ARG(F && gram && workspace, "gram: null pointer");
+  CNMF_CHECK_ARG(R > 0 && L > 0 && ld >= L, "gram: bad shape R=%d L=%lld ld=%lld", R, (long long)L,
+                 (long long)ld);
+  return launch_gram(F, ld, R, Kp, L, gram, workspace, (cudaStream_t)stream);
+}
+
+int cnmf_b200_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, int64_t ldb, int64_t N,
+                      int64_t Kd, float* C, int64_t ldc, void* stream) {
+  CNMF_CHECK_ARG(A && B && C, "gemm_nt: null pointer");
+  CNMF_CHECK_ARG(M > 0 && N > 0 && Kd > 0, "gemm_nt: empty shape");
+  CNMF_CHECK_ARG(lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned16(A) && aligned16(B) &&
+                     aligned16(C),
+                 "gemm_nt: leading dimensions must be multiples of 4 and pointers 16B aligned");
+  CNMF_CHECK_ARG(lda >= Kd && ldb >= Kd && ldc >= N, "gemm_nt: leading dimension too small");
+  return launch_gemm_nt(A, lda, M, B, ldb, N, Kd, C, ldc, (cudaStream_t)stream);
+}
+
+int64_t cnmf_b200_row_update_blocks(int64_t M) { return ceil_div(M, RU_THREADS); }
+
+int cnmf_b200_row_update(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
+                         const uint8_t* active, int64_t M, int32_t R, int32_t Kp, int32_t algo, float l1,
+                         float l2, float eps, double* partials, void* stream) {
+  CNMF_CHECK_ARG(Pt && state && gram && partials, "row_update: null pointer");
+  CNMF_CHECK_ARG(M > 0 && R > 0 && ldp >= M && lds >= M, "row_update: bad shape");
+  return launch_row_update(Pt, ldp, state, lds, gram, active, M, R, Kp, algo, l1, l2, eps, partials,
+                           (cudaStream_t)stream);
+}
+
+}  // extern "C"

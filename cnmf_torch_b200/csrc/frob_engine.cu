@@ -1,0 +1,228 @@
+// Replicate-batched dense Frobenius driver: enqueues n_iters x {H half-step, Gram(H), W half-step,
+// Gram(W)} and the objective on one stream.  Replaces the batch loop inside run_nmf
+// (/root/reference/src/cnmf/cnmf.py:819) for R replicates of one K at a time.
+#include "common.cuh"
+
+namespace cnmf {
+int launch_gram(const float*, int64_t, int, int, int64_t, float*, void*, cudaStream_t);
+int launch_gemm_nt(const float*, int64_t, int64_t, const float*, int64_t, int64_t, int64_t, float*,
+                   int64_t, cudaStream_t);
+int launch_row_update(const float*, int64_t, float*, int64_t, const float*, const uint8_t*, int64_t, int,
+                      int, int, float, float, float, double*, cudaStream_t);
+int launch_frob_objective(double, const double*, int, const double*, int, const float*, const float*, int,
+                          int, float, float, float, float, double*, cudaStream_t);
+// tcgen05 path (dense_tc.cu)
+bool tc_supported(int64_t M, int64_t Kd, int R, int Kp);
+int64_t tc_workspace_bytes(int64_t M, int64_t Kd, int R, int Kp);
+int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                        float* state, int64_t lds, const float* gram, const uint8_t* active, int R, int Kp,
+                        int algo, float l1, float l2, float eps, double* partials, void* ws,
+                        int64_t ws_bytes, cudaStream_t st);
+
+struct FrobLayout {
+  int64_t off_pt, off_gram, off_partH, off_partW, off_zero, off_tc, total;
+  int nblkH, nblkW;
+  int impl;
+};
+
+static int resolve_impl(const cnmf_b200_frob_problem* p) {
+  if (p->impl == CNMF_B200_IMPL_SIMT) return CNMF_B200_IMPL_SIMT;
+  const bool ok = tc_supported(p->n_cells, p->n_genes, p->R, p->Kp) &&
+                  tc_supported(p->n_genes, p->n_cells, p->R, p->Kp);
+  if (p->impl == CNMF_B200_IMPL_TCGEN05) return ok ? CNMF_B200_IMPL_TCGEN05 : -1;
+  return ok ? CNMF_B200_IMPL_TCGEN05 : CNMF_B200_IMPL_SIMT;
+}
+
+static FrobLayout frob_layout(const cnmf_b200_frob_problem* p) {
+  FrobLayout l{};
+  l.impl = resolve_impl(p);
+  const int64_t rk = (int64_t)p->R * p->Kp;
+  const int64_t ldmax = align_up(p->n_cells > p->n_genes ? p->n_cells : p->n_genes, 4);
+  l.nblkH = (int)cnmf_b200_row_update_blocks(p->n_cells);
+  l.nblkW = (int)cnmf_b200_row_update_blocks(p->n_genes);
+  int64_t off = 0;
+  l.off_pt = off;
+  if (l.impl == CNMF_B200_IMPL_SIMT) off += align_up(rk * ldmax * 4, 256);
+  l.off_gram = off;
+  int64_t gw = cnmf_b200_gram_workspace_bytes(p->R, p->Kp, p->n_cells);
+  int64_t gg = cnmf_b200_gram_workspace_bytes(p->R, p->Kp, p->n_genes);
+  off += align_up(gw > gg ? gw : gg, 256);
+  l.off_partH = off;
+  off += align_up((int64_t)l.nblkH * p->R * 2 * 8, 256);
+  l.off_partW = off;
+  off += align_up((int64_t)l.nblkW * p->R * 2 * 8, 256);
+  l.off_zero = off;
+  off += align_up(p->R, 256);
+  l.off_tc = off;
+  if (l.impl == CNMF_B200_IMPL_TCGEN05) {
+    int64_t a = tc_workspace_bytes(p->n_cells, p->n_genes, p->R, p->Kp);
+    int64_t b = tc_workspace_bytes(p->n_genes, p->n_cells, p->R, p->Kp);
+    off += align_up(a > b ? a : b, 256);
+  }
+  l.total = off;
+  return l;
+}
+
+static int check_problem(const cnmf_b200_frob_problem* p) {
+  CNMF_CHECK_ARG(p != nullptr, "frob: null problem");
+  CNMF_CHECK_ARG(p->n_cells > 0 && p->n_genes > 0 && p->R > 0 && p->K > 0, "frob: empty shape");
+  CNMF_CHECK_ARG(p->Kp >= p->K && p->Kp % 4 == 0 && p->Kp <= CNMF_B200_MAX_KP,
+                 "frob: Kp=%d must be a multiple of 4, >= K=%d and <= %d", p->Kp, p->K, CNMF_B200_MAX_KP);
+  CNMF_CHECK_ARG(p->algo == CNMF_B200_ALGO_MU || p->algo == CNMF_B200_ALGO_HALS, "frob: unknown algo %d",
+                 p->algo);
+  return 0;
+}
+
+static int check_pointers(const cnmf_b200_frob_problem* p) {
+  CNMF_CHECK_ARG(p->X && p->Xt && p->Wall && p->Ht && p->gramW && p->gramH && p->workspace,
+                 "frob: null device pointer");
+  CNMF_CHECK_ARG(p->ldx >= p->n_genes && p->ldxt >= p->n_cells && p->ldw >= p->n_genes &&
+                     p->ldh >= p->n_cells,
+                 "frob: leading dimension too small");
+  CNMF_CHECK_ARG(p->ldx % 4 == 0 && p->ldxt % 4 == 0 && p->ldw % 4 == 0 && p->ldh % 4 == 0,
+                 "frob: leading dimensions must be multiples of 4");
+  CNMF_CHECK_ARG(aligned16(p->X) && aligned16(p->Xt) && aligned16(p->Wall) && aligned16(p->Ht) &&
+                     aligned16(p->workspace),
+                 "frob: pointers must be 16-byte aligned");
+  return 0;
+}
+
+}  // namespace cnmf
+
+using namespace cnmf;
+
+extern "C" {
+
+int64_t cnmf_b200_frob_workspace_bytes(const cnmf_b200_frob_problem* p) {
+  if (check_problem(p) != 0) return CNMF_B200_ERR_INVALID;
+  FrobLayout l = frob_layout(p);
+  if (l.impl < 0) {
+    set_error("frob: tcgen05 path does not support this shape");
+    return CNMF_B200_ERR_UNSUPPORTED;
+  }
+  return l.total;
+}
+
+int cnmf_b200_frob_prepare(const cnmf_b200_frob_problem* p, void* stream) {
+  CNMF_TRY(check_problem(p));
+  CNMF_TRY(check_pointers(p));
+  FrobLayout l = frob_layout(p);
+  CNMF_CHECK_ARG(l.impl >= 0, "frob: tcgen05 path does not support this shape");
+  if (p->workspace_bytes < l.total) {
+    set_error("frob: workspace %lld < required %lld", (long long)p->workspace_bytes, (long long)l.total);
+    return CNMF_B200_ERR_WORKSPACE;
+  }
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  return launch_gram(p->Wall, p->ldw, p->R, p->Kp, p->n_genes, p->gramW, ws + l.off_gram,
+                     (cudaStream_t)stream);
+}
+
+int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, void* stream) {
+  reset_launch_count();
+  CNMF_TRY(check_problem(p));
+  CNMF_TRY(check_pointers(p));
+  CNMF_CHECK_ARG(n_iters >= 0, "frob: n_iters < 0");
+  FrobLayout l = frob_layout(p);
+  CNMF_CHECK_ARG(l.impl >= 0, "frob: tcgen05 path does not support this shape");
+  if (p->workspace_bytes < l.total) {
+    set_error("frob: workspace %lld < required %lld", (long long)p->workspace_bytes, (long long)l.total);
+    return CNMF_B200_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  float* Pt = reinterpret_cast<float*>(ws + l.off_pt);
+  void* gws = ws + l.off_gram;
+  double* partH = reinterpret_cast<double*>(ws + l.off_partH);
+  double* partW = reinterpret_cast<double*>(ws + l.off_partW);
+  void* tcws = ws + l.off_tc;
+  const int64_t N = p->n_cells, G = p->n_genes;
+  const int64_t rk = (int64_t)p->R * p->Kp;
+  const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
+  const int64_t tc_bytes = l.total - l.off_tc;
+
+  for (int it = 0; it < n_iters; ++it) {
+    // ---- H half-step: Pt[RKp x N] = Wall X^T ; Ht <- update(Ht; Pt, gramW)
+    if (l.impl == CNMF_B200_IMPL_SIMT) {
+      CNMF_TRY(launch_gemm_nt(p->Wall, p->ldw, rk, p->X, p->ldx, N, G, Pt, ldpH, st));
+      CNMF_TRY(launch_row_update(Pt, ldpH, p->Ht, p->ldh, p->gramW, p->active, N, p->R, p->Kp, p->algo,
+                                 p->l1_H, p->l2_H, p->eps, partH, st));
+    } else {
+      CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, p->Wall, p->ldw, p->Ht, p->ldh, p->gramW, p->active,
+                                   p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, tcws, tc_bytes,
+                                   st));
+    }
+    CNMF_TRY(launch_gram(p->Ht, p->ldh, p->R, p->Kp, N, p->gramH, gws, st));
+    // ---- W half-step: Pt[RKp x G] = Ht Xt^T ; Wall <- update(Wall; Pt, gramH)
+    if (l.impl == CNMF_B200_IMPL_SIMT) {
+      CNMF_TRY(launch_gemm_nt(p->Ht, p->ldh, rk, p->Xt, p->ldxt, G, N, Pt, ldpW, st));
+      CNMF_TRY(launch_row_update(Pt, ldpW, p->Wall, p->ldw, p->gramH, p->active, G, p->R, p->Kp, p->algo,
+                                 p->l1_W, p->l2_W, p->eps, partW, st));
+    } else {
+      CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, p->Ht, p->ldh, p->Wall, p->ldw, p->gramH,
+                                   p->active, p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, tcws,
+                                   tc_bytes, st));
+    }
+    CNMF_TRY(launch_gram(p->Wall, p->ldw, p->R, p->Kp, G, p->gramW, gws, st));
+  }
+  if (p->err2 != nullptr && n_iters > 0) {
+    CNMF_TRY(launch_frob_objective(p->normX2, partW, l.nblkW, partH, l.nblkH, p->gramW, p->gramH, p->R,
+                                   p->Kp, p->l1_H, p->l2_H, p->l1_W, p->l2_W, p->err2, st));
+  }
+  return 0;
+}
+
+/* Objective of the CURRENT state without changing it (used for the initial error that
+ * normalises the convergence test, and after the last partial block). */
+int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
+  reset_launch_count();
+  CNMF_TRY(check_problem(p));
+  CNMF_TRY(check_pointers(p));
+  CNMF_CHECK_ARG(p->err2 != nullptr, "frob_objective: err2 is NULL");
+  FrobLayout l = frob_layout(p);
+  CNMF_CHECK_ARG(l.impl >= 0, "frob: tcgen05 path does not support this shape");
+  if (p->workspace_bytes < l.total) {
+    set_error("frob: workspace %lld < required %lld", (long long)p->workspace_bytes, (long long)l.total);
+    return CNMF_B200_ERR_WORKSPACE;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  float* Pt = reinterpret_cast<float*>(ws + l.off_pt);
+  void* gws = ws + l.off_gram;
+  double* partH = reinterpret_cast<double*>(ws + l.off_partH);
+  double* partW = reinterpret_cast<double*>(ws + l.off_partW);
+  uint8_t* zero = reinterpret_cast<uint8_t*>(ws + l.off_zero);
+  void* tcws = ws + l.off_tc;
+  const int64_t N = p->n_cells, G = p->n_genes;
+  const int64_t rk = (int64_t)p->R * p->Kp;
+  const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
+  CNMF_CUDA(cudaMemsetAsync(zero, 0, p->R, st));
+  CNMF_CUDA(cudaMemsetAsync(partH, 0, (size_t)l.nblkH * p->R * 2 * 8, st));
+  CNMF_TRY(launch_gram(p->Ht, p->ldh, p->R, p->Kp, N, p->gramH, gws, st));
+  CNMF_TRY(launch_gram(p->Wall, p->ldw, p->R, p->Kp, G, p->gramW, gws, st));
+  // frozen W "half-step": only the partial sums (cross = <W, H^T X>, sum W) are produced
+  if (l.impl == CNMF_B200_IMPL_SIMT) {
+    CNMF_TRY(launch_gemm_nt(p->Ht, p->ldh, rk, p->Xt, p->ldxt, G, N, Pt, ldpW, st));
+    CNMF_TRY(launch_row_update(Pt, ldpW, p->Wall, p->ldw, p->gramH, zero, G, p->R, p->Kp, p->algo, p->l1_W,
+                               p->l2_W, p->eps, partW, st));
+  } else {
+    CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, p->Ht, p->ldh, p->Wall, p->ldw, p->gramH, zero, p->R,
+                                 p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, tcws, l.total - l.off_tc,
+                                 st));
+  }
+  // sum(H) for the L1 term comes from partH; with l1_H == 0 the zeros written above are enough
+  if (p->l1_H != 0.f) {
+    if (l.impl == CNMF_B200_IMPL_SIMT) {
+      CNMF_TRY(launch_gemm_nt(p->Wall, p->ldw, rk, p->X, p->ldx, N, G, Pt, ldpH, st));
+      CNMF_TRY(launch_row_update(Pt, ldpH, p->Ht, p->ldh, p->gramW, zero, N, p->R, p->Kp, p->algo, p->l1_H,
+                                 p->l2_H, p->eps, partH, st));
+    } else {
+      CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, p->Wall, p->ldw, p->Ht, p->ldh, p->gramW, zero, p->R,
+                                   p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, tcws,
+                                   l.total - l.off_tc, st));
+    }
+  }
+  return launch_frob_objective(p->normX2, partW, l.nblkW, partH, l.nblkH, p->gramW, p->gramH, p->R, p->Kp,
+                               p->l1_H, p->l2_H, p->l1_W, p->l2_W, p->err2, st);
+}
+
+}  // extern "C"

@@ -1,0 +1,156 @@
+"""Replicate-batched NMF engine (host side).
+
+Holds the count matrix resident on one GPU and runs R replicates of one K at a time through
+libcnmf_b200.so.  Replaces what ``cNMF._nmf`` -> ``run_nmf`` does once per replicate
+(/root/reference/src/cnmf/cnmf.py:805-821): the reference re-densifies, re-casts and
+re-uploads X for every replicate; here X is ingested once and every replicate of a K shares
+each pass over it.
+
+torch is used for device memory, streams and host<->device copies only.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import math
+from dataclasses import dataclass, field
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import FrobProblem, check, lib, ptr
+
+EPS_DEFAULT = 1e-16  # cnmf.py:269
+
+
+def pad4(n: int) -> int:
+    return (int(n) + 3) // 4 * 4
+
+
+def init_random(x_mean: float, n: int, g: int, k: int, seed: int):
+    """'random' init of run_nmf: avg = sqrt(mean(X)/K), |avg * N(0,1)|, H then W, torch CPU
+    generator seeded with ``random_state`` (sklearn _nmf.py:296-309 formula; the seed is the
+    ledger's nmf_seed, cnmf.py:885)."""
+    gen = torch.Generator(device="cpu")
+    gen.manual_seed(int(seed))
+    avg = math.sqrt(float(x_mean) / k)
+    h = torch.randn((n, k), generator=gen, dtype=torch.float32).mul_(avg).abs_()
+    w = torch.randn((k, g), generator=gen, dtype=torch.float32).mul_(avg).abs_()
+    return h, w
+
+
+@dataclass
+class BatchResult:
+    W: np.ndarray                  # [R, K, G] spectra
+    H: np.ndarray | None           # [R, N, K] usages (None unless requested)
+    err: np.ndarray                # [R] sqrt(2 * objective)  (run_nmf's third return value)
+    n_iter: np.ndarray             # [R] iterations (batch) or passes (online) run
+    trace: list = field(default_factory=list)   # [(iteration, loss[R] float64)]
+    launches: int = 0              # kernels enqueued by libcnmf_b200 for this batch
+
+
+class DenseFrobeniusEngine:
+    """X resident as dense fp32 [N x G] and its transpose [G x N]; Frobenius MU / HALS."""
+
+    def __init__(self, X, device="cuda:0"):
+        self.lib = lib()  # raises if the CUDA library is missing -- no fallback
+        if not torch.cuda.is_available():
+            raise _lib.Cnmfb200Error("CUDA device required: cnmf_torch_b200 has no CPU path")
+        self.device = torch.device(device)
+        torch.cuda.set_device(self.device)
+        if hasattr(X, "toarray"):
+            X = X.toarray()
+        xh = torch.as_tensor(np.ascontiguousarray(X)) if not torch.is_tensor(X) else X
+        self.N, self.G = int(xh.shape[0]), int(xh.shape[1])
+        self.ldx, self.ldxt = pad4(self.G), pad4(self.N)
+        xd = xh.to(self.device, dtype=torch.float32, non_blocking=True)
+        self.X = torch.zeros((self.N, self.ldx), device=self.device, dtype=torch.float32)
+        self.X[:, :self.G] = xd
+        self.Xt = torch.zeros((self.G, self.ldxt), device=self.device, dtype=torch.float32)
+        self.Xt[:, :self.N] = xd.t()
+        del xd
+        ws = torch.empty(self.lib.cnmf_b200_sumsq_workspace_bytes(), device=self.device, dtype=torch.uint8)
+        out = torch.zeros(2, device=self.device, dtype=torch.float64)
+        st = torch.cuda.current_stream().cuda_stream
+        check(self.lib.cnmf_b200_sumsq(ptr(self.X), self.N, self.G, self.ldx, ptr(out), ptr(ws), st), "sumsq")
+        self.normX2 = float(out[0].item())
+        # mean(X) for the random init, fp64 on device
+        self.x_mean = float(self.X[:, :self.G].sum(dtype=torch.float64).item()) / (self.N * self.G)
+
+    # ------------------------------------------------------------------------------------
+    def make_init(self, K: int, seeds):
+        hs, ws = [], []
+        for s in seeds:
+            h, w = init_random(self.x_mean, self.N, self.G, K, int(s))
+            hs.append(h)
+            ws.append(w)
+        return torch.stack(hs), torch.stack(ws)
+
+    def _upload_state(self, H0, W0, K, Kp):
+        R = int(W0.shape[0])
+        H0 = torch.as_tensor(H0, dtype=torch.float32)
+        W0 = torch.as_tensor(W0, dtype=torch.float32)
+        ldw, ldh = pad4(self.G), pad4(self.N)
+        Wall = torch.zeros((R, Kp, ldw), device=self.device, dtype=torch.float32)
+        Ht = torch.zeros((R, Kp, ldh), device=self.device, dtype=torch.float32)
+        Wall[:, :K, :self.G] = W0.to(self.device, non_blocking=True)
+        Ht[:, :K, :self.N] = H0.to(self.device, non_blocking=True).permute(0, 2, 1)
+        return Wall, Ht, ldw, ldh
+
+    def factorize(self, K: int, seeds=None, H0=None, W0=None, algo="mu", tol=1e-4, max_iter=500,
+                  l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT, check_every=10,
+                  impl=_lib.IMPL_AUTO, return_H=False) -> BatchResult:
+        """Batch-mode Frobenius NMF of R replicates (R = len(seeds) or W0.shape[0]).
+        Convergence per replicate as run_nmf: every ``check_every`` iterations,
+        stop when prev <= cur or |prev - cur| / init < tol; converged replicates are frozen."""
+        if H0 is None or W0 is None:
+            H0, W0 = self.make_init(K, seeds)
+        R = int(W0.shape[0])
+        Kp = pad4(K)
+        if Kp > _lib.MAX_KP:
+            raise ValueError(f"n_components={K} exceeds the engine limit {_lib.MAX_KP}")
+        algo_id = {"mu": _lib.ALGO_MU, "hals": _lib.ALGO_HALS}[algo]
+        Wall, Ht, ldw, ldh = self._upload_state(H0, W0, K, Kp)
+        dev = self.device
+        gramW = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
+        gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
+        active = torch.ones(R, device=dev, dtype=torch.uint8)
+        err2 = torch.zeros(R, device=dev, dtype=torch.float64)
+        p = FrobProblem(
+            n_cells=self.N, n_genes=self.G, X=ptr(self.X), ldx=self.ldx, Xt=ptr(self.Xt), ldxt=self.ldxt,
+            R=R, K=K, Kp=Kp, algo=algo_id, impl=impl, Wall=ptr(Wall), ldw=ldw, Ht=ptr(Ht), ldh=ldh,
+            gramW=ptr(gramW), gramH=ptr(gramH), active=ptr(active), l1_H=l1_H, l2_H=l2_H, l1_W=l1_W,
+            l2_W=l2_W, eps=eps, normX2=self.normX2, err2=ptr(err2))
+        nbytes = check(self.lib.cnmf_b200_frob_workspace_bytes(C.byref(p)), "frob_workspace_bytes")
+        ws = torch.empty(max(int(nbytes), 256), device=dev, dtype=torch.uint8)
+        p.workspace, p.workspace_bytes = ptr(ws), ws.numel()
+        st = torch.cuda.current_stream().cuda_stream
+        launches = 0
+
+        check(self.lib.cnmf_b200_frob_objective(C.byref(p), st), "frob_objective")
+        launches += self.lib.cnmf_b200_last_launch_count()
+        init = 0.5 * err2.cpu().numpy()
+        prev = init.copy()
+        trace = [(0, init.copy())]
+        n_iter = np.full(R, max_iter, dtype=np.int64)
+        alive = np.ones(R, dtype=bool)
+        it = 0
+        while it < max_iter and alive.any():
+            step = min(check_every, max_iter - it)
+            check(self.lib.cnmf_b200_frob_iterate(C.byref(p), step, st), "frob_iterate")
+            launches += self.lib.cnmf_b200_last_launch_count()
+            it += step
+            cur = 0.5 * err2.cpu().numpy()  # one small D2H per check period
+            trace.append((it, cur.copy()))
+            if it % check_every == 0:
+                conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
+                if conv.any():
+                    n_iter[conv] = it
+                    alive &= ~conv
+                    active.copy_(torch.from_numpy(alive.astype(np.uint8)), non_blocking=False)
+                prev = np.where(alive, cur, prev)
+        final = 0.5 * err2.cpu().numpy() if it > 0 else init
+        W = Wall[:, :K, :self.G].contiguous().cpu().numpy()
+        H = Ht[:, :K, :self.N].permute(0, 2, 1).contiguous().cpu().numpy() if return_H else None
+        return BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * final, 0.0)), n_iter=n_iter,
+                           trace=trace, launches=int(launches))

@@ -1,0 +1,139 @@
+/*
+ * cnmf_b200.h -- C ABI of libcnmf_b200.so: the B200 (sm_100a) kernels behind cNMF's
+ * factorize + consensus hot path.
+ *
+ * The reference (aron0093/cNMF_torch) is pure Python; its "FFI" for this path is the single
+ * Python call  run_nmf(X, **kwargs) -> (H, W, err)   at src/cnmf/cnmf.py:819 (external package
+ * nmf-torch) and the sklearn/numpy calls at src/cnmf/cnmf.py:1056-1090.  Each entry point
+ * below names the reference line(s) whose arithmetic it replaces.  The Python host layer
+ * (cnmf_torch_b200/) binds these with ctypes; INTEGRATION.md shows the reference-side stub.
+ *
+ * Conventions
+ *   - every pointer is a DEVICE pointer unless the name ends in _host; the caller owns all
+ *     memory; nothing here allocates (workspaces are sized by the *_workspace_bytes queries);
+ *   - `stream` is a cudaStream_t passed as void*; all work is asynchronous on that stream;
+ *   - return value: 0 on success, negative error code otherwise; cnmf_b200_last_error()
+ *     gives a thread-local message.  No C++ exceptions cross the boundary;
+ *   - matrices are row-major with an explicit leading dimension (elements); all leading
+ *     dimensions must be multiples of 4 and base pointers 16-byte aligned;
+ *   - orientation (nmf-torch naming, cnmf.py:758): X (N x G) ~= H (N x K) * W (K x G).
+ *     R replicates of one K are stacked: rows r*Kp .. r*Kp+K-1 of a [R*Kp x L] array belong
+ *     to replicate r (Kp = K rounded up to a multiple of 4, padding rows are zero):
+ *         W  stacked as  Wall [R*Kp x G]      (spectra, gene index contiguous)
+ *         H  stacked as  Ht   [R*Kp x N]      (usages TRANSPOSED, cell index contiguous)
+ */
+#ifndef CNMF_B200_H_
+#define CNMF_B200_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CNMF_B200_ABI_VERSION 1
+
+#define CNMF_B200_OK 0
+#define CNMF_B200_ERR_INVALID (-1)   /* bad argument (shape, alignment, enum)           */
+#define CNMF_B200_ERR_CUDA (-2)      /* a CUDA runtime/driver call failed                */
+#define CNMF_B200_ERR_WORKSPACE (-3) /* workspace too small                              */
+#define CNMF_B200_ERR_UNSUPPORTED (-4)
+
+#define CNMF_B200_ALGO_MU 0
+#define CNMF_B200_ALGO_HALS 1
+
+#define CNMF_B200_IMPL_AUTO 0
+#define CNMF_B200_IMPL_SIMT 1    /* fp32 CUDA-core GEMM + separate row update (semantic baseline) */
+#define CNMF_B200_IMPL_TCGEN05 2 /* TMA + tcgen05 TF32 GEMM, update fused in the TMEM epilogue     */
+
+#define CNMF_B200_MAX_KP 32
+
+int cnmf_b200_abi_version(void);
+const char* cnmf_b200_last_error(void);
+
+/* ------------------------------------------------------------------------------------------
+ * Dense Frobenius engine (replicate-batched).  Replaces the arithmetic of run_nmf(beta_loss=
+ * 'frobenius', algo in {'mu','hals'}) called at cnmf.py:819 for R replicates at once.
+ * ---------------------------------------------------------------------------------------- */
+
+/* out[0] = sum of squares of x (rows x cols, ld) accumulated in fp64.  ||X||_F^2 is the
+ * constant term of the Frobenius objective (sklearn _nmf.py:113-117 restated by trace identity).
+ * workspace: cnmf_b200_sumsq_workspace_bytes() bytes. */
+int64_t cnmf_b200_sumsq_workspace_bytes(void);
+int cnmf_b200_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld, double* out,
+                    void* workspace, void* stream);
+
+/* gram[r] = F_r F_r^T  (Kp x Kp, row-major) for every replicate block F_r = F[r*Kp : (r+1)*Kp, 0:L].
+ * Replaces  W @ W.T  /  H.T @ H  (pattern in-repo at cnmf.py:346). Deterministic two-stage sum. */
+int64_t cnmf_b200_gram_workspace_bytes(int32_t R, int32_t Kp, int64_t L);
+int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
+                   void* workspace, void* stream);
+
+/* C[M x N] = A[M x Kd] * B[N x Kd]^T, fp32 FFMA (CUDA cores).  Replaces  x @ W.T / H.T @ x
+ * (cnmf.py:355) in the SIMT baseline. */
+int cnmf_b200_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, int64_t ldb,
+                      int64_t N, int64_t Kd, float* C, int64_t ldc, void* stream);
+
+/* Row update of one stacked factor given Pt = F * A^T  ([R*Kp x M], ld = ldp):
+ *   MU   (cnmf.py:358-372):  s <- s * max(p - l1, 0) / (s.Gram + l2*s), rate = 0 where denom < eps
+ *   HALS (sklearn _cdnmf_fast.pyx restated): s_k <- max(0, s_k + (p_k - l1 - s.Gram_:k)/(Gram_kk + l2))
+ * for every column m < M and every replicate r with active[r] != 0 (active may be NULL = all).
+ * partials ([nblk x R x 2] doubles, nblk = cnmf_b200_row_update_blocks(M)) receives per-block
+ * sums of (new_s * p) and (new_s) for the objective. */
+int64_t cnmf_b200_row_update_blocks(int64_t M);
+int cnmf_b200_row_update(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
+                         const uint8_t* active, int64_t M, int32_t R, int32_t Kp, int32_t algo,
+                         float l1, float l2, float eps, double* partials, void* stream);
+
+typedef struct cnmf_b200_frob_problem {
+  int64_t n_cells;   /* N */
+  int64_t n_genes;   /* G */
+  const float* X;    /* [N x G]  */
+  int64_t ldx;
+  const float* Xt;   /* [G x N]  (X transposed, resident; X is static across replicates) */
+  int64_t ldxt;
+  int32_t R;         /* replicates in this batch */
+  int32_t K;         /* n_components */
+  int32_t Kp;        /* K rounded up to a multiple of 4 (<= CNMF_B200_MAX_KP) */
+  int32_t algo;      /* CNMF_B200_ALGO_* */
+  int32_t impl;      /* CNMF_B200_IMPL_* */
+  int32_t reserved;
+  float* Wall;       /* [R*Kp x G], updated in place */
+  int64_t ldw;
+  float* Ht;         /* [R*Kp x N], updated in place */
+  int64_t ldh;
+  float* gramW;      /* [R x Kp x Kp]  W_r W_r^T, must be current on entry, current on exit */
+  float* gramH;      /* [R x Kp x Kp]  H_r^T H_r, written */
+  const uint8_t* active; /* [R] 1 = update, 0 = frozen; NULL = all active */
+  float l1_H, l2_H, l1_W, l2_W;
+  float eps;         /* denominators below eps give a zero rate (cnmf.py:269, 370-371) */
+  float pad0;
+  double normX2;     /* ||X||_F^2 */
+  double* err2;      /* [R] out: 2 * objective = ||X - H W||_F^2 + regularisation (may be NULL) */
+  void* workspace;
+  int64_t workspace_bytes;
+} cnmf_b200_frob_problem;
+
+/* Bytes of workspace cnmf_b200_frob_iterate needs for this problem (only shapes/impl are read). */
+int64_t cnmf_b200_frob_workspace_bytes(const cnmf_b200_frob_problem* p);
+
+/* gramW <- Gram(Wall) (call once after initialising Wall, before the first iterate). */
+int cnmf_b200_frob_prepare(const cnmf_b200_frob_problem* p, void* stream);
+
+/* n_iters x { H half-step; gramH; W half-step; gramW }, then (if err2 != NULL) the objective of
+ * the final state via  ||X||^2 - 2 tr(W X^T H) + tr(WW^T H^T H)  (+ regularisation), combined in
+ * fp64.  One call enqueues everything; nothing synchronises.  Replaces the batch loop of
+ * run_nmf (cnmf.py:819) for R replicates. */
+int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, void* stream);
+
+/* err2[r] = objective (x2) of the CURRENT state; the factors are not modified (gramW/gramH are
+ * refreshed).  Gives the initial error that normalises run_nmf's convergence test. */
+int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream);
+
+/* Number of kernel launches the last cnmf_b200_frob_iterate on this thread enqueued. */
+int64_t cnmf_b200_last_launch_count(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* CNMF_B200_H_ */
