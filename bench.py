@@ -1,0 +1,295 @@
+"""bench.py -- NMF replicate-iterations/s of the cNMF factorize hot path on B200.
+
+Workload at every N: BASELINE.json configs[1] ("PBMC-3k shape 2.7k x 2k HVG, K=7-12, 100 replicates,
+frobenius HALS"), synthetic negative-binomial counts, variance-scaled as the reference does
+(SURVEY.md 8d).  One STEP = one convergence-check period of run_nmf's batch loop -- 10 iterations
+(H update + W update each) plus the objective -- for all 100 replicates of every K in 7..12, i.e.
+6000 replicate-iterations per GPU per step.  With N GPUs every rank runs the whole workload on its own
+replicate seeds (replicates are independent units; no data-path collective) => weak scaling.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+N_CELLS, N_GENES = 2700, 2000
+KS = list(range(7, 13))
+REPLICATES = 100
+ITERS_PER_STEP = 10
+ALGO = "hals"
+E2E_ITERS = 100  # iterations per replicate in one end-to-end public-API call
+METRIC = "nmf_replicate_iterations_per_second"
+UNIT = "replicate-iters/s"
+WORKLOAD = ("cfg2: 2700x2000 NB counts (variance-scaled), K=7..12 x 100 replicates, frobenius HALS, "
+            "batch mode, 10 iterations + objective per step")
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
+    except Exception:
+        return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock / throttle reasons of one GPU with nvidia-smi while the timed region runs."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        super().__init__(daemon=True)
+        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+
+    def run(self):
+        while not self._stop_evt.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
+                                     timeout=5).stdout.strip()
+                if out:
+                    self.rows.append([c.strip() for c in out.split(",")])
+            except Exception:
+                pass
+            self._stop_evt.wait(0.2)
+
+    def stop(self):
+        self._stop_evt.set()
+        self.join(timeout=6)
+        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({n for r in self.rows for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+def _cpu_baseline(x, seconds_target=15.0):
+    """The oracle port of run_nmf (torch CPU, all host threads) on a bounded sample of the same
+    workload: K=10, HALS, a few replicates x 10 iterations, repeated until ~seconds_target."""
+    import torch
+    from oracle import nmf_oracle as no
+    cores = torch.get_num_threads()
+    k = 10
+    done, t0, reps = 0, time.perf_counter(), 0
+    while True:
+        h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), x.shape[0], x.shape[1], k, 1000 + reps)
+        no.nmf_batch(x, h0, w0, algo=ALGO, tol=0.0, max_iter=ITERS_PER_STEP)
+        done += ITERS_PER_STEP
+        reps += 1
+        el = time.perf_counter() - t0
+        if el > seconds_target or reps >= 200:
+            break
+    return {"value": done / el, "unit": UNIT, "cores": int(cores), "kind": "port",
+            "sample": f"{reps} replicates x {ITERS_PER_STEP} HALS iterations + objective, K={k}, same X, "
+                      f"{el:.1f}s of torch-CPU work (oracle/nmf_oracle.py; nmf-torch itself is not installable here)"}
+
+
+def run_reference(args):
+    """--impl reference: the reference's CPU path for this metric.  nmf-torch is absent from the image
+    (SURVEY.md 0.2), so this times the oracle port with all host threads; rank 0 only."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import torch
+    from cnmf_torch_b200.synth import nb_counts
+    from oracle import nmf_oracle as no
+    x = nb_counts(N_CELLS, N_GENES, seed=14)
+    cores = torch.get_num_threads()
+    # one step = every K, a bounded sample of 1 replicate per K x 10 iterations
+    def step(seed0):
+        n = 0
+        for k in KS:
+            h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), N_CELLS, N_GENES, k, seed0 + k)
+            no.nmf_batch(x, h0, w0, algo=ALGO, tol=0.0, max_iter=ITERS_PER_STEP)
+            n += ITERS_PER_STEP
+        return n
+    for w in range(args.warmup):
+        step(w)
+    t0 = time.perf_counter()
+    total = 0
+    for s in range(args.steps):
+        total += step(100 + s)
+    el = time.perf_counter() - t0
+    val = total / el
+    sample = f"1 replicate per K (K=7..12) x {ITERS_PER_STEP} HALS iterations + objective per step"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / max(1, args.steps),
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "sample": sample},
+        "cpu_baseline": {"value": val, "unit": UNIT, "cores": int(cores), "kind": "port", "sample": sample},
+        "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+    }))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
+    if args.impl == "reference":
+        return run_reference(args)
+
+    import torch
+    import torch.distributed as dist
+    from cnmf_torch_b200 import _lib
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    from cnmf_torch_b200.synth import ledger_seeds, nb_counts
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    lib = _lib.lib()
+    impl = {"auto": _lib.IMPL_AUTO, "simt": _lib.IMPL_SIMT, "tcgen05": _lib.IMPL_TCGEN05}[args.path]
+
+    x = nb_counts(N_CELLS, N_GENES, seed=14)
+    x_pinned = torch.from_numpy(x).pin_memory()
+    seeds_all = ledger_seeds(len(KS) * REPLICATES * world, seed=14).reshape(world, len(KS), REPLICATES)
+    seeds = seeds_all[rank]
+
+    # ---------------- device-resident arm: `value` ------------------------------------------
+    eng = DenseFrobeniusEngine(x_pinned, device=dev, impl=impl)
+    batches = [eng.new_batch(k, seeds=seeds[i], algo=ALGO) for i, k in enumerate(KS)]
+    flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
+
+    def one_step():
+        for b in batches:
+            b.iterate(ITERS_PER_STEP)
+
+    for _ in range(args.warmup):
+        one_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    launches0 = sum(b.launches for b in batches)
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for s in range(args.steps):
+        flush.zero_()  # evict L2 between timed steps (inputs are smaller than L2)
+        ev[s][0].record()
+        one_step()
+        ev[s][1].record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms_total = float(sum(a.elapsed_time(b) for a, b in ev))
+    launches = sum(b.launches for b in batches) - launches0
+    losses = [b.read_loss() for b in batches]
+    assert all(np.isfinite(l).all() for l in losses)
+
+    # ---------------- dominant kernel alone: roofline ----------------------------------------
+    b10 = batches[KS.index(10)]
+    p = b10.p
+    st = torch.cuda.current_stream().cuda_stream
+    n_rep = 50
+    nblk = lib.cnmf_b200_row_update_blocks(eng.N)
+    part = torch.zeros(nblk * b10.R * 2, dtype=torch.float64, device=dev)
+    frozen = torch.zeros(b10.R, dtype=torch.uint8, device=dev)  # time the kernel without changing state
+    Wop = b10.Wall.clone()
+    _lib.check(lib.cnmf_b200_round_tf32(Wop.data_ptr(), Wop.numel(), st))
+
+    def dominant():
+        _lib.check(lib.cnmf_b200_dense_half_step(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, p.Ht,
+                                                 None, p.ldh, p.gramW, frozen.data_ptr(), p.R, p.Kp, p.algo, 0.0,
+                                                 0.0, p.eps, part.data_ptr(), st))
+    roof = None
+    if impl != _lib.IMPL_SIMT:
+        for _ in range(5):
+            dominant()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n_rep):
+            dominant()
+        e1.record()
+        torch.cuda.synchronize()
+        k_ms = e0.elapsed_time(e1) / n_rep
+        flops = 2.0 * eng.N * eng.G * b10.R * b10.K      # algorithmic (unpadded K), SURVEY 8d: 2*N*G*K*R per half-step
+        peaks, src = _peaks()
+        peak = peaks["bf16_tflops"] / 2.0                # tf32 tensor rate = half the bf16 rate
+        ach = flops / (k_ms * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                "traffic": None, "kernel": "tc_half_step_kernel<12,HALS> (H half-step, K=10, R=100)",
+                "kernel_ms": k_ms, "peak_source": f"{src} bf16 burst / 2 (tf32)"}
+
+    # ---------------- end-to-end arm: public API with host buffers -----------------------------
+    def e2e_step():
+        e = DenseFrobeniusEngine(x_pinned, device=dev, impl=impl)         # H2D of X (pinned)
+        out, h2d, d2h = [], x_pinned.numel() * 4, 0
+        for i, k in enumerate(KS):
+            r = e.factorize(k, seeds=seeds[i], algo=ALGO, tol=0.0, max_iter=E2E_ITERS)  # init H2D, W D2H
+            h2d += REPLICATES * k * (N_CELLS + N_GENES) * 4
+            d2h += r.W.nbytes + (E2E_ITERS // 10 + 1) * REPLICATES * 8
+            out.append(r.err)
+        return h2d, d2h
+    e2e_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    n_e2e = 2
+    for _ in range(n_e2e):
+        h2d, d2h = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = (time.perf_counter() - t0) / n_e2e
+
+    # ---------------- reduce over ranks ------------------------------------------------------
+    if world > 1:
+        t = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms_total, e2e_s = float(t[0]), float(t[1])
+        ln = torch.tensor([launches], dtype=torch.int64, device=dev)
+        dist.all_reduce(ln)
+        launches = int(ln[0])
+    units_per_step = len(KS) * REPLICATES * ITERS_PER_STEP * world
+    value = units_per_step * args.steps / (ms_total * 1e-3)
+    e2e_val = len(KS) * REPLICATES * E2E_ITERS * world / e2e_s
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "tf32" if impl != _lib.IMPL_SIMT else "f32",
+            "data": "synthetic",
+            "config": {"workload": WORKLOAD, "replicates_per_gpu": len(KS) * REPLICATES,
+                       "l2_flush_between_steps": True, "path": args.path,
+                       "e2e_step": f"DenseFrobeniusEngine(X_pinned) + factorize(K, seeds, hals, tol=0, "
+                                   f"max_iter={E2E_ITERS}) for K=7..12 (host init, H2D, D2H of spectra)"},
+            "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            line["cpu_baseline"] = _cpu_baseline(x)
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

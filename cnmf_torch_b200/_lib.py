@@ -60,6 +60,9 @@ SIGNATURES = {
     "cnmf_b200_gemm_nt": (i32, [vp, i64, i64, vp, i64, i64, i64, vp, i64, vp]),
     "cnmf_b200_row_update_blocks": (i64, [i64]),
     "cnmf_b200_row_update": (i32, [vp, i64, vp, i64, vp, vp, i64, i32, i32, i32, f32, f32, f32, vp, vp]),
+    "cnmf_b200_round_tf32": (i32, [vp, i64, vp]),
+    "cnmf_b200_dense_half_step": (i32, [vp, i64, i64, i64, vp, i64, vp, vp, i64, vp, vp, i32, i32, i32, f32, f32,
+                                        f32, vp, vp]),
     "cnmf_b200_frob_workspace_bytes": (i64, [C.POINTER(FrobProblem)]),
     "cnmf_b200_frob_prepare": (i32, [C.POINTER(FrobProblem), vp]),
     "cnmf_b200_frob_iterate": (i32, [C.POINTER(FrobProblem), i32, vp]),

@@ -1,12 +1,516 @@
-// tcgen05 / TMA path for the dense half-step (placeholder until the kernel lands).
+// Dense half-step on the 5th-gen tensor cores: TMA (SWIZZLE_128B) -> shared memory ->
+// tcgen05.mma kind::tf32 (fp32 accumulate in TMEM) -> fused row update in the epilogue.
+//
+//   D[128 rows of A  x  BN = t*KP columns]  =  A_tile[128 x Kd] * F_tile[BN x Kd]^T
+//
+// A is X (H half-step) or X^T (W half-step); F is the stacked fixed factor ([R*KP x Kd], K-major);
+// the epilogue thread that owns TMEM lane i owns row i of the tile: it reads its KP accumulator
+// columns per replicate with tcgen05.ld, applies the MU / HALS row update (common.cuh, same code
+// as the SIMT baseline) against the replicate's Gram in shared memory and writes the state
+// [R*KP x M] (coalesced across the warp).  P = A F^T is never materialised.
+//
+// Warp roles (256 threads, 1 CTA / SM, persistent over tiles):
+//   warp 0 lane 0 : TMA producer          warp 1 lane 0 : MMA issuer
+//   warp 2        : TMEM alloc / dealloc  warps 4..7    : epilogue (TMEM lane quarter = warp % 4)
+// Pipelines: smem full/empty ring (TMA <-> MMA), TMEM full/empty double buffer (MMA <-> epilogue).
+//
+// Replaces x @ W.T / H.T @ x and the update that follows (pattern in the reference at
+// /root/reference/src/cnmf/cnmf.py:355-372) for all R replicates of one K in one pass over X.
+#include <cuda.h>
+#include <cudaTypedefs.h>
+
+#include <mutex>
+#include <vector>
+
 #include "common.cuh"
+
 namespace cnmf {
-bool tc_supported(int64_t, int64_t, int, int) { return false; }
-int64_t tc_workspace_bytes(int64_t, int64_t, int, int) { return 0; }
-int launch_tc_half_step(const float*, int64_t, int64_t, int64_t, const float*, int64_t, float*, int64_t,
-                        const float*, const uint8_t*, int, int, int, float, float, float, double*, void*,
-                        int64_t, cudaStream_t) {
-  set_error("tcgen05 path not built");
-  return CNMF_B200_ERR_UNSUPPORTED;
+
+constexpr int TC_BM = 128;
+constexpr int TC_BK = 32;  // floats per k-block: 128 bytes = one swizzle-128B row
+constexpr int TC_THREADS = 256;
+constexpr int TC_MAX_BN = 256;
+constexpr int TC_TMEM_COLS = 512;
+constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;  // 16 KiB
+constexpr int TC_SMEM_LIMIT = 227 * 1024;
+constexpr int TC_MAX_STAGES = 6;
+
+struct TcParams {
+  int64_t M;       // rows of A (and columns of the state array)
+  int64_t Kd;      // contraction length
+  float* state;    // [R*KP x lds] fp32 master
+  float* state_op; // same layout, tf32-rounded copy that the NEXT half-step's MMA reads (may be null)
+  int64_t lds;
+  const float* gram;      // [R x KP x KP]
+  const uint8_t* active;  // [R] or null
+  double* partials;       // [num_m_tiles x R x 2]
+  int R;
+  int t;  // replicates per tile
+  int num_m_tiles, num_n_tiles, stages;
+  float l1, l2, eps;
+};
+
+// ---------------------------------------------------------------------------------------------
+// PTX wrappers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
 }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(ok)
+      : "r"(smem_u32(bar)), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+// Bounded wait: a protocol bug traps (kernel aborts with an error) instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if (++spins > (1u << 28)) __trap();
+  }
+}
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld4(uint32_t taddr, float& a, float& b, float& c, float& d) {
+  uint32_t r0, r1, r2, r3;
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x4.b32 {%0, %1, %2, %3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3)
+               : "r"(taddr));
+  a = __uint_as_float(r0); b = __uint_as_float(r1); c = __uint_as_float(r2); d = __uint_as_float(r3);
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+__device__ __forceinline__ float to_tf32(float v) {  // round to nearest, ties away (cvt.rna)
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
+}
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
+// K-major operand tile, rows at 128-byte pitch, SWIZZLE_128B: SBO = 8 rows * 128 B, LBO unused,
+// descriptor version 1 (sm_100), layout type 2.
+__device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((smem_addr & 0x3FFFFu) >> 4);
+  d |= static_cast<uint64_t>(1024u >> 4) << 32;
+  d |= static_cast<uint64_t>(1) << 46;
+  d |= static_cast<uint64_t>(2) << 61;
+  return d;
+}
+
+// ---------------------------------------------------------------------------------------------
+// kernel
+// ---------------------------------------------------------------------------------------------
+template <int KP, int ALGO>
+__global__ void __launch_bounds__(TC_THREADS, 1)
+tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                    const TcParams prm) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int t = prm.t;
+  const int BN = t * KP;
+  const uint32_t b_bytes = static_cast<uint32_t>(BN) * TC_BK * 4;
+  const uint32_t stage_bytes = TC_A_BYTES + b_bytes;
+  const int stages = prm.stages;
+
+  float* sgram = reinterpret_cast<float*>(smem + static_cast<size_t>(stages) * stage_bytes);
+  float* sred = sgram + t * KP * KP;                       // [4 warps][t][2]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sred + 4 * t * 2);  // 8-byte aligned: all counts even
+  uint64_t* full = bars;
+  uint64_t* empty = bars + stages;
+  uint64_t* tfull = empty + stages;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int i = 0; i < stages; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&empty[i], 1);
+    }
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(&tfull[b], 1);
+      mbar_init(&tempty[b], 4);  // one arrival per epilogue warp
+    }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                 "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int num_tiles = prm.num_m_tiles * prm.num_n_tiles;
+  const int num_kb = static_cast<int>((prm.Kd + TC_BK - 1) / TC_BK);
+
+  if (warp == 0) {
+    if (lane == 0) {
+      // ===================== TMA producer =====================
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m_tile = tile / prm.num_n_tiles, n_tile = tile - m_tile * prm.num_n_tiles;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1u);
+          uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
+          mbar_expect_tx(&full[stage], stage_bytes);
+          tma_load_2d(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
+          tma_load_2d(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK, n_tile * BN);
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      // ===================== MMA issuer =====================
+      // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=tf32 (2 at bits 7-9 / 10-12), K-major both,
+      // N>>3 at bits 17-22, M>>4 at bits 24-28
+      const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
+                             (static_cast<uint32_t>(TC_BM >> 4) << 24);
+      int stage = 0;
+      uint32_t phase = 0;
+      int lt = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+        const int buf = lt & 1;
+        const uint32_t tphase = (lt >> 1) & 1u;
+        mbar_wait(&tempty[buf], tphase ^ 1u);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * TC_MAX_BN);
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t sa = smem_u32(smem + static_cast<size_t>(stage) * stage_bytes);
+          const uint64_t a_desc = make_kmajor_sw128_desc(sa);
+          const uint64_t b_desc = make_kmajor_sw128_desc(sa + TC_A_BYTES);
+#pragma unroll
+          for (int k = 0; k < TC_BK / 8; ++k) {
+            // advance 8 tf32 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
+            tc_mma_tf32(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc,
+                        (kb | k) != 0 ? 1u : 0u);
+          }
+          tc_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
+          if (++stage == stages) { stage = 0; phase ^= 1u; }
+        }
+        tc_commit(&tfull[buf]);  // accumulator complete -> epilogue
+      }
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue =====================
+    const int q = warp - 4;  // TMEM lane quarter == warp % 4
+    const int et = threadIdx.x - 128;
+    int lt = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      const int buf = lt & 1;
+      const uint32_t tphase = (lt >> 1) & 1u;
+      const int m_tile = tile / prm.num_n_tiles, n_tile = tile - m_tile * prm.num_n_tiles;
+      const int r0 = n_tile * t;
+      for (int i = et; i < t * KP * KP; i += 128) {
+        const int rr = i / (KP * KP);
+        sgram[i] = (r0 + rr < prm.R) ? prm.gram[static_cast<int64_t>(r0) * KP * KP + i] : 0.f;
+      }
+      epi_bar_sync();
+      mbar_wait(&tfull[buf], tphase);
+      tc_fence_after();
+      const int64_t m = static_cast<int64_t>(m_tile) * TC_BM + q * 32 + lane;
+      const bool in = m < prm.M;
+      const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * TC_MAX_BN);
+      for (int rr = 0; rr < t; ++rr) {
+        const int r = r0 + rr;
+        if (r >= prm.R) break;
+        float p[KP], s[KP];
+#pragma unroll
+        for (int c = 0; c < KP; c += 4)
+          tmem_ld4(taddr + static_cast<uint32_t>(rr * KP + c), p[c], p[c + 1], p[c + 2], p[c + 3]);
+        const int64_t soff = static_cast<int64_t>(r) * KP * prm.lds + m;
+        float* sp = prm.state + soff;
+#pragma unroll
+        for (int k = 0; k < KP; ++k) s[k] = in ? sp[static_cast<int64_t>(k) * prm.lds] : 0.f;
+        tmem_ld_wait();
+        const bool act = prm.active == nullptr || prm.active[r] != 0;
+        float cross = 0.f, ssum = 0.f;
+        if (in) {
+          if (act) {
+            update_row<KP, ALGO>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps);
+#pragma unroll
+            for (int k = 0; k < KP; ++k) sp[static_cast<int64_t>(k) * prm.lds] = s[k];
+            if (prm.state_op != nullptr) {
+              float* op = prm.state_op + soff;
+#pragma unroll
+              for (int k = 0; k < KP; ++k) op[static_cast<int64_t>(k) * prm.lds] = to_tf32(s[k]);
+            }
+          }
+#pragma unroll
+          for (int k = 0; k < KP; ++k) {
+            cross = fmaf(s[k], p[k], cross);
+            ssum += s[k];
+          }
+        }
+        cross = warp_sum(cross);
+        ssum = warp_sum(ssum);
+        if (lane == 0) {
+          sred[(q * t + rr) * 2 + 0] = cross;
+          sred[(q * t + rr) * 2 + 1] = ssum;
+        }
+      }
+      // all tcgen05.ld of this buffer are complete: hand it back to the MMA warp
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[buf]);
+      epi_bar_sync();
+      for (int i = et; i < t * 2; i += 128) {
+        const int rr = i >> 1, r = r0 + rr;
+        if (r < prm.R) {
+          double v = 0.0;
+#pragma unroll
+          for (int w = 0; w < 4; ++w) v += static_cast<double>(sred[(w * t + rr) * 2 + (i & 1)]);
+          prm.partials[(static_cast<int64_t>(m_tile) * prm.R + r) * 2 + (i & 1)] = v;
+        }
+      }
+      epi_bar_sync();  // sgram / sred are rewritten by the next tile
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                 "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
+  }
+}
+
+__global__ void round_tf32_kernel(float* __restrict__ dst, const float* __restrict__ src, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = to_tf32(src[i]);
+}
+
+int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st) {
+  if (n == 0) return 0;
+  int64_t blocks = ceil_div(n, 256 * 8);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  round_tf32_kernel<<<(unsigned)blocks, 256, 0, st>>>(dst, src, n);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------
+struct TcPlan {
+  int t, BN, stages, num_m_tiles, num_n_tiles;
+  size_t smem_bytes;
+};
+
+static size_t tc_smem_bytes(int t, int Kp, int stages) {
+  const size_t stage = TC_A_BYTES + static_cast<size_t>(t) * Kp * TC_BK * 4;
+  size_t extra = static_cast<size_t>(t) * Kp * Kp * 4 + 4 * static_cast<size_t>(t) * 2 * 4;
+  extra += (2 * TC_MAX_STAGES + 4) * 8 + 16;
+  return stages * stage + extra + 1024;  // +1024: manual alignment of the dynamic base
+}
+
+static int tc_num_sms() {
+  static int sms = 0;
+  if (sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+      sms = 148;
+  }
+  return sms;
+}
+
+// Pick replicates-per-tile t (BN = t*Kp multiple of 16, <= 256) minimising waves * MMA time + epilogue.
+static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out) {
+  const int num_m = static_cast<int>(ceil_div(M, TC_BM));
+  const int64_t num_kb = ceil_div(Kd, TC_BK);
+  double best = 1e300;
+  bool found = false;
+  for (int t = 1; t * Kp <= TC_MAX_BN; ++t) {
+    const int BN = t * Kp;
+    if (BN % 16 != 0) continue;
+    int stages = TC_MAX_STAGES;
+    while (stages >= 2 && tc_smem_bytes(t, Kp, stages) > static_cast<size_t>(TC_SMEM_LIMIT)) --stages;
+    if (stages < 2) continue;
+    const int num_n = static_cast<int>(ceil_div(R, t));
+    const int64_t tiles = static_cast<int64_t>(num_m) * num_n;
+    const int64_t waves = ceil_div(tiles, sms);
+    const double mma = static_cast<double>(num_kb) * 4.0 * (BN / 2.0 > 40.0 ? BN / 2.0 : 40.0);
+    const double epi = static_cast<double>(t) * (Kp * Kp + 12.0 * Kp) * 1.5 + 1500.0;
+    const double cost = waves * mma + epi + (waves > 1 ? 0.0 : 0.0);
+    if (cost < best) {
+      best = cost;
+      found = true;
+      out->t = t; out->BN = BN; out->stages = stages; out->num_m_tiles = num_m; out->num_n_tiles = num_n;
+      out->smem_bytes = tc_smem_bytes(t, Kp, stages);
+    }
+  }
+  return found;
+}
+
+bool tc_supported(int64_t M, int64_t Kd, int R, int Kp) {
+  TcPlan p;
+  return M > 0 && Kd > 0 && R > 0 && Kp % 4 == 0 && Kp <= CNMF_B200_MAX_KP && M < (1ll << 31) &&
+         Kd < (1ll << 31) && tc_plan(M, Kd, R, Kp, 148, &p);
+}
+
+static PFN_cuTensorMapEncodeTiled_v12000 get_encode_fn() {
+  static PFN_cuTensorMapEncodeTiled_v12000 fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_cuTensorMapEncodeTiled_v12000>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr; int64_t rows, cols, ld; int box_rows;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && ld == o.ld && box_rows == o.box_rows;
+  }
+};
+struct MapEntry { MapKey key; CUtensorMap map; };
+
+// 2-D fp32 tensor [rows x cols] (row pitch ld), box = [TC_BK cols x box_rows rows], 128B swizzle,
+// out-of-bounds elements read as zero.
+static int get_tensor_map(const float* ptr, int64_t rows, int64_t cols, int64_t ld, int box_rows, CUtensorMap* out) {
+  static thread_local std::vector<MapEntry> cache;
+  MapKey key{ptr, rows, cols, ld, box_rows};
+  for (auto& e : cache)
+    if (e.key == key) { *out = e.map; return 0; }
+  auto encode = get_encode_fn();
+  if (!encode) {
+    set_error("cuTensorMapEncodeTiled entry point not available");
+    return CNMF_B200_ERR_CUDA;
+  }
+  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(cols), static_cast<cuuint64_t>(rows)};
+  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(ld) * 4};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(TC_BK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult rc = encode(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(ptr), gdim, gstride, box, estr,
+                       CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                       CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (rc != CUDA_SUCCESS) {
+    set_error("cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld ld=%lld box=%d", (int)rc, (long long)rows,
+              (long long)cols, (long long)ld, box_rows);
+    return CNMF_B200_ERR_CUDA;
+  }
+  if (cache.size() >= 64) cache.erase(cache.begin());
+  cache.push_back({key, *out});
+  return 0;
+}
+
+template <int KP, int ALGO>
+static int launch_tc_inst(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
+                          int grid, cudaStream_t st) {
+  static thread_local size_t configured = 0;
+  auto kern = tc_half_step_kernel<KP, ALGO>;
+  if (plan.smem_bytes > configured) {
+    CNMF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
+    configured = TC_SMEM_LIMIT;
+  }
+  kern<<<grid, TC_THREADS, plan.smem_bytes, st>>>(ma, mb, prm);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                        float* state, float* state_op, int64_t lds, const float* gram, const uint8_t* active, int R,
+                        int Kp, int algo, float l1, float l2, float eps, double* partials, cudaStream_t st) {
+  TcPlan plan;
+  const int sms = tc_num_sms();
+  if (!tc_plan(M, Kd, R, Kp, sms, &plan)) {
+    set_error("tcgen05 path: no tile plan for M=%lld Kd=%lld R=%d Kp=%d", (long long)M, (long long)Kd, R, Kp);
+    return CNMF_B200_ERR_UNSUPPORTED;
+  }
+  CUtensorMap ma, mb;
+  CNMF_TRY(get_tensor_map(A, M, Kd, lda, TC_BM, &ma));
+  CNMF_TRY(get_tensor_map(F, static_cast<int64_t>(R) * Kp, Kd, ldf, plan.BN, &mb));
+  TcParams prm;
+  prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.active = active;
+  prm.partials = partials; prm.R = R; prm.t = plan.t; prm.num_m_tiles = plan.num_m_tiles;
+  prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
+  const int64_t tiles = static_cast<int64_t>(plan.num_m_tiles) * plan.num_n_tiles;
+  const int grid = static_cast<int>(tiles < sms ? tiles : sms);
+  if (algo == CNMF_B200_ALGO_MU) {
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_MU>(ma, mb, prm, plan, grid, st)));
+  } else if (algo == CNMF_B200_ALGO_HALS) {
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_HALS>(ma, mb, prm, plan, grid, st)));
+  }
+  set_error("unknown algo %d", algo);
+  return CNMF_B200_ERR_INVALID;
+}
+
 }  // namespace cnmf
+
+using namespace cnmf;
+
+extern "C" {
+
+int cnmf_b200_round_tf32(float* x, int64_t n, void* stream) {
+  CNMF_CHECK_ARG(x != nullptr && n >= 0, "round_tf32: bad argument");
+  return launch_round_tf32(x, x, n, (cudaStream_t)stream);
+}
+
+int cnmf_b200_dense_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                              float* state, float* state_tf32, int64_t lds, const float* gram,
+                              const uint8_t* active, int32_t R, int32_t Kp, int32_t algo, float l1, float l2,
+                              float eps, double* partials, void* stream) {
+  CNMF_CHECK_ARG(A && F && state && gram && partials, "dense_half_step: null pointer");
+  CNMF_CHECK_ARG(M > 0 && Kd > 0 && R > 0, "dense_half_step: empty shape");
+  CNMF_CHECK_ARG(lda % 4 == 0 && ldf % 4 == 0 && aligned16(A) && aligned16(F),
+                 "dense_half_step: operands need 16-byte aligned rows (ld multiple of 4)");
+  CNMF_CHECK_ARG(lda >= Kd && ldf >= Kd && lds >= M, "dense_half_step: leading dimension too small");
+  return launch_tc_half_step(A, lda, M, Kd, F, ldf, state, state_tf32, lds, gram, active, R, Kp, algo, l1, l2, eps,
+                             partials, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -13,14 +13,14 @@ int launch_frob_objective(double, const double*, int, const double*, int, const 
                           int, float, float, float, float, double*, cudaStream_t);
 // tcgen05 path (dense_tc.cu)
 bool tc_supported(int64_t M, int64_t Kd, int R, int Kp);
-int64_t tc_workspace_bytes(int64_t M, int64_t Kd, int R, int Kp);
 int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
-                        float* state, int64_t lds, const float* gram, const uint8_t* active, int R, int Kp,
-                        int algo, float l1, float l2, float eps, double* partials, void* ws,
-                        int64_t ws_bytes, cudaStream_t st);
+                        float* state, float* state_op, int64_t lds, const float* gram, const uint8_t* active,
+                        int R, int Kp, int algo, float l1, float l2, float eps, double* partials,
+                        cudaStream_t st);
+int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st);
 
 struct FrobLayout {
-  int64_t off_pt, off_gram, off_partH, off_partW, off_zero, off_tc, total;
+  int64_t off_pt, off_gram, off_partH, off_partW, off_zero, off_wop, off_hop, total;
   int nblkH, nblkW;
   int impl;
 };
@@ -53,12 +53,11 @@ static FrobLayout frob_layout(const cnmf_b200_frob_problem* p) {
   off += align_up((int64_t)l.nblkW * p->R * 2 * 8, 256);
   l.off_zero = off;
   off += align_up(p->R, 256);
-  l.off_tc = off;
-  if (l.impl == CNMF_B200_IMPL_TCGEN05) {
-    int64_t a = tc_workspace_bytes(p->n_cells, p->n_genes, p->R, p->Kp);
-    int64_t b = tc_workspace_bytes(p->n_genes, p->n_cells, p->R, p->Kp);
-    off += align_up(a > b ? a : b, 256);
-  }
+  // tcgen05 path: tf32-rounded operand copies of the two stacked factors (same leading dims)
+  l.off_wop = off;
+  if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up(rk * p->ldw * 4, 256);
+  l.off_hop = off;
+  if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up(rk * p->ldh * 4, 256);
   l.total = off;
   return l;
 }
@@ -113,8 +112,13 @@ int cnmf_b200_frob_prepare(const cnmf_b200_frob_problem* p, void* stream) {
     return CNMF_B200_ERR_WORKSPACE;
   }
   char* ws = reinterpret_cast<char*>(p->workspace);
-  return launch_gram(p->Wall, p->ldw, p->R, p->Kp, p->n_genes, p->gramW, ws + l.off_gram,
-                     (cudaStream_t)stream);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (l.impl == CNMF_B200_IMPL_TCGEN05) {
+    const int64_t rk = (int64_t)p->R * p->Kp;
+    CNMF_TRY(launch_round_tf32(reinterpret_cast<float*>(ws + l.off_wop), p->Wall, rk * p->ldw, st));
+    CNMF_TRY(launch_round_tf32(reinterpret_cast<float*>(ws + l.off_hop), p->Ht, rk * p->ldh, st));
+  }
+  return launch_gram(p->Wall, p->ldw, p->R, p->Kp, p->n_genes, p->gramW, ws + l.off_gram, st);
 }
 
 int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, void* stream) {
@@ -134,11 +138,11 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
   void* gws = ws + l.off_gram;
   double* partH = reinterpret_cast<double*>(ws + l.off_partH);
   double* partW = reinterpret_cast<double*>(ws + l.off_partW);
-  void* tcws = ws + l.off_tc;
+  float* Wop = reinterpret_cast<float*>(ws + l.off_wop);
+  float* Hop = reinterpret_cast<float*>(ws + l.off_hop);
   const int64_t N = p->n_cells, G = p->n_genes;
   const int64_t rk = (int64_t)p->R * p->Kp;
   const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
-  const int64_t tc_bytes = l.total - l.off_tc;
 
   for (int it = 0; it < n_iters; ++it) {
     // ---- H half-step: Pt[RKp x N] = Wall X^T ; Ht <- update(Ht; Pt, gramW)
@@ -147,9 +151,8 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
       CNMF_TRY(launch_row_update(Pt, ldpH, p->Ht, p->ldh, p->gramW, p->active, N, p->R, p->Kp, p->algo,
                                  p->l1_H, p->l2_H, p->eps, partH, st));
     } else {
-      CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, p->Wall, p->ldw, p->Ht, p->ldh, p->gramW, p->active,
-                                   p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, tcws, tc_bytes,
-                                   st));
+      CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh, p->gramW, p->active,
+                                   p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, st));
     }
     CNMF_TRY(launch_gram(p->Ht, p->ldh, p->R, p->Kp, N, p->gramH, gws, st));
     // ---- W half-step: Pt[RKp x G] = Ht Xt^T ; Wall <- update(Wall; Pt, gramH)
@@ -158,9 +161,8 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
       CNMF_TRY(launch_row_update(Pt, ldpW, p->Wall, p->ldw, p->gramH, p->active, G, p->R, p->Kp, p->algo,
                                  p->l1_W, p->l2_W, p->eps, partW, st));
     } else {
-      CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, p->Ht, p->ldh, p->Wall, p->ldw, p->gramH,
-                                   p->active, p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, tcws,
-                                   tc_bytes, st));
+      CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, Wop, p->ldw, p->gramH,
+                                   p->active, p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, st));
     }
     CNMF_TRY(launch_gram(p->Wall, p->ldw, p->R, p->Kp, G, p->gramW, gws, st));
   }
@@ -191,7 +193,8 @@ int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
   double* partH = reinterpret_cast<double*>(ws + l.off_partH);
   double* partW = reinterpret_cast<double*>(ws + l.off_partW);
   uint8_t* zero = reinterpret_cast<uint8_t*>(ws + l.off_zero);
-  void* tcws = ws + l.off_tc;
+  float* Wop = reinterpret_cast<float*>(ws + l.off_wop);
+  float* Hop = reinterpret_cast<float*>(ws + l.off_hop);
   const int64_t N = p->n_cells, G = p->n_genes;
   const int64_t rk = (int64_t)p->R * p->Kp;
   const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
@@ -205,9 +208,8 @@ int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
     CNMF_TRY(launch_row_update(Pt, ldpW, p->Wall, p->ldw, p->gramH, zero, G, p->R, p->Kp, p->algo, p->l1_W,
                                p->l2_W, p->eps, partW, st));
   } else {
-    CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, p->Ht, p->ldh, p->Wall, p->ldw, p->gramH, zero, p->R,
-                                 p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, tcws, l.total - l.off_tc,
-                                 st));
+    CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, nullptr, p->ldw, p->gramH, zero,
+                                 p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, st));
   }
   // sum(H) for the L1 term comes from partH; with l1_H == 0 the zeros written above are enough
   if (p->l1_H != 0.f) {
@@ -216,9 +218,8 @@ int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
       CNMF_TRY(launch_row_update(Pt, ldpH, p->Ht, p->ldh, p->gramW, zero, N, p->R, p->Kp, p->algo, p->l1_H,
                                  p->l2_H, p->eps, partH, st));
     } else {
-      CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, p->Wall, p->ldw, p->Ht, p->ldh, p->gramW, zero, p->R,
-                                   p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, tcws,
-                                   l.total - l.off_tc, st));
+      CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, nullptr, p->ldh, p->gramW, zero,
+                                   p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, st));
     }
   }
   return launch_frob_objective(p->normX2, partW, l.nblkW, partH, l.nblkH, p->gramW, p->gramH, p->R, p->Kp,

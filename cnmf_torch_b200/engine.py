@@ -52,8 +52,9 @@ class BatchResult:
 class DenseFrobeniusEngine:
     """X resident as dense fp32 [N x G] and its transpose [G x N]; Frobenius MU / HALS."""
 
-    def __init__(self, X, device="cuda:0"):
+    def __init__(self, X, device="cuda:0", impl=_lib.IMPL_AUTO):
         self.lib = lib()  # raises if the CUDA library is missing -- no fallback
+        self.impl = impl
         if not torch.cuda.is_available():
             raise _lib.Cnmfb200Error("CUDA device required: cnmf_torch_b200 has no CPU path")
         self.device = torch.device(device)
@@ -76,6 +77,11 @@ class DenseFrobeniusEngine:
         self.normX2 = float(out[0].item())
         # mean(X) for the random init, fp64 on device
         self.x_mean = float(self.X[:, :self.G].sum(dtype=torch.float64).item()) / (self.N * self.G)
+        if impl != _lib.IMPL_SIMT:
+            # static operands of the tcgen05 path: round once to tf32 (nearest) so that the tensor
+            # core's mantissa truncation is unbiased; ||X||^2 and mean(X) above come from the fp32 X
+            check(self.lib.cnmf_b200_round_tf32(ptr(self.X), self.X.numel(), st), "round_tf32")
+            check(self.lib.cnmf_b200_round_tf32(ptr(self.Xt), self.Xt.numel(), st), "round_tf32")
 
     # ------------------------------------------------------------------------------------
     def make_init(self, K: int, seeds):
@@ -97,60 +103,99 @@ class DenseFrobeniusEngine:
         Ht[:, :K, :self.N] = H0.to(self.device, non_blocking=True).permute(0, 2, 1)
         return Wall, Ht, ldw, ldh
 
+    def new_batch(self, K: int, seeds=None, H0=None, W0=None, algo="mu", l1_H=0.0, l2_H=0.0, l1_W=0.0,
+                  l2_W=0.0, eps=EPS_DEFAULT) -> "FrobBatch":
+        """Device-resident state of R replicates of one K, ready to iterate."""
+        if H0 is None or W0 is None:
+            H0, W0 = self.make_init(K, seeds)
+        return FrobBatch(self, K, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps)
+
     def factorize(self, K: int, seeds=None, H0=None, W0=None, algo="mu", tol=1e-4, max_iter=500,
                   l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT, check_every=10,
-                  impl=_lib.IMPL_AUTO, return_H=False) -> BatchResult:
+                  return_H=False) -> BatchResult:
         """Batch-mode Frobenius NMF of R replicates (R = len(seeds) or W0.shape[0]).
         Convergence per replicate as run_nmf: every ``check_every`` iterations,
         stop when prev <= cur or |prev - cur| / init < tol; converged replicates are frozen."""
-        if H0 is None or W0 is None:
-            H0, W0 = self.make_init(K, seeds)
-        R = int(W0.shape[0])
-        Kp = pad4(K)
-        if Kp > _lib.MAX_KP:
-            raise ValueError(f"n_components={K} exceeds the engine limit {_lib.MAX_KP}")
-        algo_id = {"mu": _lib.ALGO_MU, "hals": _lib.ALGO_HALS}[algo]
-        Wall, Ht, ldw, ldh = self._upload_state(H0, W0, K, Kp)
-        dev = self.device
-        gramW = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
-        gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
-        active = torch.ones(R, device=dev, dtype=torch.uint8)
-        err2 = torch.zeros(R, device=dev, dtype=torch.float64)
-        p = FrobProblem(
-            n_cells=self.N, n_genes=self.G, X=ptr(self.X), ldx=self.ldx, Xt=ptr(self.Xt), ldxt=self.ldxt,
-            R=R, K=K, Kp=Kp, algo=algo_id, impl=impl, Wall=ptr(Wall), ldw=ldw, Ht=ptr(Ht), ldh=ldh,
-            gramW=ptr(gramW), gramH=ptr(gramH), active=ptr(active), l1_H=l1_H, l2_H=l2_H, l1_W=l1_W,
-            l2_W=l2_W, eps=eps, normX2=self.normX2, err2=ptr(err2))
-        nbytes = check(self.lib.cnmf_b200_frob_workspace_bytes(C.byref(p)), "frob_workspace_bytes")
-        ws = torch.empty(max(int(nbytes), 256), device=dev, dtype=torch.uint8)
-        p.workspace, p.workspace_bytes = ptr(ws), ws.numel()
-        st = torch.cuda.current_stream().cuda_stream
-        launches = 0
-
-        check(self.lib.cnmf_b200_frob_objective(C.byref(p), st), "frob_objective")
-        launches += self.lib.cnmf_b200_last_launch_count()
-        init = 0.5 * err2.cpu().numpy()
+        b = self.new_batch(K, seeds, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps)
+        R = b.R
+        init = b.objective()
         prev = init.copy()
         trace = [(0, init.copy())]
         n_iter = np.full(R, max_iter, dtype=np.int64)
         alive = np.ones(R, dtype=bool)
         it = 0
+        cur = init
         while it < max_iter and alive.any():
             step = min(check_every, max_iter - it)
-            check(self.lib.cnmf_b200_frob_iterate(C.byref(p), step, st), "frob_iterate")
-            launches += self.lib.cnmf_b200_last_launch_count()
+            b.iterate(step)
             it += step
-            cur = 0.5 * err2.cpu().numpy()  # one small D2H per check period
+            cur = b.read_loss()  # one small D2H per check period
             trace.append((it, cur.copy()))
             if it % check_every == 0:
                 conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
                 if conv.any():
                     n_iter[conv] = it
                     alive &= ~conv
-                    active.copy_(torch.from_numpy(alive.astype(np.uint8)), non_blocking=False)
+                    b.set_active(alive)
                 prev = np.where(alive, cur, prev)
-        final = 0.5 * err2.cpu().numpy() if it > 0 else init
-        W = Wall[:, :K, :self.G].contiguous().cpu().numpy()
-        H = Ht[:, :K, :self.N].permute(0, 2, 1).contiguous().cpu().numpy() if return_H else None
-        return BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * final, 0.0)), n_iter=n_iter,
-                           trace=trace, launches=int(launches))
+        W, H = b.results(return_H)
+        return BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_iter,
+                           trace=trace, launches=int(b.launches))
+
+
+class FrobBatch:
+    """R replicates of one K resident on the device (stacked Wall / Ht, Grams, workspace)."""
+
+    def __init__(self, eng: DenseFrobeniusEngine, K, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps):
+        self.eng, self.K = eng, int(K)
+        self.R = int(W0.shape[0])
+        self.Kp = pad4(K)
+        if self.Kp > _lib.MAX_KP:
+            raise ValueError(f"n_components={K} exceeds the engine limit {_lib.MAX_KP}")
+        algo_id = {"mu": _lib.ALGO_MU, "hals": _lib.ALGO_HALS}[algo]
+        dev = eng.device
+        self.Wall, self.Ht, ldw, ldh = eng._upload_state(H0, W0, self.K, self.Kp)
+        R, Kp = self.R, self.Kp
+        self.gramW = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
+        self.gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
+        self.active = torch.ones(R, device=dev, dtype=torch.uint8)
+        self.err2 = torch.zeros(R, device=dev, dtype=torch.float64)
+        self.p = FrobProblem(
+            n_cells=eng.N, n_genes=eng.G, X=ptr(eng.X), ldx=eng.ldx, Xt=ptr(eng.Xt), ldxt=eng.ldxt,
+            R=R, K=self.K, Kp=Kp, algo=algo_id, impl=eng.impl, Wall=ptr(self.Wall), ldw=ldw,
+            Ht=ptr(self.Ht), ldh=ldh, gramW=ptr(self.gramW), gramH=ptr(self.gramH),
+            active=ptr(self.active), l1_H=l1_H, l2_H=l2_H, l1_W=l1_W, l2_W=l2_W, eps=eps,
+            normX2=eng.normX2, err2=ptr(self.err2))
+        nbytes = check(eng.lib.cnmf_b200_frob_workspace_bytes(C.byref(self.p)), "frob_workspace_bytes")
+        self.ws = torch.empty(max(int(nbytes), 256), device=dev, dtype=torch.uint8)
+        self.p.workspace, self.p.workspace_bytes = ptr(self.ws), self.ws.numel()
+        self.launches = 0
+        check(eng.lib.cnmf_b200_frob_prepare(C.byref(self.p), self._stream()), "frob_prepare")
+
+    @staticmethod
+    def _stream():
+        return torch.cuda.current_stream().cuda_stream
+
+    def objective(self) -> np.ndarray:
+        """loss[R] of the current state (factors untouched)."""
+        check(self.eng.lib.cnmf_b200_frob_objective(C.byref(self.p), self._stream()), "frob_objective")
+        self.launches += self.eng.lib.cnmf_b200_last_launch_count()
+        return self.read_loss()
+
+    def iterate(self, n: int) -> None:
+        """Enqueue n iterations (+ objective) on the current stream; asynchronous."""
+        check(self.eng.lib.cnmf_b200_frob_iterate(C.byref(self.p), int(n), self._stream()), "frob_iterate")
+        self.launches += self.eng.lib.cnmf_b200_last_launch_count()
+
+    def read_loss(self) -> np.ndarray:
+        return 0.5 * self.err2.cpu().numpy()
+
+    def set_active(self, alive: np.ndarray) -> None:
+        self.active.copy_(torch.from_numpy(alive.astype(np.uint8)))
+
+    def results(self, return_H=False):
+        eng = self.eng
+        W = self.Wall[:, :self.K, :eng.G].contiguous().cpu().numpy()
+        H = (self.Ht[:, :self.K, :eng.N].permute(0, 2, 1).contiguous().cpu().numpy()
+             if return_H else None)
+        return W, H

@@ -85,6 +85,25 @@ int cnmf_b200_row_update(const float* Pt, int64_t ldp, float* state, int64_t lds
                          const uint8_t* active, int64_t M, int32_t R, int32_t Kp, int32_t algo,
                          float l1, float l2, float eps, double* partials, void* stream);
 
+/* In-place round-to-nearest fp32 -> tf32 (cvt.rna.tf32.f32) of n contiguous floats.  Applied once to
+ * the static operands X and X^T before the tcgen05 path reads them: the tensor core ignores the low
+ * 13 mantissa bits, and rounding first makes that error unbiased.  No reference counterpart (the
+ * reference computes x @ W.T in fp32, cnmf.py:355). */
+int cnmf_b200_round_tf32(float* x, int64_t n, void* stream);
+
+/* Fused half-step on the tensor cores (TMA -> tcgen05.mma kind::tf32 -> TMEM epilogue):
+ *   P = A[M x Kd] * F[R*Kp x Kd]^T is formed tile by tile in tensor memory and never stored;
+ *   state[R*Kp x M] receives the MU / HALS row update of cnmf_b200_row_update, partials likewise;
+ *   state_tf32 (same layout, may be NULL) receives the updated rows rounded to tf32 -- the operand
+ *   F of the next half-step, so that operand rounding stays unbiased while the master stays fp32.
+ * A and F should hold tf32-representable values (cnmf_b200_round_tf32); other bits are ignored.
+ * Replaces  x @ W.T (+ update, cnmf.py:355-372)  or  H.T @ x (+ update)  for R replicates. */
+int cnmf_b200_dense_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F,
+                              int64_t ldf, float* state, float* state_tf32, int64_t lds,
+                              const float* gram, const uint8_t* active, int32_t R, int32_t Kp,
+                              int32_t algo, float l1, float l2, float eps, double* partials,
+                              void* stream);
+
 typedef struct cnmf_b200_frob_problem {
   int64_t n_cells;   /* N */
   int64_t n_genes;   /* G */
@@ -117,7 +136,8 @@ typedef struct cnmf_b200_frob_problem {
 /* Bytes of workspace cnmf_b200_frob_iterate needs for this problem (only shapes/impl are read). */
 int64_t cnmf_b200_frob_workspace_bytes(const cnmf_b200_frob_problem* p);
 
-/* gramW <- Gram(Wall) (call once after initialising Wall, before the first iterate). */
+/* gramW <- Gram(Wall), and (tcgen05 path) the tf32 operand copies of Wall / Ht inside the workspace.
+ * Call after the host has written Wall / Ht and before cnmf_b200_frob_objective / _iterate. */
 int cnmf_b200_frob_prepare(const cnmf_b200_frob_problem* p, void* stream);
 
 /* n_iters x { H half-step; gramH; W half-step; gramW }, then (if err2 != NULL) the objective of

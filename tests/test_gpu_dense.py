@@ -136,10 +136,10 @@ def test_engine_trace_matches_oracle(small_problem, algo, K):
     from cnmf_torch_b200.engine import DenseFrobeniusEngine
     from cnmf_torch_b200 import _lib as L
     x = small_problem
-    eng = DenseFrobeniusEngine(x)
+    eng = DenseFrobeniusEngine(x, impl=L.IMPL_SIMT)
     seeds = [11, 22, 33]
     H0, W0 = eng.make_init(K, seeds)
-    res = eng.factorize(K, H0=H0, W0=W0, algo=algo, tol=0.0, max_iter=40, return_H=True, impl=L.IMPL_SIMT)
+    res = eng.factorize(K, H0=H0, W0=W0, algo=algo, tol=0.0, max_iter=40, return_H=True)
     assert res.launches > 0
     for r in range(len(seeds)):
         ora = no.nmf_batch(x, H0[r].numpy(), W0[r].numpy(), algo=algo, tol=0.0, max_iter=40)
@@ -166,10 +166,10 @@ def test_engine_convergence_and_freeze(small_problem):
     from cnmf_torch_b200.engine import DenseFrobeniusEngine
     from cnmf_torch_b200 import _lib as L
     x = small_problem
-    eng = DenseFrobeniusEngine(x)
+    eng = DenseFrobeniusEngine(x, impl=L.IMPL_SIMT)
     seeds = [1, 2, 3, 4]
     H0, W0 = eng.make_init(5, seeds)
-    res = eng.factorize(5, H0=H0, W0=W0, algo="mu", tol=1e-3, max_iter=300, impl=L.IMPL_SIMT)
+    res = eng.factorize(5, H0=H0, W0=W0, algo="mu", tol=1e-3, max_iter=300)
     assert np.all(res.n_iter % 10 == 0)
     for r in range(len(seeds)):
         ora = no.nmf_batch(x, H0[r].numpy(), W0[r].numpy(), algo="mu", tol=1e-3, max_iter=300)
