@@ -57,6 +57,8 @@ SIGNATURES = {
     "cnmf_b200_sumsq": (i32, [vp, i64, i64, i64, vp, vp, vp]),
     "cnmf_b200_gram_workspace_bytes": (i64, [i32, i32, i64]),
     "cnmf_b200_gram": (i32, [vp, i64, i32, i32, i64, vp, vp, vp]),
+    "cnmf_b200_gram_static_max_floats": (i64, []),
+    "cnmf_b200_gram_static": (i32, [vp, i64, i32, i32, i64, vp, vp]),
     "cnmf_b200_gemm_nt": (i32, [vp, i64, i64, vp, i64, i64, i64, vp, i64, vp]),
     "cnmf_b200_row_update_blocks": (i64, [i64]),
     "cnmf_b200_row_update": (i32, [vp, i64, vp, i64, vp, vp, i64, i32, i32, i32, f32, f32, f32, vp, vp]),

@@ -1,6 +1,8 @@
 // Dense Frobenius engine, CUDA-core (fp32 FFMA) kernels: the semantic baseline that the
 // tcgen05 path is checked against, plus the small kernels both paths share (Gram, sum of
 // squares, objective combine).  See include/cnmf_b200.h for the reference lines replaced.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace cnmf {
@@ -392,6 +394,79 @@ int cnmf_b200_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, in
                  "gemm_nt: leading dimensions must be multiples of 4 and pointers 16B aligned");
   CNMF_CHECK_ARG(lda >= Kd && ldb >= Kd && ldc >= N, "gemm_nt: leading dimension too small");
   return launch_gemm_nt(A, lda, M, B, ldb, N, Kd, C, ldc, (cudaStream_t)stream);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Gram for callers that cannot allocate.
+//
+// Some hosts of this library have no way to hand it a workspace: an application that has given all
+// of HBM to its own pool allocator (a later cudaMalloc would simply fail), or a latency-critical
+// loop where the implicit device-wide synchronisation of cudaMalloc / cudaFree is not acceptable.
+// For them the split partials of the Gram kernel live in the fixed array below instead of a
+// caller-provided workspace.  The array is part of the library image: every GPU that loads
+// libcnmf_b200.so carries these 4 MiB until the process exits.
+// ---------------------------------------------------------------------------------------------
+constexpr int64_t GRAM_STATIC_FLOATS = 1 << 20;  // 4 MiB: e.g. R=100, Kp=12 up to L = 100 000 columns
+static __device__ __align__(256) float g_gram_static_scratch[GRAM_STATIC_FLOATS];
+
+constexpr int GRAM_STATIC_MAX_DEVICES = 64;
+static float* g_gram_static_ptr[GRAM_STATIC_MAX_DEVICES] = {nullptr};
+static std::mutex g_gram_static_mutex;
+
+// `g_gram_static_scratch` used from host code is only a handle for the runtime, not a device
+// address; the address valid on the CURRENT device comes from cudaGetSymbolAddress.  Looked up once
+// per device (first call on that device) and cached.
+static int gram_static_scratch(float** out) {
+  int dev = -1;
+  CNMF_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= GRAM_STATIC_MAX_DEVICES) {
+    set_error("gram_static: device ordinal %d outside the supported range [0, %d)", dev,
+              GRAM_STATIC_MAX_DEVICES);
+    return CNMF_B200_ERR_UNSUPPORTED;
+  }
+  std::lock_guard<std::mutex> lock(g_gram_static_mutex);
+  if (g_gram_static_ptr[dev] == nullptr) {
+    float* p = nullptr;
+    CNMF_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_gram_static_scratch));
+    if (p == nullptr) {
+      set_error("gram_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+      return CNMF_B200_ERR_CUDA;
+    }
+    g_gram_static_ptr[dev] = p;
+  }
+  *out = g_gram_static_ptr[dev];
+  return 0;
+}
+
+int64_t cnmf_b200_gram_static_max_floats(void) { return GRAM_STATIC_FLOATS; }
+
+/* Same result as cnmf_b200_gram, but needs no workspace and allocates nothing (no cudaMalloc /
+ * cudaFree, no library allocator): the split partials go to a 4 MiB array built into the library.
+ *   - limit: R * ceil(L / 2048) * Kp * Kp  must not exceed cnmf_b200_gram_static_max_floats();
+ *     larger problems are refused with CNMF_B200_ERR_WORKSPACE (use cnmf_b200_gram with your own
+ *     workspace instead);
+ *   - the first call on each device looks up the array's device address; make that first call
+ *     before starting any stream capture on that device;
+ *   - all calls on a device share the one array and it keeps whatever the previous call left in
+ *     it.  Nothing in it has to start at zero -- every partial that is read is written first by the
+ *     same call -- but two calls that overlap on the GPU (different streams, or different host
+ *     threads on the same device) race on it.  Keep them on one stream or serialise them. */
+int cnmf_b200_gram_static(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
+                          void* stream) {
+  CNMF_CHECK_ARG(F && gram, "gram_static: null pointer");
+  CNMF_CHECK_ARG(R > 0 && L > 0 && ld >= L, "gram_static: bad shape R=%d L=%lld ld=%lld", R, (long long)L,
+                 (long long)ld);
+  CNMF_CHECK_ARG(Kp > 0 && Kp % 4 == 0 && Kp <= CNMF_B200_MAX_KP, "gram_static: Kp=%d unsupported", Kp);
+  const int64_t need = (int64_t)R * gram_splits(L) * Kp * Kp;
+  if (need > GRAM_STATIC_FLOATS) {
+    set_error("gram_static: needs %lld scratch floats, the built-in array holds %lld "
+              "(R=%d, Kp=%d, L=%lld); use cnmf_b200_gram with a caller workspace",
+              (long long)need, (long long)GRAM_STATIC_FLOATS, R, Kp, (long long)L);
+    return CNMF_B200_ERR_WORKSPACE;
+  }
+  float* scratch = nullptr;
+  CNMF_TRY(gram_static_scratch(&scratch));
+  return launch_gram(F, ld, R, Kp, L, gram, scratch, (cudaStream_t)stream);
 }
 
 int64_t cnmf_b200_row_update_blocks(int64_t M) { return ceil_div(M, RU_THREADS); }

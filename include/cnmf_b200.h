@@ -69,6 +69,18 @@ int64_t cnmf_b200_gram_workspace_bytes(int32_t R, int32_t Kp, int64_t L);
 int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
                    void* workspace, void* stream);
 
+/* cnmf_b200_gram for callers that cannot allocate device memory and hold no workspace (all of HBM
+ * already owned by the host application's pool, or a loop that cannot afford cudaMalloc's implicit
+ * device synchronisation).  No counterpart in the reference; same output as cnmf_b200_gram.
+ * The split partials live in a 4 MiB array inside the library (resident on every GPU that loads it).
+ * Refuses problems with R * ceil(L/2048) * Kp*Kp > cnmf_b200_gram_static_max_floats() (2^20) with
+ * CNMF_B200_ERR_WORKSPACE.  Allocates nothing.  The first call on a device resolves the array's
+ * address: issue it before any stream capture.  Calls share the array: calls that overlap on the GPU
+ * race; nothing in it needs clearing between calls. */
+int64_t cnmf_b200_gram_static_max_floats(void);
+int cnmf_b200_gram_static(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
+                          void* stream);
+
 /* C[M x N] = A[M x Kd] * B[N x Kd]^T, fp32 FFMA (CUDA cores).  Replaces  x @ W.T / H.T @ x
  * (cnmf.py:355) in the SIMT baseline. */
 int cnmf_b200_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, int64_t ldb,
