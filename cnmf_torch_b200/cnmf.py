@@ -1,0 +1,311 @@
+"""``cNMF`` -- the reference's pipeline object for the factorize -> combine -> consensus path, with the
+per-replicate ``run_nmf`` loop replaced by the replicate-batched B200 engine and the consensus front
+half replaced by the consensus kernel set.  Method names, arguments, file names and file formats
+follow /root/reference/src/cnmf/cnmf.py (cited per method) so the two are interchangeable on disk.
+
+Not re-implemented (out of scope / "next" rows): ``prepare`` with HVG selection
+and TPM statistics, the usage refits and OLS z-scores of the consensus back half, plotting.
+``prepare_from_matrix`` is the thin entry that writes the same three inputs ``factorize`` reads.
+"""
+from __future__ import annotations
+
+import errno
+import itertools
+import os
+import warnings
+
+import numpy as np
+import pandas as pd
+import scipy.sparse as sp
+import yaml
+
+
+# ---- .df.npz helpers (cnmf.py:32-41) --------------------------------------------------------------
+def save_df_to_npz(obj, filename):
+    np.savez_compressed(filename, data=obj.values, index=obj.index.values, columns=obj.columns.values)
+
+
+def load_df_from_npz(filename):
+    with np.load(filename, allow_pickle=True) as f:
+        return pd.DataFrame(**f)
+
+
+def save_df_to_text(obj, filename):
+    obj.to_csv(filename, sep="\t")
+
+
+def worker_filter(iterable, worker_index, total_workers):
+    """Job i belongs to worker w iff (i - w) % total == 0 (cnmf.py:53-54)."""
+    return (p for i, p in enumerate(iterable) if (i - worker_index) % total_workers == 0)
+
+
+def _mkdir(path):
+    os.makedirs(path, exist_ok=True)
+
+
+class cNMF:
+    def __init__(self, output_dir=".", name=None, device="cuda:0", impl="auto"):
+        """cnmf.py:393-414.  ``device``/``impl`` are additions (which GPU, which CUDA path)."""
+        import datetime
+        import uuid
+        self.output_dir = output_dir
+        if name is None:
+            name = "%s_%s" % (datetime.datetime.now().strftime("%Y_%m_%d"), uuid.uuid4().hex[:6])
+        self.name = name
+        self.device, self.impl = device, impl
+        self.paths = None
+        self._initialize_dirs()
+
+    def _initialize_dirs(self):
+        """Same file names as cnmf.py:416-455 (the ones this path reads or writes)."""
+        if self.paths is not None:
+            return
+        base = os.path.join(self.output_dir, self.name)
+        tmp = os.path.join(base, "cnmf_tmp")
+        _mkdir(tmp)
+        n = self.name
+        self.paths = {
+            "normalized_counts": os.path.join(tmp, n + ".norm_counts.h5ad"),
+            "normalized_counts_npz": os.path.join(tmp, n + ".norm_counts.npz"),  # side channel: no anndata in this image
+            "nmf_replicate_parameters": os.path.join(tmp, n + ".nmf_params.df.npz"),
+            "nmf_run_parameters": os.path.join(tmp, n + ".nmf_idvrun_params.yaml"),
+            "nmf_genes_list": os.path.join(base, n + ".overdispersed_genes.txt"),
+            "iter_spectra": os.path.join(tmp, n + ".spectra.k_%d.iter_%d.df.npz"),
+            "iter_usages": os.path.join(tmp, n + ".usages.k_%d.iter_%d.df.npz"),
+            "merged_spectra": os.path.join(tmp, n + ".spectra.k_%d.merged.df.npz"),
+            "local_density_cache": os.path.join(tmp, n + ".local_density_cache.k_%d.merged.df.npz"),
+            "consensus_spectra": os.path.join(tmp, n + ".spectra.k_%d.dt_%s.consensus.df.npz"),
+            "consensus_spectra__txt": os.path.join(base, n + ".spectra.k_%d.dt_%s.consensus.txt"),
+        }
+
+    # ---- inputs --------------------------------------------------------------------------------
+    def save_norm_counts(self, X, obs_names=None, var_names=None):
+        """Counterpart of cnmf.py:696-698 (sc.write of an AnnData).  Writes .h5ad when anndata is
+        importable, and always the .npz side channel (CSR float32) that ``factorize`` can read here."""
+        X = sp.csr_matrix(X) if not sp.issparse(X) else X.tocsr()
+        obs_names = np.arange(X.shape[0]).astype(str) if obs_names is None else np.asarray(obs_names).astype(str)
+        var_names = np.arange(X.shape[1]).astype(str) if var_names is None else np.asarray(var_names).astype(str)
+        np.savez_compressed(self.paths["normalized_counts_npz"], data=X.data, indices=X.indices,
+                            indptr=X.indptr, shape=np.array(X.shape), obs=obs_names, var=var_names)
+        try:
+            import anndata as ad
+            ad.AnnData(X=X.astype(np.float64), obs=pd.DataFrame(index=obs_names),
+                       var=pd.DataFrame(index=var_names)).write(self.paths["normalized_counts"])
+        except ImportError:
+            pass
+
+    def load_norm_counts(self):
+        """-> (X csr, obs_names, var_names); prefers .h5ad (cnmf.py:873) when it can be read."""
+        if os.path.exists(self.paths["normalized_counts"]):
+            try:
+                import anndata as ad
+                a = ad.read_h5ad(self.paths["normalized_counts"])
+                return sp.csr_matrix(a.X), np.asarray(a.obs.index), np.asarray(a.var.index)
+            except ImportError:
+                pass
+        with np.load(self.paths["normalized_counts_npz"], allow_pickle=False) as f:
+            X = sp.csr_matrix((f["data"], f["indices"], f["indptr"]), shape=tuple(f["shape"]))
+            return X, f["obs"], f["var"]
+
+    def prepare_from_matrix(self, norm_counts, components, n_iter=100, seed=None, beta_loss="frobenius",
+                            obs_names=None, var_names=None, alpha_usage=0.0, alpha_spectra=0.0,
+                            init="random", total_workers=-1, use_gpu=True, batch_size=5000, max_iter=1000):
+        """Writes what ``prepare`` leaves for ``factorize`` (cnmf.py:590-596): normalised counts, the
+        replicate ledger and the run_nmf kwargs.  ``norm_counts`` is the already variance-scaled HVG
+        matrix (cells x genes); zero-count cells are refused like cnmf.py:688-691."""
+        X = sp.csr_matrix(norm_counts)
+        if (np.asarray(X.sum(axis=1)).ravel() == 0).any():
+            raise Exception("Error: %d cells have zero counts of overdispersed genes. E.g. %s. Filter those "
+                            "cells and re-run or adjust the number of overdispersed genes. Quitting!"
+                            % (int((np.asarray(X.sum(axis=1)).ravel() == 0).sum()), "see matrix rows"))
+        self.save_norm_counts(X, obs_names, var_names)
+        rp, kw = self.get_nmf_iter_params(ks=components, n_iter=n_iter, random_state_seed=seed,
+                                          beta_loss=beta_loss, alpha_usage=alpha_usage,
+                                          alpha_spectra=alpha_spectra, init=init, total_workers=total_workers,
+                                          use_gpu=use_gpu, batch_size=batch_size, max_iter=max_iter)
+        self.save_nmf_iter_params(rp, kw)
+        return rp, kw
+
+    # ---- ledger (cnmf.py:701-802) ----------------------------------------------------------------
+    def get_nmf_iter_params(self, ks, n_iter=100, random_state_seed=None, beta_loss="kullback-leibler",
+                            alpha_usage=0.0, alpha_spectra=0.0, init="random", total_workers=-1,
+                            use_gpu=False, batch_size=5000, max_iter=1000):
+        """Seed ledger + run_nmf kwargs, byte-compatible with cnmf.py:701-777: n_runs counts the RAW
+        ``ks`` (cnmf.py:738), rows enumerate the de-duplicated sorted Ks (cnmf.py:735, 744), seeds are
+        ``np.random.seed(seed); randint(1, 2**31-1, n_runs)`` (cnmf.py:740-741)."""
+        if type(ks) is int:
+            ks = [ks]
+        k_list = sorted(set(list(ks)))
+        n_runs = len(ks) * n_iter
+        np.random.seed(seed=random_state_seed)
+        nmf_seeds = np.random.randint(low=1, high=(2 ** 31) - 1, size=n_runs)
+        rows = []
+        for i, (k, r) in enumerate(itertools.product(k_list, range(n_iter))):
+            rows.append([k, r, nmf_seeds[i], os.path.exists(self.paths["iter_spectra"] % (k, r))])
+        replicate_params = pd.DataFrame(rows, columns=["n_components", "iter", "nmf_seed", "completed"])
+        n_completed = replicate_params["completed"].sum()
+        if n_completed > 0:
+            warnings.warn("{n} runs already appear completed. If this is unexpected, consider\n            "
+                          "re-initializing the cnmf object with a different run name or output directory"
+                          .format(n=n_completed), UserWarning)
+        _nmf_kwargs = dict(alpha_W=alpha_spectra, alpha_H=alpha_usage, l1_ratio_H=0.0, l1_ratio_W=0.0,
+                           beta_loss=beta_loss, algo="mu", tol=1e-4, mode="online",
+                           online_chunk_max_iter=max_iter, online_chunk_size=batch_size, init=init,
+                           n_jobs=total_workers, use_gpu=use_gpu)
+        return replicate_params, _nmf_kwargs
+
+    def save_nmf_iter_params(self, replicate_params, run_params):
+        save_df_to_npz(replicate_params, self.paths["nmf_replicate_parameters"])
+        with open(self.paths["nmf_run_parameters"], "w") as F:
+            yaml.dump(run_params, F)
+
+    def update_nmf_iter_params(self):
+        """Marks ledger rows completed by file existence (cnmf.py:780-795)."""
+        with open(self.paths["nmf_run_parameters"]) as F:
+            _nmf_kwargs = yaml.load(F, Loader=yaml.FullLoader)
+        rp = load_df_from_npz(self.paths["nmf_replicate_parameters"])
+        for i in rp.index:
+            rp.at[i, "completed"] = os.path.exists(
+                self.paths["iter_spectra"] % (rp.at[i, "n_components"], rp.at[i, "iter"]))
+        print("{n} NMF runs are currently incomplete".format(n=(rp["completed"] == False).sum()))  # noqa: E712
+        self.save_nmf_iter_params(rp, _nmf_kwargs)
+
+    # ---- factorize (cnmf.py:839-892), replicate-batched ------------------------------------------
+    def factorize(self, worker_i=0, total_workers=1, skip_completed_runs=False, max_batch=None,
+                  nmf_kwargs_override=None):
+        """Same job selection as the reference (stride over ledger rows, cnmf.py:876-880) and the same
+        output per job -- ``spectra.k_%d.iter_%d.df.npz`` with index 1..K and the gene names as
+        columns (cnmf.py:889-892) -- but the selected jobs are grouped by K and each group runs as ONE
+        batch on the GPU, with X uploaded once per call instead of once per replicate."""
+        from .nmf import make_engine, run_nmf_batch
+        run_params = load_df_from_npz(self.paths["nmf_replicate_parameters"])
+        X, _, var_names = self.load_norm_counts()
+        with open(self.paths["nmf_run_parameters"]) as F:
+            kw = yaml.load(F, Loader=yaml.FullLoader)
+        if nmf_kwargs_override:
+            kw.update(nmf_kwargs_override)
+        if not skip_completed_runs:
+            jobs = list(worker_filter(range(len(run_params)), worker_i, total_workers))
+        else:
+            jobs = list(worker_filter(run_params.index[run_params["completed"] == False],  # noqa: E712
+                                      worker_i, total_workers))
+        if not jobs:
+            return
+        engine = make_engine(X, beta_loss=kw.get("beta_loss", "frobenius"), device=self.device, impl=self.impl)
+        engine_kw = {k: kw[k] for k in ("init", "algo", "mode", "tol", "alpha_W", "l1_ratio_W", "alpha_H",
+                                        "l1_ratio_H", "batch_max_iter", "online_max_pass", "online_chunk_size",
+                                        "online_chunk_max_iter", "online_h_tol", "online_w_tol") if k in kw}
+        sel = run_params.iloc[jobs, :]
+        for k, grp in sel.groupby("n_components", sort=True):
+            k = int(k)
+            idx = list(grp.index)
+            step = len(idx) if not max_batch else int(max_batch)
+            for lo in range(0, len(idx), step):
+                part = grp.loc[idx[lo:lo + step]]
+                print("[Worker %d]. Starting tasks %s (k=%d, %d replicates in one batch)."
+                      % (worker_i, list(part.index[:3]) + (["..."] if len(part) > 3 else []), k, len(part)))
+                res = run_nmf_batch(engine, k, [int(s) for s in part["nmf_seed"]], **engine_kw)
+                for j, (_, p) in enumerate(part.iterrows()):
+                    spectra = pd.DataFrame(res.W[j], index=np.arange(1, k + 1), columns=var_names)
+                    save_df_to_npz(spectra, self.paths["iter_spectra"] % (k, int(p["iter"])))
+
+    # ---- combine (cnmf.py:599-620, 895-920) -------------------------------------------------------
+    def combine(self, components=None, skip_missing_files=False):
+        if type(components) is int:
+            ks = [components]
+        elif components is None:
+            run_params = load_df_from_npz(self.paths["nmf_replicate_parameters"])
+            ks = sorted(set(run_params.n_components))
+        else:
+            ks = components
+        for k in ks:
+            self.combine_nmf(k, skip_missing_files=skip_missing_files)
+
+    def combine_nmf(self, k, skip_missing_files=False, remove_individual_iterations=False):
+        run_params = load_df_from_npz(self.paths["nmf_replicate_parameters"])
+        print("Combining factorizations for k=%d." % k)
+        subset = run_params[run_params.n_components == k].sort_values("iter")
+        combined = []
+        for _, p in subset.iterrows():
+            fn = self.paths["iter_spectra"] % (p["n_components"], p["iter"])
+            if not os.path.exists(fn):
+                if not skip_missing_files:
+                    print("Missing file: %s, run with skip_missing=True to override" % fn)
+                    raise FileNotFoundError(errno.ENOENT, os.strerror(errno.ENOENT), fn)
+                print("Missing file: %s. Skipping." % fn)
+            else:
+                spectra = load_df_from_npz(fn)
+                spectra.index = ["iter%d_topic%d" % (p["iter"], t + 1) for t in range(k)]
+                combined.append(spectra)
+        if len(combined) > 0:
+            combined = pd.concat(combined, axis=0)
+            save_df_to_npz(combined, self.paths["merged_spectra"] % k)
+        else:
+            print("No spectra found for k=%d" % k)
+        return combined
+
+    # ---- consensus, front half (cnmf.py:997-1090) -------------------------------------------------
+    def consensus(self, k, density_threshold=0.5, local_neighborhood_size=0.30, show_clustering=False,
+                  build_ref=False, skip_density_and_return_after_stats=False, close_clustergram_fig=False,
+                  refit_usage=False, normalize_tpm_spectra=False, norm_counts=None):
+        """L2-normalise the merged spectra, local-density filter, KMeans(k, n_init=10, random_state=1),
+        per-cluster median, row-normalise -- cnmf.py:1045-1090 -- on the GPU.  Writes the
+        ``local_density_cache`` (cnmf.py:1073) and the ``consensus_spectra`` files (cnmf.py:1151-1152 for
+        the spectra part) and returns (median_spectra DataFrame, labels Series, local_density DataFrame).
+        The usage refits / TPM spectra / plots that follow in the reference are outside this path."""
+        from .consensus import consensus_front_half
+        merged = load_df_from_npz(self.paths["merged_spectra"] % k)
+        dt_str = "2" if skip_density_and_return_after_stats else str(density_threshold)
+        dt_repl = dt_str.replace(".", "_")                                    # cnmf.py:1049-1052
+        n_neighbors = int(local_neighborhood_size * merged.shape[0] / k)      # cnmf.py:1053
+        cache = self.paths["local_density_cache"] % k
+        cached = None
+        if not skip_density_and_return_after_stats and os.path.isfile(cache):  # cnmf.py:1061-1062
+            cached = load_df_from_npz(cache).values[:, 0]
+        out = consensus_front_half(merged.values, k, density_threshold, n_neighbors, device=self.device,
+                                   skip_density=skip_density_and_return_after_stats, local_density=cached)
+        local_density = pd.DataFrame(out["local_density"], columns=["local_density"], index=merged.index) \
+            if out["local_density"] is not None else None
+        if local_density is not None and cached is None:
+            save_df_to_npz(local_density, cache)
+        kept_index = merged.index[out["keep"]]
+        labels = pd.Series(out["labels"], index=kept_index)
+        median = pd.DataFrame(out["median_spectra"], index=np.arange(1, k + 1), columns=merged.columns)
+        median.index.name = None
+        save_df_to_npz(median, self.paths["consensus_spectra"] % (k, dt_repl))
+        save_df_to_text(median, self.paths["consensus_spectra__txt"] % (k, dt_repl))
+        return median, labels, local_density
+
+
+def main():
+    """``cnmf {factorize,combine,consensus}`` with the reference's flags for these verbs
+    (cnmf.py:1410-1467); ``prepare`` stays with the reference."""
+    import argparse
+    parser = argparse.ArgumentParser()
+    parser.add_argument("command", type=str, choices=["factorize", "combine", "consensus"])
+    parser.add_argument("--name", type=str, nargs="?", default="cNMF")
+    parser.add_argument("--output-dir", type=str, nargs="?", default=".")
+    parser.add_argument("--total-workers", type=int, default=-1)
+    parser.add_argument("--worker-index", type=int, default=0)
+    parser.add_argument("--skip-completed-runs", action="store_true", default=False)
+    parser.add_argument("-k", "--components", type=int, nargs="+")
+    parser.add_argument("--local-density-threshold", type=float, default=0.5)
+    parser.add_argument("--local-neighborhood-size", type=float, default=0.30)
+    parser.add_argument("--device", type=str, default=None)
+    args = parser.parse_args()
+    device = args.device or "cuda:%d" % int(os.environ.get("LOCAL_RANK", "0"))
+    obj = cNMF(output_dir=args.output_dir, name=args.name, device=device)
+    if args.command == "factorize":
+        total = max(1, args.total_workers)
+        obj.factorize(worker_i=args.worker_index, total_workers=total,
+                      skip_completed_runs=args.skip_completed_runs)
+    elif args.command == "combine":
+        obj.combine(components=args.components)
+    elif args.command == "consensus":
+        ks = args.components or sorted(set(load_df_from_npz(obj.paths["nmf_replicate_parameters"]).n_components))
+        for k in ks:
+            obj.consensus(k, args.local_density_threshold, args.local_neighborhood_size)
+
+
+if __name__ == "__main__":
+    main()

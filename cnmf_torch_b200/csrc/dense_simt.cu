@@ -46,62 +46,72 @@ __global__ void __launch_bounds__(32) sumsq_final_kernel(const double* __restric
 // ---------------------------------------------------------------------------------------------
 // Gram of every replicate block: gram[r] = F_r F_r^T
 // ---------------------------------------------------------------------------------------------
-constexpr int GRAM_TILE = 64;      // columns staged per step
-constexpr int GRAM_THREADS = 256;
-constexpr int GRAM_SPLIT_LEN = 2048;  // columns per CTA (multiple of GRAM_TILE)
+constexpr int GRAM_TILE = 256;       // columns staged per step
+constexpr int GRAM_THREADS = 128;
 
-static inline int gram_splits(int64_t L) { return (int)ceil_div(L, GRAM_SPLIT_LEN); }
+static inline int64_t gram_tiles(int64_t L) { return ceil_div(L, GRAM_TILE); }
 
+// One CTA = one replicate x one 256-column tile.  The tile [KP x 256] is staged in shared memory
+// with 128-bit loads; each thread owns one 4x4 block of the KP x KP output and a slice of the
+// columns (16 FMA per 8 shared loads), slices are combined through shared memory in fixed order.
+// Output: one partial per (replicate, tile), [R][ntile][KP*KP]; gram_final_kernel sums the tiles.
 template <int KP>
 __global__ void __launch_bounds__(GRAM_THREADS) gram_partial_kernel(const float* __restrict__ F,
                                                                     int64_t ld, int64_t L,
                                                                     float* __restrict__ partial,
-                                                                    int nsplit) {
-  constexpr int NP = KP * KP;
-  constexpr int NSL = (GRAM_THREADS / NP) > 0 ? (GRAM_THREADS / NP) : 1;  // column slices
-  constexpr int OPT = (NP * NSL + GRAM_THREADS - 1) / GRAM_THREADS;       // outputs per thread
-  __shared__ float tile[KP][GRAM_TILE + 1];
-  __shared__ float red[NSL][NP];
-  const int r = blockIdx.y, split = blockIdx.x;
+                                                                    int ntile) {
+  constexpr int NB1 = KP / 4, NB = NB1 * NB1;                 // 4x4 output blocks
+  constexpr int NSL = GRAM_THREADS / NB > 0 ? GRAM_THREADS / NB : 1;  // column slices
+  static_assert(NB <= GRAM_THREADS, "one thread per output block at least");
+  __shared__ __align__(16) float tile[KP][GRAM_TILE];
+  __shared__ float red[NSL][KP * KP + 1];
+  const int r = blockIdx.y, tl = blockIdx.x;
   const float* Fr = F + (int64_t)r * KP * ld;
-  const int64_t l_begin = (int64_t)split * GRAM_SPLIT_LEN;
-  const int64_t l_end = min(L, l_begin + (int64_t)GRAM_SPLIT_LEN);
+  const int64_t l0 = (int64_t)tl * GRAM_TILE;
+  const int width = (int)min((int64_t)GRAM_TILE, L - l0);
 
-  float acc[OPT];
-#pragma unroll
-  for (int i = 0; i < OPT; ++i) acc[i] = 0.f;
-
-  for (int64_t l0 = l_begin; l0 < l_end; l0 += GRAM_TILE) {
-    for (int i = threadIdx.x; i < KP * GRAM_TILE; i += GRAM_THREADS) {
-      int a = i / GRAM_TILE, c = i - a * GRAM_TILE;
-      int64_t l = l0 + c;
-      tile[a][c] = (l < l_end) ? Fr[(int64_t)a * ld + l] : 0.f;
+  for (int i = threadIdx.x; i < KP * (GRAM_TILE / 4); i += GRAM_THREADS) {
+    const int a = i / (GRAM_TILE / 4), c = (i - a * (GRAM_TILE / 4)) * 4;
+    float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+    const float* src = Fr + (int64_t)a * ld + l0 + c;
+    if (c + 3 < width) v = *reinterpret_cast<const float4*>(src);
+    else {
+      if (c < width) v.x = src[0];
+      if (c + 1 < width) v.y = src[1];
+      if (c + 2 < width) v.z = src[2];
     }
-    __syncthreads();
-#pragma unroll
-    for (int i = 0; i < OPT; ++i) {
-      int o = threadIdx.x + i * GRAM_THREADS;
-      if (o < NP * NSL) {
-        int pair = o % NP, sl = o / NP;
-        int a = pair / KP, b = pair - a * KP;
-        float t = acc[i];
-        for (int c = sl; c < GRAM_TILE; c += NSL) t = fmaf(tile[a][c], tile[b][c], t);
-        acc[i] = t;
-      }
-    }
-    __syncthreads();
-  }
-#pragma unroll
-  for (int i = 0; i < OPT; ++i) {
-    int o = threadIdx.x + i * GRAM_THREADS;
-    if (o < NP * NSL) red[o / NP][o % NP] = acc[i];
+    *reinterpret_cast<float4*>(&tile[a][c]) = v;
   }
   __syncthreads();
-  for (int pair = threadIdx.x; pair < NP; pair += GRAM_THREADS) {
-    float t = 0.f;
+
+  const int sl = threadIdx.x % NSL, blk = threadIdx.x / NSL;
+  float acc[4][4];
 #pragma unroll
-    for (int sl = 0; sl < NSL; ++sl) t += red[sl][pair];
-    partial[((int64_t)r * nsplit + split) * NP + pair] = t;
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+  if (blk < NB) {
+    const int ba = (blk / NB1) * 4, bb = (blk % NB1) * 4;
+    for (int c = sl; c < GRAM_TILE; c += NSL) {
+      float a[4], b[4];
+#pragma unroll
+      for (int i = 0; i < 4; ++i) { a[i] = tile[ba + i][c]; b[i] = tile[bb + i][c]; }
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 4; ++j) red[sl][(ba + i) * KP + bb + j] = acc[i][j];
+  }
+  __syncthreads();
+  for (int o = threadIdx.x; o < KP * KP; o += GRAM_THREADS) {
+    float t = 0.f;
+#pragma unroll 4
+    for (int s2 = 0; s2 < NSL; ++s2) t += red[s2][o];
+    partial[((int64_t)r * ntile + tl) * (KP * KP) + o] = t;
   }
 }
 
@@ -305,13 +315,13 @@ __global__ void __launch_bounds__(32) frob_objective_kernel(
 // ---------------------------------------------------------------------------------------------
 int launch_gram(const float* F, int64_t ld, int R, int Kp, int64_t L, float* gram, void* ws,
                 cudaStream_t st) {
-  const int ns = gram_splits(L);
+  const int ntile = (int)gram_tiles(L);
   float* partial = reinterpret_cast<float*>(ws);
-  dim3 grid(ns, R);
-  CNMF_DISPATCH_KP(Kp, (gram_partial_kernel<KP><<<grid, GRAM_THREADS, 0, st>>>(F, ld, L, partial, ns)));
+  dim3 grid(ntile, R);
+  CNMF_DISPATCH_KP(Kp, (gram_partial_kernel<KP><<<grid, GRAM_THREADS, 0, st>>>(F, ld, L, partial, ntile)));
   CNMF_LAUNCH_CHECK();
   const int64_t total = (int64_t)R * Kp * Kp;
-  gram_final_kernel<<<(unsigned)ceil_div(total, 256), 256, 0, st>>>(partial, ns, Kp * Kp, gram, total);
+  gram_final_kernel<<<(unsigned)ceil_div(total, 128), 128, 0, st>>>(partial, ntile, Kp * Kp, gram, total);
   CNMF_LAUNCH_CHECK();
   return 0;
 }
@@ -374,7 +384,7 @@ int cnmf_b200_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld, doub
 }
 
 int64_t cnmf_b200_gram_workspace_bytes(int32_t R, int32_t Kp, int64_t L) {
-  return (int64_t)R * gram_splits(L) * Kp * Kp * (int64_t)sizeof(float);
+  return (int64_t)R * gram_tiles(L) * Kp * Kp * (int64_t)sizeof(float);
 }
 
 int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
@@ -406,7 +416,7 @@ int cnmf_b200_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, in
 // caller-provided workspace.  The array is part of the library image: every GPU that loads
 // libcnmf_b200.so carries these 4 MiB until the process exits.
 // ---------------------------------------------------------------------------------------------
-constexpr int64_t GRAM_STATIC_FLOATS = 1 << 20;  // 4 MiB: e.g. R=100, Kp=12 up to L = 100 000 columns
+constexpr int64_t GRAM_STATIC_FLOATS = 1 << 20;  // 4 MiB: e.g. R=100, Kp=12 up to L = 18 432 columns
 static __device__ __align__(256) float g_gram_static_scratch[GRAM_STATIC_FLOATS];
 
 constexpr int GRAM_STATIC_MAX_DEVICES = 64;
@@ -442,7 +452,7 @@ int64_t cnmf_b200_gram_static_max_floats(void) { return GRAM_STATIC_FLOATS; }
 
 /* Same result as cnmf_b200_gram, but needs no workspace and allocates nothing (no cudaMalloc /
  * cudaFree, no library allocator): the split partials go to a 4 MiB array built into the library.
- *   - limit: R * ceil(L / 2048) * Kp * Kp  must not exceed cnmf_b200_gram_static_max_floats();
+ *   - limit: R * ceil(L / 256) * Kp * Kp  must not exceed cnmf_b200_gram_static_max_floats();
  *     larger problems are refused with CNMF_B200_ERR_WORKSPACE (use cnmf_b200_gram with your own
  *     workspace instead);
  *   - the first call on each device looks up the array's device address; make that first call
@@ -457,7 +467,7 @@ int cnmf_b200_gram_static(const float* F, int64_t ld, int32_t R, int32_t Kp, int
   CNMF_CHECK_ARG(R > 0 && L > 0 && ld >= L, "gram_static: bad shape R=%d L=%lld ld=%lld", R, (long long)L,
                  (long long)ld);
   CNMF_CHECK_ARG(Kp > 0 && Kp % 4 == 0 && Kp <= CNMF_B200_MAX_KP, "gram_static: Kp=%d unsupported", Kp);
-  const int64_t need = (int64_t)R * gram_splits(L) * Kp * Kp;
+  const int64_t need = (int64_t)R * gram_tiles(L) * Kp * Kp;  // one partial per 256-column tile
   if (need > GRAM_STATIC_FLOATS) {
     set_error("gram_static: needs %lld scratch floats, the built-in array holds %lld "
               "(R=%d, Kp=%d, L=%lld); use cnmf_b200_gram with a caller workspace",

@@ -19,6 +19,8 @@
 #include <cuda.h>
 #include <cudaTypedefs.h>
 
+#include <stdlib.h>
+
 #include <mutex>
 #include <vector>
 
@@ -370,18 +372,24 @@ static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out) 
   const int64_t num_kb = ceil_div(Kd, TC_BK);
   double best = 1e300;
   bool found = false;
+  static const int forced_t = [] { const char* e = getenv("CNMF_B200_TC_T"); return e ? atoi(e) : 0; }();
   for (int t = 1; t * Kp <= TC_MAX_BN; ++t) {
     const int BN = t * Kp;
     if (BN % 16 != 0) continue;
+    if (forced_t > 0 && t != forced_t && (forced_t * Kp) % 16 == 0 && forced_t * Kp <= TC_MAX_BN) continue;
     int stages = TC_MAX_STAGES;
     while (stages >= 2 && tc_smem_bytes(t, Kp, stages) > static_cast<size_t>(TC_SMEM_LIMIT)) --stages;
     if (stages < 2) continue;
     const int num_n = static_cast<int>(ceil_div(R, t));
     const int64_t tiles = static_cast<int64_t>(num_m) * num_n;
     const int64_t waves = ceil_div(tiles, sms);
-    const double mma = static_cast<double>(num_kb) * 4.0 * (BN / 2.0 > 40.0 ? BN / 2.0 : 40.0);
+    // measured on B200 (profiles/NOTES.md): one SM ingests ~43 B/clk from L2 through TMA, so a k-block
+    // costs max(operand bytes / 43, tensor-pipe clocks); the epilogue of the last tile is exposed.
+    const double bytes_kb = (TC_BM + BN) * TC_BK * 4.0;
+    const double mma_kb = 4.0 * (BN / 2.0 > 32.0 ? BN / 2.0 : 32.0);
+    const double kb_clk = bytes_kb / 43.0 > mma_kb ? bytes_kb / 43.0 : mma_kb;
     const double epi = static_cast<double>(t) * (Kp * Kp + 12.0 * Kp) * 1.5 + 1500.0;
-    const double cost = waves * mma + epi + (waves > 1 ? 0.0 : 0.0);
+    const double cost = waves * (static_cast<double>(num_kb) * kb_clk + 1000.0) + epi;
     if (cost < best) {
       best = cost;
       found = true;

@@ -73,7 +73,7 @@ int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L,
  * already owned by the host application's pool, or a loop that cannot afford cudaMalloc's implicit
  * device synchronisation).  No counterpart in the reference; same output as cnmf_b200_gram.
  * The split partials live in a 4 MiB array inside the library (resident on every GPU that loads it).
- * Refuses problems with R * ceil(L/2048) * Kp*Kp > cnmf_b200_gram_static_max_floats() (2^20) with
+ * Refuses problems with R * ceil(L/256) * Kp*Kp > cnmf_b200_gram_static_max_floats() (2^20) with
  * CNMF_B200_ERR_WORKSPACE.  Allocates nothing.  The first call on a device resolves the array's
  * address: issue it before any stream capture.  Calls share the array: calls that overlap on the GPU
  * race; nothing in it needs clearing between calls. */

@@ -1,0 +1,121 @@
+"""CPU: the host-side mirror of the reference interface against goldens produced by the reference's
+own functions (ledger seeds, worker striding, .df.npz format, combine)."""
+import io
+import os
+
+import numpy as np
+import pandas as pd
+import pytest
+
+from cnmf_torch_b200 import cnmf as host
+
+
+def _load(golden_dir, name):
+    return np.load(os.path.join(golden_dir, name), allow_pickle=True)
+
+
+@pytest.mark.parametrize("tag", ["a", "b", "c", "d", "e"])
+def test_ledger_matches_reference(golden_dir, tmp_path, tag):
+    g = _load(golden_dir, "ledger.npz")
+    n_iter, seed = [int(v) for v in g[tag + "_args"]]
+    ks = [int(v) for v in g[tag + "_ks"]]
+    obj = host.cNMF(output_dir=str(tmp_path), name="t")
+    rp, kw = obj.get_nmf_iter_params(ks if tag != "e" else ks[0], n_iter=n_iter, random_state_seed=seed,
+                                     beta_loss="frobenius")
+    np.testing.assert_array_equal(rp[["n_components", "iter", "nmf_seed"]].values.astype(np.int64),
+                                  g[tag + "_values"])
+    np.testing.assert_array_equal(rp["completed"].values.astype(bool), g[tag + "_completed"])
+    assert sorted(kw.keys()) == list(g["kwargs_keys"])
+    assert repr(sorted(kw.items())) == str(g["kwargs_repr"])
+
+
+def test_ledger_known_answers():
+    """KATs quoted in SURVEY.md 8(a1), computed with the reference's code, seed 14."""
+    from cnmf_torch_b200.synth import ledger_seeds
+    s = ledger_seeds(45, 14)
+    assert list(s[:3]) == [59886188, 1812018521, 1173234957] and s[-1] == 1288885239
+    assert ledger_seeds(900, 14)[-1] == 1393000
+
+
+def test_worker_filter_matches_reference(golden_dir):
+    g = _load(golden_dir, "worker_filter.npz")
+    for key in g.files:
+        n, w, t = [int(v) for v in key.split("_")]
+        np.testing.assert_array_equal(np.array(list(host.worker_filter(range(n), w, t)), dtype=np.int64), g[key])
+
+
+def test_df_npz_format_is_interchangeable(golden_dir, tmp_path):
+    g = _load(golden_dir, "combine.npz")
+    # a file written by the reference's save_df_to_npz loads with our loader ...
+    ref_file = tmp_path / "ref.df.npz"
+    ref_file.write_bytes(g["iter_file_bytes"].tobytes())
+    df = host.load_df_from_npz(str(ref_file))
+    np.testing.assert_array_equal(df.values, g["k3_i0"])
+    assert list(df.index) == [1, 2, 3] and list(df.columns) == [f"g{i}" for i in range(12)]
+    # ... and a file we write has the same members, dtypes and contents
+    ours = tmp_path / "ours.df.npz"
+    host.save_df_to_npz(df, str(ours))
+    with np.load(str(ref_file), allow_pickle=True) as a, np.load(str(ours), allow_pickle=True) as b:
+        assert sorted(a.files) == sorted(b.files) == ["columns", "data", "index"]
+        for k in a.files:
+            assert a[k].dtype == b[k].dtype
+            np.testing.assert_array_equal(a[k], b[k])
+
+
+def test_combine_matches_reference(golden_dir, tmp_path):
+    g = _load(golden_dir, "combine.npz")
+    obj = host.cNMF(output_dir=str(tmp_path), name="comb")
+    rp, kw = obj.get_nmf_iter_params([3, 4], n_iter=3, random_state_seed=14, beta_loss="frobenius")
+    obj.save_nmf_iter_params(rp, kw)
+    genes = [f"g{i}" for i in range(12)]
+    for kk in (3, 4):
+        for it in range(3):
+            df = pd.DataFrame(g[f"k{kk}_i{it}"], index=np.arange(1, kk + 1), columns=genes)
+            host.save_df_to_npz(df, obj.paths["iter_spectra"] % (kk, it))
+    for kk in (3, 4):
+        m = obj.combine_nmf(kk)
+        np.testing.assert_array_equal(m.values, g[f"merged_k{kk}_data"])
+        assert list(m.index) == list(g[f"merged_k{kk}_index"])
+        assert list(m.columns) == list(g[f"merged_k{kk}_columns"])
+        m2 = host.load_df_from_npz(obj.paths["merged_spectra"] % kk)
+        np.testing.assert_array_equal(m2.values, m.values)
+    # missing file raises unless skip_missing_files (cnmf.py:904-909)
+    os.remove(obj.paths["iter_spectra"] % (3, 1))
+    with pytest.raises(FileNotFoundError):
+        obj.combine_nmf(3)
+    assert obj.combine_nmf(3, skip_missing_files=True).shape[0] == 6
+    # update_nmf_iter_params marks completion by file existence (cnmf.py:780-795)
+    obj.update_nmf_iter_params()
+    rp2 = host.load_df_from_npz(obj.paths["nmf_replicate_parameters"])
+    done = rp2[(rp2.n_components == 3)].sort_values("iter")["completed"].tolist()
+    assert done == [True, False, True]
+
+
+def test_prepare_from_matrix_rejects_zero_count_cells(tmp_path):
+    obj = host.cNMF(output_dir=str(tmp_path), name="z")
+    x = np.ones((5, 4), dtype=np.float32)
+    x[2] = 0
+    with pytest.raises(Exception, match="cells have zero counts of overdispersed genes"):
+        obj.prepare_from_matrix(x, [2], n_iter=2, seed=1)
+
+
+def test_norm_counts_side_channel_roundtrip(tmp_path):
+    obj = host.cNMF(output_dir=str(tmp_path), name="n")
+    rng = np.random.default_rng(0)
+    x = (rng.random((7, 5)) * (rng.random((7, 5)) < 0.5)).astype(np.float32)
+    x[:, 0] += 1
+    obj.save_norm_counts(x, var_names=[f"g{i}" for i in range(5)])
+    X, obs, var = obj.load_norm_counts()
+    np.testing.assert_array_equal(X.toarray(), x)
+    assert list(var) == [f"g{i}" for i in range(5)]
+
+
+def test_product_does_not_import_the_oracle():
+    """No file of the product package may reference oracle/ (the oracle is the checker only)."""
+    import cnmf_torch_b200
+    root = os.path.dirname(cnmf_torch_b200.__file__)
+    for dirpath, _, files in os.walk(root):
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cuh")):
+                text = open(os.path.join(dirpath, fn)).read()
+                assert "import oracle" not in text and "from oracle" not in text, fn

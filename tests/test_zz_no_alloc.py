@@ -56,8 +56,8 @@ def test_gram_static_rejects_oversize_problem():
     lib = L.lib()
     cap = lib.cnmf_b200_gram_static_max_floats()
     assert cap == 1 << 20
-    R, Kp = 64, 32                      # 64 * ceil(L/2048) * 1024 floats > 2^20 once L > 16 * 2048
-    Lc = 17 * 2048
+    R, Kp = 64, 32                      # 64 * ceil(L/256) * 1024 floats > 2^20 once L > 16 * 256
+    Lc = 17 * 256
     F = torch.zeros(8, 8, device="cuda")  # never read: the size check comes first
     out = torch.zeros(R, Kp, Kp, device="cuda")
     rc = lib.cnmf_b200_gram_static(F.data_ptr(), Lc, R, Kp, Lc, out.data_ptr(), None)
