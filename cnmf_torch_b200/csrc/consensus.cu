@@ -1,0 +1,540 @@
+// Consensus kernel set: pairwise Euclidean distances (fp64 accumulate), top-(n+1) local density,
+// column centring, batched Lloyd k-means (assign / update / inertia) and per-cluster medians.
+// Replaces the sklearn / numpy / pandas calls at /root/reference/src/cnmf/cnmf.py:1065-1090; the
+// numerical recipe of each kernel follows what those library calls do for float32 input
+// (sklearn/metrics/pairwise.py:376-427, 567-638; sklearn/cluster/_k_means_lloyd.pyx:_update_chunk_dense;
+// sklearn/cluster/_kmeans.py:_kmeans_single_lloyd) so that kNN sets and labels come out identical.
+#include <float.h>
+
+#include "common.cuh"
+
+namespace cnmf {
+
+// ---------------------------------------------------------------------------------------------
+// K8: D = sqrt(max(0, -2 X X^T + xx + xx^T)) with fp64 accumulation, cast to fp32 BEFORE the clamp
+// and the square root, diagonal forced to 0 (pairwise.py:404-425, 630-636).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) row_sqnorm64_kernel(const float* __restrict__ X, int64_t ld, int M,
+                                                           int G, double* __restrict__ out) {
+  const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (row >= M) return;
+  double acc = 0.0;
+  for (int g = lane; g < G; g += 32) {
+    double v = X[(int64_t)row * ld + g];
+    acc = fma(v, v, acc);
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) out[row] = acc;
+}
+
+constexpr int DT = 64, DK = 16;
+
+__global__ void __launch_bounds__(256) pairwise_dist_kernel(const float* __restrict__ X, int64_t ld, int M, int G,
+                                                            const double* __restrict__ xx,
+                                                            float* __restrict__ D, int64_t ldd, int nt) {
+  // upper-triangular tile index -> (ti, tj), ti <= tj
+  int rem = blockIdx.x, ti = 0;
+  while (rem >= nt - ti) { rem -= nt - ti; ++ti; }
+  const int tj = ti + rem;
+  __shared__ __align__(16) double As[DK][DT + 2];
+  __shared__ __align__(16) double Bs[DK][DT + 2];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int i0 = ti * DT, j0 = tj * DT;
+  double acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+  const int lrow = tid >> 2, lk = (tid & 3) * 4;
+  for (int k0 = 0; k0 < G; k0 += DK) {
+    float va[4] = {0.f, 0.f, 0.f, 0.f}, vb[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = k0 + lk + q;
+      if (k < G) {
+        if (i0 + lrow < M) va[q] = X[(int64_t)(i0 + lrow) * ld + k];
+        if (j0 + lrow < M) vb[q] = X[(int64_t)(j0 + lrow) * ld + k];
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      As[lk + q][lrow] = (double)va[q];
+      Bs[lk + q][lrow] = (double)vb[q];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < DK; ++kk) {
+      double a[4], b[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { a[q] = As[kk][ty * 4 + q]; b[q] = Bs[kk][tx * 4 + q]; }
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[p][q] = fma(a[p], b[q], acc[p][q]);
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    const int i = i0 + ty * 4 + p;
+    if (i >= M) continue;
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int j = j0 + tx * 4 + q;
+      if (j >= M) continue;
+      double d = -2.0 * acc[p][q];
+      d += xx[i];
+      d += xx[j];
+      float f = (float)d;
+      f = fmaxf(f, 0.f);
+      f = (i == j) ? 0.f : sqrtf(f);
+      D[(int64_t)i * ldd + j] = f;
+      if (ti != tj) D[(int64_t)j * ldd + i] = f;
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K9: per row, the n+1 smallest distances (cnmf.py:1067) by radix select on the fp32 bit patterns
+// (all values >= 0, so bit order == numeric order); density = sum / n (cnmf.py:1069-1072).
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) topk_density_kernel(const float* __restrict__ D, int64_t ldd, int M, int kth,
+                                                           int n_div, float* __restrict__ density,
+                                                           int* __restrict__ nbr) {
+  extern __shared__ uint32_t srow[];
+  __shared__ int hist[256];
+  __shared__ uint32_t s_prefix;
+  __shared__ int s_remaining, s_less;
+  __shared__ double sred[8];
+  const int row = blockIdx.x;
+  const float* drow = D + (int64_t)row * ldd;
+  for (int j = threadIdx.x; j < M; j += 256) srow[j] = __float_as_uint(drow[j]);
+  if (threadIdx.x == 0) { s_prefix = 0u; s_remaining = kth; s_less = 0; }
+  __syncthreads();
+  uint32_t mask = 0u;
+  for (int pass = 3; pass >= 0; --pass) {
+    hist[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t prefix = s_prefix;
+    const int shift = pass * 8;
+    for (int j = threadIdx.x; j < M; j += 256) {
+      const uint32_t b = srow[j];
+      if ((b & mask) == prefix) atomicAdd(&hist[(b >> shift) & 255u], 1);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int cum = 0, b = 0;
+      const int remaining = s_remaining;
+      for (; b < 256; ++b) {
+        if (cum + hist[b] >= remaining) break;
+        cum += hist[b];
+      }
+      s_remaining = remaining - cum;
+      s_less += cum;
+      s_prefix = prefix | ((uint32_t)b << shift);
+    }
+    __syncthreads();
+    mask |= 255u << shift;
+  }
+  const uint32_t T = s_prefix;     // bit pattern of the kth smallest value
+  const int n_less = s_less;       // values strictly smaller
+  const int ties = kth - n_less;   // copies of T that belong to the selection
+  double acc = 0.0;
+  for (int j = threadIdx.x; j < M; j += 256) {
+    const uint32_t b = srow[j];
+    if (b < T) acc += (double)__uint_as_float(b);
+  }
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) sred[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += sred[w];
+    t += (double)ties * (double)__uint_as_float(T);
+    density[row] = (float)t / (float)n_div;
+  }
+  if (nbr != nullptr && threadIdx.x < 32) {
+    // ordered compaction by one warp: indices with value < T, then the first `ties` equal to T
+    const int lane = threadIdx.x;
+    int* out = nbr + (int64_t)row * kth;
+    int n_out = 0, n_tie = 0;
+    for (int j0 = 0; j0 < M; j0 += 32) {
+      const int j = j0 + lane;
+      const uint32_t b = j < M ? srow[j] : 0xFFFFFFFFu;
+      const unsigned less = __ballot_sync(0xffffffffu, b < T);
+      if (b < T) out[n_out + __popc(less & ((1u << lane) - 1u))] = j;
+      n_out += __popc(less);
+    }
+    for (int j0 = 0; j0 < M && n_tie < ties; j0 += 32) {
+      const int j = j0 + lane;
+      const uint32_t b = j < M ? srow[j] : 0xFFFFFFFFu;
+      const unsigned eq = __ballot_sync(0xffffffffu, b == T);
+      const int pos = n_tie + __popc(eq & ((1u << lane) - 1u));
+      if (b == T && pos < ties) out[n_less + pos] = j;
+      n_tie += __popc(eq);
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K10 prologue: X -= mean over rows, the mean accumulated in fp32 in row order like numpy's
+// axis-0 reduction (sklearn/cluster/_kmeans.py:1486-1491), divided in double then rounded.
+// ---------------------------------------------------------------------------------------------
+__global__ void col_mean_seq_kernel(const float* __restrict__ X, int64_t ld, int M, int G, float* __restrict__ mean) {
+  const int g = blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= G) return;
+  float acc = 0.f;
+  for (int m = 0; m < M; ++m) acc += X[(int64_t)m * ld + g];
+  mean[g] = (float)((double)acc / (double)M);
+}
+
+__global__ void sub_mean_kernel(float* __restrict__ X, int64_t ld, int M, int G, const float* __restrict__ mean) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= (int64_t)M * G) return;
+  const int m = (int)(i / G), g = (int)(i - (int64_t)m * G);
+  X[(int64_t)m * ld + g] -= mean[g];
+}
+
+// ---------------------------------------------------------------------------------------------
+// K10 E-step, batched over inits: label = argmin_j fl32(||c_j||^2 - 2 x.c_j), first minimum wins
+// (_k_means_lloyd.pyx:_update_chunk_dense).  CTA = 128 samples x (up to 32) centres of ONE init.
+// ---------------------------------------------------------------------------------------------
+constexpr int KA_S = 128, KA_C = 32, KA_G = 32;
+
+__global__ void __launch_bounds__(256) kmeans_assign_kernel(const float* __restrict__ X, int64_t ld, int M, int G,
+                                                            const float* __restrict__ centers, int k,
+                                                            const uint8_t* __restrict__ active,
+                                                            int* __restrict__ labels, int* __restrict__ n_changed) {
+  const int init = blockIdx.y;
+  if (active != nullptr && active[init] == 0) return;
+  __shared__ float Xs[KA_S][KA_G + 1];
+  __shared__ float Cs[KA_C][KA_G + 1];
+  __shared__ float dist[KA_S][KA_C + 1];
+  __shared__ float cn[KA_C];
+  const float* C = centers + (int64_t)init * k * G;
+  const int tid = threadIdx.x, sx = tid & 31, cy = tid >> 5;
+  const int m0 = blockIdx.x * KA_S;
+  float acc[4][4];
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.f;
+  float cnorm = 0.f;
+  for (int g0 = 0; g0 < G; g0 += KA_G) {
+    for (int i = tid; i < KA_S * KA_G; i += 256) {
+      const int s = i / KA_G, g = i - s * KA_G;
+      Xs[s][g] = (m0 + s < M && g0 + g < G) ? X[(int64_t)(m0 + s) * ld + g0 + g] : 0.f;
+    }
+    for (int i = tid; i < KA_C * KA_G; i += 256) {
+      const int c = i / KA_G, g = i - c * KA_G;
+      Cs[c][g] = (c < k && g0 + g < G) ? C[(int64_t)c * G + g0 + g] : 0.f;
+    }
+    __syncthreads();
+    if (tid < KA_C) {
+#pragma unroll 8
+      for (int g = 0; g < KA_G; ++g) cnorm = fmaf(Cs[tid][g], Cs[tid][g], cnorm);
+    }
+#pragma unroll 8
+    for (int g = 0; g < KA_G; ++g) {
+      float xv[4], cv[4];
+#pragma unroll
+      for (int a = 0; a < 4; ++a) { xv[a] = Xs[sx + 32 * a][g]; cv[a] = Cs[cy * 4 + a][g]; }
+#pragma unroll
+      for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int b = 0; b < 4; ++b) acc[a][b] = fmaf(xv[a], cv[b], acc[a][b]);
+    }
+    __syncthreads();
+  }
+  if (tid < KA_C) cn[tid] = cnorm;
+  __syncthreads();
+#pragma unroll
+  for (int a = 0; a < 4; ++a)
+#pragma unroll
+    for (int b = 0; b < 4; ++b) dist[sx + 32 * a][cy * 4 + b] = fmaf(-2.f, acc[a][b], cn[cy * 4 + b]);
+  __syncthreads();
+  int changed = 0;
+  if (tid < KA_S && m0 + tid < M) {
+    float best = dist[tid][0];
+    int lab = 0;
+    for (int j = 1; j < k; ++j) {
+      const float d = dist[tid][j];
+      if (d < best) { best = d; lab = j; }
+    }
+    int* lp = labels + (int64_t)init * M + m0 + tid;
+    changed = (*lp != lab);
+    *lp = lab;
+  }
+  changed = __syncthreads_count(changed);
+  if (tid == 0 && changed) atomicAdd(&n_changed[init], changed);
+}
+
+// ---------------------------------------------------------------------------------------------
+// K10 M-step: per-cluster sums in sample order inside each segment, segments combined in order.
+// ---------------------------------------------------------------------------------------------
+constexpr int KU_G = 128;   // genes per CTA (one per thread)
+constexpr int KU_SEG = 32;  // sample segments
+
+__global__ void __launch_bounds__(KU_G) kmeans_update_kernel(const float* __restrict__ X, int64_t ld, int M, int G,
+                                                             const int* __restrict__ labels, int k,
+                                                             const uint8_t* __restrict__ active,
+                                                             float* __restrict__ part, int* __restrict__ cnt_part) {
+  const int init = blockIdx.z, seg = blockIdx.y;
+  if (active != nullptr && active[init] == 0) return;
+  __shared__ float acc[KA_C][KU_G];
+  __shared__ int cnt[KA_C];
+  const int t = threadIdx.x, g = blockIdx.x * KU_G + t;
+  for (int j = 0; j < k; ++j) acc[j][t] = 0.f;
+  if (t < KA_C) cnt[t] = 0;
+  __syncthreads();
+  const int per = (M + KU_SEG - 1) / KU_SEG;
+  const int mb = seg * per, me = min(M, mb + per);
+  const int* lab = labels + (int64_t)init * M;
+  for (int m = mb; m < me; ++m) {
+    const int l = lab[m];
+    if (g < G) acc[l][t] += X[(int64_t)m * ld + g];
+    if (t == 0) cnt[l] += 1;
+  }
+  __syncthreads();
+  float* out = part + (((int64_t)init * KU_SEG + seg) * k) * G;
+  if (g < G)
+    for (int j = 0; j < k; ++j) out[(int64_t)j * G + g] = acc[j][t];
+  if (blockIdx.x == 0 && t < k) cnt_part[((int64_t)init * KU_SEG + seg) * k + t] = cnt[t];
+}
+
+// one CTA per (centre, init): new centre = sum * fl(1/count) (_k_means_common.pyx:_average_centers),
+// centre shift = sqrt(sum (old-new)^2) in fp32; count 0 leaves the sum (0) and reports the cluster empty.
+__global__ void __launch_bounds__(128) kmeans_finalize_kernel(const float* __restrict__ part,
+                                                              const int* __restrict__ cnt_part, int G, int k,
+                                                              const uint8_t* __restrict__ active,
+                                                              const float* __restrict__ c_old, float* __restrict__ c_new,
+                                                              float* __restrict__ shift, int* __restrict__ counts) {
+  const int j = blockIdx.x, init = blockIdx.y;
+  if (active != nullptr && active[init] == 0) return;
+  __shared__ float red[4];
+  int count = 0;
+  for (int s = 0; s < KU_SEG; ++s) count += cnt_part[((int64_t)init * KU_SEG + s) * k + j];
+  const float alpha = count > 0 ? 1.0f / (float)count : 1.0f;
+  float sh = 0.f;
+  for (int g = threadIdx.x; g < G; g += 128) {
+    float tot = 0.f;
+    for (int s = 0; s < KU_SEG; ++s) tot += part[(((int64_t)init * KU_SEG + s) * k + j) * G + g];
+    const float cnew = tot * alpha;
+    const int64_t o = ((int64_t)init * k + j) * G + g;
+    const float d = c_old[o] - cnew;
+    sh = fmaf(d, d, sh);
+    c_new[o] = cnew;
+  }
+  sh = warp_sum(sh);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = sh;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    shift[init * k + j] = sqrtf(red[0] + red[1] + red[2] + red[3]);
+    counts[init * k + j] = count;
+  }
+}
+
+__global__ void __launch_bounds__(256) kmeans_inertia_kernel(const float* __restrict__ X, int64_t ld, int M, int G,
+                                                             const float* __restrict__ centers, int k,
+                                                             const int* __restrict__ labels,
+                                                             double* __restrict__ part) {
+  // one warp per sample, 8 samples per CTA; partial per CTA
+  const int init = blockIdx.y;
+  __shared__ double red[8];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m = blockIdx.x * 8 + w;
+  double acc = 0.0;
+  if (m < M) {
+    const int l = labels[(int64_t)init * M + m];
+    const float* c = centers + ((int64_t)init * k + l) * G;
+    const float* x = X + (int64_t)m * ld;
+    for (int g = lane; g < G; g += 32) {
+      const double d = (double)x[g] - (double)c[g];
+      acc = fma(d, d, acc);
+    }
+  }
+  acc = warp_sum(acc);
+  if (lane == 0) red[w] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int i = 0; i < 8; ++i) t += red[i];
+    part[(int64_t)init * gridDim.x + blockIdx.x] = t;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K11: per-cluster per-gene median (cnmf.py:1087) by rank counting, then row-normalise (cnmf.py:1090)
+// ---------------------------------------------------------------------------------------------
+constexpr int MD_G = 16;  // genes per CTA
+
+__global__ void __launch_bounds__(256) cluster_median_kernel(const float* __restrict__ X, int64_t ld, int G,
+                                                             const int* __restrict__ order,
+                                                             const int* __restrict__ offsets,
+                                                             float* __restrict__ median) {
+  extern __shared__ float vals[];  // [n][MD_G + 1]
+  const int j = blockIdx.y, g0 = blockIdx.x * MD_G;
+  const int beg = offsets[j], n = offsets[j + 1] - beg;
+  if (n <= 0) {
+    if (threadIdx.x < MD_G && g0 + threadIdx.x < G) median[(int64_t)j * G + g0 + threadIdx.x] = nanf("");
+    return;
+  }
+  __shared__ float lo[MD_G], hi[MD_G];
+  for (int i = threadIdx.x; i < n * MD_G; i += 256) {
+    const int r = i / MD_G, c = i - r * MD_G;
+    vals[r * (MD_G + 1) + c] = (g0 + c < G) ? X[(int64_t)order[beg + r] * ld + g0 + c] : 0.f;
+  }
+  __syncthreads();
+  const int r_lo = (n - 1) / 2, r_hi = n / 2;
+  for (int i = threadIdx.x; i < n * MD_G; i += 256) {
+    const int c = i % MD_G, r = i / MD_G;
+    const float v = vals[r * (MD_G + 1) + c];
+    int rank = 0;
+    for (int q = 0; q < n; ++q) {
+      const float u = vals[q * (MD_G + 1) + c];
+      rank += (u < v) || (u == v && q < r);
+    }
+    if (rank == r_lo) lo[c] = v;
+    if (rank == r_hi) hi[c] = v;
+  }
+  __syncthreads();
+  if (threadIdx.x < MD_G && g0 + threadIdx.x < G)
+    median[(int64_t)j * G + g0 + threadIdx.x] = (float)(((double)lo[threadIdx.x] + (double)hi[threadIdx.x]) * 0.5);
+}
+
+__global__ void __launch_bounds__(256) row_normalize_kernel(const float* __restrict__ in, int G, float* __restrict__ out) {
+  const int j = blockIdx.x;
+  __shared__ double red[8];
+  __shared__ float s_total;
+  double acc = 0.0;
+  for (int g = threadIdx.x; g < G; g += 256) acc += (double)in[(int64_t)j * G + g];
+  acc = warp_sum(acc);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < 8; ++w) t += red[w];
+    s_total = (float)t;
+  }
+  __syncthreads();
+  for (int g = threadIdx.x; g < G; g += 256) out[(int64_t)j * G + g] = in[(int64_t)j * G + g] / s_total;
+}
+
+}  // namespace cnmf
+
+using namespace cnmf;
+
+extern "C" {
+
+int cnmf_b200_pairwise_dist(const float* X, int64_t ld, int32_t M, int32_t G, float* D, int64_t ldd, double* sqnorm,
+                            void* stream) {
+  CNMF_CHECK_ARG(X && D && sqnorm, "pairwise_dist: null pointer");
+  CNMF_CHECK_ARG(M > 0 && G > 0 && ld >= G && ldd >= M, "pairwise_dist: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  row_sqnorm64_kernel<<<(unsigned)ceil_div(M, 8), 256, 0, st>>>(X, ld, M, G, sqnorm);
+  CNMF_LAUNCH_CHECK();
+  const int nt = (int)ceil_div(M, DT);
+  pairwise_dist_kernel<<<(unsigned)(nt * (nt + 1) / 2), 256, 0, st>>>(X, ld, M, G, sqnorm, D, ldd, nt);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int cnmf_b200_topk_density(const float* D, int64_t ldd, int32_t M, int32_t n_neighbors, float* density, int32_t* nbr,
+                           void* stream) {
+  CNMF_CHECK_ARG(D && density, "topk_density: null pointer");
+  CNMF_CHECK_ARG(M > 0 && ldd >= M, "topk_density: bad shape");
+  CNMF_CHECK_ARG(n_neighbors >= 1 && n_neighbors + 1 <= M, "topk_density: n_neighbors=%d needs 1 <= n and n+1 <= rows=%d",
+                 n_neighbors, M);
+  const size_t smem = (size_t)M * 4;
+  if (smem > 200 * 1024) {
+    set_error("topk_density: %d rows exceed the shared-memory row buffer (51200)", M);
+    return CNMF_B200_ERR_UNSUPPORTED;
+  }
+  static thread_local size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    CNMF_CUDA(cudaFuncSetAttribute(topk_density_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = 200 * 1024;
+  }
+  topk_density_kernel<<<M, 256, smem, (cudaStream_t)stream>>>(D, ldd, M, n_neighbors + 1, n_neighbors, density, nbr);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int cnmf_b200_col_center(float* X, int64_t ld, int32_t M, int32_t G, float* mean, void* stream) {
+  CNMF_CHECK_ARG(X && mean && M > 0 && G > 0 && ld >= G, "col_center: bad argument");
+  cudaStream_t st = (cudaStream_t)stream;
+  col_mean_seq_kernel<<<(unsigned)ceil_div(G, 64), 64, 0, st>>>(X, ld, M, G, mean);
+  CNMF_LAUNCH_CHECK();
+  sub_mean_kernel<<<(unsigned)ceil_div((int64_t)M * G, 256), 256, 0, st>>>(X, ld, M, G, mean);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int64_t cnmf_b200_kmeans_workspace_bytes(int32_t n_init, int32_t k, int32_t G) {
+  return (int64_t)n_init * KU_SEG * k * ((int64_t)G * 4 + 4) + 256;
+}
+
+int cnmf_b200_kmeans_assign(const float* X, int64_t ld, int32_t M, int32_t G, const float* centers, int32_t n_init,
+                            int32_t k, const uint8_t* active, int32_t* labels, int32_t* n_changed, void* stream) {
+  CNMF_CHECK_ARG(X && centers && labels && n_changed, "kmeans_assign: null pointer");
+  CNMF_CHECK_ARG(M > 0 && G > 0 && n_init > 0 && k >= 1 && k <= KA_C, "kmeans_assign: need 1 <= k <= %d (k=%d)", KA_C, k);
+  dim3 grid((unsigned)ceil_div(M, KA_S), n_init);
+  kmeans_assign_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, ld, M, G, centers, k, active, labels, n_changed);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int cnmf_b200_kmeans_update(const float* X, int64_t ld, int32_t M, int32_t G, const int32_t* labels, int32_t n_init,
+                            int32_t k, const uint8_t* active, const float* centers_old, float* centers_new,
+                            float* center_shift, int32_t* counts, void* workspace, void* stream) {
+  CNMF_CHECK_ARG(X && labels && centers_old && centers_new && center_shift && counts && workspace,
+                 "kmeans_update: null pointer");
+  CNMF_CHECK_ARG(M > 0 && G > 0 && n_init > 0 && k >= 1 && k <= KA_C, "kmeans_update: need 1 <= k <= %d", KA_C);
+  cudaStream_t st = (cudaStream_t)stream;
+  float* part = reinterpret_cast<float*>(workspace);
+  int* cnt_part = reinterpret_cast<int*>(part + (int64_t)n_init * KU_SEG * k * G);
+  dim3 grid((unsigned)ceil_div(G, KU_G), KU_SEG, n_init);
+  kmeans_update_kernel<<<grid, KU_G, 0, st>>>(X, ld, M, G, labels, k, active, part, cnt_part);
+  CNMF_LAUNCH_CHECK();
+  kmeans_finalize_kernel<<<dim3(k, n_init), 128, 0, st>>>(part, cnt_part, G, k, active, centers_old, centers_new,
+                                                          center_shift, counts);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int64_t cnmf_b200_kmeans_inertia_blocks(int32_t M) { return ceil_div(M, 8); }
+
+int cnmf_b200_kmeans_inertia(const float* X, int64_t ld, int32_t M, int32_t G, const float* centers, int32_t n_init,
+                             int32_t k, const int32_t* labels, double* partials, void* stream) {
+  CNMF_CHECK_ARG(X && centers && labels && partials, "kmeans_inertia: null pointer");
+  dim3 grid((unsigned)ceil_div(M, 8), n_init);
+  kmeans_inertia_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, ld, M, G, centers, k, labels, partials);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int cnmf_b200_cluster_median(const float* X, int64_t ld, int32_t G, const int32_t* order, const int32_t* offsets,
+                             int32_t k, int32_t max_members, float* median, float* normalized, void* stream) {
+  CNMF_CHECK_ARG(X && order && offsets && median, "cluster_median: null pointer");
+  CNMF_CHECK_ARG(k >= 1 && G > 0 && max_members >= 1, "cluster_median: bad shape");
+  const size_t smem = (size_t)max_members * (MD_G + 1) * 4;
+  if (smem > 200 * 1024) {
+    set_error("cluster_median: cluster of %d members exceeds the shared-memory tile (3000)", max_members);
+    return CNMF_B200_ERR_UNSUPPORTED;
+  }
+  static thread_local size_t configured = 0;
+  if (smem > 48 * 1024 && smem > configured) {
+    CNMF_CUDA(cudaFuncSetAttribute(cluster_median_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+    configured = 200 * 1024;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  cluster_median_kernel<<<dim3((unsigned)ceil_div(G, MD_G), k), 256, smem, st>>>(X, ld, G, order, offsets, median);
+  CNMF_LAUNCH_CHECK();
+  if (normalized != nullptr) {
+    row_normalize_kernel<<<k, 256, 0, st>>>(median, G, normalized);
+    CNMF_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+}  // extern "C"

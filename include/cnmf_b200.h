@@ -162,6 +162,56 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
  * refreshed).  Gives the initial error that normalises run_nmf's convergence test. */
 int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Consensus kernel set.  Replaces the library calls of cNMF.consensus' front half
+ * (cnmf.py:1056-1090) on the float32 dtype flow of this fork.
+ * ---------------------------------------------------------------------------------------- */
+
+/* D[M x M] = euclidean_distances(X) for float32 X as sklearn computes it (cnmf.py:1065;
+ * sklearn/metrics/pairwise.py:376-427, 567-638): -2 x.y + |x|^2 + |y|^2 accumulated in fp64,
+ * cast to fp32, clamped at 0, diagonal set to 0, square root in fp32.  sqnorm: [M] doubles scratch. */
+int cnmf_b200_pairwise_dist(const float* X, int64_t ld, int32_t M, int32_t G, float* D, int64_t ldd,
+                            double* sqnorm, void* stream);
+
+/* density[i] = (sum of the n_neighbors+1 smallest entries of row i of D) / n_neighbors
+ * = np.argpartition(D, n+1)[:, :n+1] -> take -> sum(1)/n   (cnmf.py:1067-1072).
+ * nbr (optional, [M x (n+1)] int32) receives the selected column indices (ties at the boundary
+ * resolved towards the lower index).  M <= 51200. */
+int cnmf_b200_topk_density(const float* D, int64_t ldd, int32_t M, int32_t n_neighbors, float* density,
+                           int32_t* nbr, void* stream);
+
+/* mean[g] = mean over rows (fp32 accumulation in row order, as numpy's axis-0 reduction);
+ * X -= mean in place.  KMeans.fit centres its input this way (sklearn/cluster/_kmeans.py:1486-1491). */
+int cnmf_b200_col_center(float* X, int64_t ld, int32_t M, int32_t G, float* mean, void* stream);
+
+/* Lloyd iterations of KMeans(n_clusters=k, n_init, ...) (cnmf.py:1082-1083), all n_init restarts
+ * batched: centres [n_init x k x G], labels [n_init x M].  k <= 32.
+ *   assign : labels = argmin_j fl32(|c_j|^2 - 2 x.c_j), first minimum wins; n_changed[i] += #labels
+ *            that changed (zero it before the call)       (_k_means_lloyd.pyx _update_chunk_dense)
+ *   update : centres_new = per-cluster sum * fl32(1/count), center_shift[i*k+j] = |old - new|_2,
+ *            counts[i*k+j] = members (0 => empty cluster, centre left at 0 for the caller to relocate)
+ *   inertia: partials [n_init x cnmf_b200_kmeans_inertia_blocks(M)] doubles, sum_i |x_i - c_label(i)|^2
+ * active ([n_init] bytes, may be NULL) switches converged restarts off. */
+int64_t cnmf_b200_kmeans_workspace_bytes(int32_t n_init, int32_t k, int32_t G);
+int cnmf_b200_kmeans_assign(const float* X, int64_t ld, int32_t M, int32_t G, const float* centers,
+                            int32_t n_init, int32_t k, const uint8_t* active, int32_t* labels,
+                            int32_t* n_changed, void* stream);
+int cnmf_b200_kmeans_update(const float* X, int64_t ld, int32_t M, int32_t G, const int32_t* labels,
+                            int32_t n_init, int32_t k, const uint8_t* active, const float* centers_old,
+                            float* centers_new, float* center_shift, int32_t* counts, void* workspace,
+                            void* stream);
+int64_t cnmf_b200_kmeans_inertia_blocks(int32_t M);
+int cnmf_b200_kmeans_inertia(const float* X, int64_t ld, int32_t M, int32_t G, const float* centers,
+                             int32_t n_init, int32_t k, const int32_t* labels, double* partials,
+                             void* stream);
+
+/* median[j, g] = median over the members of cluster j (rows order[offsets[j] : offsets[j+1]]) of
+ * X[:, g]  (= l2_spectra.groupby(labels).median(), cnmf.py:1087); normalized (may be NULL) = rows of
+ * median divided by their sum (cnmf.py:1090).  Clusters of up to 3000 members. */
+int cnmf_b200_cluster_median(const float* X, int64_t ld, int32_t G, const int32_t* order,
+                             const int32_t* offsets, int32_t k, int32_t max_members, float* median,
+                             float* normalized, void* stream);
+
 /* Number of kernel launches the last cnmf_b200_frob_iterate on this thread enqueued. */
 int64_t cnmf_b200_last_launch_count(void);
 
