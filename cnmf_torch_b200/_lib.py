@@ -65,6 +65,9 @@ SIGNATURES = {
     "cnmf_b200_round_tf32": (i32, [vp, i64, vp]),
     "cnmf_b200_dense_half_step": (i32, [vp, i64, i64, i64, vp, i64, vp, vp, i64, vp, vp, i32, i32, i32, f32, f32,
                                         f32, vp, vp]),
+    "cnmf_b200_l2_normalize": (i32, [vp, i64, i32, i32, vp, i64, vp]),
+    "cnmf_b200_kmeanspp_workspace_bytes": (i64, [i32, i32, i32]),
+    "cnmf_b200_kmeanspp": (i32, [vp, i64, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]),
     "cnmf_b200_pairwise_dist": (i32, [vp, i64, i32, i32, vp, i64, vp, vp]),
     "cnmf_b200_topk_density": (i32, [vp, i64, i32, i32, vp, vp, vp]),
     "cnmf_b200_col_center": (i32, [vp, i64, i32, i32, vp, vp]),

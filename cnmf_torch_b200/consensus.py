@@ -8,7 +8,6 @@ selection; sklearn/cluster/_kmeans.py:1461-1563, 630-758) so that labels come ou
 from __future__ import annotations
 
 import numpy as np
-import pandas as pd
 import torch
 
 from . import _lib
@@ -19,12 +18,17 @@ def _stream():
     return torch.cuda.current_stream().cuda_stream
 
 
-def l2_normalize_rows(spectra: np.ndarray) -> np.ndarray:
-    """cnmf.py:1056 -- kept as the reference's own pandas expression on the host (a few hundred
-    microseconds for 4000 x 2000): its float32 result depends on numpy's summation order, and every
-    later exact comparison (kNN sets, labels) starts from these bits."""
-    df = pd.DataFrame(spectra)
-    return np.ascontiguousarray(((df.T / np.sqrt((df ** 2).sum(axis=1))).T).values)
+def l2_normalize_rows(spectra) -> torch.Tensor:
+    """cnmf.py:1056 on the device, bit-identical to the reference's float32 pandas expression
+    (squares summed in gene order in fp32).  Accepts a host array or a CUDA tensor; returns [M, G]
+    float32 on the device."""
+    L = lib()
+    s = spectra if torch.is_tensor(spectra) else torch.from_numpy(np.ascontiguousarray(spectra, dtype=np.float32)).cuda()
+    s = s.contiguous()
+    out = torch.empty_like(s)
+    check(L.cnmf_b200_l2_normalize(ptr(s), s.stride(0), int(s.shape[0]), int(s.shape[1]), ptr(out), out.stride(0),
+                                   _stream()), "l2_normalize")
+    return out
 
 
 def local_density_device(l2: torch.Tensor, n_neighbors: int, return_neighbors: bool = False):
@@ -53,9 +57,10 @@ def _is_same_clustering(a: np.ndarray, b: np.ndarray, k: int) -> bool:
 
 
 def kmeans_plusplus_host(Xc_host: np.ndarray, k: int, n_init: int, random_state: int):
-    """k-means++ seeding of all restarts from ONE RandomState, in restart order (Lloyd consumes no
-    random numbers, so the draws of restart i do not depend on the outcome of restart i-1).
-    Host-side through sklearn's own routine: the seeding is bound to numpy's RandomState stream."""
+    """Optional strict mode (``seeding="sklearn"``): the seeding of all restarts through sklearn's own
+    routine on the host, from ONE RandomState in restart order.  The device seeding makes the same
+    draws; the two can differ only where sklearn's fp32 BLAS sums and the device's fp64 sums round a
+    potential differently at a searchsorted / argmin boundary."""
     from sklearn.cluster._kmeans import _kmeans_plusplus
     from sklearn.utils.extmath import row_norms
     rs = np.random.RandomState(random_state)
@@ -66,6 +71,33 @@ def kmeans_plusplus_host(Xc_host: np.ndarray, k: int, n_init: int, random_state:
         centers, _ = _kmeans_plusplus(Xc_host, k, x_squared_norms=xsq, sample_weight=w, random_state=rs)
         out.append(centers)
     return np.stack(out)
+
+
+def kmeans_plusplus_device(Xc: torch.Tensor, k: int, n_init: int, random_state: int):
+    """k-means++ seeding of all restarts on the device.  Only the random numbers are drawn on the host,
+    from the same RandomState stream and in the same order as sklearn (first centre: choice(M, p);
+    then uniform(size=n_trials) per further centre; _kmeans.py:236-258); their number does not depend
+    on the data, so all restarts can be seeded side by side.  Returns (centers [n_init,k,G], chosen)."""
+    L = lib()
+    dev = Xc.device
+    M, G = int(Xc.shape[0]), int(Xc.shape[1])
+    T = 2 + int(np.log(k))
+    rs = np.random.RandomState(random_state)
+    w = np.ones(M, dtype=np.float32)
+    first = np.empty(n_init, dtype=np.int32)
+    rnd = np.zeros((n_init, max(k - 1, 1), T), dtype=np.float64)
+    for i in range(n_init):
+        first[i] = rs.choice(M, p=w / w.sum())
+        for c in range(1, k):
+            rnd[i, c - 1] = rs.uniform(size=T)
+    first_d = torch.from_numpy(first).to(dev)
+    rnd_d = torch.from_numpy(rnd).to(dev)
+    chosen = torch.empty((n_init, k), device=dev, dtype=torch.int32)
+    centers = torch.empty((n_init, k, G), device=dev, dtype=torch.float32)
+    ws = torch.empty(int(L.cnmf_b200_kmeanspp_workspace_bytes(M, n_init, T)), device=dev, dtype=torch.uint8)
+    check(L.cnmf_b200_kmeanspp(ptr(Xc), Xc.stride(0), M, G, n_init, k, T, ptr(first_d), ptr(rnd_d), ptr(chosen),
+                               ptr(centers), ptr(ws), _stream()), "kmeanspp")
+    return centers, chosen
 
 
 def kmeans_lloyd_batched(Xc: torch.Tensor, centers0: torch.Tensor, tol: float, max_iter: int = 300):
@@ -152,7 +184,7 @@ def _relocate_empty_clusters(Xc, labels, centers_old, centers_new, counts, shift
 
 
 def kmeans_fit(X: torch.Tensor, k: int, n_init: int = 10, random_state: int = 1, max_iter: int = 300,
-               tol: float = 1e-4, centers_init: np.ndarray | None = None):
+               tol: float = 1e-4, centers_init: np.ndarray | None = None, seeding: str = "device"):
     """``KMeans(n_clusters=k, n_init=10, random_state=1).fit(X)`` (cnmf.py:1082-1083).
     Returns dict(labels (0-based, int32 host), inertia, n_iter, centers (host, original space))."""
     L = lib()
@@ -167,12 +199,16 @@ def kmeans_fit(X: torch.Tensor, k: int, n_init: int = 10, random_state: int = 1,
     Xc = X.contiguous().clone()
     mean = torch.empty(G, device=dev, dtype=torch.float32)
     check(L.cnmf_b200_col_center(ptr(Xc), Xc.stride(0), M, G, ptr(mean), _stream()), "col_center")
-    if centers_init is None:
-        centers0 = kmeans_plusplus_host(Xc.cpu().numpy(), k, n_init, random_state)
+    if centers_init is not None:
+        centers0 = torch.from_numpy(np.asarray(centers_init, dtype=np.float32)).to(dev)
+        n_init = int(centers0.shape[0])
+    elif seeding == "device":
+        centers0, _ = kmeans_plusplus_device(Xc, k, n_init, random_state)
+    elif seeding == "sklearn":
+        centers0 = torch.from_numpy(kmeans_plusplus_host(Xc.cpu().numpy(), k, n_init, random_state)).to(dev)
     else:
-        centers0 = np.asarray(centers_init, dtype=np.float32)
-        n_init = centers0.shape[0]
-    labels, inertia, centers, n_iter = kmeans_lloyd_batched(Xc, torch.from_numpy(centers0).to(dev), tol_, max_iter)
+        raise ValueError(f"seeding={seeding!r}")
+    labels, inertia, centers, n_iter = kmeans_lloyd_batched(Xc, centers0, tol_, max_iter)
     best = None
     for i in range(n_init):   # best-of-n with the same-clustering guard (_kmeans.py:1531-1541)
         if best is None or (inertia[i] < inertia[best] and not _is_same_clustering(labels[i], labels[best], k)):
@@ -201,7 +237,7 @@ def cluster_medians(X: torch.Tensor, labels0: np.ndarray, k: int):
 
 def consensus_front_half(merged_spectra: np.ndarray, k: int, density_threshold: float, n_neighbors: int,
                          device="cuda:0", skip_density: bool = False, local_density=None,
-                         return_neighbors: bool = False):
+                         return_neighbors: bool = False, seeding: str = "device"):
     """cnmf.py:1056-1090.  Returns dict(local_density, keep, labels (1-based), median_spectra,
     l2_spectra, inertia, neighbors)."""
     lib()
@@ -209,8 +245,7 @@ def consensus_front_half(merged_spectra: np.ndarray, k: int, density_threshold: 
         raise _lib.Cnmfb200Error("CUDA device required: cnmf_torch_b200 has no CPU path")
     dev = torch.device(device)
     torch.cuda.set_device(dev)
-    l2_host = l2_normalize_rows(np.asarray(merged_spectra))
-    l2 = torch.from_numpy(l2_host).to(dev)
+    l2 = l2_normalize_rows(torch.from_numpy(np.ascontiguousarray(merged_spectra, dtype=np.float32)).to(dev))
     dens_h, nbr_h = None, None
     keep = np.ones(l2.shape[0], dtype=bool)
     if not skip_density:
@@ -225,8 +260,8 @@ def consensus_front_half(merged_spectra: np.ndarray, k: int, density_threshold: 
             raise RuntimeError("Zero components remain after density filtering. "
                                "Consider increasing density threshold")
     kept = l2[torch.from_numpy(keep).to(dev)].contiguous()
-    km = kmeans_fit(kept, k)
+    km = kmeans_fit(kept, k, seeding=seeding)
     _, nrm = cluster_medians(kept, km["labels"], k)
     return dict(local_density=dens_h, keep=keep, labels=km["labels"] + 1, median_spectra=nrm.cpu().numpy(),
-                l2_spectra=l2_host, inertia=km["inertia"], neighbors=nbr_h, n_iter=km["n_iter"])
+                l2_spectra=l2.cpu().numpy(), inertia=km["inertia"], neighbors=nbr_h, n_iter=km["n_iter"])
 

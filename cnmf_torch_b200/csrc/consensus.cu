@@ -420,6 +420,169 @@ __global__ void __launch_bounds__(256) row_normalize_kernel(const float* __restr
   for (int g = threadIdx.x; g < G; g += 256) out[(int64_t)j * G + g] = in[(int64_t)j * G + g] / s_total;
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// a8: rows / ||row||_2 exactly as the reference's pandas expression evaluates it for float32
+// (cnmf.py:1056): squares rounded to fp32, summed in fp32 in column order (pandas reduces the
+// transposed block, i.e. sequentially over genes -- checked bit-for-bit against pandas in
+// tests/test_oracle_golden.py), fp32 sqrt, fp32 division.  No FMA contraction.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128) l2_normalize_kernel(const float* __restrict__ S, int64_t lds, int M, int G,
+                                                           float* __restrict__ out, int64_t ldo) {
+  __shared__ float tile[128][33];
+  __shared__ float snorm[128];
+  const int m0 = blockIdx.x * 128, t = threadIdx.x;
+  float acc = 0.f;
+  for (int g0 = 0; g0 < G; g0 += 32) {
+    for (int i = t; i < 128 * 32; i += 128) {
+      const int r = i >> 5, c = i & 31;
+      tile[r][c] = (m0 + r < M && g0 + c < G) ? S[(int64_t)(m0 + r) * lds + g0 + c] : 0.f;
+    }
+    __syncthreads();
+    const int w = min(32, G - g0);
+    for (int c = 0; c < w; ++c) acc = __fadd_rn(acc, __fmul_rn(tile[t][c], tile[t][c]));
+    __syncthreads();
+  }
+  snorm[t] = __fsqrt_rn(acc);
+  __syncthreads();
+  for (int64_t i = t; i < (int64_t)128 * G; i += 128) {
+    const int r = (int)(i / G), c = (int)(i - (int64_t)r * G);
+    if (m0 + r < M) out[(int64_t)(m0 + r) * ldo + c] = __fdiv_rn(S[(int64_t)(m0 + r) * lds + c], snorm[r]);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// K10 seeding: k-means++ of all restarts side by side (sklearn/cluster/_kmeans.py:180-278).  The
+// random numbers come from the host (numpy RandomState stream, drawn in sklearn's order); distances
+// follow _euclidean_distances for float32 (fp64 accumulate, cast, clamp); the cumulative sum that
+// searchsorted scans is the sequential fp32 np.cumsum.
+// ---------------------------------------------------------------------------------------------
+constexpr int KPP_NC = 64;   // max candidates (n_init * n_trials) handled per pass
+constexpr int KPP_GC = 64;   // genes per chunk
+
+// one lane walks the fp32 running sum once and records, for each trial value, the first index whose
+// cumulative sum reaches it (np.searchsorted(np.cumsum(closest), rand * pot), side='left', clipped)
+__global__ void __launch_bounds__(32) kpp_pick_kernel(const float* __restrict__ closest, const float* __restrict__ pot,
+                                                      const double* __restrict__ rnd, int M, int T, int step,
+                                                      int ksteps, int* __restrict__ cand) {
+  const int init = blockIdx.x;
+  if (threadIdx.x != 0) return;
+  double val[8];
+  int found[8];
+  const double p = (double)pot[init];
+  for (int t = 0; t < T; ++t) {
+    val[t] = rnd[((int64_t)init * ksteps + step) * T + t] * p;
+    found[t] = M - 1;
+  }
+  const float* c = closest + (int64_t)init * M;
+  float acc = 0.f;
+  unsigned pending = (1u << T) - 1u;
+  for (int j = 0; j < M && pending; ++j) {
+    acc = __fadd_rn(acc, c[j]);
+    for (int t = 0; t < T; ++t)
+      if ((pending >> t & 1u) && (double)acc >= val[t]) { found[t] = j; pending &= ~(1u << t); }
+  }
+  for (int t = 0; t < T; ++t) cand[init * T + t] = found[t];
+}
+
+// distances from NC candidate rows to every point; dmin = min(closest, d); per-CTA potential partials
+__global__ void __launch_bounds__(256) kpp_dist_kernel(const float* __restrict__ X, int64_t ld, int M, int G,
+                                                       const double* __restrict__ xx, const int* __restrict__ cand,
+                                                       int NC, int T, const float* __restrict__ closest,
+                                                       float* __restrict__ dmin, double* __restrict__ potpart) {
+  __shared__ float cs[KPP_NC][KPP_GC + 1];
+  __shared__ int scand[KPP_NC];
+  __shared__ float sd[8][KPP_NC];
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m = blockIdx.x * 8 + w;
+  if (threadIdx.x < NC) scand[threadIdx.x] = cand[threadIdx.x];
+  __syncthreads();
+  double acc[KPP_NC];
+#pragma unroll
+  for (int c = 0; c < KPP_NC; ++c) acc[c] = 0.0;
+  for (int g0 = 0; g0 < G; g0 += KPP_GC) {
+    for (int i = threadIdx.x; i < NC * KPP_GC; i += 256) {
+      const int c = i / KPP_GC, g = i - c * KPP_GC;
+      cs[c][g] = (g0 + g < G) ? X[(int64_t)scand[c] * ld + g0 + g] : 0.f;
+    }
+    __syncthreads();
+    if (m < M) {
+      const double x0 = (g0 + lane < G) ? (double)X[(int64_t)m * ld + g0 + lane] : 0.0;
+      const double x1 = (g0 + lane + 32 < G) ? (double)X[(int64_t)m * ld + g0 + lane + 32] : 0.0;
+#pragma unroll
+      for (int c = 0; c < KPP_NC; ++c)
+        if (c < NC) acc[c] = fma(x1, (double)cs[c][lane + 32], fma(x0, (double)cs[c][lane], acc[c]));
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int c = 0; c < KPP_NC; ++c) {
+    if (c < NC) {
+      const double dot = warp_sum(acc[c]);
+      if (lane == 0) {
+        float f = 0.f;
+        if (m < M) {
+          double d = -2.0 * dot;
+          d += xx[scand[c]];
+          d += xx[m];
+          f = fmaxf((float)d, 0.f);
+          const int init = c / T;
+          if (closest != nullptr) f = fminf(closest[(int64_t)init * M + m], f);
+          dmin[(int64_t)c * M + m] = f;
+        }
+        sd[w][c] = f;
+      }
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x < NC) {
+    double t = 0.0;
+    for (int q = 0; q < 8; ++q) t += (double)sd[q][threadIdx.x];
+    potpart[(int64_t)blockIdx.x * NC + threadIdx.x] = t;
+  }
+}
+
+// per restart: potentials of its T candidates (fixed-order sum), first minimum wins; adopt it
+__global__ void __launch_bounds__(256) kpp_select_kernel(const double* __restrict__ potpart, int nblk, int NC, int T,
+                                                         int M, const int* __restrict__ cand,
+                                                         const float* __restrict__ dmin, float* __restrict__ closest,
+                                                         float* __restrict__ pot, int* __restrict__ chosen, int k,
+                                                         int step) {
+  const int init = blockIdx.x;
+  __shared__ double sp[8][8];
+  __shared__ int s_best;
+  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (w < T) {
+    double t = 0.0;
+    for (int b = lane; b < nblk; b += 32) t += potpart[(int64_t)b * NC + init * T + w];
+    t = warp_sum(t);
+    if (lane == 0) sp[w][0] = t;
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int best = 0;
+    float bv = (float)sp[0][0];
+    for (int t = 1; t < T; ++t) {
+      const float v = (float)sp[t][0];
+      if (v < bv) { bv = v; best = t; }
+    }
+    s_best = best;
+    pot[init] = bv;
+    chosen[init * k + step] = cand[init * T + best];
+  }
+  __syncthreads();
+  const float* src = dmin + ((int64_t)init * T + s_best) * M;
+  float* dst = closest + (int64_t)init * M;
+  for (int j = threadIdx.x; j < M; j += 256) dst[j] = src[j];
+}
+
+__global__ void kpp_gather_kernel(const float* __restrict__ X, int64_t ld, int G, const int* __restrict__ chosen,
+                                  float* __restrict__ centers) {
+  const int c = blockIdx.x;  // over n_init * k
+  const float* src = X + (int64_t)chosen[c] * ld;
+  for (int g = threadIdx.x; g < G; g += blockDim.x) centers[(int64_t)c * G + g] = src[g];
+}
+
 }  // namespace cnmf
 
 using namespace cnmf;
@@ -534,6 +697,70 @@ int cnmf_b200_cluster_median(const float* X, int64_t ld, int32_t G, const int32_
     row_normalize_kernel<<<k, 256, 0, st>>>(median, G, normalized);
     CNMF_LAUNCH_CHECK();
   }
+  return 0;
+}
+
+int cnmf_b200_l2_normalize(const float* S, int64_t lds, int32_t M, int32_t G, float* out, int64_t ldo, void* stream) {
+  CNMF_CHECK_ARG(S && out && M > 0 && G > 0 && lds >= G && ldo >= G, "l2_normalize: bad argument");
+  l2_normalize_kernel<<<(unsigned)ceil_div(M, 128), 128, 0, (cudaStream_t)stream>>>(S, lds, M, G, out, ldo);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+static int64_t kpp_layout(int32_t M, int32_t n_init, int32_t T, int64_t* o_xx, int64_t* o_closest, int64_t* o_dmin,
+                          int64_t* o_cand, int64_t* o_pot, int64_t* o_part) {
+  const int64_t nblk = ceil_div(M, 8), NC = (int64_t)n_init * T;
+  int64_t off = 0;
+  *o_xx = off; off += align_up((int64_t)M * 8, 256);
+  *o_closest = off; off += align_up((int64_t)n_init * M * 4, 256);
+  *o_dmin = off; off += align_up(NC * M * 4, 256);
+  *o_cand = off; off += align_up(NC * 4, 256);
+  *o_pot = off; off += align_up((int64_t)n_init * 4, 256);
+  *o_part = off; off += align_up(nblk * NC * 8, 256);
+  return off;
+}
+
+int64_t cnmf_b200_kmeanspp_workspace_bytes(int32_t M, int32_t n_init, int32_t n_trials) {
+  int64_t a, b, c, d, e, f;
+  return kpp_layout(M, n_init, n_trials, &a, &b, &c, &d, &e, &f);
+}
+
+int cnmf_b200_kmeanspp(const float* Xc, int64_t ld, int32_t M, int32_t G, int32_t n_init, int32_t k, int32_t n_trials,
+                       const int32_t* first_idx, const double* rnd, int32_t* chosen, float* centers, void* workspace,
+                       void* stream) {
+  CNMF_CHECK_ARG(Xc && first_idx && chosen && centers && workspace && (rnd || k == 1), "kmeanspp: null pointer");
+  CNMF_CHECK_ARG(M > 0 && G > 0 && k >= 1 && k <= M && ld >= G, "kmeanspp: bad shape");
+  CNMF_CHECK_ARG(n_trials >= 1 && n_trials <= 8 && n_init >= 1 && n_init * n_trials <= KPP_NC,
+                 "kmeanspp: n_init * n_trials must be <= %d and n_trials <= 8", KPP_NC);
+  cudaStream_t st = (cudaStream_t)stream;
+  int64_t o_xx, o_closest, o_dmin, o_cand, o_pot, o_part;
+  kpp_layout(M, n_init, n_trials, &o_xx, &o_closest, &o_dmin, &o_cand, &o_pot, &o_part);
+  char* ws = reinterpret_cast<char*>(workspace);
+  double* xx = reinterpret_cast<double*>(ws + o_xx);
+  float* closest = reinterpret_cast<float*>(ws + o_closest);
+  float* dmin = reinterpret_cast<float*>(ws + o_dmin);
+  int* cand = reinterpret_cast<int*>(ws + o_cand);
+  float* pot = reinterpret_cast<float*>(ws + o_pot);
+  double* part = reinterpret_cast<double*>(ws + o_part);
+  const int nblk = (int)ceil_div(M, 8);
+  row_sqnorm64_kernel<<<(unsigned)ceil_div(M, 8), 256, 0, st>>>(Xc, ld, M, G, xx);
+  CNMF_LAUNCH_CHECK();
+  // first centre: the host-drawn index; "one candidate per restart", nothing to take the minimum with
+  kpp_dist_kernel<<<nblk, 256, 0, st>>>(Xc, ld, M, G, xx, first_idx, n_init, 1, nullptr, dmin, part);
+  CNMF_LAUNCH_CHECK();
+  kpp_select_kernel<<<n_init, 256, 0, st>>>(part, nblk, n_init, 1, M, first_idx, dmin, closest, pot, chosen, k, 0);
+  CNMF_LAUNCH_CHECK();
+  const int NC = n_init * n_trials;
+  for (int c = 1; c < k; ++c) {
+    kpp_pick_kernel<<<n_init, 32, 0, st>>>(closest, pot, rnd, M, n_trials, c - 1, k - 1, cand);
+    CNMF_LAUNCH_CHECK();
+    kpp_dist_kernel<<<nblk, 256, 0, st>>>(Xc, ld, M, G, xx, cand, NC, n_trials, closest, dmin, part);
+    CNMF_LAUNCH_CHECK();
+    kpp_select_kernel<<<n_init, 256, 0, st>>>(part, nblk, NC, n_trials, M, cand, dmin, closest, pot, chosen, k, c);
+    CNMF_LAUNCH_CHECK();
+  }
+  kpp_gather_kernel<<<n_init * k, 128, 0, st>>>(Xc, ld, G, chosen, centers);
+  CNMF_LAUNCH_CHECK();
   return 0;
 }
 

@@ -167,6 +167,11 @@ int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream);
  * (cnmf.py:1056-1090) on the float32 dtype flow of this fork.
  * ---------------------------------------------------------------------------------------- */
 
+/* out = rows of S divided by their L2 norm, evaluated exactly as the reference's float32 pandas
+ * expression (cnmf.py:1056): fp32 squares summed in gene order, fp32 sqrt, fp32 division. */
+int cnmf_b200_l2_normalize(const float* S, int64_t lds, int32_t M, int32_t G, float* out, int64_t ldo,
+                           void* stream);
+
 /* D[M x M] = euclidean_distances(X) for float32 X as sklearn computes it (cnmf.py:1065;
  * sklearn/metrics/pairwise.py:376-427, 567-638): -2 x.y + |x|^2 + |y|^2 accumulated in fp64,
  * cast to fp32, clamped at 0, diagonal set to 0, square root in fp32.  sqnorm: [M] doubles scratch. */
@@ -204,6 +209,16 @@ int64_t cnmf_b200_kmeans_inertia_blocks(int32_t M);
 int cnmf_b200_kmeans_inertia(const float* X, int64_t ld, int32_t M, int32_t G, const float* centers,
                              int32_t n_init, int32_t k, const int32_t* labels, double* partials,
                              void* stream);
+
+/* k-means++ seeding of all restarts (sklearn/cluster/_kmeans.py:180-278, reached from cnmf.py:1083).
+ * The host draws the random numbers in sklearn's order from RandomState(random_state): first_idx[i] =
+ * choice(M) and rnd[i, c, :] = uniform(size=n_trials) for c = 1..k-1 (n_trials = 2 + int(log k)); the
+ * device does the distance / potential / searchsorted arithmetic.  chosen [n_init x k] receives the
+ * sample indices, centers [n_init x k x G] the rows.  n_init * n_trials <= 64, n_trials <= 8. */
+int64_t cnmf_b200_kmeanspp_workspace_bytes(int32_t M, int32_t n_init, int32_t n_trials);
+int cnmf_b200_kmeanspp(const float* Xc, int64_t ld, int32_t M, int32_t G, int32_t n_init, int32_t k,
+                       int32_t n_trials, const int32_t* first_idx, const double* rnd, int32_t* chosen,
+                       float* centers, void* workspace, void* stream);
 
 /* median[j, g] = median over the members of cluster j (rows order[offsets[j] : offsets[j+1]]) of
  * X[:, g]  (= l2_spectra.groupby(labels).median(), cnmf.py:1087); normalized (may be NULL) = rows of

@@ -28,10 +28,11 @@ def _spectra(k, n_rep, g, seed):
 def test_pairwise_distances_match_sklearn(k, n_rep, g):
     from sklearn.metrics.pairwise import euclidean_distances
     from cnmf_torch_b200 import consensus as cs
-    l2 = cs.l2_normalize_rows(_spectra(k, n_rep, g, 3))
-    np.testing.assert_array_equal(l2, co.l2_normalize(_spectra(k, n_rep, g, 3)))
+    l2d = cs.l2_normalize_rows(_spectra(k, n_rep, g, 3))
+    l2 = l2d.cpu().numpy()
+    np.testing.assert_array_equal(l2, co.l2_normalize(_spectra(k, n_rep, g, 3)))   # bit-identical to pandas
     ref = euclidean_distances(l2)
-    _, D, _ = cs.local_density_device(torch.from_numpy(l2).cuda(), 3)
+    _, D, _ = cs.local_density_device(l2d, 3)
     got = D.cpu().numpy()
     # fp64 accumulation then one rounding to fp32: equal except where the fp64 sums straddle a rounding
     # boundary (different summation order than OpenBLAS) -- at most 1 ulp and vanishingly rare
@@ -45,10 +46,11 @@ def test_pairwise_distances_match_sklearn(k, n_rep, g):
 def test_local_density_and_knn_sets(k, n_rep, g, lns):
     from cnmf_torch_b200 import consensus as cs
     s = _spectra(k, n_rep, g, 5)
-    l2 = cs.l2_normalize_rows(s)
+    l2d = cs.l2_normalize_rows(s)
+    l2 = l2d.cpu().numpy()
     n = co.n_neighbors_for(lns, s.shape[0], k)
     dens_ref, dist_ref, part_ref = co.local_density(l2, n)
-    dens, D, nbr = cs.local_density_device(torch.from_numpy(l2).cuda(), n, return_neighbors=True)
+    dens, D, nbr = cs.local_density_device(l2d, n, return_neighbors=True)
     np.testing.assert_allclose(dens.cpu().numpy(), dens_ref, rtol=2e-6)
     nbr = nbr.cpu().numpy()
     Dh = D.cpu().numpy()
@@ -59,16 +61,46 @@ def test_local_density_and_knn_sets(k, n_rep, g, lns):
         assert len(a) == n + 1 and i in a
 
 
+@pytest.mark.parametrize("seeding", ["device", "sklearn"])
 @pytest.mark.parametrize("k,n_rep,g", [(5, 30, 80), (8, 50, 300), (13, 100, 700)])
-def test_kmeans_labels_match_sklearn(k, n_rep, g):
+def test_kmeans_labels_match_sklearn(k, n_rep, g, seeding):
     from sklearn.cluster import KMeans
     from cnmf_torch_b200 import consensus as cs
-    l2 = cs.l2_normalize_rows(_spectra(k, n_rep, g, 11))
+    l2d = cs.l2_normalize_rows(_spectra(k, n_rep, g, 11))
+    l2 = l2d.cpu().numpy()
     ref = KMeans(n_clusters=k, n_init=10, random_state=1).fit(l2.copy())
-    out = cs.kmeans_fit(torch.from_numpy(l2).cuda(), k)
+    out = cs.kmeans_fit(l2d, k, seeding=seeding)
     np.testing.assert_array_equal(out["labels"], ref.labels_)
     assert abs(out["inertia"] - ref.inertia_) / ref.inertia_ < 1e-5
     np.testing.assert_allclose(out["centers"], ref.cluster_centers_, rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("k,n_rep,g", [(5, 30, 80), (8, 50, 300), (20, 200, 2000)])
+def test_device_seeding_picks_sklearns_centres(k, n_rep, g):
+    """k-means++ on the device against sklearn's own _kmeans_plusplus fed from the same RandomState."""
+    from sklearn.cluster._kmeans import _kmeans_plusplus
+    from sklearn.utils.extmath import row_norms
+    from cnmf_torch_b200 import consensus as cs
+    from cnmf_torch_b200._lib import lib, check, ptr
+    l2d = cs.l2_normalize_rows(_spectra(k, n_rep, g, 21))
+    Xc = l2d.clone()
+    mean = torch.empty(g, device="cuda")
+    check(lib().cnmf_b200_col_center(ptr(Xc), Xc.stride(0), Xc.shape[0], g, ptr(mean),
+                                     torch.cuda.current_stream().cuda_stream))
+    Xh = Xc.cpu().numpy()
+    ref_mean = l2d.cpu().numpy().mean(axis=0)
+    np.testing.assert_array_equal(mean.cpu().numpy(), ref_mean)            # numpy's axis-0 order reproduced
+    np.testing.assert_array_equal(Xh, l2d.cpu().numpy() - ref_mean)
+    rs = np.random.RandomState(1)
+    xsq = row_norms(Xh, squared=True)
+    w = np.ones(Xh.shape[0], dtype=np.float32)
+    ref_idx = np.stack([_kmeans_plusplus(Xh, k, xsq, w, rs)[1] for _ in range(10)])
+    centers, chosen = cs.kmeans_plusplus_device(Xc, k, 10, 1)
+    chosen = chosen.cpu().numpy()
+    same = (chosen == ref_idx).all(axis=1)
+    print(f"[k-means++ k={k} M={Xh.shape[0]}] restarts with identical centre indices: {same.sum()}/10")
+    assert same.sum() >= 9        # a differing pick needs a potential within fp32 round-off of a boundary
+    np.testing.assert_array_equal(centers.cpu().numpy()[same], Xh[ref_idx[same]])
 
 
 def test_cluster_medians_match_pandas():
@@ -86,13 +118,14 @@ def test_cluster_medians_match_pandas():
     np.testing.assert_allclose(nrm.cpu().numpy(), ref_n, rtol=2e-6)
 
 
+@pytest.mark.parametrize("seeding", ["device", "sklearn"])
 @pytest.mark.parametrize("tag", ["small", "nofilter", "tightfilter", "mid"])
-def test_consensus_front_half_matches_reference_golden(golden_dir, tag):
+def test_consensus_front_half_matches_reference_golden(golden_dir, tag, seeding):
     from cnmf_torch_b200 import consensus as cs
     g = _load(golden_dir, f"consensus_{tag}.npz")
     k = int(g["k"])
     n = co.n_neighbors_for(float(g["local_neighborhood_size"]), g["spectra"].shape[0], k)
-    out = cs.consensus_front_half(g["spectra"], k, float(g["density_threshold"]), n)
+    out = cs.consensus_front_half(g["spectra"], k, float(g["density_threshold"]), n, seeding=seeding)
     np.testing.assert_allclose(out["local_density"], g["local_density"], rtol=2e-6)
     np.testing.assert_array_equal(out["keep"], g["local_density"] < float(g["density_threshold"]))
     np.testing.assert_array_equal(out["labels"], g["labels"])
