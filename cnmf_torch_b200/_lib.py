@@ -33,7 +33,7 @@ class FrobProblem(C.Structure):
     ]
 
 
-class CsrProblem(C.Structure):
+class KlProblem(C.Structure):
     """Mirror of ``cnmf_b200_kl_problem``."""
     _fields_ = [
         ("n_cells", i64), ("n_genes", i64), ("nnz", i64),
@@ -65,6 +65,11 @@ SIGNATURES = {
     "cnmf_b200_round_tf32": (i32, [vp, i64, vp]),
     "cnmf_b200_dense_half_step": (i32, [vp, i64, i64, i64, vp, i64, vp, vp, i64, vp, vp, i32, i32, i32, f32, f32,
                                         f32, vp, vp]),
+    "cnmf_b200_kl_constants": (i32, [vp, i64, vp, vp]),
+    "cnmf_b200_kl_half_step": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, i32, i32, f32, f32, f32, vp]),
+    "cnmf_b200_kl_workspace_bytes": (i64, [C.POINTER(KlProblem)]),
+    "cnmf_b200_kl_iterate": (i32, [C.POINTER(KlProblem), i32, vp]),
+    "cnmf_b200_kl_objective": (i32, [C.POINTER(KlProblem), vp]),
     "cnmf_b200_l2_normalize": (i32, [vp, i64, i32, i32, vp, i64, vp]),
     "cnmf_b200_kmeanspp_workspace_bytes": (i64, [i32, i32, i32]),
     "cnmf_b200_kmeanspp": (i32, [vp, i64, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]),

@@ -163,6 +163,51 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
 int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream);
 
 /* ------------------------------------------------------------------------------------------
+ * Sparse Kullback-Leibler engine (replicate-batched, CSR X).  Replaces run_nmf(beta_loss=
+ * 'kullback-leibler', algo='mu') called at cnmf.py:819; update rule sklearn _nmf.py:562-607, 640-678
+ * restated with the reference's epsilon rule (cnmf.py:370-371).  Factors are replicate-interleaved:
+ *     Hr [N x R*Kp]  (row = cell),   Wt [G x R*Kp]  (row = gene),   element (row, r*Kp + k).
+ * ---------------------------------------------------------------------------------------- */
+
+/* out2[0] = sum of the stored values, out2[1] = sum x log x  (fp64): the constants of the KL objective
+ * (sklearn _nmf.py:113-157). */
+int cnmf_b200_kl_constants(const float* val, int64_t nnz, double* out2, void* stream);
+
+/* One half-step: for every CSR row m < M and replicate r,
+ *   state[m, r, k] <- state[m, r, k] * max(sum_j q_mj F[j, r, k] - l1, 0) / (fsum[r, k] + l2 state[m, r, k]),
+ *   q_mj = x_mj / max(sum_k state[m, r, k] F[j, r, k], eps) over the stored entries of row m,
+ * rate 0 where the denominator is below eps.  fsum[r*Kp + k] = sum_j F[j, r, k]. */
+int cnmf_b200_kl_half_step(const int32_t* row_ptr, const int32_t* col_idx, const float* val, int64_t M,
+                           const float* F, float* state, const float* fsum, const uint8_t* active,
+                           int32_t R, int32_t Kp, float l1, float l2, float eps, void* stream);
+
+typedef struct cnmf_b200_kl_problem {
+  int64_t n_cells, n_genes, nnz;
+  const int32_t* row_ptr;    /* CSR of X   : [N+1], [nnz], [nnz] */
+  const int32_t* col_idx;
+  const float* val;
+  const int32_t* t_row_ptr;  /* CSR of X^T : [G+1], [nnz], [nnz]  (X is static: built once) */
+  const int32_t* t_col_idx;
+  const float* t_val;
+  int32_t R, K, Kp, reserved;
+  float* Hr;                 /* [N x R*Kp] updated in place */
+  float* Wt;                 /* [G x R*Kp] updated in place */
+  const uint8_t* active;     /* [R] or NULL */
+  float l1_H, l2_H, l1_W, l2_W;
+  float eps, pad0;
+  double sumX, xlogx;        /* from cnmf_b200_kl_constants */
+  double* err2;              /* [R] out: 2 * (generalised KL divergence + L1 terms); may be NULL */
+  void* workspace;
+  int64_t workspace_bytes;
+} cnmf_b200_kl_problem;
+
+int64_t cnmf_b200_kl_workspace_bytes(const cnmf_b200_kl_problem* p);
+/* n_iters x { column sums of W; H half-step; column sums of H; W half-step }, then the objective. */
+int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* stream);
+/* err2 of the current state; factors untouched. */
+int cnmf_b200_kl_objective(const cnmf_b200_kl_problem* p, void* stream);
+
+/* ------------------------------------------------------------------------------------------
  * Consensus kernel set.  Replaces the library calls of cNMF.consensus' front half
  * (cnmf.py:1056-1090) on the float32 dtype flow of this fork.
  * ---------------------------------------------------------------------------------------- */
