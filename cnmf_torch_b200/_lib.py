@@ -65,6 +65,14 @@ SIGNATURES = {
     "cnmf_b200_round_tf32": (i32, [vp, i64, vp]),
     "cnmf_b200_dense_half_step": (i32, [vp, i64, i64, i64, vp, i64, vp, vp, i64, vp, vp, i32, i32, i32, f32, f32,
                                         f32, vp, vp]),
+    "cnmf_b200_frob_objective_parts": (i32, [C.POINTER(FrobProblem), vp, vp]),
+    "cnmf_b200_frob_objective_combine": (i32, [f64, vp, vp, vp, i32, i32, f32, f32, f32, f32, vp, vp]),
+    "cnmf_b200_dense_gemm_tf32": (i32, [vp, i64, i64, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp]),
+    "cnmf_b200_round_tf32_2d": (i32, [vp, vp, i64, i64, i64, vp]),
+    "cnmf_b200_axpy": (i32, [vp, vp, i64, vp]),
+    "cnmf_b200_online_inner_workspace_bytes": (i64, [i64, i32]),
+    "cnmf_b200_online_inner": (i32, [vp, i64, vp, i64, vp, vp, vp, i64, i32, i32, f32, f32, f32, f32, i32, vp, vp,
+                                     vp, vp]),
     "cnmf_b200_kl_constants": (i32, [vp, i64, vp, vp]),
     "cnmf_b200_kl_half_step": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, i32, i32, f32, f32, f32, vp]),
     "cnmf_b200_kl_workspace_bytes": (i64, [C.POINTER(KlProblem)]),

@@ -310,6 +310,44 @@ __global__ void __launch_bounds__(32) frob_objective_kernel(
   }
 }
 
+// row-sharded variant: first reduce the per-block partials to [R x 3] sums (cross, sum W, sum H) ...
+__global__ void __launch_bounds__(32) objective_sums_kernel(const double* __restrict__ partW, int nblkW,
+                                                            const double* __restrict__ partH, int nblkH, int R,
+                                                            double* __restrict__ sums) {
+  const int r = blockIdx.x, lane = threadIdx.x;
+  double cross = 0.0, sumW = 0.0, sumH = 0.0;
+  for (int b = lane; b < nblkW; b += 32) {
+    cross += partW[((int64_t)b * R + r) * 2 + 0];
+    sumW += partW[((int64_t)b * R + r) * 2 + 1];
+  }
+  for (int b = lane; b < nblkH; b += 32) sumH += partH[((int64_t)b * R + r) * 2 + 1];
+  cross = warp_sum(cross); sumW = warp_sum(sumW); sumH = warp_sum(sumH);
+  if (lane == 0) { sums[r * 3 + 0] = cross; sums[r * 3 + 1] = sumW; sums[r * 3 + 2] = sumH; }
+}
+
+// ... then, after the caller has summed them over ranks, combine with the Grams
+__global__ void __launch_bounds__(32) objective_combine_kernel(double normX2, const double* __restrict__ sums,
+                                                               const float* __restrict__ gramW,
+                                                               const float* __restrict__ gramH, int R, int Kp,
+                                                               float l1_H, float l2_H, float l1_W, float l2_W,
+                                                               double* __restrict__ err2) {
+  const int r = blockIdx.x, lane = threadIdx.x;
+  double tr = 0.0, trW = 0.0, trH = 0.0;
+  const int np = Kp * Kp;
+  for (int i = lane; i < np; i += 32) {
+    const double gw = gramW[(int64_t)r * np + i], gh = gramH[(int64_t)r * np + i];
+    tr += gw * gh;
+    if (i / Kp == i % Kp) { trW += gw; trH += gh; }
+  }
+  tr = warp_sum(tr); trW = warp_sum(trW); trH = warp_sum(trH);
+  if (lane == 0) {
+    double v = normX2 - 2.0 * sums[r * 3 + 0] + tr;
+    v += 2.0 * ((double)l1_H * sums[r * 3 + 2] + (double)l1_W * sums[r * 3 + 1]) + (double)l2_H * trH +
+         (double)l2_W * trW;
+    err2[r] = v;
+  }
+}
+
 // ---------------------------------------------------------------------------------------------
 // host-side launchers
 // ---------------------------------------------------------------------------------------------
@@ -357,6 +395,20 @@ int launch_frob_objective(double normX2, const double* partW, int nblkW, const d
                           float l2_H, float l1_W, float l2_W, double* err2, cudaStream_t st) {
   frob_objective_kernel<<<R, 32, 0, st>>>(normX2, partW, nblkW, partH, nblkH, gramW, gramH, R, Kp,
                                           l1_H, l2_H, l1_W, l2_W, err2);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_objective_sums(const double* partW, int nblkW, const double* partH, int nblkH, int R, double* sums,
+                          cudaStream_t st) {
+  objective_sums_kernel<<<R, 32, 0, st>>>(partW, nblkW, partH, nblkH, R, sums);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_objective_combine(double normX2, const double* sums, const float* gramW, const float* gramH, int R, int Kp,
+                             float l1_H, float l2_H, float l1_W, float l2_W, double* err2, cudaStream_t st) {
+  objective_combine_kernel<<<R, 32, 0, st>>>(normX2, sums, gramW, gramH, R, Kp, l1_H, l2_H, l1_W, l2_W, err2);
   CNMF_LAUNCH_CHECK();
   return 0;
 }

@@ -36,6 +36,8 @@ constexpr int TC_TMEM_COLS = 512;
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;  // 16 KiB
 constexpr int TC_SMEM_LIMIT = 227 * 1024;
 constexpr int TC_MAX_STAGES = 6;
+constexpr int TC_MODE_STORE = 2;  // epilogue modes beyond CNMF_B200_ALGO_MU (0) / _HALS (1)
+constexpr int TC_MODE_ACCUM = 3;
 
 struct TcParams {
   int64_t M;       // rows of A (and columns of the state array)
@@ -251,9 +253,11 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t tphase = (lt >> 1) & 1u;
       const int m_tile = tile / prm.num_n_tiles, n_tile = tile - m_tile * prm.num_n_tiles;
       const int r0 = n_tile * t;
-      for (int i = et; i < t * KP * KP; i += 128) {
-        const int rr = i / (KP * KP);
-        sgram[i] = (r0 + rr < prm.R) ? prm.gram[static_cast<int64_t>(r0) * KP * KP + i] : 0.f;
+      if (ALGO < TC_MODE_STORE) {
+        for (int i = et; i < t * KP * KP; i += 128) {
+          const int rr = i / (KP * KP);
+          sgram[i] = (r0 + rr < prm.R) ? prm.gram[static_cast<int64_t>(r0) * KP * KP + i] : 0.f;
+        }
       }
       epi_bar_sync();
       mbar_wait(&tfull[buf], tphase);
@@ -271,10 +275,19 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int64_t soff = static_cast<int64_t>(r) * KP * prm.lds + m;
         float* sp = prm.state + soff;
 #pragma unroll
-        for (int k = 0; k < KP; ++k) s[k] = in ? sp[static_cast<int64_t>(k) * prm.lds] : 0.f;
+        for (int k = 0; k < KP; ++k) s[k] = (in && ALGO != TC_MODE_STORE) ? sp[static_cast<int64_t>(k) * prm.lds] : 0.f;
         tmem_ld_wait();
         const bool act = prm.active == nullptr || prm.active[r] != 0;
         float cross = 0.f, ssum = 0.f;
+        if (ALGO >= TC_MODE_STORE) {
+          // plain GEMM epilogues of the online path: state = P (store) or state += P (accumulate)
+          if (in && act) {
+#pragma unroll
+            for (int k = 0; k < KP; ++k)
+              sp[static_cast<int64_t>(k) * prm.lds] = (ALGO == TC_MODE_ACCUM) ? s[k] + p[k] : p[k];
+          }
+          continue;
+        }
         if (in) {
           if (act) {
             update_row<KP, ALGO>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps);
@@ -304,7 +317,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       __syncwarp();
       if (lane == 0) mbar_arrive(&tempty[buf]);
       epi_bar_sync();
-      for (int i = et; i < t * 2; i += 128) {
+      for (int i = et; i < t * 2 && ALGO < TC_MODE_STORE; i += 128) {
         const int rr = i >> 1, r = r0 + rr;
         if (r < prm.R) {
           double v = 0.0;
@@ -329,6 +342,24 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 __global__ void round_tf32_kernel(float* __restrict__ dst, const float* __restrict__ src, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     dst[i] = to_tf32(src[i]);
+}
+
+__global__ void round_tf32_2d_kernel(float* __restrict__ dst, const float* __restrict__ src, int64_t rows, int64_t cols,
+                                     int64_t ld) {
+  const int64_t total = rows * cols;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / cols, c = i - r * cols;
+    dst[r * ld + c] = to_tf32(src[r * ld + c]);
+  }
+}
+
+int launch_round_tf32_2d(float* dst, const float* src, int64_t rows, int64_t cols, int64_t ld, cudaStream_t st) {
+  if (rows * cols == 0) return 0;
+  int64_t blocks = ceil_div(rows * cols, 256 * 8);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  round_tf32_2d_kernel<<<(unsigned)blocks, 256, 0, st>>>(dst, src, rows, cols, ld);
+  CNMF_LAUNCH_CHECK();
+  return 0;
 }
 
 int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st) {
@@ -492,6 +523,10 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
     CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_MU>(ma, mb, prm, plan, grid, st)));
   } else if (algo == CNMF_B200_ALGO_HALS) {
     CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_HALS>(ma, mb, prm, plan, grid, st)));
+  } else if (algo == TC_MODE_STORE) {
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, TC_MODE_STORE>(ma, mb, prm, plan, grid, st)));
+  } else if (algo == TC_MODE_ACCUM) {
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, TC_MODE_ACCUM>(ma, mb, prm, plan, grid, st)));
   }
   set_error("unknown algo %d", algo);
   return CNMF_B200_ERR_INVALID;

@@ -18,6 +18,9 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
                         int R, int Kp, int algo, float l1, float l2, float eps, double* partials,
                         cudaStream_t st);
 int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st);
+int launch_objective_sums(const double*, int, const double*, int, int, double*, cudaStream_t);
+int launch_objective_combine(double, const double*, const float*, const float*, int, int, float, float, float, float,
+                             double*, cudaStream_t);
 
 struct FrobLayout {
   int64_t off_pt, off_gram, off_partH, off_partW, off_zero, off_wop, off_hop, total;
@@ -175,18 +178,7 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
 
 /* Objective of the CURRENT state without changing it (used for the initial error that
  * normalises the convergence test, and after the last partial block). */
-int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
-  reset_launch_count();
-  CNMF_TRY(check_problem(p));
-  CNMF_TRY(check_pointers(p));
-  CNMF_CHECK_ARG(p->err2 != nullptr, "frob_objective: err2 is NULL");
-  FrobLayout l = frob_layout(p);
-  CNMF_CHECK_ARG(l.impl >= 0, "frob: tcgen05 path does not support this shape");
-  if (p->workspace_bytes < l.total) {
-    set_error("frob: workspace %lld < required %lld", (long long)p->workspace_bytes, (long long)l.total);
-    return CNMF_B200_ERR_WORKSPACE;
-  }
-  cudaStream_t st = (cudaStream_t)stream;
+static int frob_objective_partials(const cnmf_b200_frob_problem* p, const FrobLayout& l, cudaStream_t st) {
   char* ws = reinterpret_cast<char*>(p->workspace);
   float* Pt = reinterpret_cast<float*>(ws + l.off_pt);
   void* gws = ws + l.off_gram;
@@ -222,8 +214,56 @@ int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
                                    p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, st));
     }
   }
-  return launch_frob_objective(p->normX2, partW, l.nblkW, partH, l.nblkH, p->gramW, p->gramH, p->R, p->Kp,
+  return 0;
+}
+
+static int frob_objective_common(const cnmf_b200_frob_problem* p, FrobLayout* l) {
+  CNMF_TRY(check_problem(p));
+  CNMF_TRY(check_pointers(p));
+  *l = frob_layout(p);
+  CNMF_CHECK_ARG(l->impl >= 0, "frob: tcgen05 path does not support this shape");
+  if (p->workspace_bytes < l->total) {
+    set_error("frob: workspace %lld < required %lld", (long long)p->workspace_bytes, (long long)l->total);
+    return CNMF_B200_ERR_WORKSPACE;
+  }
+  return 0;
+}
+
+int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
+  reset_launch_count();
+  FrobLayout l;
+  CNMF_TRY(frob_objective_common(p, &l));
+  CNMF_CHECK_ARG(p->err2 != nullptr, "frob_objective: err2 is NULL");
+  cudaStream_t st = (cudaStream_t)stream;
+  CNMF_TRY(frob_objective_partials(p, l, st));
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  return launch_frob_objective(p->normX2, reinterpret_cast<double*>(ws + l.off_partW), l.nblkW,
+                               reinterpret_cast<double*>(ws + l.off_partH), l.nblkH, p->gramW, p->gramH, p->R, p->Kp,
                                p->l1_H, p->l2_H, p->l1_W, p->l2_W, p->err2, st);
+}
+
+/* Row-sharded form of the objective: the terms that are sums over this rank's cells.  sums[r*3 + 0] =
+ * <W_r, H_r^T X> (cross term), sums[r*3 + 1] = sum(W_r), sums[r*3 + 2] = sum(H_r) over the local rows;
+ * gramH = local H^T H, gramW = W W^T.  The caller all-reduces sums[:, 0], sums[:, 2] and gramH across
+ * ranks (W is replicated) and then calls cnmf_b200_frob_objective_combine. */
+int cnmf_b200_frob_objective_parts(const cnmf_b200_frob_problem* p, double* sums, void* stream) {
+  reset_launch_count();
+  FrobLayout l;
+  CNMF_TRY(frob_objective_common(p, &l));
+  CNMF_CHECK_ARG(sums != nullptr, "frob_objective_parts: sums is NULL");
+  cudaStream_t st = (cudaStream_t)stream;
+  CNMF_TRY(frob_objective_partials(p, l, st));
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  return launch_objective_sums(reinterpret_cast<double*>(ws + l.off_partW), l.nblkW,
+                               reinterpret_cast<double*>(ws + l.off_partH), l.nblkH, p->R, sums, st);
+}
+
+int cnmf_b200_frob_objective_combine(double normX2, const double* sums, const float* gramW, const float* gramH,
+                                     int32_t R, int32_t Kp, float l1_H, float l2_H, float l1_W, float l2_W,
+                                     double* err2, void* stream) {
+  CNMF_CHECK_ARG(sums && gramW && gramH && err2 && R > 0 && Kp > 0, "frob_objective_combine: bad argument");
+  return launch_objective_combine(normX2, sums, gramW, gramH, R, Kp, l1_H, l2_H, l1_W, l2_W, err2,
+                                  (cudaStream_t)stream);
 }
 
 }  // extern "C"

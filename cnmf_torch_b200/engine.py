@@ -58,9 +58,13 @@ class BatchResult:
 class DenseFrobeniusEngine:
     """X resident as dense fp32 [N x G] and its transpose [G x N]; Frobenius MU / HALS."""
 
-    def __init__(self, X, device="cuda:0", impl=_lib.IMPL_AUTO):
+    def __init__(self, X, device="cuda:0", impl=_lib.IMPL_AUTO, row_group=None, row_offset=0):
+        """``row_group``: torch.distributed group over which the CELLS are sharded (online mode for very
+        large N); X is then this rank's block of rows and ||X||^2 / mean(X) are made global."""
         self.lib = lib()  # raises if the CUDA library is missing -- no fallback
         self.impl = impl
+        self.row_group = row_group
+        self.row_offset = int(row_offset)  # first global row of this rank's block
         if not torch.cuda.is_available():
             raise _lib.Cnmfb200Error("CUDA device required: cnmf_torch_b200 has no CPU path")
         self.device = torch.device(device)
@@ -82,7 +86,13 @@ class DenseFrobeniusEngine:
         check(self.lib.cnmf_b200_sumsq(ptr(self.X), self.N, self.G, self.ldx, ptr(out), ptr(ws), st), "sumsq")
         self.normX2 = float(out[0].item())
         # mean(X) for the random init, fp64 on device
-        self.x_mean = float(self.X[:, :self.G].sum(dtype=torch.float64).item()) / (self.N * self.G)
+        x_sum = float(self.X[:, :self.G].sum(dtype=torch.float64).item())
+        self.N_total = self.N
+        if row_group is not None:
+            from . import dist as _d
+            tot = _d.allreduce_scalars([self.normX2, x_sum, float(self.N)], self.device, row_group)
+            self.normX2, x_sum, self.N_total = float(tot[0]), float(tot[1]), int(round(tot[2]))
+        self.x_mean = x_sum / (float(self.N_total) * self.G)
         if impl != _lib.IMPL_SIMT:
             # static operands of the tcgen05 path: round once to tf32 (nearest) so that the tensor
             # core's mantissa truncation is unbiased; ||X||^2 and mean(X) above come from the fp32 X
@@ -93,8 +103,10 @@ class DenseFrobeniusEngine:
     def make_init(self, K: int, seeds):
         hs, ws = [], []
         for s in seeds:
-            h, w = init_random(self.x_mean, self.N, self.G, K, int(s))
-            hs.append(h)
+            # row-sharded: draw the GLOBAL H0 and keep this rank's rows, so a sharded run starts from
+            # exactly the state a single-GPU run would
+            h, w = init_random(self.x_mean, self.N_total, self.G, K, int(s))
+            hs.append(h[self.row_offset:self.row_offset + self.N])
             ws.append(w)
         return torch.stack(hs), torch.stack(ws)
 
@@ -147,6 +159,135 @@ class DenseFrobeniusEngine:
         W, H = b.results(return_H)
         return BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_iter,
                            trace=trace, launches=int(b.launches))
+
+    # ------------------------------------------------------------------------------------
+    def factorize_online(self, K: int, seeds=None, H0=None, W0=None, tol=1e-4, max_pass=20, chunk_size=5000,
+                         chunk_max_iter=200, h_tol=0.05, w_tol=0.05, l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0,
+                         eps=EPS_DEFAULT, return_H=False, inner_batch=4) -> BatchResult:
+        """Online-mode Frobenius MU of R replicates (run_nmf(mode='online'), what cNMF configures at
+        cnmf.py:757-771).  Per pass and per chunk of ``chunk_size`` cells: inner MU loop on h against the
+        cached x W^T (stopping rule of cnmf.py:365-378), A += h^T h, B += h^T x, inner MU loop on W against
+        (A, B); then H is refreshed on all cells and the objective decides convergence per replicate.
+        With ``row_group`` the cells are sharded over ranks: A, B and the objective terms are summed with
+        one all-reduce per chunk; W stays replicated (every rank runs the same W loop on the same sums)."""
+        from . import dist as _d
+        if self.impl == _lib.IMPL_SIMT:
+            raise NotImplementedError("online mode runs on the tcgen05 path (impl auto/tcgen05)")
+        if chunk_size % 4 != 0:
+            raise ValueError("online_chunk_size must be a multiple of 4 (16-byte aligned chunk operands)")
+        L, dev, grp = self.lib, self.device, self.row_group
+        if H0 is None or W0 is None:
+            H0, W0 = self.make_init(K, seeds)
+        b = FrobBatch(self, K, H0, W0, "mu", l1_H, l2_H, l1_W, l2_W, eps)
+        R, Kp, N, G = b.R, b.Kp, self.N, self.G
+        rk = R * Kp
+        ldw, ldh = b.p.ldw, b.p.ldh
+        st = FrobBatch._stream
+        cmax = max(1, min(chunk_size, N))
+        ldp = pad_ld(cmax)
+        f32 = dict(device=dev, dtype=torch.float32)
+        Pt = torch.zeros((rk, ldp), **f32)
+        Bst = torch.zeros((rk, ldw), **f32)
+        Bc = torch.zeros((rk, ldw), **f32)
+        A = torch.zeros((R, Kp, Kp), **f32)
+        Ac = torch.zeros((R, Kp, Kp), **f32)
+        Wop = torch.zeros((rk, ldw), **f32)
+        Hop = torch.zeros((rk, ldh), **f32)
+        done = torch.zeros(R, device=dev, dtype=torch.uint8)
+        iters = torch.zeros(R, device=dev, dtype=torch.int32)
+        npend = torch.zeros(1, device=dev, dtype=torch.int32)
+        ws_inner = torch.empty(max(256, int(L.cnmf_b200_online_inner_workspace_bytes(max(cmax, G), R))), device=dev,
+                               dtype=torch.uint8)
+        ws_gram = torch.empty(max(256, int(L.cnmf_b200_gram_workspace_bytes(R, Kp, max(cmax, G)))), device=dev,
+                              dtype=torch.uint8)
+        Wall, Ht, active = b.Wall, b.Ht, b.active
+        n_chunks = _d.allreduce_max_int((N + chunk_size - 1) // chunk_size, dev, grp)
+        inner_total = [0, 0]
+
+        def refresh_w_caches():
+            check(L.cnmf_b200_round_tf32_2d(ptr(Wop), ptr(Wall), rk, G, ldw, st()), "round_tf32_2d")
+            check(L.cnmf_b200_gram(ptr(Wall), ldw, R, Kp, G, ptr(b.gramW), ptr(ws_gram), st()), "gram")
+
+        def inner(p_ptr, p_ld, s_ptr, s_ld, g_ptr, M, tol_, l1, l2, which):
+            done.zero_()
+            n_done = 0
+            while n_done < chunk_max_iter:
+                n = min(inner_batch, chunk_max_iter - n_done)
+                check(L.cnmf_b200_online_inner(p_ptr, p_ld, s_ptr, s_ld, g_ptr, ptr(done), ptr(active), M, R, Kp,
+                                               l1, l2, eps, tol_, n, ptr(iters), ptr(npend), ptr(ws_inner), st()),
+                      "online_inner")
+                b.launches += L.cnmf_b200_last_launch_count()
+                n_done += n
+                inner_total[which] += n
+                if int(npend.item()) == 0:       # 4-byte D2H every `inner_batch` iterations
+                    break
+
+        def h_chunk(lo, c):
+            check(L.cnmf_b200_dense_gemm_tf32(ptr(self.X) + 4 * lo * self.ldx, self.ldx, c, G, ptr(Wop), ldw, ptr(Pt),
+                                              ldp, ptr(active), R, Kp, 0, st()), "gemm x W^T")
+            b.launches += 1
+            inner(ptr(Pt), ldp, ptr(Ht) + 4 * lo, ldh, ptr(b.gramW), c, h_tol, l1_H, l2_H, 0)
+
+        def objective():
+            check(L.cnmf_b200_frob_prepare(C.byref(b.p), st()), "frob_prepare")
+            if grp is None:
+                return b.objective()
+            sums = torch.zeros((R, 3), device=dev, dtype=torch.float64)
+            check(L.cnmf_b200_frob_objective_parts(C.byref(b.p), ptr(sums), st()), "objective_parts")
+            sw = sums[:, 1].clone()
+            _d.allreduce_sum_([sums, b.gramH], grp)
+            sums[:, 1] = sw                       # W is replicated: its sum must not be multiplied by P
+            check(L.cnmf_b200_frob_objective_combine(self.normX2, ptr(sums), ptr(b.gramW), ptr(b.gramH), R, Kp,
+                                                     l1_H, l2_H, l1_W, l2_W, ptr(b.err2), st()), "objective_combine")
+            return b.read_loss()
+
+        refresh_w_caches()
+        init = objective()
+        prev, cur = init.copy(), init
+        trace = [(0, init.copy())]
+        n_pass = np.full(R, max_pass, dtype=np.int64)
+        alive = np.ones(R, dtype=bool)
+        for ps in range(1, max_pass + 1):
+            A.zero_()
+            Bst.zero_()
+            for ci in range(n_chunks):
+                lo = ci * chunk_size
+                c = max(0, min(chunk_size, N - lo))
+                Ac.zero_()
+                Bc.zero_()
+                if c > 0:
+                    h_chunk(lo, c)
+                    check(L.cnmf_b200_gram(ptr(Ht) + 4 * lo, ldh, R, Kp, c, ptr(Ac), ptr(ws_gram), st()), "gram")
+                    check(L.cnmf_b200_round_tf32_2d(ptr(Hop) + 4 * lo, ptr(Ht) + 4 * lo, rk, c, ldh, st()), "round")
+                    check(L.cnmf_b200_dense_gemm_tf32(ptr(self.Xt) + 4 * lo, self.ldxt, G, c, ptr(Hop) + 4 * lo, ldh,
+                                                      ptr(Bc), ldw, ptr(active), R, Kp, 0, st()), "gemm h^T x")
+                    b.launches += 4
+                _d.allreduce_sum_([Ac, Bc], grp)          # the only data-path collective
+                check(L.cnmf_b200_axpy(ptr(A), ptr(Ac), A.numel(), st()), "axpy")
+                check(L.cnmf_b200_axpy(ptr(Bst), ptr(Bc), Bst.numel(), st()), "axpy")
+                inner(ptr(Bst), ldw, ptr(Wall), ldw, ptr(A), G, w_tol, l1_W, l2_W, 1)
+                refresh_w_caches()
+                b.launches += 5
+            for ci in range(n_chunks):                    # end of pass: H on every cell against the final W
+                lo = ci * chunk_size
+                c = max(0, min(chunk_size, N - lo))
+                if c > 0:
+                    h_chunk(lo, c)
+            cur = objective()
+            trace.append((ps, cur.copy()))
+            conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
+            if conv.any():
+                n_pass[conv] = ps
+                alive &= ~conv
+                b.set_active(alive)
+            prev = np.where(alive, cur, prev)
+            if not alive.any():
+                break
+        W, H = b.results(return_H)
+        res = BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_pass, trace=trace,
+                          launches=int(b.launches))
+        res.inner_iterations = {"h": inner_total[0], "w": inner_total[1]}
+        return res
 
 
 class FrobBatch:

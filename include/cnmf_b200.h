@@ -162,6 +162,42 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
  * refreshed).  Gives the initial error that normalises run_nmf's convergence test. */
 int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream);
 
+/* Row-sharded objective (cells split over ranks, W replicated): _parts leaves the rank-local terms --
+ * sums[r*3+0] = <W_r, H_r^T X> over the local cells, sums[r*3+1] = sum(W_r), sums[r*3+2] = local sum(H_r),
+ * gramH = local H^T H, gramW = W W^T -- the caller adds sums[:,0], sums[:,2] and gramH over ranks
+ * (ncclAllReduce, sum) and _combine forms err2 with the global ||X||^2. */
+int cnmf_b200_frob_objective_parts(const cnmf_b200_frob_problem* p, double* sums, void* stream);
+int cnmf_b200_frob_objective_combine(double normX2, const double* sums, const float* gramW, const float* gramH,
+                                     int32_t R, int32_t Kp, float l1_H, float l2_H, float l1_W, float l2_W,
+                                     double* err2, void* stream);
+
+/* ------------------------------------------------------------------------------------------
+ * Online mode building blocks (run_nmf(mode='online'), the mode cNMF itself configures at
+ * cnmf.py:757-771).  Per chunk of online_chunk_size cells: P = x W^T once, inner MU loop on h until
+ * its relative change < h_tol (the reference's own fit_H_online, cnmf.py:355-378), A += h^T h,
+ * B += h^T x, inner MU loop on W against (A, B) until w_tol.
+ * ---------------------------------------------------------------------------------------- */
+
+/* out[R*Kp x M] (= or +=) F[R*Kp x Kd] * A[M x Kd]^T on the tensor cores (tf32 operands, fp32
+ * accumulate); accumulate != 0 adds to out.  The GEMMs x @ W.T and h.T @ x of the online loop. */
+int cnmf_b200_dense_gemm_tf32(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                              float* out, int64_t ldo, const uint8_t* active, int32_t R, int32_t Kp,
+                              int32_t accumulate, void* stream);
+/* dst = round-to-nearest tf32 of a [rows x cols] block with row pitch ld (both arrays). */
+int cnmf_b200_round_tf32_2d(float* dst, const float* src, int64_t rows, int64_t cols, int64_t ld, void* stream);
+/* y += x  (A += h^T h). */
+int cnmf_b200_axpy(float* y, const float* x, int64_t n, void* stream);
+
+/* n_iters x { s <- s * max(p - l1, 0) / (s G + l2 s) on every column of state [R*Kp x M];
+ *             rel_r = ||new - old||_F / (||old||_F + eps);  iters[r] += 1;  done[r] = (rel_r < tol) }
+ * for the replicates with done[r] == 0 (and active[r] != 0).  n_pending[0] = replicates still running
+ * after the last iteration.  (cnmf.py:365-378; also the W loop on the sufficient statistics.) */
+int64_t cnmf_b200_online_inner_workspace_bytes(int64_t M, int32_t R);
+int cnmf_b200_online_inner(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram, uint8_t* done,
+                           const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
+                           float tol, int32_t n_iters, int32_t* iters, int32_t* n_pending, void* workspace,
+                           void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Sparse Kullback-Leibler engine (replicate-batched, CSR X).  Replaces run_nmf(beta_loss=
  * 'kullback-leibler', algo='mu') called at cnmf.py:819; update rule sklearn _nmf.py:562-607, 640-678
