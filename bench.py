@@ -144,6 +144,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
+    ap.add_argument("--streams", type=int, default=1, help="1: one stream per K-batch (default); 0: single stream")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
@@ -175,9 +176,11 @@ def main():
     batches = [eng.new_batch(k, seeds=seeds[i], algo=ALGO) for i, k in enumerate(KS)]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
+    from cnmf_torch_b200.engine import iterate_concurrently
+    streams = [torch.cuda.Stream(device=dev) for _ in batches] if args.streams else None
+
     def one_step():
-        for b in batches:
-            b.iterate(ITERS_PER_STEP)
+        iterate_concurrently(batches, ITERS_PER_STEP, streams)
 
     for _ in range(args.warmup):
         one_step()
@@ -241,12 +244,12 @@ def main():
     # ---------------- end-to-end arm: public API with host buffers -----------------------------
     def e2e_step():
         e = DenseFrobeniusEngine(x_pinned, device=dev, impl=impl)         # H2D of X (pinned)
-        out, h2d, d2h = [], x_pinned.numel() * 4, 0
-        for i, k in enumerate(KS):
-            r = e.factorize(k, seeds=seeds[i], algo=ALGO, tol=0.0, max_iter=E2E_ITERS)  # init H2D, W D2H
+        h2d, d2h = x_pinned.numel() * 4, 0
+        res = e.factorize_many(KS, {k: seeds[i] for i, k in enumerate(KS)}, algo=ALGO, tol=0.0,
+                               max_iter=E2E_ITERS)                        # host init, H2D, all K, D2H of spectra
+        for k in KS:
             h2d += REPLICATES * k * (N_CELLS + N_GENES) * 4
-            d2h += r.W.nbytes + (E2E_ITERS // 10 + 1) * REPLICATES * 8
-            out.append(r.err)
+            d2h += res[k].W.nbytes + (E2E_ITERS // 10 + 1) * REPLICATES * 8
         return h2d, d2h
     e2e_step()
     torch.cuda.synchronize()
@@ -279,8 +282,9 @@ def main():
             "data": "synthetic",
             "config": {"workload": WORKLOAD, "replicates_per_gpu": len(KS) * REPLICATES,
                        "l2_flush_between_steps": True, "path": args.path,
-                       "e2e_step": f"DenseFrobeniusEngine(X_pinned) + factorize(K, seeds, hals, tol=0, "
-                                   f"max_iter={E2E_ITERS}) for K=7..12 (host init, H2D, D2H of spectra)"},
+                       "k_batches_on_separate_streams": bool(args.streams),
+                       "e2e_step": f"DenseFrobeniusEngine(X_pinned).factorize_many(K=7..12, seeds, hals, tol=0, "
+                                   f"max_iter={E2E_ITERS}): host init draws, H2D of X and inits, D2H of spectra"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
         }

@@ -196,6 +196,23 @@ class cNMF:
                                         "l1_ratio_H", "batch_max_iter", "online_max_pass", "online_chunk_size",
                                         "online_chunk_max_iter", "online_h_tol", "online_w_tol") if k in kw}
         sel = run_params.iloc[jobs, :]
+        if (kw.get("mode", "batch") == "batch" and hasattr(engine, "factorize_many") and not max_batch
+                and engine_kw.get("init", "random") == "random"):
+            # all K at once: K-batches overlap on separate streams (engine.factorize_many)
+            from .nmf import _reg
+            groups = {int(k): g for k, g in sel.groupby("n_components", sort=True)}
+            print("[Worker %d]. Starting %d tasks: %s." % (worker_i, len(sel), ", ".join(
+                "k=%d x %d replicates" % (k, len(g)) for k, g in groups.items())))
+            reg = _reg(engine_kw.get("alpha_W", 0.0), engine_kw.get("l1_ratio_W", 0.0),
+                       engine_kw.get("alpha_H", 0.0), engine_kw.get("l1_ratio_H", 0.0))
+            res = engine.factorize_many(list(groups), {k: [int(s) for s in g["nmf_seed"]] for k, g in groups.items()},
+                                        algo=engine_kw.get("algo", "mu"), tol=engine_kw.get("tol", 1e-4),
+                                        max_iter=int(engine_kw.get("batch_max_iter", 500)), **reg)
+            for k, g in groups.items():
+                for j, (_, p) in enumerate(g.iterrows()):
+                    spectra = pd.DataFrame(res[k].W[j], index=np.arange(1, k + 1), columns=var_names)
+                    save_df_to_npz(spectra, self.paths["iter_spectra"] % (k, int(p["iter"])))
+            return
         for k, grp in sel.groupby("n_components", sort=True):
             k = int(k)
             idx = list(grp.index)
@@ -243,6 +260,25 @@ class cNMF:
         else:
             print("No spectra found for k=%d" % k)
         return combined
+
+    # ---- usage refit (cnmf.py:923-994) ---------------------------------------------------------------
+    def refit_usage(self, X, spectra, usage=None, seed=None):
+        """cnmf.py:923-976: kwargs from the YAML -> fit_H_online (chunk size / max iterations from the
+        run parameters, h_tol 0.05, L1 strength = l1_ratio_H as the reference passes it).  Frobenius only,
+        like the reference's fit_H_online."""
+        from .refit import fit_H_online
+        with open(self.paths["nmf_run_parameters"]) as F:
+            kw = yaml.load(F, Loader=yaml.FullLoader)
+        return fit_H_online(X, spectra, H_init=usage, chunk_size=kw["online_chunk_size"],
+                            chunk_max_iter=kw["online_chunk_max_iter"], h_tol=0.05, l1_reg_H=kw["l1_ratio_H"],
+                            l2_reg_H=0.0, epsilon=1e-16, device=self.device, seed=seed)
+
+    def refit_spectra(self, X, usage, seed=None):
+        """cnmf.py:979-994: the transposed problem."""
+        X = getattr(X, "values", X)
+        usage = getattr(usage, "values", usage)
+        Xt = X.T.tocsr() if sp.issparse(X) else np.ascontiguousarray(np.asarray(X).T)
+        return self.refit_usage(Xt, np.ascontiguousarray(np.asarray(usage).T), seed=seed).T
 
     # ---- consensus, front half (cnmf.py:997-1090) -------------------------------------------------
     def consensus(self, k, density_threshold=0.5, local_neighborhood_size=0.30, show_clustering=False,

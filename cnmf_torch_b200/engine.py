@@ -101,14 +101,30 @@ class DenseFrobeniusEngine:
 
     # ------------------------------------------------------------------------------------
     def make_init(self, K: int, seeds):
-        hs, ws = [], []
-        for s in seeds:
+        """H0 [R, N, K], W0 [R, K, G] on the host (pinned), one torch CPU generator per replicate seed --
+        the draws nmf-torch's CPU path would make.  Replicates are drawn by a small thread pool (torch.randn
+        releases the GIL) straight into pinned staging buffers."""
+        from concurrent.futures import ThreadPoolExecutor
+        seeds = [int(s) for s in seeds]
+        R = len(seeds)
+        pin = torch.cuda.is_available()
+        H0 = torch.empty((R, self.N, K), dtype=torch.float32, pin_memory=pin)
+        W0 = torch.empty((R, K, self.G), dtype=torch.float32, pin_memory=pin)
+
+        def one(i):
             # row-sharded: draw the GLOBAL H0 and keep this rank's rows, so a sharded run starts from
             # exactly the state a single-GPU run would
-            h, w = init_random(self.x_mean, self.N_total, self.G, K, int(s))
-            hs.append(h[self.row_offset:self.row_offset + self.N])
-            ws.append(w)
-        return torch.stack(hs), torch.stack(ws)
+            h, w = init_random(self.x_mean, self.N_total, self.G, K, seeds[i])
+            H0[i].copy_(h[self.row_offset:self.row_offset + self.N])
+            W0[i].copy_(w)
+
+        if R <= 2:
+            for i in range(R):
+                one(i)
+        else:
+            with ThreadPoolExecutor(max_workers=min(8, R)) as pool:
+                list(pool.map(one, range(R)))
+        return H0, W0
 
     def _upload_state(self, H0, W0, K, Kp):
         R = int(W0.shape[0])
@@ -135,30 +151,25 @@ class DenseFrobeniusEngine:
         Convergence per replicate as run_nmf: every ``check_every`` iterations,
         stop when prev <= cur or |prev - cur| / init < tol; converged replicates are frozen."""
         b = self.new_batch(K, seeds, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps)
-        R = b.R
-        init = b.objective()
-        prev = init.copy()
-        trace = [(0, init.copy())]
-        n_iter = np.full(R, max_iter, dtype=np.int64)
-        alive = np.ones(R, dtype=bool)
-        it = 0
-        cur = init
-        while it < max_iter and alive.any():
-            step = min(check_every, max_iter - it)
-            b.iterate(step)
-            it += step
-            cur = b.read_loss()  # one small D2H per check period
-            trace.append((it, cur.copy()))
-            if it % check_every == 0:
-                conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
-                if conv.any():
-                    n_iter[conv] = it
-                    alive &= ~conv
-                    b.set_active(alive)
-                prev = np.where(alive, cur, prev)
-        W, H = b.results(return_H)
-        return BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_iter,
-                           trace=trace, launches=int(b.launches))
+        return run_batches([b], tol, max_iter, check_every, return_H)[0]
+
+    def factorize_many(self, ks, seeds_by_k, algo="mu", tol=1e-4, max_iter=500, l1_H=0.0, l2_H=0.0, l1_W=0.0,
+                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False):
+        """Several K at once (the shape of a cNMF run: K = 5..13 x 100 replicates).  The K-batches are
+        independent, so their kernels run on separate streams and overlap, their inits are drawn by a
+        thread pool while earlier batches are already uploading, and convergence is checked for all of
+        them in lock-step (one small D2H per batch per check period).  Returns {K: BatchResult}."""
+        from concurrent.futures import ThreadPoolExecutor
+        ks = [int(k) for k in ks]
+        with ThreadPoolExecutor(max_workers=max(1, min(len(ks), 4))) as pool:
+            futs = [pool.submit(self.make_init, k, seeds_by_k[k]) for k in ks]
+            batches = []
+            for k, f in zip(ks, futs):
+                H0, W0 = f.result()
+                batches.append(FrobBatch(self, k, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps))
+        streams = [torch.cuda.Stream(device=self.device) for _ in batches]
+        res = run_batches(batches, tol, max_iter, check_every, return_H, streams)
+        return dict(zip(ks, res))
 
     # ------------------------------------------------------------------------------------
     def factorize_online(self, K: int, seeds=None, H0=None, W0=None, tol=1e-4, max_pass=20, chunk_size=5000,
@@ -288,6 +299,60 @@ class DenseFrobeniusEngine:
                           launches=int(b.launches))
         res.inner_iterations = {"h": inner_total[0], "w": inner_total[1]}
         return res
+
+
+def run_batches(batches, tol, max_iter, check_every=10, return_H=False, streams=None):
+    """run_nmf's batch loop for a list of resident batches in lock-step: every ``check_every`` iterations the
+    objective of every replicate is read back (R doubles per batch) and replicates with
+    prev <= cur or |prev - cur| / init < tol are frozen (their state stops changing on the device)."""
+    st = [dict(init=b.objective()) for b in batches]
+    for s, b in zip(st, batches):
+        s.update(prev=s["init"].copy(), cur=s["init"], trace=[(0, s["init"].copy())],
+                 n_iter=np.full(b.R, max_iter, dtype=np.int64), alive=np.ones(b.R, dtype=bool))
+    it = 0
+    while it < max_iter and any(s["alive"].any() for s in st):
+        step = min(check_every, max_iter - it)
+        live = [i for i, s in enumerate(st) if s["alive"].any()]
+        iterate_concurrently([batches[i] for i in live], step, [streams[i] for i in live] if streams else None)
+        it += step
+        for i in live:
+            s, b = st[i], batches[i]
+            cur = b.read_loss()
+            s["cur"] = cur
+            s["trace"].append((it, cur.copy()))
+            if it % check_every == 0:
+                conv = s["alive"] & ((s["prev"] <= cur) | (np.abs((s["prev"] - cur) / s["init"]) < tol))
+                if conv.any():
+                    s["n_iter"][conv] = it
+                    s["alive"] &= ~conv
+                    b.set_active(s["alive"])
+                s["prev"] = np.where(s["alive"], cur, s["prev"])
+    out = []
+    for s, b in zip(st, batches):
+        W, H = b.results(return_H)
+        out.append(BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * s["cur"], 0.0)), n_iter=s["n_iter"],
+                               trace=s["trace"], launches=int(b.launches)))
+    return out
+
+
+def iterate_concurrently(batches, n: int, streams=None):
+    """Enqueue ``n`` iterations of several independent batches (different K) on side streams that fork
+    from / join into the current stream, so that their kernels overlap: one K-batch alone leaves SMs idle
+    (its persistent GEMM has fewer tiles than SMs and its small Gram kernels are latency-bound)."""
+    cur = torch.cuda.current_stream()
+    if streams is None or len(batches) == 1:
+        for b in batches:
+            b.iterate(n)
+        return
+    fork = torch.cuda.Event()
+    fork.record(cur)
+    for b, s in zip(batches, streams):
+        s.wait_event(fork)
+        with torch.cuda.stream(s):
+            b.iterate(n)
+        done = torch.cuda.Event()
+        done.record(s)
+        cur.wait_event(done)
 
 
 class FrobBatch:

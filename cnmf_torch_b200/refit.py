@@ -1,0 +1,83 @@
+"""``fit_H_online`` on the GPU -- the usage refit that follows the consensus front half
+(/root/reference/src/cnmf/cnmf.py:260-388, called through ``refit_usage`` / ``refit_spectra`` at
+cnmf.py:923-994, 1093, 1126, 1148).  Same signature and stopping rule as the reference; the arithmetic is
+the online engine's own building blocks with the spectra held fixed: per chunk one fp32 GEMM x W^T, then
+the inner multiplicative-update loop until the relative change of h falls below ``h_tol``.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+from . import _lib
+from ._lib import check, lib, ptr
+from .engine import pad4
+
+
+def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0.05, l1_reg_H=0.0, l2_reg_H=0.0,
+                 epsilon=1e-16, device="cuda:0", seed=None, inner_batch=4):
+    """Online MU for H with W fixed.  X: cells x genes (array, DataFrame or scipy sparse), W: programs x genes.
+    ``H_init=None`` draws uniform(0, 1) like the reference (cnmf.py:342-343) -- from a generator seeded with
+    ``seed`` when given, which the reference does not offer (its refit is not reproducible).  ``device`` must be
+    a CUDA device: there is no CPU path here.  Returns H as a float32 numpy array (cells x programs)."""
+    L = lib()
+    if not torch.cuda.is_available() or str(device).startswith("cpu"):
+        raise _lib.Cnmfb200Error("cnmf_torch_b200.fit_H_online runs on a CUDA device only")
+    dev = torch.device("cuda:0" if str(device) == "cuda" else device)
+    torch.cuda.set_device(dev)
+    X = getattr(X, "values", X)
+    W = np.asarray(getattr(W, "values", W), dtype=np.float32)
+    H_init = getattr(H_init, "values", H_init)
+    if hasattr(X, "toarray"):
+        X = X.toarray()
+    X = np.ascontiguousarray(X, dtype=np.float32)
+    n, g = X.shape
+    k = W.shape[0]
+    Kp = pad4(k)
+    if Kp > _lib.MAX_KP:
+        raise ValueError(f"{k} programs exceed the engine limit {_lib.MAX_KP}")
+    st = torch.cuda.current_stream().cuda_stream
+    ldg = pad4(g)
+    Wd = torch.zeros((Kp, ldg), device=dev, dtype=torch.float32)
+    Wd[:k, :g] = torch.from_numpy(W).to(dev)
+    if H_init is None:
+        gen = torch.Generator(device="cpu")
+        if seed is not None:
+            gen.manual_seed(int(seed))
+        else:
+            gen.seed()
+        h0 = torch.rand((n, k), generator=gen, dtype=torch.float32)
+    else:
+        h0 = torch.from_numpy(np.asarray(H_init, dtype=np.float32)).clamp(min=0.0)   # cnmf.py:345
+    ldn = pad4(n)
+    Ht = torch.zeros((Kp, ldn), device=dev, dtype=torch.float32)
+    Ht[:k, :n] = h0.to(dev).t()
+    gram = torch.zeros((1, Kp, Kp), device=dev, dtype=torch.float32)
+    ws_g = torch.empty(max(256, int(L.cnmf_b200_gram_workspace_bytes(1, Kp, g))), device=dev, dtype=torch.uint8)
+    check(L.cnmf_b200_gram(ptr(Wd), ldg, 1, Kp, g, ptr(gram), ptr(ws_g), st), "gram")       # W W^T, cnmf.py:346
+    cmax = min(int(chunk_size), n)
+    ldp = pad4(cmax)
+    Pt = torch.zeros((Kp, ldp), device=dev, dtype=torch.float32)
+    xbuf = torch.zeros((cmax, ldg), device=dev, dtype=torch.float32)
+    done = torch.zeros(1, device=dev, dtype=torch.uint8)
+    iters = torch.zeros(1, device=dev, dtype=torch.int32)
+    npend = torch.zeros(1, device=dev, dtype=torch.int32)
+    ws = torch.empty(max(256, int(L.cnmf_b200_online_inner_workspace_bytes(cmax, 1))), device=dev, dtype=torch.uint8)
+    Hs = torch.zeros((Kp, ldp), device=dev, dtype=torch.float32)   # chunk-local state: 16-byte aligned columns
+    for lo in range(0, n, int(chunk_size)):
+        c = min(int(chunk_size), n - lo)
+        xbuf[:c, :g] = torch.from_numpy(X[lo:lo + c]).to(dev)                             # chunk upload (cnmf.py:351)
+        check(L.cnmf_b200_gemm_nt(ptr(Wd), ldg, Kp, ptr(xbuf), ldg, c, g, ptr(Pt), ldp, st), "gemm x W^T")
+        Hs[:, :c] = Ht[:, lo:lo + c]
+        done.zero_()
+        n_done = 0
+        while n_done < chunk_max_iter:
+            m = min(inner_batch, chunk_max_iter - n_done)
+            check(L.cnmf_b200_online_inner(ptr(Pt), ldp, ptr(Hs), ldp, ptr(gram), ptr(done), None, c, 1, Kp,
+                                           float(l1_reg_H), float(l2_reg_H), float(epsilon), float(h_tol), m,
+                                           ptr(iters), ptr(npend), ptr(ws), st), "online_inner")
+            n_done += m
+            if int(npend.item()) == 0:
+                break
+        Ht[:, lo:lo + c] = Hs[:, :c]
+    return Ht[:k, :n].t().contiguous().cpu().numpy()
