@@ -98,6 +98,60 @@ def _cpu_baseline(x, seconds_target=15.0):
                       f"{el:.1f}s of torch-CPU work (oracle/nmf_oracle.py; nmf-torch itself is not installable here)"}
 
 
+def _extras(dev):
+    """Side measurements on the other BASELINE.json configs (not the bench metric): wall-times of the
+    device paths, with the host library path of the reference beside the consensus number."""
+    import torch
+    from cnmf_torch_b200 import consensus as cs
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    from cnmf_torch_b200.synth import nb_counts, replicate_spectra
+    out = {}
+    # cfg-4: consensus front half, 200 replicates x K=20 over 2000 genes
+    s = replicate_spectra(20, 200, 2000, seed=14)
+    cs.consensus_front_half(s, 20, 0.5, 60, device=dev)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(3):
+        r = cs.consensus_front_half(s, 20, 0.5, 60, device=dev)
+    torch.cuda.synchronize()
+    out["consensus_cfg4_ms"] = (time.perf_counter() - t0) / 3 * 1e3
+    try:
+        from oracle import consensus_oracle as co
+        t0 = time.perf_counter()
+        ref = co.consensus_front_half(s, 20, 0.5, 0.30)
+        out["consensus_cfg4_host_sklearn_ms"] = (time.perf_counter() - t0) * 1e3
+        out["consensus_cfg4_labels_identical"] = bool(np.array_equal(ref["labels"], r["labels"]))
+    except Exception as e:  # the oracle is optional here
+        out["consensus_cfg4_host_sklearn_ms"] = None
+    # cfg-3 shape at reduced N: sparse KL MU, 20 000 x 2000 at ~7 % density, K=9, R=100
+    xk = nb_counts(20000, 2000, seed=14, libsize=170.0)
+    eng = SparseKLEngine(xk, device=dev)
+    b = eng.new_batch(9, seeds=list(range(100)))
+    b.iterate(2)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    b.iterate(5)
+    torch.cuda.synchronize()
+    dt = (time.perf_counter() - t0) / 5
+    out["kl_sparse_20k_cells"] = {"density": float((xk > 0).mean()), "nnz": int(eng.nnz), "ms_per_batched_iter": dt * 1e3,
+                                  "replicate_iters_per_s": 100 / dt,
+                                  "algorithmic_hbm_gb_s": (8 * eng.nnz + 100 * 8 * 9 * (20000 + 2000)) / dt / 1e9}
+    del eng, b
+    # cfg-1/2 in the reference's default mode: online MU, chunk 5000, K=9, R=100, 3 passes
+    xo = nb_counts(3000, 2000, seed=14)
+    e2 = DenseFrobeniusEngine(xo, device=dev)
+    e2.factorize_online(9, seeds=list(range(100)), tol=0.0, max_pass=1, chunk_max_iter=1000)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    res = e2.factorize_online(9, seeds=list(range(100)), tol=0.0, max_pass=3, chunk_max_iter=1000)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    out["online_mu_3000x2000_K9_R100"] = {"s_per_3_passes": dt, "inner_iterations": res.inner_iterations,
+                                          "replicate_passes_per_s": 300 / dt}
+    return out
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path for this metric.  nmf-torch is absent from the image
     (SURVEY.md 0.2), so this times the oracle port with all host threads; rank 0 only."""
@@ -144,6 +198,7 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
+    ap.add_argument("--no-extras", action="store_true", help="skip the consensus / KL / online side measurements")
     ap.add_argument("--streams", type=int, default=1, help="1: one stream per K-batch (default); 0: single stream")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
@@ -262,6 +317,11 @@ def main():
     torch.cuda.synchronize()
     e2e_s = (time.perf_counter() - t0) / n_e2e
 
+    # ---------------- other configs of BASELINE.json, reported as extras (rank 0, N=1 only) -----
+    extras = None
+    if world == 1 and not args.no_extras:
+        extras = _extras(dev)
+
     # ---------------- reduce over ranks ------------------------------------------------------
     if world > 1:
         t = torch.tensor([ms_total, e2e_s], dtype=torch.float64, device=dev)
@@ -288,6 +348,8 @@ def main():
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
         }
+        if extras is not None:
+            line["extras"] = extras
         if not args.no_cpu_baseline and world == 1:
             line["cpu_baseline"] = _cpu_baseline(x)
         print(json.dumps(line))

@@ -103,15 +103,27 @@ __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
 #pragma unroll
     for (int k = 0; k < KP; ++k) s[k] = out[k];
   } else {
+    // HALS sweep with a running product d = s.G kept up to date after every component (the same
+    // arithmetic as recomputing s.G_:k before step k, but the per-step dependency is one FMA instead
+    // of a KP-long dot product: the KP updates of d are independent of each other).
+    float d[KP];
+#pragma unroll
+    for (int j = 0; j < KP; ++j) {
+      float t = 0.f;
+#pragma unroll
+      for (int i = 0; i < KP; ++i) t = fmaf(s[i], gram[i * KP + j], t);
+      d[j] = t;
+    }
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
-      float d = gram[k * KP + k] + l2;
-      float dot = 0.f;
+      const float gkk = gram[k * KP + k] + l2;
+      const float g = p[k] - d[k] - l1;
+      const float v = (gkk < eps) ? 0.f : fmaxf(s[k] + __fdiv_rn(g, gkk), 0.f);
+      const float delta = v - s[k];
+      s[k] = v;
 #pragma unroll
-      for (int j = 0; j < KP; ++j) dot = fmaf(s[j], gram[j * KP + k], dot);
-      float g = p[k] - dot - l1;
-      float v = fmaxf(s[k] + __fdiv_rn(g, d), 0.f);
-      s[k] = (d < eps) ? 0.f : v;
+      for (int j = 0; j < KP; ++j)
+        if (j > k) d[j] = fmaf(delta, gram[k * KP + j], d[j]);
     }
   }
 }

@@ -30,7 +30,13 @@ namespace cnmf {
 
 constexpr int TC_BM = 128;
 constexpr int TC_BK = 32;  // floats per k-block: 128 bytes = one swizzle-128B row
-constexpr int TC_THREADS = 256;
+constexpr int TC_THREADS = 256;  // 4 control warps + 4 epilogue warps: the minimum; see tc_epi_groups()
+// Epilogue warpgroups (128 threads each).  All of them cover the 128 TMEM lanes (warp % 4 = lane quarter);
+// warpgroup g takes the replicates rr = g (mod groups) of a tile.  The row update is a per-thread dependency
+// chain (HALS sweeps k in order), so the only way to hide its latency is more resident warps per scheduler;
+// the register file (64K) bounds how many: ~100 regs/thread at KP<=12 allows 3 groups + the control warps.
+__host__ __device__ constexpr int tc_epi_groups(int kp) { return kp <= 12 ? 3 : (kp <= 20 ? 2 : 1); }
+__host__ __device__ constexpr int tc_threads(int kp) { return 128 + 128 * tc_epi_groups(kp); }
 constexpr int TC_MAX_BN = 256;
 constexpr int TC_TMEM_COLS = 512;
 constexpr int TC_A_BYTES = TC_BM * TC_BK * 4;  // 16 KiB
@@ -50,7 +56,7 @@ struct TcParams {
   double* partials;       // [num_m_tiles x R x 2]
   int R;
   int t;  // replicates per tile
-  int num_m_tiles, num_n_tiles, stages;
+  int num_m_tiles, num_m_groups, num_n_tiles, stages;
   float l1, l2, eps;
 };
 
@@ -126,7 +132,8 @@ __device__ __forceinline__ float to_tf32(float v) {  // round to nearest, ties a
   asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
   return __uint_as_float(r);
 }
-__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+template <int NT>
+__device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory"); }
 
 // K-major operand tile, rows at 128-byte pitch, SWIZZLE_128B: SBO = 8 rows * 128 B, LBO unused,
 // descriptor version 1 (sm_100), layout type 2.
@@ -140,10 +147,59 @@ __device__ __forceinline__ uint64_t make_kmajor_sw128_desc(uint32_t smem_addr) {
 }
 
 // ---------------------------------------------------------------------------------------------
-// kernel
+// kernel.  CG = 1: one CTA per tile.  CG = 2: a CTA pair (cluster of 2, tcgen05 cta_group::2) works on
+// a 256-row x BN tile: each CTA stages its own 128 rows of A and HALF of the B tile, the leader's
+// single thread issues M=256 MMAs that read both CTAs' shared memory, each CTA keeps its 128 x BN
+// accumulator half in its own tensor memory and runs its own epilogue.  Per SM that cuts the operand
+// bytes per k-block from (128 + BN) to (128 + BN/2) rows -- the measured limiter (profiles/NOTES.md).
 // ---------------------------------------------------------------------------------------------
-template <int KP, int ALGO>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+// TMA load issued by either CTA of a pair; the bytes are accounted on the LEADER's mbarrier
+// (peer bit of the shared::cluster address cleared).
+__device__ __forceinline__ void tma_load_2d_pair(void* dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+      ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tc_commit_pair(uint64_t* bar) {  // arrives on this barrier in BOTH CTAs
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(
+                   smem_u32(bar)),
+               "h"(static_cast<uint16_t>(3))
+               : "memory");
+}
+__device__ __forceinline__ void tc_mma_tf32_pair(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,
+                                                 uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::tf32 [%0], %1, %2, %3, p;\n\t"
+      "}" ::"r"(d_tmem),
+      "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {  // arrive on `bar` of CTA `cta`
+  asm volatile(
+      "{\n\t"
+      ".reg .b32 remAddr32;\n\t"
+      "mapa.shared::cluster.u32  remAddr32, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64  _, [remAddr32];\n\t"
+      "}" ::"r"(smem_u32(bar)),
+      "r"(cta)
+      : "memory");
+}
+
+template <int KP, int ALGO, int CG>
+__global__ void __launch_bounds__(tc_threads(KP), 1)
 tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const TcParams prm) {
   extern __shared__ uint8_t smem_raw[];
@@ -151,7 +207,9 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = prm.t;
   const int BN = t * KP;
-  const uint32_t b_bytes = static_cast<uint32_t>(BN) * TC_BK * 4;
+  const uint32_t cta_rank = (CG == 2) ? cluster_ctarank() : 0u;
+  const bool leader = cta_rank == 0u;
+  const uint32_t b_bytes = static_cast<uint32_t>(BN / CG) * TC_BK * 4;  // this CTA's share of the B tile
   const uint32_t stage_bytes = TC_A_BYTES + b_bytes;
   const int stages = prm.stages;
 
@@ -175,51 +233,67 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     }
     for (int b = 0; b < 2; ++b) {
       mbar_init(&tfull[b], 1);
-      mbar_init(&tempty[b], 4);  // one arrival per epilogue warp
+      mbar_init(&tempty[b], 4 * tc_epi_groups(KP) * CG);  // one arrival per epilogue warp of every CTA of the group
     }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
-                 "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    if (CG == 2) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::);
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(tmem_slot)),
+                   "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::);
+    }
   }
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int num_tiles = prm.num_m_tiles * prm.num_n_tiles;
+  // tiles are indexed per CTA group: group tile -> (m_group, n_tile); this CTA's rows = m_group*CG + rank
+  const int num_tiles = prm.num_m_groups * prm.num_n_tiles;
+  const int group_id = blockIdx.x / CG, num_groups = gridDim.x / CG;
   const int num_kb = static_cast<int>((prm.Kd + TC_BK - 1) / TC_BK);
 
   if (warp == 0) {
     if (lane == 0) {
-      // ===================== TMA producer =====================
+      // ===================== TMA producer (every CTA) =====================
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m_tile = tile / prm.num_n_tiles, n_tile = tile - m_tile * prm.num_n_tiles;
+      for (int tile = group_id; tile < num_tiles; tile += num_groups) {
+        const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
+        const int m_tile = m_group * CG + static_cast<int>(cta_rank);
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1u);
           uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
-          mbar_expect_tx(&full[stage], stage_bytes);
-          tma_load_2d(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
-          tma_load_2d(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK, n_tile * BN);
+          if (CG == 2) {
+            if (leader) mbar_expect_tx(&full[stage], 2u * stage_bytes);  // both CTAs' bytes land on the leader
+            tma_load_2d_pair(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
+            tma_load_2d_pair(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK,
+                             n_tile * BN + static_cast<int>(cta_rank) * (BN / 2));
+          } else {
+            mbar_expect_tx(&full[stage], stage_bytes);
+            tma_load_2d(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
+            tma_load_2d(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK, n_tile * BN);
+          }
           if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
-      // ===================== MMA issuer =====================
+    if (lane == 0 && leader) {
+      // ===================== MMA issuer (leader CTA of the group) =====================
       // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=tf32 (2 at bits 7-9 / 10-12), K-major both,
-      // N>>3 at bits 17-22, M>>4 at bits 24-28
+      // N>>3 at bits 17-22, M>>4 at bits 24-28 (M = 128 per CTA, 256 for a pair)
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
-                             (static_cast<uint32_t>(TC_BM >> 4) << 24);
+                             (static_cast<uint32_t>((TC_BM * CG) >> 4) << 24);
       int stage = 0;
       uint32_t phase = 0;
       int lt = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+      for (int tile = group_id; tile < num_tiles; tile += num_groups, ++lt) {
         const int buf = lt & 1;
         const uint32_t tphase = (lt >> 1) & 1u;
         mbar_wait(&tempty[buf], tphase ^ 1u);
@@ -234,48 +308,76 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < TC_BK / 8; ++k) {
             // advance 8 tf32 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-            tc_mma_tf32(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc,
-                        (kb | k) != 0 ? 1u : 0u);
+            if (CG == 2)
+              tc_mma_tf32_pair(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k),
+                               idesc, (kb | k) != 0 ? 1u : 0u);
+            else
+              tc_mma_tf32(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc,
+                          (kb | k) != 0 ? 1u : 0u);
           }
-          tc_commit(&empty[stage]);  // frees the smem slot when these MMAs retire
+          // frees the smem slot (in both CTAs of a pair) when these MMAs retire
+          if (CG == 2) tc_commit_pair(&empty[stage]); else tc_commit(&empty[stage]);
           if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
-        tc_commit(&tfull[buf]);  // accumulator complete -> epilogue
+        // accumulator complete -> epilogue (of both CTAs)
+        if (CG == 2) tc_commit_pair(&tfull[buf]); else tc_commit(&tfull[buf]);
       }
     }
   } else if (warp >= 4) {
-    // ===================== epilogue =====================
-    const int q = warp - 4;  // TMEM lane quarter == warp % 4
+    // ===================== epilogue (every CTA, its own 128 rows) =====================
+    constexpr int EG = tc_epi_groups(KP), ET = 128 * EG;
+    const int q = warp & 3;         // TMEM lane quarter == warp % 4
+    const int eg = (warp - 4) >> 2;  // epilogue warpgroup: takes replicates rr = eg (mod EG)
     const int et = threadIdx.x - 128;
     int lt = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x, ++lt) {
+    for (int tile = group_id; tile < num_tiles; tile += num_groups, ++lt) {
       const int buf = lt & 1;
       const uint32_t tphase = (lt >> 1) & 1u;
-      const int m_tile = tile / prm.num_n_tiles, n_tile = tile - m_tile * prm.num_n_tiles;
+      const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
+      const int m_tile = m_group * CG + static_cast<int>(cta_rank);
       const int r0 = n_tile * t;
       if (ALGO < TC_MODE_STORE) {
-        for (int i = et; i < t * KP * KP; i += 128) {
+        for (int i = et; i < t * KP * KP; i += ET) {
           const int rr = i / (KP * KP);
           sgram[i] = (r0 + rr < prm.R) ? prm.gram[static_cast<int64_t>(r0) * KP * KP + i] : 0.f;
         }
       }
-      epi_bar_sync();
+      epi_bar_sync<ET>();
       mbar_wait(&tfull[buf], tphase);
       tc_fence_after();
       const int64_t m = static_cast<int64_t>(m_tile) * TC_BM + q * 32 + lane;
       const bool in = m < prm.M;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * TC_MAX_BN);
-      for (int rr = 0; rr < t; ++rr) {
+      // software pipeline over the replicates of the tile: the state of replicate rr+1 is requested
+      // before replicate rr is updated, so its global-load latency hides behind the update
+      constexpr bool kPrefetch = (KP <= 20) && (ALGO != TC_MODE_STORE);
+      const bool want_sums = (ALGO < TC_MODE_STORE) && prm.partials != nullptr;
+      float s[KP], s_nxt[kPrefetch ? KP : 1];
+      if (kPrefetch && r0 + eg < prm.R) {
+        const float* sp0 = prm.state + static_cast<int64_t>(r0 + eg) * KP * prm.lds + m;
+#pragma unroll
+        for (int k = 0; k < KP; ++k) s[k] = in ? sp0[static_cast<int64_t>(k) * prm.lds] : 0.f;
+      }
+      for (int rr = eg; rr < t; rr += EG) {
         const int r = r0 + rr;
         if (r >= prm.R) break;
-        float p[KP], s[KP];
+        float p[KP];
 #pragma unroll
         for (int c = 0; c < KP; c += 4)
           tmem_ld4(taddr + static_cast<uint32_t>(rr * KP + c), p[c], p[c + 1], p[c + 2], p[c + 3]);
         const int64_t soff = static_cast<int64_t>(r) * KP * prm.lds + m;
         float* sp = prm.state + soff;
+        if (kPrefetch) {
+          if (rr + EG < t && r + EG < prm.R) {
+            const float* spn = sp + static_cast<int64_t>(KP) * EG * prm.lds;
 #pragma unroll
-        for (int k = 0; k < KP; ++k) s[k] = (in && ALGO != TC_MODE_STORE) ? sp[static_cast<int64_t>(k) * prm.lds] : 0.f;
+            for (int k = 0; k < KP; ++k) s_nxt[k] = in ? spn[static_cast<int64_t>(k) * prm.lds] : 0.f;
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < KP; ++k)
+            s[k] = (in && ALGO != TC_MODE_STORE) ? sp[static_cast<int64_t>(k) * prm.lds] : 0.f;
+        }
         tmem_ld_wait();
         const bool act = prm.active == nullptr || prm.active[r] != 0;
         float cross = 0.f, ssum = 0.f;
@@ -286,38 +388,48 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             for (int k = 0; k < KP; ++k)
               sp[static_cast<int64_t>(k) * prm.lds] = (ALGO == TC_MODE_ACCUM) ? s[k] + p[k] : p[k];
           }
-          continue;
-        }
-        if (in) {
-          if (act) {
-            update_row<KP, ALGO>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps);
+        } else {
+          if (in) {
+            if (act) {
+              update_row<KP, ALGO>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps);
 #pragma unroll
-            for (int k = 0; k < KP; ++k) sp[static_cast<int64_t>(k) * prm.lds] = s[k];
-            if (prm.state_op != nullptr) {
-              float* op = prm.state_op + soff;
+              for (int k = 0; k < KP; ++k) sp[static_cast<int64_t>(k) * prm.lds] = s[k];
+              if (prm.state_op != nullptr) {
+                float* op = prm.state_op + soff;
 #pragma unroll
-              for (int k = 0; k < KP; ++k) op[static_cast<int64_t>(k) * prm.lds] = to_tf32(s[k]);
+                for (int k = 0; k < KP; ++k) op[static_cast<int64_t>(k) * prm.lds] = to_tf32(s[k]);
+              }
+            }
+            if (want_sums) {
+#pragma unroll
+              for (int k = 0; k < KP; ++k) {
+                cross = fmaf(s[k], p[k], cross);
+                ssum += s[k];
+              }
             }
           }
-#pragma unroll
-          for (int k = 0; k < KP; ++k) {
-            cross = fmaf(s[k], p[k], cross);
-            ssum += s[k];
+          if (want_sums) {
+            cross = warp_sum(cross);
+            ssum = warp_sum(ssum);
+            if (lane == 0) {
+              sred[(q * t + rr) * 2 + 0] = cross;
+              sred[(q * t + rr) * 2 + 1] = ssum;
+            }
           }
         }
-        cross = warp_sum(cross);
-        ssum = warp_sum(ssum);
-        if (lane == 0) {
-          sred[(q * t + rr) * 2 + 0] = cross;
-          sred[(q * t + rr) * 2 + 1] = ssum;
+        if (kPrefetch) {
+#pragma unroll
+          for (int k = 0; k < KP; ++k) s[k] = s_nxt[k];
         }
       }
-      // all tcgen05.ld of this buffer are complete: hand it back to the MMA warp
+      // all tcgen05.ld of this buffer are complete: hand it back to the MMA warp (of the leader CTA)
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(&tempty[buf]);
-      epi_bar_sync();
-      for (int i = et; i < t * 2 && ALGO < TC_MODE_STORE; i += 128) {
+      if (lane == 0) {
+        if (CG == 2) mbar_arrive_cta(&tempty[buf], 0u); else mbar_arrive(&tempty[buf]);
+      }
+      epi_bar_sync<ET>();
+      for (int i = et; i < t * 2 && ALGO < TC_MODE_STORE && prm.partials != nullptr && m_tile < prm.num_m_tiles; i += ET) {
         const int rr = i >> 1, r = r0 + rr;
         if (r < prm.R) {
           double v = 0.0;
@@ -326,16 +438,20 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           prm.partials[(static_cast<int64_t>(m_tile) * prm.R + r) * 2 + (i & 1)] = v;
         }
       }
-      epi_bar_sync();  // sgram / sred are rewritten by the next tile
+      epi_bar_sync<ET>();  // sgram / sred are rewritten by the next tile
     }
   }
 
   tc_fence_before();
-  __syncthreads();
+  if (CG == 2) cluster_sync_all(); else __syncthreads();
   if (warp == 2) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
-                 "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
+    if (CG == 2)
+      asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                   "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
+    else
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base),
+                   "r"(static_cast<uint32_t>(TC_TMEM_COLS)));
   }
 }
 
@@ -375,12 +491,12 @@ int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st) 
 // host side
 // ---------------------------------------------------------------------------------------------
 struct TcPlan {
-  int t, BN, stages, num_m_tiles, num_n_tiles;
+  int t, BN, stages, num_m_tiles, num_m_groups, num_n_tiles, cg;
   size_t smem_bytes;
 };
 
-static size_t tc_smem_bytes(int t, int Kp, int stages) {
-  const size_t stage = TC_A_BYTES + static_cast<size_t>(t) * Kp * TC_BK * 4;
+static size_t tc_smem_bytes(int t, int Kp, int stages, int cg) {
+  const size_t stage = TC_A_BYTES + static_cast<size_t>(t) * Kp / cg * TC_BK * 4;
   size_t extra = static_cast<size_t>(t) * Kp * Kp * 4 + 4 * static_cast<size_t>(t) * 2 * 4;
   extra += (2 * TC_MAX_STAGES + 4) * 8 + 16;
   return stages * stage + extra + 1024;  // +1024: manual alignment of the dynamic base
@@ -397,35 +513,44 @@ static int tc_num_sms() {
   return sms;
 }
 
-// Pick replicates-per-tile t (BN = t*Kp multiple of 16, <= 256) minimising waves * MMA time + epilogue.
+// Pick the CTA group size (1, or a pair sharing the B tile) and replicates-per-tile t (BN = t*Kp, a
+// multiple of 16, <= 256) from a cost model calibrated on B200 (profiles/NOTES.md): one SM ingests
+// ~43 B/clk from L2 through TMA, so a k-block costs max(operand bytes per SM / 43, tensor-pipe clocks);
+// tiles run in waves over the SMs (pairs: over SM pairs); the epilogue of the last tile is exposed.
 static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out) {
   const int num_m = static_cast<int>(ceil_div(M, TC_BM));
   const int64_t num_kb = ceil_div(Kd, TC_BK);
   double best = 1e300;
   bool found = false;
   static const int forced_t = [] { const char* e = getenv("CNMF_B200_TC_T"); return e ? atoi(e) : 0; }();
-  for (int t = 1; t * Kp <= TC_MAX_BN; ++t) {
-    const int BN = t * Kp;
-    if (BN % 16 != 0) continue;
-    if (forced_t > 0 && t != forced_t && (forced_t * Kp) % 16 == 0 && forced_t * Kp <= TC_MAX_BN) continue;
-    int stages = TC_MAX_STAGES;
-    while (stages >= 2 && tc_smem_bytes(t, Kp, stages) > static_cast<size_t>(TC_SMEM_LIMIT)) --stages;
-    if (stages < 2) continue;
-    const int num_n = static_cast<int>(ceil_div(R, t));
-    const int64_t tiles = static_cast<int64_t>(num_m) * num_n;
-    const int64_t waves = ceil_div(tiles, sms);
-    // measured on B200 (profiles/NOTES.md): one SM ingests ~43 B/clk from L2 through TMA, so a k-block
-    // costs max(operand bytes / 43, tensor-pipe clocks); the epilogue of the last tile is exposed.
-    const double bytes_kb = (TC_BM + BN) * TC_BK * 4.0;
-    const double mma_kb = 4.0 * (BN / 2.0 > 32.0 ? BN / 2.0 : 32.0);
-    const double kb_clk = bytes_kb / 43.0 > mma_kb ? bytes_kb / 43.0 : mma_kb;
-    const double epi = static_cast<double>(t) * (Kp * Kp + 12.0 * Kp) * 1.5 + 1500.0;
-    const double cost = waves * (static_cast<double>(num_kb) * kb_clk + 1000.0) + epi;
-    if (cost < best) {
-      best = cost;
-      found = true;
-      out->t = t; out->BN = BN; out->stages = stages; out->num_m_tiles = num_m; out->num_n_tiles = num_n;
-      out->smem_bytes = tc_smem_bytes(t, Kp, stages);
+  static const int forced_cg = [] { const char* e = getenv("CNMF_B200_TC_CG"); return e ? atoi(e) : 0; }();
+  for (int cg = 1; cg <= 2; ++cg) {
+    if (cg == 2 && (num_m < 2 || sms < 2)) continue;
+    if (forced_cg > 0 && cg != forced_cg && !(forced_cg == 2 && num_m < 2)) continue;
+    for (int t = 1; t * Kp <= TC_MAX_BN; ++t) {
+      const int BN = t * Kp;
+      if (BN % 16 != 0) continue;
+      if (forced_t > 0 && t != forced_t && (forced_t * Kp) % 16 == 0 && forced_t * Kp <= TC_MAX_BN) continue;
+      static const int max_stages = [] { const char* e = getenv("CNMF_B200_TC_STAGES"); return e ? atoi(e) : TC_MAX_STAGES; }();
+      int stages = max_stages < TC_MAX_STAGES ? max_stages : TC_MAX_STAGES;
+      while (stages >= 2 && tc_smem_bytes(t, Kp, stages, cg) > static_cast<size_t>(TC_SMEM_LIMIT)) --stages;
+      if (stages < 2) continue;
+      const int num_n = static_cast<int>(ceil_div(R, t));
+      const int num_g = static_cast<int>(ceil_div(num_m, cg));
+      const int64_t tiles = static_cast<int64_t>(num_g) * num_n;
+      const int64_t waves = ceil_div(tiles, sms / cg);
+      const double bytes_kb = (TC_BM + BN / cg) * TC_BK * 4.0;
+      const double mma_kb = 4.0 * (BN / 2.0 > 32.0 ? BN / 2.0 : 32.0);
+      const double kb_clk = bytes_kb / 43.0 > mma_kb ? bytes_kb / 43.0 : mma_kb;
+      const double epi = static_cast<double>(t) * (Kp * Kp + 12.0 * Kp) * 1.5 + 1500.0;
+      const double cost = waves * (static_cast<double>(num_kb) * kb_clk + 1000.0) + epi + (cg == 2 ? 1500.0 : 0.0);
+      if (cost < best) {
+        best = cost;
+        found = true;
+        out->t = t; out->BN = BN; out->stages = stages; out->num_m_tiles = num_m; out->num_m_groups = num_g;
+        out->num_n_tiles = num_n; out->cg = cg;
+        out->smem_bytes = tc_smem_bytes(t, Kp, stages, cg);
+      }
     }
   }
   return found;
@@ -487,18 +612,37 @@ static int get_tensor_map(const float* ptr, int64_t rows, int64_t cols, int64_t 
   return 0;
 }
 
+template <int KP, int ALGO, int CG>
+static int launch_tc_inst2(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
+                           int grid, cudaStream_t st) {
+  static thread_local bool configured = false;
+  auto kern = tc_half_step_kernel<KP, ALGO, CG>;
+  if (!configured) {
+    CNMF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
+    configured = true;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(grid);
+  cfg.blockDim = dim3(tc_threads(KP));
+  cfg.dynamicSmemBytes = plan.smem_bytes;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = CG;
+  attr[0].val.clusterDim.y = 1;
+  attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  CNMF_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, prm));
+  count_launch();
+  return 0;
+}
+
 template <int KP, int ALGO>
 static int launch_tc_inst(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
                           int grid, cudaStream_t st) {
-  static thread_local size_t configured = 0;
-  auto kern = tc_half_step_kernel<KP, ALGO>;
-  if (plan.smem_bytes > configured) {
-    CNMF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
-    configured = TC_SMEM_LIMIT;
-  }
-  kern<<<grid, TC_THREADS, plan.smem_bytes, st>>>(ma, mb, prm);
-  CNMF_LAUNCH_CHECK();
-  return 0;
+  if (plan.cg == 2) return launch_tc_inst2<KP, ALGO, 2>(ma, mb, prm, plan, grid, st);
+  return launch_tc_inst2<KP, ALGO, 1>(ma, mb, prm, plan, grid, st);
 }
 
 int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
@@ -512,13 +656,14 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
   }
   CUtensorMap ma, mb;
   CNMF_TRY(get_tensor_map(A, M, Kd, lda, TC_BM, &ma));
-  CNMF_TRY(get_tensor_map(F, static_cast<int64_t>(R) * Kp, Kd, ldf, plan.BN, &mb));
+  CNMF_TRY(get_tensor_map(F, static_cast<int64_t>(R) * Kp, Kd, ldf, plan.BN / plan.cg, &mb));
   TcParams prm;
   prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.active = active;
-  prm.partials = partials; prm.R = R; prm.t = plan.t; prm.num_m_tiles = plan.num_m_tiles;
+  prm.partials = partials; prm.R = R; prm.t = plan.t; prm.num_m_tiles = plan.num_m_tiles; prm.num_m_groups = plan.num_m_groups;
   prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
-  const int64_t tiles = static_cast<int64_t>(plan.num_m_tiles) * plan.num_n_tiles;
-  const int grid = static_cast<int>(tiles < sms ? tiles : sms);
+  const int64_t tiles = static_cast<int64_t>(plan.num_m_groups) * plan.num_n_tiles;  // per CTA group
+  const int64_t slots = sms / plan.cg;
+  const int grid = static_cast<int>((tiles < slots ? tiles : slots) * plan.cg);
   if (algo == CNMF_B200_ALGO_MU) {
     CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_MU>(ma, mb, prm, plan, grid, st)));
   } else if (algo == CNMF_B200_ALGO_HALS) {
@@ -547,7 +692,7 @@ int cnmf_b200_dense_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd
                               float* state, float* state_tf32, int64_t lds, const float* gram,
                               const uint8_t* active, int32_t R, int32_t Kp, int32_t algo, float l1, float l2,
                               float eps, double* partials, void* stream) {
-  CNMF_CHECK_ARG(A && F && state && gram && partials, "dense_half_step: null pointer");
+  CNMF_CHECK_ARG(A && F && state && gram, "dense_half_step: null pointer");
   CNMF_CHECK_ARG(M > 0 && Kd > 0 && R > 0, "dense_half_step: empty shape");
   CNMF_CHECK_ARG(lda % 4 == 0 && ldf % 4 == 0 && aligned16(A) && aligned16(F),
                  "dense_half_step: operands need 16-byte aligned rows (ld multiple of 4)");

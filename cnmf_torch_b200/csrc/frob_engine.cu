@@ -148,6 +148,10 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
   const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
 
   for (int it = 0; it < n_iters; ++it) {
+    // the objective only reads the partial sums of the last iteration (tcgen05 path skips them otherwise)
+    const bool last = (it == n_iters - 1) && p->err2 != nullptr;
+    double* pH = (last || l.impl == CNMF_B200_IMPL_SIMT) ? partH : nullptr;
+    double* pW = (last || l.impl == CNMF_B200_IMPL_SIMT) ? partW : nullptr;
     // ---- H half-step: Pt[RKp x N] = Wall X^T ; Ht <- update(Ht; Pt, gramW)
     if (l.impl == CNMF_B200_IMPL_SIMT) {
       CNMF_TRY(launch_gemm_nt(p->Wall, p->ldw, rk, p->X, p->ldx, N, G, Pt, ldpH, st));
@@ -155,7 +159,7 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
                                  p->l1_H, p->l2_H, p->eps, partH, st));
     } else {
       CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh, p->gramW, p->active,
-                                   p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, partH, st));
+                                   p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st));
     }
     CNMF_TRY(launch_gram(p->Ht, p->ldh, p->R, p->Kp, N, p->gramH, gws, st));
     // ---- W half-step: Pt[RKp x G] = Ht Xt^T ; Wall <- update(Wall; Pt, gramH)
@@ -165,7 +169,7 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
                                  p->l1_W, p->l2_W, p->eps, partW, st));
     } else {
       CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, Wop, p->ldw, p->gramH,
-                                   p->active, p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, st));
+                                   p->active, p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, pW, st));
     }
     CNMF_TRY(launch_gram(p->Wall, p->ldw, p->R, p->Kp, G, p->gramW, gws, st));
   }

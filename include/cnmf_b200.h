@@ -105,7 +105,8 @@ int cnmf_b200_round_tf32(float* x, int64_t n, void* stream);
 
 /* Fused half-step on the tensor cores (TMA -> tcgen05.mma kind::tf32 -> TMEM epilogue):
  *   P = A[M x Kd] * F[R*Kp x Kd]^T is formed tile by tile in tensor memory and never stored;
- *   state[R*Kp x M] receives the MU / HALS row update of cnmf_b200_row_update, partials likewise;
+ *   state[R*Kp x M] receives the MU / HALS row update of cnmf_b200_row_update, partials likewise
+ *   (partials may be NULL: the objective's partial sums are then skipped);
  *   state_tf32 (same layout, may be NULL) receives the updated rows rounded to tf32 -- the operand
  *   F of the next half-step, so that operand rounding stays unbiased while the master stays fp32.
  * A and F should hold tf32-representable values (cnmf_b200_round_tf32); other bits are ignored.

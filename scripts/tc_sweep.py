@@ -14,11 +14,16 @@ st = torch.cuda.current_stream().cuda_stream
 frozen = torch.zeros(b.R, dtype=torch.uint8, device="cuda")
 part = torch.zeros(64 * b.R * 2, dtype=torch.float64, device="cuda")
 Wop = b.Wall.clone(); Hop = b.Ht.clone()
-def h(): _lib.check(lib.cnmf_b200_dense_half_step(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, p.Ht, None, p.ldh, p.gramW, frozen.data_ptr(), p.R, p.Kp, p.algo, 0., 0., p.eps, part.data_ptr(), st))
-def w(): _lib.check(lib.cnmf_b200_dense_half_step(p.Xt, p.ldxt, p.n_genes, p.n_cells, Hop.data_ptr(), p.ldh, p.Wall, None, p.ldw, p.gramH, frozen.data_ptr(), p.R, p.Kp, p.algo, 0., 0., p.eps, part.data_ptr(), st))
+ACT = None if os.environ.get("LIVE") else frozen.data_ptr()
+PART = None if os.environ.get("NOPART") else part.data_ptr()
+Hop2 = b.Ht.clone(); Wop2 = b.Wall.clone()
+def h(): _lib.check(lib.cnmf_b200_dense_half_step(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, p.Ht, Hop2.data_ptr(), p.ldh, p.gramW, ACT, p.R, p.Kp, p.algo, 0., 0., p.eps, PART, st))
+def w(): _lib.check(lib.cnmf_b200_dense_half_step(p.Xt, p.ldxt, p.n_genes, p.n_cells, Hop.data_ptr(), p.ldh, p.Wall, Wop2.data_ptr(), p.ldw, p.gramH, ACT, p.R, p.Kp, p.algo, 0., 0., p.eps, PART, st))
 ws = torch.empty(lib.cnmf_b200_gram_workspace_bytes(p.R, p.Kp, p.n_cells), dtype=torch.uint8, device="cuda")
 def g(): _lib.check(lib.cnmf_b200_gram(p.Ht, p.ldh, p.R, p.Kp, p.n_cells, p.gramH, ws.data_ptr(), st))
-for name, fn in (("H", h), ("W", w), ("gramH", g)):
+Pbuf = torch.zeros(p.R * p.Kp, p.ldh, device="cuda")
+def gs(): _lib.check(lib.cnmf_b200_dense_gemm_tf32(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, Pbuf.data_ptr(), p.ldh, None, p.R, p.Kp, 0, st))
+for name, fn in (("H", h), ("W", w), ("gemmH", gs), ("gramH", g)):
     for _ in range(5): fn()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
