@@ -103,27 +103,27 @@ __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
 #pragma unroll
     for (int k = 0; k < KP; ++k) s[k] = out[k];
   } else {
-    // HALS sweep with a running product d = s.G kept up to date after every component (the same
-    // arithmetic as recomputing s.G_:k before step k, but the per-step dependency is one FMA instead
-    // of a KP-long dot product: the KP updates of d are independent of each other).
-    float d[KP];
+    // HALS sweep on a running residual r_j = p_j - l1 - (s.G)_j kept up to date after every component:
+    // the same arithmetic as recomputing p_k - s.G_:k before step k, but the per-step dependency is one
+    // FMA instead of a KP-long dot product (the KP updates of r are independent of each other), and p is
+    // dead once r is formed.
+    float r[KP];
 #pragma unroll
     for (int j = 0; j < KP; ++j) {
       float t = 0.f;
 #pragma unroll
       for (int i = 0; i < KP; ++i) t = fmaf(s[i], gram[i * KP + j], t);
-      d[j] = t;
+      r[j] = p[j] - t - l1;
     }
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
       const float gkk = gram[k * KP + k] + l2;
-      const float g = p[k] - d[k] - l1;
-      const float v = (gkk < eps) ? 0.f : fmaxf(s[k] + __fdiv_rn(g, gkk), 0.f);
+      const float v = (gkk < eps) ? 0.f : fmaxf(s[k] + __fdiv_rn(r[k], gkk), 0.f);
       const float delta = v - s[k];
       s[k] = v;
 #pragma unroll
       for (int j = 0; j < KP; ++j)
-        if (j > k) d[j] = fmaf(delta, gram[k * KP + j], d[j]);
+        if (j > k) r[j] = fmaf(-delta, gram[k * KP + j], r[j]);
     }
   }
 }

@@ -35,7 +35,7 @@ constexpr int TC_THREADS = 256;  // 4 control warps + 4 epilogue warps: the mini
 // warpgroup g takes the replicates rr = g (mod groups) of a tile.  The row update is a per-thread dependency
 // chain (HALS sweeps k in order), so the only way to hide its latency is more resident warps per scheduler;
 // the register file (64K) bounds how many: ~100 regs/thread at KP<=12 allows 3 groups + the control warps.
-__host__ __device__ constexpr int tc_epi_groups(int kp) { return kp <= 12 ? 3 : (kp <= 20 ? 2 : 1); }
+__host__ __device__ constexpr int tc_epi_groups(int kp) { return kp <= 8 ? 3 : (kp <= 20 ? 2 : 1); }
 __host__ __device__ constexpr int tc_threads(int kp) { return 128 + 128 * tc_epi_groups(kp); }
 constexpr int TC_MAX_BN = 256;
 constexpr int TC_TMEM_COLS = 512;
@@ -198,7 +198,7 @@ __device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {  
       : "memory");
 }
 
-template <int KP, int ALGO, int CG>
+template <int KP, int ALGO, int CG, bool SUMS>
 __global__ void __launch_bounds__(tc_threads(KP), 1)
 tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const TcParams prm) {
@@ -350,8 +350,8 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * TC_MAX_BN);
       // software pipeline over the replicates of the tile: the state of replicate rr+1 is requested
       // before replicate rr is updated, so its global-load latency hides behind the update
-      constexpr bool kPrefetch = (KP <= 20) && (ALGO != TC_MODE_STORE);
-      const bool want_sums = (ALGO < TC_MODE_STORE) && prm.partials != nullptr;
+      constexpr bool kPrefetch = (KP <= 12) && (ALGO != TC_MODE_STORE);
+      constexpr bool want_sums = SUMS && (ALGO < TC_MODE_STORE);  // compile-time: p is dead after the update otherwise
       float s[KP], s_nxt[kPrefetch ? KP : 1];
       if (kPrefetch && r0 + eg < prm.R) {
         const float* sp0 = prm.state + static_cast<int64_t>(r0 + eg) * KP * prm.lds + m;
@@ -429,7 +429,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         if (CG == 2) mbar_arrive_cta(&tempty[buf], 0u); else mbar_arrive(&tempty[buf]);
       }
       epi_bar_sync<ET>();
-      for (int i = et; i < t * 2 && ALGO < TC_MODE_STORE && prm.partials != nullptr && m_tile < prm.num_m_tiles; i += ET) {
+      for (int i = et; i < t * 2 && want_sums && m_tile < prm.num_m_tiles; i += ET) {
         const int rr = i >> 1, r = r0 + rr;
         if (r < prm.R) {
           double v = 0.0;
@@ -525,8 +525,8 @@ static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out) 
   static const int forced_t = [] { const char* e = getenv("CNMF_B200_TC_T"); return e ? atoi(e) : 0; }();
   static const int forced_cg = [] { const char* e = getenv("CNMF_B200_TC_CG"); return e ? atoi(e) : 0; }();
   for (int cg = 1; cg <= 2; ++cg) {
-    if (cg == 2 && (num_m < 2 || sms < 2)) continue;
-    if (forced_cg > 0 && cg != forced_cg && !(forced_cg == 2 && num_m < 2)) continue;
+    if (cg == 2 && (num_m < 2 || sms < 2 || forced_cg != 2)) continue;  // pairs: opt-in (CNMF_B200_TC_CG=2), measured no faster
+    if (forced_cg == 2 && cg == 1 && num_m >= 2) continue;
     for (int t = 1; t * Kp <= TC_MAX_BN; ++t) {
       const int BN = t * Kp;
       if (BN % 16 != 0) continue;
@@ -612,11 +612,11 @@ static int get_tensor_map(const float* ptr, int64_t rows, int64_t cols, int64_t 
   return 0;
 }
 
-template <int KP, int ALGO, int CG>
-static int launch_tc_inst2(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
+template <int KP, int ALGO, int CG, bool SUMS>
+static int launch_tc_inst3(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
                            int grid, cudaStream_t st) {
   static thread_local bool configured = false;
-  auto kern = tc_half_step_kernel<KP, ALGO, CG>;
+  auto kern = tc_half_step_kernel<KP, ALGO, CG, SUMS>;
   if (!configured) {
     CNMF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
     configured = true;
@@ -636,6 +636,13 @@ static int launch_tc_inst2(const CUtensorMap& ma, const CUtensorMap& mb, const T
   CNMF_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, prm));
   count_launch();
   return 0;
+}
+
+template <int KP, int ALGO, int CG>
+static int launch_tc_inst2(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
+                           int grid, cudaStream_t st) {
+  if (ALGO < TC_MODE_STORE && prm.partials != nullptr) return launch_tc_inst3<KP, ALGO, CG, true>(ma, mb, prm, plan, grid, st);
+  return launch_tc_inst3<KP, ALGO, CG, false>(ma, mb, prm, plan, grid, st);
 }
 
 template <int KP, int ALGO>
