@@ -74,7 +74,8 @@ SIGNATURES = {
     "cnmf_b200_online_inner": (i32, [vp, i64, vp, i64, vp, vp, vp, i64, i32, i32, f32, f32, f32, f32, i32, vp, vp,
                                      vp, vp]),
     "cnmf_b200_kl_constants": (i32, [vp, i64, vp, vp]),
-    "cnmf_b200_kl_half_step": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, i32, i32, f32, f32, f32, vp]),
+    "cnmf_b200_to_half": (i32, [vp, vp, i64, vp]),
+    "cnmf_b200_kl_half_step": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, vp, i32, i32, f32, f32, f32, vp]),
     "cnmf_b200_kl_workspace_bytes": (i64, [C.POINTER(KlProblem)]),
     "cnmf_b200_kl_iterate": (i32, [C.POINTER(KlProblem), i32, vp]),
     "cnmf_b200_kl_objective": (i32, [C.POINTER(KlProblem), vp]),

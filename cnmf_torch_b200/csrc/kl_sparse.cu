@@ -13,12 +13,14 @@
 // Replaces run_nmf(beta_loss='kullback-leibler') (external nmf-torch, called at
 // /root/reference/src/cnmf/cnmf.py:819); the update is sklearn/decomposition/_nmf.py:562-607 /
 // 640-678 restated with the reference's epsilon rule (cnmf.py:370-371).
+#include <cuda_fp16.h>
+
 #include "common.cuh"
 
 namespace cnmf {
 
 constexpr int KL_THREADS = 128;  // replicates per CTA (one per thread)
-constexpr int KL_ROWS = 4;       // CSR rows per CTA, processed one after the other
+constexpr int KL_ROWS = 4;       // max CSR rows per CTA (one after the other); 1 when there are few, long rows
 
 template <int KP>
 __device__ __forceinline__ void load_vec(const float* __restrict__ p, float (&v)[KP]) {
@@ -29,19 +31,41 @@ __device__ __forceinline__ void load_vec(const float* __restrict__ p, float (&v)
   }
 }
 
+// The fixed factor is gathered once per non-zero and replicate: that gather (nnz * R * Kp values per
+// half-step) is what bounds the kernel, so the gathered copy is kept in fp16 (11-bit significand, the same
+// operand precision as the tf32 copies of the dense path; values below 6e-5 become subnormal, an absolute
+// error < 3e-8 that is irrelevant inside s = h.w).  Masters stay fp32; every half-step writes the fp16
+// copy of the factor it updates next to the fp32 state.
+template <int KP>
+__device__ __forceinline__ void load_vec_h(const __half* __restrict__ p, float (&v)[KP]) {
+#pragma unroll
+  for (int c = 0; c < KP; c += 4) {
+    const uint2 t = *reinterpret_cast<const uint2*>(p + c);
+    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&t.x));
+    const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
+    v[c] = a.x; v[c + 1] = a.y; v[c + 2] = b.x; v[c + 3] = b.y;
+  }
+}
+
+__global__ void to_half_kernel(const float* __restrict__ src, __half* __restrict__ dst, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    dst[i] = __float2half_rn(fminf(src[i], 65504.f));
+}
+
 template <int KP>
 __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
     const int* __restrict__ row_ptr, const int* __restrict__ col_idx, const float* __restrict__ val, int64_t M,
-    const float* __restrict__ F, float* __restrict__ state, const float* __restrict__ fsum,
-    const uint8_t* __restrict__ active, int R, float l1, float l2, float eps) {
+    const __half* __restrict__ F, float* __restrict__ state, __half* __restrict__ state_h,
+    const float* __restrict__ fsum, const uint8_t* __restrict__ active, int R, float l1, float l2, float eps,
+    int rows_per_cta) {
   const int r = blockIdx.y * KL_THREADS + threadIdx.x;
   if (r >= R) return;
   if (active != nullptr && active[r] == 0) return;
   const int64_t rk = (int64_t)R * KP;
   float den[KP];
   load_vec<KP>(fsum + (int64_t)r * KP, den);
-  const int64_t row0 = (int64_t)blockIdx.x * KL_ROWS;
-  for (int rr = 0; rr < KL_ROWS; ++rr) {
+  const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;
+  for (int rr = 0; rr < rows_per_cta; ++rr) {
     const int64_t row = row0 + rr;
     if (row >= M) break;
     float* sp = state + row * rk + (int64_t)r * KP;
@@ -51,30 +75,37 @@ __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
     for (int k = 0; k < KP; ++k) num[k] = 0.f;
     const int beg = row_ptr[row], end = row_ptr[row + 1];
     int p = beg;
-    // two non-zeros in flight per thread to overlap the dependent index -> gather latency
-    for (; p + 1 < end; p += 2) {
-      const int j0 = col_idx[p], j1 = col_idx[p + 1];
-      const float x0 = val[p], x1 = val[p + 1];
-      float w0[KP], w1[KP];
-      load_vec<KP>(F + (int64_t)j0 * rk + (int64_t)r * KP, w0);
-      load_vec<KP>(F + (int64_t)j1 * rk + (int64_t)r * KP, w1);
-      float s0 = 0.f, s1 = 0.f;
+    // several non-zeros in flight per thread: the index -> gather -> dot -> divide chain of one non-zero is
+    // long, and with one thread per (row, replicate) there is no other source of parallelism
+    constexpr int U = (KP <= 12) ? 4 : 2;
+    for (; p + U <= end; p += U) {
+      int j[U];
+      float x[U], w[U][KP], sa[U], sb[U], q[U];
 #pragma unroll
-      for (int k = 0; k < KP; ++k) { s0 = fmaf(h[k], w0[k], s0); s1 = fmaf(h[k], w1[k], s1); }
-      const float q0 = x0 > 0.f ? __fdiv_rn(x0, fmaxf(s0, eps)) : 0.f;
-      const float q1 = x1 > 0.f ? __fdiv_rn(x1, fmaxf(s1, eps)) : 0.f;
+      for (int u = 0; u < U; ++u) { j[u] = col_idx[p + u]; x[u] = val[p + u]; }
 #pragma unroll
-      for (int k = 0; k < KP; ++k) num[k] = fmaf(q1, w1[k], fmaf(q0, w0[k], num[k]));
+      for (int u = 0; u < U; ++u) load_vec_h<KP>(F + (int64_t)j[u] * rk + (int64_t)r * KP, w[u]);
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        sa[u] = 0.f; sb[u] = 0.f;
+#pragma unroll
+        for (int k = 0; k < KP; k += 2) { sa[u] = fmaf(h[k], w[u][k], sa[u]); sb[u] = fmaf(h[k + 1], w[u][k + 1], sb[u]); }
+        q[u] = x[u] > 0.f ? __fdiv_rn(x[u], fmaxf(sa[u] + sb[u], eps)) : 0.f;
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u)
+#pragma unroll
+        for (int k = 0; k < KP; ++k) num[k] = fmaf(q[u], w[u][k], num[k]);
     }
-    if (p < end) {
+    for (; p < end; ++p) {
       const int j0 = col_idx[p];
       const float x0 = val[p];
       float w0[KP];
-      load_vec<KP>(F + (int64_t)j0 * rk + (int64_t)r * KP, w0);
-      float s0 = 0.f;
+      load_vec_h<KP>(F + (int64_t)j0 * rk + (int64_t)r * KP, w0);
+      float s0 = 0.f, s1 = 0.f;
 #pragma unroll
-      for (int k = 0; k < KP; ++k) s0 = fmaf(h[k], w0[k], s0);
-      const float q0 = x0 > 0.f ? __fdiv_rn(x0, fmaxf(s0, eps)) : 0.f;
+      for (int k = 0; k < KP; k += 2) { s0 = fmaf(h[k], w0[k], s0); s1 = fmaf(h[k + 1], w0[k + 1], s1); }
+      const float q0 = x0 > 0.f ? __fdiv_rn(x0, fmaxf(s0 + s1, eps)) : 0.f;
 #pragma unroll
       for (int k = 0; k < KP; ++k) num[k] = fmaf(q0, w0[k], num[k]);
     }
@@ -87,6 +118,16 @@ __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
     }
 #pragma unroll
     for (int c = 0; c < KP; c += 4) *reinterpret_cast<float4*>(sp + c) = make_float4(h[c], h[c + 1], h[c + 2], h[c + 3]);
+    if (state_h != nullptr) {
+      __half* hp = state_h + row * rk + (int64_t)r * KP;
+#pragma unroll
+      for (int c = 0; c < KP; c += 4) {
+        uint2 t;
+        *reinterpret_cast<__half2*>(&t.x) = __floats2half2_rn(fminf(h[c], 65504.f), fminf(h[c + 1], 65504.f));
+        *reinterpret_cast<__half2*>(&t.y) = __floats2half2_rn(fminf(h[c + 2], 65504.f), fminf(h[c + 3], 65504.f));
+        *reinterpret_cast<uint2*>(hp + c) = t;
+      }
+    }
   }
 }
 
@@ -199,18 +240,29 @@ static int launch_colsum(const float* A, int64_t L, int64_t C, float* out, doubl
   return 0;
 }
 
-static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t M, const float* F, float* state,
-                          const float* fsum, const uint8_t* active, int R, int Kp, float l1, float l2, float eps,
-                          cudaStream_t st) {
-  dim3 grid((unsigned)ceil_div(M, KL_ROWS), (unsigned)ceil_div(R, KL_THREADS));
-  CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP><<<grid, KL_THREADS, 0, st>>>(rp, ci, v, M, F, state, fsum, active, R,
-                                                                               l1, l2, eps)));
+static int launch_to_half(const float* src, __half* dst, int64_t n, cudaStream_t st) {
+  if (n == 0) return 0;
+  int64_t blocks = ceil_div(n, 256 * 8);
+  if (blocks > 148 * 16) blocks = 148 * 16;
+  to_half_kernel<<<(unsigned)blocks, 256, 0, st>>>(src, dst, n);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t M, const __half* F, float* state,
+                          __half* state_h, const float* fsum, const uint8_t* active, int R, int Kp, float l1, float l2,
+                          float eps, cudaStream_t st) {
+  // few long rows (the gene-major half-step): one row per CTA so that there are enough CTAs to fill the SMs
+  const int rows = M >= 148 * 5 * 4 * KL_ROWS ? KL_ROWS : 1;
+  dim3 grid((unsigned)ceil_div(M, rows), (unsigned)ceil_div(R, KL_THREADS));
+  CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP><<<grid, KL_THREADS, 0, st>>>(rp, ci, v, M, F, state, state_h, fsum,
+                                                                               active, R, l1, l2, eps, rows)));
   CNMF_LAUNCH_CHECK();
   return 0;
 }
 
 struct KlLayout {
-  int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_cpart, off_opart, total;
+  int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_cpart, off_opart, off_wh, off_hh, total;
   int nblk_obj;
 };
 
@@ -226,6 +278,8 @@ static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
   l.off_cpart = off; off += align_up(ceil_div(Lmax, CS_ROWS) * C * 4, 256);
   l.nblk_obj = (int)ceil_div(p->n_cells, KLO_ROWS);
   l.off_opart = off; off += align_up((int64_t)l.nblk_obj * p->R * 8, 256);
+  l.off_wh = off; off += align_up(p->n_genes * C * 2, 256);   // fp16 gather copies of Wt and Hr
+  l.off_hh = off; off += align_up(p->n_cells * C * 2, 256);
   l.total = off;
   return l;
 }
@@ -289,13 +343,20 @@ int64_t cnmf_b200_kl_workspace_bytes(const cnmf_b200_kl_problem* p) {
   return kl_layout(p).total;
 }
 
-int cnmf_b200_kl_half_step(const int32_t* row_ptr, const int32_t* col_idx, const float* val, int64_t M, const float* F,
-                           float* state, const float* fsum, const uint8_t* active, int32_t R, int32_t Kp, float l1,
-                           float l2, float eps, void* stream) {
-  CNMF_CHECK_ARG(row_ptr && col_idx && val && F && state && fsum, "kl_half_step: null pointer");
+int cnmf_b200_to_half(const float* src, void* dst, int64_t n, void* stream) {
+  CNMF_CHECK_ARG(src && dst && n >= 0, "to_half: bad argument");
+  return launch_to_half(src, reinterpret_cast<__half*>(dst), n, (cudaStream_t)stream);
+}
+
+int cnmf_b200_kl_half_step(const int32_t* row_ptr, const int32_t* col_idx, const float* val, int64_t M,
+                           const void* F_half, float* state, void* state_half, const float* fsum,
+                           const uint8_t* active, int32_t R, int32_t Kp, float l1, float l2, float eps, void* stream) {
+  CNMF_CHECK_ARG(row_ptr && col_idx && val && F_half && state && fsum, "kl_half_step: null pointer");
   CNMF_CHECK_ARG(M > 0 && R > 0, "kl_half_step: empty shape");
-  CNMF_CHECK_ARG(aligned16(F) && aligned16(state) && aligned16(fsum), "kl_half_step: pointers must be 16-byte aligned");
-  return launch_kl_half(row_ptr, col_idx, val, M, F, state, fsum, active, R, Kp, l1, l2, eps, (cudaStream_t)stream);
+  CNMF_CHECK_ARG((reinterpret_cast<uintptr_t>(F_half) & 7u) == 0 && aligned16(state) && aligned16(fsum),
+                 "kl_half_step: F_half must be 8-byte, state and fsum 16-byte aligned");
+  return launch_kl_half(row_ptr, col_idx, val, M, reinterpret_cast<const __half*>(F_half), state,
+                        reinterpret_cast<__half*>(state_half), fsum, active, R, Kp, l1, l2, eps, (cudaStream_t)stream);
 }
 
 int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* stream) {
@@ -309,12 +370,17 @@ int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* s
   float* hsum = reinterpret_cast<float*>(ws + l.off_hsum);
   float* cpart = reinterpret_cast<float*>(ws + l.off_cpart);
   const int64_t C = (int64_t)p->R * p->Kp;
+  __half* Wh = reinterpret_cast<__half*>(ws + l.off_wh);
+  __half* Hh = reinterpret_cast<__half*>(ws + l.off_hh);
+  if (n_iters > 0) CNMF_TRY(launch_to_half(p->Wt, Wh, p->n_genes * C, st));  // Hh is written by the first H half-step
   for (int it = 0; it < n_iters; ++it) {
     CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, nullptr, cpart, st));
-    CNMF_TRY(launch_kl_half(p->row_ptr, p->col_idx, p->val, p->n_cells, p->Wt, p->Hr, wsum, p->active, p->R, p->Kp,
+    CNMF_TRY(launch_kl_half(p->row_ptr, p->col_idx, p->val, p->n_cells, Wh, p->Hr, Hh, wsum, p->active, p->R, p->Kp,
                             p->l1_H, p->l2_H, p->eps, st));
+    if (it == 0 && p->active != nullptr)  // frozen replicates skip the write: their copy must exist too
+      CNMF_TRY(launch_to_half(p->Hr, Hh, p->n_cells * C, st));
     CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, nullptr, cpart, st));
-    CNMF_TRY(launch_kl_half(p->t_row_ptr, p->t_col_idx, p->t_val, p->n_genes, p->Hr, p->Wt, hsum, p->active, p->R,
+    CNMF_TRY(launch_kl_half(p->t_row_ptr, p->t_col_idx, p->t_val, p->n_genes, Hh, p->Wt, Wh, hsum, p->active, p->R,
                             p->Kp, p->l1_W, p->l2_W, p->eps, st));
   }
   if (p->err2 != nullptr && n_iters > 0) CNMF_TRY(kl_objective_impl(p, l, st));

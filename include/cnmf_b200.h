@@ -210,13 +210,19 @@ int cnmf_b200_online_inner(const float* Pt, int64_t ldp, float* state, int64_t l
  * (sklearn _nmf.py:113-157). */
 int cnmf_b200_kl_constants(const float* val, int64_t nnz, double* out2, void* stream);
 
+/* dst (fp16) = src rounded to nearest, clamped at 65504.  The gathered copy of a factor. */
+int cnmf_b200_to_half(const float* src, void* dst, int64_t n, void* stream);
+
 /* One half-step: for every CSR row m < M and replicate r,
  *   state[m, r, k] <- state[m, r, k] * max(sum_j q_mj F[j, r, k] - l1, 0) / (fsum[r, k] + l2 state[m, r, k]),
  *   q_mj = x_mj / max(sum_k state[m, r, k] F[j, r, k], eps) over the stored entries of row m,
- * rate 0 where the denominator is below eps.  fsum[r*Kp + k] = sum_j F[j, r, k]. */
+ * rate 0 where the denominator is below eps.  fsum[r*Kp + k] = sum_j F[j, r, k] (from the fp32 master).
+ * F_half is the fp16 copy of the fixed factor (the per-non-zero gather is what bounds this kernel);
+ * state_half (may be NULL) receives the fp16 copy of the updated rows for the next half-step. */
 int cnmf_b200_kl_half_step(const int32_t* row_ptr, const int32_t* col_idx, const float* val, int64_t M,
-                           const float* F, float* state, const float* fsum, const uint8_t* active,
-                           int32_t R, int32_t Kp, float l1, float l2, float eps, void* stream);
+                           const void* F_half, float* state, void* state_half, const float* fsum,
+                           const uint8_t* active, int32_t R, int32_t Kp, float l1, float l2, float eps,
+                           void* stream);
 
 typedef struct cnmf_b200_kl_problem {
   int64_t n_cells, n_genes, nnz;

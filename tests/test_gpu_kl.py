@@ -31,7 +31,9 @@ def test_kl_constants(problem):
 
 @pytest.mark.parametrize("K", [3, 5, 9, 13])
 def test_kl_single_iteration_matches_oracle(problem, K):
-    """One full iteration (H then W) elementwise against the oracle's dense formula."""
+    """One full iteration (H then W) elementwise against the oracle's dense formula.  The gathered copy of
+    the fixed factor is fp16 (11-bit significand, like the tf32 operands of the dense path), so single
+    entries agree to ~1e-3 relative; the objective-level bar of north_star is checked in the next test."""
     from cnmf_torch_b200.kl_engine import SparseKLEngine
     eng = SparseKLEngine(problem)
     H0, W0 = eng.make_init(K, [7, 8])
@@ -42,8 +44,9 @@ def test_kl_single_iteration_matches_oracle(problem, K):
     for r in range(2):
         h = no.mu_kl_H(xt, H0[r], W0[r], 0.0, 0.0, 1e-16)
         w = no.mu_kl_W(xt, h, W0[r], 0.0, 0.0, 1e-16)
-        np.testing.assert_allclose(H[r], h.numpy(), rtol=3e-5, atol=1e-7)
-        np.testing.assert_allclose(W[r], w.numpy(), rtol=3e-5, atol=1e-7)
+        np.testing.assert_allclose(H[r], h.numpy(), rtol=2e-3, atol=1e-6)
+        np.testing.assert_allclose(W[r], w.numpy(), rtol=2e-3, atol=1e-6)
+        assert np.abs(H[r] / np.maximum(h.numpy(), 1e-12) - 1).mean() < 2e-4    # unbiased, small on average
 
 
 @pytest.mark.parametrize("K", [5, 12])
