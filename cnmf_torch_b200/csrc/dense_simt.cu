@@ -399,6 +399,17 @@ int launch_frob_objective(double normX2, const double* partW, int nblkW, const d
   return 0;
 }
 
+__global__ void add_cross_kernel(double* __restrict__ part, const double* __restrict__ extra, int64_t n) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) part[i * 2] += extra[i * 2];   // entry 0 of every (block, replicate) pair is the cross term
+}
+
+int launch_add_cross(double* part, const double* extra, int64_t n, cudaStream_t st) {
+  add_cross_kernel<<<(unsigned)ceil_div(n, 256), 256, 0, st>>>(part, extra, n);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
 int launch_objective_sums(const double* partW, int nblkW, const double* partH, int nblkH, int R, double* sums,
                           cudaStream_t st) {
   objective_sums_kernel<<<R, 32, 0, st>>>(partW, nblkW, partH, nblkH, R, sums);

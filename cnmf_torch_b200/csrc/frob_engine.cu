@@ -19,11 +19,14 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
                         cudaStream_t st);
 int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st);
 int launch_objective_sums(const double*, int, const double*, int, int, double*, cudaStream_t);
+int launch_add_cross(double* part, const double* extra, int64_t n, cudaStream_t st);
+int launch_residual_tf32(float* dst, const float* master, const float* rounded, int64_t rows, int64_t cols, int64_t ld,
+                         cudaStream_t st);
 int launch_objective_combine(double, const double*, const float*, const float*, int, int, float, float, float, float,
                              double*, cudaStream_t);
 
 struct FrobLayout {
-  int64_t off_pt, off_gram, off_partH, off_partW, off_zero, off_wop, off_hop, total;
+  int64_t off_pt, off_gram, off_partH, off_partW, off_zero, off_wop, off_hop, off_hlo, off_partW2, total;
   int nblkH, nblkW;
   int impl;
 };
@@ -61,8 +64,31 @@ static FrobLayout frob_layout(const cnmf_b200_frob_problem* p) {
   if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up(rk * p->ldw * 4, 256);
   l.off_hop = off;
   if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up(rk * p->ldh * 4, 256);
+  // ... and, for the objective only, the residual H - tf32(H) with its own partial sums
+  l.off_hlo = off;
+  if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up(rk * p->ldh * 4, 256);
+  l.off_partW2 = off;
+  if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up((int64_t)l.nblkW * p->R * 2 * 8, 256);
   l.total = off;
   return l;
+}
+
+// tcgen05 path: the cross term <W, H^T X> was formed from the tf32 copy of H.  Add <W, (H - tf32 H)^T X>
+// (a second frozen pass on the residual) so that the objective is evaluated for the fp32 factors: without
+// it the evaluation noise (~2.5e-5 relative) trips run_nmf's "prev <= cur" stop a check or two early.
+static int tc_cross_residual(const cnmf_b200_frob_problem* p, const FrobLayout& l, cudaStream_t st) {
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  float* Hop = reinterpret_cast<float*>(ws + l.off_hop);
+  float* Hlo = reinterpret_cast<float*>(ws + l.off_hlo);
+  double* partW = reinterpret_cast<double*>(ws + l.off_partW);
+  double* partW2 = reinterpret_cast<double*>(ws + l.off_partW2);
+  uint8_t* zero = reinterpret_cast<uint8_t*>(ws + l.off_zero);
+  const int64_t rk = (int64_t)p->R * p->Kp;
+  CNMF_CUDA(cudaMemsetAsync(zero, 0, p->R, st));
+  CNMF_TRY(launch_residual_tf32(Hlo, p->Ht, Hop, rk, p->n_cells, p->ldh, st));
+  CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, p->n_genes, p->n_cells, Hlo, p->ldh, p->Wall, nullptr, p->ldw, p->gramH,
+                               zero, p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW2, st));
+  return launch_add_cross(partW, partW2, (int64_t)l.nblkW * p->R, st);
 }
 
 static int check_problem(const cnmf_b200_frob_problem* p) {
@@ -174,6 +200,7 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
     CNMF_TRY(launch_gram(p->Wall, p->ldw, p->R, p->Kp, G, p->gramW, gws, st));
   }
   if (p->err2 != nullptr && n_iters > 0) {
+    if (l.impl == CNMF_B200_IMPL_TCGEN05) CNMF_TRY(tc_cross_residual(p, l, st));
     CNMF_TRY(launch_frob_objective(p->normX2, partW, l.nblkW, partH, l.nblkH, p->gramW, p->gramH, p->R,
                                    p->Kp, p->l1_H, p->l2_H, p->l1_W, p->l2_W, p->err2, st));
   }
@@ -206,6 +233,7 @@ static int frob_objective_partials(const cnmf_b200_frob_problem* p, const FrobLa
   } else {
     CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, nullptr, p->ldw, p->gramH, zero,
                                  p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, partW, st));
+    CNMF_TRY(tc_cross_residual(p, l, st));
   }
   // sum(H) for the L1 term comes from partH; with l1_H == 0 the zeros written above are enough
   if (p->l1_H != 0.f) {

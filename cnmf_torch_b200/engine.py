@@ -83,21 +83,23 @@ class DenseFrobeniusEngine:
         ws = torch.empty(self.lib.cnmf_b200_sumsq_workspace_bytes(), device=self.device, dtype=torch.uint8)
         out = torch.zeros(2, device=self.device, dtype=torch.float64)
         st = torch.cuda.current_stream().cuda_stream
+        # mean(X) for the random init: from the fp32 matrix, fp64 on device
+        x_sum = float(self.X[:, :self.G].sum(dtype=torch.float64).item())
+        if impl != _lib.IMPL_SIMT:
+            # static operands of the tcgen05 path: round once to tf32 (nearest) so that the tensor core's
+            # mantissa truncation is unbiased.  The objective is then evaluated for the matrix the tensor
+            # cores actually see, ||tf32(X)||^2 (relative difference to ||X||^2 ~1e-7), which keeps the
+            # trace identity self-consistent.
+            check(self.lib.cnmf_b200_round_tf32(ptr(self.X), self.X.numel(), st), "round_tf32")
+            check(self.lib.cnmf_b200_round_tf32(ptr(self.Xt), self.Xt.numel(), st), "round_tf32")
         check(self.lib.cnmf_b200_sumsq(ptr(self.X), self.N, self.G, self.ldx, ptr(out), ptr(ws), st), "sumsq")
         self.normX2 = float(out[0].item())
-        # mean(X) for the random init, fp64 on device
-        x_sum = float(self.X[:, :self.G].sum(dtype=torch.float64).item())
         self.N_total = self.N
         if row_group is not None:
             from . import dist as _d
             tot = _d.allreduce_scalars([self.normX2, x_sum, float(self.N)], self.device, row_group)
             self.normX2, x_sum, self.N_total = float(tot[0]), float(tot[1]), int(round(tot[2]))
         self.x_mean = x_sum / (float(self.N_total) * self.G)
-        if impl != _lib.IMPL_SIMT:
-            # static operands of the tcgen05 path: round once to tf32 (nearest) so that the tensor
-            # core's mantissa truncation is unbiased; ||X||^2 and mean(X) above come from the fp32 X
-            check(self.lib.cnmf_b200_round_tf32(ptr(self.X), self.X.numel(), st), "round_tf32")
-            check(self.lib.cnmf_b200_round_tf32(ptr(self.Xt), self.Xt.numel(), st), "round_tf32")
 
     # ------------------------------------------------------------------------------------
     def make_init(self, K: int, seeds):
