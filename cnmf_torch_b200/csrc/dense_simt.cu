@@ -351,17 +351,30 @@ __global__ void __launch_bounds__(32) objective_combine_kernel(double normX2, co
 // ---------------------------------------------------------------------------------------------
 // host-side launchers
 // ---------------------------------------------------------------------------------------------
-int launch_gram(const float* F, int64_t ld, int R, int Kp, int64_t L, float* gram, void* ws,
-                cudaStream_t st) {
+int gram_num_tiles(int64_t L) { return (int)gram_tiles(L); }
+
+int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st) {
   const int ntile = (int)gram_tiles(L);
   float* partial = reinterpret_cast<float*>(ws);
   dim3 grid(ntile, R);
   CNMF_DISPATCH_KP(Kp, (gram_partial_kernel<KP><<<grid, GRAM_THREADS, 0, st>>>(F, ld, L, partial, ntile)));
   CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cudaStream_t st) {
+  const int ntile = (int)gram_tiles(L);
   const int64_t total = (int64_t)R * Kp * Kp;
-  gram_final_kernel<<<(unsigned)ceil_div(total, 128), 128, 0, st>>>(partial, ntile, Kp * Kp, gram, total);
+  gram_final_kernel<<<(unsigned)ceil_div(total, 128), 128, 0, st>>>(reinterpret_cast<const float*>(ws), ntile, Kp * Kp,
+                                                                    gram, total);
   CNMF_LAUNCH_CHECK();
   return 0;
+}
+
+int launch_gram(const float* F, int64_t ld, int R, int Kp, int64_t L, float* gram, void* ws,
+                cudaStream_t st) {
+  CNMF_TRY(launch_gram_partial(F, ld, R, Kp, L, ws, st));
+  return launch_gram_final(ws, L, R, Kp, gram, st);
 }
 
 int launch_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, int64_t ldb, int64_t N,

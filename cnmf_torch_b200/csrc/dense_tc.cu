@@ -51,7 +51,8 @@ struct TcParams {
   float* state;    // [R*KP x lds] fp32 master
   float* state_op; // same layout, tf32-rounded copy that the NEXT half-step's MMA reads (may be null)
   int64_t lds;
-  const float* gram;      // [R x KP x KP]
+  const float* gram;      // [R x KP x KP], or (gram_ntile > 0) the per-tile partials [R x gram_ntile x KP*KP]
+  int gram_ntile;
   const uint8_t* active;  // [R] or null
   double* partials;       // [num_m_tiles x R x 2]
   int R;
@@ -339,7 +340,20 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       if (ALGO < TC_MODE_STORE) {
         for (int i = et; i < t * KP * KP; i += ET) {
           const int rr = i / (KP * KP);
-          sgram[i] = (r0 + rr < prm.R) ? prm.gram[static_cast<int64_t>(r0) * KP * KP + i] : 0.f;
+          float g = 0.f;
+          if (r0 + rr < prm.R) {
+            if (prm.gram_ntile > 0) {
+              // fused final stage of the Gram: fixed-order fp64 sum of the per-tile partials (these warps
+              // are otherwise idle while the first tile's main loop runs)
+              const float* pp = prm.gram + (static_cast<int64_t>(r0 + rr) * prm.gram_ntile) * (KP * KP) + (i - rr * KP * KP);
+              double acc = 0.0;
+              for (int tl = 0; tl < prm.gram_ntile; ++tl) acc += static_cast<double>(pp[static_cast<int64_t>(tl) * KP * KP]);
+              g = static_cast<float>(acc);
+            } else {
+              g = prm.gram[static_cast<int64_t>(r0) * KP * KP + i];
+            }
+          }
+          sgram[i] = g;
         }
       }
       epi_bar_sync<ET>();
@@ -673,9 +687,23 @@ static int launch_tc_inst(const CUtensorMap& ma, const CUtensorMap& mb, const Tc
   return launch_tc_inst2<KP, ALGO, 1>(ma, mb, prm, plan, grid, st);
 }
 
+int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                          float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
+                          const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
+                          double* partials, cudaStream_t st);
+
 int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                         float* state, float* state_op, int64_t lds, const float* gram, const uint8_t* active, int R,
                         int Kp, int algo, float l1, float l2, float eps, double* partials, cudaStream_t st) {
+  return launch_tc_half_step_g(A, lda, M, Kd, F, ldf, state, state_op, lds, gram, 0, active, R, Kp, algo, l1, l2, eps,
+                               partials, st);
+}
+
+// gram_ntile > 0: `gram` holds the Gram kernel's per-tile partials and the epilogue warps sum them
+int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                          float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
+                          const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
+                          double* partials, cudaStream_t st) {
   TcPlan plan;
   const int sms = tc_num_sms();
   if (!tc_plan(M, Kd, R, Kp, sms, &plan)) {
@@ -686,7 +714,7 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
   CNMF_TRY(get_tensor_map(A, M, Kd, lda, TC_BM, &ma));
   CNMF_TRY(get_tensor_map(F, static_cast<int64_t>(R) * Kp, Kd, ldf, plan.BN / plan.cg, &mb));
   TcParams prm;
-  prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.active = active;
+  prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.gram_ntile = gram_ntile; prm.active = active;
   prm.partials = partials; prm.R = R; prm.t = plan.t; prm.num_m_tiles = plan.num_m_tiles; prm.num_m_groups = plan.num_m_groups;
   prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
   const int64_t tiles = static_cast<int64_t>(plan.num_m_groups) * plan.num_n_tiles;  // per CTA group

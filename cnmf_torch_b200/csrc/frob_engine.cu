@@ -17,6 +17,13 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
                         float* state, float* state_op, int64_t lds, const float* gram, const uint8_t* active,
                         int R, int Kp, int algo, float l1, float l2, float eps, double* partials,
                         cudaStream_t st);
+int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                          float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
+                          const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
+                          double* partials, cudaStream_t st);
+int gram_num_tiles(int64_t L);
+int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st);
+int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cudaStream_t st);
 int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st);
 int launch_objective_sums(const double*, int, const double*, int, int, double*, cudaStream_t);
 int launch_add_cross(double* part, const double* extra, int64_t n, cudaStream_t st);
@@ -26,7 +33,7 @@ int launch_objective_combine(double, const double*, const float*, const float*, 
                              double*, cudaStream_t);
 
 struct FrobLayout {
-  int64_t off_pt, off_gram, off_partH, off_partW, off_zero, off_wop, off_hop, off_hlo, off_partW2, total;
+  int64_t off_pt, off_gram, off_gram2, off_partH, off_partW, off_zero, off_wop, off_hop, off_hlo, off_partW2, total;
   int nblkH, nblkW;
   int impl;
 };
@@ -52,6 +59,8 @@ static FrobLayout frob_layout(const cnmf_b200_frob_problem* p) {
   l.off_gram = off;
   int64_t gw = cnmf_b200_gram_workspace_bytes(p->R, p->Kp, p->n_cells);
   int64_t gg = cnmf_b200_gram_workspace_bytes(p->R, p->Kp, p->n_genes);
+  off += align_up(gw > gg ? gw : gg, 256);
+  l.off_gram2 = off;  // second partial buffer: both Grams' partials are live at once on the tcgen05 path
   off += align_up(gw > gg ? gw : gg, 256);
   l.off_partH = off;
   off += align_up((int64_t)l.nblkH * p->R * 2 * 8, 256);
@@ -173,31 +182,44 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
   const int64_t rk = (int64_t)p->R * p->Kp;
   const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
 
+  void* gws2 = ws + l.off_gram2;
+  const int ntH = gram_num_tiles(N), ntW = gram_num_tiles(G);
   for (int it = 0; it < n_iters; ++it) {
     // the objective only reads the partial sums of the last iteration (tcgen05 path skips them otherwise)
     const bool last = (it == n_iters - 1) && p->err2 != nullptr;
     double* pH = (last || l.impl == CNMF_B200_IMPL_SIMT) ? partH : nullptr;
     double* pW = (last || l.impl == CNMF_B200_IMPL_SIMT) ? partW : nullptr;
-    // ---- H half-step: Pt[RKp x N] = Wall X^T ; Ht <- update(Ht; Pt, gramW)
     if (l.impl == CNMF_B200_IMPL_SIMT) {
+      // ---- H half-step: Pt[RKp x N] = Wall X^T ; Ht <- update(Ht; Pt, gramW)
       CNMF_TRY(launch_gemm_nt(p->Wall, p->ldw, rk, p->X, p->ldx, N, G, Pt, ldpH, st));
       CNMF_TRY(launch_row_update(Pt, ldpH, p->Ht, p->ldh, p->gramW, p->active, N, p->R, p->Kp, p->algo,
                                  p->l1_H, p->l2_H, p->eps, partH, st));
-    } else {
-      CNMF_TRY(launch_tc_half_step(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh, p->gramW, p->active,
-                                   p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st));
-    }
-    CNMF_TRY(launch_gram(p->Ht, p->ldh, p->R, p->Kp, N, p->gramH, gws, st));
-    // ---- W half-step: Pt[RKp x G] = Ht Xt^T ; Wall <- update(Wall; Pt, gramH)
-    if (l.impl == CNMF_B200_IMPL_SIMT) {
+      CNMF_TRY(launch_gram(p->Ht, p->ldh, p->R, p->Kp, N, p->gramH, gws, st));
+      // ---- W half-step: Pt[RKp x G] = Ht Xt^T ; Wall <- update(Wall; Pt, gramH)
       CNMF_TRY(launch_gemm_nt(p->Ht, p->ldh, rk, p->Xt, p->ldxt, G, N, Pt, ldpW, st));
       CNMF_TRY(launch_row_update(Pt, ldpW, p->Wall, p->ldw, p->gramH, p->active, G, p->R, p->Kp, p->algo,
                                  p->l1_W, p->l2_W, p->eps, partW, st));
+      CNMF_TRY(launch_gram(p->Wall, p->ldw, p->R, p->Kp, G, p->gramW, gws, st));
     } else {
-      CNMF_TRY(launch_tc_half_step(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, Wop, p->ldw, p->gramH,
-                                   p->active, p->R, p->Kp, p->algo, p->l1_W, p->l2_W, p->eps, pW, st));
+      // tcgen05 path: 4 launches per iteration.  The Gram kernels leave per-tile partials; the half-step
+      // that consumes a Gram sums them in its (otherwise idle) epilogue warps.
+      if (it == 0)
+        CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh, p->gramW, 0, p->active,
+                                       p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st));
+      else
+        CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh,
+                                       reinterpret_cast<const float*>(gws2), ntW, p->active, p->R, p->Kp, p->algo,
+                                       p->l1_H, p->l2_H, p->eps, pH, st));
+      CNMF_TRY(launch_gram_partial(p->Ht, p->ldh, p->R, p->Kp, N, gws, st));
+      CNMF_TRY(launch_tc_half_step_g(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, Wop, p->ldw,
+                                     reinterpret_cast<const float*>(gws), ntH, p->active, p->R, p->Kp, p->algo,
+                                     p->l1_W, p->l2_W, p->eps, pW, st));
+      CNMF_TRY(launch_gram_partial(p->Wall, p->ldw, p->R, p->Kp, G, gws2, st));
+      if (it == n_iters - 1) {  // leave both Grams in their final form (objective, next call, API contract)
+        CNMF_TRY(launch_gram_final(gws, N, p->R, p->Kp, p->gramH, st));
+        CNMF_TRY(launch_gram_final(gws2, G, p->R, p->Kp, p->gramW, st));
+      }
     }
-    CNMF_TRY(launch_gram(p->Wall, p->ldw, p->R, p->Kp, G, p->gramW, gws, st));
   }
   if (p->err2 != nullptr && n_iters > 0) {
     if (l.impl == CNMF_B200_IMPL_TCGEN05) CNMF_TRY(tc_cross_residual(p, l, st));
