@@ -228,7 +228,13 @@ def main():
 
     # ---------------- device-resident arm: `value` ------------------------------------------
     eng = DenseFrobeniusEngine(x_pinned, device=dev, impl=impl)
-    batches = [eng.new_batch(k, seeds=seeds[i], algo=ALGO) for i, k in enumerate(KS)]
+    # replicates of K values that share a padded Kp are stacked into one batch (K=7,8 -> Kp 8; K=9..12 -> Kp 12),
+    # exactly as the public factorize_many does
+    from cnmf_torch_b200.engine import FrobBatch, pad4
+    stacks = {}
+    for i, k in enumerate(KS):
+        stacks.setdefault(pad4(k), []).append((k,) + tuple(eng.make_init(k, seeds[i])))
+    batches = [FrobBatch(eng, None, None, None, ALGO, 0.0, 0.0, 0.0, 0.0, 1e-16, groups=g) for g in stacks.values()]
     flush = torch.empty(256 * 1024 * 1024, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     from cnmf_torch_b200.engine import iterate_concurrently
@@ -263,7 +269,7 @@ def main():
     assert all(np.isfinite(l).all() for l in losses)
 
     # ---------------- dominant kernel alone: roofline ----------------------------------------
-    b10 = batches[KS.index(10)]
+    b10 = eng.new_batch(10, seeds=seeds[KS.index(10)], algo=ALGO)
     p = b10.p
     st = torch.cuda.current_stream().cuda_stream
     n_rep = 50

@@ -115,6 +115,58 @@ __global__ void __launch_bounds__(GRAM_THREADS) gram_partial_kernel(const float*
   }
 }
 
+// Kp <= 12: the upper triangle of the Gram (Kp(Kp+1)/2 <= 78 values) fits in registers.  One CTA = one
+// replicate x one column split; lane = column inside a 32-column group (coalesced loads, no shared-memory
+// staging, no barrier in the main loop), warps stride over the groups, two groups in flight per warp.
+// Far fewer and longer-lived CTAs than the tiled kernel: with thousands of tiny CTAs (R = 400) the tiled
+// kernel spent its time in CTA scheduling, not in arithmetic.
+constexpr int GW_THREADS = 256;
+constexpr int GW_SPLIT = 8192;  // columns per CTA
+
+template <int KP>
+__global__ void __launch_bounds__(GW_THREADS) gram_warp_kernel(const float* __restrict__ F, int64_t ld, int64_t L,
+                                                               float* __restrict__ partial, int nsplit) {
+  constexpr int NT = KP * (KP + 1) / 2;
+  __shared__ float red[GW_THREADS / 32][NT];
+  const int r = blockIdx.y, split = blockIdx.x;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const float* Fr = F + (int64_t)r * KP * ld;
+  const int64_t l_begin = (int64_t)split * GW_SPLIT;
+  const int64_t l_end = min(L, l_begin + (int64_t)GW_SPLIT);
+  float acc[NT];
+#pragma unroll
+  for (int i = 0; i < NT; ++i) acc[i] = 0.f;
+  for (int64_t l0 = l_begin + warp * 32; l0 < l_end; l0 += (GW_THREADS / 32) * 32 * 2) {
+    float f0[KP], f1[KP];
+    const int64_t c0 = l0 + lane, c1 = l0 + (GW_THREADS / 32) * 32 + lane;
+#pragma unroll
+    for (int a = 0; a < KP; ++a) {
+      f0[a] = c0 < l_end ? Fr[(int64_t)a * ld + c0] : 0.f;
+      f1[a] = c1 < l_end ? Fr[(int64_t)a * ld + c1] : 0.f;
+    }
+    int t = 0;
+#pragma unroll
+    for (int a = 0; a < KP; ++a)
+#pragma unroll
+      for (int b = a; b < KP; ++b, ++t) acc[t] = fmaf(f1[a], f1[b], fmaf(f0[a], f0[b], acc[t]));
+  }
+#pragma unroll
+  for (int i = 0; i < NT; ++i) {
+    const float v = warp_sum(acc[i]);
+    if (lane == 0) red[warp][i] = v;
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < KP * KP; i += GW_THREADS) {
+    const int a = i / KP, b = i - a * KP;
+    const int lo = a < b ? a : b, hi = a < b ? b : a;
+    const int t = lo * KP - lo * (lo - 1) / 2 + (hi - lo);  // index of (lo, hi) in the row-major upper triangle
+    float v = 0.f;
+#pragma unroll
+    for (int w = 0; w < GW_THREADS / 32; ++w) v += red[w][t];
+    partial[((int64_t)r * nsplit + split) * (KP * KP) + i] = v;
+  }
+}
+
 __global__ void gram_final_kernel(const float* __restrict__ partial, int nsplit, int np,
                                   float* __restrict__ gram, int64_t total) {
   int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;  // over R*np
@@ -351,11 +403,23 @@ __global__ void __launch_bounds__(32) objective_combine_kernel(double normX2, co
 // ---------------------------------------------------------------------------------------------
 // host-side launchers
 // ---------------------------------------------------------------------------------------------
-int gram_num_tiles(int64_t L) { return (int)gram_tiles(L); }
+// number of partial Grams per replicate that launch_gram_partial leaves in the workspace
+int gram_num_tiles(int64_t L, int Kp) { return Kp <= 12 ? (int)ceil_div(L, GW_SPLIT) : (int)gram_tiles(L); }
 
 int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st) {
-  const int ntile = (int)gram_tiles(L);
   float* partial = reinterpret_cast<float*>(ws);
+  if (Kp <= 12) {
+    const int ns = (int)ceil_div(L, GW_SPLIT);
+    dim3 grid(ns, R);
+    switch (Kp) {
+      case 4: gram_warp_kernel<4><<<grid, GW_THREADS, 0, st>>>(F, ld, L, partial, ns); break;
+      case 8: gram_warp_kernel<8><<<grid, GW_THREADS, 0, st>>>(F, ld, L, partial, ns); break;
+      default: gram_warp_kernel<12><<<grid, GW_THREADS, 0, st>>>(F, ld, L, partial, ns); break;
+    }
+    CNMF_LAUNCH_CHECK();
+    return 0;
+  }
+  const int ntile = (int)gram_tiles(L);
   dim3 grid(ntile, R);
   CNMF_DISPATCH_KP(Kp, (gram_partial_kernel<KP><<<grid, GRAM_THREADS, 0, st>>>(F, ld, L, partial, ntile)));
   CNMF_LAUNCH_CHECK();
@@ -363,7 +427,7 @@ int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, vo
 }
 
 int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cudaStream_t st) {
-  const int ntile = (int)gram_tiles(L);
+  const int ntile = gram_num_tiles(L, Kp);
   const int64_t total = (int64_t)R * Kp * Kp;
   gram_final_kernel<<<(unsigned)ceil_div(total, 128), 128, 0, st>>>(reinterpret_cast<const float*>(ws), ntile, Kp * Kp,
                                                                     gram, total);

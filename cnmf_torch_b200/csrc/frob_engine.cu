@@ -21,7 +21,7 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
                           double* partials, cudaStream_t st);
-int gram_num_tiles(int64_t L);
+int gram_num_tiles(int64_t L, int Kp);
 int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st);
 int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cudaStream_t st);
 int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st);
@@ -183,7 +183,7 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
   const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
 
   void* gws2 = ws + l.off_gram2;
-  const int ntH = gram_num_tiles(N), ntW = gram_num_tiles(G);
+  const int ntH = gram_num_tiles(N, p->Kp), ntW = gram_num_tiles(G, p->Kp);
   for (int it = 0; it < n_iters; ++it) {
     // the objective only reads the partial sums of the last iteration (tcgen05 path skips them otherwise)
     const bool last = (it == n_iters - 1) && p->err2 != nullptr;

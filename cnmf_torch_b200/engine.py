@@ -154,15 +154,23 @@ class DenseFrobeniusEngine:
         them in lock-step (one small D2H per batch per check period).  Returns {K: BatchResult}."""
         from concurrent.futures import ThreadPoolExecutor
         ks = [int(k) for k in ks]
+        stacks = {}
+        for k in ks:                       # K values with the same padded Kp share one stack
+            stacks.setdefault(pad4(k), []).append(k)
         with ThreadPoolExecutor(max_workers=max(1, min(len(ks), 3))) as pool:
-            futs = [pool.submit(self.make_init, k, seeds_by_k[k]) for k in ks]
+            futs = {k: pool.submit(self.make_init, k, seeds_by_k[k]) for k in ks}
             batches = []
-            for k, f in zip(ks, futs):
-                H0, W0 = f.result()
-                batches.append(FrobBatch(self, k, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps))
+            for kp, group in stacks.items():
+                groups = [(k,) + tuple(futs[k].result()) for k in group]
+                batches.append(FrobBatch(self, None, None, None, algo, l1_H, l2_H, l1_W, l2_W, eps, groups=groups))
         streams = [torch.cuda.Stream(device=self.device) for _ in batches]
         res = run_batches(batches, tol, max_iter, check_every, return_H, streams)
-        return dict(zip(ks, res))
+        out = {}
+        for b, rb in zip(batches, res):
+            for k, sl, W, H in b.results_by_group(return_H):
+                out[k] = BatchResult(W=W, H=H, err=rb.err[sl], n_iter=rb.n_iter[sl],
+                                     trace=[(it, v[sl]) for it, v in rb.trace], launches=rb.launches)
+        return out
 
     # ------------------------------------------------------------------------------------
     def factorize_online(self, K: int, seeds=None, H0=None, W0=None, tol=1e-4, max_pass=20, chunk_size=5000,
@@ -322,7 +330,7 @@ def run_batches(batches, tol, max_iter, check_every=10, return_H=False, streams=
                 s["prev"] = np.where(s["alive"], cur, s["prev"])
     out = []
     for s, b in zip(st, batches):
-        W, H = b.results(return_H)
+        W, H = b.results(return_H) if len(b.Ks) == 1 else (None, None)   # mixed-K stacks: results_by_group
         out.append(BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * s["cur"], 0.0)), n_iter=s["n_iter"],
                                trace=s["trace"], launches=int(b.launches)))
     return out
@@ -349,17 +357,32 @@ def iterate_concurrently(batches, n: int, streams=None):
 
 
 class FrobBatch:
-    """R replicates of one K resident on the device (stacked Wall / Ht, Grams, workspace)."""
+    """Replicates resident on the device (stacked Wall / Ht, Grams, workspace).  Usually R replicates of one
+    K; ``groups`` = [(K, H0, W0), ...] stacks replicates of DIFFERENT K that share the same padded Kp (e.g.
+    K = 9, 10, 11, 12 -> Kp = 12): the kernels only see Kp (padding rows are zero and stay zero), and a
+    taller stack means more tiles per launch -- better SM fill, and the epilogue of one tile overlaps the
+    main loop of the next."""
 
-    def __init__(self, eng: DenseFrobeniusEngine, K, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps):
-        self.eng, self.K = eng, int(K)
-        self.R = int(W0.shape[0])
-        self.Kp = pad4(K)
+    def __init__(self, eng: DenseFrobeniusEngine, K, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps, groups=None):
+        if groups is None:
+            groups = [(int(K), H0, W0)]
+        self.eng = eng
+        self.Ks = [int(g[0]) for g in groups]
+        self.Rs = [int(g[2].shape[0]) for g in groups]
+        self.K = max(self.Ks)
+        self.R = sum(self.Rs)
+        self.Kp = pad4(self.K)
         if self.Kp > _lib.MAX_KP:
-            raise ValueError(f"n_components={K} exceeds the engine limit {_lib.MAX_KP}")
+            raise ValueError(f"n_components={self.K} exceeds the engine limit {_lib.MAX_KP}")
+        if any(pad4(k) != self.Kp for k in self.Ks):
+            raise ValueError("all K of one stack must round up to the same multiple of 4")
         algo_id = {"mu": _lib.ALGO_MU, "hals": _lib.ALGO_HALS}[algo]
         dev = eng.device
-        self.Wall, self.Ht, ldw, ldh = eng._upload_state(H0, W0, self.K, self.Kp)
+        parts = [eng._upload_state(h0, w0, k, self.Kp) for k, h0, w0 in groups]
+        ldw, ldh = parts[0][2], parts[0][3]
+        self.Wall = parts[0][0] if len(parts) == 1 else torch.cat([q[0] for q in parts], 0)
+        self.Ht = parts[0][1] if len(parts) == 1 else torch.cat([q[1] for q in parts], 0)
+        del parts
         R, Kp = self.R, self.Kp
         self.gramW = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
         self.gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
@@ -399,8 +422,19 @@ class FrobBatch:
         self.active.copy_(torch.from_numpy(alive.astype(np.uint8)))
 
     def results(self, return_H=False):
+        """(W [R, K, G], H [R, N, K] or None) -- for a mixed-K stack use ``results_by_group``."""
         eng = self.eng
         W = self.Wall[:, :self.K, :eng.G].contiguous().cpu().numpy()
         H = (self.Ht[:, :self.K, :eng.N].permute(0, 2, 1).contiguous().cpu().numpy()
              if return_H else None)
         return W, H
+
+    def results_by_group(self, return_H=False):
+        """[(K, slice of replicates, W [R_k, K, G], H or None)] for every group of the stack."""
+        eng, out, lo = self.eng, [], 0
+        for k, r in zip(self.Ks, self.Rs):
+            W = self.Wall[lo:lo + r, :k, :eng.G].contiguous().cpu().numpy()
+            H = (self.Ht[lo:lo + r, :k, :eng.N].permute(0, 2, 1).contiguous().cpu().numpy() if return_H else None)
+            out.append((k, slice(lo, lo + r), W, H))
+            lo += r
+        return out

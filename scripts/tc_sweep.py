@@ -8,7 +8,8 @@ lib = _lib.lib()
 x = nb_counts(2700, 2000, seed=14)
 eng = DenseFrobeniusEngine(x)
 K = int(os.environ.get("K", "10"))
-b = eng.new_batch(K, seeds=list(range(100)), algo="hals")
+RR = int(os.environ.get("R", "100"))
+b = eng.new_batch(K, seeds=list(range(RR)), algo="hals")
 p = b.p
 st = torch.cuda.current_stream().cuda_stream
 frozen = torch.zeros(b.R, dtype=torch.uint8, device="cuda")
