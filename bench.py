@@ -45,36 +45,63 @@ def _peaks():
 
 
 class ClockSampler(threading.Thread):
-    """Samples SM clock / throttle reasons of one GPU with nvidia-smi while the timed region runs."""
+    """Samples SM clock / throttle reasons of one GPU while the timed region runs (NVML every 10 ms; falls
+    back to the nvidia-smi query of the profiling recipe every 200 ms if NVML cannot be loaded)."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index: int):
         super().__init__(daemon=True)
-        self.index, self.rows, self._stop_evt = index, [], threading.Event()
+        self.index, self.sm, self.max_sm, self.reasons, self._stop_evt = index, [], [], set(), threading.Event()
+        self.nvml = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nvml = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+        except Exception:
+            self.nvml = None
+
+    def _sample_nvml(self):
+        n = self.nvml
+        self.sm.append(float(n.nvmlDeviceGetClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        self.max_sm.append(float(n.nvmlDeviceGetMaxClockInfo(self.handle, n.NVML_CLOCK_SM)))
+        r = n.nvmlDeviceGetCurrentClocksEventReasons(self.handle) if hasattr(n, "nvmlDeviceGetCurrentClocksEventReasons") \
+            else n.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+        for name, bit in (("hw_slowdown", 0x8), ("sw_power_cap", 0x4), ("sw_thermal_slowdown", 0x20),
+                          ("hw_thermal_slowdown", 0x40)):
+            if r & bit:
+                self.reasons.add(name)
+
+    def _sample_smi(self):
+        out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
+                              "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout.strip()
+        if out:
+            c = [v.strip() for v in out.split(",")]
+            self.sm.append(float(c[0])); self.max_sm.append(float(c[1]))
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], c[3:7]):
+                if v.lower().startswith("active"):
+                    self.reasons.add(name)
 
     def run(self):
         while not self._stop_evt.is_set():
             try:
-                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}",
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True,
-                                     timeout=5).stdout.strip()
-                if out:
-                    self.rows.append([c.strip() for c in out.split(",")])
+                if self.nvml is not None:
+                    self._sample_nvml()
+                else:
+                    self._sample_smi()
             except Exception:
                 pass
-            self._stop_evt.wait(0.2)
+            self._stop_evt.wait(0.01 if self.nvml is not None else 0.2)
 
     def stop(self):
         self._stop_evt.set()
         self.join(timeout=6)
-        sm = [float(r[0]) for r in self.rows if r and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) > 1 and r[1].replace(".", "").isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({n for r in self.rows for n, v in zip(names, r[3:7]) if v.lower().startswith("active")})
-        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        return {"sm_mhz": float(np.median(self.sm)) if self.sm else None,
+                "sm_max_mhz": max(self.max_sm) if self.max_sm else None,
+                "reasons": sorted(self.reasons), "samples": len(self.sm),
+                "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
 def _cpu_baseline(x, seconds_target=15.0):
@@ -193,7 +220,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
@@ -243,6 +270,48 @@ def main():
     def one_step():
         iterate_concurrently(batches, ITERS_PER_STEP, streams)
 
+    # ---------------- dominant kernel alone: roofline (before the long timed region: burst clocks,
+    # compared with the burst peak; after a sustained tensor load the 1 kW cap lowers the SM clock) ----
+    # the H half-step of the Kp=12 stack (K=9..12, 400 replicates), exactly as the timed steps launch it
+    # (live HALS update, tf32 operand copy written, no partial sums), on a scratch copy of the state
+    big = max(batches, key=lambda b: b.R * b.Kp)
+    p = big.p
+    st = torch.cuda.current_stream().cuda_stream
+    n_rep = 30
+    Wop = big.Wall.clone()
+    _lib.check(lib.cnmf_b200_round_tf32(Wop.data_ptr(), Wop.numel(), st))
+    Hs, Hop = big.Ht.clone(), big.Ht.clone()
+
+    def dominant():
+        _lib.check(lib.cnmf_b200_dense_half_step(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, Hs.data_ptr(),
+                                                 Hop.data_ptr(), p.ldh, p.gramW, None, p.R, p.Kp, p.algo, 0.0, 0.0,
+                                                 p.eps, None, st))
+    roof = None
+    if impl != _lib.IMPL_SIMT:
+        for _ in range(5):
+            dominant()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(n_rep):
+            dominant()
+        e1.record()
+        torch.cuda.synchronize()
+        k_ms = e0.elapsed_time(e1) / n_rep
+        cols = sum(k * r for k, r in zip(big.Ks, big.Rs))  # algorithmic factor columns (unpadded K)
+        flops = 2.0 * eng.N * eng.G * cols               # 2*N*G*K per replicate and half-step
+        peaks, src = _peaks()
+        peak = peaks["bf16_tflops"] / 2.0                # tf32 tensor rate = half the bf16 rate
+        ach = flops / (k_ms * 1e-3) / 1e12
+        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                # dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full`
+                # capture (profiles/r01_tc_half_step_stack_full_raw.csv): 160.3 + 57.8 MB; algorithmic bytes
+                # (X + W copy + H read + H and H-copy write) = 216 MB
+                "traffic": 218.1e6,
+                "kernel": f"tc_half_step_kernel<{big.Kp},HALS> (H half-step, K={big.Ks}, R={big.R}, live update)",
+                "kernel_ms": k_ms, "padded_frac": ach / peak * big.Kp * big.R / cols,
+                "peak_source": f"{src} bf16 burst / 2 (tf32)"}
+    del Wop, Hs, Hop
+
     for _ in range(args.warmup):
         one_step()
     torch.cuda.synchronize()
@@ -267,40 +336,6 @@ def main():
     launches = sum(b.launches for b in batches) - launches0
     losses = [b.read_loss() for b in batches]
     assert all(np.isfinite(l).all() for l in losses)
-
-    # ---------------- dominant kernel alone: roofline ----------------------------------------
-    b10 = eng.new_batch(10, seeds=seeds[KS.index(10)], algo=ALGO)
-    p = b10.p
-    st = torch.cuda.current_stream().cuda_stream
-    n_rep = 50
-    nblk = lib.cnmf_b200_row_update_blocks(eng.N)
-    part = torch.zeros(nblk * b10.R * 2, dtype=torch.float64, device=dev)
-    frozen = torch.zeros(b10.R, dtype=torch.uint8, device=dev)  # time the kernel without changing state
-    Wop = b10.Wall.clone()
-    _lib.check(lib.cnmf_b200_round_tf32(Wop.data_ptr(), Wop.numel(), st))
-
-    def dominant():
-        _lib.check(lib.cnmf_b200_dense_half_step(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, p.Ht,
-                                                 None, p.ldh, p.gramW, frozen.data_ptr(), p.R, p.Kp, p.algo, 0.0,
-                                                 0.0, p.eps, part.data_ptr(), st))
-    roof = None
-    if impl != _lib.IMPL_SIMT:
-        for _ in range(5):
-            dominant()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        for _ in range(n_rep):
-            dominant()
-        e1.record()
-        torch.cuda.synchronize()
-        k_ms = e0.elapsed_time(e1) / n_rep
-        flops = 2.0 * eng.N * eng.G * b10.R * b10.K      # algorithmic (unpadded K), SURVEY 8d: 2*N*G*K*R per half-step
-        peaks, src = _peaks()
-        peak = peaks["bf16_tflops"] / 2.0                # tf32 tensor rate = half the bf16 rate
-        ach = flops / (k_ms * 1e-3) / 1e12
-        roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                "traffic": None, "kernel": "tc_half_step_kernel<12,HALS> (H half-step, K=10, R=100)",
-                "kernel_ms": k_ms, "peak_source": f"{src} bf16 burst / 2 (tf32)"}
 
     # ---------------- end-to-end arm: public API with host buffers -----------------------------
     def e2e_step():
