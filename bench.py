@@ -104,12 +104,22 @@ class ClockSampler(threading.Thread):
                 "source": "nvml" if self.nvml is not None else "nvidia-smi"}
 
 
+def _use_all_host_threads(torch):
+    """torchrun exports OMP_NUM_THREADS=1; the CPU arm is meant to use every host thread it can."""
+    try:
+        n = len(os.sched_getaffinity(0))
+    except Exception:
+        n = os.cpu_count() or 1
+    torch.set_num_threads(max(1, n))
+    return torch.get_num_threads()
+
+
 def _cpu_baseline(x, seconds_target=15.0):
     """The oracle port of run_nmf (torch CPU, all host threads) on a bounded sample of the same
     workload: K=10, HALS, a few replicates x 10 iterations, repeated until ~seconds_target."""
     import torch
     from oracle import nmf_oracle as no
-    cores = torch.get_num_threads()
+    cores = _use_all_host_threads(torch)
     k = 10
     done, t0, reps = 0, time.perf_counter(), 0
     while True:
@@ -189,7 +199,7 @@ def run_reference(args):
     from cnmf_torch_b200.synth import nb_counts
     from oracle import nmf_oracle as no
     x = nb_counts(N_CELLS, N_GENES, seed=14)
-    cores = torch.get_num_threads()
+    cores = _use_all_host_threads(torch)
     # one step = every K, a bounded sample of 1 replicate per K x 10 iterations
     def step(seed0):
         n = 0
