@@ -72,6 +72,7 @@ class DenseFrobeniusEngine:
         if hasattr(X, "toarray"):
             X = X.toarray()
         xh = torch.as_tensor(np.ascontiguousarray(X)) if not torch.is_tensor(X) else X
+        self._x_host = xh   # kept only for host-side inits that need the matrix (NNDSVD)
         self.N, self.G = int(xh.shape[0]), int(xh.shape[1])
         self.ldx, self.ldxt = pad_ld(self.G), pad_ld(self.N)
         xd = xh.to(self.device, dtype=torch.float32, non_blocking=True)
@@ -100,6 +101,9 @@ class DenseFrobeniusEngine:
             tot = _d.allreduce_scalars([self.normX2, x_sum, float(self.N)], self.device, row_group)
             self.normX2, x_sum, self.N_total = float(tot[0]), float(tot[1]), int(round(tot[2]))
         self.x_mean = x_sum / (float(self.N_total) * self.G)
+
+    def host_matrix(self) -> np.ndarray:
+        return np.asarray(self._x_host.cpu().numpy() if torch.is_tensor(self._x_host) else self._x_host, dtype=np.float64)
 
     # ------------------------------------------------------------------------------------
     def make_init(self, K: int, seeds):

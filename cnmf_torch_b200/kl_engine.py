@@ -24,6 +24,7 @@ class SparseKLEngine:
         if torch.is_tensor(X):
             X = X.cpu().numpy()
         csr = sp.csr_matrix(X, dtype=np.float32)
+        self._csr_host = csr
         csr.eliminate_zeros()
         csr.sort_indices()
         csc = csr.T.tocsr()
@@ -45,6 +46,9 @@ class SparseKLEngine:
     @staticmethod
     def _stream():
         return torch.cuda.current_stream().cuda_stream
+
+    def host_matrix(self) -> np.ndarray:
+        return np.asarray(self._csr_host.toarray(), dtype=np.float64)
 
     def make_init(self, K, seeds):
         hs, ws = zip(*[init_random(self.x_mean, self.N, self.G, K, int(s)) for s in seeds])

@@ -25,6 +25,26 @@ def _reg(alpha_W, l1_ratio_W, alpha_H, l1_ratio_H):
                 l1_W=alpha_W * l1_ratio_W, l2_W=alpha_W * (1.0 - l1_ratio_W))
 
 
+def nndsvd_init(engine, k, seeds, init):
+    """NNDSVD family (reachable from the cnmf CLI, cnmf.py:1427): nmf-torch delegates to scikit-learn's
+    ``_initialize_nmf`` on the host (sklearn/decomposition/_nmf.py:214-366); so does this.  'nndsvd' and
+    'nndsvda' do not depend on the seed: the replicates of a batch then start identically."""
+    import torch
+    from sklearn.decomposition._nmf import _initialize_nmf
+    x = engine.host_matrix()
+    hs, ws = [], []
+    cache = {}
+    for s in seeds:
+        key = int(s) if init == "nndsvdar" else 0
+        if key not in cache:
+            Wsk, Hsk = _initialize_nmf(x, k, init=init, random_state=int(s))   # sklearn: X ~ W_sk H_sk
+            cache[key] = (torch.from_numpy(np.ascontiguousarray(Wsk, dtype=np.float32)),
+                          torch.from_numpy(np.ascontiguousarray(Hsk, dtype=np.float32)))
+        hs.append(cache[key][0])      # usages   (N x K)  = sklearn's W
+        ws.append(cache[key][1])      # spectra  (K x G)  = sklearn's H
+    return torch.stack(hs), torch.stack(ws)
+
+
 def make_engine(X, beta_loss="frobenius", device="cuda:0", impl="auto"):
     """Ingest X once (cf. the per-replicate densify + upload at cnmf.py:817-819)."""
     if beta_loss in ("frobenius", 2, 2.0):
@@ -42,8 +62,15 @@ def run_nmf_batch(engine, n_components, seeds, init="random", algo="mu", mode="b
                   online_max_pass=20, online_chunk_size=5000, online_chunk_max_iter=200, online_h_tol=0.05,
                   online_w_tol=0.05, return_H=False, H0=None, W0=None):
     """R = len(seeds) replicates of one K on a resident engine. Returns engine.BatchResult."""
+    if init not in ("random", "nndsvd", "nndsvda", "nndsvdar") and (H0 is None or W0 is None):
+        raise ValueError(f"init={init!r}: expected 'random' or 'nndsvd[a|ar]'")
     if init != "random" and (H0 is None or W0 is None):
-        raise NotImplementedError(f"init={init!r}: only 'random' (or explicit H0/W0) is implemented")
+        H0, W0 = nndsvd_init(engine, int(n_components), seeds, init)
+    if mode == "online" and not hasattr(engine, "factorize_online"):
+        # sufficient statistics (A = h^T h, B = h^T x) exist for the Frobenius loss only: nmf-torch itself
+        # switches beta != 2 to batch mode, and cNMF always passes mode='online' (cnmf.py:765)
+        print("Online mode only works for beta_loss='frobenius'. Switch to batch mode.")
+        mode = "batch"
     if algo not in ("mu", "hals"):
         raise NotImplementedError(f"algo={algo!r}: 'mu' and 'hals' are implemented")
     reg = _reg(alpha_W, l1_ratio_W, alpha_H, l1_ratio_H)

@@ -94,3 +94,26 @@ def test_run_nmf_dropin_kl_and_frobenius(problem):
         assert abs(err - eo) / eo < 1e-3
     with pytest.raises(Exception):
         run_nmf(problem, use_gpu=False, **{k: v for k, v in kw.items() if k != "use_gpu"})
+
+
+def test_cnmf_default_online_kwargs_with_kl_fall_back_to_batch(problem, capsys):
+    """cNMF always writes mode='online' (cnmf.py:765); with beta_loss='kullback-leibler' there are no
+    sufficient statistics, so -- like nmf-torch -- the run switches to batch mode instead of failing."""
+    from cnmf_torch_b200.nmf import run_nmf
+    kw = dict(alpha_W=0.0, alpha_H=0.0, l1_ratio_H=0.0, l1_ratio_W=0.0, beta_loss="kullback-leibler", algo="mu",
+              tol=1e-4, mode="online", online_chunk_max_iter=1000, online_chunk_size=5000, init="random", n_jobs=-1,
+              use_gpu=True, random_state=3, n_components=4)
+    H, W, err = run_nmf(problem, **kw)
+    assert "Switch to batch" in capsys.readouterr().out
+    ho, wo, eo = no.run_nmf_oracle(problem, **{k: v for k, v in kw.items() if k != "use_gpu"})
+    assert abs(err - eo) / eo < 1e-3 and _pearson(W, wo) >= 0.999
+
+
+@pytest.mark.parametrize("beta", ["frobenius", "kullback-leibler"])
+def test_nndsvd_init_through_run_nmf(problem, beta):
+    from cnmf_torch_b200.nmf import run_nmf
+    kw = dict(beta_loss=beta, algo="mu", tol=1e-4, mode="batch", init="nndsvd", random_state=5, n_components=5,
+              batch_max_iter=60)
+    H, W, err = run_nmf(problem, use_gpu=True, **kw)
+    ho, wo, eo = no.run_nmf_oracle(problem, **kw)
+    assert abs(err - eo) / eo < 1e-3 and _pearson(W, wo) >= 0.999
