@@ -90,7 +90,7 @@ __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
         sa[u] = 0.f; sb[u] = 0.f;
 #pragma unroll
         for (int k = 0; k < KP; k += 2) { sa[u] = fmaf(h[k], w[u][k], sa[u]); sb[u] = fmaf(h[k + 1], w[u][k + 1], sb[u]); }
-        q[u] = x[u] > 0.f ? __fdiv_rn(x[u], fmaxf(sa[u] + sb[u], eps)) : 0.f;
+        q[u] = __fdividef(x[u], fmaxf(sa[u] + sb[u], eps));  // stored entries are > 0 (checked at ingest); 2-ulp divide
       }
 #pragma unroll
       for (int u = 0; u < U; ++u)
@@ -105,7 +105,7 @@ __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
       float s0 = 0.f, s1 = 0.f;
 #pragma unroll
       for (int k = 0; k < KP; k += 2) { s0 = fmaf(h[k], w0[k], s0); s1 = fmaf(h[k + 1], w0[k + 1], s1); }
-      const float q0 = x0 > 0.f ? __fdiv_rn(x0, fmaxf(s0 + s1, eps)) : 0.f;
+      const float q0 = __fdividef(x0, fmaxf(s0 + s1, eps));
 #pragma unroll
       for (int k = 0; k < KP; ++k) num[k] = fmaf(q0, w0[k], num[k]);
     }

@@ -115,12 +115,21 @@ class DenseFrobeniusEngine:
         pin = torch.cuda.is_available()
         H0 = torch.empty((R, self.N, K), dtype=torch.float32, pin_memory=pin)
         W0 = torch.empty((R, K, self.G), dtype=torch.float32, pin_memory=pin)
+        avg = math.sqrt(float(self.x_mean) / K)
         for i in range(R):
-            # row-sharded: draw the GLOBAL H0 and keep this rank's rows, so a sharded run starts from
-            # exactly the state a single-GPU run would
-            h, w = init_random(self.x_mean, self.N_total, self.G, K, seeds[i])
-            H0[i].copy_(h[self.row_offset:self.row_offset + self.N])
-            W0[i].copy_(w)
+            if self.N_total != self.N:
+                # row-sharded: draw the GLOBAL H0 and keep this rank's rows, so a sharded run starts from
+                # exactly the state a single-GPU run would
+                h, w = init_random(self.x_mean, self.N_total, self.G, K, seeds[i])
+                H0[i].copy_(h[self.row_offset:self.row_offset + self.N])
+                W0[i].copy_(w)
+            else:
+                # the same draws as init_random (H then W from one generator), written straight into the
+                # pinned staging buffers
+                gen = torch.Generator(device="cpu")
+                gen.manual_seed(seeds[i])
+                torch.randn((self.N, K), generator=gen, dtype=torch.float32, out=H0[i]).mul_(avg).abs_()
+                torch.randn((K, self.G), generator=gen, dtype=torch.float32, out=W0[i]).mul_(avg).abs_()
         return H0, W0
 
     def _upload_state(self, H0, W0, K, Kp):

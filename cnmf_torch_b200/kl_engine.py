@@ -27,6 +27,8 @@ class SparseKLEngine:
         self._csr_host = csr
         csr.eliminate_zeros()
         csr.sort_indices()
+        if csr.nnz and float(csr.data.min()) < 0.0:
+            raise ValueError("X must be non-negative")   # the kernels rely on stored entries being > 0
         csc = csr.T.tocsr()
         csc.sort_indices()
         self.N, self.G = csr.shape
