@@ -460,85 +460,132 @@ __global__ void __launch_bounds__(128) l2_normalize_kernel(const float* __restri
 constexpr int KPP_NC = 64;   // max candidates (n_init * n_trials) handled per pass
 constexpr int KPP_GC = 64;   // genes per chunk
 
-// one lane walks the fp32 running sum once and records, for each trial value, the first index whose
-// cumulative sum reaches it (np.searchsorted(np.cumsum(closest), rand * pot), side='left', clipped)
+// One warp per restart walks the fp32 running sum (np.cumsum is a sequential fp32 sum, so the additions
+// cannot be re-associated) and records, for each trial value, the first index whose cumulative sum reaches
+// it: np.searchsorted(np.cumsum(closest), rand * pot), side='left', clipped.  The 32 lanes load 32
+// consecutive values at once (coalesced) and every lane replays the same sequential adds from shuffles, so
+// the dependent chain is the 4-cycle FADD, not a global-memory round trip per element.
 __global__ void __launch_bounds__(32) kpp_pick_kernel(const float* __restrict__ closest, const float* __restrict__ pot,
                                                       const double* __restrict__ rnd, int M, int T, int step,
                                                       int ksteps, int* __restrict__ cand) {
-  const int init = blockIdx.x;
-  if (threadIdx.x != 0) return;
-  double val[8];
-  int found[8];
+  const int init = blockIdx.x, lane = threadIdx.x;
+  constexpr int TMAX = 8;
+  // (double)acc >= val  <=>  acc >= (smallest float that is >= val): the thresholds are rounded UP to float
+  // once, so the sequential loop compares floats and stays off the fp64 pipe
+  float val[TMAX];
+  int found[TMAX];
   const double p = (double)pot[init];
-  for (int t = 0; t < T; ++t) {
-    val[t] = rnd[((int64_t)init * ksteps + step) * T + t] * p;
+  const float kNever = __int_as_float(0x7f800000);  // +inf: unused / already found
+#pragma unroll
+  for (int t = 0; t < TMAX; ++t) {
+    val[t] = t < T ? __double2float_ru(rnd[((int64_t)init * ksteps + step) * T + t] * p) : kNever;
     found[t] = M - 1;
   }
   const float* c = closest + (int64_t)init * M;
   float acc = 0.f;
-  unsigned pending = (1u << T) - 1u;
-  for (int j = 0; j < M && pending; ++j) {
-    acc = __fadd_rn(acc, c[j]);
-    for (int t = 0; t < T; ++t)
-      if ((pending >> t & 1u) && (double)acc >= val[t]) { found[t] = j; pending &= ~(1u << t); }
+  float vmin = kNever;  // smallest threshold still pending: one compare per element on the common path
+#pragma unroll
+  for (int t = 0; t < TMAX; ++t) vmin = fminf(vmin, val[t]);
+  int n_pending = T;
+  for (int j0 = 0; j0 < M && n_pending > 0; j0 += 32) {
+    const float mine = (j0 + lane < M) ? c[j0 + lane] : 0.f;
+    const int n = min(32, M - j0);
+    for (int i = 0; i < n; ++i) {
+      acc = __fadd_rn(acc, __shfl_sync(0xffffffffu, mine, i));
+      if (acc >= vmin) {
+        vmin = kNever;
+#pragma unroll
+        for (int t = 0; t < TMAX; ++t) {
+          if (acc >= val[t]) { found[t] = j0 + i; val[t] = kNever; --n_pending; }
+          vmin = fminf(vmin, val[t]);
+        }
+      }
+    }
   }
-  for (int t = 0; t < T; ++t) cand[init * T + t] = found[t];
+  if (lane == 0) {
+#pragma unroll
+    for (int t = 0; t < TMAX; ++t)
+      if (t < T) cand[init * T + t] = found[t];
+  }
 }
 
-// distances from NC candidate rows to every point; dmin = min(closest, d); per-CTA potential partials
+// distances from NC (<= 64) candidate rows to every point, as a tiled fp64 GEMM (64 points x 64 candidates
+// per CTA, 4x4 per thread): dmin = min(closest, d); per-CTA potential partials [gridDim.x x NC]
 __global__ void __launch_bounds__(256) kpp_dist_kernel(const float* __restrict__ X, int64_t ld, int M, int G,
                                                        const double* __restrict__ xx, const int* __restrict__ cand,
                                                        int NC, int T, const float* __restrict__ closest,
                                                        float* __restrict__ dmin, double* __restrict__ potpart) {
-  __shared__ float cs[KPP_NC][KPP_GC + 1];
+  __shared__ __align__(16) double As[DK][DT + 2];   // points
+  __shared__ __align__(16) double Bs[DK][DT + 2];   // candidates
   __shared__ int scand[KPP_NC];
-  __shared__ float sd[8][KPP_NC];
-  const int w = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int m = blockIdx.x * 8 + w;
-  if (threadIdx.x < NC) scand[threadIdx.x] = cand[threadIdx.x];
+  __shared__ float spot[KPP_NC][17];
+  const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4;
+  const int i0 = blockIdx.x * DT;
+  if (tid < KPP_NC) scand[tid] = tid < NC ? cand[tid] : -1;
   __syncthreads();
-  double acc[KPP_NC];
+  double acc[4][4];
 #pragma unroll
-  for (int c = 0; c < KPP_NC; ++c) acc[c] = 0.0;
-  for (int g0 = 0; g0 < G; g0 += KPP_GC) {
-    for (int i = threadIdx.x; i < NC * KPP_GC; i += 256) {
-      const int c = i / KPP_GC, g = i - c * KPP_GC;
-      cs[c][g] = (g0 + g < G) ? X[(int64_t)scand[c] * ld + g0 + g] : 0.f;
-    }
-    __syncthreads();
-    if (m < M) {
-      const double x0 = (g0 + lane < G) ? (double)X[(int64_t)m * ld + g0 + lane] : 0.0;
-      const double x1 = (g0 + lane + 32 < G) ? (double)X[(int64_t)m * ld + g0 + lane + 32] : 0.0;
+  for (int a = 0; a < 4; ++a)
 #pragma unroll
-      for (int c = 0; c < KPP_NC; ++c)
-        if (c < NC) acc[c] = fma(x1, (double)cs[c][lane + 32], fma(x0, (double)cs[c][lane], acc[c]));
-    }
-    __syncthreads();
-  }
+    for (int b = 0; b < 4; ++b) acc[a][b] = 0.0;
+  const int lrow = tid >> 2, lk = (tid & 3) * 4;
+  const int crow = scand[lrow];
+  for (int k0 = 0; k0 < G; k0 += DK) {
+    float va[4] = {0.f, 0.f, 0.f, 0.f}, vb[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-  for (int c = 0; c < KPP_NC; ++c) {
-    if (c < NC) {
-      const double dot = warp_sum(acc[c]);
-      if (lane == 0) {
-        float f = 0.f;
-        if (m < M) {
-          double d = -2.0 * dot;
-          d += xx[scand[c]];
-          d += xx[m];
-          f = fmaxf((float)d, 0.f);
-          const int init = c / T;
-          if (closest != nullptr) f = fminf(closest[(int64_t)init * M + m], f);
-          dmin[(int64_t)c * M + m] = f;
-        }
-        sd[w][c] = f;
+    for (int q = 0; q < 4; ++q) {
+      const int k = k0 + lk + q;
+      if (k < G) {
+        if (i0 + lrow < M) va[q] = X[(int64_t)(i0 + lrow) * ld + k];
+        if (crow >= 0) vb[q] = X[(int64_t)crow * ld + k];
       }
     }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      As[lk + q][lrow] = (double)va[q];
+      Bs[lk + q][lrow] = (double)vb[q];
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < DK; ++kk) {
+      double a[4], b[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) { a[q] = As[kk][ty * 4 + q]; b[q] = Bs[kk][tx * 4 + q]; }
+#pragma unroll
+      for (int p = 0; p < 4; ++p)
+#pragma unroll
+        for (int q = 0; q < 4; ++q) acc[p][q] = fma(a[p], b[q], acc[p][q]);
+    }
+    __syncthreads();
+  }
+  // thread (ty, tx): points i0 + ty*4 + p, candidates tx*4 + q
+#pragma unroll
+  for (int q = 0; q < 4; ++q) {
+    const int c = tx * 4 + q;
+    float psum = 0.f;
+    if (c < NC) {
+      const int init = c / T;
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const int m = i0 + ty * 4 + p;
+        if (m < M) {
+          double d = -2.0 * acc[p][q];
+          d += xx[scand[c]];
+          d += xx[m];
+          float f = fmaxf((float)d, 0.f);
+          if (closest != nullptr) f = fminf(closest[(int64_t)init * M + m], f);
+          dmin[(int64_t)c * M + m] = f;
+          psum += f;   // 4 values per thread; the cross-thread sum below is fp64
+        }
+      }
+      spot[c][ty] = psum;
+    }
   }
   __syncthreads();
-  if (threadIdx.x < NC) {
+  if (tid < NC) {
     double t = 0.0;
-    for (int q = 0; q < 8; ++q) t += (double)sd[q][threadIdx.x];
-    potpart[(int64_t)blockIdx.x * NC + threadIdx.x] = t;
+    for (int y = 0; y < 16; ++y) t += (double)spot[tid][y];
+    potpart[(int64_t)blockIdx.x * NC + tid] = t;
   }
 }
 
@@ -709,7 +756,7 @@ int cnmf_b200_l2_normalize(const float* S, int64_t lds, int32_t M, int32_t G, fl
 
 static int64_t kpp_layout(int32_t M, int32_t n_init, int32_t T, int64_t* o_xx, int64_t* o_closest, int64_t* o_dmin,
                           int64_t* o_cand, int64_t* o_pot, int64_t* o_part) {
-  const int64_t nblk = ceil_div(M, 8), NC = (int64_t)n_init * T;
+  const int64_t nblk = ceil_div(M, DT), NC = (int64_t)n_init * T;
   int64_t off = 0;
   *o_xx = off; off += align_up((int64_t)M * 8, 256);
   *o_closest = off; off += align_up((int64_t)n_init * M * 4, 256);
@@ -742,7 +789,7 @@ int cnmf_b200_kmeanspp(const float* Xc, int64_t ld, int32_t M, int32_t G, int32_
   int* cand = reinterpret_cast<int*>(ws + o_cand);
   float* pot = reinterpret_cast<float*>(ws + o_pot);
   double* part = reinterpret_cast<double*>(ws + o_part);
-  const int nblk = (int)ceil_div(M, 8);
+  const int nblk = (int)ceil_div(M, DT);
   row_sqnorm64_kernel<<<(unsigned)ceil_div(M, 8), 256, 0, st>>>(Xc, ld, M, G, xx);
   CNMF_LAUNCH_CHECK();
   // first centre: the host-drawn index; "one candidate per restart", nothing to take the minimum with
