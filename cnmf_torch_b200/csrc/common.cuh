@@ -48,6 +48,16 @@ void reset_launch_count();
     if (_rc != 0) return _rc;   \
   } while (0)
 
+// cudaFuncSetAttribute is per device: remember, per kernel, on which devices the opt-in shared-memory size
+// has been set (bit d of the mask = device ordinal d; ordinals >= 64 are simply set every time).
+static inline bool needs_func_attr(unsigned long long* mask) {
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return true;
+  if (*mask >> dev & 1ull) return false;
+  *mask |= 1ull << dev;
+  return true;
+}
+
 static inline int64_t ceil_div(int64_t a, int64_t b) { return (a + b - 1) / b; }
 static inline int64_t align_up(int64_t a, int64_t b) { return ceil_div(a, b) * b; }
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15u) == 0; }

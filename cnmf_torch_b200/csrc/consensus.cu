@@ -660,11 +660,9 @@ int cnmf_b200_topk_density(const float* D, int64_t ldd, int32_t M, int32_t n_nei
     set_error("topk_density: %d rows exceed the shared-memory row buffer (51200)", M);
     return CNMF_B200_ERR_UNSUPPORTED;
   }
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  static unsigned long long configured = 0;
+  if (smem > 48 * 1024 && needs_func_attr(&configured))
     CNMF_CUDA(cudaFuncSetAttribute(topk_density_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    configured = 200 * 1024;
-  }
   topk_density_kernel<<<M, 256, smem, (cudaStream_t)stream>>>(D, ldd, M, n_neighbors + 1, n_neighbors, density, nbr);
   CNMF_LAUNCH_CHECK();
   return 0;
@@ -732,11 +730,9 @@ int cnmf_b200_cluster_median(const float* X, int64_t ld, int32_t G, const int32_
     set_error("cluster_median: cluster of %d members exceeds the shared-memory tile (3000)", max_members);
     return CNMF_B200_ERR_UNSUPPORTED;
   }
-  static thread_local size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
+  static unsigned long long configured = 0;
+  if (smem > 48 * 1024 && needs_func_attr(&configured))
     CNMF_CUDA(cudaFuncSetAttribute(cluster_median_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-    configured = 200 * 1024;
-  }
   cudaStream_t st = (cudaStream_t)stream;
   cluster_median_kernel<<<dim3((unsigned)ceil_div(G, MD_G), k), 256, smem, st>>>(X, ld, G, order, offsets, median);
   CNMF_LAUNCH_CHECK();

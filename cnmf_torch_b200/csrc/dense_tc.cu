@@ -650,12 +650,10 @@ static int get_tensor_map(const float* ptr, int64_t rows, int64_t cols, int64_t 
 template <int KP, int ALGO, int CG, bool SUMS>
 static int launch_tc_inst3(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
                            int grid, cudaStream_t st) {
-  static thread_local bool configured = false;
+  static unsigned long long configured = 0;  // per-device bit mask (benign race: setting twice is harmless)
   auto kern = tc_half_step_kernel<KP, ALGO, CG, SUMS>;
-  if (!configured) {
+  if (needs_func_attr(&configured))
     CNMF_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_LIMIT));
-    configured = true;
-  }
   cudaLaunchConfig_t cfg{};
   cfg.gridDim = dim3(grid);
   cfg.blockDim = dim3(tc_threads(KP));
