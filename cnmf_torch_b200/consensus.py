@@ -56,23 +56,6 @@ def _is_same_clustering(a: np.ndarray, b: np.ndarray, k: int) -> bool:
     return True
 
 
-def kmeans_plusplus_host(Xc_host: np.ndarray, k: int, n_init: int, random_state: int):
-    """Optional strict mode (``seeding="sklearn"``): the seeding of all restarts through sklearn's own
-    routine on the host, from ONE RandomState in restart order.  The device seeding makes the same
-    draws; the two can differ only where sklearn's fp32 BLAS sums and the device's fp64 sums round a
-    potential differently at a searchsorted / argmin boundary."""
-    from sklearn.cluster._kmeans import _kmeans_plusplus
-    from sklearn.utils.extmath import row_norms
-    rs = np.random.RandomState(random_state)
-    xsq = row_norms(Xc_host, squared=True)
-    w = np.ones(Xc_host.shape[0], dtype=Xc_host.dtype)
-    out = []
-    for _ in range(n_init):
-        centers, _ = _kmeans_plusplus(Xc_host, k, x_squared_norms=xsq, sample_weight=w, random_state=rs)
-        out.append(centers)
-    return np.stack(out)
-
-
 def kmeans_plusplus_device(Xc: torch.Tensor, k: int, n_init: int, random_state: int):
     """k-means++ seeding of all restarts on the device.  Only the random numbers are drawn on the host,
     from the same RandomState stream and in the same order as sklearn (first centre: choice(M, p);
@@ -184,9 +167,10 @@ def _relocate_empty_clusters(Xc, labels, centers_old, centers_new, counts, shift
 
 
 def kmeans_fit(X: torch.Tensor, k: int, n_init: int = 10, random_state: int = 1, max_iter: int = 300,
-               tol: float = 1e-4, centers_init: np.ndarray | None = None, seeding: str = "device"):
+               tol: float = 1e-4, centers_init: np.ndarray | None = None):
     """``KMeans(n_clusters=k, n_init=10, random_state=1).fit(X)`` (cnmf.py:1082-1083).
-    Returns dict(labels (0-based, int32 host), inertia, n_iter, centers (host, original space))."""
+    ``centers_init`` ([n_init, k, G], in the CENTRED space) replaces the k-means++ seeding (tests use it to
+    feed sklearn's own seeds).  Returns dict(labels (0-based, int32 host), inertia, n_iter, centers (host, original space))."""
     L = lib()
     dev = X.device
     M, G = int(X.shape[0]), int(X.shape[1])
@@ -202,12 +186,8 @@ def kmeans_fit(X: torch.Tensor, k: int, n_init: int = 10, random_state: int = 1,
     if centers_init is not None:
         centers0 = torch.from_numpy(np.asarray(centers_init, dtype=np.float32)).to(dev)
         n_init = int(centers0.shape[0])
-    elif seeding == "device":
-        centers0, _ = kmeans_plusplus_device(Xc, k, n_init, random_state)
-    elif seeding == "sklearn":
-        centers0 = torch.from_numpy(kmeans_plusplus_host(Xc.cpu().numpy(), k, n_init, random_state)).to(dev)
     else:
-        raise ValueError(f"seeding={seeding!r}")
+        centers0, _ = kmeans_plusplus_device(Xc, k, n_init, random_state)
     labels, inertia, centers, n_iter = kmeans_lloyd_batched(Xc, centers0, tol_, max_iter)
     best = None
     for i in range(n_init):   # best-of-n with the same-clustering guard (_kmeans.py:1531-1541)
@@ -237,9 +217,10 @@ def cluster_medians(X: torch.Tensor, labels0: np.ndarray, k: int):
 
 def consensus_front_half(merged_spectra: np.ndarray, k: int, density_threshold: float, n_neighbors: int,
                          device="cuda:0", skip_density: bool = False, local_density=None,
-                         return_neighbors: bool = False, seeding: str = "device"):
+                         return_neighbors: bool = False, centers_init_fn=None):
     """cnmf.py:1056-1090.  Returns dict(local_density, keep, labels (1-based), median_spectra,
-    l2_spectra, inertia, neighbors)."""
+    l2_spectra, inertia, neighbors).  ``centers_init_fn(kept_l2_spectra) -> [n_init, k, G]`` (centred space) is a
+    test hook that replaces the device seeding."""
     lib()
     if not torch.cuda.is_available():
         raise _lib.Cnmfb200Error("CUDA device required: cnmf_torch_b200 has no CPU path")
@@ -260,7 +241,7 @@ def consensus_front_half(merged_spectra: np.ndarray, k: int, density_threshold: 
             raise RuntimeError("Zero components remain after density filtering. "
                                "Consider increasing density threshold")
     kept = l2[torch.from_numpy(keep).to(dev)].contiguous()
-    km = kmeans_fit(kept, k, seeding=seeding)
+    km = kmeans_fit(kept, k, centers_init=None if centers_init_fn is None else centers_init_fn(kept))
     _, nrm = cluster_medians(kept, km["labels"], k)
     return dict(local_density=dens_h, keep=keep, labels=km["labels"] + 1, median_spectra=nrm.cpu().numpy(),
                 l2_spectra=l2.cpu().numpy(), inertia=km["inertia"], neighbors=nbr_h, n_iter=km["n_iter"])

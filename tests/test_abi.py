@@ -73,3 +73,27 @@ int main(void){printf("%zu %zu %zu %zu %zu\n", sizeof(cnmf_b200_frob_problem),
     P = _lib.FrobProblem
     assert [int(v) for v in out] == [C.sizeof(P), P.Wall.offset, P.active.offset, P.normX2.offset,
                                      P.workspace_bytes.offset]
+
+
+def test_missing_library_fails_loudly(monkeypatch, tmp_path):
+    """No fallback: without the built CUDA library the product refuses to run."""
+    from cnmf_torch_b200 import _lib
+    monkeypatch.setattr(_lib, "_LIB", None)
+    monkeypatch.setattr(_lib, "LIB_PATH", str(tmp_path / "absent.so"))
+    with pytest.raises(_lib.Cnmfb200Error, match="no CPU or PyTorch fallback"):
+        _lib.lib()
+
+
+def test_engines_refuse_to_run_without_cuda():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("needs a machine without a GPU")
+    import numpy as np
+    from cnmf_torch_b200 import _lib
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    from cnmf_torch_b200.consensus import consensus_front_half
+    x = np.ones((8, 6), dtype=np.float32)
+    for fn in (lambda: DenseFrobeniusEngine(x), lambda: SparseKLEngine(x), lambda: consensus_front_half(x, 2, 0.5, 1)):
+        with pytest.raises(_lib.Cnmfb200Error, match="CUDA device required"):
+            fn()

@@ -15,6 +15,21 @@ from oracle import consensus_oracle as co
 pytestmark = pytest.mark.gpu
 
 
+def _sklearn_seeds(k, n_init=10, random_state=1):
+    """centers_init_fn for the strict variant of a test: sklearn's own k-means++ seeds (host), all restarts
+    from one RandomState in restart order, computed on the centred data exactly as KMeans.fit does."""
+    def fn(kept):
+        from sklearn.cluster._kmeans import _kmeans_plusplus
+        from sklearn.utils.extmath import row_norms
+        x = kept.cpu().numpy()
+        xc = x - x.mean(axis=0)
+        rs = np.random.RandomState(random_state)
+        w = np.ones(xc.shape[0], dtype=xc.dtype)
+        xsq = row_norms(xc, squared=True)
+        return np.stack([_kmeans_plusplus(xc, k, xsq, w, rs)[0] for _ in range(n_init)])
+    return fn
+
+
 def _load(golden_dir, name):
     return np.load(os.path.join(golden_dir, name), allow_pickle=True)
 
@@ -69,7 +84,7 @@ def test_kmeans_labels_match_sklearn(k, n_rep, g, seeding):
     l2d = cs.l2_normalize_rows(_spectra(k, n_rep, g, 11))
     l2 = l2d.cpu().numpy()
     ref = KMeans(n_clusters=k, n_init=10, random_state=1).fit(l2.copy())
-    out = cs.kmeans_fit(l2d, k, seeding=seeding)
+    out = cs.kmeans_fit(l2d, k, centers_init=None if seeding == "device" else _sklearn_seeds(k)(l2d))
     np.testing.assert_array_equal(out["labels"], ref.labels_)
     assert abs(out["inertia"] - ref.inertia_) / ref.inertia_ < 1e-5
     np.testing.assert_allclose(out["centers"], ref.cluster_centers_, rtol=1e-4, atol=1e-6)
@@ -125,7 +140,8 @@ def test_consensus_front_half_matches_reference_golden(golden_dir, tag, seeding)
     g = _load(golden_dir, f"consensus_{tag}.npz")
     k = int(g["k"])
     n = co.n_neighbors_for(float(g["local_neighborhood_size"]), g["spectra"].shape[0], k)
-    out = cs.consensus_front_half(g["spectra"], k, float(g["density_threshold"]), n, seeding=seeding)
+    out = cs.consensus_front_half(g["spectra"], k, float(g["density_threshold"]), n,
+                                  centers_init_fn=None if seeding == "device" else _sklearn_seeds(k))
     np.testing.assert_allclose(out["local_density"], g["local_density"], rtol=2e-6)
     np.testing.assert_array_equal(out["keep"], g["local_density"] < float(g["density_threshold"]))
     np.testing.assert_array_equal(out["labels"], g["labels"])
