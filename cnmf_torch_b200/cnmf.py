@@ -321,8 +321,10 @@ def main():
     parser.add_argument("command", type=str, choices=["factorize", "combine", "consensus"])
     parser.add_argument("--name", type=str, nargs="?", default="cNMF")
     parser.add_argument("--output-dir", type=str, nargs="?", default=".")
-    parser.add_argument("--total-workers", type=int, default=-1)
-    parser.add_argument("--worker-index", type=int, default=0)
+    parser.add_argument("--total-workers", type=int, default=None,
+                        help="workers the replicate jobs are strided over (default: WORLD_SIZE under torchrun, else 1)")
+    parser.add_argument("--worker-index", type=int, default=None,
+                        help="this worker's index (default: RANK under torchrun, else 0)")
     parser.add_argument("--skip-completed-runs", action="store_true", default=False)
     parser.add_argument("-k", "--components", type=int, nargs="+")
     parser.add_argument("--local-density-threshold", type=float, default=0.5)
@@ -332,9 +334,11 @@ def main():
     device = args.device or "cuda:%d" % int(os.environ.get("LOCAL_RANK", "0"))
     obj = cNMF(output_dir=args.output_dir, name=args.name, device=device)
     if args.command == "factorize":
-        total = max(1, args.total_workers)
-        obj.factorize(worker_i=args.worker_index, total_workers=total,
-                      skip_completed_runs=args.skip_completed_runs)
+        # one process per GPU:  torchrun --nproc-per-node 8 -m cnmf_torch_b200.cnmf factorize --name ...
+        # strides the replicate ledger over the ranks exactly like worker_filter (cnmf.py:53-54, 876-880)
+        total = args.total_workers if args.total_workers and args.total_workers > 0 else int(os.environ.get("WORLD_SIZE", "1"))
+        index = args.worker_index if args.worker_index is not None else int(os.environ.get("RANK", "0"))
+        obj.factorize(worker_i=index, total_workers=max(1, total), skip_completed_runs=args.skip_completed_runs)
     elif args.command == "combine":
         obj.combine(components=args.components)
     elif args.command == "consensus":
