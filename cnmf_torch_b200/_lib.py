@@ -91,6 +91,8 @@ SIGNATURES = {
     "cnmf_b200_kmeans_inertia_blocks": (i64, [i32]),
     "cnmf_b200_kmeans_inertia": (i32, [vp, i64, i32, i32, vp, i32, i32, vp, vp, vp]),
     "cnmf_b200_cluster_median": (i32, [vp, i64, i32, vp, vp, i32, i32, vp, vp, vp]),
+    "cnmf_b200_silhouette": (i32, [vp, i64, i32, vp, vp, i32, vp, vp]),
+    "cnmf_b200_ols_xty": (i32, [vp, vp, vp, i32, vp, i32, vp, vp, vp, vp]),
     "cnmf_b200_frob_workspace_bytes": (i64, [C.POINTER(FrobProblem)]),
     "cnmf_b200_frob_prepare": (i32, [C.POINTER(FrobProblem), vp]),
     "cnmf_b200_frob_iterate": (i32, [C.POINTER(FrobProblem), i32, vp]),

@@ -300,6 +300,18 @@ class cNMF:
             cached = load_df_from_npz(cache).values[:, 0]
         out = consensus_front_half(merged.values, k, density_threshold, n_neighbors, device=self.device,
                                    skip_density=skip_density_and_return_after_stats, local_density=cached)
+        if skip_density_and_return_after_stats:
+            # k-selection statistics (cnmf.py:1093-1110): refit usages against the consensus spectra, silhouette of
+            # the clustering, prediction error of the rank-k reconstruction
+            from .stats import prediction_error, silhouette_score
+            X = norm_counts if norm_counts is not None else self.load_norm_counts()[0]
+            median = pd.DataFrame(out["median_spectra"], index=np.arange(1, k + 1), columns=merged.columns)
+            rf_usages = self.refit_usage(X, median.values, seed=1)
+            sil = silhouette_score(out["l2_spectra"], out["labels"] - 1, k, device=self.device)
+            err = prediction_error(X, rf_usages, median.values, device=self.device)
+            return pd.DataFrame([k, density_threshold, sil, err],
+                                index=["k", "local_density_threshold", "silhouette", "prediction_error"],
+                                columns=["stats"])
         local_density = pd.DataFrame(out["local_density"], columns=["local_density"], index=merged.index) \
             if out["local_density"] is not None else None
         if local_density is not None and cached is None:
@@ -311,6 +323,23 @@ class cNMF:
         save_df_to_npz(median, self.paths["consensus_spectra"] % (k, dt_repl))
         save_df_to_text(median, self.paths["consensus_spectra__txt"] % (k, dt_repl))
         return median, labels, local_density
+
+
+def _k_selection_stats(self):
+    """The table behind ``k_selection_plot`` (cnmf.py:1293-1309) -- one ``consensus(k,
+    skip_density_and_return_after_stats=True)`` per K, saved as ``k_selection_stats.df.npz``; the figure itself
+    is the reference's matplotlib code and stays there."""
+    run_params = load_df_from_npz(self.paths["nmf_replicate_parameters"])
+    X = self.load_norm_counts()[0]
+    stats = [self.consensus(int(k), skip_density_and_return_after_stats=True, norm_counts=X).stats
+             for k in sorted(set(run_params.n_components))]
+    stats = pd.DataFrame(stats)
+    stats.reset_index(drop=True, inplace=True)
+    save_df_to_npz(stats, os.path.join(self.output_dir, self.name, self.name + ".k_selection_stats.df.npz"))
+    return stats
+
+
+cNMF.k_selection_stats = _k_selection_stats
 
 
 def main():

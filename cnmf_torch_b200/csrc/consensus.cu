@@ -630,6 +630,74 @@ __global__ void kpp_gather_kernel(const float* __restrict__ X, int64_t ld, int G
   for (int g = threadIdx.x; g < G; g += blockDim.x) centers[(int64_t)c * G + g] = src[g];
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// f3 (k-selection statistics, cnmf.py:1096-1110): silhouette of the KMeans labels on the L2 spectra.
+// One CTA per sample: per-cluster sums of its row of the distance matrix, intra = sum_own / (n_own - 1),
+// inter = min over other clusters of sum_c / n_c, s = (inter - intra) / max(intra, inter)
+// (sklearn/metrics/cluster/_unsupervised.py:_silhouette_reduce, silhouette_samples).
+// ---------------------------------------------------------------------------------------------
+constexpr int SIL_THREADS = 128;
+
+__global__ void __launch_bounds__(SIL_THREADS) silhouette_kernel(const float* __restrict__ D, int64_t ldd, int M,
+                                                                 const int* __restrict__ labels,
+                                                                 const int* __restrict__ counts, int k,
+                                                                 float* __restrict__ sil) {
+  __shared__ float part[KA_C][SIL_THREADS];
+  __shared__ double csum[KA_C];
+  const int i = blockIdx.x, t = threadIdx.x;
+  for (int c = 0; c < k; ++c) part[c][t] = 0.f;
+  const float* drow = D + (int64_t)i * ldd;
+  for (int j = t; j < M; j += SIL_THREADS) part[labels[j]][t] += drow[j];   // each thread owns its column
+  __syncthreads();
+  if (t < k) {
+    double acc = 0.0;
+    for (int q = 0; q < SIL_THREADS; ++q) acc += (double)part[t][q];        // fixed order
+    csum[t] = acc;
+  }
+  __syncthreads();
+  if (t == 0) {
+    const int own = labels[i];
+    const int n_own = counts[own];
+    float out = 0.f;
+    if (n_own > 1) {
+      const float intra = (float)csum[own] / (float)(n_own - 1);
+      float inter = INFINITY;
+      for (int c = 0; c < k; ++c)
+        if (c != own && counts[c] > 0) inter = fminf(inter, (float)csum[c] / (float)counts[c]);
+      const float den = fmaxf(intra, inter);
+      out = (inter - intra) / den;
+      if (!(out == out) || isinf(out)) out = 0.f;   // nan_to_num
+    }
+    sil[i] = out;
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// f2 (cnmf.py:56-126, efficient_ols_all_cols): the accumulations X^T X and X^T Y in fp64.
+//   xty[k, j] = sum_i x[i, k] * y[i, j]  over the stored entries of column j of Y (CSC), plus
+//   ysum[j], ysq[j] (for the global mean / variance of Y's columns) and xsum[k].
+// One warp per target column; K <= 32 predictors, lane = predictor.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) ols_xty_kernel(const int64_t* __restrict__ col_ptr, const int* __restrict__ row_idx,
+                                                      const float* __restrict__ val, int n_targets,
+                                                      const float* __restrict__ Xp, int K,
+                                                      double* __restrict__ xty, double* __restrict__ ysum,
+                                                      double* __restrict__ ysq) {
+  const int j = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+  if (j >= n_targets) return;
+  double acc = 0.0, s1 = 0.0, s2 = 0.0;
+  for (int64_t p = col_ptr[j]; p < col_ptr[j + 1]; ++p) {
+    const double y = (double)val[p];
+    const int i = row_idx[p];
+    if (lane < K) acc = fma((double)Xp[(int64_t)i * K + lane], y, acc);
+    s1 += y;
+    s2 = fma(y, y, s2);
+  }
+  if (lane < K) xty[(int64_t)lane * n_targets + j] = acc;
+  if (lane == 0) { ysum[j] = s1; ysq[j] = s2; }
+}
+
 }  // namespace cnmf
 
 using namespace cnmf;
@@ -803,6 +871,25 @@ int cnmf_b200_kmeanspp(const float* Xc, int64_t ld, int32_t M, int32_t G, int32_
     CNMF_LAUNCH_CHECK();
   }
   kpp_gather_kernel<<<n_init * k, 128, 0, st>>>(Xc, ld, G, chosen, centers);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int cnmf_b200_silhouette(const float* D, int64_t ldd, int32_t M, const int32_t* labels, const int32_t* counts, int32_t k,
+                         float* sil, void* stream) {
+  CNMF_CHECK_ARG(D && labels && counts && sil, "silhouette: null pointer");
+  CNMF_CHECK_ARG(M > 0 && ldd >= M && k >= 1 && k <= KA_C, "silhouette: need 1 <= k <= %d", KA_C);
+  silhouette_kernel<<<M, SIL_THREADS, 0, (cudaStream_t)stream>>>(D, ldd, M, labels, counts, k, sil);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int cnmf_b200_ols_xty(const int64_t* col_ptr, const int32_t* row_idx, const float* val, int32_t n_targets, const float* X,
+                      int32_t K, double* xty, double* ysum, double* ysq, void* stream) {
+  CNMF_CHECK_ARG(col_ptr && row_idx && val && X && xty && ysum && ysq, "ols_xty: null pointer");
+  CNMF_CHECK_ARG(n_targets > 0 && K >= 1 && K <= 32, "ols_xty: need 1 <= K <= 32 predictors");
+  ols_xty_kernel<<<(unsigned)ceil_div(n_targets, 8), 256, 0, (cudaStream_t)stream>>>(col_ptr, row_idx, val, n_targets, X, K,
+                                                                                   xty, ysum, ysq);
   CNMF_LAUNCH_CHECK();
   return 0;
 }

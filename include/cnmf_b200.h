@@ -315,6 +315,23 @@ int cnmf_b200_cluster_median(const float* X, int64_t ld, int32_t G, const int32_
                              const int32_t* offsets, int32_t k, int32_t max_members, float* median,
                              float* normalized, void* stream);
 
+/* ------------------------------------------------------------------------------------------
+ * Rows after the hot path: k-selection statistics and the OLS accumulation.
+ * ---------------------------------------------------------------------------------------- */
+
+/* sil[i] = silhouette coefficient of sample i given the distance matrix D (cnmf_b200_pairwise_dist), labels in
+ * 0..k-1 and the cluster sizes: silhouette_score(l2_spectra, labels, metric='euclidean') at cnmf.py:1097 is
+ * their mean.  k <= 32. */
+int cnmf_b200_silhouette(const float* D, int64_t ldd, int32_t M, const int32_t* labels, const int32_t* counts,
+                         int32_t k, float* sil, void* stream);
+
+/* The fp64 accumulations of efficient_ols_all_cols (cnmf.py:56-126): xty[k, j] = sum_i X[i, k] Y[i, j] over
+ * the stored entries of the CSC target matrix Y (col_ptr int64 [n_targets+1], row_idx, val), with
+ * ysum[j] = sum_i Y[i, j] and ysq[j] = sum_i Y[i, j]^2 for the global column mean / variance.
+ * X: [n_samples x K] fp32 row-major, K <= 32. */
+int cnmf_b200_ols_xty(const int64_t* col_ptr, const int32_t* row_idx, const float* val, int32_t n_targets,
+                      const float* X, int32_t K, double* xty, double* ysum, double* ysq, void* stream);
+
 /* Number of kernel launches the last cnmf_b200_frob_iterate on this thread enqueued. */
 int64_t cnmf_b200_last_launch_count(void);
 

@@ -51,9 +51,30 @@ class _Stop(Exception):
     pass
 
 
+def make_ols(ref):
+    """efficient_ols_all_cols (cnmf.py:56-126) and get_mean_var on a sparse and a dense target matrix."""
+    import scipy.sparse as sps
+    rng = np.random.default_rng(5)
+    n, k, t = 700, 6, 45
+    X = rng.gamma(1.0, 1.0, size=(n, k)).astype(np.float32)
+    Yd = (rng.gamma(0.5, 2.0, size=(n, t)) * (rng.random((n, t)) < 0.3)).astype(np.float32)
+    Yd[:, 7] = 0.0                      # a constant column exercises the variance floor
+    out = dict(X=X, Y=Yd)
+    out["beta_dense_raw"] = ref.efficient_ols_all_cols(X, Yd, batch_size=128, normalize_y=False)
+    out["beta_dense_norm"] = ref.efficient_ols_all_cols(X, Yd, batch_size=128, normalize_y=True)
+    out["beta_sparse_norm"] = ref.efficient_ols_all_cols(X, sps.csr_matrix(Yd), batch_size=256, normalize_y=True)
+    m, v = ref.get_mean_var(sps.csr_matrix(Yd))
+    out["mean"], out["var"] = m, v
+    np.savez_compressed(os.path.join(HERE, "ols.npz"), **out)
+    print("ols golden:", {k_: getattr(v_, "shape", None) for k_, v_ in out.items()})
+
+
 def main():
     ref = load_reference()
+    if "--only-ols" in sys.argv:
+        return make_ols(ref)
     tmp = tempfile.mkdtemp()
+    make_ols(ref)
 
     # ---- ledger (cnmf.py:701-777) ------------------------------------------------------
     led = {}
