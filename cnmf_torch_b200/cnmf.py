@@ -213,6 +213,26 @@ class cNMF:
                     spectra = pd.DataFrame(res[k].W[j], index=np.arange(1, k + 1), columns=var_names)
                     save_df_to_npz(spectra, self.paths["iter_spectra"] % (k, int(p["iter"])))
             return
+        if (kw.get("mode", "batch") == "online" and hasattr(engine, "factorize_online_many") and not max_batch
+                and engine_kw.get("init", "random") == "random"):
+            # the reference's default mode: K values sharing a padded Kp run as one stack
+            from .nmf import _reg
+            groups = {int(k): g for k, g in sel.groupby("n_components", sort=True)}
+            print("[Worker %d]. Starting %d tasks (online mode): %s." % (worker_i, len(sel), ", ".join(
+                "k=%d x %d replicates" % (k, len(g)) for k, g in groups.items())))
+            reg = _reg(engine_kw.get("alpha_W", 0.0), engine_kw.get("l1_ratio_W", 0.0),
+                       engine_kw.get("alpha_H", 0.0), engine_kw.get("l1_ratio_H", 0.0))
+            res = engine.factorize_online_many(
+                list(groups), {k: [int(s) for s in g["nmf_seed"]] for k, g in groups.items()},
+                tol=engine_kw.get("tol", 1e-4), max_pass=int(engine_kw.get("online_max_pass", 20)),
+                chunk_size=int(engine_kw.get("online_chunk_size", 5000)),
+                chunk_max_iter=int(engine_kw.get("online_chunk_max_iter", 200)),
+                h_tol=engine_kw.get("online_h_tol", 0.05), w_tol=engine_kw.get("online_w_tol", 0.05), **reg)
+            for k, g in groups.items():
+                for j, (_, p) in enumerate(g.iterrows()):
+                    spectra = pd.DataFrame(res[k].W[j], index=np.arange(1, k + 1), columns=var_names)
+                    save_df_to_npz(spectra, self.paths["iter_spectra"] % (k, int(p["iter"])))
+            return
         for k, grp in sel.groupby("n_components", sort=True):
             k = int(k)
             idx = list(grp.index)

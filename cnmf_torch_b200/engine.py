@@ -186,9 +186,21 @@ class DenseFrobeniusEngine:
         return out
 
     # ------------------------------------------------------------------------------------
+    def factorize_online_many(self, ks, seeds_by_k, **kw):
+        """Online mode for several K: K values that share a padded Kp run as ONE stack (as ``factorize_many``
+        does in batch mode).  Returns {K: BatchResult}."""
+        stacks = {}
+        for k in [int(k) for k in ks]:
+            stacks.setdefault(pad4(k), []).append(k)
+        out = {}
+        for group in stacks.values():
+            groups = [(k,) + tuple(self.make_init(k, seeds_by_k[k])) for k in group]
+            out.update(self.factorize_online(None, groups=groups, **kw))
+        return out
+
     def factorize_online(self, K: int, seeds=None, H0=None, W0=None, tol=1e-4, max_pass=20, chunk_size=5000,
                          chunk_max_iter=200, h_tol=0.05, w_tol=0.05, l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0,
-                         eps=EPS_DEFAULT, return_H=False, inner_batch=4) -> BatchResult:
+                         eps=EPS_DEFAULT, return_H=False, inner_batch=4, groups=None):
         """Online-mode Frobenius MU of R replicates (run_nmf(mode='online'), what cNMF configures at
         cnmf.py:757-771).  Per pass and per chunk of ``chunk_size`` cells: inner MU loop on h against the
         cached x W^T (stopping rule of cnmf.py:365-378), A += h^T h, B += h^T x, inner MU loop on W against
@@ -201,9 +213,9 @@ class DenseFrobeniusEngine:
         if chunk_size % 4 != 0:
             raise ValueError("online_chunk_size must be a multiple of 4 (16-byte aligned chunk operands)")
         L, dev, grp = self.lib, self.device, self.row_group
-        if H0 is None or W0 is None:
+        if groups is None and (H0 is None or W0 is None):
             H0, W0 = self.make_init(K, seeds)
-        b = FrobBatch(self, K, H0, W0, "mu", l1_H, l2_H, l1_W, l2_W, eps)
+        b = FrobBatch(self, K, H0, W0, "mu", l1_H, l2_H, l1_W, l2_W, eps, groups=groups)
         R, Kp, N, G = b.R, b.Kp, self.N, self.G
         rk = R * Kp
         ldw, ldh = b.p.ldw, b.p.ldh
@@ -308,10 +320,18 @@ class DenseFrobeniusEngine:
             prev = np.where(alive, cur, prev)
             if not alive.any():
                 break
+        err = np.sqrt(np.maximum(2.0 * cur, 0.0))
+        inner = {"h": inner_total[0], "w": inner_total[1]}
+        if groups is not None:   # a stack of several K: one result per K
+            out = {}
+            for k, sl, W, H in b.results_by_group(return_H):
+                out[k] = BatchResult(W=W, H=H, err=err[sl], n_iter=n_pass[sl], trace=[(it, v[sl]) for it, v in trace],
+                                     launches=int(b.launches))
+                out[k].inner_iterations = inner
+            return out
         W, H = b.results(return_H)
-        res = BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_pass, trace=trace,
-                          launches=int(b.launches))
-        res.inner_iterations = {"h": inner_total[0], "w": inner_total[1]}
+        res = BatchResult(W=W, H=H, err=err, n_iter=n_pass, trace=trace, launches=int(b.launches))
+        res.inner_iterations = inner
         return res
 
 

@@ -103,3 +103,17 @@ def test_online_convergence_and_run_nmf_default_kwargs(problem):
     assert H.shape == ho.shape and W.shape == wo.shape
     assert abs(err - eo) / eo < 1e-3
     assert _pearson(W, wo) >= 0.999
+
+
+def test_online_stack_of_several_k_matches_single_k_runs(problem):
+    """K = 5, 6, 7 share Kp = 8: run as one stack, each replicate must come out as in its own single-K run."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    eng = DenseFrobeniusEngine(problem)
+    seeds = {5: [1, 2], 6: [3], 7: [4, 5]}
+    many = eng.factorize_online_many([5, 6, 7], seeds, tol=0.0, max_pass=3, chunk_size=100, chunk_max_iter=40)
+    for k, sd in seeds.items():
+        one = eng.factorize_online(k, seeds=sd, tol=0.0, max_pass=3, chunk_size=100, chunk_max_iter=40)
+        assert many[k].W.shape == one.W.shape
+        for r in range(len(sd)):
+            assert abs(many[k].err[r] - one.err[r]) / one.err[r] < 1e-4
+            assert _pearson(many[k].W[r], one.W[r]) >= 0.9999
