@@ -44,15 +44,17 @@ def _mkdir(path):
 
 
 class cNMF:
-    def __init__(self, output_dir=".", name=None, device="cuda:0", impl="auto"):
-        """cnmf.py:393-414.  ``device``/``impl`` are additions (which GPU, which CUDA path)."""
+    def __init__(self, output_dir=".", name=None, device="cuda:0", impl="auto", init_device=None):
+        """cnmf.py:393-414.  ``device``/``impl`` are additions (which GPU, which CUDA path); ``init_device``
+        ("cpu"/"cuda") overrides which torch generator draws the random init (default: as the ledger's
+        use_gpu flag says, see ``factorize``)."""
         import datetime
         import uuid
         self.output_dir = output_dir
         if name is None:
             name = "%s_%s" % (datetime.datetime.now().strftime("%Y_%m_%d"), uuid.uuid4().hex[:6])
         self.name = name
-        self.device, self.impl = device, impl
+        self.device, self.impl, self.init_device = device, impl, init_device
         self.paths = None
         self._initialize_dirs()
 
@@ -191,7 +193,12 @@ class cNMF:
                                       worker_i, total_workers))
         if not jobs:
             return
-        engine = make_engine(X, beta_loss=kw.get("beta_loss", "frobenius"), device=self.device, impl=self.impl)
+        # the ledger's use_gpu flag keeps the one meaning it can have on a GPU-only engine: WHICH torch generator
+        # draws the random init (device generator under use_gpu=True, host generator otherwise -- nmf-torch draws
+        # on the device it computes on), so replicates start where the reference's would for that flag
+        init_device = self.init_device or ("cuda" if kw.get("use_gpu", True) else "cpu")
+        engine = make_engine(X, beta_loss=kw.get("beta_loss", "frobenius"), device=self.device, impl=self.impl,
+                             init_device=init_device)
         engine_kw = {k: kw[k] for k in ("init", "algo", "mode", "tol", "alpha_W", "l1_ratio_W", "alpha_H",
                                         "l1_ratio_H", "batch_max_iter", "online_max_pass", "online_chunk_size",
                                         "online_chunk_max_iter", "online_h_tol", "online_w_tol") if k in kw}
@@ -379,9 +386,11 @@ def main():
     parser.add_argument("--local-density-threshold", type=float, default=0.5)
     parser.add_argument("--local-neighborhood-size", type=float, default=0.30)
     parser.add_argument("--device", type=str, default=None)
+    parser.add_argument("--init-device", type=str, choices=["cpu", "cuda"], default=None,
+                        help="[factorize] torch generator that draws the random init (default: the run's use_gpu flag)")
     args = parser.parse_args()
     device = args.device or "cuda:%d" % int(os.environ.get("LOCAL_RANK", "0"))
-    obj = cNMF(output_dir=args.output_dir, name=args.name, device=device)
+    obj = cNMF(output_dir=args.output_dir, name=args.name, device=device, init_device=args.init_device)
     if args.command == "factorize":
         # one process per GPU:  torchrun --nproc-per-node 8 -m cnmf_torch_b200.cnmf factorize --name ...
         # strides the replicate ledger over the ranks exactly like worker_filter (cnmf.py:53-54, 876-880)

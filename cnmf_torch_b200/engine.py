@@ -45,6 +45,58 @@ def init_random(x_mean: float, n: int, g: int, k: int, seed: int):
     return h, w
 
 
+def draw_init(x_mean, n_total, n, row_offset, g, k, seeds, device, init_device="cpu"):
+    """H0 [R, n, k], W0 [R, k, g] for R = len(seeds) replicates: |sqrt(mean(X)/k) * N(0,1)|, H then W from one
+    generator seeded with the replicate's ``random_state`` (see ``init_random``).
+
+    ``init_device`` picks WHICH torch generator draws, i.e. which of nmf-torch's two streams the replicates
+    start from: "cpu" = the host generator (what the reference draws with use_gpu=False, cnmf.py:461/770, and
+    what the oracle draws), written into pinned staging buffers; "cuda" = the device generator (what
+    ``torch.manual_seed(seed); torch.randn(..., device='cuda')`` yields, i.e. the reference with use_gpu=True),
+    drawn straight into device memory -- no host RNG time and no H2D copy of the initial state.
+    A row-sharded engine (n_total != n) draws the GLOBAL H0 and keeps its own rows, so a sharded run starts from
+    exactly the state a single-GPU run would."""
+    if init_device not in ("cpu", "cuda"):
+        raise ValueError(f"init_device={init_device!r}: expected 'cpu' or 'cuda'")
+    seeds = [int(s) for s in seeds]
+    R = len(seeds)
+    avg = math.sqrt(float(x_mean) / k)
+    sharded = n_total != n
+    if init_device == "cuda":
+        f32 = dict(device=device, dtype=torch.float32)
+        H0 = torch.empty((R, n, k), **f32)
+        W0 = torch.empty((R, k, g), **f32)
+        gen = torch.Generator(device=device)
+        tmp = torch.empty((n_total, k), **f32) if sharded else None
+        for i in range(R):
+            gen.manual_seed(seeds[i])
+            if sharded:
+                torch.randn((n_total, k), generator=gen, out=tmp)
+                H0[i].copy_(tmp[row_offset:row_offset + n])
+            else:
+                torch.randn((n, k), generator=gen, out=H0[i])
+            torch.randn((k, g), generator=gen, out=W0[i])
+        H0.mul_(avg).abs_()
+        W0.mul_(avg).abs_()
+        return H0, W0
+    pin = torch.cuda.is_available()
+    H0 = torch.empty((R, n, k), dtype=torch.float32, pin_memory=pin)
+    W0 = torch.empty((R, k, g), dtype=torch.float32, pin_memory=pin)
+    for i in range(R):
+        if sharded:
+            h, w = init_random(x_mean, n_total, g, k, seeds[i])
+            H0[i].copy_(h[row_offset:row_offset + n])
+            W0[i].copy_(w)
+        else:
+            # the same draws as init_random, written straight into the pinned staging buffers (about 0.1 ms
+            # per replicate at 2700 x 2000, K=10; a thread pool over replicates measured slower than this loop)
+            gen = torch.Generator(device="cpu")
+            gen.manual_seed(seeds[i])
+            torch.randn((n, k), generator=gen, dtype=torch.float32, out=H0[i]).mul_(avg).abs_()
+            torch.randn((k, g), generator=gen, dtype=torch.float32, out=W0[i]).mul_(avg).abs_()
+    return H0, W0
+
+
 @dataclass
 class BatchResult:
     W: np.ndarray                  # [R, K, G] spectra
@@ -58,11 +110,13 @@ class BatchResult:
 class DenseFrobeniusEngine:
     """X resident as dense fp32 [N x G] and its transpose [G x N]; Frobenius MU / HALS."""
 
-    def __init__(self, X, device="cuda:0", impl=_lib.IMPL_AUTO, row_group=None, row_offset=0):
+    def __init__(self, X, device="cuda:0", impl=_lib.IMPL_AUTO, row_group=None, row_offset=0, init_device="cpu"):
         """``row_group``: torch.distributed group over which the CELLS are sharded (online mode for very
-        large N); X is then this rank's block of rows and ||X||^2 / mean(X) are made global."""
+        large N); X is then this rank's block of rows and ||X||^2 / mean(X) are made global.
+        ``init_device``: which torch generator draws the 'random' init (see ``draw_init``)."""
         self.lib = lib()  # raises if the CUDA library is missing -- no fallback
         self.impl = impl
+        self.init_device = init_device
         self.row_group = row_group
         self.row_offset = int(row_offset)  # first global row of this rank's block
         if not torch.cuda.is_available():
@@ -106,31 +160,10 @@ class DenseFrobeniusEngine:
         return np.asarray(self._x_host.cpu().numpy() if torch.is_tensor(self._x_host) else self._x_host, dtype=np.float64)
 
     # ------------------------------------------------------------------------------------
-    def make_init(self, K: int, seeds):
-        """H0 [R, N, K], W0 [R, K, G] on the host (pinned staging buffers), one torch CPU generator per
-        replicate seed -- the draws nmf-torch's CPU path would make (about 0.1 ms per replicate at
-        2700 x 2000, K=10; a thread pool over replicates measured slower than this loop)."""
-        seeds = [int(s) for s in seeds]
-        R = len(seeds)
-        pin = torch.cuda.is_available()
-        H0 = torch.empty((R, self.N, K), dtype=torch.float32, pin_memory=pin)
-        W0 = torch.empty((R, K, self.G), dtype=torch.float32, pin_memory=pin)
-        avg = math.sqrt(float(self.x_mean) / K)
-        for i in range(R):
-            if self.N_total != self.N:
-                # row-sharded: draw the GLOBAL H0 and keep this rank's rows, so a sharded run starts from
-                # exactly the state a single-GPU run would
-                h, w = init_random(self.x_mean, self.N_total, self.G, K, seeds[i])
-                H0[i].copy_(h[self.row_offset:self.row_offset + self.N])
-                W0[i].copy_(w)
-            else:
-                # the same draws as init_random (H then W from one generator), written straight into the
-                # pinned staging buffers
-                gen = torch.Generator(device="cpu")
-                gen.manual_seed(seeds[i])
-                torch.randn((self.N, K), generator=gen, dtype=torch.float32, out=H0[i]).mul_(avg).abs_()
-                torch.randn((K, self.G), generator=gen, dtype=torch.float32, out=W0[i]).mul_(avg).abs_()
-        return H0, W0
+    def make_init(self, K: int, seeds, init_device=None):
+        """H0 [R, N, K], W0 [R, K, G] of the 'random' init, one generator per replicate seed (``draw_init``)."""
+        return draw_init(self.x_mean, self.N_total, self.N, self.row_offset, self.G, int(K), seeds, self.device,
+                         init_device or self.init_device)
 
     def _upload_state(self, H0, W0, K, Kp):
         R = int(W0.shape[0])
@@ -170,7 +203,9 @@ class DenseFrobeniusEngine:
         stacks = {}
         for k in ks:                       # K values with the same padded Kp share one stack
             stacks.setdefault(pad4(k), []).append(k)
-        with ThreadPoolExecutor(max_workers=max(1, min(len(ks), 3))) as pool:
+        # host draws: a few threads, so that earlier batches upload while later ones are drawn; device draws are
+        # just kernel launches on the current stream
+        with ThreadPoolExecutor(max_workers=1 if self.init_device == "cuda" else max(1, min(len(ks), 3))) as pool:
             futs = {k: pool.submit(self.make_init, k, seeds_by_k[k]) for k in ks}
             batches = []
             for kp, group in stacks.items():
@@ -454,20 +489,37 @@ class FrobBatch:
     def set_active(self, alive: np.ndarray) -> None:
         self.active.copy_(torch.from_numpy(alive.astype(np.uint8)))
 
+    @staticmethod
+    def _to_host(views):
+        """Device views -> host arrays through pinned staging buffers (torch's caching host allocator), all copies
+        enqueued before the one synchronisation; pageable destinations cost ~7x more at 45 MB of spectra."""
+        bufs = []
+        for v in views:
+            if v is None:
+                bufs.append(None)
+                continue
+            b = torch.empty(v.shape, dtype=v.dtype, pin_memory=True)
+            b.copy_(v, non_blocking=True)
+            bufs.append(b)
+        torch.cuda.current_stream().synchronize()
+        return [None if b is None else b.numpy() for b in bufs]
+
     def results(self, return_H=False):
         """(W [R, K, G], H [R, N, K] or None) -- for a mixed-K stack use ``results_by_group``."""
         eng = self.eng
-        W = self.Wall[:, :self.K, :eng.G].contiguous().cpu().numpy()
-        H = (self.Ht[:, :self.K, :eng.N].permute(0, 2, 1).contiguous().cpu().numpy()
-             if return_H else None)
+        W, H = self._to_host([self.Wall[:, :self.K, :eng.G],
+                              self.Ht[:, :self.K, :eng.N].permute(0, 2, 1) if return_H else None])
         return W, H
 
     def results_by_group(self, return_H=False):
         """[(K, slice of replicates, W [R_k, K, G], H or None)] for every group of the stack."""
-        eng, out, lo = self.eng, [], 0
+        eng, views, lo = self.eng, [], 0
         for k, r in zip(self.Ks, self.Rs):
-            W = self.Wall[lo:lo + r, :k, :eng.G].contiguous().cpu().numpy()
-            H = (self.Ht[lo:lo + r, :k, :eng.N].permute(0, 2, 1).contiguous().cpu().numpy() if return_H else None)
-            out.append((k, slice(lo, lo + r), W, H))
+            views.append(self.Wall[lo:lo + r, :k, :eng.G])
+            views.append(self.Ht[lo:lo + r, :k, :eng.N].permute(0, 2, 1) if return_H else None)
+            lo += r
+        host, out, lo = self._to_host(views), [], 0
+        for i, (k, r) in enumerate(zip(self.Ks, self.Rs)):
+            out.append((k, slice(lo, lo + r), host[2 * i], host[2 * i + 1]))
             lo += r
         return out

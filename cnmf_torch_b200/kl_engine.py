@@ -11,12 +11,13 @@ import torch
 
 from . import _lib
 from ._lib import KlProblem, check, lib, ptr
-from .engine import EPS_DEFAULT, BatchResult, init_random, pad4
+from .engine import EPS_DEFAULT, BatchResult, draw_init, pad4
 
 
 class SparseKLEngine:
-    def __init__(self, X, device="cuda:0"):
+    def __init__(self, X, device="cuda:0", init_device="cpu"):
         self.lib = lib()
+        self.init_device = init_device   # which torch generator draws the 'random' init (engine.draw_init)
         if not torch.cuda.is_available():
             raise _lib.Cnmfb200Error("CUDA device required: cnmf_torch_b200 has no CPU path")
         self.device = torch.device(device)
@@ -52,9 +53,9 @@ class SparseKLEngine:
     def host_matrix(self) -> np.ndarray:
         return np.asarray(self._csr_host.toarray(), dtype=np.float64)
 
-    def make_init(self, K, seeds):
-        hs, ws = zip(*[init_random(self.x_mean, self.N, self.G, K, int(s)) for s in seeds])
-        return torch.stack(hs), torch.stack(ws)
+    def make_init(self, K, seeds, init_device=None):
+        return draw_init(self.x_mean, self.N, self.N, 0, self.G, int(K), seeds, self.device,
+                         init_device or self.init_device)
 
     def new_batch(self, K, seeds=None, H0=None, W0=None, l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT):
         if H0 is None or W0 is None:

@@ -45,14 +45,16 @@ def nndsvd_init(engine, k, seeds, init):
     return torch.stack(hs), torch.stack(ws)
 
 
-def make_engine(X, beta_loss="frobenius", device="cuda:0", impl="auto"):
-    """Ingest X once (cf. the per-replicate densify + upload at cnmf.py:817-819)."""
+def make_engine(X, beta_loss="frobenius", device="cuda:0", impl="auto", init_device="cpu"):
+    """Ingest X once (cf. the per-replicate densify + upload at cnmf.py:817-819).  ``init_device``: which torch
+    generator draws the 'random' init -- "cpu" (the reference with use_gpu=False, and the oracle) or "cuda" (the
+    reference with use_gpu=True); see engine.draw_init."""
     if beta_loss in ("frobenius", 2, 2.0):
         from .engine import DenseFrobeniusEngine
-        return DenseFrobeniusEngine(X, device=device, impl=_IMPL[impl])
+        return DenseFrobeniusEngine(X, device=device, impl=_IMPL[impl], init_device=init_device)
     if beta_loss in ("kullback-leibler", 1, 1.0):
         from .kl_engine import SparseKLEngine
-        return SparseKLEngine(X, device=device)
+        return SparseKLEngine(X, device=device, init_device=init_device)
     raise NotImplementedError(
         f"beta_loss={beta_loss!r}: this engine implements 'frobenius' and 'kullback-leibler'")
 
@@ -89,8 +91,13 @@ def run_nmf(X, n_components, init="random", beta_loss="frobenius", algo="mu", mo
             n_jobs=-1, random_state=0, use_gpu=True, alpha_W=0.0, l1_ratio_W=0.0, alpha_H=0.0,
             l1_ratio_H=0.0, fp_precision="float", batch_max_iter=500, online_max_pass=20,
             online_chunk_size=5000, online_chunk_max_iter=200, online_h_tol=0.05, online_w_tol=0.05,
-            online_usage_tol=None, online_spectra_tol=None, device="cuda:0", impl="auto", **unknown):
-    """One replicate, the reference's call shape.  Returns (H, W, err)."""
+            online_usage_tol=None, online_spectra_tol=None, device="cuda:0", impl="auto", init_device="cuda",
+            **unknown):
+    """One replicate, the reference's call shape.  Returns (H, W, err).
+
+    ``init_device`` (not a reference kwarg): the 'random' init is drawn by the device generator, as nmf-torch
+    does under use_gpu=True -- the only mode this GPU-only function has; pass "cpu" to start from the draws the
+    reference makes under use_gpu=False (and the oracle makes)."""
     if unknown:
         raise TypeError(f"run_nmf got unexpected keyword arguments {sorted(unknown)}")
     if use_gpu is False:
@@ -103,7 +110,7 @@ def run_nmf(X, n_components, init="random", beta_loss="frobenius", algo="mu", mo
         online_w_tol = online_spectra_tol
     if beta_loss in ("kullback-leibler", 1, 1.0) and algo != "mu":
         algo = "mu"  # only MU exists for beta != 2 (nmf-torch falls back the same way)
-    eng = make_engine(X, beta_loss=beta_loss, device=device, impl=impl)
+    eng = make_engine(X, beta_loss=beta_loss, device=device, impl=impl, init_device=init_device)
     res = run_nmf_batch(eng, n_components, [int(random_state)], init=init, algo=algo, mode=mode, tol=tol,
                         alpha_W=alpha_W, l1_ratio_W=l1_ratio_W, alpha_H=alpha_H, l1_ratio_H=l1_ratio_H,
                         batch_max_iter=batch_max_iter, online_max_pass=online_max_pass,

@@ -1,0 +1,90 @@
+"""GPU: the 'random' init and its two streams (engine.draw_init).
+
+nmf-torch seeds torch with ``random_state`` and draws |sqrt(mean(X)/K) * randn| for H then W on the device it
+computes on; the host stream (use_gpu=False, the oracle's) and the device stream (use_gpu=True) are both offered.
+PARITY UNPINNED against nmf-torch itself (absent here): what is pinned is that each stream equals what torch's
+own generator of that device yields for the seed."""
+import math
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def counts():
+    from cnmf_torch_b200.synth import nb_counts
+    return nb_counts(500, 240, k_true=5, seed=3, libsize=500.0)
+
+
+def test_device_stream_equals_torch_default_cuda_generator(counts):
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    eng = DenseFrobeniusEngine(counts, init_device="cuda")
+    K, seeds = 6, [11, 59886188, 0]
+    H0, W0 = eng.make_init(K, seeds)
+    assert H0.is_cuda and W0.is_cuda and H0.shape == (3, 500, K) and W0.shape == (3, K, 240)
+    avg = math.sqrt(eng.x_mean / K)
+    for i, s in enumerate(seeds):
+        torch.manual_seed(s)                                        # what run_nmf does before the draws
+        h = torch.abs(avg * torch.randn((500, K), dtype=torch.float32, device="cuda"))
+        w = torch.abs(avg * torch.randn((K, 240), dtype=torch.float32, device="cuda"))
+        assert torch.equal(h, H0[i]) and torch.equal(w, W0[i])     # bit-identical
+    H1, W1 = eng.make_init(K, seeds)
+    assert torch.equal(H0, H1) and torch.equal(W0, W1)             # deterministic
+
+
+def test_host_stream_equals_oracle_and_half_normal_moments(counts):
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    from oracle import nmf_oracle as no
+    eng = DenseFrobeniusEngine(counts)
+    H0, W0 = eng.make_init(5, [7, 8])
+    assert not H0.is_cuda
+    for i, s in enumerate([7, 8]):
+        h, w = no.init_random(float(counts.mean(dtype=np.float64)), 500, 240, 5, s)
+        assert np.array_equal(np.asarray(h), H0[i].numpy()) and np.array_equal(np.asarray(w), W0[i].numpy())
+    # both streams are |avg * N(0,1)|: E = avg * sqrt(2/pi)
+    Hd, Wd = eng.make_init(5, list(range(40)), init_device="cuda")
+    avg = math.sqrt(eng.x_mean / 5)
+    for t in (Hd, Wd):
+        assert (t >= 0).all() and abs(float(t.mean()) / (avg * math.sqrt(2 / math.pi)) - 1) < 0.01
+
+
+@pytest.mark.parametrize("mode", ["batch", "online", "kl"])
+def test_factorize_from_device_init_equals_explicit_init(counts, mode):
+    """Drawing on the device is only a different source of H0/W0: passing the same arrays explicitly (through the
+    host) gives bit-identical results."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    eng = (SparseKLEngine if mode == "kl" else DenseFrobeniusEngine)(counts, init_device="cuda")
+    seeds = [3, 4, 5]
+    H0, W0 = eng.make_init(5, seeds)
+    if mode == "online":
+        a = eng.factorize_online(5, seeds=seeds, tol=0.0, max_pass=2, chunk_size=200, chunk_max_iter=30)
+        b = eng.factorize_online(5, H0=H0.cpu(), W0=W0.cpu(), tol=0.0, max_pass=2, chunk_size=200, chunk_max_iter=30)
+    else:
+        a = eng.factorize(5, seeds=seeds, tol=0.0, max_iter=20)
+        b = eng.factorize(5, H0=H0.cpu(), W0=W0.cpu(), tol=0.0, max_iter=20)
+    assert np.array_equal(a.W, b.W) and np.array_equal(a.err, b.err)
+
+
+def test_use_gpu_flag_selects_the_stream_in_cnmf_factorize(tmp_path, counts):
+    """cNMF.factorize: the ledger's use_gpu flag picks the generator (device under True, host under False), and
+    the constructor's init_device overrides it."""
+    from cnmf_torch_b200 import cnmf as host
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    out = {}
+    for tag, use_gpu, override in (("dev", True, None), ("host", False, None), ("forced", True, "cpu")):
+        obj = host.cNMF(output_dir=str(tmp_path), name=tag, init_device=override)
+        obj.prepare_from_matrix(counts, [4], n_iter=3, seed=14, beta_loss="frobenius", use_gpu=use_gpu)
+        obj.factorize(nmf_kwargs_override=dict(mode="batch", batch_max_iter=20, tol=0.0))
+        out[tag] = np.stack([host.load_df_from_npz(obj.paths["iter_spectra"] % (4, i)).values for i in range(3)])
+        rp = host.load_df_from_npz(obj.paths["nmf_replicate_parameters"])
+    assert np.array_equal(out["host"], out["forced"]) and not np.array_equal(out["host"], out["dev"])
+    X, _, _ = obj.load_norm_counts()
+    seeds = [int(s) for s in rp["nmf_seed"]]
+    for tag, dev in (("host", "cpu"), ("dev", "cuda")):
+        eng = DenseFrobeniusEngine(X, init_device=dev)
+        ref = eng.factorize(4, seeds=seeds, tol=0.0, max_iter=20)
+        assert np.array_equal(ref.W, out[tag])

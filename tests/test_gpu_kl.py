@@ -88,7 +88,7 @@ def test_run_nmf_dropin_kl_and_frobenius(problem):
     kw = dict(alpha_W=0.0, alpha_H=0.0, l1_ratio_H=0.0, l1_ratio_W=0.0, algo="mu", tol=1e-4, mode="batch",
               init="random", n_jobs=-1, use_gpu=True, random_state=11, n_components=5)
     for beta in ("frobenius", "kullback-leibler"):
-        H, W, err = run_nmf(problem.astype(np.float64), beta_loss=beta, **kw)
+        H, W, err = run_nmf(problem.astype(np.float64), beta_loss=beta, init_device="cpu", **kw)
         assert H.shape == (problem.shape[0], 5) and W.shape == (5, problem.shape[1]) and np.isfinite(err)
         ho, wo, eo = no.run_nmf_oracle(problem, beta_loss=beta, **{k: v for k, v in kw.items() if k != "use_gpu"})
         assert abs(err - eo) / eo < 1e-3
@@ -103,7 +103,7 @@ def test_cnmf_default_online_kwargs_with_kl_fall_back_to_batch(problem, capsys):
     kw = dict(alpha_W=0.0, alpha_H=0.0, l1_ratio_H=0.0, l1_ratio_W=0.0, beta_loss="kullback-leibler", algo="mu",
               tol=1e-4, mode="online", online_chunk_max_iter=1000, online_chunk_size=5000, init="random", n_jobs=-1,
               use_gpu=True, random_state=3, n_components=4)
-    H, W, err = run_nmf(problem, **kw)
+    H, W, err = run_nmf(problem, init_device="cpu", **kw)     # the oracle draws from the host generator
     assert "Switch to batch" in capsys.readouterr().out
     ho, wo, eo = no.run_nmf_oracle(problem, **{k: v for k, v in kw.items() if k != "use_gpu"})
     assert abs(err - eo) / eo < 1e-3 and _pearson(W, wo) >= 0.999

@@ -98,7 +98,7 @@ def test_online_convergence_and_run_nmf_default_kwargs(problem):
     kw = dict(alpha_W=0.0, alpha_H=0.0, l1_ratio_H=0.0, l1_ratio_W=0.0, beta_loss="frobenius", algo="mu", tol=1e-4,
               mode="online", online_chunk_max_iter=1000, online_chunk_size=5000, init="random", n_jobs=-1, use_gpu=True,
               random_state=59886188, n_components=7)
-    H, W, err = run_nmf(problem.astype(np.float64), **kw)
+    H, W, err = run_nmf(problem.astype(np.float64), init_device="cpu", **kw)   # host generator, as the oracle
     ho, wo, eo = no.run_nmf_oracle(problem, **{k: v for k, v in kw.items() if k != "use_gpu"})
     assert H.shape == ho.shape and W.shape == wo.shape
     assert abs(err - eo) / eo < 1e-3
