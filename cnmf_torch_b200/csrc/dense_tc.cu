@@ -59,6 +59,7 @@ struct TcParams {
   int t;  // replicates per tile
   int num_m_tiles, num_m_groups, num_n_tiles, stages;
   float l1, l2, eps;
+  int dbg;  // dev probes (CNMF_B200_TC_DEBUG): 1 = main loop without MMAs, 2 = main loop without TMA loads
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -102,6 +103,21 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, u
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
       ::"r"(smem_u32(dst)), "l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
       : "memory");
+}
+// One lane of a converged warp (deterministic for a full mask).  The producer and MMA warps run their loops with
+// all 32 lanes and issue through the elected lane: inside an `if (lane == 0)` region ptxas cannot prove
+// convergence and wraps every UTCHMMA / UTCBAR / UBLKCP in an ELECT ... BRA.U.ANY loop, which made the issue
+// loop (not the tensor pipe) the limiter of the main loop (profiles/NOTES.md, "issue-bound main loop").
+__device__ __forceinline__ bool elect_one() {
+  uint32_t el;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(el));
+  return el != 0;
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
@@ -260,33 +276,38 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int num_kb = static_cast<int>((prm.Kd + TC_BK - 1) / TC_BK);
 
   if (warp == 0) {
-    if (lane == 0) {
-      // ===================== TMA producer (every CTA) =====================
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = group_id; tile < num_tiles; tile += num_groups) {
-        const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
-        const int m_tile = m_group * CG + static_cast<int>(cta_rank);
-        for (int kb = 0; kb < num_kb; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1u);
+    // ===================== TMA producer (every CTA; whole warp, one elected lane issues) =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    for (int tile = group_id; tile < num_tiles; tile += num_groups) {
+      const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
+      const int m_tile = m_group * CG + static_cast<int>(cta_rank);
+      for (int kb = 0; kb < num_kb; ++kb) {
+        mbar_wait(&empty[stage], phase ^ 1u);
+        if (elect_one()) {
           uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
-          if (CG == 2) {
+          if (CG == 2 && (prm.dbg & 2)) {
+            if (leader) mbar_arrive(&full[stage]);
+          } else if (CG == 2) {
             if (leader) mbar_expect_tx(&full[stage], 2u * stage_bytes);  // both CTAs' bytes land on the leader
             tma_load_2d_pair(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
             tma_load_2d_pair(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK,
                              n_tile * BN + static_cast<int>(cta_rank) * (BN / 2));
+          } else if (prm.dbg & 2) {
+            mbar_arrive(&full[stage]);
           } else {
             mbar_expect_tx(&full[stage], stage_bytes);
             tma_load_2d(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
             tma_load_2d(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK, n_tile * BN);
           }
-          if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
+        __syncwarp();
+        if (++stage == stages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp == 1) {
-    if (lane == 0 && leader) {
-      // ===================== MMA issuer (leader CTA of the group) =====================
+    if (leader) {
+      // ===================== MMA issuer (leader CTA of the group; whole warp, one elected lane issues) ==========
       // instruction descriptor: D=f32 (bits 4-5 = 1), A=B=tf32 (2 at bits 7-9 / 10-12), K-major both,
       // N>>3 at bits 17-22, M>>4 at bits 24-28 (M = 128 per CTA, 256 for a pair)
       const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | (static_cast<uint32_t>(BN >> 3) << 17) |
@@ -303,25 +324,36 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
-          const uint32_t sa = smem_u32(smem + static_cast<size_t>(stage) * stage_bytes);
-          const uint64_t a_desc = make_kmajor_sw128_desc(sa);
-          const uint64_t b_desc = make_kmajor_sw128_desc(sa + TC_A_BYTES);
+          if (elect_one()) {
+            if (prm.dbg & 1) {
+              if (CG == 2) { mbar_arrive_cta(&empty[stage], 0u); mbar_arrive_cta(&empty[stage], 1u); }
+              else mbar_arrive(&empty[stage]);
+            } else {
+              const uint32_t sa = smem_u32(smem + static_cast<size_t>(stage) * stage_bytes);
+              const uint64_t a_desc = make_kmajor_sw128_desc(sa);
+              const uint64_t b_desc = make_kmajor_sw128_desc(sa + TC_A_BYTES);
 #pragma unroll
-          for (int k = 0; k < TC_BK / 8; ++k) {
-            // advance 8 tf32 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
-            if (CG == 2)
-              tc_mma_tf32_pair(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k),
-                               idesc, (kb | k) != 0 ? 1u : 0u);
-            else
-              tc_mma_tf32(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k), idesc,
-                          (kb | k) != 0 ? 1u : 0u);
+              for (int k = 0; k < TC_BK / 8; ++k) {
+                // advance 8 tf32 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
+                if (CG == 2)
+                  tc_mma_tf32_pair(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k),
+                                   idesc, (kb | k) != 0 ? 1u : 0u);
+                else
+                  tc_mma_tf32(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k),
+                              idesc, (kb | k) != 0 ? 1u : 0u);
+              }
+              // frees the smem slot (in both CTAs of a pair) when these MMAs retire
+              if (CG == 2) tc_commit_pair(&empty[stage]); else tc_commit(&empty[stage]);
+            }
           }
-          // frees the smem slot (in both CTAs of a pair) when these MMAs retire
-          if (CG == 2) tc_commit_pair(&empty[stage]); else tc_commit(&empty[stage]);
+          __syncwarp();
           if (++stage == stages) { stage = 0; phase ^= 1u; }
         }
         // accumulator complete -> epilogue (of both CTAs)
-        if (CG == 2) tc_commit_pair(&tfull[buf]); else tc_commit(&tfull[buf]);
+        if (elect_one()) {
+          if (CG == 2) tc_commit_pair(&tfull[buf]); else tc_commit(&tfull[buf]);
+        }
+        __syncwarp();
       }
     }
   } else if (warp >= 4) {
@@ -715,6 +747,8 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
   prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.gram_ntile = gram_ntile; prm.active = active;
   prm.partials = partials; prm.R = R; prm.t = plan.t; prm.num_m_tiles = plan.num_m_tiles; prm.num_m_groups = plan.num_m_groups;
   prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
+  static const int dbg = [] { const char* e = getenv("CNMF_B200_TC_DEBUG"); return e ? atoi(e) : 0; }();
+  prm.dbg = dbg;
   const int64_t tiles = static_cast<int64_t>(plan.num_m_groups) * plan.num_n_tiles;  // per CTA group
   const int64_t slots = sms / plan.cg;
   const int grid = static_cast<int>((tiles < slots ? tiles : slots) * plan.cg);
