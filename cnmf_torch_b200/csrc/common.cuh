@@ -94,10 +94,13 @@ __device__ __forceinline__ double warp_sum(double v) {
 // p[k]  : (Y F^T)[row, r*KP + k]     s[k] : state[row, r*KP + k] (in/out)
 // gram  : KP x KP Gram of the fixed factor (shared memory; read as broadcast)
 // MU   : cnmf.py:358-372   HALS : sklearn _cdnmf_fast.pyx column sweep restated
+// ginv : optional (HALS) KP reciprocals of the regularised diagonal, 1/(G_kk + l2), or a negative value where
+//        G_kk + l2 < eps (component frozen at 0): the tcgen05 epilogue precomputes them once per tile, which
+//        takes the division (~14 instructions per component) out of the per-row instruction stream.
 template <int KP, int ALGO>
 __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
                                            const float* __restrict__ gram, float l1, float l2,
-                                           float eps) {
+                                           float eps, const float* __restrict__ ginv = nullptr) {
   if (ALGO == CNMF_B200_ALGO_MU) {
     float out[KP];
 #pragma unroll
@@ -127,8 +130,16 @@ __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
     }
 #pragma unroll
     for (int k = 0; k < KP; ++k) {
-      const float gkk = gram[k * KP + k] + l2;
-      const float v = (gkk < eps) ? 0.f : fmaxf(s[k] + __fdiv_rn(r[k], gkk), 0.f);
+      // s + r * (1/g) in every path (the reciprocal correctly rounded): at most ~1 ulp of the quotient away from
+      // the s + r / g of the restated coordinate descent, and the same arithmetic on the SIMT and tcgen05 paths
+      float inv;
+      if (ginv != nullptr) {
+        inv = ginv[k];
+      } else {
+        const float gkk = gram[k * KP + k] + l2;
+        inv = (gkk < eps) ? -1.f : __frcp_rn(gkk);
+      }
+      const float v = (inv < 0.f) ? 0.f : fmaxf(fmaf(r[k], inv, s[k]), 0.f);
       const float delta = v - s[k];
       s[k] = v;
 #pragma unroll

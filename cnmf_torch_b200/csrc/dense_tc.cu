@@ -35,7 +35,13 @@ constexpr int TC_THREADS = 256;  // 4 control warps + 4 epilogue warps: the mini
 // warpgroup g takes the replicates rr = g (mod groups) of a tile.  The row update is a per-thread dependency
 // chain (HALS sweeps k in order), so the only way to hide its latency is more resident warps per scheduler;
 // the register file (64K) bounds how many: ~100 regs/thread at KP<=12 allows 3 groups + the control warps.
-__host__ __device__ constexpr int tc_epi_groups(int kp) { return kp <= 8 ? 3 : (kp <= 20 ? 2 : 1); }
+#ifndef TC_EG12
+#define TC_EG12 2
+#endif
+#ifndef TC_PF12
+#define TC_PF12 1
+#endif
+__host__ __device__ constexpr int tc_epi_groups(int kp) { return kp <= 8 ? 3 : (kp <= 12 ? TC_EG12 : (kp <= 20 ? 2 : 1)); }
 __host__ __device__ constexpr int tc_threads(int kp) { return 128 + 128 * tc_epi_groups(kp); }
 constexpr int TC_MAX_BN = 256;
 constexpr int TC_TMEM_COLS = 512;
@@ -59,7 +65,8 @@ struct TcParams {
   int t;  // replicates per tile
   int num_m_tiles, num_m_groups, num_n_tiles, stages;
   float l1, l2, eps;
-  int dbg;  // dev probes (CNMF_B200_TC_DEBUG): 1 = main loop without MMAs, 2 = main loop without TMA loads
+  int dbg;  // dev probes (CNMF_B200_TC_DEBUG)
+  long long* prof;  // dev probe: clock64 stamps of CTA 0's first epilogue warp (CNMF_B200_TC_PROF = device pointer): 1 = main loop without MMAs, 2 = main loop without TMA loads
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -220,7 +227,9 @@ __global__ void __launch_bounds__(tc_threads(KP), 1)
 tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                     const TcParams prm) {
   extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  // 1024-byte alignment by pointer arithmetic ON the __shared__ array: a round trip through uintptr_t loses the
+  // address space and every later access (the Gram reads of the epilogue) becomes a generic LD.E instead of LDS
+  uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int t = prm.t;
   const int BN = t * KP;
@@ -238,6 +247,8 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tfull = empty + stages;
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+  uint8_t* sact = reinterpret_cast<uint8_t*>(tmem_slot + 2);  // [t] active flags of the tile's replicates
+  float* sginv = reinterpret_cast<float*>(sact + 64);         // [t][KP] HALS: 1/(G_kk + l2), < 0 where frozen
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
@@ -388,15 +399,32 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           sgram[i] = g;
         }
       }
+      // active flags of the tile's replicates: read once here instead of one dependent global load per replicate
+      // inside the update loop
+      for (int i = et; i < t; i += ET)
+        sact[i] = (r0 + i < prm.R && (prm.active == nullptr || prm.active[r0 + i] != 0)) ? 1 : 0;
+      const bool prof = prm.prof != nullptr && blockIdx.x == 0 && et == 0 && lt == 0;
+      int pi = 0;
+      if (prof) prm.prof[pi++] = clock64();
       epi_bar_sync<ET>();
+      if (ALGO == CNMF_B200_ALGO_HALS) {
+        // reciprocals of the regularised diagonal, once per tile (these warps idle here while the main loop runs)
+        for (int i = et; i < t * KP; i += ET) {
+          const int rr = i / KP, k = i - rr * KP;
+          const float gkk = sgram[rr * KP * KP + k * KP + k] + prm.l2;
+          sginv[i] = (gkk < prm.eps) ? -1.f : __frcp_rn(gkk);
+        }
+        epi_bar_sync<ET>();
+      }
       mbar_wait(&tfull[buf], tphase);
       tc_fence_after();
+      if (prof) prm.prof[pi++] = clock64();
       const int64_t m = static_cast<int64_t>(m_tile) * TC_BM + q * 32 + lane;
       const bool in = m < prm.M;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * TC_MAX_BN);
       // software pipeline over the replicates of the tile: the state of replicate rr+1 is requested
       // before replicate rr is updated, so its global-load latency hides behind the update
-      constexpr bool kPrefetch = (KP <= 12) && (ALGO != TC_MODE_STORE);
+      constexpr bool kPrefetch = (KP <= 8 || (KP == 12 && TC_PF12)) && (ALGO != TC_MODE_STORE);
       constexpr bool want_sums = SUMS && (ALGO < TC_MODE_STORE);  // compile-time: p is dead after the update otherwise
       float s[KP], s_nxt[kPrefetch ? KP : 1];
       if (kPrefetch && r0 + eg < prm.R) {
@@ -425,7 +453,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             s[k] = (in && ALGO != TC_MODE_STORE) ? sp[static_cast<int64_t>(k) * prm.lds] : 0.f;
         }
         tmem_ld_wait();
-        const bool act = prm.active == nullptr || prm.active[r] != 0;
+        const bool act = sact[rr] != 0;
         float cross = 0.f, ssum = 0.f;
         if (ALGO >= TC_MODE_STORE) {
           // plain GEMM epilogues of the online path: state = P (store) or state += P (accumulate)
@@ -437,7 +465,8 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         } else {
           if (in) {
             if (act) {
-              update_row<KP, ALGO>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps);
+              update_row<KP, ALGO>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps,
+                                   ALGO == CNMF_B200_ALGO_HALS ? sginv + rr * KP : nullptr);
 #pragma unroll
               for (int k = 0; k < KP; ++k) sp[static_cast<int64_t>(k) * prm.lds] = s[k];
               if (prm.state_op != nullptr) {
@@ -467,6 +496,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < KP; ++k) s[k] = s_nxt[k];
         }
+        if (prof && pi < 60) prm.prof[pi++] = clock64();
       }
       // all tcgen05.ld of this buffer are complete: hand it back to the MMA warp (of the leader CTA)
       tc_fence_before();
@@ -484,7 +514,8 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           prm.partials[(static_cast<int64_t>(m_tile) * prm.R + r) * 2 + (i & 1)] = v;
         }
       }
-      epi_bar_sync<ET>();  // sgram / sred are rewritten by the next tile
+      epi_bar_sync<ET>();  // sgram / sred / sact are rewritten by the next tile
+      if (prof) { prm.prof[pi++] = clock64(); prm.prof[63] = pi; }
     }
   }
 
@@ -565,7 +596,8 @@ struct TcPlan {
 static size_t tc_smem_bytes(int t, int Kp, int stages, int cg) {
   const size_t stage = TC_A_BYTES + static_cast<size_t>(t) * Kp / cg * TC_BK * 4;
   size_t extra = static_cast<size_t>(t) * Kp * Kp * 4 + 4 * static_cast<size_t>(t) * 2 * 4;
-  extra += (2 * TC_MAX_STAGES + 4) * 8 + 16;
+  extra += (2 * TC_MAX_STAGES + 4) * 8 + 16 + 64;  // barriers, TMEM slot, per-tile active flags (t <= 64)
+  extra += static_cast<size_t>(t) * Kp * 4;         // reciprocal diagonals (HALS)
   return stages * stage + extra + 1024;  // +1024: manual alignment of the dynamic base
 }
 
@@ -749,6 +781,7 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
   prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
   static const int dbg = [] { const char* e = getenv("CNMF_B200_TC_DEBUG"); return e ? atoi(e) : 0; }();
   prm.dbg = dbg;
+  { const char* e = getenv("CNMF_B200_TC_PROF"); prm.prof = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr; }
   const int64_t tiles = static_cast<int64_t>(plan.num_m_groups) * plan.num_n_tiles;  // per CTA group
   const int64_t slots = sms / plan.cg;
   const int grid = static_cast<int>((tiles < slots ? tiles : slots) * plan.cg);

@@ -149,8 +149,9 @@ def test_engine_tc_matches_simt_engine(problem):
     H0, W0 = e1.make_init(8, list(range(40)))
     a = e1.factorize(8, H0=H0, W0=W0, algo="hals", tol=1e-4, max_iter=200)
     b = e2.factorize(8, H0=H0, W0=W0, algo="hals", tol=1e-4, max_iter=200)
-    # stopping is a threshold on a small difference: most replicates stop at the same check, none far off
-    assert np.mean(a.n_iter == b.n_iter) >= 0.7 and np.all(np.abs(a.n_iter - b.n_iter) <= 20)
+    # stopping is a threshold on a small difference (checked every 10 iterations): most replicates stop at the
+    # same check, none more than three checks apart
+    assert np.mean(a.n_iter == b.n_iter) >= 0.7 and np.all(np.abs(a.n_iter - b.n_iter) <= 30)
     assert np.max(np.abs(a.err - b.err) / a.err) < 1e-3
     same = a.n_iter == b.n_iter
     for r in np.where(same)[0][:10]:
