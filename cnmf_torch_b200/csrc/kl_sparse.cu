@@ -19,8 +19,9 @@
 
 namespace cnmf {
 
-constexpr int KL_THREADS = 128;  // replicates per CTA (one per thread)
-constexpr int KL_ROWS = 4;       // max CSR rows per CTA (one after the other); 1 when there are few, long rows
+constexpr int KL_THREADS = 128;  // (row, replicate) pairs per CTA, one per thread
+constexpr int KL_SEG_MAX = 2048;  // engine path: rows longer than the segment length (256 .. 2048, kl_seg_len) are cut
+constexpr int KL_SEG_MIN = 256;
 
 template <int KP>
 __device__ __forceinline__ void load_vec(const float* __restrict__ p, float (&v)[KP]) {
@@ -52,87 +53,204 @@ __global__ void to_half_kernel(const float* __restrict__ src, __half* __restrict
     dst[i] = __float2half_rn(fminf(src[i], 65504.f));
 }
 
+// One thread = one (row, replicate) pair, pairs numbered row-major with the replicate fastest and packed densely
+// over the threads of the grid: a CTA is 128 consecutive pairs whatever R is (R = 13 replicates per GPU in an 8-way
+// sharded run fills the lanes as well as R = 128; with one CTA per row only 13 of 128 lanes worked).  Lanes of a
+// warp may sit in two or three consecutive rows: their index/value loads coalesce per row and the loop runs to the
+// longest of those rows.
 template <int KP>
-__global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
-    const int* __restrict__ row_ptr, const int* __restrict__ col_idx, const float* __restrict__ val, int64_t M,
-    const __half* __restrict__ F, float* __restrict__ state, __half* __restrict__ state_h,
-    const float* __restrict__ fsum, const uint8_t* __restrict__ active, int R, float l1, float l2, float eps,
-    int rows_per_cta) {
-  const int r = blockIdx.y * KL_THREADS + threadIdx.x;
-  if (r >= R) return;
-  if (active != nullptr && active[r] == 0) return;
-  const int64_t rk = (int64_t)R * KP;
+__device__ __forceinline__ void kl_apply_update(float (&h)[KP], const float (&num)[KP], const float* __restrict__ fsum_r,
+                                                float l1, float l2, float eps, float* __restrict__ sp,
+                                                __half* __restrict__ hp) {
   float den[KP];
-  load_vec<KP>(fsum + (int64_t)r * KP, den);
-  const int64_t row0 = (int64_t)blockIdx.x * rows_per_cta;
-  for (int rr = 0; rr < rows_per_cta; ++rr) {
-    const int64_t row = row0 + rr;
-    if (row >= M) break;
-    float* sp = state + row * rk + (int64_t)r * KP;
-    float h[KP], num[KP];
-    load_vec<KP>(sp, h);
+  load_vec<KP>(fsum_r, den);
 #pragma unroll
-    for (int k = 0; k < KP; ++k) num[k] = 0.f;
-    const int beg = row_ptr[row], end = row_ptr[row + 1];
-    int p = beg;
-    // several non-zeros in flight per thread: the index -> gather -> dot -> divide chain of one non-zero is
-    // long, and with one thread per (row, replicate) there is no other source of parallelism
-    constexpr int U = (KP <= 12) ? 4 : 2;
-    for (; p + U <= end; p += U) {
-      int j[U];
-      float x[U], w[U][KP], sa[U], sb[U], q[U];
+  for (int k = 0; k < KP; ++k) {
+    const float d = fmaf(l2, h[k], den[k]);
+    const float n = l1 > 0.f ? fmaxf(num[k] - l1, 0.f) : num[k];
+    const float rate = d < eps ? 0.f : __fdiv_rn(n, d);
+    h[k] *= rate;
+  }
 #pragma unroll
-      for (int u = 0; u < U; ++u) { j[u] = col_idx[p + u]; x[u] = val[p + u]; }
+  for (int c = 0; c < KP; c += 4) *reinterpret_cast<float4*>(sp + c) = make_float4(h[c], h[c + 1], h[c + 2], h[c + 3]);
+  if (hp != nullptr) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) load_vec_h<KP>(F + (int64_t)j[u] * rk + (int64_t)r * KP, w[u]);
-#pragma unroll
-      for (int u = 0; u < U; ++u) {
-        sa[u] = 0.f; sb[u] = 0.f;
-#pragma unroll
-        for (int k = 0; k < KP; k += 2) { sa[u] = fmaf(h[k], w[u][k], sa[u]); sb[u] = fmaf(h[k + 1], w[u][k + 1], sb[u]); }
-        q[u] = __fdividef(x[u], fmaxf(sa[u] + sb[u], eps));  // stored entries are > 0 (checked at ingest); 2-ulp divide
-      }
-#pragma unroll
-      for (int u = 0; u < U; ++u)
-#pragma unroll
-        for (int k = 0; k < KP; ++k) num[k] = fmaf(q[u], w[u][k], num[k]);
-    }
-    for (; p < end; ++p) {
-      const int j0 = col_idx[p];
-      const float x0 = val[p];
-      float w0[KP];
-      load_vec_h<KP>(F + (int64_t)j0 * rk + (int64_t)r * KP, w0);
-      float s0 = 0.f, s1 = 0.f;
-#pragma unroll
-      for (int k = 0; k < KP; k += 2) { s0 = fmaf(h[k], w0[k], s0); s1 = fmaf(h[k + 1], w0[k + 1], s1); }
-      const float q0 = __fdividef(x0, fmaxf(s0 + s1, eps));
-#pragma unroll
-      for (int k = 0; k < KP; ++k) num[k] = fmaf(q0, w0[k], num[k]);
-    }
-#pragma unroll
-    for (int k = 0; k < KP; ++k) {
-      const float d = fmaf(l2, h[k], den[k]);
-      const float n = l1 > 0.f ? fmaxf(num[k] - l1, 0.f) : num[k];
-      const float rate = d < eps ? 0.f : __fdiv_rn(n, d);
-      h[k] *= rate;
-    }
-#pragma unroll
-    for (int c = 0; c < KP; c += 4) *reinterpret_cast<float4*>(sp + c) = make_float4(h[c], h[c + 1], h[c + 2], h[c + 3]);
-    if (state_h != nullptr) {
-      __half* hp = state_h + row * rk + (int64_t)r * KP;
-#pragma unroll
-      for (int c = 0; c < KP; c += 4) {
-        uint2 t;
-        *reinterpret_cast<__half2*>(&t.x) = __floats2half2_rn(fminf(h[c], 65504.f), fminf(h[c + 1], 65504.f));
-        *reinterpret_cast<__half2*>(&t.y) = __floats2half2_rn(fminf(h[c + 2], 65504.f), fminf(h[c + 3], 65504.f));
-        *reinterpret_cast<uint2*>(hp + c) = t;
-      }
+    for (int c = 0; c < KP; c += 4) {
+      uint2 t;
+      *reinterpret_cast<__half2*>(&t.x) = __floats2half2_rn(fminf(h[c], 65504.f), fminf(h[c + 1], 65504.f));
+      *reinterpret_cast<__half2*>(&t.y) = __floats2half2_rn(fminf(h[c + 2], 65504.f), fminf(h[c + 3], 65504.f));
+      *reinterpret_cast<uint2*>(hp + c) = t;
     }
   }
 }
 
-// sum over non-zeros of x * log(max(s, eps)) per replicate; per-CTA fp64 partials [gridDim.x x R]
-constexpr int KLO_ROWS = 64;
+// Segment table of one CSR matrix (engine path, built on the device by kl_build_segments): rows longer than the segment length
+// entries are cut into segments of that length.  A gene expressed in every cell is a row of N entries in CSR(X^T); one
+// thread walking it alone (20 000 entries ~ 1.6 ms) set the duration of the whole gene-major half-step whatever R.
+// A thread then is a (segment, replicate) pair; segments of a cut row leave their KP numerators in `part` and
+// kl_finish_rows_kernel adds them in segment order (deterministic) and applies the update.
+struct KlSegs {
+  const int* row_seg_ptr;   // [M + 1] first segment of each row
+  const int* row_slot_ptr;  // [M + 1] first partial slot of each row (rows with one segment own none)
+  const int* seg_row;       // [nseg]
+  const int* seg_beg;       // [nseg] first entry of the segment
+  const int* multi_rows;    // [n_multi] rows that were cut (any order)
+  const int* n_multi;       // [1]
+  float* part;              // [slots x R*KP]
+  int seg_len;              // entries per segment
+};
+
+template <int KP, bool SEG>
+__global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
+    const int* __restrict__ row_ptr, const int* __restrict__ col_idx, const float* __restrict__ val, int64_t M,
+    const __half* __restrict__ F, float* __restrict__ state, __half* __restrict__ state_h,
+    const float* __restrict__ fsum, const uint8_t* __restrict__ active, int R, float l1, float l2, float eps,
+    const KlSegs sg) {
+  const int64_t g = (int64_t)blockIdx.x * KL_THREADS + threadIdx.x;
+  const int64_t unit = g / R;             // row, or segment
+  const int r = (int)(g - unit * R);
+  int64_t row = unit;
+  int beg, end, slot = -1;
+  if (SEG) {
+    if (unit >= sg.row_seg_ptr[M]) return;
+    row = sg.seg_row[unit];
+    beg = sg.seg_beg[unit];
+    const int row_end = row_ptr[row + 1];
+    end = beg + sg.seg_len < row_end ? beg + sg.seg_len : row_end;
+    const int s0 = sg.row_seg_ptr[row];
+    if (sg.row_seg_ptr[row + 1] - s0 > 1) slot = sg.row_slot_ptr[row] + (int)(unit - s0);
+  } else {
+    if (row >= M) return;
+    beg = row_ptr[row];
+    end = row_ptr[row + 1];
+  }
+  if (active != nullptr && active[r] == 0) return;
+  const int64_t rk = (int64_t)R * KP;
+  float* sp = state + row * rk + (int64_t)r * KP;
+  float h[KP], num[KP];
+  load_vec<KP>(sp, h);
+#pragma unroll
+  for (int k = 0; k < KP; ++k) num[k] = 0.f;
+  int p = beg;
+  // several non-zeros in flight per thread: the index -> gather -> dot -> divide chain of one non-zero is
+  // long, and with one thread per (row, replicate) there is no other source of parallelism
+  constexpr int U = (KP <= 12) ? 4 : 2;
+  for (; p + U <= end; p += U) {
+    int j[U];
+    float x[U], w[U][KP], sa[U], sb[U], q[U];
+#pragma unroll
+    for (int u = 0; u < U; ++u) { j[u] = col_idx[p + u]; x[u] = val[p + u]; }
+#pragma unroll
+    for (int u = 0; u < U; ++u) load_vec_h<KP>(F + (int64_t)j[u] * rk + (int64_t)r * KP, w[u]);
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      sa[u] = 0.f; sb[u] = 0.f;
+#pragma unroll
+      for (int k = 0; k < KP; k += 2) { sa[u] = fmaf(h[k], w[u][k], sa[u]); sb[u] = fmaf(h[k + 1], w[u][k + 1], sb[u]); }
+      q[u] = __fdividef(x[u], fmaxf(sa[u] + sb[u], eps));  // stored entries are > 0 (checked at ingest); 2-ulp divide
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u)
+#pragma unroll
+      for (int k = 0; k < KP; ++k) num[k] = fmaf(q[u], w[u][k], num[k]);
+  }
+  for (; p < end; ++p) {
+    const int j0 = col_idx[p];
+    const float x0 = val[p];
+    float w0[KP];
+    load_vec_h<KP>(F + (int64_t)j0 * rk + (int64_t)r * KP, w0);
+    float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+    for (int k = 0; k < KP; k += 2) { s0 = fmaf(h[k], w0[k], s0); s1 = fmaf(h[k + 1], w0[k + 1], s1); }
+    const float q0 = __fdividef(x0, fmaxf(s0 + s1, eps));
+#pragma unroll
+    for (int k = 0; k < KP; ++k) num[k] = fmaf(q0, w0[k], num[k]);
+  }
+  if (SEG && slot >= 0) {   // a cut row: numerators of this segment only
+    float* pp = sg.part + (int64_t)slot * rk + (int64_t)r * KP;
+#pragma unroll
+    for (int c = 0; c < KP; c += 4)
+      *reinterpret_cast<float4*>(pp + c) = make_float4(num[c], num[c + 1], num[c + 2], num[c + 3]);
+    return;
+  }
+  kl_apply_update<KP>(h, num, fsum + (int64_t)r * KP, l1, l2, eps, sp,
+                      state_h != nullptr ? state_h + row * rk + (int64_t)r * KP : nullptr);
+}
+
+// rows that were cut into segments: numerators = sum of the segments' partials in segment order
+template <int KP>
+__global__ void __launch_bounds__(KL_THREADS) kl_finish_rows_kernel(float* __restrict__ state, __half* __restrict__ state_h,
+                                                                     const float* __restrict__ fsum,
+                                                                     const uint8_t* __restrict__ active, int R, float l1,
+                                                                     float l2, float eps, const KlSegs sg) {
+  const int64_t g = (int64_t)blockIdx.x * KL_THREADS + threadIdx.x;
+  const int64_t mi = g / R;
+  if (mi >= *sg.n_multi) return;
+  const int r = (int)(g - mi * R);
+  if (active != nullptr && active[r] == 0) return;
+  const int64_t row = sg.multi_rows[mi];
+  const int64_t rk = (int64_t)R * KP;
+  const int nseg = sg.row_seg_ptr[row + 1] - sg.row_seg_ptr[row];
+  const float* pp = sg.part + (int64_t)sg.row_slot_ptr[row] * rk + (int64_t)r * KP;
+  float h[KP], num[KP], t[KP];
+  load_vec<KP>(pp, num);
+  for (int s2 = 1; s2 < nseg; ++s2) {
+    load_vec<KP>(pp + (int64_t)s2 * rk, t);
+#pragma unroll
+    for (int k = 0; k < KP; ++k) num[k] += t[k];
+  }
+  float* sp = state + row * rk + (int64_t)r * KP;
+  load_vec<KP>(sp, h);
+  kl_apply_update<KP>(h, num, fsum + (int64_t)r * KP, l1, l2, eps, sp,
+                      state_h != nullptr ? state_h + row * rk + (int64_t)r * KP : nullptr);
+}
+
+// ---- segment table construction (one CTA of 1024 threads scans the rows; M is at most a few million) ----------
+__global__ void __launch_bounds__(1024) kl_seg_scan_kernel(const int* __restrict__ row_ptr, int64_t M, int seg_len,
+                                                           int* __restrict__ row_seg_ptr, int* __restrict__ row_slot_ptr) {
+  __shared__ int s_seg[1024], s_slot[1024];
+  const int t = threadIdx.x;
+  const int64_t chunk = (M + 1023) / 1024;
+  const int64_t lo = t * chunk, hi = lo + chunk < M ? lo + chunk : M;
+  int a = 0, b = 0;
+  for (int64_t i = lo; i < hi; ++i) {
+    const int len = row_ptr[i + 1] - row_ptr[i];
+    const int c = len > seg_len ? (len + seg_len - 1) / seg_len : 1;
+    a += c;
+    b += c > 1 ? c : 0;
+  }
+  s_seg[t] = a; s_slot[t] = b;
+  __syncthreads();
+  for (int off = 1; off < 1024; off <<= 1) {   // Hillis-Steele inclusive scan
+    const int va = t >= off ? s_seg[t - off] : 0, vb = t >= off ? s_slot[t - off] : 0;
+    __syncthreads();
+    s_seg[t] += va; s_slot[t] += vb;
+    __syncthreads();
+  }
+  a = s_seg[t] - a; b = s_slot[t] - b;       // exclusive prefix of this thread's chunk
+  for (int64_t i = lo; i < hi; ++i) {
+    row_seg_ptr[i] = a; row_slot_ptr[i] = b;
+    const int len = row_ptr[i + 1] - row_ptr[i];
+    const int c = len > seg_len ? (len + seg_len - 1) / seg_len : 1;
+    a += c;
+    b += c > 1 ? c : 0;
+  }
+  if (t == 1023) { row_seg_ptr[M] = s_seg[1023]; row_slot_ptr[M] = s_slot[1023]; }
+}
+
+__global__ void __launch_bounds__(256) kl_seg_fill_kernel(const int* __restrict__ row_ptr, int64_t M, int seg_len,
+                                                          const int* __restrict__ row_seg_ptr, int* __restrict__ seg_row,
+                                                          int* __restrict__ seg_beg, int* __restrict__ multi_rows,
+                                                          int* __restrict__ n_multi) {
+  const int64_t row = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (row >= M) return;
+  const int s0 = row_seg_ptr[row], n = row_seg_ptr[row + 1] - s0, beg = row_ptr[row];
+  for (int i = 0; i < n; ++i) { seg_row[s0 + i] = (int)row; seg_beg[s0 + i] = beg + i * seg_len; }
+  if (n > 1) multi_rows[atomicAdd(n_multi, 1)] = (int)row;   // list order is irrelevant to the result
+}
+
+// sum over non-zeros of x * log(max(s, eps)) per replicate; fp64 partials per block of KLO_ROWS rows [nblk x R]
+constexpr int KLO_ROWS = 8;
 
 template <int KP>
 __global__ void __launch_bounds__(KL_THREADS) kl_xlogs_kernel(const int* __restrict__ row_ptr,
@@ -140,11 +258,14 @@ __global__ void __launch_bounds__(KL_THREADS) kl_xlogs_kernel(const int* __restr
                                                               const float* __restrict__ val, int64_t M,
                                                               const float* __restrict__ Hr, const float* __restrict__ Wt,
                                                               int R, float eps, double* __restrict__ partial) {
-  const int r = blockIdx.y * KL_THREADS + threadIdx.x;
-  if (r >= R) return;
+  // one thread = (block of KLO_ROWS rows, replicate), pairs packed densely over the grid like the half-step
+  const int64_t g = (int64_t)blockIdx.x * KL_THREADS + threadIdx.x;
+  const int64_t blk = g / R;
+  const int64_t row0 = blk * KLO_ROWS;
+  if (row0 >= M) return;
+  const int r = (int)(g - blk * R);
   const int64_t rk = (int64_t)R * KP;
   double acc = 0.0;
-  const int64_t row0 = (int64_t)blockIdx.x * KLO_ROWS;
   for (int rr = 0; rr < KLO_ROWS; ++rr) {
     const int64_t row = row0 + rr;
     if (row >= M) break;
@@ -152,19 +273,32 @@ __global__ void __launch_bounds__(KL_THREADS) kl_xlogs_kernel(const int* __restr
     load_vec<KP>(Hr + row * rk + (int64_t)r * KP, h);
     const int beg = row_ptr[row], end = row_ptr[row + 1];
     float racc = 0.f;
-    for (int p = beg; p < end; ++p) {
+    int p = beg;
+    for (; p + 2 <= end; p += 2) {   // two entries in flight
+      const int j0 = col_idx[p], j1 = col_idx[p + 1];
+      const float x0 = val[p], x1 = val[p + 1];
+      float w0[KP], w1[KP];
+      load_vec<KP>(Wt + (int64_t)j0 * rk + (int64_t)r * KP, w0);
+      load_vec<KP>(Wt + (int64_t)j1 * rk + (int64_t)r * KP, w1);
+      float s0 = 0.f, s1 = 0.f;
+#pragma unroll
+      for (int k = 0; k < KP; ++k) { s0 = fmaf(h[k], w0[k], s0); s1 = fmaf(h[k], w1[k], s1); }
+      if (x0 > 0.f) racc = fmaf(x0, logf(fmaxf(s0, eps)), racc);
+      if (x1 > 0.f) racc = fmaf(x1, logf(fmaxf(s1, eps)), racc);
+    }
+    if (p < end) {
       const int j = col_idx[p];
       const float x = val[p];
       float w[KP];
       load_vec<KP>(Wt + (int64_t)j * rk + (int64_t)r * KP, w);
-      float s = 0.f;
+      float s0 = 0.f;
 #pragma unroll
-      for (int k = 0; k < KP; ++k) s = fmaf(h[k], w[k], s);
-      if (x > 0.f) racc = fmaf(x, logf(fmaxf(s, eps)), racc);
+      for (int k = 0; k < KP; ++k) s0 = fmaf(h[k], w[k], s0);
+      if (x > 0.f) racc = fmaf(x, logf(fmaxf(s0, eps)), racc);
     }
     acc += (double)racc;
   }
-  partial[(int64_t)blockIdx.x * R + r] = acc;
+  partial[blk * R + r] = acc;
 }
 
 // column sums of a [L x C] row-major array: per-CTA partials over 256-row slabs, then a fixed-order sum
@@ -191,13 +325,21 @@ __global__ void __launch_bounds__(128) colsum_final_kernel(const float* __restri
 }
 
 // err2[r] = 2 * ( sum x log x - sum x log s - sum x + sum_k hsum_k wsum_k + regularisation )
-__global__ void __launch_bounds__(32) kl_objective_kernel(double xlogx, double sumX, const double* __restrict__ partial,
-                                                          int nblk, const double* __restrict__ hsum,
-                                                          const double* __restrict__ wsum, int R, int Kp, float l1_H,
-                                                          float l1_W, double* __restrict__ err2) {
-  const int r = blockIdx.x, lane = threadIdx.x;
+__global__ void __launch_bounds__(256) kl_objective_kernel(double xlogx, double sumX, const double* __restrict__ partial,
+                                                           int nblk, const double* __restrict__ hsum,
+                                                           const double* __restrict__ wsum, int R, int Kp, float l1_H,
+                                                           float l1_W, double* __restrict__ err2) {
+  // one CTA per replicate; fixed assignment of partials to threads and a fixed reduction tree: deterministic
+  __shared__ double sx[8];
+  const int r = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   double xls = 0.0;
-  for (int b = lane; b < nblk; b += 32) xls += partial[(int64_t)b * R + r];
+  for (int b = threadIdx.x; b < nblk; b += 256) xls += partial[(int64_t)b * R + r];
+  xls = warp_sum(xls);
+  if (lane == 0) sx[warp] = xls;
+  __syncthreads();
+  if (warp != 0) return;
+  xls = 0.0;
+  for (int w = 0; w < 8; ++w) xls += sx[w];
   double ss = 0.0, sh = 0.0, sw = 0.0;
   for (int k = lane; k < Kp; k += 32) {
     const double a = hsum[(int64_t)r * Kp + k], b = wsum[(int64_t)r * Kp + k];
@@ -205,7 +347,7 @@ __global__ void __launch_bounds__(32) kl_objective_kernel(double xlogx, double s
     sh += a;
     sw += b;
   }
-  xls = warp_sum(xls); ss = warp_sum(ss); sh = warp_sum(sh); sw = warp_sum(sw);
+  ss = warp_sum(ss); sh = warp_sum(sh); sw = warp_sum(sw);
   if (lane == 0) err2[r] = 2.0 * (xlogx - xls - sumX + ss + (double)l1_H * sh + (double)l1_W * sw);
 }
 
@@ -249,20 +391,83 @@ static int launch_to_half(const float* src, __half* dst, int64_t n, cudaStream_t
   return 0;
 }
 
+// sg == nullptr: one thread per (row, replicate) (the standalone entry point, which has no workspace for a
+// segment table); else one thread per (segment, replicate) + the pass that finishes the cut rows.
 static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t M, const __half* F, float* state,
                           __half* state_h, const float* fsum, const uint8_t* active, int R, int Kp, float l1, float l2,
-                          float eps, cudaStream_t st) {
-  // few long rows (the gene-major half-step): one row per CTA so that there are enough CTAs to fill the SMs
-  const int rows = M >= 148 * 5 * 4 * KL_ROWS ? KL_ROWS : 1;
-  dim3 grid((unsigned)ceil_div(M, rows), (unsigned)ceil_div(R, KL_THREADS));
-  CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP><<<grid, KL_THREADS, 0, st>>>(rp, ci, v, M, F, state, state_h, fsum,
-                                                                               active, R, l1, l2, eps, rows)));
+                          float eps, cudaStream_t st, const KlSegs* sg = nullptr, int64_t nseg_max = 0,
+                          int64_t multi_max = 0) {
+  const int64_t blocks = ceil_div((sg ? nseg_max : M) * R, KL_THREADS);
+  CNMF_CHECK_ARG(blocks < (1ll << 31), "kl: rows * replicates too large for one launch");
+  if (sg == nullptr) {
+    KlSegs none{};
+    CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, false><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
+                             rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, none)));
+    CNMF_LAUNCH_CHECK();
+    return 0;
+  }
+  CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, true><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
+                           rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, *sg)));
   CNMF_LAUNCH_CHECK();
+  if (multi_max > 0) {
+    const int64_t fb = ceil_div(multi_max * R, KL_THREADS);
+    CNMF_DISPATCH_KP(Kp, (kl_finish_rows_kernel<KP><<<(unsigned)fb, KL_THREADS, 0, st>>>(state, state_h, fsum, active, R,
+                                                                                          l1, l2, eps, *sg)));
+    CNMF_LAUNCH_CHECK();
+  }
+  return 0;
+}
+
+// Segment length for a matrix of M rows and nnz entries at R replicates: long enough that whole rows stay whole
+// where there is parallelism anyway, short enough that (segments x R) threads fill the GPU when R is small (an
+// 8-way sharded run has R = 12 or 13 per K) -- a thread walks its entries one gather latency after the other.
+static int kl_seg_len(int64_t M, int64_t nnz, int R) {
+  const int64_t want = 148ll * 2048;                     // resident threads of the GPU
+  const int64_t spare = want - M * R;
+  int64_t s = spare > 0 ? (nnz * R) / spare : KL_SEG_MAX;
+  int len = KL_SEG_MIN;
+  while (len < KL_SEG_MAX && len * 2 <= s) len *= 2;
+  return len;
+}
+// bounds of the table
+static int64_t kl_nseg_max(int64_t M, int64_t nnz, int seg) { return M + nnz / seg; }
+static int64_t kl_multi_max(int64_t nnz, int seg) { return nnz / seg; }            // rows longer than seg
+static int64_t kl_slot_max(int64_t nnz, int seg) { return 2 * (nnz / seg) + 2; }   // their segments
+
+struct KlSegLayout { int64_t off_rsp, off_rslot, off_srow, off_sbeg, off_multi, off_nmulti; };
+
+static int64_t kl_seg_layout(int64_t M, int64_t nnz, int seg, int64_t off, KlSegLayout* o) {
+  o->off_rsp = off; off += align_up((M + 1) * 4, 256);
+  o->off_rslot = off; off += align_up((M + 1) * 4, 256);
+  o->off_srow = off; off += align_up(kl_nseg_max(M, nnz, seg) * 4, 256);
+  o->off_sbeg = off; off += align_up(kl_nseg_max(M, nnz, seg) * 4, 256);
+  o->off_multi = off; off += align_up((kl_multi_max(nnz, seg) + 1) * 4, 256);
+  o->off_nmulti = off; off += 256;
+  return off;
+}
+
+static int kl_build_segments(const int* row_ptr, int64_t M, int seg, char* ws, const KlSegLayout& o, float* part,
+                             KlSegs* out, cudaStream_t st) {
+  int* rsp = reinterpret_cast<int*>(ws + o.off_rsp);
+  int* rslot = reinterpret_cast<int*>(ws + o.off_rslot);
+  int* srow = reinterpret_cast<int*>(ws + o.off_srow);
+  int* sbeg = reinterpret_cast<int*>(ws + o.off_sbeg);
+  int* multi = reinterpret_cast<int*>(ws + o.off_multi);
+  int* nmulti = reinterpret_cast<int*>(ws + o.off_nmulti);
+  CNMF_CUDA(cudaMemsetAsync(nmulti, 0, 4, st));
+  kl_seg_scan_kernel<<<1, 1024, 0, st>>>(row_ptr, M, seg, rsp, rslot);
+  CNMF_LAUNCH_CHECK();
+  kl_seg_fill_kernel<<<(unsigned)ceil_div(M, 256), 256, 0, st>>>(row_ptr, M, seg, rsp, srow, sbeg, multi, nmulti);
+  CNMF_LAUNCH_CHECK();
+  out->row_seg_ptr = rsp; out->row_slot_ptr = rslot; out->seg_row = srow; out->seg_beg = sbeg;
+  out->multi_rows = multi; out->n_multi = nmulti; out->part = part; out->seg_len = seg;
   return 0;
 }
 
 struct KlLayout {
-  int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_cpart, off_opart, off_wh, off_hh, total;
+  int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_cpart, off_opart, off_wh, off_hh, off_part, total;
+  KlSegLayout segX, segXt;
+  int seg_x, seg_xt;  // segment lengths of CSR(X) and CSR(X^T)
   int nblk_obj;
 };
 
@@ -280,6 +485,13 @@ static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
   l.off_opart = off; off += align_up((int64_t)l.nblk_obj * p->R * 8, 256);
   l.off_wh = off; off += align_up(p->n_genes * C * 2, 256);   // fp16 gather copies of Wt and Hr
   l.off_hh = off; off += align_up(p->n_cells * C * 2, 256);
+  // segment tables of CSR(X) and CSR(X^T) and the partial numerators of cut rows (one buffer: the two half-steps
+  // of an iteration run one after the other)
+  l.seg_x = kl_seg_len(p->n_cells, p->nnz, p->R);
+  l.seg_xt = kl_seg_len(p->n_genes, p->nnz, p->R);
+  off = kl_seg_layout(p->n_cells, p->nnz, l.seg_x, off, &l.segX);
+  off = kl_seg_layout(p->n_genes, p->nnz, l.seg_xt, off, &l.segXt);
+  l.off_part = off; off += align_up(kl_slot_max(p->nnz, l.seg_x < l.seg_xt ? l.seg_x : l.seg_xt) * C * 4, 256);
   l.total = off;
   return l;
 }
@@ -315,11 +527,11 @@ static int kl_objective_impl(const cnmf_b200_kl_problem* p, const KlLayout& l, c
   const int64_t C = (int64_t)p->R * p->Kp;
   CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, wsum64, cpart, st));
   CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, hsum64, cpart, st));
-  dim3 grid((unsigned)l.nblk_obj, (unsigned)ceil_div(p->R, KL_THREADS));
+  const unsigned grid = (unsigned)ceil_div((int64_t)l.nblk_obj * p->R, KL_THREADS);
   CNMF_DISPATCH_KP(p->Kp, (kl_xlogs_kernel<KP><<<grid, KL_THREADS, 0, st>>>(p->row_ptr, p->col_idx, p->val, p->n_cells,
                                                                               p->Hr, p->Wt, p->R, p->eps, opart)));
   CNMF_LAUNCH_CHECK();
-  kl_objective_kernel<<<p->R, 32, 0, st>>>(p->xlogx, p->sumX, opart, l.nblk_obj, hsum64, wsum64, p->R, p->Kp, p->l1_H,
+  kl_objective_kernel<<<p->R, 256, 0, st>>>(p->xlogx, p->sumX, opart, l.nblk_obj, hsum64, wsum64, p->R, p->Kp, p->l1_H,
                                            p->l1_W, p->err2);
   CNMF_LAUNCH_CHECK();
   return 0;
@@ -373,15 +585,23 @@ int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* s
   __half* Wh = reinterpret_cast<__half*>(ws + l.off_wh);
   __half* Hh = reinterpret_cast<__half*>(ws + l.off_hh);
   if (n_iters > 0) CNMF_TRY(launch_to_half(p->Wt, Wh, p->n_genes * C, st));  // Hh is written by the first H half-step
+  KlSegs sgX{}, sgXt{};
+  float* part = reinterpret_cast<float*>(ws + l.off_part);
+  if (n_iters > 0) {  // stateless: the tables are rebuilt per call (a few tiny kernels against >= 1 iteration)
+    CNMF_TRY(kl_build_segments(p->row_ptr, p->n_cells, l.seg_x, ws, l.segX, part, &sgX, st));
+    CNMF_TRY(kl_build_segments(p->t_row_ptr, p->n_genes, l.seg_xt, ws, l.segXt, part, &sgXt, st));
+  }
+  const int64_t nsX = kl_nseg_max(p->n_cells, p->nnz, l.seg_x), nsXt = kl_nseg_max(p->n_genes, p->nnz, l.seg_xt);
+  const int64_t mmX = kl_multi_max(p->nnz, l.seg_x), mmXt = kl_multi_max(p->nnz, l.seg_xt);
   for (int it = 0; it < n_iters; ++it) {
     CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, nullptr, cpart, st));
     CNMF_TRY(launch_kl_half(p->row_ptr, p->col_idx, p->val, p->n_cells, Wh, p->Hr, Hh, wsum, p->active, p->R, p->Kp,
-                            p->l1_H, p->l2_H, p->eps, st));
+                            p->l1_H, p->l2_H, p->eps, st, &sgX, nsX, mmX));
     if (it == 0 && p->active != nullptr)  // frozen replicates skip the write: their copy must exist too
       CNMF_TRY(launch_to_half(p->Hr, Hh, p->n_cells * C, st));
     CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, nullptr, cpart, st));
     CNMF_TRY(launch_kl_half(p->t_row_ptr, p->t_col_idx, p->t_val, p->n_genes, Hh, p->Wt, Wh, hsum, p->active, p->R,
-                            p->Kp, p->l1_W, p->l2_W, p->eps, st));
+                            p->Kp, p->l1_W, p->l2_W, p->eps, st, &sgXt, nsXt, mmXt));
   }
   if (p->err2 != nullptr && n_iters > 0) CNMF_TRY(kl_objective_impl(p, l, st));
   return 0;
