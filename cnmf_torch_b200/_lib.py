@@ -63,6 +63,7 @@ SIGNATURES = {
     "cnmf_b200_row_update_blocks": (i64, [i64]),
     "cnmf_b200_row_update": (i32, [vp, i64, vp, i64, vp, vp, i64, i32, i32, i32, f32, f32, f32, vp, vp]),
     "cnmf_b200_round_tf32": (i32, [vp, i64, vp]),
+    "cnmf_b200_init_random": (i32, [vp, i32, i32, i32, i64, i64, i64, i64, f32, vp, i64, vp, i64, vp]),
     "cnmf_b200_dense_half_step": (i32, [vp, i64, i64, i64, vp, i64, vp, vp, i64, vp, vp, i32, i32, i32, f32, f32,
                                         f32, vp, vp]),
     "cnmf_b200_frob_objective_parts": (i32, [C.POINTER(FrobProblem), vp, vp]),

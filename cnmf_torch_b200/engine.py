@@ -98,6 +98,13 @@ def draw_init(x_mean, n_total, n, row_offset, g, k, seeds, device, init_device="
 
 
 @dataclass
+class SeedInit:
+    """Stands in for (H0, W0) in a FrobBatch group: 'draw the random init of these seeds on the device, straight
+    into the stacked layout' (cnmf_b200_init_random; bit-identical to draw_init(..., init_device="cuda"))."""
+    seeds: list
+
+
+@dataclass
 class BatchResult:
     W: np.ndarray                  # [R, K, G] spectra
     H: np.ndarray | None           # [R, N, K] usages (None unless requested)
@@ -165,6 +172,13 @@ class DenseFrobeniusEngine:
         return draw_init(self.x_mean, self.N_total, self.N, self.row_offset, self.G, int(K), seeds, self.device,
                          init_device or self.init_device)
 
+    def _init_for(self, K, seeds):
+        """(H0, W0) for a FrobBatch: host arrays from the host generator, or a SeedInit marker when the init is
+        drawn by the device generator (then it never exists outside the batch's own layout)."""
+        if self.init_device == "cuda" and self.N_total * int(K) < 2 ** 31 and int(K) * self.G < 2 ** 31:
+            return SeedInit([int(s) for s in seeds]), None
+        return self.make_init(K, seeds)
+
     def _upload_state(self, H0, W0, K, Kp):
         R = int(W0.shape[0])
         H0 = torch.as_tensor(H0, dtype=torch.float32)
@@ -180,7 +194,7 @@ class DenseFrobeniusEngine:
                   l2_W=0.0, eps=EPS_DEFAULT) -> "FrobBatch":
         """Device-resident state of R replicates of one K, ready to iterate."""
         if H0 is None or W0 is None:
-            H0, W0 = self.make_init(K, seeds)
+            H0, W0 = self._init_for(K, seeds)
         return FrobBatch(self, K, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps)
 
     def factorize(self, K: int, seeds=None, H0=None, W0=None, algo="mu", tol=1e-4, max_iter=500,
@@ -206,7 +220,7 @@ class DenseFrobeniusEngine:
         # host draws: a few threads, so that earlier batches upload while later ones are drawn; device draws are
         # just kernel launches on the current stream
         with ThreadPoolExecutor(max_workers=1 if self.init_device == "cuda" else max(1, min(len(ks), 3))) as pool:
-            futs = {k: pool.submit(self.make_init, k, seeds_by_k[k]) for k in ks}
+            futs = {k: pool.submit(self._init_for, k, seeds_by_k[k]) for k in ks}
             batches = []
             for kp, group in stacks.items():
                 groups = [(k,) + tuple(futs[k].result()) for k in group]
@@ -229,7 +243,7 @@ class DenseFrobeniusEngine:
             stacks.setdefault(pad4(k), []).append(k)
         out = {}
         for group in stacks.values():
-            groups = [(k,) + tuple(self.make_init(k, seeds_by_k[k])) for k in group]
+            groups = [(k,) + tuple(self._init_for(k, seeds_by_k[k])) for k in group]
             out.update(self.factorize_online(None, groups=groups, **kw))
         return out
 
@@ -249,7 +263,7 @@ class DenseFrobeniusEngine:
             raise ValueError("online_chunk_size must be a multiple of 4 (16-byte aligned chunk operands)")
         L, dev, grp = self.lib, self.device, self.row_group
         if groups is None and (H0 is None or W0 is None):
-            H0, W0 = self.make_init(K, seeds)
+            H0, W0 = self._init_for(K, seeds)
         b = FrobBatch(self, K, H0, W0, "mu", l1_H, l2_H, l1_W, l2_W, eps, groups=groups)
         R, Kp, N, G = b.R, b.Kp, self.N, self.G
         rk = R * Kp
@@ -436,7 +450,7 @@ class FrobBatch:
             groups = [(int(K), H0, W0)]
         self.eng = eng
         self.Ks = [int(g[0]) for g in groups]
-        self.Rs = [int(g[2].shape[0]) for g in groups]
+        self.Rs = [len(g[1].seeds) if isinstance(g[1], SeedInit) else int(g[2].shape[0]) for g in groups]
         self.K = max(self.Ks)
         self.R = sum(self.Rs)
         self.Kp = pad4(self.K)
@@ -446,12 +460,25 @@ class FrobBatch:
             raise ValueError("all K of one stack must round up to the same multiple of 4")
         algo_id = {"mu": _lib.ALGO_MU, "hals": _lib.ALGO_HALS}[algo]
         dev = eng.device
-        parts = [eng._upload_state(h0, w0, k, self.Kp) for k, h0, w0 in groups]
-        ldw, ldh = parts[0][2], parts[0][3]
-        self.Wall = parts[0][0] if len(parts) == 1 else torch.cat([q[0] for q in parts], 0)
-        self.Ht = parts[0][1] if len(parts) == 1 else torch.cat([q[1] for q in parts], 0)
-        del parts
         R, Kp = self.R, self.Kp
+        if all(isinstance(g[1], SeedInit) for g in groups):
+            # drawn on the device straight into the stacked layout: one launch per K of the stack
+            ldw, ldh = pad_ld(eng.G), pad_ld(eng.N)
+            self.Wall = torch.zeros((R, Kp, ldw), device=dev, dtype=torch.float32)
+            self.Ht = torch.zeros((R, Kp, ldh), device=dev, dtype=torch.float32)
+            lo = 0
+            for (k, si, _), r in zip(groups, self.Rs):
+                seeds = torch.tensor(si.seeds, dtype=torch.int64, device=dev)
+                check(eng.lib.cnmf_b200_init_random(ptr(seeds), r, k, Kp, eng.N_total, eng.N, eng.row_offset, eng.G,
+                                                    math.sqrt(float(eng.x_mean) / k), ptr(self.Ht[lo:]), ldh,
+                                                    ptr(self.Wall[lo:]), ldw, self._stream()), "init_random")
+                lo += r
+        else:
+            parts = [eng._upload_state(h0, w0, k, self.Kp) for k, h0, w0 in groups]
+            ldw, ldh = parts[0][2], parts[0][3]
+            self.Wall = parts[0][0] if len(parts) == 1 else torch.cat([q[0] for q in parts], 0)
+            self.Ht = parts[0][1] if len(parts) == 1 else torch.cat([q[1] for q in parts], 0)
+            del parts
         self.gramW = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
         self.gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
         self.active = torch.ones(R, device=dev, dtype=torch.uint8)

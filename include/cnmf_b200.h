@@ -146,6 +146,19 @@ typedef struct cnmf_b200_frob_problem {
   int64_t workspace_bytes;
 } cnmf_b200_frob_problem;
 
+/* 'random' init of R replicates of one K, drawn on the device into the stacked layout:
+ *   Ht[(r*Kp + k) * ldh + i] = |avg * z_H[i, k]|  (i = cell - row_offset, 0 <= i < n_local),
+ *   Wall[(r*Kp + k) * ldw + j] = |avg * z_W[k, j]|,
+ * where z_H [n_total x K] then z_W [K x n_genes] are what torch's CUDA generator seeded with seeds[r] yields
+ * (torch.randn on this GPU: Philox4_32_10 via cuRAND's device API with ATen's grid geometry, restated here), i.e.
+ * run_nmf(init='random', random_state=seeds[r]) of nmf-torch under use_gpu=True (called at cnmf.py:819; the seed
+ * is the ledger's nmf_seed, cnmf.py:885).  avg = sqrt(mean(X) / K).  seeds: DEVICE array [R].  Rows k >= K and
+ * padding columns are not written (the caller zero-fills).  A row-sharded caller passes its block of rows
+ * (row_offset, n_local) of the n_total cells and gets its block of the global draw. */
+int cnmf_b200_init_random(const int64_t* seeds, int32_t R, int32_t K, int32_t Kp, int64_t n_total, int64_t n_local,
+                          int64_t row_offset, int64_t n_genes, float avg, float* Ht, int64_t ldh, float* Wall,
+                          int64_t ldw, void* stream);
+
 /* Bytes of workspace cnmf_b200_frob_iterate needs for this problem (only shapes/impl are read). */
 int64_t cnmf_b200_frob_workspace_bytes(const cnmf_b200_frob_problem* p);
 

@@ -88,3 +88,44 @@ def test_use_gpu_flag_selects_the_stream_in_cnmf_factorize(tmp_path, counts):
         eng = DenseFrobeniusEngine(X, init_device=dev)
         ref = eng.factorize(4, seeds=seeds, tol=0.0, max_iter=20)
         assert np.array_equal(ref.W, out[tag])
+
+
+@pytest.mark.parametrize("shape", [(500, 240), (5000, 2000), (37, 19)])
+def test_fused_device_init_is_bit_identical_to_torch(shape):
+    """cnmf_b200_init_random (all replicates of a K in one launch, written straight into the stacked K-major
+    layout) restates ATen's grid-stride Philox geometry: every value equals torch's own CUDA generator's."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine, FrobBatch, SeedInit
+    from cnmf_torch_b200.synth import nb_counts
+    n, g = shape
+    x = nb_counts(n, g, k_true=4, seed=5, libsize=300.0)
+    eng = DenseFrobeniusEngine(x, init_device="cuda")
+    for K, seeds in ((7, [3, 14, 59886188, 2**31 + 5]), (12, [0, 1]), (13, [9])):
+        b = eng.new_batch(K, seeds=seeds)                    # SeedInit path
+        H0, W0 = eng.make_init(K, seeds)                     # torch.randn per replicate
+        assert torch.equal(b.Ht[:, :K, :n].permute(0, 2, 1), H0) and torch.equal(b.Wall[:, :K, :g], W0)
+        assert float(b.Ht[:, K:].abs().sum()) == 0.0 and float(b.Ht[:, :, n:].abs().sum()) == 0.0
+        assert float(b.Wall[:, K:].abs().sum()) == 0.0 and float(b.Wall[:, :, g:].abs().sum()) == 0.0
+    # a stack of several K, and a row-sharded engine keeping its block of the global draw
+    grp = [(9, SeedInit([1, 2, 3]), None), (11, SeedInit([4, 5]), None)]
+    st = FrobBatch(eng, None, None, None, "mu", 0, 0, 0, 0, 1e-16, groups=grp)
+    H9, W9 = eng.make_init(9, [1, 2, 3]); H11, W11 = eng.make_init(11, [4, 5])
+    assert torch.equal(st.Ht[:3, :9, :n].permute(0, 2, 1), H9) and torch.equal(st.Ht[3:, :11, :n].permute(0, 2, 1), H11)
+    assert torch.equal(st.Wall[:3, :9, :g], W9) and torch.equal(st.Wall[3:, :11, :g], W11)
+    if n >= 100:
+        lo, hi = n // 5, n // 5 + n // 2
+        part = DenseFrobeniusEngine(x[lo:hi], init_device="cuda")
+        part.N_total, part.row_offset, part.x_mean = n, lo, eng.x_mean      # what a row group's all-reduce sets
+        pb = part.new_batch(7, seeds=[3, 14])
+        H0, W0 = eng.make_init(7, [3, 14])
+        assert torch.equal(pb.Ht[:, :7, :hi - lo].permute(0, 2, 1), H0[:, lo:hi]) and torch.equal(pb.Wall[:, :7, :g], W0)
+
+
+def test_fused_device_init_large_tensor_multiple_grid_strides():
+    """More elements than one pass of torch's capped grid (148 SMs x 8 blocks x 256 threads x 4): the grid-stride
+    loop runs twice and the Philox offset of the W draw moves accordingly."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    x = np.ones((160000, 64), dtype=np.float32)
+    eng = DenseFrobeniusEngine(x, init_device="cuda")
+    b = eng.new_batch(15, seeds=[7, 8])
+    H0, W0 = eng.make_init(15, [7, 8])
+    assert torch.equal(b.Ht[:, :15, :160000].permute(0, 2, 1), H0) and torch.equal(b.Wall[:, :15, :64], W0)
