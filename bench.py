@@ -316,7 +316,7 @@ def main():
                 # dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full`
                 # capture (profiles/r01_tc_half_step_stack_full_raw.csv): 160.3 + 57.8 MB; algorithmic bytes
                 # (X + W copy + H read + H and H-copy write) = 216 MB
-                "traffic": 218.1e6,
+                "traffic": 221.0e6,
                 "kernel": f"tc_half_step_kernel<{big.Kp},HALS> (H half-step, K={big.Ks}, R={big.R}, live update)",
                 "kernel_ms": k_ms, "padded_frac": ach / peak * big.Kp * big.R / cols,
                 "peak_source": f"{src} bf16 burst / 2 (tf32)"}
