@@ -314,7 +314,7 @@ def main():
         ach = flops / (k_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                 # dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full`
-                # capture (profiles/r01_tc_half_step_stack_full_raw.csv): 160.3 + 57.8 MB; algorithmic bytes
+                # capture (profiles/r01_tc_half_step_f_full_raw.csv): 161.5 + 59.5 MB; algorithmic bytes
                 # (X + W copy + H read + H and H-copy write) = 216 MB
                 "traffic": 221.0e6,
                 "kernel": f"tc_half_step_kernel<{big.Kp},HALS> (H half-step, K={big.Ks}, R={big.R}, live update)",
