@@ -117,3 +117,42 @@ def test_nndsvd_init_through_run_nmf(problem, beta):
     H, W, err = run_nmf(problem, use_gpu=True, **kw)
     ho, wo, eo = no.run_nmf_oracle(problem, **kw)
     assert abs(err - eo) / eo < 1e-3 and _pearson(W, wo) >= 0.999
+
+
+def test_kl_cut_rows_empty_rows_and_many_segments():
+    """Edge cases of the segment table: genes expressed in every cell (rows of CSR(X^T) cut into a dozen segments,
+    finished by kl_finish_rows_kernel), a gene and a cell without any count (empty rows in either orientation), rows
+    of exactly one segment length, and R not a divisor of the CTA size -- one iteration against the oracle's dense
+    formula, and bit-identical results when the same replicates run in batches of another size (another packing of
+    (segment, replicate) pairs over threads, another segment length)."""
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    rng = np.random.default_rng(7)
+    n, g = 3100, 90
+    x = (rng.poisson(0.3, size=(n, g)) * (rng.random((n, g)) < 0.4)).astype(np.float32)
+    x[:, 0] = rng.poisson(3.0, size=n) + 1          # expressed everywhere: 3100 entries in its CSR(X^T) row
+    x[:, 1] = rng.poisson(2.0, size=n) + 1
+    x[:, 2] = 0.0                                   # never expressed: empty row of CSR(X^T)
+    x[:256, 3] = 1.0; x[256:, 3] = 0.0              # exactly 256 entries
+    x[5, :] = 0.0; x[5, 0] = 0.0                    # a cell without counts: empty row of CSR(X)
+    x[5, :3] = 0.0
+    eng = SparseKLEngine(x)
+    K, seeds = 5, [1, 2, 3, 4, 5, 6, 7]
+    H0, W0 = eng.make_init(K, seeds)
+    b = eng.new_batch(K, H0=H0, W0=W0)
+    b.iterate(1)
+    W, H = b.results(True)
+    xt = torch.from_numpy(x)
+    for r in (0, 3, 6):
+        h = no.mu_kl_H(xt, H0[r], W0[r], 0.0, 0.0, 1e-16)
+        w = no.mu_kl_W(xt, h, W0[r], 0.0, 0.0, 1e-16)
+        np.testing.assert_allclose(H[r], h.numpy(), rtol=2e-3, atol=1e-6)
+        np.testing.assert_allclose(W[r], w.numpy(), rtol=2e-3, atol=1e-6)
+        assert np.all(W[r][:, 2] == 0.0) and np.all(H[r][5] == 0.0)       # nothing to explain: the rate is zero
+    # the objective after 10 iterations, and independence of the batch composition
+    full = eng.factorize(K, H0=H0, W0=W0, tol=0.0, max_iter=10, return_H=True)
+    part = eng.factorize(K, H0=H0[2:5], W0=W0[2:5], tol=0.0, max_iter=10, return_H=True)
+    for r in range(3):
+        ora = no.nmf_batch(x, H0[2 + r].numpy(), W0[2 + r].numpy(), beta_loss="kullback-leibler", tol=0.0, max_iter=10)
+        assert abs(part.trace[-1][1][r] - ora["trace"][-1][1]) / ora["trace"][-1][1] < 1e-3
+    np.testing.assert_allclose(full.W[2:5], part.W, rtol=1e-5, atol=1e-8)
+    np.testing.assert_allclose(full.err[2:5], part.err, rtol=1e-6)
