@@ -186,7 +186,42 @@ def _extras(dev):
     dt = time.perf_counter() - t0
     out["online_mu_3000x2000_K9_R100"] = {"s_per_3_passes": dt, "inner_iterations": res.inner_iterations,
                                           "replicate_passes_per_s": 300 / dt}
+    del e2
+    out["pipeline_cfg2"] = _pipeline_wall(dev)
     return out
+
+
+def _pipeline_wall(dev):
+    """BASELINE.json's second metric on cfg-2: wall time of factorize + combine + consensus through the cNMF mirror
+    (files and all): K = 7..12 x 100 replicates, frobenius HALS batch mode with the reference's tol (1e-4) and
+    stopping rule, then the consensus front half for every K."""
+    import shutil
+    import tempfile
+    import torch
+    from cnmf_torch_b200 import cnmf as host
+    from cnmf_torch_b200.synth import nb_counts
+    x = nb_counts(N_CELLS, N_GENES, seed=14)
+    tmp = tempfile.mkdtemp(prefix="cnmf_b200_bench_")
+    try:
+        obj = host.cNMF(output_dir=tmp, name="cfg2", device=str(dev))
+        obj.prepare_from_matrix(x, KS, n_iter=REPLICATES, seed=14, beta_loss="frobenius")
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        obj.factorize(nmf_kwargs_override=dict(mode="batch", algo=ALGO, batch_max_iter=500))
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        obj.combine()
+        t2 = time.perf_counter()
+        for k in KS:
+            obj.consensus(k, density_threshold=0.5, local_neighborhood_size=0.30)
+        torch.cuda.synchronize()
+        t3 = time.perf_counter()
+        return {"factorize_s": t1 - t0, "combine_s": t2 - t1, "consensus_s": t3 - t2, "total_s": t3 - t0,
+                "what": f"cNMF mirror on {N_CELLS}x{N_GENES}: factorize K={KS[0]}..{KS[-1]} x {REPLICATES} replicates "
+                        f"({ALGO}, batch, tol 1e-4, up to 500 iterations, {len(KS) * REPLICATES} spectra files written), "
+                        f"combine, consensus(k, 0.5, 0.30) for every K"}
+    finally:
+        shutil.rmtree(tmp, ignore_errors=True)
 
 
 def run_reference(args):
