@@ -123,6 +123,38 @@ __global__ void __launch_bounds__(GRAM_THREADS) gram_partial_kernel(const float*
 constexpr int GW_THREADS = 256;
 constexpr int GW_SPLIT = 8192;  // columns per CTA (smaller splits measured slower: the per-CTA reduction dominates)
 
+// Sum N per-lane values over the 32 lanes of a warp by recursive halving: at every step a lane keeps one half of
+// its vector and hands the other half to its partner (lane ^ O), so the five steps cost N/2 + N/4 + ... ~ N
+// shuffles instead of 5 N for N independent butterflies.  Afterwards lane L holds the totals of at most
+// ceil(N/32) original indices; `put(i, v)` is called for each of them.  Fixed tree: deterministic.
+template <int N, int O>
+struct WarpHalving {
+  static constexpr int H = (N + 1) / 2;
+  // a[0..cnt) are the values of original indices base .. base+cnt-1 (a[j] = 0 for j >= cnt)
+  template <typename Put>
+  static __device__ __forceinline__ void run(const float (&a)[N], int lane, int base, int cnt, Put put) {
+    const bool up = (lane & O) != 0;
+    float k[H];
+#pragma unroll
+    for (int j = 0; j < H; ++j) {
+      const float lo = a[j];
+      const float hi = (j + H < N) ? a[j + H] : 0.f;
+      k[j] = (up ? hi : lo) + __shfl_xor_sync(0xffffffffu, up ? lo : hi, O);
+    }
+    const int cnt_lo = cnt < H ? cnt : H;
+    WarpHalving<H, O / 2>::run(k, lane, up ? base + H : base, up ? cnt - cnt_lo : cnt_lo, put);
+  }
+};
+template <int N>
+struct WarpHalving<N, 0> {
+  template <typename Put>
+  static __device__ __forceinline__ void run(const float (&a)[N], int, int base, int cnt, Put put) {
+#pragma unroll
+    for (int j = 0; j < N; ++j)
+      if (j < cnt) put(base + j, a[j]);
+  }
+};
+
 template <int KP>
 __global__ void __launch_bounds__(GW_THREADS) gram_warp_kernel(const float* __restrict__ F, int64_t ld, int64_t L,
                                                                float* __restrict__ partial, int nsplit) {
@@ -150,11 +182,7 @@ __global__ void __launch_bounds__(GW_THREADS) gram_warp_kernel(const float* __re
 #pragma unroll
       for (int b = a; b < KP; ++b, ++t) acc[t] = fmaf(f1[a], f1[b], fmaf(f0[a], f0[b], acc[t]));
   }
-#pragma unroll
-  for (int i = 0; i < NT; ++i) {
-    const float v = warp_sum(acc[i]);
-    if (lane == 0) red[warp][i] = v;
-  }
+  WarpHalving<NT, 16>::run(acc, lane, 0, NT, [&](int i, float v) { red[warp][i] = v; });
   __syncthreads();
   for (int i = threadIdx.x; i < KP * KP; i += GW_THREADS) {
     const int a = i / KP, b = i - a * KP;
