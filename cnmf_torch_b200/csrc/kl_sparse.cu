@@ -84,20 +84,27 @@ __device__ __forceinline__ void kl_apply_update(float (&h)[KP], const float (&nu
   }
 }
 
-// Segment table of one CSR matrix (engine path, built on the device by kl_build_segments): rows longer than the segment length
-// entries are cut into segments of that length.  A gene expressed in every cell is a row of N entries in CSR(X^T); one
-// thread walking it alone (20 000 entries ~ 1.6 ms) set the duration of the whole gene-major half-step whatever R.
-// A thread then is a (segment, replicate) pair; segments of a cut row leave their KP numerators in `part` and
-// kl_finish_rows_kernel adds them in segment order (deterministic) and applies the update.
+// Segment table of one CSR matrix (engine path, built on the device by kl_build_segments).
+//  * Rows longer than the segment length are cut into segments of that length.  A gene expressed in every cell is
+//    a row of N entries in CSR(X^T); one thread walking it alone (20 000 entries ~ 1.6 ms) set the duration of the
+//    whole gene-major half-step whatever R.  A thread then is a (segment, replicate) pair; segments of a cut row leave
+//    their KP numerators in `part` and a finish pass adds them in segment order (deterministic) and applies the update.
+//  * Column blocks (nb > 1, the gene-major half-step of a large matrix): a row is first cut at multiples of `block`
+//    COLUMNS (cells), and segments are numbered block-major -- all rows' entries in cells [0, block) first, then
+//    [block, 2 block), ... -- so that the threads resident at one time gather rows of the fixed factor from one or two
+//    cell blocks (tens of MB, L2-resident) instead of from all cells (240 MB of fp16 H at 100 000 cells, R = 100:
+//    every gather a DRAM access).  "Virtual row" v = b * M + row; with nb = 1 it is the row itself.
 struct KlSegs {
-  const int* row_seg_ptr;   // [M + 1] first segment of each row
-  const int* row_slot_ptr;  // [M + 1] first partial slot of each row (rows with one segment own none)
-  const int* seg_row;       // [nseg]
+  const int* vseg_ptr;      // [V + 1] first segment of each virtual row, V = nb * M
+  const int* row_slot_ptr;  // [M + 1] nb == 1: first partial slot of each cut row (rows of one segment own none)
+  const int* seg_vrow;      // [nseg]
   const int* seg_beg;       // [nseg] first entry of the segment
-  const int* multi_rows;    // [n_multi] rows that were cut (any order)
+  const int* vend;          // [V] end of each virtual row's entries (nb == 1: row_ptr + 1)
+  const int* multi_rows;    // nb == 1: [n_multi] rows that were cut (any order)
   const int* n_multi;       // [1]
-  float* part;              // [slots x R*KP]
+  float* part;              // [slots x R*KP]; nb > 1: one slot per segment
   int seg_len;              // entries per segment
+  int nb;                   // column blocks
 };
 
 template <int KP, bool SEG>
@@ -112,13 +119,18 @@ __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
   int64_t row = unit;
   int beg, end, slot = -1;
   if (SEG) {
-    if (unit >= sg.row_seg_ptr[M]) return;
-    row = sg.seg_row[unit];
+    if (unit >= sg.vseg_ptr[M * sg.nb]) return;
+    const int v = sg.seg_vrow[unit];
+    row = sg.nb > 1 ? v % M : v;
     beg = sg.seg_beg[unit];
-    const int row_end = row_ptr[row + 1];
-    end = beg + sg.seg_len < row_end ? beg + sg.seg_len : row_end;
-    const int s0 = sg.row_seg_ptr[row];
-    if (sg.row_seg_ptr[row + 1] - s0 > 1) slot = sg.row_slot_ptr[row] + (int)(unit - s0);
+    const int v_end = sg.vend[v];
+    end = beg + sg.seg_len < v_end ? beg + sg.seg_len : v_end;
+    if (sg.nb > 1) {
+      slot = (int)unit;   // every row is finished by kl_finish_all_kernel
+    } else {
+      const int s0 = sg.vseg_ptr[v];
+      if (sg.vseg_ptr[v + 1] - s0 > 1) slot = sg.row_slot_ptr[v] + (int)(unit - s0);
+    }
   } else {
     if (row >= M) return;
     beg = row_ptr[row];
@@ -177,7 +189,7 @@ __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
                       state_h != nullptr ? state_h + row * rk + (int64_t)r * KP : nullptr);
 }
 
-// rows that were cut into segments: numerators = sum of the segments' partials in segment order
+// rows that were cut into segments (nb == 1): numerators = sum of the segments' partials in segment order
 template <int KP>
 __global__ void __launch_bounds__(KL_THREADS) kl_finish_rows_kernel(float* __restrict__ state, __half* __restrict__ state_h,
                                                                      const float* __restrict__ fsum,
@@ -190,7 +202,7 @@ __global__ void __launch_bounds__(KL_THREADS) kl_finish_rows_kernel(float* __res
   if (active != nullptr && active[r] == 0) return;
   const int64_t row = sg.multi_rows[mi];
   const int64_t rk = (int64_t)R * KP;
-  const int nseg = sg.row_seg_ptr[row + 1] - sg.row_seg_ptr[row];
+  const int nseg = sg.vseg_ptr[row + 1] - sg.vseg_ptr[row];
   const float* pp = sg.part + (int64_t)sg.row_slot_ptr[row] * rk + (int64_t)r * KP;
   float h[KP], num[KP], t[KP];
   load_vec<KP>(pp, num);
@@ -205,17 +217,68 @@ __global__ void __launch_bounds__(KL_THREADS) kl_finish_rows_kernel(float* __res
                       state_h != nullptr ? state_h + row * rk + (int64_t)r * KP : nullptr);
 }
 
-// ---- segment table construction (one CTA of 1024 threads scans the rows; M is at most a few million) ----------
-__global__ void __launch_bounds__(1024) kl_seg_scan_kernel(const int* __restrict__ row_ptr, int64_t M, int seg_len,
-                                                           int* __restrict__ row_seg_ptr, int* __restrict__ row_slot_ptr) {
+// column-blocked table (nb > 1): every row is finished here -- its segments of block 0, then block 1, ... in order
+template <int KP>
+__global__ void __launch_bounds__(KL_THREADS) kl_finish_all_kernel(int64_t M, float* __restrict__ state,
+                                                                    __half* __restrict__ state_h,
+                                                                    const float* __restrict__ fsum,
+                                                                    const uint8_t* __restrict__ active, int R, float l1,
+                                                                    float l2, float eps, const KlSegs sg) {
+  const int64_t g = (int64_t)blockIdx.x * KL_THREADS + threadIdx.x;
+  const int64_t row = g / R;
+  if (row >= M) return;
+  const int r = (int)(g - row * R);
+  if (active != nullptr && active[r] == 0) return;
+  const int64_t rk = (int64_t)R * KP;
+  float h[KP], num[KP], t[KP];
+#pragma unroll
+  for (int k = 0; k < KP; ++k) num[k] = 0.f;
+  for (int b = 0; b < sg.nb; ++b) {
+    const int64_t v = (int64_t)b * M + row;
+    for (int sgi = sg.vseg_ptr[v]; sgi < sg.vseg_ptr[v + 1]; ++sgi) {
+      load_vec<KP>(sg.part + (int64_t)sgi * rk + (int64_t)r * KP, t);
+#pragma unroll
+      for (int k = 0; k < KP; ++k) num[k] += t[k];
+    }
+  }
+  float* sp = state + row * rk + (int64_t)r * KP;
+  load_vec<KP>(sp, h);
+  kl_apply_update<KP>(h, num, fsum + (int64_t)r * KP, l1, l2, eps, sp,
+                      state_h != nullptr ? state_h + row * rk + (int64_t)r * KP : nullptr);
+}
+
+// ---- segment table construction -------------------------------------------------------------------------------
+// entries of row j with column in [b * block, (b+1) * block): vbeg / vend of virtual row b * M + j (columns sorted)
+__global__ void __launch_bounds__(256) kl_block_bounds_kernel(const int* __restrict__ row_ptr,
+                                                              const int* __restrict__ col_idx, int64_t M, int nb,
+                                                              int block, int* __restrict__ vbeg, int* __restrict__ vend) {
+  const int64_t g = (int64_t)blockIdx.x * 256 + threadIdx.x;   // (row, boundary b = 0 .. nb)
+  const int64_t row = g / (nb + 1);
+  if (row >= M) return;
+  const int b = (int)(g - row * (nb + 1));
+  int lo = row_ptr[row], hi = row_ptr[row + 1];
+  const int64_t key = (int64_t)b * block;
+  while (lo < hi) {   // first entry with column >= key
+    const int mid = (lo + hi) >> 1;
+    if (col_idx[mid] < key) lo = mid + 1; else hi = mid;
+  }
+  if (b < nb) vbeg[(int64_t)b * M + row] = lo;
+  if (b > 0) vend[(int64_t)(b - 1) * M + row] = lo;
+}
+
+// one CTA of 1024 threads scans the V virtual rows (a few million at most).  min_one: a row without entries still
+// gets a segment (nb == 1: its update, a zero rate, is applied by the half-step kernel itself)
+__global__ void __launch_bounds__(1024) kl_seg_scan_kernel(const int* __restrict__ vbeg, const int* __restrict__ vend,
+                                                           int64_t V, int seg_len, int min_one,
+                                                           int* __restrict__ vseg_ptr, int* __restrict__ row_slot_ptr) {
   __shared__ int s_seg[1024], s_slot[1024];
   const int t = threadIdx.x;
-  const int64_t chunk = (M + 1023) / 1024;
-  const int64_t lo = t * chunk, hi = lo + chunk < M ? lo + chunk : M;
+  const int64_t chunk = (V + 1023) / 1024;
+  const int64_t lo = t * chunk, hi = lo + chunk < V ? lo + chunk : V;
   int a = 0, b = 0;
   for (int64_t i = lo; i < hi; ++i) {
-    const int len = row_ptr[i + 1] - row_ptr[i];
-    const int c = len > seg_len ? (len + seg_len - 1) / seg_len : 1;
+    const int len = vend[i] - vbeg[i];
+    const int c = len > seg_len ? (len + seg_len - 1) / seg_len : (len > 0 || min_one ? 1 : 0);
     a += c;
     b += c > 1 ? c : 0;
   }
@@ -229,24 +292,28 @@ __global__ void __launch_bounds__(1024) kl_seg_scan_kernel(const int* __restrict
   }
   a = s_seg[t] - a; b = s_slot[t] - b;       // exclusive prefix of this thread's chunk
   for (int64_t i = lo; i < hi; ++i) {
-    row_seg_ptr[i] = a; row_slot_ptr[i] = b;
-    const int len = row_ptr[i + 1] - row_ptr[i];
-    const int c = len > seg_len ? (len + seg_len - 1) / seg_len : 1;
+    vseg_ptr[i] = a;
+    if (row_slot_ptr != nullptr) row_slot_ptr[i] = b;
+    const int len = vend[i] - vbeg[i];
+    const int c = len > seg_len ? (len + seg_len - 1) / seg_len : (len > 0 || min_one ? 1 : 0);
     a += c;
     b += c > 1 ? c : 0;
   }
-  if (t == 1023) { row_seg_ptr[M] = s_seg[1023]; row_slot_ptr[M] = s_slot[1023]; }
+  if (t == 1023) {
+    vseg_ptr[V] = s_seg[1023];
+    if (row_slot_ptr != nullptr) row_slot_ptr[V] = s_slot[1023];
+  }
 }
 
-__global__ void __launch_bounds__(256) kl_seg_fill_kernel(const int* __restrict__ row_ptr, int64_t M, int seg_len,
-                                                          const int* __restrict__ row_seg_ptr, int* __restrict__ seg_row,
+__global__ void __launch_bounds__(256) kl_seg_fill_kernel(const int* __restrict__ vbeg, int64_t V, int seg_len,
+                                                          const int* __restrict__ vseg_ptr, int* __restrict__ seg_vrow,
                                                           int* __restrict__ seg_beg, int* __restrict__ multi_rows,
                                                           int* __restrict__ n_multi) {
-  const int64_t row = (int64_t)blockIdx.x * 256 + threadIdx.x;
-  if (row >= M) return;
-  const int s0 = row_seg_ptr[row], n = row_seg_ptr[row + 1] - s0, beg = row_ptr[row];
-  for (int i = 0; i < n; ++i) { seg_row[s0 + i] = (int)row; seg_beg[s0 + i] = beg + i * seg_len; }
-  if (n > 1) multi_rows[atomicAdd(n_multi, 1)] = (int)row;   // list order is irrelevant to the result
+  const int64_t v = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (v >= V) return;
+  const int s0 = vseg_ptr[v], n = vseg_ptr[v + 1] - s0, beg = vbeg[v];
+  for (int i = 0; i < n; ++i) { seg_vrow[s0 + i] = (int)v; seg_beg[s0 + i] = beg + i * seg_len; }
+  if (multi_rows != nullptr && n > 1) multi_rows[atomicAdd(n_multi, 1)] = (int)v;   // list order is irrelevant
 }
 
 // sum over non-zeros of x * log(max(s, eps)) per replicate; fp64 partials per block of KLO_ROWS rows [nblk x R]
@@ -392,7 +459,8 @@ static int launch_to_half(const float* src, __half* dst, int64_t n, cudaStream_t
 }
 
 // sg == nullptr: one thread per (row, replicate) (the standalone entry point, which has no workspace for a
-// segment table); else one thread per (segment, replicate) + the pass that finishes the cut rows.
+// segment table); else one thread per (segment, replicate) + the pass that finishes the cut rows (nb == 1) or
+// every row (column-blocked table).
 static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t M, const __half* F, float* state,
                           __half* state_h, const float* fsum, const uint8_t* active, int R, int Kp, float l1, float l2,
                           float eps, cudaStream_t st, const KlSegs* sg = nullptr, int64_t nseg_max = 0,
@@ -409,7 +477,12 @@ static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t 
   CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, true><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
                            rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, *sg)));
   CNMF_LAUNCH_CHECK();
-  if (multi_max > 0) {
+  if (sg->nb > 1) {
+    const int64_t fb = ceil_div(M * R, KL_THREADS);
+    CNMF_DISPATCH_KP(Kp, (kl_finish_all_kernel<KP><<<(unsigned)fb, KL_THREADS, 0, st>>>(M, state, state_h, fsum, active,
+                                                                                         R, l1, l2, eps, *sg)));
+    CNMF_LAUNCH_CHECK();
+  } else if (multi_max > 0) {
     const int64_t fb = ceil_div(multi_max * R, KL_THREADS);
     CNMF_DISPATCH_KP(Kp, (kl_finish_rows_kernel<KP><<<(unsigned)fb, KL_THREADS, 0, st>>>(state, state_h, fsum, active, R,
                                                                                           l1, l2, eps, *sg)));
@@ -429,45 +502,82 @@ static int kl_seg_len(int64_t M, int64_t nnz, int R) {
   while (len < KL_SEG_MAX && len * 2 <= s) len *= 2;
   return len;
 }
+// Column block (in columns) of a matrix whose half-step gathers rows of a fixed factor with n_cols rows of R*Kp fp16
+// values: 0 (no blocking) while that factor fits the L2 budget, else the largest power of two such that two blocks
+// of it do (the resident threads straddle at most two blocks).
+constexpr int64_t KL_L2_BUDGET = 40ll << 20;
+static int kl_col_block(int64_t n_cols, int R, int Kp) {
+  static const int mode = [] { const char* e = getenv("CNMF_B200_KL_BLOCK"); return e ? atoi(e) : -1; }();  // dev knob
+  if (mode == 0) return 0;
+  const int64_t row_bytes = (int64_t)R * Kp * 2;
+  if (mode > 0) return mode < n_cols ? mode : 0;
+  if (n_cols * row_bytes <= KL_L2_BUDGET) return 0;
+  int64_t b = 1024;
+  while (2 * (b * 2) * row_bytes <= KL_L2_BUDGET) b *= 2;
+  return b < n_cols ? (int)b : 0;
+}
 // bounds of the table
-static int64_t kl_nseg_max(int64_t M, int64_t nnz, int seg) { return M + nnz / seg; }
+static int64_t kl_nseg_max(int64_t V, int64_t nnz, int seg) { return V + nnz / seg; }
 static int64_t kl_multi_max(int64_t nnz, int seg) { return nnz / seg; }            // rows longer than seg
-static int64_t kl_slot_max(int64_t nnz, int seg) { return 2 * (nnz / seg) + 2; }   // their segments
+static int64_t kl_slot_max(int64_t V, int64_t nnz, int seg, int nb) {              // partial slots
+  return nb > 1 ? kl_nseg_max(V, nnz, seg) : 2 * (nnz / seg) + 2;
+}
 
-struct KlSegLayout { int64_t off_rsp, off_rslot, off_srow, off_sbeg, off_multi, off_nmulti; };
+struct KlSegLayout {
+  int64_t off_vsp, off_rslot, off_svrow, off_sbeg, off_multi, off_nmulti, off_vbeg, off_vend;
+  int seg, block, nb;
+  int64_t V;
+};
 
-static int64_t kl_seg_layout(int64_t M, int64_t nnz, int seg, int64_t off, KlSegLayout* o) {
-  o->off_rsp = off; off += align_up((M + 1) * 4, 256);
-  o->off_rslot = off; off += align_up((M + 1) * 4, 256);
-  o->off_srow = off; off += align_up(kl_nseg_max(M, nnz, seg) * 4, 256);
-  o->off_sbeg = off; off += align_up(kl_nseg_max(M, nnz, seg) * 4, 256);
-  o->off_multi = off; off += align_up((kl_multi_max(nnz, seg) + 1) * 4, 256);
+static int64_t kl_seg_layout(int64_t M, int64_t n_cols, int64_t nnz, int R, int Kp, bool allow_blocks, int64_t off,
+                             KlSegLayout* o) {
+  o->seg = kl_seg_len(M, nnz, R);
+  o->block = allow_blocks ? kl_col_block(n_cols, R, Kp) : 0;
+  o->nb = o->block > 0 ? (int)ceil_div(n_cols, o->block) : 1;
+  o->V = M * o->nb;
+  o->off_vsp = off; off += align_up((o->V + 1) * 4, 256);
+  o->off_rslot = off; off += align_up((o->V + 1) * 4, 256);
+  o->off_svrow = off; off += align_up(kl_nseg_max(o->V, nnz, o->seg) * 4, 256);
+  o->off_sbeg = off; off += align_up(kl_nseg_max(o->V, nnz, o->seg) * 4, 256);
+  o->off_multi = off; off += align_up((kl_multi_max(nnz, o->seg) + 1) * 4, 256);
   o->off_nmulti = off; off += 256;
+  o->off_vbeg = off; if (o->nb > 1) off += align_up(o->V * 4, 256);
+  o->off_vend = off; if (o->nb > 1) off += align_up(o->V * 4, 256);
   return off;
 }
 
-static int kl_build_segments(const int* row_ptr, int64_t M, int seg, char* ws, const KlSegLayout& o, float* part,
-                             KlSegs* out, cudaStream_t st) {
-  int* rsp = reinterpret_cast<int*>(ws + o.off_rsp);
+static int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, char* ws, const KlSegLayout& o,
+                             float* part, KlSegs* out, cudaStream_t st) {
+  int* vsp = reinterpret_cast<int*>(ws + o.off_vsp);
   int* rslot = reinterpret_cast<int*>(ws + o.off_rslot);
-  int* srow = reinterpret_cast<int*>(ws + o.off_srow);
+  int* svrow = reinterpret_cast<int*>(ws + o.off_svrow);
   int* sbeg = reinterpret_cast<int*>(ws + o.off_sbeg);
   int* multi = reinterpret_cast<int*>(ws + o.off_multi);
   int* nmulti = reinterpret_cast<int*>(ws + o.off_nmulti);
+  const int* vbeg = row_ptr;
+  const int* vend = row_ptr + 1;
+  if (o.nb > 1) {
+    int* vb = reinterpret_cast<int*>(ws + o.off_vbeg);
+    int* ve = reinterpret_cast<int*>(ws + o.off_vend);
+    kl_block_bounds_kernel<<<(unsigned)ceil_div(M * (o.nb + 1), 256), 256, 0, st>>>(row_ptr, col_idx, M, o.nb, o.block,
+                                                                                     vb, ve);
+    CNMF_LAUNCH_CHECK();
+    vbeg = vb; vend = ve;
+  }
   CNMF_CUDA(cudaMemsetAsync(nmulti, 0, 4, st));
-  kl_seg_scan_kernel<<<1, 1024, 0, st>>>(row_ptr, M, seg, rsp, rslot);
+  kl_seg_scan_kernel<<<1, 1024, 0, st>>>(vbeg, vend, o.V, o.seg, o.nb > 1 ? 0 : 1, vsp, o.nb > 1 ? nullptr : rslot);
   CNMF_LAUNCH_CHECK();
-  kl_seg_fill_kernel<<<(unsigned)ceil_div(M, 256), 256, 0, st>>>(row_ptr, M, seg, rsp, srow, sbeg, multi, nmulti);
+  kl_seg_fill_kernel<<<(unsigned)ceil_div(o.V, 256), 256, 0, st>>>(vbeg, o.V, o.seg, vsp, svrow, sbeg,
+                                                                   o.nb > 1 ? nullptr : multi, nmulti);
   CNMF_LAUNCH_CHECK();
-  out->row_seg_ptr = rsp; out->row_slot_ptr = rslot; out->seg_row = srow; out->seg_beg = sbeg;
-  out->multi_rows = multi; out->n_multi = nmulti; out->part = part; out->seg_len = seg;
+  out->vseg_ptr = vsp; out->row_slot_ptr = rslot; out->seg_vrow = svrow; out->seg_beg = sbeg; out->vend = vend;
+  out->multi_rows = multi; out->n_multi = nmulti; out->part = part; out->seg_len = o.seg; out->nb = o.nb;
   return 0;
 }
 
 struct KlLayout {
   int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_cpart, off_opart, off_wh, off_hh, off_part, total;
-  KlSegLayout segX, segXt;
-  int seg_x, seg_xt;  // segment lengths of CSR(X) and CSR(X^T)
+  KlSegLayout segX, segXt;  // CSR(X): never column-blocked (gathers W, G rows); CSR(X^T): blocked over cells when H is large
   int nblk_obj;
 };
 
@@ -487,11 +597,11 @@ static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
   l.off_hh = off; off += align_up(p->n_cells * C * 2, 256);
   // segment tables of CSR(X) and CSR(X^T) and the partial numerators of cut rows (one buffer: the two half-steps
   // of an iteration run one after the other)
-  l.seg_x = kl_seg_len(p->n_cells, p->nnz, p->R);
-  l.seg_xt = kl_seg_len(p->n_genes, p->nnz, p->R);
-  off = kl_seg_layout(p->n_cells, p->nnz, l.seg_x, off, &l.segX);
-  off = kl_seg_layout(p->n_genes, p->nnz, l.seg_xt, off, &l.segXt);
-  l.off_part = off; off += align_up(kl_slot_max(p->nnz, l.seg_x < l.seg_xt ? l.seg_x : l.seg_xt) * C * 4, 256);
+  off = kl_seg_layout(p->n_cells, p->n_genes, p->nnz, p->R, p->Kp, false, off, &l.segX);
+  off = kl_seg_layout(p->n_genes, p->n_cells, p->nnz, p->R, p->Kp, true, off, &l.segXt);
+  const int64_t sx = kl_slot_max(l.segX.V, p->nnz, l.segX.seg, l.segX.nb);
+  const int64_t sxt = kl_slot_max(l.segXt.V, p->nnz, l.segXt.seg, l.segXt.nb);
+  l.off_part = off; off += align_up((sx > sxt ? sx : sxt) * C * 4, 256);
   l.total = off;
   return l;
 }
@@ -588,11 +698,11 @@ int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* s
   KlSegs sgX{}, sgXt{};
   float* part = reinterpret_cast<float*>(ws + l.off_part);
   if (n_iters > 0) {  // stateless: the tables are rebuilt per call (a few tiny kernels against >= 1 iteration)
-    CNMF_TRY(kl_build_segments(p->row_ptr, p->n_cells, l.seg_x, ws, l.segX, part, &sgX, st));
-    CNMF_TRY(kl_build_segments(p->t_row_ptr, p->n_genes, l.seg_xt, ws, l.segXt, part, &sgXt, st));
+    CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, &sgX, st));
+    CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, &sgXt, st));
   }
-  const int64_t nsX = kl_nseg_max(p->n_cells, p->nnz, l.seg_x), nsXt = kl_nseg_max(p->n_genes, p->nnz, l.seg_xt);
-  const int64_t mmX = kl_multi_max(p->nnz, l.seg_x), mmXt = kl_multi_max(p->nnz, l.seg_xt);
+  const int64_t nsX = kl_nseg_max(l.segX.V, p->nnz, l.segX.seg), nsXt = kl_nseg_max(l.segXt.V, p->nnz, l.segXt.seg);
+  const int64_t mmX = kl_multi_max(p->nnz, l.segX.seg), mmXt = kl_multi_max(p->nnz, l.segXt.seg);
   for (int it = 0; it < n_iters; ++it) {
     CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, nullptr, cpart, st));
     CNMF_TRY(launch_kl_half(p->row_ptr, p->col_idx, p->val, p->n_cells, Wh, p->Hr, Hh, wsum, p->active, p->R, p->Kp,

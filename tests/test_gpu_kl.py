@@ -156,3 +156,18 @@ def test_kl_cut_rows_empty_rows_and_many_segments():
         assert abs(part.trace[-1][1][r] - ora["trace"][-1][1]) / ora["trace"][-1][1] < 1e-3
     np.testing.assert_allclose(full.W[2:5], part.W, rtol=1e-5, atol=1e-8)
     np.testing.assert_allclose(full.err[2:5], part.err, rtol=1e-6)
+
+
+def test_kl_column_blocked_gene_major_pass_matches_oracle():
+    """The gene-major half-step of a large matrix walks CSR(X^T) cell block by cell block (so the rows of H gathered
+    by the threads resident at one time fit in L2) and finishes every gene from per-segment partials.  The block
+    size is chosen from the problem size when the library is first used; CNMF_B200_KL_BLOCK=128 forces 4-25 blocks
+    on the small problems of this file, which then must pass the same oracle comparisons."""
+    import os, subprocess, sys
+    if os.environ.get("CNMF_B200_KL_BLOCK"):
+        pytest.skip("already inside the forced-block run")
+    here = os.path.abspath(__file__)
+    rc = subprocess.run([sys.executable, "-m", "pytest", here, "-x", "-q", "-k",
+                         "single_iteration or trace_matches or cut_rows or convergence_freeze"],
+                        env=dict(os.environ, CNMF_B200_KL_BLOCK="128"), capture_output=True, text=True)
+    assert rc.returncode == 0, rc.stdout[-2000:] + rc.stderr[-2000:]
