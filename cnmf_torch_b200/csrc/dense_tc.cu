@@ -76,6 +76,7 @@ struct TcParams {
   unsigned int sk_epoch;
   int64_t sk_base;
   int sk_rem;
+  int helpers;  // 1: warps 0-3 join the epilogue of the CTA's last tile (whole-tile schedule, MU/HALS, CG = 1)
   int dbg;  // dev probes (CNMF_B200_TC_DEBUG)
   long long* prof;  // dev probe: clock64 stamps of CTA 0's first epilogue warp (CNMF_B200_TC_PROF = device pointer): 1 = main loop without MMAs, 2 = main loop without TMA loads
 };
@@ -169,6 +170,12 @@ __device__ __forceinline__ float to_tf32(float v) {  // round to nearest, ties a
 }
 template <int NT>
 __device__ __forceinline__ void epi_bar_sync() { asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory"); }
+// the epilogue barrier of a CTA's LAST tile, which warps 0-3 join (see `helpers`): NT epilogue threads + 128
+template <int NT>
+__device__ __forceinline__ void epi_bar_sync(bool with_helpers) {
+  if (with_helpers) asm volatile("bar.sync 2, %0;" ::"n"(NT + 128) : "memory");
+  else asm volatile("bar.sync 1, %0;" ::"n"(NT) : "memory");
+}
 
 // K-major operand tile, rows at 128-byte pitch, SWIZZLE_128B: SBO = 8 rows * 128 B, LBO unused,
 // descriptor version 1 (sm_100), layout type 2.
@@ -426,16 +433,25 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         __syncwarp();
       }
     }
-  } else if (warp >= 4) {
+  }
+  // The update of one tile is instruction-issue bound and takes about half a main loop; it hides behind the next
+  // tile's main loop except for the LAST tile of the CTA, when the producer, MMA and allocator warps have nothing
+  // left to do: they join that tile's epilogue as one more warpgroup (replicates dealt over EG + 1 groups).
+  const bool helpers = (CG == 1) && !sk && (ALGO < TC_MODE_STORE) && prm.helpers != 0;
+  if (warp >= 4 || helpers) {
     // ===================== epilogue (every CTA, its own 128 rows) =====================
     constexpr int EG = tc_epi_groups(KP), ET = 128 * EG;
+    const bool helper = warp < 4;
     const int q = warp & 3;         // TMEM lane quarter == warp % 4
-    const int eg = (warp - 4) >> 2;  // epilogue warpgroup: takes replicates rr = eg (mod EG)
-    const int et = threadIdx.x - 128;
+    const int eg = helper ? EG : (warp - 4) >> 2;  // epilogue warpgroup: takes replicates rr = eg (mod groups)
+    const int et = helper ? (1 << 30) : static_cast<int>(threadIdx.x) - 128;  // helpers skip the cooperative loops
     int lt = 0;
     TcWork work(prm, group_id, num_groups, num_tiles, num_kb, sk);
     int tile, kb0, kb1;
     for (; work.next(tile, kb0, kb1); ++lt) {
+      const bool last = helpers && tile + num_groups >= num_tiles;
+      if (helper && !last) continue;
+      const int egs = last ? EG + 1 : EG;   // warpgroups sharing this tile
       const int buf = lt & 1;
       const uint32_t tphase = (lt >> 1) & 1u;
       const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
@@ -492,7 +508,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const bool prof = prm.prof != nullptr && blockIdx.x == 0 && et == 0 && lt == 0;
       int pi = 0;
       if (prof) prm.prof[pi++] = clock64();
-      epi_bar_sync<ET>();
+      epi_bar_sync<ET>(last);
       if (ALGO == CNMF_B200_ALGO_HALS) {
         // reciprocals of the regularised diagonal, once per tile (these warps idle here while the main loop runs)
         for (int i = et; i < t * KP; i += ET) {
@@ -500,7 +516,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           const float gkk = sgram[rr * KP * KP + k * KP + k] + prm.l2;
           sginv[i] = (gkk < prm.eps) ? -1.f : __frcp_rn(gkk);
         }
-        epi_bar_sync<ET>();
+        epi_bar_sync<ET>(last);
       }
       mbar_wait(&tfull[buf], tphase);
       tc_fence_after();
@@ -530,7 +546,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
         for (int k = 0; k < KP; ++k) s[k] = in ? sp0[static_cast<int64_t>(k) * prm.lds] : 0.f;
       }
-      for (int rr = eg; rr < t; rr += EG) {
+      for (int rr = eg; rr < t; rr += egs) {
         const int r = r0 + rr;
         if (r >= prm.R) break;
         float p[KP];
@@ -540,8 +556,8 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         const int64_t soff = static_cast<int64_t>(r) * KP * prm.lds + m;
         float* sp = prm.state + soff;
         if (kPrefetch) {
-          if (rr + EG < t && r + EG < prm.R) {
-            const float* spn = sp + static_cast<int64_t>(KP) * EG * prm.lds;
+          if (rr + egs < t && r + egs < prm.R) {
+            const float* spn = sp + static_cast<int64_t>(KP) * egs * prm.lds;
 #pragma unroll
             for (int k = 0; k < KP; ++k) s_nxt[k] = in ? spn[static_cast<int64_t>(k) * prm.lds] : 0.f;
           }
@@ -607,10 +623,10 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // all tcgen05.ld of this buffer are complete: hand it back to the MMA warp (of the leader CTA)
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) {
+      if (lane == 0 && !helper) {   // (nobody waits for the last tile's buffer)
         if (CG == 2) mbar_arrive_cta(&tempty[buf], 0u); else mbar_arrive(&tempty[buf]);
       }
-      epi_bar_sync<ET>();
+      epi_bar_sync<ET>(last);
       for (int i = et; i < t * 2 && want_sums && m_tile < prm.num_m_tiles; i += ET) {
         const int rr = i >> 1, r = r0 + rr;
         if (r < prm.R) {
@@ -620,7 +636,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           prm.partials[(static_cast<int64_t>(m_tile) * prm.R + r) * 2 + (i & 1)] = v;
         }
       }
-      epi_bar_sync<ET>();  // sgram / sred / sact are rewritten by the next tile
+      epi_bar_sync<ET>(last);  // sgram / sred / sact are rewritten by the next tile
       if (prof) { prm.prof[pi++] = clock64(); prm.prof[63] = pi; }
     }
   }
@@ -919,6 +935,8 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
   prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
   static const int dbg = [] { const char* e = getenv("CNMF_B200_TC_DEBUG"); return e ? atoi(e) : 0; }();
   prm.dbg = dbg;
+  static const int helpers = [] { const char* e = getenv("CNMF_B200_TC_HELPERS"); return e ? atoi(e) : 1; }();
+  prm.helpers = helpers;
   { const char* e = getenv("CNMF_B200_TC_PROF"); prm.prof = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr; }
   const int64_t tiles = static_cast<int64_t>(plan.num_m_groups) * plan.num_n_tiles;  // per CTA group
   const int64_t slots = sms / plan.cg;
