@@ -371,13 +371,17 @@ __global__ void __launch_bounds__(KL_THREADS) kl_xlogs_kernel(const int* __restr
 // column sums of a [L x C] row-major array: per-CTA partials over 256-row slabs, then a fixed-order sum
 constexpr int CS_ROWS = 256;
 
+template <bool SQ>
 __global__ void __launch_bounds__(128) colsum_partial_kernel(const float* __restrict__ A, int64_t L, int64_t C,
                                                              float* __restrict__ partial) {
   const int64_t c = (int64_t)blockIdx.x * 128 + threadIdx.x;
   if (c >= C) return;
   const int64_t l0 = (int64_t)blockIdx.y * CS_ROWS, l1 = min(L, l0 + (int64_t)CS_ROWS);
   float acc = 0.f;
-  for (int64_t l = l0; l < l1; ++l) acc += A[l * C + c];
+  for (int64_t l = l0; l < l1; ++l) {
+    const float a = A[l * C + c];
+    acc = SQ ? fmaf(a, a, acc) : acc + a;   // SQ: column sums of squares (the L2 term of the objective)
+  }
   partial[(int64_t)blockIdx.y * C + c] = acc;
 }
 
@@ -395,7 +399,9 @@ __global__ void __launch_bounds__(128) colsum_final_kernel(const float* __restri
 __global__ void __launch_bounds__(256) kl_objective_kernel(double xlogx, double sumX, const double* __restrict__ partial,
                                                            int nblk, const double* __restrict__ hsum,
                                                            const double* __restrict__ wsum, int R, int Kp, float l1_H,
-                                                           float l1_W, double* __restrict__ err2) {
+                                                           float l1_W, const double* __restrict__ hsq,
+                                                           const double* __restrict__ wsq, float l2_H, float l2_W,
+                                                           double* __restrict__ err2) {
   // one CTA per replicate; fixed assignment of partials to threads and a fixed reduction tree: deterministic
   __shared__ double sx[8];
   const int r = blockIdx.x, lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -415,7 +421,13 @@ __global__ void __launch_bounds__(256) kl_objective_kernel(double xlogx, double 
     sw += b;
   }
   ss = warp_sum(ss); sh = warp_sum(sh); sw = warp_sum(sw);
-  if (lane == 0) err2[r] = 2.0 * (xlogx - xls - sumX + ss + (double)l1_H * sh + (double)l1_W * sw);
+  double q = 0.0;   // l2_H ||H_r||^2 + l2_W ||W_r||^2 (= 2 x the 0.5 l2 ||.||^2 terms)
+  if (hsq != nullptr) {
+    for (int k = lane; k < Kp; k += 32)
+      q += (double)l2_H * hsq[(int64_t)r * Kp + k] + (double)l2_W * wsq[(int64_t)r * Kp + k];
+    q = warp_sum(q);
+  }
+  if (lane == 0) err2[r] = 2.0 * (xlogx - xls - sumX + ss + (double)l1_H * sh + (double)l1_W * sw) + q;
 }
 
 // sum x and sum x log x over the stored values (constants of the KL objective), fp64, one CTA
@@ -439,10 +451,11 @@ __global__ void __launch_bounds__(1024) kl_constants_kernel(const float* __restr
 }
 
 static int launch_colsum(const float* A, int64_t L, int64_t C, float* out, double* out64, float* partial,
-                         cudaStream_t st) {
+                         cudaStream_t st, bool squares = false) {
   const int nslab = (int)ceil_div(L, CS_ROWS);
   dim3 grid((unsigned)ceil_div(C, 128), nslab);
-  colsum_partial_kernel<<<grid, 128, 0, st>>>(A, L, C, partial);
+  if (squares) colsum_partial_kernel<true><<<grid, 128, 0, st>>>(A, L, C, partial);
+  else colsum_partial_kernel<false><<<grid, 128, 0, st>>>(A, L, C, partial);
   CNMF_LAUNCH_CHECK();
   colsum_final_kernel<<<(unsigned)ceil_div(C, 128), 128, 0, st>>>(partial, nslab, C, out, out64);
   CNMF_LAUNCH_CHECK();
@@ -576,7 +589,7 @@ static int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, 
 }
 
 struct KlLayout {
-  int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_cpart, off_opart, off_wh, off_hh, off_part, total;
+  int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_wsq64, off_hsq64, off_cpart, off_opart, off_wh, off_hh, off_part, total;
   KlSegLayout segX, segXt;  // CSR(X): never column-blocked (gathers W, G rows); CSR(X^T): blocked over cells when H is large
   int nblk_obj;
 };
@@ -590,6 +603,8 @@ static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
   l.off_hsum = off; off += align_up(C * 4, 256);
   l.off_wsum64 = off; off += align_up(C * 8, 256);
   l.off_hsum64 = off; off += align_up(C * 8, 256);
+  l.off_wsq64 = off; off += align_up(C * 8, 256);
+  l.off_hsq64 = off; off += align_up(C * 8, 256);
   l.off_cpart = off; off += align_up(ceil_div(Lmax, CS_ROWS) * C * 4, 256);
   l.nblk_obj = (int)ceil_div(p->n_cells, KLO_ROWS);
   l.off_opart = off; off += align_up((int64_t)l.nblk_obj * p->R * 8, 256);
@@ -641,8 +656,16 @@ static int kl_objective_impl(const cnmf_b200_kl_problem* p, const KlLayout& l, c
   CNMF_DISPATCH_KP(p->Kp, (kl_xlogs_kernel<KP><<<grid, KL_THREADS, 0, st>>>(p->row_ptr, p->col_idx, p->val, p->n_cells,
                                                                               p->Hr, p->Wt, p->R, p->eps, opart)));
   CNMF_LAUNCH_CHECK();
+  double* wsq64 = nullptr;
+  double* hsq64 = nullptr;
+  if (p->l2_H != 0.f || p->l2_W != 0.f) {   // hsum / wsum (fp32 outputs) are scratch here: the next iteration recomputes them
+    wsq64 = reinterpret_cast<double*>(ws + l.off_wsq64);
+    hsq64 = reinterpret_cast<double*>(ws + l.off_hsq64);
+    CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, wsq64, cpart, st, true));
+    CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, hsq64, cpart, st, true));
+  }
   kl_objective_kernel<<<p->R, 256, 0, st>>>(p->xlogx, p->sumX, opart, l.nblk_obj, hsum64, wsum64, p->R, p->Kp, p->l1_H,
-                                           p->l1_W, p->err2);
+                                           p->l1_W, hsq64, wsq64, p->l2_H, p->l2_W, p->err2);
   CNMF_LAUNCH_CHECK();
   return 0;
 }

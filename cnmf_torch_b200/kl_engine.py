@@ -95,9 +95,6 @@ class SparseKLEngine:
 
 class KlBatch:
     def __init__(self, eng: SparseKLEngine, K, H0, W0, l1_H, l2_H, l1_W, l2_W, eps):
-        if l2_H or l2_W:
-            raise NotImplementedError("KL engine: the L2 term of the objective is not implemented (alpha with "
-                                      "l1_ratio < 1); cNMF passes alpha = 0")
         self.eng, self.K = eng, int(K)
         self.R, self.Kp = int(W0.shape[0]), pad4(K)
         if self.Kp > _lib.MAX_KP:

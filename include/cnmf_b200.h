@@ -252,7 +252,7 @@ typedef struct cnmf_b200_kl_problem {
   float l1_H, l2_H, l1_W, l2_W;
   float eps, pad0;
   double sumX, xlogx;        /* from cnmf_b200_kl_constants */
-  double* err2;              /* [R] out: 2 * (generalised KL divergence + L1 terms); may be NULL */
+  double* err2;              /* [R] out: 2 * (generalised KL divergence + L1 and 0.5*l2*||.||^2 terms); may be NULL */
   void* workspace;
   int64_t workspace_bytes;
 } cnmf_b200_kl_problem;

@@ -9,7 +9,7 @@ x = nb_counts(N, 2000, seed=14, libsize=400.0)
 eng = DenseFrobeniusEngine(x, init_device="cuda")
 def run(p):
     torch.cuda.synchronize(); t0 = time.perf_counter()
-    res = eng.factorize_online(K, seeds=list(range(1, R + 1)), tol=0.0, max_pass=p, chunk_size=5000, chunk_max_iter=1000)
+    res = eng.factorize_online(K, seeds=list(range(1, R + 1)), tol=0.0, max_pass=p, chunk_size=5000, chunk_max_iter=1000, inner_batch=int(os.environ.get("IB", "4")))
     torch.cuda.synchronize(); return time.perf_counter() - t0, res
 run(1)
 t2, r2 = run(2); t4, r4 = run(4)

@@ -171,3 +171,21 @@ def test_kl_column_blocked_gene_major_pass_matches_oracle():
                          "single_iteration or trace_matches or cut_rows or convergence_freeze"],
                         env=dict(os.environ, CNMF_B200_KL_BLOCK="128"), capture_output=True, text=True)
     assert rc.returncode == 0, rc.stdout[-2000:] + rc.stderr[-2000:]
+
+
+def test_kl_with_l1_and_l2_regularisation_matches_oracle(problem):
+    """alpha_usage / alpha_spectra reach run_nmf as pure L2 strengths (cNMF fixes l1_ratio = 0, cnmf.py:757-761):
+    update denominators and the 0.5 * l2 * ||.||^2 terms of the objective."""
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    eng = SparseKLEngine(problem)
+    reg = dict(l1_H=0.02, l2_H=0.1, l1_W=0.01, l2_W=0.3)
+    H0, W0 = eng.make_init(5, [3, 4])
+    res = eng.factorize(5, H0=H0, W0=W0, tol=0.0, max_iter=30, return_H=True, **reg)
+    for r in range(2):
+        ora = no.nmf_batch(problem, H0[r].numpy(), W0[r].numpy(), beta_loss="kullback-leibler", tol=0.0, max_iter=30,
+                           l1_h=reg["l1_H"], l2_h=reg["l2_H"], l1_w=reg["l1_W"], l2_w=reg["l2_W"])
+        for (it_o, obj_o), (it_g, obj_g) in zip(ora["trace"], res.trace):
+            assert it_o == it_g and abs(obj_g[r] - obj_o) / obj_o < 1e-3, (r, it_o, obj_g[r], obj_o)
+        assert _pearson(res.W[r], ora["W"]) >= 0.999 and _pearson(res.H[r], ora["H"]) >= 0.999
+    plain = eng.factorize(5, H0=H0, W0=W0, tol=0.0, max_iter=30)
+    assert np.all(res.trace[-1][1] != plain.trace[-1][1])      # the terms are really there
