@@ -229,10 +229,7 @@ class cNMF:
             res = engine.factorize_many(list(groups), {k: [int(s) for s in g["nmf_seed"]] for k, g in groups.items()},
                                         algo=engine_kw.get("algo", "mu"), tol=engine_kw.get("tol", 1e-4),
                                         max_iter=int(engine_kw.get("batch_max_iter", 500)), **reg)
-            _save_spectra_files(
-                (self.paths["iter_spectra"] % (k, int(p["iter"])),
-                 pd.DataFrame(res[k].W[j], index=np.arange(1, k + 1), columns=var_names))
-                for k, g in groups.items() for j, (_, p) in enumerate(g.iterrows()))
+            self._write_spectra(res, groups, var_names, whole_ledger=len(sel) == len(run_params))
             return
         if (kw.get("mode", "batch") == "online" and hasattr(engine, "factorize_online_many") and not max_batch
                 and engine_kw.get("init", "random") == "random"):
@@ -249,10 +246,7 @@ class cNMF:
                 chunk_size=int(engine_kw.get("online_chunk_size", 5000)),
                 chunk_max_iter=int(engine_kw.get("online_chunk_max_iter", 200)),
                 h_tol=engine_kw.get("online_h_tol", 0.05), w_tol=engine_kw.get("online_w_tol", 0.05), **reg)
-            _save_spectra_files(
-                (self.paths["iter_spectra"] % (k, int(p["iter"])),
-                 pd.DataFrame(res[k].W[j], index=np.arange(1, k + 1), columns=var_names))
-                for k, g in groups.items() for j, (_, p) in enumerate(g.iterrows()))
+            self._write_spectra(res, groups, var_names, whole_ledger=len(sel) == len(run_params))
             return
         for k, grp in sel.groupby("n_components", sort=True):
             k = int(k)
@@ -267,6 +261,44 @@ class cNMF:
                     (self.paths["iter_spectra"] % (k, int(p["iter"])),
                      pd.DataFrame(res.W[j], index=np.arange(1, k + 1), columns=var_names))
                     for j, (_, p) in enumerate(part.iterrows()))
+
+    def _write_spectra(self, res, groups, var_names, whole_ledger):
+        """Per-replicate ``spectra.k_%d.iter_%d.df.npz`` files (cnmf.py:889-892) on host threads, and -- SURVEY 8 row
+        f4 -- when this call holds EVERY replicate of a K (one worker, nothing skipped), that K's merged file as
+        ``combine_nmf`` would build it (cnmf.py:895-920: rows in ``iter`` order, labels ``iter%d_topic%d``) straight
+        from memory; ``combine`` then finds it up to date instead of re-reading the replicate files."""
+        jobs = [(self.paths["iter_spectra"] % (k, int(p["iter"])),
+                 pd.DataFrame(res[k].W[j], index=np.arange(1, k + 1), columns=var_names))
+                for k, g in groups.items() for j, (_, p) in enumerate(g.iterrows())]
+        merged = []
+        if whole_ledger:
+            for k, g in groups.items():
+                order = np.argsort(g["iter"].values, kind="stable")
+                its = g["iter"].values[order]
+                data = np.concatenate([res[k].W[j] for j in order], axis=0)
+                index = ["iter%d_topic%d" % (it, t + 1) for it in its for t in range(k)]
+                merged.append((self.paths["merged_spectra"] % k, pd.DataFrame(data, index=index, columns=var_names)))
+        with _io_pool() as pool:
+            first = [pool.submit(save_df_to_npz, df, fn) for fn, df in jobs]
+            for f in first:
+                f.result()
+            # merged files strictly after their replicate files: combine's up-to-date test compares mtimes
+            for f in [pool.submit(save_df_to_npz, df, fn) for fn, df in merged]:
+                f.result()
+
+    def _merged_is_current(self, k, subset):
+        """The merged file of k exists, has one block of k rows per ledger replicate and is not older than any of
+        their files (it was written by ``factorize`` from the same results, or by an earlier ``combine``)."""
+        fn = self.paths["merged_spectra"] % k
+        if not os.path.exists(fn):
+            return False
+        t = os.path.getmtime(fn)
+        for _, p in subset.iterrows():
+            f = self.paths["iter_spectra"] % (p["n_components"], p["iter"])
+            if not os.path.exists(f) or os.path.getmtime(f) > t:
+                return False
+        with np.load(fn, allow_pickle=True) as z:
+            return z["data"].shape[0] == k * len(subset)
 
     # ---- combine (cnmf.py:599-620, 895-920) -------------------------------------------------------
     def combine(self, components=None, skip_missing_files=False):
@@ -286,6 +318,9 @@ class cNMF:
         run_params = load_df_from_npz(self.paths["nmf_replicate_parameters"])
         print("Combining factorizations for k=%d." % k)
         subset = run_params[run_params.n_components == k].sort_values("iter")
+        if self._merged_is_current(k, subset):
+            print("Merged spectra for k=%d are up to date." % k)
+            return load_df_from_npz(self.paths["merged_spectra"] % k)
         combined, present = [], []
         for _, p in subset.iterrows():
             fn = self.paths["iter_spectra"] % (p["n_components"], p["iter"])

@@ -39,7 +39,7 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
     st = torch.cuda.current_stream().cuda_stream
     ldg = pad4(g)
     Wd = torch.zeros((Kp, ldg), device=dev, dtype=torch.float32)
-    Wd[:k, :g] = torch.from_numpy(W).to(dev)
+    Wd[:k, :g] = torch.from_numpy(np.array(W, dtype=np.float32, copy=True)).to(dev)   # (W may be a read-only view)
     if H_init is None:
         gen = torch.Generator(device="cpu")
         if seed is not None:

@@ -66,3 +66,31 @@ def test_cli_verbs(tmp_path, counts):
     subprocess.run(base + ["consensus"] + common + ["-k", "3", "--local-density-threshold", "2.0"], check=True, env=env)
     assert os.path.exists(obj.paths["merged_spectra"] % 3)
     assert os.path.exists(obj.paths["consensus_spectra__txt"] % (3, "2_0"))
+
+
+def test_factorize_writes_merged_spectra_identical_to_combine(tmp_path, counts):
+    """a single worker that ran every replicate writes each K's merged file itself; it must be the
+    file combine_nmf builds from the per-replicate files (cnmf.py:895-920), and combine must rebuild it as soon as a
+    replicate file is newer."""
+    from cnmf_torch_b200 import cnmf as host
+    obj = host.cNMF(output_dir=str(tmp_path), name="m")
+    obj.prepare_from_matrix(counts, [3, 4], n_iter=5, seed=14, beta_loss="frobenius")
+    obj.factorize(nmf_kwargs_override=dict(mode="batch", batch_max_iter=30))
+    direct = {k: host.load_df_from_npz(obj.paths["merged_spectra"] % k) for k in (3, 4)}
+    stamp = os.path.getmtime(obj.paths["merged_spectra"] % 3)
+    obj.combine()                                                  # up to date: untouched
+    assert os.path.getmtime(obj.paths["merged_spectra"] % 3) == stamp
+    for k in (3, 4):
+        os.remove(obj.paths["merged_spectra"] % k)
+    obj.combine()                                                  # rebuilt from the replicate files
+    for k in (3, 4):
+        rebuilt = host.load_df_from_npz(obj.paths["merged_spectra"] % k)
+        assert list(rebuilt.index) == list(direct[k].index) and list(rebuilt.columns) == list(direct[k].columns)
+        assert np.array_equal(rebuilt.values, direct[k].values) and rebuilt.values.dtype == direct[k].values.dtype
+    # a replicate re-run later makes the merged file stale
+    os.remove(obj.paths["iter_spectra"] % (3, 2))
+    obj.update_nmf_iter_params()
+    obj.factorize(skip_completed_runs=True, nmf_kwargs_override=dict(mode="batch", batch_max_iter=30))
+    assert not obj._merged_is_current(3, host.load_df_from_npz(obj.paths["nmf_replicate_parameters"]).query("n_components == 3"))
+    obj.combine(components=3)
+    assert obj._merged_is_current(3, host.load_df_from_npz(obj.paths["nmf_replicate_parameters"]).query("n_components == 3"))
