@@ -3,9 +3,9 @@ per-replicate ``run_nmf`` loop replaced by the replicate-batched B200 engine and
 half replaced by the consensus kernel set.  Method names, arguments, file names and file formats
 follow /root/reference/src/cnmf/cnmf.py (cited per method) so the two are interchangeable on disk.
 
-Not re-implemented (out of scope / "next" rows): ``prepare`` with HVG selection
-and TPM statistics, the usage refits and OLS z-scores of the consensus back half, plotting.
-``prepare_from_matrix`` is the thin entry that writes the same three inputs ``factorize`` reads.
+Not re-implemented (out of scope): ``prepare`` with HVG selection, plotting, the starCAT
+reference.  ``prepare_from_matrix`` is the thin entry that writes the same inputs ``factorize`` and ``consensus``
+read (normalised counts, ledger, kwargs, gene list and -- optionally -- the TPM matrix with its statistics).
 """
 from __future__ import annotations
 
@@ -92,6 +92,15 @@ class cNMF:
             "local_density_cache": os.path.join(tmp, n + ".local_density_cache.k_%d.merged.df.npz"),
             "consensus_spectra": os.path.join(tmp, n + ".spectra.k_%d.dt_%s.consensus.df.npz"),
             "consensus_spectra__txt": os.path.join(base, n + ".spectra.k_%d.dt_%s.consensus.txt"),
+            "consensus_usages": os.path.join(tmp, n + ".usages.k_%d.dt_%s.consensus.df.npz"),
+            "consensus_usages__txt": os.path.join(base, n + ".usages.k_%d.dt_%s.consensus.txt"),
+            "gene_spectra_score": os.path.join(tmp, n + ".gene_spectra_score.k_%d.dt_%s.df.npz"),
+            "gene_spectra_score__txt": os.path.join(base, n + ".gene_spectra_score.k_%d.dt_%s.txt"),
+            "gene_spectra_tpm": os.path.join(tmp, n + ".gene_spectra_tpm.k_%d.dt_%s.df.npz"),
+            "gene_spectra_tpm__txt": os.path.join(base, n + ".gene_spectra_tpm.k_%d.dt_%s.txt"),
+            "tpm": os.path.join(tmp, n + ".tpm.h5ad"),
+            "tpm_npz": os.path.join(tmp, n + ".tpm.npz"),                        # side channel, as for the norm counts
+            "tpm_stats": os.path.join(tmp, n + ".tpm_stats.df.npz"),
         }
 
     # ---- inputs --------------------------------------------------------------------------------
@@ -123,9 +132,38 @@ class cNMF:
             X = sp.csr_matrix((f["data"], f["indices"], f["indptr"]), shape=tuple(f["shape"]))
             return X, f["obs"], f["var"]
 
+    def save_tpm(self, tpm, obs_names=None, var_names=None):
+        """What ``prepare`` leaves for the consensus back half (cnmf.py:545-580): the TPM matrix over ALL genes and
+        its per-gene mean / population standard deviation (``tpm_stats``, columns ``__mean`` / ``__std``)."""
+        T = sp.csr_matrix(tpm) if not sp.issparse(tpm) else tpm.tocsr()
+        obs_names = np.arange(T.shape[0]).astype(str) if obs_names is None else np.asarray(obs_names).astype(str)
+        var_names = np.arange(T.shape[1]).astype(str) if var_names is None else np.asarray(var_names).astype(str)
+        np.savez_compressed(self.paths["tpm_npz"], data=T.data, indices=T.indices, indptr=T.indptr,
+                            shape=np.array(T.shape), obs=obs_names, var=var_names)
+        mean = np.asarray(T.mean(axis=0)).ravel()
+        sq = np.asarray(T.multiply(T).mean(axis=0)).ravel()
+        std = np.sqrt(np.maximum(sq - mean ** 2, 0.0))                        # ddof = 0 (cnmf.py:571-575)
+        save_df_to_npz(pd.DataFrame([mean, std], index=["__mean", "__std"], columns=var_names).T, self.paths["tpm_stats"])
+
+    def load_tpm(self):
+        """-> (TPM csr, obs_names, var_names) or None when ``prepare`` left no TPM matrix."""
+        if os.path.exists(self.paths["tpm"]):
+            try:
+                import anndata as ad
+                a = ad.read_h5ad(self.paths["tpm"])
+                return sp.csr_matrix(a.X), np.asarray(a.obs.index), np.asarray(a.var.index)
+            except ImportError:
+                pass
+        if not os.path.exists(self.paths["tpm_npz"]):
+            return None
+        with np.load(self.paths["tpm_npz"], allow_pickle=False) as f:
+            T = sp.csr_matrix((f["data"], f["indices"], f["indptr"]), shape=tuple(f["shape"]))
+            return T, f["obs"], f["var"]
+
     def prepare_from_matrix(self, norm_counts, components, n_iter=100, seed=None, beta_loss="frobenius",
                             obs_names=None, var_names=None, alpha_usage=0.0, alpha_spectra=0.0,
-                            init="random", total_workers=-1, use_gpu=True, batch_size=5000, max_iter=1000):
+                            init="random", total_workers=-1, use_gpu=True, batch_size=5000, max_iter=1000,
+                            tpm=None, tpm_var_names=None):
         """Writes what ``prepare`` leaves for ``factorize`` (cnmf.py:590-596): normalised counts, the
         replicate ledger and the run_nmf kwargs.  ``norm_counts`` is the already variance-scaled HVG
         matrix (cells x genes); zero-count cells are refused like cnmf.py:688-691."""
@@ -135,6 +173,10 @@ class cNMF:
                             "cells and re-run or adjust the number of overdispersed genes. Quitting!"
                             % (int((np.asarray(X.sum(axis=1)).ravel() == 0).sum()), "see matrix rows"))
         self.save_norm_counts(X, obs_names, var_names)
+        if tpm is not None:   # enables the TPM / z-score outputs of ``consensus`` (cnmf.py:1124-1133)
+            self.save_tpm(tpm, obs_names, tpm_var_names)
+        with open(self.paths["nmf_genes_list"], "w") as F:                    # cnmf.py:684-685
+            F.write("\n".join(np.arange(X.shape[1]).astype(str) if var_names is None else np.asarray(var_names).astype(str)))
         rp, kw = self.get_nmf_iter_params(ks=components, n_iter=n_iter, random_state_seed=seed,
                                           beta_loss=beta_loss, alpha_usage=alpha_usage,
                                           alpha_spectra=alpha_spectra, init=init, total_workers=total_workers,
@@ -364,12 +406,16 @@ class cNMF:
     # ---- consensus, front half (cnmf.py:997-1090) -------------------------------------------------
     def consensus(self, k, density_threshold=0.5, local_neighborhood_size=0.30, show_clustering=False,
                   build_ref=False, skip_density_and_return_after_stats=False, close_clustergram_fig=False,
-                  refit_usage=False, normalize_tpm_spectra=False, norm_counts=None):
-        """L2-normalise the merged spectra, local-density filter, KMeans(k, n_init=10, random_state=1),
-        per-cluster median, row-normalise -- cnmf.py:1045-1090 -- on the GPU.  Writes the
-        ``local_density_cache`` (cnmf.py:1073) and the ``consensus_spectra`` files (cnmf.py:1151-1152 for
-        the spectra part) and returns (median_spectra DataFrame, labels Series, local_density DataFrame).
-        The usage refits / TPM spectra / plots that follow in the reference are outside this path."""
+                  refit_usage=True, normalize_tpm_spectra=False, norm_counts=None, seed=None):
+        """cnmf.py:997-1160.  Front half on the GPU: L2-normalise the merged spectra, local-density filter,
+        KMeans(k, n_init=10, random_state=1), per-cluster median, row-normalise (writes the ``local_density_cache``,
+        cnmf.py:1073).  Back half (rows f1/f2): usages refitted against the consensus spectra on the normalised
+        counts, programs reordered by total usage, and -- when ``prepare`` left a TPM matrix (``save_tpm``) --
+        spectra in TPM units (``refit_spectra``), z-score spectra (OLS of the z-scored TPM against the usages) and,
+        with ``refit_usage``, a final usage refit on the std-scaled HVG TPM; files as the reference names them
+        (cnmf.py:1151-1160).  ``seed`` (an addition): the reference's three refits start from unseeded
+        ``torch.rand``; an int seeds one generator they draw from in the same order.  Returns (consensus spectra
+        DataFrame, labels Series, local_density DataFrame); plots and the starCAT reference are outside this path."""
         from .consensus import consensus_front_half
         merged = load_df_from_npz(self.paths["merged_spectra"] % k)
         dt_str = "2" if skip_density_and_return_after_stats else str(density_threshold)
@@ -401,8 +447,61 @@ class cNMF:
         labels = pd.Series(out["labels"], index=kept_index)
         median = pd.DataFrame(out["median_spectra"], index=np.arange(1, k + 1), columns=merged.columns)
         median.index.name = None
-        save_df_to_npz(median, self.paths["consensus_spectra"] % (k, dt_repl))
+
+        # ---- back half ---------------------------------------------------------------------------------------
+        import torch
+        gen = None
+        if seed is not None:
+            gen = torch.Generator(device="cpu")
+            gen.manual_seed(int(seed))
+        if norm_counts is not None:
+            Xn, obs_names = norm_counts, np.arange(norm_counts.shape[0]).astype(str)
+        else:
+            Xn, obs_names, _ = self.load_norm_counts()
+        rf_usages = pd.DataFrame(self.refit_usage(Xn, median.values, seed=gen), index=obs_names,
+                                 columns=median.index)                                       # cnmf.py:1093-1094
+        norm_usages = rf_usages.div(rf_usages.sum(axis=1), axis=0)                           # cnmf.py:1113-1120
+        reorder = norm_usages.sum(axis=0).sort_values(ascending=False)
+        rf_usages = rf_usages.loc[:, reorder.index]
+        norm_usages = norm_usages.loc[:, reorder.index]
+        median = median.loc[reorder.index, :]
+        rf_usages.columns = np.arange(1, rf_usages.shape[1] + 1)
+        norm_usages.columns = rf_usages.columns
+        median.index = rf_usages.columns
+        tpm = self.load_tpm()
+        if tpm is not None:
+            T, _, tpm_var = tpm
+            from .stats import efficient_ols_all_cols
+            tpm_stats = load_df_from_npz(self.paths["tpm_stats"])
+            spectra_tpm = pd.DataFrame(self.refit_spectra(T, norm_usages.values, seed=gen), index=rf_usages.columns,
+                                       columns=tpm_var)                                      # cnmf.py:1126-1127
+            if normalize_tpm_spectra:
+                spectra_tpm = spectra_tpm.div(spectra_tpm.sum(axis=1), axis=0) * 1e6
+            usage_coef = pd.DataFrame(efficient_ols_all_cols(rf_usages.values, T, normalize_y=True, device=self.device),
+                                      index=rf_usages.columns, columns=tpm_var)              # cnmf.py:1132-1133
+            if refit_usage:
+                # final refit on the std-scaled (ddof = 1, not centred) HVG columns of the TPM matrix, cnmf.py:1135-1149
+                hvgs = open(self.paths["nmf_genes_list"]).read().split("\n")
+                pos = pd.Index(tpm_var).get_indexer(hvgs)
+                Th = sp.csc_matrix(T)[:, pos].astype(np.float64)
+                n_c = Th.shape[0]
+                mean = np.asarray(Th.mean(axis=0)).ravel()
+                var = (np.asarray(Th.multiply(Th).mean(axis=0)).ravel() - mean ** 2) * (n_c / max(n_c - 1, 1))
+                std = np.sqrt(np.maximum(var, 0.0))
+                std[std == 0] = 1.0                                  # scanpy's scale leaves constant genes alone
+                norm_tpm = sp.csr_matrix(Th.multiply(1.0 / std))
+                spectra_tpm_rf = spectra_tpm.loc[:, hvgs].div(tpm_stats.loc[hvgs, "__std"], axis=1)
+                rf_usages = pd.DataFrame(self.refit_usage(norm_tpm, spectra_tpm_rf.values, seed=gen), index=obs_names,
+                                         columns=spectra_tpm_rf.index)
+        save_df_to_npz(median, self.paths["consensus_spectra"] % (k, dt_repl))                # cnmf.py:1151-1160
+        save_df_to_npz(rf_usages, self.paths["consensus_usages"] % (k, dt_repl))
         save_df_to_text(median, self.paths["consensus_spectra__txt"] % (k, dt_repl))
+        save_df_to_text(rf_usages, self.paths["consensus_usages__txt"] % (k, dt_repl))
+        if tpm is not None:
+            save_df_to_npz(spectra_tpm, self.paths["gene_spectra_tpm"] % (k, dt_repl))
+            save_df_to_text(spectra_tpm, self.paths["gene_spectra_tpm__txt"] % (k, dt_repl))
+            save_df_to_npz(usage_coef, self.paths["gene_spectra_score"] % (k, dt_repl))
+            save_df_to_text(usage_coef, self.paths["gene_spectra_score__txt"] % (k, dt_repl))
         return median, labels, local_density
 
 

@@ -41,11 +41,14 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
     Wd = torch.zeros((Kp, ldg), device=dev, dtype=torch.float32)
     Wd[:k, :g] = torch.from_numpy(np.array(W, dtype=np.float32, copy=True)).to(dev)   # (W may be a read-only view)
     if H_init is None:
-        gen = torch.Generator(device="cpu")
-        if seed is not None:
-            gen.manual_seed(int(seed))
+        if isinstance(seed, torch.Generator):
+            gen = seed                    # a caller's generator: consecutive refits continue one stream
         else:
-            gen.seed()
+            gen = torch.Generator(device="cpu")
+            if seed is not None:
+                gen.manual_seed(int(seed))
+            else:
+                gen.seed()
         h0 = torch.rand((n, k), generator=gen, dtype=torch.float32)
     else:
         h0 = torch.from_numpy(np.asarray(H_init, dtype=np.float32)).clamp(min=0.0)   # cnmf.py:345

@@ -69,12 +69,80 @@ def make_ols(ref):
     print("ols golden:", {k_: getattr(v_, "shape", None) for k_, v_ in out.items()})
 
 
+class _FakeVarObs:
+    def __init__(self, index):
+        self.index = pd.Index(index)
+
+
+class _FakeAnnData:
+    """The attributes cNMF.consensus touches on sc.read(...) results: X, obs.index, var.index, [:, genes]."""
+    def __init__(self, X, obs, var):
+        self.X, self.obs, self.var = X, _FakeVarObs(obs), _FakeVarObs(var)
+
+    def __getitem__(self, key):
+        rows, cols = key
+        assert rows == slice(None)
+        pos = self.var.index.get_indexer(list(cols))
+        return _FakeAnnData(np.array(self.X[:, pos], copy=True), self.obs.index, list(cols))
+
+
+def make_backhalf(ref, tmp):
+    """The reference's whole cNMF.consensus (front half + usage refit, reordering, TPM spectra, z-score spectra, final
+    usage refit; cnmf.py:997-1160) on a small dense problem, with torch seeded so that the three unseeded
+    torch.rand inits of fit_H_online are reproducible."""
+    import torch
+    rng = np.random.default_rng(21)
+    n, g_all, k, n_rep = 260, 140, 4, 18
+    hv_pos = np.sort(rng.choice(g_all, 70, replace=False))
+    genes_all = np.array([f"g{i}" for i in range(g_all)])
+    hvgs = list(genes_all[hv_pos])
+    cells = np.array([f"c{i}" for i in range(n)])
+    progs = rng.gamma(0.4, 1.0, size=(k, g_all)) + 1e-2
+    usage = rng.dirichlet(np.full(k, 0.4), size=n)
+    counts = rng.poisson(usage @ progs * 30.0).astype(np.float64)
+    counts[counts.sum(1) == 0, 0] = 1.0
+    tpm = counts / counts.sum(1, keepdims=True) * 1e6
+    norm = counts[:, hv_pos] / counts[:, hv_pos].std(axis=0, ddof=1)
+    spectra = synth_spectra(k, n_rep, len(hvgs), seed=8)
+    obj = ref.cNMF(output_dir=tmp, name="back")
+    rp, kw = obj.get_nmf_iter_params([k], n_iter=n_rep, random_state_seed=14, beta_loss="frobenius", batch_size=100)
+    obj.save_nmf_iter_params(rp, kw)
+    idx = [f"iter{i // k}_topic{i % k + 1}" for i in range(spectra.shape[0])]
+    ref.save_df_to_npz(pd.DataFrame(spectra, index=idx, columns=hvgs), obj.paths["merged_spectra"] % k)
+    with open(obj.paths["nmf_genes_list"], "w") as F:
+        F.write("\n".join(hvgs))
+    stats = pd.DataFrame([tpm.mean(axis=0), tpm.std(axis=0, ddof=0)], index=["__mean", "__std"], columns=genes_all).T
+    ref.save_df_to_npz(stats, obj.paths["tpm_stats"])
+    fake = {obj.paths["normalized_counts"]: _FakeAnnData(norm, cells, hvgs),
+            obj.paths["tpm"]: _FakeAnnData(tpm, cells, genes_all)}
+    ref.sc.read = lambda path, *_a, **_k: fake[path]
+    out = {}
+    for tag, flags in {"refit": dict(refit_usage=True), "norefit": dict(refit_usage=False, normalize_tpm_spectra=True)}.items():
+        torch.manual_seed(77)
+        obj.consensus(k, density_threshold=0.5, local_neighborhood_size=0.30, show_clustering=False, build_ref=False,
+                      **flags)
+        dt = "0_5"
+        for key in ("consensus_spectra", "consensus_usages", "gene_spectra_tpm", "gene_spectra_score"):
+            df = ref.load_df_from_npz(obj.paths[key] % (k, dt))
+            out[f"{tag}_{key}"] = df.values
+            out[f"{tag}_{key}_index"] = np.array(list(df.index), dtype=str)
+            out[f"{tag}_{key}_columns"] = np.array(list(df.columns), dtype=str)
+        os.remove(obj.paths["local_density_cache"] % k)
+    np.savez_compressed(os.path.join(HERE, "consensus_backhalf.npz"), norm=norm.astype(np.float32), tpm=tpm,
+                        spectra=spectra, k=k, hvgs=np.array(hvgs), genes_all=genes_all, cells=cells, torch_seed=77,
+                        batch_size=100, **out)
+    print("backhalf golden:", {k_: v.shape for k_, v in out.items() if not k_.endswith(("index", "columns"))})
+
+
 def main():
     ref = load_reference()
     if "--only-ols" in sys.argv:
         return make_ols(ref)
+    if "--only-backhalf" in sys.argv:
+        return make_backhalf(ref, tempfile.mkdtemp())
     tmp = tempfile.mkdtemp()
     make_ols(ref)
+    make_backhalf(ref, tempfile.mkdtemp())
 
     # ---- ledger (cnmf.py:701-777) ------------------------------------------------------
     led = {}

@@ -119,3 +119,25 @@ def test_product_does_not_import_the_oracle():
             if fn.endswith((".py", ".cu", ".cuh")):
                 text = open(os.path.join(dirpath, fn)).read()
                 assert "import oracle" not in text and "from oracle" not in text, fn
+
+
+def test_tpm_side_channel_and_stats(tmp_path):
+    """save_tpm writes what prepare leaves for the consensus back half: the TPM matrix and per-gene mean / population
+    std (cnmf.py:570-580: StandardScaler var ** .5 for sparse input, std(ddof=0) for dense)."""
+    import scipy.sparse as sp
+    from sklearn.preprocessing import StandardScaler
+    from cnmf_torch_b200 import cnmf as host
+    rng = np.random.default_rng(3)
+    tpm = (rng.gamma(0.5, 50.0, size=(40, 17)) * (rng.random((40, 17)) < 0.4))
+    tpm[:, 5] = 0.0
+    obj = host.cNMF(output_dir=str(tmp_path), name="t")
+    obj.save_tpm(tpm, obs_names=[f"c{i}" for i in range(40)], var_names=[f"g{i}" for i in range(17)])
+    T, obs, var = obj.load_tpm()
+    assert np.array_equal(T.toarray(), tpm) and list(var) == [f"g{i}" for i in range(17)] and obs[3] == "c3"
+    stats = host.load_df_from_npz(obj.paths["tpm_stats"])
+    sc = StandardScaler(with_mean=False).fit(sp.csr_matrix(tpm))
+    assert list(stats.columns) == ["__mean", "__std"] and list(stats.index) == list(var)
+    np.testing.assert_allclose(stats["__mean"].values.astype(float), sc.mean_, rtol=1e-12)
+    np.testing.assert_allclose(stats["__std"].values.astype(float), sc.var_ ** .5, rtol=1e-9, atol=1e-12)
+    np.testing.assert_allclose(stats["__std"].values.astype(float), tpm.std(axis=0, ddof=0), rtol=1e-9, atol=1e-12)
+    assert host.cNMF(output_dir=str(tmp_path), name="none").load_tpm() is None
