@@ -505,6 +505,28 @@ class cNMF:
         return median, labels, local_density
 
 
+def _load_results(self, K, density_threshold, n_top_genes=100, norm_usage=True):
+    """cnmf.py:1335-1385: (usage cells x K, spectra_scores genes x K, spectra_tpm genes x K, top_genes n_top x K) read
+    back from the text files ``consensus`` wrote for (K, density_threshold)."""
+    dt = str(density_threshold).replace(".", "_")
+    spectra_scores = pd.read_csv(self.paths["gene_spectra_score__txt"] % (K, dt), sep="\t", index_col=0).T
+    spectra_tpm = pd.read_csv(self.paths["gene_spectra_tpm__txt"] % (K, dt), sep="\t", index_col=0).T
+    usage = pd.read_csv(self.paths["consensus_usages__txt"] % (K, dt), sep="\t", index_col=0)
+    if norm_usage:
+        usage = usage.div(usage.sum(axis=1), axis=0)
+    try:
+        usage.columns = [int(x) for x in usage.columns]
+    except ValueError:
+        print("Usage matrix columns include non integer values")
+    top_genes = [list(spectra_scores.sort_values(by=gep, ascending=False).index[:n_top_genes])
+                 for gep in spectra_scores.columns]
+    top_genes = pd.DataFrame(top_genes, index=spectra_scores.columns).T
+    return usage, spectra_scores, spectra_tpm, top_genes
+
+
+cNMF.load_results = _load_results
+
+
 def _k_selection_stats(self):
     """The table behind ``k_selection_plot`` (cnmf.py:1293-1309) -- one ``consensus(k,
     skip_density_and_return_after_stats=True)`` per K, saved as ``k_selection_stats.df.npz``; the figure itself

@@ -40,6 +40,10 @@ def test_consensus_back_half_matches_reference_files(tmp_path, golden_dir, tag, 
         np.testing.assert_allclose(df.values, ref, rtol=rtol, atol=rtol * scale, err_msg=key)
         assert _pearson(df.values, ref) >= 0.9999, key
         assert os.path.exists(obj.paths[key + "__txt"] % (k, "0_5"))
+    usage, scores, tpm_sp, top = obj.load_results(k, 0.5, n_top_genes=10)          # cnmf.py:1335-1385
+    assert usage.shape == (len(cells), k) and np.allclose(usage.sum(axis=1), 1.0) and list(usage.columns) == [1, 2, 3, 4]
+    assert scores.shape == (len(genes_all), k) and tpm_sp.shape == (len(genes_all), k) and top.shape == (10, k)
+    assert top.iloc[0, 0] == scores.iloc[:, 0].idxmax()
 
 
 def test_consensus_without_tpm_writes_spectra_and_usages_only(tmp_path, golden_dir):
