@@ -195,3 +195,22 @@ def test_streamk_schedule_matches_whole_tile_schedule():
             # 20 iterations amplify the rounding differences (HALS more than MU: its clamp at zero switches)
             assert np.abs(a[k] - b[k]).max() <= (5e-2 if "hals" in k else 2e-3) * scale, k
             assert _pearson(a[k], b[k]) >= 0.9999
+
+
+@pytest.mark.parametrize("N,G,K,R", [(50, 37, 2, 1), (129, 33, 6, 3), (1000, 31, 3, 7), (77, 500, 32, 2), (300, 130, 17, 5)])
+@pytest.mark.parametrize("algo", ["mu", "hals"])
+def test_engine_tc_ragged_shapes_match_oracle(N, G, K, R, algo):
+    """Ragged and extreme shapes on the tcgen05 path: fewer rows than one tile, leading dimensions that are not a
+    multiple of the padding, one replicate, the largest K (32), odd K."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    from cnmf_torch_b200.synth import nb_counts
+    L, _ = _lib()
+    x = nb_counts(N, G, k_true=min(K, 5), seed=N + G, libsize=40.0 * G ** 0.5)
+    eng = DenseFrobeniusEngine(x, impl=L.IMPL_TCGEN05)
+    H0, W0 = eng.make_init(K, list(range(R)))
+    res = eng.factorize(K, H0=H0, W0=W0, algo=algo, tol=0.0, max_iter=20, return_H=True)
+    for r in range(R):
+        ora = no.nmf_batch(x, H0[r].numpy(), W0[r].numpy(), algo=algo, tol=0.0, max_iter=20)
+        for (it_o, obj_o), (it_g, obj_g) in zip(ora["trace"], res.trace):
+            assert it_o == it_g and abs(obj_g[r] - obj_o) / obj_o < 1e-3, (r, it_o, obj_g[r], obj_o)
+        assert _pearson(res.W[r], ora["W"]) >= 0.999 and _pearson(res.H[r], ora["H"]) >= 0.999
