@@ -120,7 +120,6 @@ __global__ void __launch_bounds__(GRAM_THREADS) gram_partial_kernel(const float*
 // staging, no barrier in the main loop), warps stride over the groups, two groups in flight per warp.
 // Far fewer and longer-lived CTAs than the tiled kernel: with thousands of tiny CTAs (R = 400) the tiled
 // kernel spent its time in CTA scheduling, not in arithmetic.
-constexpr int GW_THREADS = 256;
 constexpr int GW_SPLIT = 8192;  // columns per CTA (smaller splits measured slower: the per-CTA reduction dominates)
 
 // Sum N per-lane values over the 32 lanes of a warp by recursive halving: at every step a lane keeps one half of
@@ -155,7 +154,7 @@ struct WarpHalving<N, 0> {
   }
 };
 
-template <int KP>
+template <int KP, int GW_THREADS>
 __global__ void __launch_bounds__(GW_THREADS) gram_warp_kernel(const float* __restrict__ F, int64_t ld, int64_t L,
                                                                float* __restrict__ partial, int nsplit) {
   constexpr int NT = KP * (KP + 1) / 2;
@@ -439,10 +438,23 @@ int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, vo
   if (Kp <= 12) {
     const int ns = (int)ceil_div(L, GW_SPLIT);
     dim3 grid(ns, R);
+    // one CTA per (replicate, column split).  With 256 threads two CTAs fit an SM: beyond 296 CTAs a second, mostly
+    // empty wave starts, and 128-thread CTAs (four per SM, twice the columns per warp) finish sooner
+    // (R=400, Kp=12: 18.5 -> 14.4 us; R=200, Kp=8: 10.1 us with 256 threads, 11.4 with 128).
+    const bool narrow = static_cast<int64_t>(ns) * R > 296;
     switch (Kp) {
-      case 4: gram_warp_kernel<4><<<grid, GW_THREADS, 0, st>>>(F, ld, L, partial, ns); break;
-      case 8: gram_warp_kernel<8><<<grid, GW_THREADS, 0, st>>>(F, ld, L, partial, ns); break;
-      default: gram_warp_kernel<12><<<grid, GW_THREADS, 0, st>>>(F, ld, L, partial, ns); break;
+      case 4:
+        if (narrow) gram_warp_kernel<4, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
+        else gram_warp_kernel<4, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
+        break;
+      case 8:
+        if (narrow) gram_warp_kernel<8, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
+        else gram_warp_kernel<8, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
+        break;
+      default:
+        if (narrow) gram_warp_kernel<12, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
+        else gram_warp_kernel<12, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
+        break;
     }
     CNMF_LAUNCH_CHECK();
     return 0;
