@@ -42,12 +42,6 @@ def _io_pool():
     return ThreadPoolExecutor(max_workers=max(1, min(16, os.cpu_count() or 1)))
 
 
-def _save_spectra_files(paths_and_frames):
-    with _io_pool() as pool:
-        for f in [pool.submit(save_df_to_npz, df, fn) for fn, df in paths_and_frames]:
-            f.result()
-
-
 def worker_filter(iterable, worker_index, total_workers):
     """Job i belongs to worker w iff (i - w) % total == 0 (cnmf.py:53-54)."""
     return (p for i, p in enumerate(iterable) if (i - worker_index) % total_workers == 0)
@@ -299,10 +293,10 @@ class cNMF:
                 print("[Worker %d]. Starting tasks %s (k=%d, %d replicates in one batch)."
                       % (worker_i, list(part.index[:3]) + (["..."] if len(part) > 3 else []), k, len(part)))
                 res = run_nmf_batch(engine, k, [int(s) for s in part["nmf_seed"]], **engine_kw)
-                _save_spectra_files(
-                    (self.paths["iter_spectra"] % (k, int(p["iter"])),
-                     pd.DataFrame(res.W[j], index=np.arange(1, k + 1), columns=var_names))
-                    for j, (_, p) in enumerate(part.iterrows()))
+                # (per K, so that a long run leaves its finished K on disk; the merged file too when this batch is
+                # every replicate of the K in the ledger)
+                self._write_spectra({k: res}, {k: part}, var_names,
+                                    whole_ledger=len(part) == int((run_params["n_components"] == k).sum()))
 
     def _write_spectra(self, res, groups, var_names, whole_ledger):
         """Per-replicate ``spectra.k_%d.iter_%d.df.npz`` files (cnmf.py:889-892) on host threads, and -- SURVEY 8 row

@@ -68,13 +68,14 @@ def test_cli_verbs(tmp_path, counts):
     assert os.path.exists(obj.paths["consensus_spectra__txt"] % (3, "2_0"))
 
 
-def test_factorize_writes_merged_spectra_identical_to_combine(tmp_path, counts):
+@pytest.mark.parametrize("beta_loss", ["frobenius", "kullback-leibler"])
+def test_factorize_writes_merged_spectra_identical_to_combine(tmp_path, counts, beta_loss):
     """a single worker that ran every replicate writes each K's merged file itself; it must be the
     file combine_nmf builds from the per-replicate files (cnmf.py:895-920), and combine must rebuild it as soon as a
     replicate file is newer."""
     from cnmf_torch_b200 import cnmf as host
     obj = host.cNMF(output_dir=str(tmp_path), name="m")
-    obj.prepare_from_matrix(counts, [3, 4], n_iter=5, seed=14, beta_loss="frobenius")
+    obj.prepare_from_matrix(counts, [3, 4], n_iter=5, seed=14, beta_loss=beta_loss)
     obj.factorize(nmf_kwargs_override=dict(mode="batch", batch_max_iter=30))
     direct = {k: host.load_df_from_npz(obj.paths["merged_spectra"] % k) for k in (3, 4)}
     stamp = os.path.getmtime(obj.paths["merged_spectra"] % 3)
