@@ -214,3 +214,27 @@ def test_engine_tc_ragged_shapes_match_oracle(N, G, K, R, algo):
         for (it_o, obj_o), (it_g, obj_g) in zip(ora["trace"], res.trace):
             assert it_o == it_g and abs(obj_g[r] - obj_o) / obj_o < 1e-3, (r, it_o, obj_g[r], obj_o)
         assert _pearson(res.W[r], ora["W"]) >= 0.999 and _pearson(res.H[r], ora["H"]) >= 0.999
+
+
+@pytest.mark.parametrize("algo", ["mu", "hals"])
+def test_factorize_many_stacks_match_single_k_runs(problem, algo):
+    """factorize_many stacks K values that share a padded Kp into one batch (K = 5..8 -> Kp 8, K = 9, 10 -> Kp 12) and
+    runs the stacks on separate streams; every K must come out as if it had been run alone, with the same stopping
+    iteration per replicate."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    L, _ = _lib()
+    eng = DenseFrobeniusEngine(problem, impl=L.IMPL_TCGEN05)
+    ks = [5, 6, 7, 8, 9, 10]
+    seeds = {k: [100 * k + i for i in range(7 if k % 2 else 4)] for k in ks}
+    many = eng.factorize_many(ks, seeds, algo=algo, tol=1e-4, max_iter=60, return_H=True)
+    for k in ks:
+        one = eng.factorize(k, seeds=seeds[k], algo=algo, tol=1e-4, max_iter=60, return_H=True)
+        assert many[k].W.shape == one.W.shape == (len(seeds[k]), k, problem.shape[1])
+        assert np.array_equal(many[k].n_iter, one.n_iter), (k, many[k].n_iter, one.n_iter)
+        np.testing.assert_allclose(many[k].err, one.err, rtol=1e-6)
+        np.testing.assert_allclose(many[k].W, one.W, rtol=1e-4, atol=1e-6 * np.abs(one.W).max())
+        np.testing.assert_allclose(many[k].H, one.H, rtol=1e-4, atol=1e-6 * np.abs(one.H).max())
+        # the stack keeps checking while any of its K still runs: the single run's trace is a prefix of it
+        n = len(one.trace)
+        assert [it for it, _ in many[k].trace][:n] == [it for it, _ in one.trace]
+        np.testing.assert_allclose(many[k].trace[n - 1][1], one.trace[n - 1][1], rtol=1e-6)
