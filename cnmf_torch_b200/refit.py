@@ -28,9 +28,12 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
     X = getattr(X, "values", X)
     W = np.asarray(getattr(W, "values", W), dtype=np.float32)
     H_init = getattr(H_init, "values", H_init)
-    if hasattr(X, "toarray"):
-        X = X.toarray()
-    X = np.ascontiguousarray(X, dtype=np.float32)
+    sparse = hasattr(X, "toarray")
+    if sparse:
+        X = X.tocsr()      # densified one chunk at a time below (the reference densifies the whole matrix, cnmf.py:329-330;
+                           # TPM over all genes x 100 000 cells would be 8 GB of host memory)
+    else:
+        X = np.ascontiguousarray(X, dtype=np.float32)
     n, g = X.shape
     k = W.shape[0]
     Kp = pad4(k)
@@ -69,7 +72,9 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
     Hs = torch.zeros((Kp, ldp), device=dev, dtype=torch.float32)   # chunk-local state: 16-byte aligned columns
     for lo in range(0, n, int(chunk_size)):
         c = min(int(chunk_size), n - lo)
-        xbuf[:c, :g] = torch.from_numpy(X[lo:lo + c]).to(dev)                             # chunk upload (cnmf.py:351)
+        xc = X[lo:lo + c]
+        xc = np.ascontiguousarray(xc.toarray(), dtype=np.float32) if sparse else xc
+        xbuf[:c, :g] = torch.from_numpy(xc).to(dev)                                       # chunk upload (cnmf.py:351)
         check(L.cnmf_b200_gemm_nt(ptr(Wd), ldg, Kp, ptr(xbuf), ldg, c, g, ptr(Pt), ldp, st), "gemm x W^T")
         Hs[:, :c] = Ht[:, lo:lo + c]
         done.zero_()
