@@ -19,16 +19,62 @@
 
 namespace cnmf {
 
+// The KL path pads K to an EVEN Kp (the dense path needs multiples of 4 for its MMA shapes; here every padded
+// component is a gathered value, a conversion and two FMAs per stored entry and replicate: K = 9 or 10 at Kp = 10
+// instead of 12 is 17 % less of everything).
+#define KL_DISPATCH_KP(kp, ...)                                                                       \
+  switch (kp) {                                                                                       \
+    case 2:  { constexpr int KP = 2;  __VA_ARGS__; } break;                                           \
+    case 4:  { constexpr int KP = 4;  __VA_ARGS__; } break;                                           \
+    case 6:  { constexpr int KP = 6;  __VA_ARGS__; } break;                                           \
+    case 8:  { constexpr int KP = 8;  __VA_ARGS__; } break;                                           \
+    case 10: { constexpr int KP = 10; __VA_ARGS__; } break;                                           \
+    case 12: { constexpr int KP = 12; __VA_ARGS__; } break;                                           \
+    case 14: { constexpr int KP = 14; __VA_ARGS__; } break;                                           \
+    case 16: { constexpr int KP = 16; __VA_ARGS__; } break;                                           \
+    case 18: { constexpr int KP = 18; __VA_ARGS__; } break;                                           \
+    case 20: { constexpr int KP = 20; __VA_ARGS__; } break;                                           \
+    case 22: { constexpr int KP = 22; __VA_ARGS__; } break;                                           \
+    case 24: { constexpr int KP = 24; __VA_ARGS__; } break;                                           \
+    case 26: { constexpr int KP = 26; __VA_ARGS__; } break;                                           \
+    case 28: { constexpr int KP = 28; __VA_ARGS__; } break;                                           \
+    case 30: { constexpr int KP = 30; __VA_ARGS__; } break;                                           \
+    case 32: { constexpr int KP = 32; __VA_ARGS__; } break;                                           \
+    default:                                                                                          \
+      cnmf::set_error("kl: Kp=%d unsupported (even, <= 32)", (int)(kp));                              \
+      return CNMF_B200_ERR_INVALID;                                                                   \
+  }
+
 constexpr int KL_THREADS = 128;  // (row, replicate) pairs per CTA, one per thread
 constexpr int KL_SEG_MAX = 2048;  // engine path: rows longer than the segment length (256 .. 2048, kl_seg_len) are cut
 constexpr int KL_SEG_MIN = 256;
 
+// KP is even.  A multiple of 4: 16-byte (fp32) / 8-byte (fp16) accesses; otherwise 8-byte / 4-byte ones (a replicate's
+// KP values start at r * KP elements, which is then only 8- / 4-byte aligned).
 template <int KP>
 __device__ __forceinline__ void load_vec(const float* __restrict__ p, float (&v)[KP]) {
+  if constexpr (KP % 4 == 0) {
 #pragma unroll
-  for (int c = 0; c < KP; c += 4) {
-    const float4 t = *reinterpret_cast<const float4*>(p + c);
-    v[c] = t.x; v[c + 1] = t.y; v[c + 2] = t.z; v[c + 3] = t.w;
+    for (int c = 0; c < KP; c += 4) {
+      const float4 t = *reinterpret_cast<const float4*>(p + c);
+      v[c] = t.x; v[c + 1] = t.y; v[c + 2] = t.z; v[c + 3] = t.w;
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < KP; c += 2) {
+      const float2 t = *reinterpret_cast<const float2*>(p + c);
+      v[c] = t.x; v[c + 1] = t.y;
+    }
+  }
+}
+template <int KP>
+__device__ __forceinline__ void store_vec(float* __restrict__ p, const float (&v)[KP]) {
+  if constexpr (KP % 4 == 0) {
+#pragma unroll
+    for (int c = 0; c < KP; c += 4) *reinterpret_cast<float4*>(p + c) = make_float4(v[c], v[c + 1], v[c + 2], v[c + 3]);
+  } else {
+#pragma unroll
+    for (int c = 0; c < KP; c += 2) *reinterpret_cast<float2*>(p + c) = make_float2(v[c], v[c + 1]);
   }
 }
 
@@ -39,12 +85,36 @@ __device__ __forceinline__ void load_vec(const float* __restrict__ p, float (&v)
 // copy of the factor it updates next to the fp32 state.
 template <int KP>
 __device__ __forceinline__ void load_vec_h(const __half* __restrict__ p, float (&v)[KP]) {
+  if constexpr (KP % 4 == 0) {
 #pragma unroll
-  for (int c = 0; c < KP; c += 4) {
-    const uint2 t = *reinterpret_cast<const uint2*>(p + c);
-    const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&t.x));
-    const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
-    v[c] = a.x; v[c + 1] = a.y; v[c + 2] = b.x; v[c + 3] = b.y;
+    for (int c = 0; c < KP; c += 4) {
+      const uint2 t = *reinterpret_cast<const uint2*>(p + c);
+      const float2 a = __half22float2(*reinterpret_cast<const __half2*>(&t.x));
+      const float2 b = __half22float2(*reinterpret_cast<const __half2*>(&t.y));
+      v[c] = a.x; v[c + 1] = a.y; v[c + 2] = b.x; v[c + 3] = b.y;
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < KP; c += 2) {
+      const float2 a = __half22float2(*reinterpret_cast<const __half2*>(p + c));
+      v[c] = a.x; v[c + 1] = a.y;
+    }
+  }
+}
+template <int KP>
+__device__ __forceinline__ void store_vec_h(__half* __restrict__ p, const float (&v)[KP]) {
+  if constexpr (KP % 4 == 0) {
+#pragma unroll
+    for (int c = 0; c < KP; c += 4) {
+      uint2 t;
+      *reinterpret_cast<__half2*>(&t.x) = __floats2half2_rn(fminf(v[c], 65504.f), fminf(v[c + 1], 65504.f));
+      *reinterpret_cast<__half2*>(&t.y) = __floats2half2_rn(fminf(v[c + 2], 65504.f), fminf(v[c + 3], 65504.f));
+      *reinterpret_cast<uint2*>(p + c) = t;
+    }
+  } else {
+#pragma unroll
+    for (int c = 0; c < KP; c += 2)
+      *reinterpret_cast<__half2*>(p + c) = __floats2half2_rn(fminf(v[c], 65504.f), fminf(v[c + 1], 65504.f));
   }
 }
 
@@ -71,17 +141,8 @@ __device__ __forceinline__ void kl_apply_update(float (&h)[KP], const float (&nu
     const float rate = d < eps ? 0.f : __fdiv_rn(n, d);
     h[k] *= rate;
   }
-#pragma unroll
-  for (int c = 0; c < KP; c += 4) *reinterpret_cast<float4*>(sp + c) = make_float4(h[c], h[c + 1], h[c + 2], h[c + 3]);
-  if (hp != nullptr) {
-#pragma unroll
-    for (int c = 0; c < KP; c += 4) {
-      uint2 t;
-      *reinterpret_cast<__half2*>(&t.x) = __floats2half2_rn(fminf(h[c], 65504.f), fminf(h[c + 1], 65504.f));
-      *reinterpret_cast<__half2*>(&t.y) = __floats2half2_rn(fminf(h[c + 2], 65504.f), fminf(h[c + 3], 65504.f));
-      *reinterpret_cast<uint2*>(hp + c) = t;
-    }
-  }
+  store_vec<KP>(sp, h);
+  if (hp != nullptr) store_vec_h<KP>(hp, h);
 }
 
 // Segment table of one CSR matrix (engine path, built on the device by kl_build_segments).
@@ -180,9 +241,7 @@ __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
   }
   if (SEG && slot >= 0) {   // a cut row: numerators of this segment only
     float* pp = sg.part + (int64_t)slot * rk + (int64_t)r * KP;
-#pragma unroll
-    for (int c = 0; c < KP; c += 4)
-      *reinterpret_cast<float4*>(pp + c) = make_float4(num[c], num[c + 1], num[c + 2], num[c + 3]);
+    store_vec<KP>(pp, num);
     return;
   }
   kl_apply_update<KP>(h, num, fsum + (int64_t)r * KP, l1, l2, eps, sp,
@@ -482,22 +541,22 @@ static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t 
   CNMF_CHECK_ARG(blocks < (1ll << 31), "kl: rows * replicates too large for one launch");
   if (sg == nullptr) {
     KlSegs none{};
-    CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, false><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
+    KL_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, false><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
                              rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, none)));
     CNMF_LAUNCH_CHECK();
     return 0;
   }
-  CNMF_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, true><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
+  KL_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, true><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
                            rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, *sg)));
   CNMF_LAUNCH_CHECK();
   if (sg->nb > 1) {
     const int64_t fb = ceil_div(M * R, KL_THREADS);
-    CNMF_DISPATCH_KP(Kp, (kl_finish_all_kernel<KP><<<(unsigned)fb, KL_THREADS, 0, st>>>(M, state, state_h, fsum, active,
+    KL_DISPATCH_KP(Kp, (kl_finish_all_kernel<KP><<<(unsigned)fb, KL_THREADS, 0, st>>>(M, state, state_h, fsum, active,
                                                                                          R, l1, l2, eps, *sg)));
     CNMF_LAUNCH_CHECK();
   } else if (multi_max > 0) {
     const int64_t fb = ceil_div(multi_max * R, KL_THREADS);
-    CNMF_DISPATCH_KP(Kp, (kl_finish_rows_kernel<KP><<<(unsigned)fb, KL_THREADS, 0, st>>>(state, state_h, fsum, active, R,
+    KL_DISPATCH_KP(Kp, (kl_finish_rows_kernel<KP><<<(unsigned)fb, KL_THREADS, 0, st>>>(state, state_h, fsum, active, R,
                                                                                           l1, l2, eps, *sg)));
     CNMF_LAUNCH_CHECK();
   }
@@ -625,8 +684,8 @@ static int kl_check(const cnmf_b200_kl_problem* p, bool pointers) {
   CNMF_CHECK_ARG(p != nullptr, "kl: null problem");
   CNMF_CHECK_ARG(p->n_cells > 0 && p->n_genes > 0 && p->R > 0 && p->K > 0 && p->nnz >= 0, "kl: empty shape");
   CNMF_CHECK_ARG(p->nnz < (1ll << 31), "kl: nnz must fit int32 offsets");
-  CNMF_CHECK_ARG(p->Kp >= p->K && p->Kp % 4 == 0 && p->Kp <= CNMF_B200_MAX_KP,
-                 "kl: Kp=%d must be a multiple of 4, >= K=%d and <= %d", p->Kp, p->K, CNMF_B200_MAX_KP);
+  CNMF_CHECK_ARG(p->Kp >= p->K && p->Kp % 2 == 0 && p->Kp <= CNMF_B200_MAX_KP,
+                 "kl: Kp=%d must be even, >= K=%d and <= %d", p->Kp, p->K, CNMF_B200_MAX_KP);
   if (pointers) {
     CNMF_CHECK_ARG(p->row_ptr && p->col_idx && p->val && p->t_row_ptr && p->t_col_idx && p->t_val && p->Hr && p->Wt &&
                        p->workspace,
@@ -653,7 +712,7 @@ static int kl_objective_impl(const cnmf_b200_kl_problem* p, const KlLayout& l, c
   CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, wsum64, cpart, st));
   CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, hsum64, cpart, st));
   const unsigned grid = (unsigned)ceil_div((int64_t)l.nblk_obj * p->R, KL_THREADS);
-  CNMF_DISPATCH_KP(p->Kp, (kl_xlogs_kernel<KP><<<grid, KL_THREADS, 0, st>>>(p->row_ptr, p->col_idx, p->val, p->n_cells,
+  KL_DISPATCH_KP(p->Kp, (kl_xlogs_kernel<KP><<<grid, KL_THREADS, 0, st>>>(p->row_ptr, p->col_idx, p->val, p->n_cells,
                                                                               p->Hr, p->Wt, p->R, p->eps, opart)));
   CNMF_LAUNCH_CHECK();
   double* wsq64 = nullptr;

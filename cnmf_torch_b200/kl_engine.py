@@ -4,6 +4,7 @@ replicates of one K interleaved in Hr [N x R*Kp] / Wt [G x R*Kp].  Replaces the 
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import numpy as np
 import scipy.sparse as sp
@@ -11,7 +12,13 @@ import torch
 
 from . import _lib
 from ._lib import KlProblem, check, lib, ptr
-from .engine import EPS_DEFAULT, BatchResult, draw_init, pad4
+from .engine import EPS_DEFAULT, BatchResult, draw_init
+
+
+def pad2(k: int) -> int:
+    """The KL kernels take any even Kp: every padded component is a gathered value and two FMAs per stored entry."""
+    m = 4 if os.environ.get("CNMF_B200_KL_PAD4") else 2      # (dev knob: the multiple-of-4 padding of the dense path)
+    return (int(k) + m - 1) // m * m
 
 
 class SparseKLEngine:
@@ -96,7 +103,7 @@ class SparseKLEngine:
 class KlBatch:
     def __init__(self, eng: SparseKLEngine, K, H0, W0, l1_H, l2_H, l1_W, l2_W, eps):
         self.eng, self.K = eng, int(K)
-        self.R, self.Kp = int(W0.shape[0]), pad4(K)
+        self.R, self.Kp = int(W0.shape[0]), pad2(K)
         if self.Kp > _lib.MAX_KP:
             raise ValueError(f"n_components={K} exceeds the engine limit {_lib.MAX_KP}")
         dev = eng.device

@@ -245,7 +245,7 @@ typedef struct cnmf_b200_kl_problem {
   const int32_t* t_row_ptr;  /* CSR of X^T : [G+1], [nnz], [nnz]  (X is static: built once) */
   const int32_t* t_col_idx;
   const float* t_val;
-  int32_t R, K, Kp, reserved;
+  int32_t R, K, Kp, reserved; /* Kp: K rounded up to an EVEN number here (<= CNMF_B200_MAX_KP); padding columns zero */
   float* Hr;                 /* [N x R*Kp] updated in place */
   float* Wt;                 /* [G x R*Kp] updated in place */
   const uint8_t* active;     /* [R] or NULL */
