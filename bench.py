@@ -204,7 +204,7 @@ def _pipeline_wall(dev):
     tmp = tempfile.mkdtemp(prefix="cnmf_b200_bench_")
     try:
         obj = host.cNMF(output_dir=tmp, name="cfg2", device=str(dev))
-        obj.prepare_from_matrix(x, KS, n_iter=REPLICATES, seed=14, beta_loss="frobenius")
+        obj.prepare_from_matrix(x, KS, n_iter=REPLICATES, seed=14, beta_loss="frobenius", use_gpu=True)  # `cnmf prepare --use_gpu`
         torch.cuda.synchronize()
         t0 = time.perf_counter()
         obj.factorize(nmf_kwargs_override=dict(mode="batch", algo=ALGO, batch_max_iter=500))

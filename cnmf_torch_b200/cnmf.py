@@ -156,11 +156,17 @@ class cNMF:
 
     def prepare_from_matrix(self, norm_counts, components, n_iter=100, seed=None, beta_loss="frobenius",
                             obs_names=None, var_names=None, alpha_usage=0.0, alpha_spectra=0.0,
-                            init="random", total_workers=-1, use_gpu=True, batch_size=5000, max_iter=1000,
+                            init="random", total_workers=-1, use_gpu=False, batch_size=5000, max_iter=1000,
                             tpm=None, tpm_var_names=None):
         """Writes what ``prepare`` leaves for ``factorize`` (cnmf.py:590-596): normalised counts, the
         replicate ledger and the run_nmf kwargs.  ``norm_counts`` is the already variance-scaled HVG
-        matrix (cells x genes); zero-count cells are refused like cnmf.py:688-691."""
+        matrix (cells x genes); zero-count cells are refused like cnmf.py:688-691.  Defaults are ``prepare``'s
+        (cnmf.py:457-462: use_gpu=False -- here that flag selects the init stream, see ``factorize``), so the YAML
+        equals the reference's.  ``beta_loss='itakura-saito'`` is refused here, before anything is written, rather
+        than at the first factorize batch."""
+        if beta_loss in ("itakura-saito", 0, 0.0):
+            from .nmf import ITAKURA_SAITO_REFUSAL
+            raise NotImplementedError(ITAKURA_SAITO_REFUSAL)
         X = sp.csr_matrix(norm_counts)
         if (np.asarray(X.sum(axis=1)).ravel() == 0).any():
             raise Exception("Error: %d cells have zero counts of overdispersed genes. E.g. %s. Filter those "
@@ -246,7 +252,7 @@ class cNMF:
         # the ledger's use_gpu flag keeps the one meaning it can have on a GPU-only engine: WHICH torch generator
         # draws the random init (device generator under use_gpu=True, host generator otherwise -- nmf-torch draws
         # on the device it computes on), so replicates start where the reference's would for that flag
-        init_device = self.init_device or ("cuda" if kw.get("use_gpu", True) else "cpu")
+        init_device = self.init_device or ("cuda" if kw.get("use_gpu", False) else "cpu")
         engine = make_engine(X, beta_loss=kw.get("beta_loss", "frobenius"), device=self.device, impl=self.impl,
                              init_device=init_device)
         engine_kw = {k: kw[k] for k in ("init", "algo", "mode", "tol", "alpha_W", "l1_ratio_W", "alpha_H",
@@ -426,6 +432,7 @@ class cNMF:
             # the clustering, prediction error of the rank-k reconstruction
             from .stats import prediction_error, silhouette_score
             X = norm_counts if norm_counts is not None else self.load_norm_counts()[0]
+            X = X[0] if isinstance(X, tuple) else X
             median = pd.DataFrame(out["median_spectra"], index=np.arange(1, k + 1), columns=merged.columns)
             rf_usages = self.refit_usage(X, median.values, seed=1)
             sil = silhouette_score(out["l2_spectra"], out["labels"] - 1, k, device=self.device)
@@ -448,7 +455,9 @@ class cNMF:
         if seed is not None:
             gen = torch.Generator(device="cpu")
             gen.manual_seed(int(seed))
-        if norm_counts is not None:
+        if isinstance(norm_counts, tuple):                 # what load_norm_counts returns, kept by the caller
+            Xn, obs_names = norm_counts[0], norm_counts[1]
+        elif norm_counts is not None:
             Xn, obs_names = norm_counts, np.arange(norm_counts.shape[0]).astype(str)
         else:
             Xn, obs_names, _ = self.load_norm_counts()
@@ -477,6 +486,9 @@ class cNMF:
                 # final refit on the std-scaled (ddof = 1, not centred) HVG columns of the TPM matrix, cnmf.py:1135-1149
                 hvgs = open(self.paths["nmf_genes_list"]).read().split("\n")
                 pos = pd.Index(tpm_var).get_indexer(hvgs)
+                if (pos < 0).any():
+                    raise KeyError("%d high-variance genes are missing from the TPM matrix, e.g. %r"
+                                   % (int((pos < 0).sum()), hvgs[int(np.argmax(pos < 0))]))
                 Th = sp.csc_matrix(T)[:, pos].astype(np.float64)
                 n_c = Th.shape[0]
                 mean = np.asarray(Th.mean(axis=0)).ravel()
@@ -538,26 +550,62 @@ def _k_selection_stats(self):
 cNMF.k_selection_stats = _k_selection_stats
 
 
-def main():
-    """``cnmf {factorize,combine,consensus}`` with the reference's flags for these verbs
-    (cnmf.py:1410-1467); ``prepare`` stays with the reference."""
+def k_selection_plot(self, close_fig=False):
+    """cnmf.py:1274-1332 computes the stability / prediction-error table and draws it with matplotlib.  This path
+    writes the table (``k_selection_stats.df.npz``, what ``k_selection_stats`` returns); the figure is plotting and
+    stays with the reference."""
+    stats = self.k_selection_stats()
+    print("k_selection_plot: statistics written to %s; the figure itself is drawn by the reference's matplotlib code."
+          % os.path.join(self.output_dir, self.name, self.name + ".k_selection_stats.df.npz"))
+    return stats
+
+
+cNMF.k_selection_plot = k_selection_plot
+
+
+def main(argv=None):
+    """The ``cnmf`` command line with the reference's verbs and flags (cnmf.py:1410-1472).  ``factorize``,
+    ``combine``, ``consensus`` and ``k_selection_plot`` run here; ``prepare`` (HVG selection on AnnData) stays with
+    the reference and says so.  Every flag the reference declares is accepted, so a script written for it runs
+    unchanged: those that only concern ``prepare`` or plotting are parsed and, where they cannot take effect, named
+    in a message.  ``--worker-index`` (commented out in the reference, cnmf.py:1430), ``--device`` and
+    ``--init-device`` are additions."""
     import argparse
     parser = argparse.ArgumentParser()
-    parser.add_argument("command", type=str, choices=["factorize", "combine", "consensus"])
+    parser.add_argument("command", type=str, choices=["prepare", "factorize", "combine", "consensus", "k_selection_plot"])
     parser.add_argument("--name", type=str, nargs="?", default="cNMF")
     parser.add_argument("--output-dir", type=str, nargs="?", default=".")
-    parser.add_argument("--total-workers", type=int, default=None,
+    parser.add_argument("-c", "--counts", type=str, default=None)
+    parser.add_argument("-k", "--components", type=int, nargs="+")
+    parser.add_argument("-n", "--n-iter", type=int, default=100)
+    parser.add_argument("--total-workers", type=int, default=-1,
                         help="workers the replicate jobs are strided over (default: WORLD_SIZE under torchrun, else 1)")
+    parser.add_argument("--use_gpu", action="store_true", default=False)
+    parser.add_argument("--seed", type=int, default=None)
+    parser.add_argument("--genes-file", type=str, default=None)
+    parser.add_argument("--numgenes", type=int, default=2000)
+    parser.add_argument("--tpm", type=str, default=None)
+    parser.add_argument("--max-nmf-iter", type=int, default=1000)
+    parser.add_argument("--beta-loss", type=str, choices=["frobenius", "kullback-leibler", "itakura-saito"],
+                        default="frobenius")
+    parser.add_argument("--init", type=str, choices=["random", "nndsvd"], default="random")
+    parser.add_argument("--densify", dest="densify", action="store_true", default=False)
+    parser.add_argument("--batch_size", type=int, default=5000)
     parser.add_argument("--worker-index", type=int, default=None,
                         help="this worker's index (default: RANK under torchrun, else 0)")
     parser.add_argument("--skip-completed-runs", action="store_true", default=False)
-    parser.add_argument("-k", "--components", type=int, nargs="+")
     parser.add_argument("--local-density-threshold", type=float, default=0.5)
     parser.add_argument("--local-neighborhood-size", type=float, default=0.30)
+    parser.add_argument("--show-clustering", dest="show_clustering", action="store_true")
+    parser.add_argument("--build-reference", dest="build_reference", action="store_true", default=True)
     parser.add_argument("--device", type=str, default=None)
     parser.add_argument("--init-device", type=str, choices=["cpu", "cuda"], default=None,
                         help="[factorize] torch generator that draws the random init (default: the run's use_gpu flag)")
-    args = parser.parse_args()
+    args = parser.parse_args(argv)
+    if args.command == "prepare":
+        parser.exit(2, "cnmf_torch_b200: `prepare` (count loading, TPM, high-variance gene selection) is not part of "
+                       "this path -- run the reference's `cnmf prepare` with the same --name/--output-dir (its files are "
+                       "read as they are), or call cNMF.prepare_from_matrix on an already normalised matrix.\n")
     device = args.device or "cuda:%d" % int(os.environ.get("LOCAL_RANK", "0"))
     obj = cNMF(output_dir=args.output_dir, name=args.name, device=device, init_device=args.init_device)
     if args.command == "factorize":
@@ -569,9 +617,15 @@ def main():
     elif args.command == "combine":
         obj.combine(components=args.components)
     elif args.command == "consensus":
+        if args.show_clustering:
+            print("--show-clustering: the clustergram figure is plotting and stays with the reference; "
+                  "consensus files are written as usual.")
         ks = args.components or sorted(set(load_df_from_npz(obj.paths["nmf_replicate_parameters"]).n_components))
+        X = obj.load_norm_counts() if len(ks) > 1 else None        # read once for every K's usage refit
         for k in ks:
-            obj.consensus(k, args.local_density_threshold, args.local_neighborhood_size)
+            obj.consensus(k, args.local_density_threshold, args.local_neighborhood_size, norm_counts=X)
+    elif args.command == "k_selection_plot":
+        obj.k_selection_plot(close_fig=True)
 
 
 if __name__ == "__main__":

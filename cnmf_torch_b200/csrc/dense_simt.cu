@@ -451,10 +451,13 @@ int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, vo
         if (narrow) gram_warp_kernel<8, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
         else gram_warp_kernel<8, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
         break;
-      default:
+      case 12:
         if (narrow) gram_warp_kernel<12, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
         else gram_warp_kernel<12, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
         break;
+      default:
+        set_error("gram: Kp=%d unsupported (multiples of 4 up to %d)", Kp, CNMF_B200_MAX_KP);
+        return CNMF_B200_ERR_INVALID;
     }
     CNMF_LAUNCH_CHECK();
     return 0;
@@ -563,6 +566,15 @@ int cnmf_b200_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld, doub
   return 0;
 }
 
+// Kp a multiple of 4 in (0, CNMF_B200_MAX_KP]; the tiled kernel (Kp >= 16) reads F with 16-byte loads
+static int gram_check_layout(const char* who, const float* F, int64_t ld, int Kp) {
+  CNMF_CHECK_ARG(Kp > 0 && Kp % 4 == 0 && Kp <= CNMF_B200_MAX_KP,
+                 "%s: Kp=%d unsupported (multiples of 4 up to %d)", who, Kp, CNMF_B200_MAX_KP);
+  CNMF_CHECK_ARG(Kp <= 12 || (ld % 4 == 0 && aligned16(F)),
+                 "%s: for Kp > 12 ld must be a multiple of 4 and F 16-byte aligned", who);
+  return 0;
+}
+
 int64_t cnmf_b200_gram_workspace_bytes(int32_t R, int32_t Kp, int64_t L) {
   return (int64_t)R * gram_tiles(L) * Kp * Kp * (int64_t)sizeof(float);
 }
@@ -572,6 +584,7 @@ int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L,
   CNMF_CHECK_ARG(F && gram && workspace, "gram: null pointer");
   CNMF_CHECK_ARG(R > 0 && L > 0 && ld >= L, "gram: bad shape R=%d L=%lld ld=%lld", R, (long long)L,
                  (long long)ld);
+  CNMF_TRY(gram_check_layout("gram", F, ld, Kp));
   return launch_gram(F, ld, R, Kp, L, gram, workspace, (cudaStream_t)stream);
 }
 
@@ -646,7 +659,7 @@ int cnmf_b200_gram_static(const float* F, int64_t ld, int32_t R, int32_t Kp, int
   CNMF_CHECK_ARG(F && gram, "gram_static: null pointer");
   CNMF_CHECK_ARG(R > 0 && L > 0 && ld >= L, "gram_static: bad shape R=%d L=%lld ld=%lld", R, (long long)L,
                  (long long)ld);
-  CNMF_CHECK_ARG(Kp > 0 && Kp % 4 == 0 && Kp <= CNMF_B200_MAX_KP, "gram_static: Kp=%d unsupported", Kp);
+  CNMF_TRY(gram_check_layout("gram_static", F, ld, Kp));
   const int64_t need = (int64_t)R * gram_tiles(L) * Kp * Kp;  // one partial per 256-column tile
   if (need > GRAM_STATIC_FLOATS) {
     set_error("gram_static: needs %lld scratch floats, the built-in array holds %lld "

@@ -4,7 +4,10 @@ called as ``(usages, spectra, err) = run_nmf(X, **nmf_kwargs)`` at cnmf.py:819.
 Same keyword arguments (cnmf.py:757-771 + ``random_state`` / ``n_components`` set at cnmf.py:885-886),
 same return order and types: ``H`` (N x K usages), ``W`` (K x G spectra) as host float32 arrays and
 the scalar ``err = sqrt(2 * objective)``.  Everything runs on the GPU through libcnmf_b200.so; there is
-no CPU path (``use_gpu=False`` is refused rather than silently honoured some other way).
+no CPU path.  ``use_gpu`` (False by default in nmf-torch and in every YAML ``cnmf prepare`` writes without
+``--use_gpu``, cnmf.py:461, 770, 1420) keeps the one meaning it can have here: which torch generator draws
+the random init -- the host generator under False, so a replicate starts exactly where the reference's CPU
+run starts, the device generator under True.
 
 ``run_nmf_batch`` is the replicate-batched form the ``cNMF.factorize`` override uses: many seeds of one
 K share every pass over X.
@@ -16,6 +19,12 @@ import numpy as np
 from . import _lib
 
 _IMPL = {"auto": _lib.IMPL_AUTO, "simt": _lib.IMPL_SIMT, "tcgen05": _lib.IMPL_TCGEN05}
+
+
+ITAKURA_SAITO_REFUSAL = (
+    "beta_loss='itakura-saito' is not implemented by cnmf_torch_b200: the divergence is +inf wherever X is zero, "
+    "and a normalised count matrix always has zeros (scikit-learn refuses beta_loss <= 0 on such a matrix for the "
+    "same reason). Use 'frobenius' or 'kullback-leibler'.")
 
 
 def _reg(alpha_W, l1_ratio_W, alpha_H, l1_ratio_H):
@@ -55,8 +64,9 @@ def make_engine(X, beta_loss="frobenius", device="cuda:0", impl="auto", init_dev
     if beta_loss in ("kullback-leibler", 1, 1.0):
         from .kl_engine import SparseKLEngine
         return SparseKLEngine(X, device=device, init_device=init_device)
-    raise NotImplementedError(
-        f"beta_loss={beta_loss!r}: this engine implements 'frobenius' and 'kullback-leibler'")
+    if beta_loss in ("itakura-saito", 0, 0.0):
+        raise NotImplementedError(ITAKURA_SAITO_REFUSAL)
+    raise ValueError(f"beta_loss={beta_loss!r}: expected 'frobenius', 'kullback-leibler' or 'itakura-saito'")
 
 
 def run_nmf_batch(engine, n_components, seeds, init="random", algo="mu", mode="batch", tol=1e-4,
@@ -88,20 +98,21 @@ def run_nmf_batch(engine, n_components, seeds, init="random", algo="mu", mode="b
 
 
 def run_nmf(X, n_components, init="random", beta_loss="frobenius", algo="mu", mode="batch", tol=1e-4,
-            n_jobs=-1, random_state=0, use_gpu=True, alpha_W=0.0, l1_ratio_W=0.0, alpha_H=0.0,
+            n_jobs=-1, random_state=0, use_gpu=False, alpha_W=0.0, l1_ratio_W=0.0, alpha_H=0.0,
             l1_ratio_H=0.0, fp_precision="float", batch_max_iter=500, online_max_pass=20,
             online_chunk_size=5000, online_chunk_max_iter=200, online_h_tol=0.05, online_w_tol=0.05,
-            online_usage_tol=None, online_spectra_tol=None, device="cuda:0", impl="auto", init_device="cuda",
+            online_usage_tol=None, online_spectra_tol=None, device="cuda:0", impl="auto", init_device=None,
             **unknown):
     """One replicate, the reference's call shape.  Returns (H, W, err).
 
-    ``init_device`` (not a reference kwarg): the 'random' init is drawn by the device generator, as nmf-torch
-    does under use_gpu=True -- the only mode this GPU-only function has; pass "cpu" to start from the draws the
-    reference makes under use_gpu=False (and the oracle makes)."""
+    ``use_gpu`` selects the init stream, not the processor (always the GPU): False -> torch's host generator,
+    True -> the device generator, as nmf-torch draws on the device it computes on.  ``init_device`` ("cpu" /
+    "cuda", not a reference kwarg) overrides that choice.  ``n_jobs`` (host threads in nmf-torch) has nothing to
+    set here and is accepted."""
     if unknown:
         raise TypeError(f"run_nmf got unexpected keyword arguments {sorted(unknown)}")
-    if use_gpu is False:
-        raise _lib.Cnmfb200Error("cnmf_torch_b200.run_nmf is GPU-only: use_gpu=False is not available")
+    if init_device is None:
+        init_device = "cuda" if use_gpu else "cpu"
     if fp_precision not in ("float", np.float32, "float32"):
         raise NotImplementedError("state precision is float32 (nmf-torch's default fp_precision='float')")
     if online_usage_tol is not None:

@@ -64,7 +64,9 @@ int cnmf_b200_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld, doub
                     void* workspace, void* stream);
 
 /* gram[r] = F_r F_r^T  (Kp x Kp, row-major) for every replicate block F_r = F[r*Kp : (r+1)*Kp, 0:L].
- * Replaces  W @ W.T  /  H.T @ H  (pattern in-repo at cnmf.py:346). Deterministic two-stage sum. */
+ * Replaces  W @ W.T  /  H.T @ H  (pattern in-repo at cnmf.py:346). Deterministic two-stage sum.
+ * Kp: a multiple of 4 in (0, CNMF_B200_MAX_KP] (anything else is CNMF_B200_ERR_INVALID); for Kp > 12
+ * ld must be a multiple of 4 and F 16-byte aligned (the tiled kernel reads F with 16-byte loads). */
 int64_t cnmf_b200_gram_workspace_bytes(int32_t R, int32_t Kp, int64_t L);
 int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
                    void* workspace, void* stream);
@@ -75,8 +77,12 @@ int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L,
  * The split partials live in a 4 MiB array inside the library (resident on every GPU that loads it).
  * Refuses problems with R * ceil(L/256) * Kp*Kp > cnmf_b200_gram_static_max_floats() (2^20) with
  * CNMF_B200_ERR_WORKSPACE.  Allocates nothing.  The first call on a device resolves the array's
- * address: issue it before any stream capture.  Calls share the array: calls that overlap on the GPU
- * race; nothing in it needs clearing between calls. */
+ * address: issue it before any stream capture, and before the host application takes the rest of
+ * device memory -- with lazy module loading that first lookup may be what loads the library image
+ * (including the array) onto the device, and it may synchronise.  The address is cached per device
+ * ordinal for the life of the process: after cudaDeviceReset the library must be reloaded.  Calls
+ * share the array: calls that overlap on the GPU race; nothing in it needs clearing between calls.
+ * Same Kp / ld / alignment rules as cnmf_b200_gram. */
 int64_t cnmf_b200_gram_static_max_floats(void);
 int cnmf_b200_gram_static(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
                           void* stream);

@@ -51,6 +51,35 @@ def test_gemm_nt_matches_torch(M, N, Kd):
         assert torch.all(Cm[:, N:] == -7.0)   # padding untouched
 
 
+@pytest.mark.parametrize("Kp", [0, -4, 6, 10, 36])
+def test_gram_rejects_unsupported_kp(Kp):
+    """cnmf_b200_gram used to run the <12> kernel for any Kp <= 12 (wrong stride, out-of-bounds reads)."""
+    L, lib = _lib()
+    F = torch.rand(64, 64, device="cuda")
+    out = torch.zeros(4, 32, 32, device="cuda")
+    ws = torch.zeros(1 << 16, device="cuda")
+    for fn, args in ((lib.cnmf_b200_gram, (ws.data_ptr(), _stream())), (lib.cnmf_b200_gram_static, (_stream(),))):
+        rc = fn(F.data_ptr(), 64, 1, Kp, 64, out.data_ptr(), *args)
+        assert rc == L.ERR_INVALID and b"unsupported" in lib.cnmf_b200_last_error()
+
+
+def test_gram_rejects_misaligned_wide_kp():
+    L, lib = _lib()
+    F = torch.rand(16 * 67 + 8, device="cuda")
+    out = torch.zeros(1, 16, 16, device="cuda")
+    ws = torch.zeros(1 << 16, device="cuda")
+    rc = lib.cnmf_b200_gram(F.data_ptr(), 67, 1, 16, 64, out.data_ptr(), ws.data_ptr(), _stream())
+    assert rc == L.ERR_INVALID and b"16-byte aligned" in lib.cnmf_b200_last_error()
+    rc = lib.cnmf_b200_gram(F.data_ptr() + 4, 68, 1, 16, 64, out.data_ptr(), ws.data_ptr(), _stream())
+    assert rc == L.ERR_INVALID
+    # Kp <= 12 reads scalars: any ld is fine
+    out12 = torch.zeros(1, 12, 12, device="cuda")
+    L.check(lib.cnmf_b200_gram(F.data_ptr(), 67, 1, 12, 64, out12.data_ptr(), ws.data_ptr(), _stream()))
+    torch.cuda.synchronize()
+    Fr = F[:12 * 67].reshape(12, 67)[:, :64].double()
+    torch.testing.assert_close(out12[0], (Fr @ Fr.T).float(), rtol=2e-5, atol=1e-5)
+
+
 def test_gemm_nt_rejects_bad_alignment():
     L, lib = _lib()
     A = torch.rand(8, 8, device="cuda")

@@ -92,8 +92,40 @@ def test_run_nmf_dropin_kl_and_frobenius(problem):
         assert H.shape == (problem.shape[0], 5) and W.shape == (5, problem.shape[1]) and np.isfinite(err)
         ho, wo, eo = no.run_nmf_oracle(problem, beta_loss=beta, **{k: v for k, v in kw.items() if k != "use_gpu"})
         assert abs(err - eo) / eo < 1e-3
-    with pytest.raises(Exception):
-        run_nmf(problem, use_gpu=False, **{k: v for k, v in kw.items() if k != "use_gpu"})
+
+
+def test_run_nmf_with_the_reference_default_kwargs(problem):
+    """The exact dict ``cnmf prepare`` writes without --use_gpu (cnmf.py:757-771: use_gpu=False, n_jobs=-1,
+    mode='online') plus the two keys the worker loop adds (cnmf.py:885-886, numpy integers as pandas hands them
+    over).  use_gpu=False selects the host generator's init stream -- the oracle's -- not a CPU path."""
+    from cnmf_torch_b200.nmf import run_nmf
+    for beta in ("frobenius", "kullback-leibler"):
+        kw = dict(alpha_W=0.0, alpha_H=0.0, l1_ratio_H=0.0, l1_ratio_W=0.0, beta_loss=beta, algo="mu", tol=1e-4,
+                  mode="online", online_chunk_max_iter=1000, online_chunk_size=5000, init="random", n_jobs=-1,
+                  use_gpu=False)
+        kw["random_state"] = np.int64(12345)
+        kw["n_components"] = np.int64(5)
+        H, W, err = run_nmf(problem, **kw)
+        assert H.shape == (problem.shape[0], 5) and W.shape == (5, problem.shape[1])
+        ho, wo, eo = no.run_nmf_oracle(problem, **{k: v for k, v in kw.items() if k not in ("use_gpu", "n_jobs")})
+        assert abs(err - eo) / eo < 1e-3
+        assert _pearson(W, wo) >= 0.999
+        # use_gpu=True starts from the device generator's draws: another replicate, same quality
+        H2, W2, err2 = run_nmf(problem, **{**kw, "use_gpu": True})
+        assert not np.allclose(W2, W) and abs(err2 - err) / err < 0.05
+
+
+def test_itakura_saito_is_refused_with_the_reason(problem, tmp_path):
+    """A ``choices=`` value of the reference CLI (cnmf.py:1426).  Refused where the run is set up, with the reason."""
+    from cnmf_torch_b200.cnmf import cNMF
+    from cnmf_torch_b200.nmf import run_nmf
+    with pytest.raises(NotImplementedError, match="zero"):
+        run_nmf(problem, n_components=4, beta_loss="itakura-saito")
+    obj = cNMF(output_dir=str(tmp_path), name="is")
+    with pytest.raises(NotImplementedError, match="zero"):
+        obj.prepare_from_matrix(problem, [4], n_iter=2, seed=1, beta_loss="itakura-saito")
+    with pytest.raises(ValueError):
+        run_nmf(problem, n_components=4, beta_loss="hellinger")
 
 
 def test_cnmf_default_online_kwargs_with_kl_fall_back_to_batch(problem, capsys):

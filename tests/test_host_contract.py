@@ -141,3 +141,39 @@ def test_tpm_side_channel_and_stats(tmp_path):
     np.testing.assert_allclose(stats["__std"].values.astype(float), sc.var_ ** .5, rtol=1e-9, atol=1e-12)
     np.testing.assert_allclose(stats["__std"].values.astype(float), tpm.std(axis=0, ddof=0), rtol=1e-9, atol=1e-12)
     assert host.cNMF(output_dir=str(tmp_path), name="none").load_tpm() is None
+
+
+def test_cli_accepts_every_flag_the_reference_declares(tmp_path, capsys):
+    """cnmf.py:1410-1435: a command line written for the reference must parse here.  ``prepare`` is outside this
+    path and says so; ``combine`` runs on the CPU and is exercised end to end."""
+    obj = host.cNMF(output_dir=str(tmp_path), name="cli")
+    rp, kw = obj.get_nmf_iter_params([2], n_iter=2, random_state_seed=1, beta_loss="frobenius")
+    obj.save_nmf_iter_params(rp, kw)
+    for it in range(2):
+        host.save_df_to_npz(pd.DataFrame(np.full((2, 3), it + 1.0, dtype=np.float32), index=[1, 2],
+                                         columns=["a", "b", "c"]), obj.paths["iter_spectra"] % (2, it))
+    every_flag = ["--name", "cli", "--output-dir", str(tmp_path), "-c", "counts.h5ad", "-k", "2", "-n", "2",
+                  "--total-workers", "1", "--use_gpu", "--seed", "3", "--genes-file", "g.txt", "--numgenes", "500",
+                  "--tpm", "tpm.df.npz", "--max-nmf-iter", "200", "--beta-loss", "itakura-saito", "--init", "nndsvd",
+                  "--densify", "--batch_size", "1000", "--skip-completed-runs", "--local-density-threshold", "0.3",
+                  "--local-neighborhood-size", "0.2", "--show-clustering", "--build-reference"]
+    host.main(["combine"] + every_flag)
+    assert host.load_df_from_npz(obj.paths["merged_spectra"] % 2).shape == (4, 3)
+    with pytest.raises(SystemExit) as e:
+        host.main(["prepare"] + every_flag)
+    assert e.value.code == 2 and "prepare_from_matrix" in capsys.readouterr().err
+    with pytest.raises(SystemExit):
+        host.main(["plot_everything", "--name", "cli"])          # not one of the reference's verbs
+
+
+def test_prepare_from_matrix_writes_the_reference_default_kwargs(tmp_path):
+    """use_gpu=False unless asked, like ``cnmf prepare`` without --use_gpu (cnmf.py:461, 770, 1420)."""
+    import yaml
+    obj = host.cNMF(output_dir=str(tmp_path), name="d")
+    obj.prepare_from_matrix(np.ones((4, 3), dtype=np.float32), [2], n_iter=2, seed=1)
+    kw = yaml.load(open(obj.paths["nmf_run_parameters"]), Loader=yaml.FullLoader)
+    assert kw == dict(alpha_W=0.0, alpha_H=0.0, l1_ratio_H=0.0, l1_ratio_W=0.0, beta_loss="frobenius", algo="mu",
+                      tol=1e-4, mode="online", online_chunk_max_iter=1000, online_chunk_size=5000, init="random",
+                      n_jobs=-1, use_gpu=False)
+    with pytest.raises(NotImplementedError, match="zero"):
+        obj.prepare_from_matrix(np.ones((4, 3), dtype=np.float32), [2], n_iter=2, beta_loss="itakura-saito")
