@@ -7,12 +7,21 @@ frobenius HALS"), synthetic negative-binomial counts, variance-scaled as the ref
 6000 replicate-iterations per GPU per step.  With N GPUs every rank runs the whole workload on its own
 replicate seeds (replicates are independent units; no data-path collective) => weak scaling.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config cfg2|cfg3|cfg5]
+
+--config (default cfg2, the line the driver records):
+  cfg3  BASELINE.json configs[2]: 100 000 x 2000 CSR, K=5..13 x 100 replicates, KL MU.  ONE ledger of 900 jobs split over
+        the ranks with the reference's stride rule (worker_filter, cnmf.py:53-54) => strong scaling; a step = 10
+        iterations + objective of every job of the rank.
+  cfg5  BASELINE.json configs[4]: 1 000 000 x 2000 dense, online mode, chunk 5000, K=15 x 50 replicates, cells
+        row-sharded over the ranks with one NCCL all-reduce of the chunk statistics [A | B] per step; a step = one
+        pass over all cells (nmf-torch counts passes as the iterations of online mode).
 """
 from __future__ import annotations
 
 import argparse
 import json
+import math
 import os
 import subprocess
 import sys
@@ -31,10 +40,53 @@ REPLICATES = 100
 ITERS_PER_STEP = 10
 ALGO = "hals"
 E2E_ITERS = 100  # iterations per replicate in one end-to-end public-API call
+KL_PROFILE_CSV = "r02_kl_slab_full_raw.csv"
+TC_PROFILE_CSV = "r02_tc_half_step_full_raw.csv"   # ncu --set full raw page of the dominant kernel, this round
 METRIC = "nmf_replicate_iterations_per_second"
 UNIT = "replicate-iters/s"
 WORKLOAD = ("cfg2: 2700x2000 NB counts (variance-scaled), K=7..12 x 100 replicates, frobenius HALS, "
             "batch mode, 10 iterations + objective per step")
+
+
+CFG3 = dict(cells=100000, genes=2000, ks=list(range(5, 14)), replicates=100, libsize=170.0, e2e_iters=20)
+CFG5 = dict(cells=1000000, genes=2000, k=15, replicates=50, chunk=5000)
+WORKLOAD3 = ("cfg3: 100000x2000 CSR NB counts (~8 % stored, variance-scaled), K=5..13 x 100 replicates = ONE ledger of "
+             "900 jobs strided over the ranks (worker_filter), beta_loss=kullback-leibler MU, batch mode, 10 iterations "
+             "+ objective per step")
+WORKLOAD5 = ("cfg5: 1000000x2000 dense NB counts, online mode, chunk 5000, K=15 x 50 replicates, cells row-sharded over "
+             "the ranks, one all-reduce of the chunk statistics [A | B] per chunk step; one step = one pass over all cells "
+             "(inner h / W loops to tol 0.05, H refresh, objective)")
+
+
+def _config(name, path="auto", streams=1):
+    """The config object of a bench line -- the SAME for the b200 arm and the reference arm of a config, sampling rule
+    of the CPU arm included."""
+    if name == "cfg2":
+        return {"workload": WORKLOAD, "replicates_per_gpu": len(KS) * REPLICATES, "l2_flush_between_steps": True,
+                "path": path, "k_batches_on_separate_streams": bool(streams),
+                "e2e_step": f"DenseFrobeniusEngine(X_pinned).factorize_many(K=7..12, seeds, hals, tol=0, "
+                            f"max_iter={E2E_ITERS}) per step: H2D of X from pinned host memory, random inits drawn by "
+                            f"the device generator (init_device='cuda', nmf-torch's use_gpu=True stream), D2H of the "
+                            f"objectives every 10 iterations and of all spectra",
+                "reference_arm_sampling": f"the CPU arm (--impl reference) runs 1 replicate per K (K=7..12) x "
+                                          f"{ITERS_PER_STEP} HALS iterations + objective per step: replicates are "
+                                          f"independent and the CPU path runs them one after the other, so its "
+                                          f"replicate-iterations/s does not depend on how many are run"}
+    if name == "cfg3":
+        return {"workload": WORKLOAD3, "jobs": len(CFG3["ks"]) * CFG3["replicates"], "inputs_larger_than_l2": True,
+                "e2e_step": f"SparseKLEngine(X csr on the host).factorize_many(this rank's jobs, tol=0, "
+                            f"max_iter={CFG3['e2e_iters']}) per step: CSR upload, device-drawn inits, D2H of objectives "
+                            f"and spectra",
+                "reference_arm_sampling": "the CPU arm runs 1 replicate of K=9 x 2 KL MU iterations + objective (dense, "
+                                          "torch CPU) per step on the same matrix; replicates are independent and run "
+                                          "one after the other on the CPU"}
+    if name == "cfg5":
+        return {"workload": WORKLOAD5, "inputs_larger_than_l2": True,
+                "e2e_step": "DenseFrobeniusEngine(this rank's cells, pinned host memory).factorize_online(max_pass=1) "
+                            "per step: H2D of X, device-drawn inits, D2H of spectra",
+                "reference_arm_sampling": "the CPU arm runs 1 replicate x 1 pass over the first 100 000 cells (20 chunks) "
+                                          "per step and divides by 10: the chunk loop is linear in the number of cells"}
+    raise ValueError(name)
 
 
 def _peaks():
@@ -42,6 +94,28 @@ def _peaks():
         return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json"))), "measured"
     except Exception:
         return {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0}, "fallback"
+
+
+def _traffic_from_profile(csv_name, kernel_substr):
+    """dram__bytes_read.sum + dram__bytes_write.sum of the named kernel's launch in a committed `ncu --set full`
+    raw page (profiles/<csv_name>), per launch; None when the capture is absent (then the line says so)."""
+    import csv
+    path = os.path.join(ROOT, "profiles", csv_name)
+    if not os.path.exists(path):
+        return None
+    try:
+        rows = list(csv.reader(open(path)))
+        hdr, units = rows[0], rows[1]
+        ki, ri, wi = hdr.index("Kernel Name"), hdr.index("dram__bytes_read.sum"), hdr.index("dram__bytes_write.sum")
+        mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
+        best = None
+        for r in rows[2:]:
+            if kernel_substr in r[ki]:
+                v = float(r[ri].replace(",", "")) * mult.get(units[ri], 1.0) + float(r[wi].replace(",", "")) * mult.get(units[wi], 1.0)
+                best = v if best is None else max(best, v)
+        return best
+    except Exception:
+        return None
 
 
 class ClockSampler(threading.Thread):
@@ -114,9 +188,12 @@ def _use_all_host_threads(torch):
     return torch.get_num_threads()
 
 
-def _cpu_baseline(x, seconds_target=15.0):
-    """The oracle port of run_nmf (torch CPU, all host threads) on a bounded sample of the same
-    workload: K=10, HALS, a few replicates x 10 iterations, repeated until ~seconds_target."""
+def _cpu_baseline(x, seconds_target=12.0):
+    """The oracle port of run_nmf (torch CPU, all host threads) on a bounded sample of the same workload: K=10, HALS,
+    a few replicates x 10 iterations + objective (trace identity, as a competent CPU implementation evaluates it),
+    repeated until ~seconds_target.  scikit-learn's coordinate-descent solver from the same init is timed beside it
+    (``sklearn_cd``): an independent, compiled CPU implementation of the same HALS sweep, so that the ratio does not
+    rest on the restatement alone."""
     import torch
     from oracle import nmf_oracle as no
     cores = _use_all_host_threads(torch)
@@ -124,15 +201,30 @@ def _cpu_baseline(x, seconds_target=15.0):
     done, t0, reps = 0, time.perf_counter(), 0
     while True:
         h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), x.shape[0], x.shape[1], k, 1000 + reps)
-        no.nmf_batch(x, h0, w0, algo=ALGO, tol=0.0, max_iter=ITERS_PER_STEP)
+        no.nmf_batch(x, h0, w0, algo=ALGO, tol=0.0, max_iter=ITERS_PER_STEP, objective="trace")
         done += ITERS_PER_STEP
         reps += 1
         el = time.perf_counter() - t0
         if el > seconds_target or reps >= 200:
             break
-    return {"value": done / el, "unit": UNIT, "cores": int(cores), "kind": "port",
-            "sample": f"{reps} replicates x {ITERS_PER_STEP} HALS iterations + objective, K={k}, same X, "
-                      f"{el:.1f}s of torch-CPU work (oracle/nmf_oracle.py; nmf-torch itself is not installable here)"}
+    out = {"value": done / el, "unit": UNIT, "cores": int(cores), "kind": "port",
+           "sample": f"{reps} replicates x {ITERS_PER_STEP} HALS iterations + objective (trace identity), K={k}, same X, "
+                     f"{el:.1f}s of torch-CPU work (oracle/nmf_oracle.py; nmf-torch itself is not installable here)"}
+    try:
+        from sklearn.decomposition import non_negative_factorization
+        x64 = x.astype(np.float64)
+        h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), x.shape[0], x.shape[1], k, 999)
+        n_it, t0 = 0, time.perf_counter()
+        while time.perf_counter() - t0 < 4.0:
+            non_negative_factorization(x64, W=h0.astype(np.float64).copy(), H=w0.astype(np.float64).copy(),
+                                       n_components=k, init="custom", solver="cd", max_iter=ITERS_PER_STEP, tol=0)
+            n_it += ITERS_PER_STEP
+        out["sklearn_cd"] = {"value": n_it / (time.perf_counter() - t0), "unit": UNIT,
+                             "note": "sklearn non_negative_factorization(solver='cd', init='custom') from the same "
+                                     "kind of init, fp64, same X, K=10; its own threading"}
+    except Exception as e:   # the comparison is optional
+        out["sklearn_cd"] = {"error": str(e)[:100]}
+    return out
 
 
 def _extras(dev):
@@ -224,6 +316,37 @@ def _pipeline_wall(dev):
         shutil.rmtree(tmp, ignore_errors=True)
 
 
+def _cfg3_matrix():
+    from cnmf_torch_b200.synth import nb_counts
+    return nb_counts(CFG3["cells"], CFG3["genes"], seed=14, libsize=CFG3["libsize"])
+
+
+def _cfg5_block_device(n_rows, seed, dev):
+    """One rank's block of the cfg-5 matrix, drawn on the device (a 1 M x 2000 host draw takes minutes): NB counts
+    from 10 gene programs, every gene scaled to unit variance like the reference's normalisation.  fp32 [n_rows x G]."""
+    import torch
+    g = torch.Generator(device=dev)
+    g.manual_seed(14)                                        # the programs are the same on every rank
+    G, kt = CFG5["genes"], 10
+    prog = torch._standard_gamma(torch.full((kt, G), 0.3, device=dev), generator=g) + 1e-6
+    prog /= prog.sum(1, keepdim=True)
+    g.manual_seed(1000 + seed)
+    out = torch.empty((n_rows, G), device=dev, dtype=torch.float32)
+    for lo in range(0, n_rows, 50000):
+        hi = min(n_rows, lo + 50000)
+        usage = torch._standard_gamma(torch.full((hi - lo, kt), 0.2, device=dev), generator=g) + 1e-8
+        usage /= usage.sum(1, keepdim=True)
+        lib = torch.exp(torch.randn((hi - lo, 1), device=dev, generator=g) * 0.35 + math.log(600.0))
+        mu = lib * (usage @ prog)
+        lam = torch._standard_gamma(torch.full_like(mu, 2.0), generator=g) * (mu / 2.0)
+        out[lo:hi] = torch.poisson(lam, generator=g)
+    out[:, :] += (out.sum(1, keepdim=True) == 0) * (1.0 / G)      # no all-zero cell
+    std = out.std(dim=0, unbiased=True)
+    std[std == 0] = 1.0
+    out /= std
+    return out
+
+
 def run_reference(args):
     """--impl reference: the reference's CPU path for this metric.  nmf-torch is absent from the image
     (SURVEY.md 0.2), so this times the oracle port with all host threads; rank 0 only."""
@@ -233,16 +356,36 @@ def run_reference(args):
     import torch
     from cnmf_torch_b200.synth import nb_counts
     from oracle import nmf_oracle as no
-    x = nb_counts(N_CELLS, N_GENES, seed=14)
     cores = _use_all_host_threads(torch)
-    # one step = every K, a bounded sample of 1 replicate per K x 10 iterations
-    def step(seed0):
-        n = 0
-        for k in KS:
-            h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), N_CELLS, N_GENES, k, seed0 + k)
-            no.nmf_batch(x, h0, w0, algo=ALGO, tol=0.0, max_iter=ITERS_PER_STEP)
-            n += ITERS_PER_STEP
-        return n
+    cfg = args.config
+    if cfg == "cfg2":
+        x = nb_counts(N_CELLS, N_GENES, seed=14)
+
+        def step(seed0):   # every K, 1 replicate per K x 10 iterations + objective
+            n = 0
+            for k in KS:
+                h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), N_CELLS, N_GENES, k, seed0 + k)
+                no.nmf_batch(x, h0, w0, algo=ALGO, tol=0.0, max_iter=ITERS_PER_STEP, objective="trace")
+                n += ITERS_PER_STEP
+            return n
+        scaling, dtype = "weak", "f32"
+    elif cfg == "cfg3":
+        x = _cfg3_matrix()
+
+        def step(seed0):   # 1 replicate of K=9 x 2 KL iterations + objective on the dense matrix
+            h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), x.shape[0], x.shape[1], 9, seed0)
+            no.nmf_batch(x, h0, w0, beta_loss="kullback-leibler", tol=0.0, max_iter=2, check_every=2)
+            return 2
+        scaling, dtype = "strong", "f32"
+    else:
+        from cnmf_torch_b200.synth import nb_counts as nbc
+        x = nbc(100000, CFG5["genes"], seed=14, libsize=600.0)
+
+        def step(seed0):   # 1 replicate x 1 pass over 100 000 cells = 1/10 of a pass over the config's 1 M cells
+            h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), x.shape[0], x.shape[1], CFG5["k"], seed0)
+            no.nmf_online(x, h0, w0, tol=0.0, max_pass=1, chunk_size=CFG5["chunk"], chunk_max_iter=200)
+            return 0.1
+        scaling, dtype = "strong", "f32"
     for w in range(args.warmup):
         step(w)
     t0 = time.perf_counter()
@@ -251,15 +394,224 @@ def run_reference(args):
         total += step(100 + s)
     el = time.perf_counter() - t0
     val = total / el
-    sample = f"1 replicate per K (K=7..12) x {ITERS_PER_STEP} HALS iterations + objective per step"
+    config = _config(cfg, args.path, args.streams)
+    sample = config["reference_arm_sampling"]
     print(json.dumps({
         "impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * el / max(1, args.steps),
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "sample": sample},
+        "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": dtype, "data": "synthetic",
+        "config": config,
         "cpu_baseline": {"value": val, "unit": UNIT, "cores": int(cores), "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
+
+
+def _dist_setup():
+    import torch
+    import torch.distributed as dist
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    return rank, world, local, dev
+
+
+def _timed_steps(args, one_step, world, local, flush=None):
+    """W warm-up steps, then K steps timed with CUDA events on the current stream, barrier + synchronize on both sides;
+    returns (sum of the step times in ms on this rank, clocks sampled meanwhile)."""
+    import torch
+    import torch.distributed as dist
+    for _ in range(args.warmup):
+        one_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local)
+    sampler.start()
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    for s_ in range(args.steps):
+        if flush is not None:
+            flush.zero_()
+        ev[s_][0].record()
+        one_step()
+        ev[s_][1].record()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    return float(sum(a.elapsed_time(b) for a, b in ev)), clocks
+
+
+def _max_over_ranks(values, dev, world):
+    import torch
+    import torch.distributed as dist
+    if world == 1:
+        return [float(v) for v in values]
+    t = torch.tensor(values, dtype=torch.float64, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return [float(v) for v in t]
+
+
+def run_cfg3(args):
+    """BASELINE.json configs[2]: one ledger of 900 KL jobs, strided over the ranks (strong scaling)."""
+    import scipy.sparse as sp
+    import torch
+    import torch.distributed as dist
+    from cnmf_torch_b200 import cnmf as host
+    from cnmf_torch_b200.kl_engine import KlBatch, SparseKLEngine, pad2
+    from cnmf_torch_b200.synth import ledger_seeds
+    rank, world, local, dev = _dist_setup()
+    ks, R = CFG3["ks"], CFG3["replicates"]
+    x = _cfg3_matrix()
+    xs = sp.csr_matrix(x)
+    seeds = ledger_seeds(len(ks) * R, seed=14)
+    ledger = [(k, int(seeds[i * R + r])) for i, k in enumerate(ks) for r in range(R)]      # cnmf.py:744 order
+    mine = list(host.worker_filter(ledger, rank, world))
+    by_k = {}
+    for k, sd in mine:
+        by_k.setdefault(k, []).append(sd)
+    eng = SparseKLEngine(xs, device=dev, init_device="cuda")
+    stacks = {}
+    for k in by_k:
+        stacks.setdefault(pad2(k), []).append(k)
+    batches = [KlBatch(eng, None, None, None, 0.0, 0.0, 0.0, 0.0, 1e-16,
+                       groups=[(k,) + tuple(eng._init_for(k, by_k[k])) for k in group]) for group in stacks.values()]
+    n_mine = len(mine)
+
+    def one_step():
+        for b in batches:
+            b.iterate(ITERS_PER_STEP)
+
+    # dominant kernel: the H half-step (slab kernel) of the tallest stack, timed alone through one iteration's events
+    big = max(batches, key=lambda b: b.R * b.Kp)
+    big.iterate(1)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    big.iterate(4)
+    e1.record()
+    torch.cuda.synchronize()
+    it_ms = e0.elapsed_time(e1) / 4
+    launches0 = sum(b.launches for b in batches)
+    ms_total, clocks = _timed_steps(args, one_step, world, local)
+    launches = sum(b.launches for b in batches) - launches0
+    losses = [b.read_loss() for b in batches]
+    assert all(np.isfinite(l).all() for l in losses)
+    del batches, big
+
+    def e2e_step():
+        e = SparseKLEngine(xs, device=dev, init_device="cuda")
+        res = e.factorize_many(list(by_k), by_k, tol=0.0, max_iter=CFG3["e2e_iters"])
+        h2d = xs.data.nbytes * 2 + xs.indices.nbytes * 2 + xs.indptr.nbytes + (xs.shape[1] + 1) * 4
+        d2h = sum(r.W.nbytes + (CFG3["e2e_iters"] // 10 + 1) * len(by_k[k]) * 8 for k, r in res.items())
+        return h2d, d2h
+    e2e_step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    t0 = time.perf_counter()
+    h2d, d2h = e2e_step()
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    ms_total, e2e_s, it_ms_max = _max_over_ranks([ms_total, e2e_s, it_ms], dev, world)
+    jobs = len(ledger)
+    value = jobs * ITERS_PER_STEP * args.steps / (ms_total * 1e-3)
+    if rank == 0:
+        peaks, src = _peaks()
+        nnz = int(xs.nnz)
+        rk = sum(len(v) * k for k, v in by_k.items() if pad2(k) == max(stacks))       # K x replicates of the big stack
+        r_big = sum(len(v) for k, v in by_k.items() if pad2(k) == max(stacks))
+        # algorithmic bytes of one batched iteration of that stack (SURVEY 8d): X's CSR twice + factors read and written
+        abytes = 2 * (8 * nnz + 4 * (x.shape[0] + 1)) + 8 * rk * (x.shape[0] + x.shape[1])
+        aflops = 2.0 * 2 * nnz * 2 * rk                 # 2 half-steps x (s and numerator) x K FMAs per entry
+        fma_peak = 148 * 128 * 2 * (clocks["sm_mhz"] or 1900.0) * 1e6 / 1e12
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f16 operands, f32 accumulation", "data": "synthetic", "config": _config("cfg3"),
+            "e2e": {"value": jobs * CFG3["e2e_iters"] / e2e_s, "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+                    "d2h_bytes_per_step": int(d2h)},
+            "gpu_launches": int(launches), "clocks": clocks,
+            "roofline": {"bound": "hbm", "achieved": abytes / (it_ms_max * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
+                         "unit": "GB/s", "frac": abytes / (it_ms_max * 1e-3) / 1e9 / peaks["hbm_gbs"],
+                         "traffic": _traffic_from_profile(KL_PROFILE_CSV, "kl_slab_kernel"),
+                         "kernel": f"one batched KL iteration of the Kp={max(stacks)} stack on rank 0 ({r_big} replicates): "
+                                   f"kl_slab_kernel x2 + finish + column sums", "kernel_ms": it_ms_max,
+                         "peak_source": src,
+                         "note": "the algorithmic bytes are tiny against the arithmetic: this path is bound by the fp32 FMA "
+                                 "pipe (instruction issue), see roofline_fma"},
+            "roofline_fma": {"bound": "fp32 FMA pipe", "achieved": aflops / (it_ms_max * 1e-3) / 1e12, "peak": fma_peak,
+                             "unit": "TFLOP/s", "frac": aflops / (it_ms_max * 1e-3) / 1e12 / fma_peak,
+                             "peak_source": "148 SMs x 128 lanes x 2 x measured SM clock (FFMA / FHFMA issue rate "
+                                            "measured at 122-124 of 128 lanes/clk/SM: profiles/r02_simt_rate.txt)"},
+            "jobs_per_rank": n_mine,
+        }
+        if not args.no_cpu_baseline and world == 1:
+            import torch as _t
+            from oracle import nmf_oracle as no
+            cores = _use_all_host_threads(_t)
+            h0, w0 = no.init_random(float(x.mean(dtype=np.float64)), x.shape[0], x.shape[1], 9, 1)
+            t0 = time.perf_counter()
+            no.nmf_batch(x, h0, w0, beta_loss="kullback-leibler", tol=0.0, max_iter=4, check_every=4)
+            el = time.perf_counter() - t0
+            line["cpu_baseline"] = {"value": 4 / el, "unit": UNIT, "cores": int(cores), "kind": "port",
+                                    "sample": f"1 replicate x 4 KL MU iterations + objective, K=9, dense on the host, {el:.1f}s"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def run_cfg5(args):
+    """BASELINE.json configs[4]: online mode over row-sharded cells with the NCCL all-reduce of [A | B]."""
+    import torch
+    import torch.distributed as dist
+    from cnmf_torch_b200 import dist as d
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    rank, world, local, dev = _dist_setup()
+    n_total, K, R, chunk = CFG5["cells"], CFG5["k"], CFG5["replicates"], CFG5["chunk"]
+    lo, hi = d.shard_rows(n_total, rank, world)
+    xd = _cfg5_block_device(hi - lo, rank, dev)
+    eng = DenseFrobeniusEngine(xd, device=dev, row_group=dist.group.WORLD if world > 1 else None, row_offset=lo,
+                               init_device="cuda")
+    seeds = list(range(R))
+    prof = {}
+
+    def one_step():
+        res = eng.factorize_online(K, seeds=seeds, tol=0.0, max_pass=1, chunk_size=chunk, chunk_max_iter=200,
+                                   profile=prof)
+        prof["last"] = res
+    ms_total, clocks = _timed_steps(args, one_step, world, local)
+    res = prof["last"]
+    ar_ms = prof.get("allreduce_ms", 0.0)
+    ms_total, ar_ms = _max_over_ranks([ms_total, ar_ms], dev, world)
+    value = R * args.steps / (ms_total * 1e-3)
+    if rank == 0:
+        peaks, src = _peaks()
+        n_steps = args.steps + args.warmup
+        flops = 2.0 * 2 * n_total * CFG5["genes"] * K * R * 2      # x W^T twice (chunk pass + refresh) and h^T x
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms_total / args.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "tf32", "data": "synthetic (drawn on the device)", "config": _config("cfg5"),
+            "e2e": None, "gpu_launches": int(res.launches), "clocks": clocks,
+            "online": {"inner_iterations_per_pass": res.inner_iterations, "chunks_per_rank": (hi - lo + chunk - 1) // chunk,
+                       "allreduce_ms_per_pass": ar_ms / max(1, n_steps),
+                       "allreduce_share_of_pass": (ar_ms / max(1, n_steps)) / (ms_total / args.steps) if world > 1 else 0.0,
+                       "allreduce_bytes_per_chunk_step": int(R * 16 * (16 + CFG5["genes"]) * 4)},
+            "roofline": {"bound": "tensor", "achieved": flops / (ms_total / args.steps * 1e-3) / 1e12 * 0.75,
+                         "peak": peaks["bf16_tflops"] / 2.0 * world, "unit": "TFLOP/s",
+                         "frac": flops * 0.75 / (ms_total / args.steps * 1e-3) / 1e12 / (peaks["bf16_tflops"] / 2.0 * world),
+                         "traffic": None, "kernel": "whole pass: 3 GEMM sweeps over X (x W^T, h^T x, x W^T of the refresh) "
+                                                    "against the pass time, all ranks", "peak_source": f"{src} bf16 burst / 2 (tf32)"},
+        }
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def main():
@@ -268,6 +620,7 @@ def main():
     ap.add_argument("--steps", type=int, default=100)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--config", default="cfg2", choices=["cfg2", "cfg3", "cfg5"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
     ap.add_argument("--no-extras", action="store_true", help="skip the consensus / KL / online side measurements")
@@ -276,6 +629,10 @@ def main():
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     if args.impl == "reference":
         return run_reference(args)
+    if args.config == "cfg3":
+        return run_cfg3(args)
+    if args.config == "cfg5":
+        return run_cfg5(args)
 
     import torch
     import torch.distributed as dist
@@ -348,10 +705,11 @@ def main():
         peak = peaks["bf16_tflops"] / 2.0                # tf32 tensor rate = half the bf16 rate
         ach = flops / (k_ms * 1e-3) / 1e12
         roof = {"bound": "tensor", "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
-                # dram__bytes_read.sum + dram__bytes_write.sum of this launch in the committed `ncu --set full`
-                # capture (profiles/r01_tc_half_step_f_full_raw.csv): 161.5 + 59.5 MB; algorithmic bytes
-                # (X + W copy + H read + H and H-copy write) = 216 MB
-                "traffic": 221.0e6,
+                # dram__bytes_read.sum + dram__bytes_write.sum of this launch, read from the committed `ncu --set full`
+                # capture of the same launch (null when no capture of this round's kernel is committed); algorithmic
+                # bytes (X + W copy + H read + H and H-copy write) = 216 MB
+                "traffic": _traffic_from_profile(TC_PROFILE_CSV, "tc_half_step_kernel"),
+                "traffic_source": "profiles/" + TC_PROFILE_CSV,
                 "kernel": f"tc_half_step_kernel<{big.Kp},HALS> (H half-step, K={big.Ks}, R={big.R}, live update)",
                 "kernel_ms": k_ms, "padded_frac": ach / peak * big.Kp * big.R / cols,
                 "peak_source": f"{src} bf16 burst / 2 (tf32)"}
@@ -432,17 +790,11 @@ def main():
             "warmup": args.warmup, "ms_per_step": ms_total / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "tf32" if impl != _lib.IMPL_SIMT else "f32",
             "data": "synthetic",
-            "config": {"workload": WORKLOAD, "replicates_per_gpu": len(KS) * REPLICATES,
-                       "l2_flush_between_steps": True, "path": args.path,
-                       "k_batches_on_separate_streams": bool(args.streams),
-                       "e2e_step": f"DenseFrobeniusEngine(X_pinned).factorize_many(K=7..12, seeds, hals, tol=0, "
-                                   f"max_iter={E2E_ITERS}) per step: H2D of X from pinned host memory, random inits "
-                                   f"drawn by the device generator (init_device='cuda', nmf-torch's use_gpu=True "
-                                   f"stream), D2H of the objectives every 10 iterations and of all spectra",
-                       "e2e_host_generator_init": {
-                           "value": len(KS) * REPLICATES * E2E_ITERS * world / e2e_host_s, "unit": UNIT,
-                           "note": "same step with init_device='cpu': inits drawn by torch's host generator (the "
-                                   "reference's use_gpu=False stream, the oracle's) and uploaded"}},
+            "config": _config("cfg2", args.path, args.streams),
+            "e2e_host_generator_init": {
+                "value": len(KS) * REPLICATES * E2E_ITERS * world / e2e_host_s, "unit": UNIT,
+                "note": "the e2e step with init_device='cpu': inits drawn by torch's host generator (the reference's "
+                        "use_gpu=False stream, the oracle's) and uploaded"},
             "e2e": {"value": e2e_val, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof,
         }

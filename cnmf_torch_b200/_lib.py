@@ -13,6 +13,7 @@ LIB_PATH = os.path.join(_PKG, "lib", "libcnmf_b200.so")
 
 ALGO_MU, ALGO_HALS = 0, 1
 IMPL_AUTO, IMPL_SIMT, IMPL_TCGEN05 = 0, 1, 2
+KL_IMPL_GATHER, KL_IMPL_SLAB = 0, 1
 MAX_KP = 32
 
 ERR_INVALID, ERR_CUDA, ERR_WORKSPACE, ERR_UNSUPPORTED = -1, -2, -3, -4
@@ -39,7 +40,7 @@ class KlProblem(C.Structure):
         ("n_cells", i64), ("n_genes", i64), ("nnz", i64),
         ("row_ptr", vp), ("col_idx", vp), ("val", vp),
         ("t_row_ptr", vp), ("t_col_idx", vp), ("t_val", vp),
-        ("R", i32), ("K", i32), ("Kp", i32), ("reserved", i32),
+        ("R", i32), ("K", i32), ("Kp", i32), ("impl", i32),
         ("Hr", vp), ("Wt", vp),
         ("active", vp),
         ("l1_H", f32), ("l2_H", f32), ("l1_W", f32), ("l2_W", f32), ("eps", f32), ("pad0", f32),
@@ -80,6 +81,8 @@ SIGNATURES = {
     "cnmf_b200_kl_workspace_bytes": (i64, [C.POINTER(KlProblem)]),
     "cnmf_b200_kl_iterate": (i32, [C.POINTER(KlProblem), i32, vp]),
     "cnmf_b200_kl_objective": (i32, [C.POINTER(KlProblem), vp]),
+    "cnmf_b200_kl_range_flag": (i32, [C.POINTER(KlProblem), C.POINTER(i32), vp]),
+    "cnmf_b200_kl_range_flag_clear": (i32, [C.POINTER(KlProblem), vp]),
     "cnmf_b200_l2_normalize": (i32, [vp, i64, i32, i32, vp, i64, vp]),
     "cnmf_b200_kmeanspp_workspace_bytes": (i64, [i32, i32, i32]),
     "cnmf_b200_kmeanspp": (i32, [vp, i64, i32, i32, i32, i32, i32, vp, vp, vp, vp, vp, vp]),

@@ -259,7 +259,14 @@ class cNMF:
                                         "l1_ratio_H", "batch_max_iter", "online_max_pass", "online_chunk_size",
                                         "online_chunk_max_iter", "online_h_tol", "online_w_tol") if k in kw}
         sel = run_params.iloc[jobs, :]
-        if (kw.get("mode", "batch") == "batch" and hasattr(engine, "factorize_many") and not max_batch
+        mode = kw.get("mode", "batch")
+        if mode == "online" and not hasattr(engine, "factorize_online"):
+            # sufficient statistics exist for the Frobenius loss only: nmf-torch itself switches beta != 2 to batch
+            # mode, and cNMF always writes mode='online' (cnmf.py:765)
+            print("Online mode only works for beta_loss='frobenius'. Switch to batch mode.")
+            mode = "batch"
+            engine_kw["mode"] = "batch"
+        if (mode == "batch" and hasattr(engine, "factorize_many") and not max_batch
                 and engine_kw.get("init", "random") == "random"):
             # all K at once: K-batches overlap on separate streams (engine.factorize_many)
             from .nmf import _reg
@@ -273,7 +280,7 @@ class cNMF:
                                         max_iter=int(engine_kw.get("batch_max_iter", 500)), **reg)
             self._write_spectra(res, groups, var_names, whole_ledger=len(sel) == len(run_params))
             return
-        if (kw.get("mode", "batch") == "online" and hasattr(engine, "factorize_online_many") and not max_batch
+        if (mode == "online" and hasattr(engine, "factorize_online_many") and not max_batch
                 and engine_kw.get("init", "random") == "random"):
             # the reference's default mode: K values sharing a padded Kp run as one stack
             from .nmf import _reg

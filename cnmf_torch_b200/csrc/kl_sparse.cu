@@ -16,6 +16,8 @@
 #include <cuda_fp16.h>
 
 #include "common.cuh"
+#include "kl_slab.cuh"
+#include "kl_tables.cuh"
 
 namespace cnmf {
 
@@ -155,28 +157,31 @@ __device__ __forceinline__ void kl_apply_update(float (&h)[KP], const float (&nu
 //    [block, 2 block), ... -- so that the threads resident at one time gather rows of the fixed factor from one or two
 //    cell blocks (tens of MB, L2-resident) instead of from all cells (240 MB of fp16 H at 100 000 cells, R = 100:
 //    every gather a DRAM access).  "Virtual row" v = b * M + row; with nb = 1 it is the row itself.
-struct KlSegs {
-  const int* vseg_ptr;      // [V + 1] first segment of each virtual row, V = nb * M
-  const int* row_slot_ptr;  // [M + 1] nb == 1: first partial slot of each cut row (rows of one segment own none)
-  const int* seg_vrow;      // [nseg]
-  const int* seg_beg;       // [nseg] first entry of the segment
-  const int* vend;          // [V] end of each virtual row's entries (nb == 1: row_ptr + 1)
-  const int* multi_rows;    // nb == 1: [n_multi] rows that were cut (any order)
-  const int* n_multi;       // [1]
-  float* part;              // [slots x R*KP]; nb > 1: one slot per segment
-  int seg_len;              // entries per segment
-  int nb;                   // column blocks
-};
 
 template <int KP, bool SEG>
 __global__ void __launch_bounds__(KL_THREADS) kl_half_step_kernel(
     const int* __restrict__ row_ptr, const int* __restrict__ col_idx, const float* __restrict__ val, int64_t M,
     const __half* __restrict__ F, float* __restrict__ state, __half* __restrict__ state_h,
     const float* __restrict__ fsum, const uint8_t* __restrict__ active, int R, float l1, float l2, float eps,
-    const KlSegs sg) {
+    const KlSegs sg, const int gr) {
   const int64_t g = (int64_t)blockIdx.x * KL_THREADS + threadIdx.x;
-  const int64_t unit = g / R;             // row, or segment
-  const int r = (int)(g - unit * R);
+  int64_t unit;                           // row, or segment
+  int r;
+  if (gr > 0) {
+    // replicate-group-major numbering: all units for replicates [0, gr), then [gr, 2 gr), ...  The CTAs resident at
+    // one time then gather the fixed factor of ONE group of gr replicates -- n_cols * gr * KP * 2 bytes, which the
+    // L1 holds when gr is small -- instead of all R replicates' (L2 only).
+    const int64_t units = SEG ? (int64_t)sg.vseg_ptr[M * sg.nb] : M;
+    const int64_t per_group = units * gr;
+    const int64_t grp = g / per_group;
+    const int64_t within = g - grp * per_group;
+    unit = within / gr;
+    r = (int)(grp * gr + (within - unit * gr));
+    if (r >= R) return;
+  } else {
+    unit = g / R;
+    r = (int)(g - unit * R);
+  }
   int64_t row = unit;
   int beg, end, slot = -1;
   if (SEG) {
@@ -521,6 +526,22 @@ static int launch_colsum(const float* A, int64_t L, int64_t C, float* out, doubl
   return 0;
 }
 
+// gather path: its fp16 copies saturate at 65504; an entry beyond that raises the range flag (checked on the masters
+// at the start and at the end of every cnmf_b200_kl_iterate call) so that the host can refuse instead of going on
+__global__ void __launch_bounds__(256) kl_range_check_kernel(const float* __restrict__ a, int64_t n, int* __restrict__ flag) {
+  bool bad = false;
+  for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < n; i += (int64_t)gridDim.x * 256) bad |= !(a[i] <= 65504.f);
+  if (bad) atomicOr(flag, 1);
+}
+static int launch_range_check(const float* a, int64_t n, int* flag, cudaStream_t st) {
+  int64_t blocks = ceil_div(n, 256 * 8);
+  if (blocks > 148 * 8) blocks = 148 * 8;
+  if (blocks < 1) blocks = 1;
+  kl_range_check_kernel<<<(unsigned)blocks, 256, 0, st>>>(a, n, flag);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
 static int launch_to_half(const float* src, __half* dst, int64_t n, cudaStream_t st) {
   if (n == 0) return 0;
   int64_t blocks = ceil_div(n, 256 * 8);
@@ -536,18 +557,20 @@ static int launch_to_half(const float* src, __half* dst, int64_t n, cudaStream_t
 static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t M, const __half* F, float* state,
                           __half* state_h, const float* fsum, const uint8_t* active, int R, int Kp, float l1, float l2,
                           float eps, cudaStream_t st, const KlSegs* sg = nullptr, int64_t nseg_max = 0,
-                          int64_t multi_max = 0) {
-  const int64_t blocks = ceil_div((sg ? nseg_max : M) * R, KL_THREADS);
+                          int64_t multi_max = 0, int gr = 0) {
+  if (gr >= R) gr = 0;
+  const int64_t Rpad = gr > 0 ? ceil_div(R, gr) * gr : R;   // group-major numbering: the last group is padded
+  const int64_t blocks = ceil_div((sg ? nseg_max : M) * Rpad, KL_THREADS);
   CNMF_CHECK_ARG(blocks < (1ll << 31), "kl: rows * replicates too large for one launch");
   if (sg == nullptr) {
     KlSegs none{};
     KL_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, false><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
-                             rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, none)));
+                             rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, none, gr)));
     CNMF_LAUNCH_CHECK();
     return 0;
   }
   KL_DISPATCH_KP(Kp, (kl_half_step_kernel<KP, true><<<(unsigned)blocks, KL_THREADS, 0, st>>>(
-                           rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, *sg)));
+                           rp, ci, v, M, F, state, state_h, fsum, active, R, l1, l2, eps, *sg, gr)));
   CNMF_LAUNCH_CHECK();
   if (sg->nb > 1) {
     const int64_t fb = ceil_div(M * R, KL_THREADS);
@@ -588,18 +611,19 @@ static int kl_col_block(int64_t n_cols, int R, int Kp) {
   while (2 * (b * 2) * row_bytes <= KL_L2_BUDGET) b *= 2;
   return b < n_cols ? (int)b : 0;
 }
+// Replicates per group of the cell-major half-step (gathers rows of W): as many as keep one group's fp16 slice of W,
+// n_genes * gr * Kp * 2 bytes, within an L1 budget.  0 = no grouping.  (CNMF_B200_KL_GR overrides: dev knob.)
+static int kl_rep_group(int64_t n_genes, int Kp) {
+  static const int forced = [] { const char* e = getenv("CNMF_B200_KL_GR"); return e ? atoi(e) : -1; }();
+  if (forced >= 0) return forced;
+  return 0;
+}
 // bounds of the table
-static int64_t kl_nseg_max(int64_t V, int64_t nnz, int seg) { return V + nnz / seg; }
 static int64_t kl_multi_max(int64_t nnz, int seg) { return nnz / seg; }            // rows longer than seg
 static int64_t kl_slot_max(int64_t V, int64_t nnz, int seg, int nb) {              // partial slots
   return nb > 1 ? kl_nseg_max(V, nnz, seg) : 2 * (nnz / seg) + 2;
 }
 
-struct KlSegLayout {
-  int64_t off_vsp, off_rslot, off_svrow, off_sbeg, off_multi, off_nmulti, off_vbeg, off_vend;
-  int seg, block, nb;
-  int64_t V;
-};
 
 static int64_t kl_seg_layout(int64_t M, int64_t n_cols, int64_t nnz, int R, int Kp, bool allow_blocks, int64_t off,
                              KlSegLayout* o) {
@@ -615,11 +639,29 @@ static int64_t kl_seg_layout(int64_t M, int64_t n_cols, int64_t nnz, int R, int 
   o->off_nmulti = off; off += 256;
   o->off_vbeg = off; if (o->nb > 1) off += align_up(o->V * 4, 256);
   o->off_vend = off; if (o->nb > 1) off += align_up(o->V * 4, 256);
+  o->all_partial = false;
   return off;
 }
 
-static int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, char* ws, const KlSegLayout& o,
-                             float* part, KlSegs* out, cudaStream_t st) {
+int64_t kl_seg_layout_explicit(int64_t M, int64_t n_cols, int64_t nnz, int seg, int block, int64_t off, KlSegLayout* o) {
+  o->seg = seg;
+  o->block = block;
+  o->nb = block > 0 ? (int)ceil_div(n_cols, block) : 1;
+  o->V = M * o->nb;
+  o->all_partial = true;
+  o->off_vsp = off; off += align_up((o->V + 1) * 4, 256);
+  o->off_rslot = off;
+  o->off_svrow = off; off += align_up(kl_nseg_max(o->V, nnz, o->seg) * 4, 256);
+  o->off_sbeg = off; off += align_up(kl_nseg_max(o->V, nnz, o->seg) * 4, 256);
+  o->off_multi = off;
+  o->off_nmulti = off; off += 256;
+  o->off_vbeg = off; if (o->nb > 1) off += align_up(o->V * 4, 256);
+  o->off_vend = off; if (o->nb > 1) off += align_up(o->V * 4, 256);
+  return off;
+}
+
+int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, char* ws, const KlSegLayout& o, float* part,
+                      KlSegs* out, cudaStream_t st) {
   int* vsp = reinterpret_cast<int*>(ws + o.off_vsp);
   int* rslot = reinterpret_cast<int*>(ws + o.off_rslot);
   int* svrow = reinterpret_cast<int*>(ws + o.off_svrow);
@@ -636,11 +678,12 @@ static int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, 
     CNMF_LAUNCH_CHECK();
     vbeg = vb; vend = ve;
   }
+  const bool partial = o.nb > 1 || o.all_partial;   // one partial slot per segment, empty virtual rows own none
   CNMF_CUDA(cudaMemsetAsync(nmulti, 0, 4, st));
-  kl_seg_scan_kernel<<<1, 1024, 0, st>>>(vbeg, vend, o.V, o.seg, o.nb > 1 ? 0 : 1, vsp, o.nb > 1 ? nullptr : rslot);
+  kl_seg_scan_kernel<<<1, 1024, 0, st>>>(vbeg, vend, o.V, o.seg, partial ? 0 : 1, vsp, partial ? nullptr : rslot);
   CNMF_LAUNCH_CHECK();
   kl_seg_fill_kernel<<<(unsigned)ceil_div(o.V, 256), 256, 0, st>>>(vbeg, o.V, o.seg, vsp, svrow, sbeg,
-                                                                   o.nb > 1 ? nullptr : multi, nmulti);
+                                                                   partial ? nullptr : multi, nmulti);
   CNMF_LAUNCH_CHECK();
   out->vseg_ptr = vsp; out->row_slot_ptr = rslot; out->seg_vrow = svrow; out->seg_beg = sbeg; out->vend = vend;
   out->multi_rows = multi; out->n_multi = nmulti; out->part = part; out->seg_len = o.seg; out->nb = o.nb;
@@ -649,12 +692,17 @@ static int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, 
 
 struct KlLayout {
   int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_wsq64, off_hsq64, off_cpart, off_opart, off_wh, off_hh, off_part, total;
+  int64_t off_flag, off_wcumX, off_wcumXt;   // slab path: range flag, static work split of the two matrices
   KlSegLayout segX, segXt;  // CSR(X): never column-blocked (gathers W, G rows); CSR(X^T): blocked over cells when H is large
   int nblk_obj;
+  bool slab;
 };
+
+static bool kl_use_slab(const cnmf_b200_kl_problem* p) { return p->impl == CNMF_B200_KL_IMPL_SLAB; }
 
 static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
   KlLayout l{};
+  l.slab = kl_use_slab(p);
   const int64_t C = (int64_t)p->R * p->Kp;
   const int64_t Lmax = p->n_cells > p->n_genes ? p->n_cells : p->n_genes;
   int64_t off = 0;
@@ -665,6 +713,23 @@ static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
   l.off_wsq64 = off; off += align_up(C * 8, 256);
   l.off_hsq64 = off; off += align_up(C * 8, 256);
   l.off_cpart = off; off += align_up(ceil_div(Lmax, CS_ROWS) * C * 4, 256);
+  l.off_flag = off; off += 256;
+  if (l.slab) {
+    // fp16 copies in the pair-interleaved layout [rows][RP][Kp/2] x 8 bytes; objective partials [SMs][R]
+    const int64_t C16 = (int64_t)((p->R + 1) / 2) * (p->Kp / 2) * 8;
+    l.nblk_obj = ks_sm_count();
+    l.off_opart = off; off += align_up((int64_t)l.nblk_obj * p->R * 8, 256);
+    l.off_wh = off; off += align_up(p->n_genes * C16, 256);
+    l.off_hh = off; off += align_up(p->n_cells * C16, 256);
+    off = kl_seg_layout_explicit(p->n_cells, p->n_genes, p->nnz, ks_seg_len(p->Kp), ks_block_cols(p->n_genes), off, &l.segX);
+    off = kl_seg_layout_explicit(p->n_genes, p->n_cells, p->nnz, ks_seg_len(p->Kp), ks_block_cols(p->n_cells), off, &l.segXt);
+    const int64_t sx = kl_nseg_max(l.segX.V, p->nnz, l.segX.seg), sxt = kl_nseg_max(l.segXt.V, p->nnz, l.segXt.seg);
+    l.off_wcumX = off; off += align_up((sx + 1) * 4, 256);
+    l.off_wcumXt = off; off += align_up((sxt + 1) * 4, 256);
+    l.off_part = off; off += align_up((sx > sxt ? sx : sxt) * C * 4, 256);
+    l.total = off;
+    return l;
+  }
   l.nblk_obj = (int)ceil_div(p->n_cells, KLO_ROWS);
   l.off_opart = off; off += align_up((int64_t)l.nblk_obj * p->R * 8, 256);
   l.off_wh = off; off += align_up(p->n_genes * C * 2, 256);   // fp16 gather copies of Wt and Hr
@@ -684,6 +749,8 @@ static int kl_check(const cnmf_b200_kl_problem* p, bool pointers) {
   CNMF_CHECK_ARG(p != nullptr, "kl: null problem");
   CNMF_CHECK_ARG(p->n_cells > 0 && p->n_genes > 0 && p->R > 0 && p->K > 0 && p->nnz >= 0, "kl: empty shape");
   CNMF_CHECK_ARG(p->nnz < (1ll << 31), "kl: nnz must fit int32 offsets");
+  CNMF_CHECK_ARG(p->impl == CNMF_B200_KL_IMPL_SLAB || p->impl == CNMF_B200_KL_IMPL_GATHER, "kl: unknown impl %d", p->impl);
+  CNMF_CHECK_ARG(p->n_cells < (1ll << 31) / 64 && p->n_genes < (1ll << 31) / 64, "kl: more than 2^25 rows or columns");
   CNMF_CHECK_ARG(p->Kp >= p->K && p->Kp % 2 == 0 && p->Kp <= CNMF_B200_MAX_KP,
                  "kl: Kp=%d must be even, >= K=%d and <= %d", p->Kp, p->K, CNMF_B200_MAX_KP);
   if (pointers) {
@@ -700,7 +767,53 @@ static int kl_check(const cnmf_b200_kl_problem* p, bool pointers) {
   return 0;
 }
 
-static int kl_objective_impl(const cnmf_b200_kl_problem* p, const KlLayout& l, cudaStream_t st) {
+// arguments of the slab kernel for CSR(X) (rows = cells, fixed factor W) or CSR(X^T) (rows = genes, fixed factor H)
+static KlSlabArgs kl_slab_args(const cnmf_b200_kl_problem* p, const KlLayout& l, bool transposed, const KlSegs& sg,
+                               int grid) {
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  const uint2* W16 = reinterpret_cast<const uint2*>(ws + l.off_wh);
+  const uint2* H16 = reinterpret_cast<const uint2*>(ws + l.off_hh);
+  const KlSegLayout& o = transposed ? l.segXt : l.segX;
+  KlSlabArgs a{};
+  a.col_idx = transposed ? p->t_col_idx : p->col_idx;
+  a.val = transposed ? p->t_val : p->val;
+  a.M = (int)(transposed ? p->n_genes : p->n_cells);
+  a.C = (int)(transposed ? p->n_cells : p->n_genes);
+  a.F16 = transposed ? H16 : W16;
+  a.S16 = transposed ? W16 : H16;
+  a.R = p->R;
+  a.RP = (p->R + 1) / 2;
+  a.ngroups = ks_num_groups(p->R, p->Kp);
+  a.active = p->active;
+  a.eps = p->eps;
+  a.vseg_ptr = sg.vseg_ptr; a.seg_vrow = sg.seg_vrow; a.seg_beg = sg.seg_beg; a.vend = sg.vend;
+  a.wcum = reinterpret_cast<const int*>(ws + (transposed ? l.off_wcumXt : l.off_wcumX));
+  a.nb = o.nb; a.block = o.block; a.seg_len = o.seg;
+  a.part = sg.part;
+  a.opart = nullptr;
+  a.grid = grid;
+  return a;
+}
+
+// slab path: fp16 copies of both factors from the fp32 masters, segment table + work split of CSR(X) (and CSR(X^T))
+static int kl_slab_prepare(const cnmf_b200_kl_problem* p, const KlLayout& l, bool both, KlSegs* sgX, KlSegs* sgXt,
+                           cudaStream_t st) {
+  char* ws = reinterpret_cast<char*>(p->workspace);
+  int* flag = reinterpret_cast<int*>(ws + l.off_flag);
+  float* part = reinterpret_cast<float*>(ws + l.off_part);
+  CNMF_TRY(launch_kl_to_half_pairs(p->Wt, ws + l.off_wh, p->n_genes, p->R, p->Kp, flag, st));
+  CNMF_TRY(launch_kl_to_half_pairs(p->Hr, ws + l.off_hh, p->n_cells, p->R, p->Kp, flag, st));
+  CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, sgX, st));
+  CNMF_TRY(launch_kl_work_scan(*sgX, l.segX.V, p->Kp, reinterpret_cast<int*>(ws + l.off_wcumX), st));
+  if (both) {
+    CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, sgXt, st));
+    CNMF_TRY(launch_kl_work_scan(*sgXt, l.segXt.V, p->Kp, reinterpret_cast<int*>(ws + l.off_wcumXt), st));
+  }
+  return 0;
+}
+
+static int kl_objective_impl(const cnmf_b200_kl_problem* p, const KlLayout& l, cudaStream_t st,
+                             const KlSegs* sgX = nullptr) {
   char* ws = reinterpret_cast<char*>(p->workspace);
   float* wsum = reinterpret_cast<float*>(ws + l.off_wsum);
   float* hsum = reinterpret_cast<float*>(ws + l.off_hsum);
@@ -711,10 +824,18 @@ static int kl_objective_impl(const cnmf_b200_kl_problem* p, const KlLayout& l, c
   const int64_t C = (int64_t)p->R * p->Kp;
   CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, wsum64, cpart, st));
   CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, hsum64, cpart, st));
-  const unsigned grid = (unsigned)ceil_div((int64_t)l.nblk_obj * p->R, KL_THREADS);
-  KL_DISPATCH_KP(p->Kp, (kl_xlogs_kernel<KP><<<grid, KL_THREADS, 0, st>>>(p->row_ptr, p->col_idx, p->val, p->n_cells,
-                                                                              p->Hr, p->Wt, p->R, p->eps, opart)));
-  CNMF_LAUNCH_CHECK();
+  if (l.slab) {
+    // sum x log(s) by the slab kernel on the fp16 copies (the caller has made them current): [SMs][R] partials
+    CNMF_CUDA(cudaMemsetAsync(opart, 0, (size_t)l.nblk_obj * p->R * 8, st));
+    KlSlabArgs a = kl_slab_args(p, l, /*transposed=*/false, *sgX, l.nblk_obj);
+    a.opart = opart;
+    CNMF_TRY(launch_kl_slab(a, p->Kp, 1, st));
+  } else {
+    const unsigned grid = (unsigned)ceil_div((int64_t)l.nblk_obj * p->R, KL_THREADS);
+    KL_DISPATCH_KP(p->Kp, (kl_xlogs_kernel<KP><<<grid, KL_THREADS, 0, st>>>(p->row_ptr, p->col_idx, p->val, p->n_cells,
+                                                                                p->Hr, p->Wt, p->R, p->eps, opart)));
+    CNMF_LAUNCH_CHECK();
+  }
   double* wsq64 = nullptr;
   double* hsq64 = nullptr;
   if (p->l2_H != 0.f || p->l2_W != 0.f) {   // hsum / wsum (fp32 outputs) are scratch here: the next iteration recomputes them
@@ -774,28 +895,51 @@ int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* s
   float* hsum = reinterpret_cast<float*>(ws + l.off_hsum);
   float* cpart = reinterpret_cast<float*>(ws + l.off_cpart);
   const int64_t C = (int64_t)p->R * p->Kp;
+  if (n_iters == 0) return 0;
+  if (l.slab) {
+    KlSegs sgX{}, sgXt{};
+    int* flag = reinterpret_cast<int*>(ws + l.off_flag);
+    CNMF_TRY(kl_slab_prepare(p, l, true, &sgX, &sgXt, st));   // stateless: copies and tables are rebuilt per call
+    const KlSlabArgs aX = kl_slab_args(p, l, false, sgX, 0), aXt = kl_slab_args(p, l, true, sgXt, 0);
+    for (int it = 0; it < n_iters; ++it) {
+      CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, nullptr, cpart, st));
+      CNMF_TRY(launch_kl_slab(aX, p->Kp, 0, st));
+      CNMF_TRY(launch_kl_finish_slab(p->n_cells, p->Hr, ws + l.off_hh, wsum, p->active, p->R, p->Kp, p->l1_H, p->l2_H,
+                                     p->eps, sgX, flag, st));
+      CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, nullptr, cpart, st));
+      CNMF_TRY(launch_kl_slab(aXt, p->Kp, 0, st));
+      CNMF_TRY(launch_kl_finish_slab(p->n_genes, p->Wt, ws + l.off_wh, hsum, p->active, p->R, p->Kp, p->l1_W, p->l2_W,
+                                     p->eps, sgXt, flag, st));
+    }
+    if (p->err2 != nullptr) CNMF_TRY(kl_objective_impl(p, l, st, &sgX));
+    return 0;
+  }
   __half* Wh = reinterpret_cast<__half*>(ws + l.off_wh);
   __half* Hh = reinterpret_cast<__half*>(ws + l.off_hh);
-  if (n_iters > 0) CNMF_TRY(launch_to_half(p->Wt, Wh, p->n_genes * C, st));  // Hh is written by the first H half-step
+  int* gflag = reinterpret_cast<int*>(ws + l.off_flag);
+  CNMF_TRY(launch_range_check(p->Hr, p->n_cells * C, gflag, st));
+  CNMF_TRY(launch_range_check(p->Wt, p->n_genes * C, gflag, st));
+  CNMF_TRY(launch_to_half(p->Wt, Wh, p->n_genes * C, st));  // Hh is written by the first H half-step
   KlSegs sgX{}, sgXt{};
   float* part = reinterpret_cast<float*>(ws + l.off_part);
-  if (n_iters > 0) {  // stateless: the tables are rebuilt per call (a few tiny kernels against >= 1 iteration)
-    CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, &sgX, st));
-    CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, &sgXt, st));
-  }
+  // stateless: the tables are rebuilt per call (a few tiny kernels against >= 1 iteration)
+  CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, &sgX, st));
+  CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, &sgXt, st));
   const int64_t nsX = kl_nseg_max(l.segX.V, p->nnz, l.segX.seg), nsXt = kl_nseg_max(l.segXt.V, p->nnz, l.segXt.seg);
   const int64_t mmX = kl_multi_max(p->nnz, l.segX.seg), mmXt = kl_multi_max(p->nnz, l.segXt.seg);
   for (int it = 0; it < n_iters; ++it) {
     CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, nullptr, cpart, st));
     CNMF_TRY(launch_kl_half(p->row_ptr, p->col_idx, p->val, p->n_cells, Wh, p->Hr, Hh, wsum, p->active, p->R, p->Kp,
-                            p->l1_H, p->l2_H, p->eps, st, &sgX, nsX, mmX));
+                            p->l1_H, p->l2_H, p->eps, st, &sgX, nsX, mmX, kl_rep_group(p->n_genes, p->Kp)));
     if (it == 0 && p->active != nullptr)  // frozen replicates skip the write: their copy must exist too
       CNMF_TRY(launch_to_half(p->Hr, Hh, p->n_cells * C, st));
     CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, nullptr, cpart, st));
     CNMF_TRY(launch_kl_half(p->t_row_ptr, p->t_col_idx, p->t_val, p->n_genes, Hh, p->Wt, Wh, hsum, p->active, p->R,
                             p->Kp, p->l1_W, p->l2_W, p->eps, st, &sgXt, nsXt, mmXt));
   }
-  if (p->err2 != nullptr && n_iters > 0) CNMF_TRY(kl_objective_impl(p, l, st));
+  CNMF_TRY(launch_range_check(p->Hr, p->n_cells * C, gflag, st));
+  CNMF_TRY(launch_range_check(p->Wt, p->n_genes * C, gflag, st));
+  if (p->err2 != nullptr) CNMF_TRY(kl_objective_impl(p, l, st));
   return 0;
 }
 
@@ -803,7 +947,30 @@ int cnmf_b200_kl_objective(const cnmf_b200_kl_problem* p, void* stream) {
   reset_launch_count();
   CNMF_TRY(kl_check(p, true));
   CNMF_CHECK_ARG(p->err2 != nullptr, "kl_objective: err2 is NULL");
-  return kl_objective_impl(p, kl_layout(p), (cudaStream_t)stream);
+  const KlLayout l = kl_layout(p);
+  if (l.slab) {
+    KlSegs sgX{}, sgXt{};
+    CNMF_TRY(kl_slab_prepare(p, l, false, &sgX, &sgXt, (cudaStream_t)stream));
+    return kl_objective_impl(p, l, (cudaStream_t)stream, &sgX);
+  }
+  return kl_objective_impl(p, l, (cudaStream_t)stream);
+}
+
+int cnmf_b200_kl_range_flag(const cnmf_b200_kl_problem* p, int32_t* flag_host, void* stream) {
+  CNMF_TRY(kl_check(p, true));
+  CNMF_CHECK_ARG(flag_host != nullptr, "kl_range_flag: null output");
+  const KlLayout l = kl_layout(p);
+  cudaStream_t st = (cudaStream_t)stream;
+  CNMF_CUDA(cudaMemcpyAsync(flag_host, reinterpret_cast<char*>(p->workspace) + l.off_flag, 4, cudaMemcpyDeviceToHost, st));
+  CNMF_CUDA(cudaStreamSynchronize(st));
+  return 0;
+}
+
+int cnmf_b200_kl_range_flag_clear(const cnmf_b200_kl_problem* p, void* stream) {
+  CNMF_TRY(kl_check(p, true));
+  const KlLayout l = kl_layout(p);
+  CNMF_CUDA(cudaMemsetAsync(reinterpret_cast<char*>(p->workspace) + l.off_flag, 0, 4, (cudaStream_t)stream));
+  return 0;
 }
 
 }  // extern "C"

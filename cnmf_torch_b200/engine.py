@@ -249,13 +249,15 @@ class DenseFrobeniusEngine:
 
     def factorize_online(self, K: int, seeds=None, H0=None, W0=None, tol=1e-4, max_pass=20, chunk_size=5000,
                          chunk_max_iter=200, h_tol=0.05, w_tol=0.05, l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0,
-                         eps=EPS_DEFAULT, return_H=False, inner_batch=4, groups=None):
+                         eps=EPS_DEFAULT, return_H=False, inner_batch=4, groups=None, profile=None):
         """Online-mode Frobenius MU of R replicates (run_nmf(mode='online'), what cNMF configures at
         cnmf.py:757-771).  Per pass and per chunk of ``chunk_size`` cells: inner MU loop on h against the
         cached x W^T (stopping rule of cnmf.py:365-378), A += h^T h, B += h^T x, inner MU loop on W against
         (A, B); then H is refreshed on all cells and the objective decides convergence per replicate.
         With ``row_group`` the cells are sharded over ranks: A, B and the objective terms are summed with
-        one all-reduce per chunk; W stays replicated (every rank runs the same W loop on the same sums)."""
+        one all-reduce per chunk; W stays replicated (every rank runs the same W loop on the same sums).
+        ``profile`` (a dict): device time spent in the all-reduces of [A | B] is added to profile["allreduce_ms"]
+        (CUDA events around every collective; read after the last pass)."""
         from . import dist as _d
         if self.impl == _lib.IMPL_SIMT:
             raise NotImplementedError("online mode runs on the tcgen05 path (impl auto/tcgen05)")
@@ -327,6 +329,7 @@ class DenseFrobeniusEngine:
                                                      l1_H, l2_H, l1_W, l2_W, ptr(b.err2), st()), "objective_combine")
             return b.read_loss()
 
+        ar_events = []
         refresh_w_caches()
         init = objective()
         prev, cur = init.copy(), init
@@ -348,7 +351,14 @@ class DenseFrobeniusEngine:
                     check(L.cnmf_b200_dense_gemm_tf32(ptr(self.Xt) + 4 * lo, self.ldxt, G, c, ptr(Hop) + 4 * lo, ldh,
                                                       ptr(Bc), ldw, ptr(active), R, Kp, 0, st()), "gemm h^T x")
                     b.launches += 4
-                _d.allreduce_sum_([Ac, Bc], grp)          # the only data-path collective
+                if profile is not None and grp is not None:
+                    ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
+                    ev[0].record()
+                    _d.allreduce_sum_([Ac, Bc], grp)
+                    ev[1].record()
+                    ar_events.append(ev)
+                else:
+                    _d.allreduce_sum_([Ac, Bc], grp)      # the only data-path collective
                 check(L.cnmf_b200_axpy(ptr(A), ptr(Ac), A.numel(), st()), "axpy")
                 check(L.cnmf_b200_axpy(ptr(Bst), ptr(Bc), Bst.numel(), st()), "axpy")
                 inner(ptr(Bst), ldw, ptr(Wall), ldw, ptr(A), G, w_tol, l1_W, l2_W, 1)
@@ -370,6 +380,9 @@ class DenseFrobeniusEngine:
             if not alive.any():
                 break
         err = np.sqrt(np.maximum(2.0 * cur, 0.0))
+        if profile is not None and ar_events:
+            torch.cuda.synchronize()
+            profile["allreduce_ms"] = profile.get("allreduce_ms", 0.0) + float(sum(a.elapsed_time(b) for a, b in ar_events))
         inner = {"h": inner_total[0], "w": inner_total[1]}
         if groups is not None:   # a stack of several K: one result per K
             out = {}

@@ -1,9 +1,10 @@
 """Replicate-batched sparse KL engine (host side): CSR X and CSR X^T resident on one GPU, R
-replicates of one K interleaved in Hr [N x R*Kp] / Wt [G x R*Kp].  Replaces the per-replicate
+replicates interleaved in Hr [N x R*Kp] / Wt [G x R*Kp].  Replaces the per-replicate
 ``run_nmf(beta_loss='kullback-leibler')`` of /root/reference/src/cnmf/cnmf.py:805-821."""
 from __future__ import annotations
 
 import ctypes as C
+import math
 import os
 
 import numpy as np
@@ -12,7 +13,9 @@ import torch
 
 from . import _lib
 from ._lib import KlProblem, check, lib, ptr
-from .engine import EPS_DEFAULT, BatchResult, draw_init
+from .engine import EPS_DEFAULT, BatchResult, SeedInit, draw_init
+
+_KL_IMPL = {"slab": _lib.KL_IMPL_SLAB, "gather": _lib.KL_IMPL_GATHER}
 
 
 def pad2(k: int) -> int:
@@ -22,36 +25,48 @@ def pad2(k: int) -> int:
 
 
 class SparseKLEngine:
-    def __init__(self, X, device="cuda:0", init_device="cpu"):
+    def __init__(self, X, device="cuda:0", init_device="cpu", impl=None, normalise=True):
+        """``impl``: "gather" (coalesced L2-gather kernels, default) or "slab" (shared-memory slab kernels); env
+        CNMF_B200_KL_IMPL overrides the default.
+        ``normalise``: the kernels gather fp16 copies of the factors, so the engine works on X * c^2 with c the power
+        of two that brings mean(X * c^2) to about 1 -- KL multiplicative updates are exactly covariant (H, W scale
+        by c, a power of two: the same bits), and factor entries then sit in the middle of the fp16 range whatever
+        the units of X.  Results and objectives are returned in the units of X."""
         self.lib = lib()
         self.init_device = init_device   # which torch generator draws the 'random' init (engine.draw_init)
+        self.impl = _KL_IMPL[impl or os.environ.get("CNMF_B200_KL_IMPL", "gather")]
         if not torch.cuda.is_available():
             raise _lib.Cnmfb200Error("CUDA device required: cnmf_torch_b200 has no CPU path")
         self.device = torch.device(device)
         torch.cuda.set_device(self.device)
         if torch.is_tensor(X):
             X = X.cpu().numpy()
-        csr = sp.csr_matrix(X, dtype=np.float32)
-        self._csr_host = csr
+        csr = sp.csr_matrix(X, dtype=np.float32, copy=True)   # never touch the caller's buffers
         csr.eliminate_zeros()
         csr.sort_indices()
+        self._csr_host = csr
         if csr.nnz and float(csr.data.min()) < 0.0:
             raise ValueError("X must be non-negative")   # the kernels rely on stored entries being > 0
-        csc = csr.T.tocsr()
-        csc.sort_indices()
         self.N, self.G = csr.shape
         self.nnz = int(csr.nnz)
         if self.nnz >= 2 ** 31:
             raise ValueError("nnz must fit 32-bit offsets")
+        sum_x = float(csr.data.sum(dtype=np.float64))
+        self.x_mean = sum_x / (float(self.N) * float(self.G))         # of the caller's X: the init is the reference's
+        self.c = 1.0
+        if normalise and self.x_mean > 0:
+            self.c = 2.0 ** int(round(-0.5 * math.log2(self.x_mean)))
+        csc = csr.T.tocsr()
+        csc.sort_indices()
         dev = self.device
+        c2 = np.float32(self.c * self.c)
         up = lambda a, dt: torch.from_numpy(np.ascontiguousarray(a.astype(dt))).to(dev)
-        self.row_ptr, self.col_idx, self.val = up(csr.indptr, np.int32), up(csr.indices, np.int32), up(csr.data, np.float32)
-        self.t_row_ptr, self.t_col_idx, self.t_val = up(csc.indptr, np.int32), up(csc.indices, np.int32), up(csc.data, np.float32)
+        self.row_ptr, self.col_idx, self.val = up(csr.indptr, np.int32), up(csr.indices, np.int32), up(csr.data * c2, np.float32)
+        self.t_row_ptr, self.t_col_idx, self.t_val = up(csc.indptr, np.int32), up(csc.indices, np.int32), up(csc.data * c2, np.float32)
         out = torch.zeros(2, device=dev, dtype=torch.float64)
         check(self.lib.cnmf_b200_kl_constants(ptr(self.val), self.nnz, ptr(out), self._stream()), "kl_constants")
         o = out.cpu().numpy()
-        self.sumX, self.xlogx = float(o[0]), float(o[1])
-        self.x_mean = self.sumX / (float(self.N) * float(self.G))
+        self.sumX, self.xlogx = float(o[0]), float(o[1])               # of the scaled matrix the kernels see
 
     @staticmethod
     def _stream():
@@ -64,9 +79,16 @@ class SparseKLEngine:
         return draw_init(self.x_mean, self.N, self.N, 0, self.G, int(K), seeds, self.device,
                          init_device or self.init_device)
 
+    def _init_for(self, K, seeds):
+        """(H0, W0) host arrays from the host generator, or a SeedInit marker: the draw then happens on the device
+        (cnmf_b200_init_random, bit-identical to torch's CUDA generator) straight into the batch."""
+        if self.init_device == "cuda" and self.N * int(K) < 2 ** 31 and int(K) * self.G < 2 ** 31:
+            return SeedInit([int(s) for s in seeds]), None
+        return self.make_init(K, seeds)
+
     def new_batch(self, K, seeds=None, H0=None, W0=None, l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT):
         if H0 is None or W0 is None:
-            H0, W0 = self.make_init(K, seeds)
+            H0, W0 = self._init_for(K, seeds)
         return KlBatch(self, K, H0, W0, l1_H, l2_H, l1_W, l2_W, eps)
 
     def factorize(self, K, seeds=None, H0=None, W0=None, algo="mu", tol=1e-4, max_iter=500, l1_H=0.0, l2_H=0.0,
@@ -75,55 +97,118 @@ class SparseKLEngine:
         if algo != "mu":
             raise NotImplementedError("only multiplicative updates exist for beta_loss='kullback-leibler'")
         b = self.new_batch(K, seeds, H0, W0, l1_H, l2_H, l1_W, l2_W, eps)
-        R = b.R
-        init = b.objective()
-        prev, cur = init.copy(), init
-        trace = [(0, init.copy())]
-        n_iter = np.full(R, max_iter, dtype=np.int64)
-        alive = np.ones(R, dtype=bool)
-        it = 0
-        while it < max_iter and alive.any():
-            step = min(check_every, max_iter - it)
-            b.iterate(step)
-            it += step
-            cur = b.read_loss()
-            trace.append((it, cur.copy()))
-            if it % check_every == 0:
-                conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
-                if conv.any():
-                    n_iter[conv] = it
-                    alive &= ~conv
-                    b.set_active(alive)
-                prev = np.where(alive, cur, prev)
+        r = _run_kl_batch(b, tol, max_iter, check_every)
         W, H = b.results(return_H)
-        return BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_iter, trace=trace,
-                           launches=int(b.launches))
+        return BatchResult(W=W, H=H, launches=int(b.launches), **r)
+
+    def factorize_many(self, ks, seeds_by_k, algo="mu", tol=1e-4, max_iter=500, l1_H=0.0, l2_H=0.0, l1_W=0.0,
+                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False):
+        """Several K in one call (the shape of a cNMF run: K = 5..13 x 100 replicates).  K values that round up to
+        the same even Kp are stacked into ONE batch (K = 9, 10 -> Kp 10): the kernels only see Kp, a taller stack
+        fills the replicate groups of the slab kernel better (13 replicates of one K on one of 8 GPUs are 2 groups
+        and a third; 26 are 4 and a third), and X is streamed once for both.  A slab kernel launch occupies every SM,
+        so stacks run one after the other (no side streams as on the dense path).  Returns {K: BatchResult}."""
+        if algo != "mu":
+            raise NotImplementedError("only multiplicative updates exist for beta_loss='kullback-leibler'")
+        stacks = {}
+        for k in [int(k) for k in ks]:
+            stacks.setdefault(pad2(k), []).append(k)
+        out = {}
+        for group in stacks.values():
+            groups = [(k,) + tuple(self._init_for(k, seeds_by_k[k])) for k in group]
+            b = KlBatch(self, None, None, None, l1_H, l2_H, l1_W, l2_W, eps, groups=groups)
+            r = _run_kl_batch(b, tol, max_iter, check_every)
+            for k, sl, W, H in b.results_by_group(return_H):
+                out[k] = BatchResult(W=W, H=H, err=r["err"][sl], n_iter=r["n_iter"][sl],
+                                     trace=[(it, v[sl]) for it, v in r["trace"]], launches=int(b.launches))
+            del b
+        return out
+
+
+def _run_kl_batch(b: "KlBatch", tol, max_iter, check_every):
+    """run_nmf's batch loop on a resident KL batch: objective every ``check_every`` iterations, replicates with
+    prev <= cur or |prev - cur| / init < tol are frozen."""
+    R = b.R
+    init = b.objective()
+    prev, cur = init.copy(), init
+    trace = [(0, init.copy())]
+    n_iter = np.full(R, max_iter, dtype=np.int64)
+    alive = np.ones(R, dtype=bool)
+    it = 0
+    while it < max_iter and alive.any():
+        step = min(check_every, max_iter - it)
+        b.iterate(step)
+        it += step
+        cur = b.read_loss()
+        trace.append((it, cur.copy()))
+        if it % check_every == 0:
+            conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
+            if conv.any():
+                n_iter[conv] = it
+                alive &= ~conv
+                b.set_active(alive)
+            prev = np.where(alive, cur, prev)
+    return dict(err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_iter, trace=trace)
 
 
 class KlBatch:
-    def __init__(self, eng: SparseKLEngine, K, H0, W0, l1_H, l2_H, l1_W, l2_W, eps):
-        self.eng, self.K = eng, int(K)
-        self.R, self.Kp = int(W0.shape[0]), pad2(K)
+    """Replicates resident on the device.  ``groups`` = [(K, H0, W0) | (K, SeedInit, None), ...] stacks replicates of
+    different K that share the same even Kp (padding components are zero and stay zero)."""
+
+    def __init__(self, eng: SparseKLEngine, K, H0, W0, l1_H, l2_H, l1_W, l2_W, eps, groups=None):
+        if groups is None:
+            groups = [(int(K), H0, W0)]
+        self.eng = eng
+        self.Ks = [int(g[0]) for g in groups]
+        self.Rs = [len(g[1].seeds) if isinstance(g[1], SeedInit) else int(g[2].shape[0]) for g in groups]
+        self.K = max(self.Ks)
+        self.R, self.Kp = sum(self.Rs), pad2(self.K)
         if self.Kp > _lib.MAX_KP:
-            raise ValueError(f"n_components={K} exceeds the engine limit {_lib.MAX_KP}")
+            raise ValueError(f"n_components={self.K} exceeds the engine limit {_lib.MAX_KP}")
+        if any(pad2(k) != self.Kp for k in self.Ks):
+            raise ValueError("all K of one stack must round up to the same even number")
         dev = eng.device
         R, Kp = self.R, self.Kp
-        H0 = torch.as_tensor(H0, dtype=torch.float32).to(dev)   # [R, N, K]
-        W0 = torch.as_tensor(W0, dtype=torch.float32).to(dev)   # [R, K, G]
         self.Hr = torch.zeros((eng.N, R, Kp), device=dev, dtype=torch.float32)
         self.Wt = torch.zeros((eng.G, R, Kp), device=dev, dtype=torch.float32)
-        self.Hr[:, :, :K] = H0.permute(1, 0, 2)
-        self.Wt[:, :, :K] = W0.permute(2, 0, 1)
+        lo = 0
+        for (k, h0, w0), r in zip(groups, self.Rs):
+            if isinstance(h0, SeedInit):
+                # device draw (one launch for the r replicates of this K) into the dense engine's K-major layout,
+                # then one permuted copy into the replicate-interleaved layout of this path
+                ldh, ldw = (eng.N + 3) // 4 * 4, (eng.G + 3) // 4 * 4
+                Ht = torch.zeros((r, Kp, ldh), device=dev, dtype=torch.float32)
+                Wall = torch.zeros((r, Kp, ldw), device=dev, dtype=torch.float32)
+                seeds = torch.tensor(h0.seeds, dtype=torch.int64, device=dev)
+                check(eng.lib.cnmf_b200_init_random(ptr(seeds), r, k, Kp, eng.N, eng.N, 0, eng.G,
+                                                    math.sqrt(float(eng.x_mean) / k), ptr(Ht), ldh, ptr(Wall), ldw,
+                                                    eng._stream()), "init_random")
+                self.Hr[:, lo:lo + r, :] = Ht[:, :, :eng.N].permute(2, 0, 1)
+                self.Wt[:, lo:lo + r, :] = Wall[:, :, :eng.G].permute(2, 0, 1)
+                del Ht, Wall
+            else:
+                h0 = torch.as_tensor(h0, dtype=torch.float32).to(dev)   # [r, N, k]
+                w0 = torch.as_tensor(w0, dtype=torch.float32).to(dev)   # [r, k, G]
+                self.Hr[:, lo:lo + r, :k] = h0.permute(1, 0, 2)
+                self.Wt[:, lo:lo + r, :k] = w0.permute(2, 0, 1)
+            lo += r
+        if eng.c != 1.0:               # the engine's units: X * c^2 = (cH)(cW); a power of two, exact
+            self.Hr.mul_(eng.c)
+            self.Wt.mul_(eng.c)
         self.active = torch.ones(R, device=dev, dtype=torch.uint8)
         self.err2 = torch.zeros(R, device=dev, dtype=torch.float64)
         self.p = KlProblem(
             n_cells=eng.N, n_genes=eng.G, nnz=eng.nnz, row_ptr=ptr(eng.row_ptr), col_idx=ptr(eng.col_idx),
             val=ptr(eng.val), t_row_ptr=ptr(eng.t_row_ptr), t_col_idx=ptr(eng.t_col_idx), t_val=ptr(eng.t_val),
-            R=R, K=self.K, Kp=Kp, Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active), l1_H=l1_H, l2_H=l2_H,
-            l1_W=l1_W, l2_W=l2_W, eps=eps, sumX=eng.sumX, xlogx=eng.xlogx, err2=ptr(self.err2))
+            R=R, K=self.K, Kp=Kp, impl=eng.impl, Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active),
+            # an L1 strength is compared with a numerator, which scales like the factors; an L2 strength multiplies a
+            # factor entry against a denominator that scales the same way
+            l1_H=l1_H * eng.c, l2_H=l2_H, l1_W=l1_W * eng.c, l2_W=l2_W, eps=eps, sumX=eng.sumX, xlogx=eng.xlogx,
+            err2=ptr(self.err2))
         nbytes = check(eng.lib.cnmf_b200_kl_workspace_bytes(C.byref(self.p)), "kl_workspace_bytes")
         self.ws = torch.empty(max(int(nbytes), 256), device=dev, dtype=torch.uint8)
         self.p.workspace, self.p.workspace_bytes = ptr(self.ws), self.ws.numel()
+        check(eng.lib.cnmf_b200_kl_range_flag_clear(C.byref(self.p), eng._stream()), "kl_range_flag_clear")
         self.launches = 0
 
     def objective(self):
@@ -135,13 +220,38 @@ class KlBatch:
         check(self.eng.lib.cnmf_b200_kl_iterate(C.byref(self.p), int(n), self.eng._stream()), "kl_iterate")
         self.launches += self.eng.lib.cnmf_b200_last_launch_count()
 
+    def check_range(self):
+        """Raise if a factor entry (or, on the slab path, a ratio x / (WH)) left the fp16 range of the gathered
+        copies since the batch was created -- the affected entries are inf/NaN, nothing was clamped silently."""
+        flag = C.c_int32(0)
+        check(self.eng.lib.cnmf_b200_kl_range_flag(C.byref(self.p), C.byref(flag), self.eng._stream()), "kl_range_flag")
+        if flag.value != 0:
+            raise _lib.Cnmfb200Error(
+                "sparse KL: a factor entry exceeded 65504 in the engine's units (X scaled to mean ~1): the fp16 copies "
+                "the kernels gather cannot hold it. This happens with an initial H0/W0 many orders of magnitude away "
+                "from sqrt(mean(X)/K); rescale the initial factors (H*a, W/a leave the product unchanged).")
+
     def read_loss(self):
-        return 0.5 * self.err2.cpu().numpy()
+        self.check_range()
+        return 0.5 * self.err2.cpu().numpy() / (self.eng.c * self.eng.c)
 
     def set_active(self, alive):
         self.active.copy_(torch.from_numpy(alive.astype(np.uint8)))
 
     def results(self, return_H=False):
-        W = self.Wt[:, :, :self.K].permute(1, 2, 0).contiguous().cpu().numpy()
-        H = self.Hr[:, :, :self.K].permute(1, 0, 2).contiguous().cpu().numpy() if return_H else None
+        """(W [R, K, G], H [R, N, K] or None) in the units of the caller's X -- for a mixed-K stack use
+        ``results_by_group``."""
+        inv = 1.0 / self.eng.c
+        W = (self.Wt[:, :, :self.K].permute(1, 2, 0) * inv).contiguous().cpu().numpy()
+        H = (self.Hr[:, :, :self.K].permute(1, 0, 2) * inv).contiguous().cpu().numpy() if return_H else None
         return W, H
+
+    def results_by_group(self, return_H=False):
+        """[(K, slice of replicates, W [R_k, K, G], H or None)] for every group of the stack."""
+        inv, out, lo = 1.0 / self.eng.c, [], 0
+        for k, r in zip(self.Ks, self.Rs):
+            W = (self.Wt[:, lo:lo + r, :k].permute(1, 2, 0) * inv).contiguous().cpu().numpy()
+            H = (self.Hr[:, lo:lo + r, :k].permute(1, 0, 2) * inv).contiguous().cpu().numpy() if return_H else None
+            out.append((k, slice(lo, lo + r), W, H))
+            lo += r
+        return out

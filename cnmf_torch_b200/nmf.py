@@ -60,10 +60,10 @@ def make_engine(X, beta_loss="frobenius", device="cuda:0", impl="auto", init_dev
     reference with use_gpu=True); see engine.draw_init."""
     if beta_loss in ("frobenius", 2, 2.0):
         from .engine import DenseFrobeniusEngine
-        return DenseFrobeniusEngine(X, device=device, impl=_IMPL[impl], init_device=init_device)
+        return DenseFrobeniusEngine(X, device=device, impl=_IMPL.get(impl, _lib.IMPL_AUTO), init_device=init_device)
     if beta_loss in ("kullback-leibler", 1, 1.0):
         from .kl_engine import SparseKLEngine
-        return SparseKLEngine(X, device=device, init_device=init_device)
+        return SparseKLEngine(X, device=device, init_device=init_device, impl=impl if impl in ("slab", "gather") else None)
     if beta_loss in ("itakura-saito", 0, 0.0):
         raise NotImplementedError(ITAKURA_SAITO_REFUSAL)
     raise ValueError(f"beta_loss={beta_loss!r}: expected 'frobenius', 'kullback-leibler' or 'itakura-saito'")

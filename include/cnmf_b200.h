@@ -251,7 +251,8 @@ typedef struct cnmf_b200_kl_problem {
   const int32_t* t_row_ptr;  /* CSR of X^T : [G+1], [nnz], [nnz]  (X is static: built once) */
   const int32_t* t_col_idx;
   const float* t_val;
-  int32_t R, K, Kp, reserved; /* Kp: K rounded up to an EVEN number here (<= CNMF_B200_MAX_KP); padding columns zero */
+  int32_t R, K, Kp;          /* Kp: K rounded up to an EVEN number here (<= CNMF_B200_MAX_KP); padding columns zero */
+  int32_t impl;              /* CNMF_B200_KL_IMPL_GATHER (0, default) or CNMF_B200_KL_IMPL_SLAB */
   float* Hr;                 /* [N x R*Kp] updated in place */
   float* Wt;                 /* [G x R*Kp] updated in place */
   const uint8_t* active;     /* [R] or NULL */
@@ -263,11 +264,29 @@ typedef struct cnmf_b200_kl_problem {
   int64_t workspace_bytes;
 } cnmf_b200_kl_problem;
 
+/* The two kernel families behind cnmf_b200_kl_iterate / _objective (same update rule, same results within the
+ * tolerances of the tests):
+ *   GATHER -- one thread per (row segment, replicate), lanes = consecutive replicates, the fp16 copy of the fixed
+ *             factor gathered from L2 in coalesced runs (also what the standalone cnmf_b200_kl_half_step runs);
+ *             the default: faster at the cfg-3 shape (100 000 cells: 7.4 vs 9.4 ms per batched iteration);
+ *   SLAB   -- the fixed factor's fp16 copy of one replicate group and one block of columns is staged in shared
+ *             memory (bank-conflict-free line layout) and gathered from there; fp16 x fp16 + fp32 FMAs (FHFMA);
+ *             70 x less L2 traffic, faster on small matrices (20 000 cells: 1.74 vs 1.92 ms). */
+#define CNMF_B200_KL_IMPL_GATHER 0
+#define CNMF_B200_KL_IMPL_SLAB 1
+
 int64_t cnmf_b200_kl_workspace_bytes(const cnmf_b200_kl_problem* p);
 /* n_iters x { column sums of W; H half-step; column sums of H; W half-step }, then the objective. */
 int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* stream);
 /* err2 of the current state; factors untouched. */
 int cnmf_b200_kl_objective(const cnmf_b200_kl_problem* p, void* stream);
+/* The gathered copies are fp16: a factor entry above 65504 (or a ratio x / (WH) that overflows fp16 on the slab
+ * path) cannot be represented.  Nothing is clamped silently: the kernels raise a flag in the workspace instead, the
+ * affected entries turn into inf/NaN, and this call reads the flag back (synchronises the stream): 0 = all values in
+ * range since the last clear.  run_nmf has no counterpart (fp32 throughout); the host layer turns a raised flag into
+ * an error that says so.  */
+int cnmf_b200_kl_range_flag(const cnmf_b200_kl_problem* p, int32_t* flag_host, void* stream);
+int cnmf_b200_kl_range_flag_clear(const cnmf_b200_kl_problem* p, void* stream);
 
 /* ------------------------------------------------------------------------------------------
  * Consensus kernel set.  Replaces the library calls of cNMF.consensus' front half

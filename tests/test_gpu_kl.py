@@ -13,6 +13,14 @@ def _pearson(a, b):
     return float(np.corrcoef(a.ravel().astype(np.float64), b.ravel().astype(np.float64))[0, 1])
 
 
+@pytest.fixture(autouse=True, params=["slab", "gather"])
+def kl_impl(request, monkeypatch):
+    """Every test of this file runs on both kernel families behind cnmf_b200_kl_iterate (include/cnmf_b200.h:
+    CNMF_B200_KL_IMPL_SLAB, the default, and CNMF_B200_KL_IMPL_GATHER)."""
+    monkeypatch.setenv("CNMF_B200_KL_IMPL", request.param)
+    return request.param
+
+
 @pytest.fixture(scope="module")
 def problem():
     from cnmf_torch_b200.synth import nb_counts
@@ -23,6 +31,8 @@ def test_kl_constants(problem):
     from cnmf_torch_b200.kl_engine import SparseKLEngine
     eng = SparseKLEngine(problem)
     x = problem.astype(np.float64)
+    x = x * eng.c ** 2          # the engine's units: X scaled by a power of four to mean ~1
+    assert 0.25 <= x.mean() <= 4.0 and np.log2(eng.c) == int(np.log2(eng.c))
     assert abs(eng.sumX - x.sum()) / x.sum() < 1e-12
     xl = (x[x > 0] * np.log(x[x > 0])).sum()
     assert abs(eng.xlogx - xl) <= 1e-9 * max(1.0, abs(xl))
@@ -151,7 +161,7 @@ def test_nndsvd_init_through_run_nmf(problem, beta):
     assert abs(err - eo) / eo < 1e-3 and _pearson(W, wo) >= 0.999
 
 
-def test_kl_cut_rows_empty_rows_and_many_segments():
+def test_kl_cut_rows_empty_rows_and_many_segments(kl_impl):
     """Edge cases of the segment table: genes expressed in every cell (rows of CSR(X^T) cut into a dozen segments,
     finished by kl_finish_rows_kernel), a gene and a cell without any count (empty rows in either orientation), rows
     of exactly one segment length, and R not a divisor of the CTA size -- one iteration against the oracle's dense
@@ -186,11 +196,13 @@ def test_kl_cut_rows_empty_rows_and_many_segments():
     for r in range(3):
         ora = no.nmf_batch(x, H0[2 + r].numpy(), W0[2 + r].numpy(), beta_loss="kullback-leibler", tol=0.0, max_iter=10)
         assert abs(part.trace[-1][1][r] - ora["trace"][-1][1]) / ora["trace"][-1][1] < 1e-3
-    np.testing.assert_allclose(full.W[2:5], part.W, rtol=1e-5, atol=1e-8)
-    np.testing.assert_allclose(full.err[2:5], part.err, rtol=1e-6)
+    # (gather: a replicate's arithmetic does not depend on its neighbours; slab: its lane -- entry slot and rotation
+    # of the operands -- does, so sums are taken in another order: round-off, amplified over 10 iterations)
+    np.testing.assert_allclose(full.W[2:5], part.W, rtol=1e-5 if kl_impl == "gather" else 1e-3, atol=1e-6)
+    np.testing.assert_allclose(full.err[2:5], part.err, rtol=1e-6 if kl_impl == "gather" else 1e-5)
 
 
-def test_kl_column_blocked_gene_major_pass_matches_oracle():
+def test_kl_column_blocked_gene_major_pass_matches_oracle(kl_impl):
     """The gene-major half-step of a large matrix walks CSR(X^T) cell block by cell block (so the rows of H gathered
     by the threads resident at one time fit in L2) and finishes every gene from per-segment partials.  The block
     size is chosen from the problem size when the library is first used; CNMF_B200_KL_BLOCK=128 forces 4-25 blocks
@@ -199,9 +211,13 @@ def test_kl_column_blocked_gene_major_pass_matches_oracle():
     if os.environ.get("CNMF_B200_KL_BLOCK"):
         pytest.skip("already inside the forced-block run")
     here = os.path.abspath(__file__)
+    # the slab path blocks the columns of BOTH matrices by its shared-memory size: 96 lines and 100-entry segments put
+    # the same small problems through 3-33 column blocks per half-step, slab reloads and cut rows
     rc = subprocess.run([sys.executable, "-m", "pytest", here, "-x", "-q", "-k",
-                         "single_iteration or trace_matches or cut_rows or convergence_freeze"],
-                        env=dict(os.environ, CNMF_B200_KL_BLOCK="128"), capture_output=True, text=True)
+                         "(single_iteration or trace_matches or cut_rows or convergence_freeze or l1_and_l2) and "
+                         + kl_impl],
+                        env=dict(os.environ, CNMF_B200_KL_BLOCK="128", CNMF_B200_KS_LINES="96", CNMF_B200_KS_SEG="100"),
+                        capture_output=True, text=True)
     assert rc.returncode == 0, rc.stdout[-2000:] + rc.stderr[-2000:]
 
 
@@ -221,3 +237,35 @@ def test_kl_with_l1_and_l2_regularisation_matches_oracle(problem):
         assert _pearson(res.W[r], ora["W"]) >= 0.999 and _pearson(res.H[r], ora["H"]) >= 0.999
     plain = eng.factorize(5, H0=H0, W0=W0, tol=0.0, max_iter=30)
     assert np.all(res.trace[-1][1] != plain.trace[-1][1])      # the terms are really there
+
+
+def test_kl_data_scale_and_out_of_range_init_are_handled_not_clamped(problem):
+    """The gathered copies are fp16.  (i) The units of X do not matter: the engine works on X scaled by a power of four
+    to mean ~1, which KL multiplicative updates follow exactly -- X * 1e-6 and X * 1e6 give the factors of X scaled by
+    1e-3 and 1e3.  (ii) An initial factor many orders of magnitude out of range is REFUSED (an error that says why),
+    never silently saturated at 65504 as round 1's kernel did."""
+    from cnmf_torch_b200 import _lib
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    K, seeds = 5, [3, 4]
+    base = SparseKLEngine(problem)
+    H0, W0 = base.make_init(K, seeds)
+    ref = base.factorize(K, H0=H0, W0=W0, tol=0.0, max_iter=20, return_H=True)
+    for scale in (1e-6, 1e6):
+        eng = SparseKLEngine(problem * np.float32(scale))
+        s = np.float32(np.sqrt(scale))
+        res = eng.factorize(K, H0=H0 * s, W0=W0 * s, tol=0.0, max_iter=20, return_H=True)
+        for r in range(2):
+            assert abs(res.trace[-1][1][r] / scale - ref.trace[-1][1][r]) / ref.trace[-1][1][r] < 1e-3
+            assert _pearson(res.W[r], ref.W[r]) >= 0.9999 and _pearson(res.H[r], ref.H[r]) >= 0.9999
+            np.testing.assert_allclose(res.W[r].sum() / s, ref.W[r].sum(), rtol=1e-2)
+    # entries of H0 up to ~1e8 in the engine's units (W0 shrunk to keep the product): beyond fp16
+    big = 3e7
+    with pytest.raises(_lib.Cnmfb200Error, match="65504"):
+        base.factorize(K, H0=H0 * np.float32(big), W0=W0 / np.float32(big), tol=0.0, max_iter=10)
+    # ... while a merely large but representable start runs and reaches the same objective as the oracle
+    mid = 64.0
+    res = base.factorize(K, H0=H0 * np.float32(mid), W0=W0 / np.float32(mid), tol=0.0, max_iter=20)
+    for r in range(2):
+        ora = no.nmf_batch(problem, (H0[r] * mid).numpy(), (W0[r] / mid).numpy(), beta_loss="kullback-leibler", tol=0.0,
+                           max_iter=20)
+        assert abs(res.trace[-1][1][r] - ora["trace"][-1][1]) / ora["trace"][-1][1] < 1e-3
