@@ -253,20 +253,27 @@ def _extras(dev):
         out["consensus_cfg4_labels_identical"] = bool(np.array_equal(ref["labels"], r["labels"]))
     except Exception as e:  # the oracle is optional here
         out["consensus_cfg4_host_sklearn_ms"] = None
-    # cfg-3 shape at reduced N: sparse KL MU, 20 000 x 2000 at ~7 % density, K=9, R=100
-    xk = nb_counts(20000, 2000, seed=14, libsize=170.0)
-    eng = SparseKLEngine(xk, device=dev)
-    b = eng.new_batch(9, seeds=list(range(100)))
-    b.iterate(2)
-    torch.cuda.synchronize()
-    t0 = time.perf_counter()
-    b.iterate(5)
-    torch.cuda.synchronize()
-    dt = (time.perf_counter() - t0) / 5
-    out["kl_sparse_20k_cells"] = {"density": float((xk > 0).mean()), "nnz": int(eng.nnz), "ms_per_batched_iter": dt * 1e3,
-                                  "replicate_iters_per_s": 100 / dt,
-                                  "algorithmic_hbm_gb_s": (8 * eng.nnz + 100 * 8 * 9 * (20000 + 2000)) / dt / 1e9}
-    del eng, b
+    # cfg-3: sparse KL MU, K=9, R=100, one K-batch alone -- at 20 000 cells (round 1's extra) and at the config's own
+    # 100 000 cells (`--config cfg3` runs the whole K=5..13 ledger)
+    for cells, key in ((20000, "kl_sparse_20k_cells"), (CFG3["cells"], "kl_sparse_cfg3_100k_cells")):
+        xk = nb_counts(cells, 2000, seed=14, libsize=170.0)
+        eng = SparseKLEngine(xk, device=dev, init_device="cuda")
+        b = eng.new_batch(9, seeds=list(range(100)))
+        b.iterate(2)
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        b.iterate(10)
+        e1.record()
+        torch.cuda.synchronize()
+        dt = e0.elapsed_time(e1) / 10 * 1e-3
+        out[key] = {"density": float(eng.nnz) / (cells * 2000.0), "nnz": int(eng.nnz), "ms_per_batched_iter": dt * 1e3,
+                    "replicate_iters_per_s": 100 / dt,
+                    "algorithmic_hbm_gb_s": (2 * 8 * eng.nnz + 100 * 8 * 9 * (cells + 2000)) / dt / 1e9,
+                    "fp32_fma_tflops_algorithmic": 2.0 * 2 * eng.nnz * 100 * 2 * 9 / dt / 1e12,
+                    "kernels": "gather family (default); includes 1/10 of an objective evaluation"}
+        del eng, b, xk
+        torch.cuda.empty_cache()
     # cfg-1/2 in the reference's default mode: online MU, chunk 5000, K=9, R=100, 3 passes
     xo = nb_counts(3000, 2000, seed=14)
     e2 = DenseFrobeniusEngine(xo, device=dev, init_device="cuda")   # host-generator draws would be 3/4 of the time

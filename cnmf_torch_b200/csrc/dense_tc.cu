@@ -66,19 +66,8 @@ struct TcParams {
   int t;  // replicates per tile
   int num_m_tiles, num_m_groups, num_n_tiles, stages;
   float l1, l2, eps;
-  // stream-K (CG = 1, sk_scratch != null): the num_tiles x num_kb k-blocks are cut into gridDim.x contiguous,
-  // equally long ranges (CTA c: sk_base + (c < sk_rem) units).  A CTA whose range ends inside a tile leaves its
-  // partial accumulator in its scratch slot and publishes sk_epoch in its flag; the CTA holding the tile's last
-  // k-block adds the partials of the lower-numbered CTAs in index order and runs the epilogue.  A CTA only ever
-  // waits for LOWER-numbered CTAs, and those publish before doing anything else (TcWork::next).
-  float* sk_scratch;        // [gridDim.x][TC_MAX_BN][TC_BM]
-  unsigned int* sk_flags;   // [gridDim.x]
-  unsigned int sk_epoch;
-  int64_t sk_base;
-  int sk_rem;
-  int helpers;  // 1: warps 0-3 join the epilogue of the CTA's last tile (whole-tile schedule, MU/HALS, CG = 1)
-  int dbg;  // dev probes (CNMF_B200_TC_DEBUG)
-  long long* prof;  // dev probe: clock64 stamps of CTA 0's first epilogue warp (CNMF_B200_TC_PROF = device pointer): 1 = main loop without MMAs, 2 = main loop without TMA loads
+  int helpers;  // 1: warps 0-3 join the epilogue of the CTA's last tile (MU/HALS, CG = 1)
+  int dbg;  // dev probes (CNMF_B200_TC_DEBUG): 1 = main loop without MMAs, 2 = main loop without TMA loads
 };
 
 // ---------------------------------------------------------------------------------------------
@@ -240,48 +229,18 @@ __device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {  
       : "memory");
 }
 
-// Work iterator shared by the three roles of a CTA.  Data-parallel: whole tiles, tile = group, group + groups, ...
-// Stream-K: the CTA's contiguous range of k-block units, cut at tile boundaries into segments [kb0, kb1) of a tile.
+// Work iterator shared by the three roles of a CTA: whole tiles, tile = group, group + groups, ...
 struct TcWork {
-  bool sk;
-  int num_kb, num_tiles, num_groups;
-  int tile;          // data-parallel cursor
-  int64_t u, uend;   // stream-K cursor
-  __device__ __forceinline__ TcWork(const TcParams& prm, int group_id, int num_groups_, int num_tiles_, int num_kb_, bool sk_)
-      : sk(sk_), num_kb(num_kb_), num_tiles(num_tiles_), num_groups(num_groups_), tile(group_id), u(0), uend(0) {
-    if (sk) {
-      const int64_t c = blockIdx.x;
-      u = c * prm.sk_base + (c < prm.sk_rem ? c : prm.sk_rem);
-      uend = u + prm.sk_base + (c < prm.sk_rem ? 1 : 0);
-    }
-  }
-  __device__ __forceinline__ bool next(int& t_out, int& kb0, int& kb1) {
-    if (sk) {
-      // The range is walked from its END: the segment a CTA cannot finish (the first k-blocks of the tile at the
-      // end of its range) is computed and published first, and the segment it finishes for a lower-numbered CTA
-      // (the last k-blocks of the tile at the start of its range) comes last, when that CTA's partial has long
-      // been published.  Walking forward would make every CTA wait for its predecessor's LAST action with an
-      // accumulator parked in TMEM.
-      if (u >= uend) return false;
-      t_out = static_cast<int>((uend - 1) / num_kb);
-      kb1 = static_cast<int>(uend - static_cast<int64_t>(t_out) * num_kb);
-      const int64_t left = uend - u;
-      kb0 = (kb1 < left) ? 0 : kb1 - static_cast<int>(left);
-      uend -= kb1 - kb0;
-      return true;
-    }
+  int num_tiles, num_groups, tile;
+  __device__ __forceinline__ TcWork(int group_id, int num_groups_, int num_tiles_)
+      : num_tiles(num_tiles_), num_groups(num_groups_), tile(group_id) {}
+  __device__ __forceinline__ bool next(int& t_out) {
     if (tile >= num_tiles) return false;
-    t_out = tile; kb0 = 0; kb1 = num_kb;
+    t_out = tile;
     tile += num_groups;
     return true;
   }
 };
-// CTA that owns stream-K unit `unit`
-__device__ __forceinline__ int sk_cta_of(const TcParams& prm, int64_t unit) {
-  const int64_t big = static_cast<int64_t>(prm.sk_rem) * (prm.sk_base + 1);
-  if (unit < big) return static_cast<int>(unit / (prm.sk_base + 1));
-  return prm.sk_rem + static_cast<int>((unit - big) / prm.sk_base);
-}
 
 template <int KP, int ALGO, int CG, bool SUMS>
 __global__ void __launch_bounds__(tc_threads(KP), 1)
@@ -346,18 +305,17 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   const int num_tiles = prm.num_m_groups * prm.num_n_tiles;
   const int group_id = blockIdx.x / CG, num_groups = gridDim.x / CG;
   const int num_kb = static_cast<int>((prm.Kd + TC_BK - 1) / TC_BK);
-  const bool sk = (CG == 1) && prm.sk_scratch != nullptr;
 
   if (warp == 0) {
     // ===================== TMA producer (every CTA; whole warp, one elected lane issues) =====================
     int stage = 0;
     uint32_t phase = 0;
-    TcWork work(prm, group_id, num_groups, num_tiles, num_kb, sk);
-    int tile, kb0, kb1;
-    while (work.next(tile, kb0, kb1)) {
+    TcWork work(group_id, num_groups, num_tiles);
+    int tile;
+    while (work.next(tile)) {
       const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
       const int m_tile = m_group * CG + static_cast<int>(cta_rank);
-      for (int kb = kb0; kb < kb1; ++kb) {
+      for (int kb = 0; kb < num_kb; ++kb) {
         mbar_wait(&empty[stage], phase ^ 1u);
         if (elect_one()) {
           uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
@@ -390,15 +348,15 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       int stage = 0;
       uint32_t phase = 0;
       int lt = 0;
-      TcWork work(prm, group_id, num_groups, num_tiles, num_kb, sk);
-      int tile, kb0, kb1;
-      for (; work.next(tile, kb0, kb1); ++lt) {
+      TcWork work(group_id, num_groups, num_tiles);
+      int tile;
+      for (; work.next(tile); ++lt) {
         const int buf = lt & 1;
         const uint32_t tphase = (lt >> 1) & 1u;
         mbar_wait(&tempty[buf], tphase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * TC_MAX_BN);
-        for (int kb = kb0; kb < kb1; ++kb) {
+        for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           if (elect_one()) {
@@ -414,10 +372,10 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                 // advance 8 tf32 = 32 bytes inside the 128-byte swizzle row: +2 in the (addr >> 4) field
                 if (CG == 2)
                   tc_mma_tf32_pair(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k),
-                                   idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+                                   idesc, (kb > 0 || k != 0) ? 1u : 0u);
                 else
                   tc_mma_tf32(d_tmem, a_desc + static_cast<uint64_t>(2 * k), b_desc + static_cast<uint64_t>(2 * k),
-                              idesc, (kb > kb0 || k != 0) ? 1u : 0u);
+                              idesc, (kb > 0 || k != 0) ? 1u : 0u);
               }
               // frees the smem slot (in both CTAs of a pair) when these MMAs retire
               if (CG == 2) tc_commit_pair(&empty[stage]); else tc_commit(&empty[stage]);
@@ -437,7 +395,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   // The update of one tile is instruction-issue bound and takes about half a main loop; it hides behind the next
   // tile's main loop except for the LAST tile of the CTA, when the producer, MMA and allocator warps have nothing
   // left to do: they join that tile's epilogue as one more warpgroup (replicates dealt over EG + 1 groups).
-  const bool helpers = (CG == 1) && !sk && (ALGO < TC_MODE_STORE) && prm.helpers != 0;
+  const bool helpers = (CG == 1) && (ALGO < TC_MODE_STORE) && prm.helpers != 0;
   if (warp >= 4 || helpers) {
     // ===================== epilogue (every CTA, its own 128 rows) =====================
     constexpr int EG = tc_epi_groups(KP), ET = 128 * EG;
@@ -446,9 +404,9 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     const int eg = helper ? EG : (warp - 4) >> 2;  // epilogue warpgroup: takes replicates rr = eg (mod groups)
     const int et = helper ? (1 << 30) : static_cast<int>(threadIdx.x) - 128;  // helpers skip the cooperative loops
     int lt = 0;
-    TcWork work(prm, group_id, num_groups, num_tiles, num_kb, sk);
-    int tile, kb0, kb1;
-    for (; work.next(tile, kb0, kb1); ++lt) {
+    TcWork work(group_id, num_groups, num_tiles);
+    int tile;
+    for (; work.next(tile); ++lt) {
       const bool last = helpers && tile + num_groups >= num_tiles;
       if (helper && !last) continue;
       const int egs = last ? EG + 1 : EG;   // warpgroups sharing this tile
@@ -457,31 +415,6 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
       const int m_tile = m_group * CG + static_cast<int>(cta_rank);
       const int r0 = n_tile * t;
-      if (sk && kb1 < num_kb) {
-        // ---- stream-K, range ends inside the tile: leave the partial accumulator in this CTA's slot ----
-        mbar_wait(&tfull[buf], tphase);
-        tc_fence_after();
-        float* slot = prm.sk_scratch + static_cast<size_t>(blockIdx.x) * (TC_MAX_BN * TC_BM) + q * 32 + lane;
-        const uint32_t ta = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * TC_MAX_BN);
-        for (int c = eg * 8; c < BN; c += EG * 8) {   // BN is a multiple of 16
-          float v[8];
-          tmem_ld4(ta + static_cast<uint32_t>(c), v[0], v[1], v[2], v[3]);
-          tmem_ld4(ta + static_cast<uint32_t>(c + 4), v[4], v[5], v[6], v[7]);
-          tmem_ld_wait();
-#pragma unroll
-          for (int j = 0; j < 8; ++j) slot[static_cast<size_t>(c + j) * TC_BM] = v[j];
-        }
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(&tempty[buf]);
-        __threadfence();
-        epi_bar_sync<ET>();
-        if (et == 0)
-          asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(prm.sk_flags + blockIdx.x), "r"(prm.sk_epoch) : "memory");
-        continue;
-      }
-      // stream-K, tile started by lower-numbered CTAs: their partials are added below, in CTA order
-      const int sk_first = (sk && kb0 > 0) ? sk_cta_of(prm, static_cast<int64_t>(tile) * num_kb) : static_cast<int>(blockIdx.x);
       if (ALGO < TC_MODE_STORE) {
         for (int i = et; i < t * KP * KP; i += ET) {
           const int rr = i / (KP * KP);
@@ -505,9 +438,6 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       // inside the update loop
       for (int i = et; i < t; i += ET)
         sact[i] = (r0 + i < prm.R && (prm.active == nullptr || prm.active[r0 + i] != 0)) ? 1 : 0;
-      const bool prof = prm.prof != nullptr && blockIdx.x == 0 && et == 0 && lt == 0;
-      int pi = 0;
-      if (prof) prm.prof[pi++] = clock64();
       epi_bar_sync<ET>(last);
       if (ALGO == CNMF_B200_ALGO_HALS) {
         // reciprocals of the regularised diagonal, once per tile (these warps idle here while the main loop runs)
@@ -520,19 +450,6 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       mbar_wait(&tfull[buf], tphase);
       tc_fence_after();
-      if (sk_first < static_cast<int>(blockIdx.x)) {
-        if (et == 0) {
-          for (int c = sk_first; c < static_cast<int>(blockIdx.x); ++c) {
-            uint32_t v = 0, spins = 0;
-            do {
-              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(prm.sk_flags + c) : "memory");
-              if (v != prm.sk_epoch && ++spins > (1u << 26)) __trap();   // bounded: a scheduling bug aborts, not hangs
-            } while (v != prm.sk_epoch);
-          }
-        }
-        epi_bar_sync<ET>();
-      }
-      if (prof) prm.prof[pi++] = clock64();
       const int64_t m = static_cast<int64_t>(m_tile) * TC_BM + q * 32 + lane;
       const bool in = m < prm.M;
       const uint32_t taddr = tmem_base + (static_cast<uint32_t>(q * 32) << 16) + static_cast<uint32_t>(buf * TC_MAX_BN);
@@ -567,14 +484,6 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
             s[k] = (in && ALGO != TC_MODE_STORE) ? sp[static_cast<int64_t>(k) * prm.lds] : 0.f;
         }
         tmem_ld_wait();
-        if (sk_first < static_cast<int>(blockIdx.x)) {
-          for (int c = sk_first; c < static_cast<int>(blockIdx.x); ++c) {
-            const float* ps = prm.sk_scratch + static_cast<size_t>(c) * (TC_MAX_BN * TC_BM) +
-                              static_cast<size_t>(rr * KP) * TC_BM + q * 32 + lane;
-#pragma unroll
-            for (int k = 0; k < KP; ++k) p[k] += __ldcg(ps + static_cast<size_t>(k) * TC_BM);
-          }
-        }
         const bool act = sact[rr] != 0;
         float cross = 0.f, ssum = 0.f;
         if (ALGO >= TC_MODE_STORE) {
@@ -618,7 +527,6 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
 #pragma unroll
           for (int k = 0; k < KP; ++k) s[k] = s_nxt[k];
         }
-        if (prof && pi < 60) prm.prof[pi++] = clock64();
       }
       // all tcgen05.ld of this buffer are complete: hand it back to the MMA warp (of the leader CTA)
       tc_fence_before();
@@ -637,7 +545,6 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         }
       }
       epi_bar_sync<ET>(last);  // sgram / sred / sact are rewritten by the next tile
-      if (prof) { prm.prof[pi++] = clock64(); prm.prof[63] = pi; }
     }
   }
 
@@ -712,7 +619,6 @@ int launch_round_tf32(float* dst, const float* src, int64_t n, cudaStream_t st) 
 // ---------------------------------------------------------------------------------------------
 struct TcPlan {
   int t, BN, stages, num_m_tiles, num_m_groups, num_n_tiles, cg;
-  bool sk;  // stream-K schedule (needs scratch); else whole tiles per CTA
   size_t smem_bytes;
 };
 
@@ -739,12 +645,7 @@ static int tc_num_sms() {
 // multiple of 16, <= 256) from a cost model calibrated on B200 (profiles/NOTES.md): one SM ingests
 // ~43 B/clk from L2 through TMA, so a k-block costs max(operand bytes per SM / 43, tensor-pipe clocks);
 // tiles run in waves over the SMs (pairs: over SM pairs); the epilogue of the last tile is exposed.
-static int tc_streamk_mode() {
-  static const int mode = [] { const char* e = getenv("CNMF_B200_TC_SK"); return e ? atoi(e) : 0; }();
-  return mode;
-}
-
-static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out, bool sk_ok = false) {
+static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out) {
   const int num_m = static_cast<int>(ceil_div(M, TC_BM));
   const int64_t num_kb = ceil_div(Kd, TC_BK);
   double best = 1e300;
@@ -773,29 +674,13 @@ static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out, 
       if (kb_clk < 500.0 + 0.6 * BN) kb_clk = 500.0 + 0.6 * BN;
       if (cg == 2) kb_clk *= 0.92;
       const double epi = static_cast<double>(t) * (Kp * Kp + 12.0 * Kp) * 1.5 + 1500.0;
-      // Stream-K is opt-in (CNMF_B200_TC_SK = 1: where the cost model prefers it, 2: wherever feasible; default 0):
-      // measured slower than whole tiles (K=8, R=200 alone: 128 vs 109 us per iteration) because the fold-in of the
-      // partials sits in the latency-bound update loop, and in a multi-K run the other stacks' kernels already
-      // fill the idle SMs of a partial wave (profiles/NOTES.md).
-      static const int sk_mode = tc_streamk_mode();
-      const bool sk_feasible = sk_ok && cg == 1 && sk_mode != 0 && tiles * num_kb >= sms;
-      for (int mode = 0; mode < 2; ++mode) {
-        double cost;
-        if (mode == 0) {
-          if (sk_feasible && sk_mode == 2) continue;
-          cost = waves * (static_cast<double>(num_kb) * kb_clk + 1000.0) + epi + (cg == 2 ? 1500.0 : 0.0);
-        } else {
-          // stream-K: k-blocks spread evenly; each CTA publishes one partial tile and folds one in (~4000 clk)
-          if (!sk_feasible) continue;
-          cost = static_cast<double>(ceil_div(tiles * num_kb, sms)) * kb_clk + 1000.0 + epi + 4000.0;
-        }
-        if (cost < best) {
-          best = cost;
-          found = true;
-          out->t = t; out->BN = BN; out->stages = stages; out->num_m_tiles = num_m; out->num_m_groups = num_g;
-          out->num_n_tiles = num_n; out->cg = cg; out->sk = (mode == 1);
-          out->smem_bytes = tc_smem_bytes(t, Kp, stages, cg);
-        }
+      const double cost = waves * (static_cast<double>(num_kb) * kb_clk + 1000.0) + epi + (cg == 2 ? 1500.0 : 0.0);
+      if (cost < best) {
+        best = cost;
+        found = true;
+        out->t = t; out->BN = BN; out->stages = stages; out->num_m_tiles = num_m; out->num_m_groups = num_g;
+        out->num_n_tiles = num_n; out->cg = cg;
+        out->smem_bytes = tc_smem_bytes(t, Kp, stages, cg);
       }
     }
   }
@@ -899,14 +784,7 @@ static int launch_tc_inst(const CUtensorMap& ma, const CUtensorMap& mb, const Tc
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st, float* sk_scratch = nullptr,
-                          unsigned int* sk_flags = nullptr);
-
-// bytes of stream-K scratch (partial accumulator slots) and flags for one problem
-int64_t tc_streamk_scratch_bytes() {
-  return tc_streamk_mode() == 0 ? 0 : static_cast<int64_t>(tc_num_sms()) * TC_MAX_BN * TC_BM * 4;
-}
-int64_t tc_streamk_flag_bytes() { return align_up(static_cast<int64_t>(tc_num_sms()) * 4, 256); }
+                          double* partials, cudaStream_t st);
 
 int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                         float* state, float* state_op, int64_t lds, const float* gram, const uint8_t* active, int R,
@@ -919,10 +797,10 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st, float* sk_scratch, unsigned int* sk_flags) {
+                          double* partials, cudaStream_t st) {
   TcPlan plan;
   const int sms = tc_num_sms();
-  if (!tc_plan(M, Kd, R, Kp, sms, &plan, sk_scratch != nullptr && sk_flags != nullptr)) {
+  if (!tc_plan(M, Kd, R, Kp, sms, &plan)) {
     set_error("tcgen05 path: no tile plan for M=%lld Kd=%lld R=%d Kp=%d", (long long)M, (long long)Kd, R, Kp);
     return CNMF_B200_ERR_UNSUPPORTED;
   }
@@ -937,21 +815,9 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
   prm.dbg = dbg;
   static const int helpers = [] { const char* e = getenv("CNMF_B200_TC_HELPERS"); return e ? atoi(e) : 1; }();
   prm.helpers = helpers;
-  { const char* e = getenv("CNMF_B200_TC_PROF"); prm.prof = e ? reinterpret_cast<long long*>(strtoull(e, nullptr, 0)) : nullptr; }
   const int64_t tiles = static_cast<int64_t>(plan.num_m_groups) * plan.num_n_tiles;  // per CTA group
   const int64_t slots = sms / plan.cg;
-  int grid = static_cast<int>((tiles < slots ? tiles : slots) * plan.cg);
-  prm.sk_scratch = nullptr; prm.sk_flags = nullptr; prm.sk_epoch = 0; prm.sk_base = 0; prm.sk_rem = 0;
-  if (plan.sk) {
-    static std::atomic<unsigned int> epoch{0};
-    const int64_t units = tiles * ceil_div(Kd, TC_BK);
-    grid = sms;                                  // units >= sms (tc_plan): every CTA owns at least one k-block
-    prm.sk_scratch = sk_scratch; prm.sk_flags = sk_flags;
-    unsigned int e = ++epoch;
-    if (e == 0) e = ++epoch;                     // flags are zero-initialised: epoch 0 is never published
-    prm.sk_epoch = e;
-    prm.sk_base = units / grid; prm.sk_rem = static_cast<int>(units % grid);
-  }
+  const int grid = static_cast<int>((tiles < slots ? tiles : slots) * plan.cg);
   if (algo == CNMF_B200_ALGO_MU) {
     CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_MU>(ma, mb, prm, plan, grid, st)));
   } else if (algo == CNMF_B200_ALGO_HALS) {

@@ -20,10 +20,7 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st, float* sk_scratch = nullptr,
-                          unsigned int* sk_flags = nullptr);
-int64_t tc_streamk_scratch_bytes();
-int64_t tc_streamk_flag_bytes();
+                          double* partials, cudaStream_t st);
 int gram_num_tiles(int64_t L, int Kp);
 int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st);
 int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cudaStream_t st);
@@ -36,7 +33,7 @@ int launch_objective_combine(double, const double*, const float*, const float*, 
                              double*, cudaStream_t);
 
 struct FrobLayout {
-  int64_t off_pt, off_gram, off_gram2, off_partH, off_partW, off_zero, off_wop, off_hop, off_hlo, off_partW2, off_sk, off_skflags, total;
+  int64_t off_pt, off_gram, off_gram2, off_partH, off_partW, off_zero, off_wop, off_hop, off_hlo, off_partW2, total;
   int nblkH, nblkW;
   int impl;
 };
@@ -81,11 +78,6 @@ static FrobLayout frob_layout(const cnmf_b200_frob_problem* p) {
   if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up(rk * p->ldh * 4, 256);
   l.off_partW2 = off;
   if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up((int64_t)l.nblkW * p->R * 2 * 8, 256);
-  // ... and the stream-K schedule's partial-accumulator slots and flags (flags zeroed by frob_prepare)
-  l.off_sk = off;
-  if (l.impl == CNMF_B200_IMPL_TCGEN05) off += align_up(tc_streamk_scratch_bytes(), 256);
-  l.off_skflags = off;
-  if (l.impl == CNMF_B200_IMPL_TCGEN05) off += tc_streamk_flag_bytes();
   l.total = off;
   return l;
 }
@@ -163,7 +155,6 @@ int cnmf_b200_frob_prepare(const cnmf_b200_frob_problem* p, void* stream) {
     const int64_t rk = (int64_t)p->R * p->Kp;
     CNMF_TRY(launch_round_tf32(reinterpret_cast<float*>(ws + l.off_wop), p->Wall, rk * p->ldw, st));
     CNMF_TRY(launch_round_tf32(reinterpret_cast<float*>(ws + l.off_hop), p->Ht, rk * p->ldh, st));
-    CNMF_CUDA(cudaMemsetAsync(ws + l.off_skflags, 0, tc_streamk_flag_bytes(), st));  // no stream-K epoch published yet
   }
   return launch_gram(p->Wall, p->ldw, p->R, p->Kp, p->n_genes, p->gramW, ws + l.off_gram, st);
 }
@@ -192,8 +183,6 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
   const int64_t ldpH = align_up(N, 4), ldpW = align_up(G, 4);
 
   void* gws2 = ws + l.off_gram2;
-  float* sk = l.impl == CNMF_B200_IMPL_TCGEN05 ? reinterpret_cast<float*>(ws + l.off_sk) : nullptr;
-  unsigned int* skf = l.impl == CNMF_B200_IMPL_TCGEN05 ? reinterpret_cast<unsigned int*>(ws + l.off_skflags) : nullptr;
   const int ntH = gram_num_tiles(N, p->Kp), ntW = gram_num_tiles(G, p->Kp);
   for (int it = 0; it < n_iters; ++it) {
     // the objective only reads the partial sums of the last iteration (tcgen05 path skips them otherwise)
@@ -216,15 +205,15 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
       // that consumes a Gram sums them in its (otherwise idle) epilogue warps.
       if (it == 0)
         CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh, p->gramW, 0, p->active,
-                                       p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st, sk, skf));
+                                       p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st));
       else
         CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh,
                                        reinterpret_cast<const float*>(gws2), ntW, p->active, p->R, p->Kp, p->algo,
-                                       p->l1_H, p->l2_H, p->eps, pH, st, sk, skf));
+                                       p->l1_H, p->l2_H, p->eps, pH, st));
       CNMF_TRY(launch_gram_partial(p->Ht, p->ldh, p->R, p->Kp, N, gws, st));
       CNMF_TRY(launch_tc_half_step_g(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, Wop, p->ldw,
                                      reinterpret_cast<const float*>(gws), ntH, p->active, p->R, p->Kp, p->algo,
-                                     p->l1_W, p->l2_W, p->eps, pW, st, sk, skf));
+                                     p->l1_W, p->l2_W, p->eps, pW, st));
       CNMF_TRY(launch_gram_partial(p->Wall, p->ldw, p->R, p->Kp, G, gws2, st));
       if (it == n_iters - 1) {  // leave both Grams in their final form (objective, next call, API contract)
         CNMF_TRY(launch_gram_final(gws, N, p->R, p->Kp, p->gramH, st));

@@ -158,45 +158,6 @@ def test_engine_tc_matches_simt_engine(problem):
         assert _pearson(a.W[r], b.W[r]) >= 0.999
 
 
-def test_streamk_schedule_matches_whole_tile_schedule():
-    """The opt-in stream-K schedule (CNMF_B200_TC_SK=2: every half-step split into equal k-block ranges, partial
-    accumulators folded in CTA order) gives the whole-tile schedule's result up to fp32 summation order.  The
-    schedule is chosen when the library is loaded, hence the two subprocesses."""
-    import os, subprocess, sys, tempfile
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    code = (
-        "import sys, numpy as np; sys.path.insert(0, %r)\n"
-        "from cnmf_torch_b200.engine import DenseFrobeniusEngine\n"
-        "from cnmf_torch_b200.synth import nb_counts\n"
-        "x = nb_counts(1500, 900, k_true=6, seed=3, libsize=800.0)\n"
-        "eng = DenseFrobeniusEngine(x)\n"
-        "out = {}\n"
-        "for algo in ('mu', 'hals'):\n"
-        "    for K, R in ((7, 60), (12, 33)):\n"
-        "        res = eng.factorize(K, seeds=list(range(R)), algo=algo, tol=0.0, max_iter=20, return_H=True)\n"
-        "        out['W_%%s_%%d' %% (algo, K)] = res.W; out['H_%%s_%%d' %% (algo, K)] = res.H\n"
-        "        out['e_%%s_%%d' %% (algo, K)] = res.err\n"
-        "np.savez(sys.argv[1], **out)\n" % root)
-    outs = []
-    with tempfile.TemporaryDirectory() as tmp:
-        for mode in ("0", "2"):
-            path = os.path.join(tmp, f"sk{mode}.npz")
-            subprocess.run([sys.executable, "-c", code, path], check=True, env=dict(os.environ, CNMF_B200_TC_SK=mode))
-            with np.load(path) as z:
-                outs.append({k: z[k] for k in z.files})
-    a, b = outs
-    for k in a:
-        if k.startswith("e_"):
-            # the tensor core's fp32 accumulation is not round-to-nearest: cutting a tile's K range in two shifts
-            # every objective by a few 1e-6 relative, all in the same direction
-            np.testing.assert_allclose(a[k], b[k], rtol=1e-4)
-        else:
-            scale = np.abs(a[k]).max()
-            # 20 iterations amplify the rounding differences (HALS more than MU: its clamp at zero switches)
-            assert np.abs(a[k] - b[k]).max() <= (5e-2 if "hals" in k else 2e-3) * scale, k
-            assert _pearson(a[k], b[k]) >= 0.9999
-
-
 @pytest.mark.parametrize("N,G,K,R", [(50, 37, 2, 1), (129, 33, 6, 3), (1000, 31, 3, 7), (77, 500, 32, 2), (300, 130, 17, 5)])
 @pytest.mark.parametrize("algo", ["mu", "hals"])
 def test_engine_tc_ragged_shapes_match_oracle(N, G, K, R, algo):
