@@ -75,6 +75,8 @@ SIGNATURES = {
     "cnmf_b200_online_inner_workspace_bytes": (i64, [i64, i32]),
     "cnmf_b200_online_inner": (i32, [vp, i64, vp, i64, vp, vp, vp, i64, i32, i32, f32, f32, f32, f32, i32, vp, vp,
                                      vp, vp]),
+    "cnmf_b200_online_loop_workspace_bytes": (i64, [i32]),
+    "cnmf_b200_online_loop": (i32, [vp, i64, vp, i64, vp, vp, i64, i32, i32, f32, f32, f32, f32, i32, vp, vp, vp, vp]),
     "cnmf_b200_kl_constants": (i32, [vp, i64, vp, vp]),
     "cnmf_b200_to_half": (i32, [vp, vp, i64, vp]),
     "cnmf_b200_kl_half_step": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, vp, i32, i32, f32, f32, f32, vp]),

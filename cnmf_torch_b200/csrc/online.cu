@@ -91,6 +91,100 @@ __global__ void __launch_bounds__(1024) online_flag_kernel(const double* __restr
   if (threadIdx.x == 0) n_pending[0] = pending;
 }
 
+// ---------------------------------------------------------------------------------------------------------------
+// The whole inner loop of a chunk in ONE launch.  The two-kernels-per-iteration form above returns to the host
+// every few iterations to learn whether any replicate is still running (a 4-byte copy and a stream synchronise:
+// half of an online pass was launch and sync latency).  Here a replicate is owned by `nslab` CTAs (column slabs of
+// its factor) that stay resident for the entire loop: every iteration each CTA updates its columns, leaves its
+// partial sums of |new - old|^2 and |old|^2 in a slot, and the CTAs of the replicate meet at a counter in global
+// memory (release / acquire); each then adds the slots in slab order -- the same number in every CTA -- and the
+// replicate stops, on the device, exactly where `online_flag_kernel` would have stopped it.  Launched
+// cooperatively (all CTAs co-resident: the spin-wait needs it); replicates beyond the number of resident slots are
+// taken in turn by the same CTAs.
+constexpr int ONP_THREADS = 256;
+constexpr int ONP_MAX_SLABS = 8;
+
+template <int KP>
+__global__ void __launch_bounds__(ONP_THREADS) online_inner_persistent_kernel(
+    const float* __restrict__ Pt, int64_t ldp, float* __restrict__ state, int64_t lds, const float* __restrict__ gram,
+    const uint8_t* __restrict__ active, int64_t M, int R, float l1, float l2, float eps, float tol, int max_iter,
+    int nslab, int* __restrict__ iters, unsigned int* __restrict__ arrive, double* __restrict__ slots,
+    unsigned long long* __restrict__ total_iters) {
+  __shared__ float sgram[KP * KP];
+  __shared__ double red[ONP_THREADS / 32][2];
+  __shared__ int s_done;
+  const int slab = blockIdx.x % nslab, rslot = blockIdx.x / nslab, rstride = gridDim.x / nslab;
+  const int64_t cols_per = ((M + nslab - 1) / nslab + 3) / 4 * 4;
+  const int64_t c0 = (int64_t)slab * cols_per, c1 = (c0 + cols_per < M) ? c0 + cols_per : M;
+  for (int r = rslot; r < R; r += rstride) {
+    if (active != nullptr && active[r] == 0) continue;   // uniform over the replicate's CTAs
+    __syncthreads();
+    for (int i = threadIdx.x; i < KP * KP; i += ONP_THREADS) sgram[i] = gram[(int64_t)r * KP * KP + i];
+    __syncthreads();
+    const int64_t base = (int64_t)r * KP;
+    int it = 0;
+    while (it < max_iter) {
+      double dd = 0.0, nn = 0.0;
+      for (int64_t m = c0 + threadIdx.x; m < c1; m += ONP_THREADS) {
+        float p[KP], s[KP], old[KP];
+#pragma unroll
+        for (int k = 0; k < KP; ++k) {
+          p[k] = Pt[(base + k) * ldp + m];
+          s[k] = state[(base + k) * lds + m];
+          old[k] = s[k];
+        }
+        update_row<KP, CNMF_B200_ALGO_MU>(p, s, sgram, l1, l2, eps);
+        float d2 = 0.f, n2 = 0.f;
+#pragma unroll
+        for (int k = 0; k < KP; ++k) {
+          state[(base + k) * lds + m] = s[k];
+          const float d = s[k] - old[k];
+          d2 = fmaf(d, d, d2);
+          n2 = fmaf(old[k], old[k], n2);
+        }
+        dd += (double)d2;
+        nn += (double)n2;
+      }
+      dd = warp_sum(dd);
+      nn = warp_sum(nn);
+      if ((threadIdx.x & 31) == 0) { red[threadIdx.x >> 5][0] = dd; red[threadIdx.x >> 5][1] = nn; }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int w = 0; w < ONP_THREADS / 32; ++w) { a += red[w][0]; b += red[w][1]; }
+        if (nslab > 1) {
+          double* mine = slots + (((int64_t)r * ONP_MAX_SLABS + slab) * 2 + (it & 1)) * 2;
+          __stcg(mine, a);
+          __stcg(mine + 1, b);
+          __threadfence();
+          atomicAdd(arrive + r, 1u);
+          const unsigned int target = (unsigned int)nslab * (unsigned int)(it + 1);
+          unsigned int seen = 0, spins = 0;
+          do {
+            asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(arrive + r) : "memory");
+            if (seen < target && ++spins > (1u << 27)) __trap();   // a scheduling bug aborts instead of hanging
+          } while (seen < target);
+          a = 0.0; b = 0.0;
+          for (int sl = 0; sl < nslab; ++sl) {   // slab order: every CTA of the replicate forms the same sums
+            const double* q = slots + (((int64_t)r * ONP_MAX_SLABS + sl) * 2 + (it & 1)) * 2;
+            a += __ldcg(q);
+            b += __ldcg(q + 1);
+          }
+        }
+        const float rel = (float)sqrt(a) / ((float)sqrt(b) + eps);   // as online_flag_kernel / cnmf.py:374-378
+        s_done = rel < tol ? 1 : 0;
+      }
+      __syncthreads();
+      ++it;
+      if (s_done) break;
+    }
+    if (slab == 0 && threadIdx.x == 0) {
+      iters[r] += it;
+      if (total_iters != nullptr) atomicMax(total_iters, (unsigned long long)it);
+    }
+  }
+}
+
 __global__ void axpy_kernel(float* __restrict__ y, const float* __restrict__ x, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     y[i] += x[i];
@@ -157,6 +251,53 @@ int cnmf_b200_online_inner(const float* Pt, int64_t ldp, float* state, int64_t l
     online_flag_kernel<<<1, 1024, 0, st>>>(partials, nblk, R, tol, eps, done, active, iters, n_pending);
     CNMF_LAUNCH_CHECK();
   }
+  return 0;
+}
+
+int64_t cnmf_b200_online_loop_workspace_bytes(int32_t R) {
+  return align_up((int64_t)R * 4, 256) + (int64_t)R * ONP_MAX_SLABS * 2 * 2 * 8;
+}
+
+/* The inner loop to convergence in one cooperative launch (see online_inner_persistent_kernel): no host round
+ * trips.  iters[r] += iterations run by replicate r; max_iters_seen (optional, device, 64-bit) is raised to the
+ * largest count (what the host-driven form reports as "inner iterations").  Replaces the loop of
+ * fit_H_online (cnmf.py:355-378) for R replicates at once. */
+int cnmf_b200_online_loop(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
+                          const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
+                          float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
+                          void* workspace, void* stream) {
+  reset_launch_count();
+  CNMF_CHECK_ARG(Pt && state && gram && iters && workspace, "online_loop: null pointer");
+  CNMF_CHECK_ARG(M > 0 && R > 0 && ldp >= M && lds >= M && max_iter >= 0, "online_loop: bad shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  unsigned int* arrive = reinterpret_cast<unsigned int*>(workspace);
+  double* slots = reinterpret_cast<double*>(reinterpret_cast<char*>(workspace) + align_up((int64_t)R * 4, 256));
+  CNMF_CUDA(cudaMemsetAsync(arrive, 0, (size_t)R * 4, st));
+  int dev = 0, sms = 148;
+  CNMF_CUDA(cudaGetDevice(&dev));
+  CNMF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+  int per_sm = 0;
+  const void* kern = nullptr;
+  CNMF_DISPATCH_KP(Kp, { kern = reinterpret_cast<const void*>(online_inner_persistent_kernel<KP>);
+                         CNMF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, online_inner_persistent_kernel<KP>,
+                                                                                ONP_THREADS, 0)); });
+  if (per_sm > 2) per_sm = 2;   // leave room for the kernels of other streams
+  CNMF_CHECK_ARG(per_sm >= 1, "online_loop: kernel does not fit an SM");
+  const int resident = per_sm * sms;
+  int nslab = resident / R;
+  const int max_slabs_cols = (int)ceil_div(M, ONP_THREADS);
+  if (nslab > ONP_MAX_SLABS) nslab = ONP_MAX_SLABS;
+  if (nslab > max_slabs_cols) nslab = max_slabs_cols;
+  if (nslab < 1) nslab = 1;
+  const int rslots = R * nslab <= resident ? R : resident / nslab;
+  const int grid = rslots * nslab;
+  int64_t M_ = M;
+  int R_ = R, max_iter_ = max_iter;
+  void* args[] = {(void*)&Pt, (void*)&ldp, (void*)&state, (void*)&lds, (void*)&gram, (void*)&active, (void*)&M_, (void*)&R_,
+                  (void*)&l1, (void*)&l2, (void*)&eps, (void*)&tol, (void*)&max_iter_, (void*)&nslab, (void*)&iters,
+                  (void*)&arrive, (void*)&slots, (void*)&max_iters_seen};
+  CNMF_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(ONP_THREADS), args, 0, st));
+  count_launch();
   return 0;
 }
 

@@ -281,34 +281,24 @@ class DenseFrobeniusEngine:
         Ac = torch.zeros((R, Kp, Kp), **f32)
         Wop = torch.zeros((rk, ldw), **f32)
         Hop = torch.zeros((rk, ldh), **f32)
-        done = torch.zeros(R, device=dev, dtype=torch.uint8)
-        iters = torch.zeros(R, device=dev, dtype=torch.int32)
-        npend = torch.zeros(1, device=dev, dtype=torch.int32)
-        ws_inner = torch.empty(max(256, int(L.cnmf_b200_online_inner_workspace_bytes(max(cmax, G), R))), device=dev,
-                               dtype=torch.uint8)
         ws_gram = torch.empty(max(256, int(L.cnmf_b200_gram_workspace_bytes(R, Kp, max(cmax, G)))), device=dev,
                               dtype=torch.uint8)
         Wall, Ht, active = b.Wall, b.Ht, b.active
         n_chunks = _d.allreduce_max_int((N + chunk_size - 1) // chunk_size, dev, grp)
-        inner_total = [0, 0]
 
         def refresh_w_caches():
             check(L.cnmf_b200_round_tf32_2d(ptr(Wop), ptr(Wall), rk, G, ldw, st()), "round_tf32_2d")
             check(L.cnmf_b200_gram(ptr(Wall), ldw, R, Kp, G, ptr(b.gramW), ptr(ws_gram), st()), "gram")
 
+        iters_hw = torch.zeros((2, R), device=dev, dtype=torch.int32)     # inner iterations per replicate: h loops, W loops
+        ws_loop = torch.empty(max(256, int(L.cnmf_b200_online_loop_workspace_bytes(R))), device=dev, dtype=torch.uint8)
+
         def inner(p_ptr, p_ld, s_ptr, s_ld, g_ptr, M, tol_, l1, l2, which):
-            done.zero_()
-            n_done = 0
-            while n_done < chunk_max_iter:
-                n = min(inner_batch, chunk_max_iter - n_done)
-                check(L.cnmf_b200_online_inner(p_ptr, p_ld, s_ptr, s_ld, g_ptr, ptr(done), ptr(active), M, R, Kp,
-                                               l1, l2, eps, tol_, n, ptr(iters), ptr(npend), ptr(ws_inner), st()),
-                      "online_inner")
-                b.launches += L.cnmf_b200_last_launch_count()
-                n_done += n
-                inner_total[which] += n
-                if int(npend.item()) == 0:       # 4-byte D2H every `inner_batch` iterations
-                    break
+            # the whole inner loop in one launch: replicates stop on the device (no host round trip per few iterations)
+            check(L.cnmf_b200_online_loop(p_ptr, p_ld, s_ptr, s_ld, g_ptr, ptr(active), M, R, Kp, l1, l2, eps, tol_,
+                                          int(chunk_max_iter), ptr(iters_hw[which]), None, ptr(ws_loop), st()),
+                  "online_loop")
+            b.launches += 1
 
         def h_chunk(lo, c):
             check(L.cnmf_b200_dense_gemm_tf32(ptr(self.X) + 4 * lo * self.ldx, self.ldx, c, G, ptr(Wop), ldw, ptr(Pt),
@@ -383,7 +373,8 @@ class DenseFrobeniusEngine:
         if profile is not None and ar_events:
             torch.cuda.synchronize()
             profile["allreduce_ms"] = profile.get("allreduce_ms", 0.0) + float(sum(a.elapsed_time(b) for a, b in ar_events))
-        inner = {"h": inner_total[0], "w": inner_total[1]}
+        it_host = iters_hw.cpu().numpy()
+        inner = {"h": int(it_host[0].max()), "w": int(it_host[1].max())}   # of the replicate that iterated most
         if groups is not None:   # a stack of several K: one result per K
             out = {}
             for k, sl, W, H in b.results_by_group(return_H):

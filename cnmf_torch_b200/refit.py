@@ -65,10 +65,8 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
     ldp = pad4(cmax)
     Pt = torch.zeros((Kp, ldp), device=dev, dtype=torch.float32)
     xbuf = torch.zeros((cmax, ldg), device=dev, dtype=torch.float32)
-    done = torch.zeros(1, device=dev, dtype=torch.uint8)
     iters = torch.zeros(1, device=dev, dtype=torch.int32)
-    npend = torch.zeros(1, device=dev, dtype=torch.int32)
-    ws = torch.empty(max(256, int(L.cnmf_b200_online_inner_workspace_bytes(cmax, 1))), device=dev, dtype=torch.uint8)
+    ws = torch.empty(max(256, int(L.cnmf_b200_online_loop_workspace_bytes(1))), device=dev, dtype=torch.uint8)
     Hs = torch.zeros((Kp, ldp), device=dev, dtype=torch.float32)   # chunk-local state: 16-byte aligned columns
     for lo in range(0, n, int(chunk_size)):
         c = min(int(chunk_size), n - lo)
@@ -77,15 +75,9 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
         xbuf[:c, :g] = torch.from_numpy(xc).to(dev)                                       # chunk upload (cnmf.py:351)
         check(L.cnmf_b200_gemm_nt(ptr(Wd), ldg, Kp, ptr(xbuf), ldg, c, g, ptr(Pt), ldp, st), "gemm x W^T")
         Hs[:, :c] = Ht[:, lo:lo + c]
-        done.zero_()
-        n_done = 0
-        while n_done < chunk_max_iter:
-            m = min(inner_batch, chunk_max_iter - n_done)
-            check(L.cnmf_b200_online_inner(ptr(Pt), ldp, ptr(Hs), ldp, ptr(gram), ptr(done), None, c, 1, Kp,
-                                           float(l1_reg_H), float(l2_reg_H), float(epsilon), float(h_tol), m,
-                                           ptr(iters), ptr(npend), ptr(ws), st), "online_inner")
-            n_done += m
-            if int(npend.item()) == 0:
-                break
+        # the chunk's inner loop to convergence in one launch (stops on the device, cnmf.py:365-378)
+        check(L.cnmf_b200_online_loop(ptr(Pt), ldp, ptr(Hs), ldp, ptr(gram), None, c, 1, Kp, float(l1_reg_H),
+                                      float(l2_reg_H), float(epsilon), float(h_tol), int(chunk_max_iter), ptr(iters),
+                                      None, ptr(ws), st), "online_loop")
         Ht[:, lo:lo + c] = Hs[:, :c]
     return Ht[:k, :n].t().contiguous().cpu().numpy()

@@ -218,6 +218,17 @@ int cnmf_b200_online_inner(const float* Pt, int64_t ldp, float* state, int64_t l
                            float tol, int32_t n_iters, int32_t* iters, int32_t* n_pending, void* workspace,
                            void* stream);
 
+/* The same loop run TO CONVERGENCE in one launch, no host round trip: every replicate iterates until rel_r < tol or
+ * max_iter, decided on the device (the replicate's CTAs meet at a counter in global memory after every iteration; a
+ * cooperative launch keeps them co-resident).  iters[r] += iterations run; max_iters_seen (device, optional) is raised
+ * to the largest of them.  Same arithmetic and stopping rule as cnmf_b200_online_inner (cnmf.py:365-378).
+ * workspace: cnmf_b200_online_loop_workspace_bytes(R) bytes. */
+int64_t cnmf_b200_online_loop_workspace_bytes(int32_t R);
+int cnmf_b200_online_loop(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
+                          const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
+                          float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
+                          void* workspace, void* stream);
+
 /* ------------------------------------------------------------------------------------------
  * Sparse Kullback-Leibler engine (replicate-batched, CSR X).  Replaces run_nmf(beta_loss=
  * 'kullback-leibler', algo='mu') called at cnmf.py:819; update rule sklearn _nmf.py:562-607, 640-678

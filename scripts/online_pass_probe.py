@@ -1,17 +1,21 @@
-"""Dev probe: wall time per online pass (difference of a 4-pass and a 2-pass run), device-drawn init."""
+"""Dev probe: one rank's share of cfg-5 (online mode, chunk 5000, K=15, R=50) -- ms per pass, and under
+`ncu --metrics gpu__time_duration.sum` the launch list of a pass.
+    python scripts/online_pass_probe.py [cells]"""
 import os, sys, time
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 import torch
-from cnmf_torch_b200.synth import nb_counts
+import bench
 from cnmf_torch_b200.engine import DenseFrobeniusEngine
-N = int(os.environ.get("N", "50000")); K = int(os.environ.get("K", "15")); R = int(os.environ.get("R", "50"))
-x = nb_counts(N, 2000, seed=14, libsize=400.0)
-eng = DenseFrobeniusEngine(x, init_device="cuda")
-def run(p):
-    torch.cuda.synchronize(); t0 = time.perf_counter()
-    res = eng.factorize_online(K, seeds=list(range(1, R + 1)), tol=0.0, max_pass=p, chunk_size=5000, chunk_max_iter=1000, inner_batch=int(os.environ.get("IB", "4")))
-    torch.cuda.synchronize(); return time.perf_counter() - t0, res
-run(1)
-t2, r2 = run(2); t4, r4 = run(4)
-print(f"online N={N} K={K} R={R}: 2 passes {t2*1e3:.1f} ms, 4 passes {t4*1e3:.1f} ms -> {(t4-t2)/2*1e3:.1f} ms per pass; "
-      f"inner iterations (4 passes) {r4.inner_iterations}, launches {r4.launches}")
+n = int(sys.argv[1]) if len(sys.argv) > 1 else 125000
+dev = torch.device("cuda", 0)
+x = bench._cfg5_block_device(n, 0, dev)
+eng = DenseFrobeniusEngine(x, device=dev, init_device="cuda")
+kw = dict(tol=0.0, chunk_size=5000, chunk_max_iter=200)
+eng.factorize_online(15, seeds=list(range(50)), max_pass=1, **kw)
+torch.cuda.synchronize()
+for passes in (1, 3):
+    t0 = time.perf_counter()
+    res = eng.factorize_online(15, seeds=list(range(50)), max_pass=passes, **kw)
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    print(f"{n} cells, {passes} pass(es): {dt * 1e3:.1f} ms total, inner iterations {res.inner_iterations}, launches {res.launches}")

@@ -72,6 +72,64 @@ def test_online_inner_loop_matches_reference_fit_H_online(golden_dir):
         np.testing.assert_allclose(out, g["out_" + tag], rtol=2e-4, atol=1e-6)
 
 
+def test_persistent_loop_matches_reference_fit_H_online_and_the_stepwise_form(golden_dir):
+    """cnmf_b200_online_loop (the whole inner loop in one cooperative launch, stopping decided on the device) against
+    the REFERENCE's fit_H_online output, and against the two-kernels-per-iteration form for many replicates at once:
+    several column slabs per replicate (R small), one slab (R large), more replicates than resident CTAs."""
+    import os
+    from cnmf_torch_b200 import _lib as L
+    lib = L.lib()
+    st = torch.cuda.current_stream().cuda_stream
+    g = np.load(os.path.join(golden_dir, "fit_h_online.npz"), allow_pickle=True)
+    x, w, h0 = g["x"], g["w"], g["h_init"]
+    n, k = h0.shape
+    Kp = 8
+    for tag, chunk, tol, max_it in (("default", 100, 0.05, 200), ("tight", 64, 1e-3, 50)):
+        out = np.zeros_like(h0)
+        for lo in range(0, n, chunk):
+            c = min(chunk, n - lo)
+            ld = (c + 3) // 4 * 4
+            P = torch.zeros(Kp, ld, device="cuda"); S = torch.zeros(Kp, ld, device="cuda")
+            P[:k, :c] = torch.from_numpy((x[lo:lo + c] @ w.T).T.copy()).cuda()
+            S[:k, :c] = torch.from_numpy(np.clip(h0[lo:lo + c], 0, None).T.copy()).cuda()
+            gram = torch.zeros(1, Kp, Kp, device="cuda"); gram[0, :k, :k] = torch.from_numpy(w @ w.T).cuda()
+            iters = torch.zeros(1, dtype=torch.int32, device="cuda")
+            ws = torch.empty(int(lib.cnmf_b200_online_loop_workspace_bytes(1)) + 256, dtype=torch.uint8, device="cuda")
+            L.check(lib.cnmf_b200_online_loop(P.data_ptr(), ld, S.data_ptr(), ld, gram.data_ptr(), None, c, 1, Kp, 0.0, 0.0,
+                                              1e-16, tol, max_it, iters.data_ptr(), None, ws.data_ptr(), st))
+            out[lo:lo + c] = S[:k, :c].T.cpu().numpy()
+        np.testing.assert_allclose(out, g["out_" + tag], rtol=2e-4, atol=1e-6)
+    # many replicates: identical iteration counts and states as the stepwise form
+    torch.manual_seed(3)
+    for R, M, Kp in ((3, 5000, 16), (50, 2000, 16), (130, 777, 12), (700, 300, 4)):
+        ld = (M + 3) // 4 * 4
+        P = torch.rand(R * Kp, ld, device="cuda") * 3.0
+        S0 = torch.rand(R * Kp, ld, device="cuda") + 0.05
+        Gm = torch.rand(R, Kp, Kp, device="cuda")
+        Gm = Gm @ Gm.transpose(1, 2) + 0.1 * torch.eye(Kp, device="cuda")
+        active = torch.ones(R, dtype=torch.uint8, device="cuda"); active[R // 2] = 0
+        tol, max_it = 2e-2, 40
+        # stepwise
+        S1 = S0.clone()
+        done = torch.zeros(R, dtype=torch.uint8, device="cuda"); it1 = torch.zeros(R, dtype=torch.int32, device="cuda")
+        npend = torch.zeros(1, dtype=torch.int32, device="cuda")
+        ws1 = torch.empty(int(lib.cnmf_b200_online_inner_workspace_bytes(M, R)) + 256, dtype=torch.uint8, device="cuda")
+        L.check(lib.cnmf_b200_online_inner(P.data_ptr(), ld, S1.data_ptr(), ld, Gm.data_ptr(), done.data_ptr(),
+                                           active.data_ptr(), M, R, Kp, 0.01, 0.02, 1e-16, tol, max_it, it1.data_ptr(),
+                                           npend.data_ptr(), ws1.data_ptr(), st))
+        # one launch
+        S2 = S0.clone()
+        it2 = torch.zeros(R, dtype=torch.int32, device="cuda")
+        ws2 = torch.empty(int(lib.cnmf_b200_online_loop_workspace_bytes(R)) + 256, dtype=torch.uint8, device="cuda")
+        L.check(lib.cnmf_b200_online_loop(P.data_ptr(), ld, S2.data_ptr(), ld, Gm.data_ptr(), active.data_ptr(), M, R, Kp,
+                                          0.01, 0.02, 1e-16, tol, max_it, it2.data_ptr(), None, ws2.data_ptr(), st))
+        torch.cuda.synchronize()
+        assert torch.equal(it1, it2), (R, M, Kp, it1[:8].tolist(), it2[:8].tolist())
+        assert int(it2[R // 2]) == 0 and torch.equal(S2[(R // 2) * Kp:(R // 2 + 1) * Kp], S0[(R // 2) * Kp:(R // 2 + 1) * Kp])
+        assert 1 < int(it2.max()) and int(it2[it2 > 0].min()) < max_it      # replicates really stop at different times
+        torch.testing.assert_close(S2, S1, rtol=0, atol=0)
+
+
 @pytest.mark.parametrize("K,chunk", [(5, 100), (9, 5000), (6, 248)])
 def test_online_engine_matches_oracle(problem, K, chunk):
     from cnmf_torch_b200.engine import DenseFrobeniusEngine
