@@ -48,6 +48,20 @@ class KlProblem(C.Structure):
     ]
 
 
+class OnlineChunkArgs(C.Structure):
+    """Mirror of ``cnmf_b200_online_chunk_args``."""
+    _fields_ = [
+        ("x", vp), ("ldx", i64), ("xt", vp), ("ldxt", i64), ("c", i64), ("n_genes", i64), ("R", i32), ("Kp", i32),
+        ("Wall", vp), ("Wop", vp), ("ldw", i64), ("Ht", vp), ("ldh", i64), ("Hs", vp), ("Hopc", vp), ("Pt", vp),
+        ("ldp", i64), ("Wlo", vp), ("cross", vp), ("gramH_acc", vp),
+        ("gramW", vp), ("A", vp), ("Ac", vp), ("Bst", vp), ("Bc", vp), ("active", vp),
+        ("l1_H", f32), ("l2_H", f32), ("l1_W", f32), ("l2_W", f32), ("eps", f32), ("h_tol", f32), ("w_tol", f32),
+        ("max_iter", i32), ("iters_h", vp), ("iters_w", vp), ("ws_loop", vp), ("ws_gram", vp),
+    ]
+
+
+ONLINE_REFRESH, ONLINE_USAGE, ONLINE_SPECTRA = 0, 1, 2
+
 # name -> (restype, argtypes).  Every symbol include/cnmf_b200.h declares must be listed here;
 # tests/test_abi.py checks the header against this table and the built library.
 SIGNATURES = {
@@ -77,6 +91,7 @@ SIGNATURES = {
                                      vp, vp]),
     "cnmf_b200_online_loop_workspace_bytes": (i64, [i32]),
     "cnmf_b200_online_loop": (i32, [vp, i64, vp, i64, vp, vp, i64, i32, i32, f32, f32, f32, f32, i32, vp, vp, vp, vp]),
+    "cnmf_b200_online_chunk": (i32, [C.POINTER(OnlineChunkArgs), i32, vp]),
     "cnmf_b200_kl_constants": (i32, [vp, i64, vp, vp]),
     "cnmf_b200_to_half": (i32, [vp, vp, i64, vp]),
     "cnmf_b200_kl_half_step": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, vp, i32, i32, f32, f32, f32, vp]),

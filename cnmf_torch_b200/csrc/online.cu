@@ -9,6 +9,8 @@
 // is iterated on (A, B) until w_tol.  The two inner loops are the same computation:
 //     s <- s * max(p - l1, 0) / (s G + l2 s)           (update_row, common.cuh)
 // with (p, G) = (x W^T, W W^T) for h and (B, A) for W, so one kernel serves both.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace cnmf {
@@ -104,12 +106,14 @@ __global__ void __launch_bounds__(1024) online_flag_kernel(const double* __restr
 constexpr int ONP_THREADS = 256;
 constexpr int ONP_MAX_SLABS = 8;
 
-template <int KP>
-__global__ void __launch_bounds__(ONP_THREADS) online_inner_persistent_kernel(
+// REGS > 0: the CTA's columns fit REGS per thread and their state lives in registers for the whole loop (read once,
+// written once): an iteration then streams only P from L2 -- a third of the bytes of the streaming form (REGS = 0).
+template <int KP, int REGS>
+__global__ void __launch_bounds__(ONP_THREADS, REGS > 0 ? 2 : 1) online_inner_persistent_kernel(
     const float* __restrict__ Pt, int64_t ldp, float* __restrict__ state, int64_t lds, const float* __restrict__ gram,
     const uint8_t* __restrict__ active, int64_t M, int R, float l1, float l2, float eps, float tol, int max_iter,
     int nslab, int* __restrict__ iters, unsigned int* __restrict__ arrive, double* __restrict__ slots,
-    unsigned long long* __restrict__ total_iters) {
+    unsigned long long* __restrict__ total_iters, double* __restrict__ cross) {
   __shared__ float sgram[KP * KP];
   __shared__ double red[ONP_THREADS / 32][2];
   __shared__ int s_done;
@@ -122,9 +126,42 @@ __global__ void __launch_bounds__(ONP_THREADS) online_inner_persistent_kernel(
     for (int i = threadIdx.x; i < KP * KP; i += ONP_THREADS) sgram[i] = gram[(int64_t)r * KP * KP + i];
     __syncthreads();
     const int64_t base = (int64_t)r * KP;
+    float sreg[REGS > 0 ? REGS : 1][KP];
+    if (REGS > 0) {
+#pragma unroll
+      for (int j = 0; j < REGS; ++j) {
+        const int64_t m = c0 + threadIdx.x + (int64_t)j * ONP_THREADS;
+#pragma unroll
+        for (int k = 0; k < KP; ++k) sreg[j][k] = m < c1 ? state[(base + k) * lds + m] : 0.f;
+      }
+    }
     int it = 0;
     while (it < max_iter) {
       double dd = 0.0, nn = 0.0;
+      if (REGS > 0) {
+#pragma unroll
+        for (int j = 0; j < REGS; ++j) {
+          const int64_t m = c0 + threadIdx.x + (int64_t)j * ONP_THREADS;
+          if (m < c1) {
+            float p[KP], old[KP];
+#pragma unroll
+            for (int k = 0; k < KP; ++k) {
+              p[k] = Pt[(base + k) * ldp + m];
+              old[k] = sreg[j][k];
+            }
+            update_row<KP, CNMF_B200_ALGO_MU>(p, sreg[j], sgram, l1, l2, eps);
+            float d2 = 0.f, n2 = 0.f;
+#pragma unroll
+            for (int k = 0; k < KP; ++k) {
+              const float d = sreg[j][k] - old[k];
+              d2 = fmaf(d, d, d2);
+              n2 = fmaf(old[k], old[k], n2);
+            }
+            dd += (double)d2;
+            nn += (double)n2;
+          }
+        }
+      } else {
       for (int64_t m = c0 + threadIdx.x; m < c1; m += ONP_THREADS) {
         float p[KP], s[KP], old[KP];
 #pragma unroll
@@ -144,6 +181,7 @@ __global__ void __launch_bounds__(ONP_THREADS) online_inner_persistent_kernel(
         }
         dd += (double)d2;
         nn += (double)n2;
+      }
       }
       dd = warp_sum(dd);
       nn = warp_sum(nn);
@@ -178,6 +216,53 @@ __global__ void __launch_bounds__(ONP_THREADS) online_inner_persistent_kernel(
       ++it;
       if (s_done) break;
     }
+    if (REGS > 0) {
+#pragma unroll
+      for (int j = 0; j < REGS; ++j) {
+        const int64_t m = c0 + threadIdx.x + (int64_t)j * ONP_THREADS;
+        if (m < c1) {
+#pragma unroll
+          for (int k = 0; k < KP; ++k) state[(base + k) * lds + m] = sreg[j][k];
+        }
+      }
+    }
+    if (cross != nullptr) {
+      // cross[r] += <s, p> over all columns (the cross term of the Frobenius objective, <H, X W^T>): per-CTA fp64
+      // partials, met at the same counter, added in slab order by the replicate's first CTA
+      double cc = 0.0;
+      for (int64_t m = c0 + threadIdx.x; m < c1; m += ONP_THREADS) {
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < KP; ++k) acc = fmaf(state[(base + k) * lds + m], Pt[(base + k) * ldp + m], acc);
+        cc += (double)acc;
+      }
+      cc = warp_sum(cc);
+      __syncthreads();
+      if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5][0] = cc;
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        double a = 0.0;
+        for (int w = 0; w < ONP_THREADS / 32; ++w) a += red[w][0];
+        if (nslab > 1) {
+          double* mine = slots + (((int64_t)r * ONP_MAX_SLABS + slab) * 2 + (it & 1)) * 2;
+          __stcg(mine, a);
+          __threadfence();
+          atomicAdd(arrive + r, 1u);
+          if (slab == 0) {
+            const unsigned int target = (unsigned int)nslab * (unsigned int)(it + 1);
+            unsigned int seen = 0, spins = 0;
+            do {
+              asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(seen) : "l"(arrive + r) : "memory");
+              if (seen < target && ++spins > (1u << 27)) __trap();
+            } while (seen < target);
+            a = 0.0;
+            for (int sl = 0; sl < nslab; ++sl)
+              a += __ldcg(slots + (((int64_t)r * ONP_MAX_SLABS + sl) * 2 + (it & 1)) * 2);
+          }
+        }
+        if (slab == 0) cross[r] += a;
+      }
+    }
     if (slab == 0 && threadIdx.x == 0) {
       iters[r] += it;
       if (total_iters != nullptr) atomicMax(total_iters, (unsigned long long)it);
@@ -194,6 +279,9 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
                         float* state_op, int64_t lds, const float* gram, const uint8_t* active, int R, int Kp, int algo,
                         float l1, float l2, float eps, double* partials, cudaStream_t st);
 int launch_round_tf32_2d(float* dst, const float* src, int64_t rows, int64_t cols, int64_t ld, cudaStream_t st);
+int launch_gram(const float* F, int64_t ld, int R, int Kp, int64_t L, float* gram, void* ws, cudaStream_t st);
+int launch_residual_tf32(float* dst, const float* master, const float* rounded, int64_t rows, int64_t cols, int64_t ld,
+                         cudaStream_t st);
 
 }  // namespace cnmf
 
@@ -262,10 +350,23 @@ int64_t cnmf_b200_online_loop_workspace_bytes(int32_t R) {
  * trips.  iters[r] += iterations run by replicate r; max_iters_seen (optional, device, 64-bit) is raised to the
  * largest count (what the host-driven form reports as "inner iterations").  Replaces the loop of
  * fit_H_online (cnmf.py:355-378) for R replicates at once. */
+static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
+                            const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
+                            float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
+                            void* workspace, double* cross, void* stream);
+
 int cnmf_b200_online_loop(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                           const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                           float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
                           void* workspace, void* stream) {
+  return online_loop_impl(Pt, ldp, state, lds, gram, active, M, R, Kp, l1, l2, eps, tol, max_iter, iters, max_iters_seen,
+                          workspace, nullptr, stream);
+}
+
+static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
+                            const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
+                            float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
+                            void* workspace, double* cross, void* stream) {
   reset_launch_count();
   CNMF_CHECK_ARG(Pt && state && gram && iters && workspace, "online_loop: null pointer");
   CNMF_CHECK_ARG(M > 0 && R > 0 && ldp >= M && lds >= M && max_iter >= 0, "online_loop: bad shape");
@@ -276,28 +377,126 @@ int cnmf_b200_online_loop(const float* Pt, int64_t ldp, float* state, int64_t ld
   int dev = 0, sms = 148;
   CNMF_CUDA(cudaGetDevice(&dev));
   CNMF_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-  int per_sm = 0;
+  // The register form (a CTA's columns <= 4 per thread, state in registers, 2 CTAs per SM) when the replicates' slabs
+  // fit the resident CTAs that way; else the streaming form with its own residency.
+  auto plan = [&](int resident, int* nslab_out, int* grid_out) {
+    int ns = resident / R;
+    const int max_slabs_cols = (int)ceil_div(M, ONP_THREADS);
+    if (ns > ONP_MAX_SLABS) ns = ONP_MAX_SLABS;
+    if (ns > max_slabs_cols) ns = max_slabs_cols;
+    if (ns < 1) ns = 1;
+    const int rslots = R * ns <= resident ? R : resident / ns;
+    *nslab_out = ns;
+    *grid_out = rslots * ns;
+  };
   const void* kern = nullptr;
-  CNMF_DISPATCH_KP(Kp, { kern = reinterpret_cast<const void*>(online_inner_persistent_kernel<KP>);
-                         CNMF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, online_inner_persistent_kernel<KP>,
-                                                                                ONP_THREADS, 0)); });
-  if (per_sm > 2) per_sm = 2;   // leave room for the kernels of other streams
-  CNMF_CHECK_ARG(per_sm >= 1, "online_loop: kernel does not fit an SM");
-  const int resident = per_sm * sms;
-  int nslab = resident / R;
-  const int max_slabs_cols = (int)ceil_div(M, ONP_THREADS);
-  if (nslab > ONP_MAX_SLABS) nslab = ONP_MAX_SLABS;
-  if (nslab > max_slabs_cols) nslab = max_slabs_cols;
-  if (nslab < 1) nslab = 1;
-  const int rslots = R * nslab <= resident ? R : resident / nslab;
-  const int grid = rslots * nslab;
+  int nslab = 1, grid = 1;
+  static const bool no_regs = getenv("CNMF_B200_ONLINE_NOREG") != nullptr;   // dev knob
+  if (Kp <= 16 && !no_regs) {
+    int per_sm_r = 0;
+    CNMF_DISPATCH_KP(Kp, CNMF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                             &per_sm_r, online_inner_persistent_kernel<KP, 4>, ONP_THREADS, 0)));
+    if (per_sm_r > 2) per_sm_r = 2;   // leave room for the kernels of other streams
+    if (per_sm_r >= 1) {
+      plan(per_sm_r * sms, &nslab, &grid);
+      const int64_t cols_per = (ceil_div(M, nslab) + 3) / 4 * 4;
+      const int cpt = (int)ceil_div(cols_per, ONP_THREADS);
+      if (cpt <= 2) {
+        CNMF_DISPATCH_KP(Kp, kern = reinterpret_cast<const void*>(online_inner_persistent_kernel<KP, 2>));
+      } else if (cpt <= 4) {
+        CNMF_DISPATCH_KP(Kp, kern = reinterpret_cast<const void*>(online_inner_persistent_kernel<KP, 4>));
+      }
+    }
+  }
+  if (kern == nullptr) {
+    int per_sm = 0;
+    CNMF_DISPATCH_KP(Kp, { kern = reinterpret_cast<const void*>(online_inner_persistent_kernel<KP, 0>);
+                           CNMF_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(
+                               &per_sm, online_inner_persistent_kernel<KP, 0>, ONP_THREADS, 0)); });
+    if (per_sm > 2) per_sm = 2;
+    CNMF_CHECK_ARG(per_sm >= 1, "online_loop: kernel does not fit an SM");
+    plan(per_sm * sms, &nslab, &grid);
+  }
   int64_t M_ = M;
   int R_ = R, max_iter_ = max_iter;
   void* args[] = {(void*)&Pt, (void*)&ldp, (void*)&state, (void*)&lds, (void*)&gram, (void*)&active, (void*)&M_, (void*)&R_,
                   (void*)&l1, (void*)&l2, (void*)&eps, (void*)&tol, (void*)&max_iter_, (void*)&nslab, (void*)&iters,
-                  (void*)&arrive, (void*)&slots, (void*)&max_iters_seen};
+                  (void*)&arrive, (void*)&slots, (void*)&max_iters_seen, (void*)&cross};
   CNMF_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(ONP_THREADS), args, 0, st));
   count_launch();
+  return 0;
+}
+
+/* One chunk of an online pass as ONE call (the kernels are the ones above and the tensor-core GEMM; what this saves
+ * is the host: a dozen library calls per chunk from Python cost more than the kernels they enqueue).  The chunk's
+ * usages are worked on in a COMPACT scratch copy (Hs, [R*Kp x ldp]): in the resident array a row of the chunk is
+ * ldh floats from the next -- 4 MB at a million cells, one page per row for every TMA box and every warp.
+ *   phase CNMF_B200_ONLINE_USAGE   : P = x W^T, inner loop on the chunk's usages, then the chunk's statistics
+ *                                    Ac = h^T h and Bc = h^T x;
+ *   phase CNMF_B200_ONLINE_REFRESH : P = x W^T to fp32 accuracy (a second pass on W - tf32(W)), inner loop (max_iter
+ *                                    may be 0: evaluation only), cross += <h, P>, gramH_acc += h^T h: the refresh of H
+ *                                    at the end of a pass and, on the way, the data-dependent terms of the objective;
+ *   phase CNMF_B200_ONLINE_SPECTRA : A += Ac, B += Bc (after the caller's all-reduce when cells are sharded), inner
+ *                                    loop on W against (A, B), then W's tf32 copy, its residual and Gram. */
+static int copy_rows(float* dst, int64_t ldd, const float* src, int64_t lds_, int64_t rows, int64_t cols, cudaStream_t st) {
+  CNMF_CUDA(cudaMemcpy2DAsync(dst, (size_t)ldd * 4, src, (size_t)lds_ * 4, (size_t)cols * 4, (size_t)rows,
+                              cudaMemcpyDeviceToDevice, st));
+  return 0;
+}
+
+int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, void* stream) {
+  reset_launch_count();
+  CNMF_CHECK_ARG(a != nullptr, "online_chunk: null arguments");
+  CNMF_CHECK_ARG(a->R > 0 && a->Kp > 0 && a->n_genes > 0, "online_chunk: empty shape");
+  cudaStream_t st = (cudaStream_t)stream;
+  const int64_t rk = (int64_t)a->R * a->Kp;
+  int64_t n = 0;
+  if (phase == CNMF_B200_ONLINE_USAGE || phase == CNMF_B200_ONLINE_REFRESH) {
+    CNMF_CHECK_ARG(a->c > 0 && a->x && a->Wop && a->Ht && a->Hs && a->Pt && a->gramW && a->iters_h && a->ws_loop &&
+                       a->ws_gram && a->Ac, "online_chunk: null pointer (usage phase)");
+    CNMF_CHECK_ARG(a->ldp >= a->c && a->ldp % 4 == 0, "online_chunk: ldp too small or not a multiple of 4");
+    CNMF_TRY(copy_rows(a->Hs, a->ldp, a->Ht, a->ldh, rk, a->c, st));
+    CNMF_TRY(cnmf_b200_dense_gemm_tf32(a->x, a->ldx, a->c, a->n_genes, a->Wop, a->ldw, a->Pt, a->ldp, a->active, a->R,
+                                       a->Kp, 0, stream));
+    n += 2;
+    const bool refresh = phase == CNMF_B200_ONLINE_REFRESH;
+    if (refresh && a->Wlo != nullptr) {
+      CNMF_TRY(cnmf_b200_dense_gemm_tf32(a->x, a->ldx, a->c, a->n_genes, a->Wlo, a->ldw, a->Pt, a->ldp, a->active, a->R,
+                                         a->Kp, 1, stream));
+      n += 1;
+    }
+    CNMF_TRY(online_loop_impl(a->Pt, a->ldp, a->Hs, a->ldp, a->gramW, a->active, a->c, a->R, a->Kp, a->l1_H, a->l2_H,
+                              a->eps, a->h_tol, a->max_iter, a->iters_h, nullptr, a->ws_loop,
+                              refresh ? a->cross : nullptr, stream));
+    CNMF_TRY(launch_gram(a->Hs, a->ldp, a->R, a->Kp, a->c, a->Ac, a->ws_gram, st));
+    n += 3;
+    if (refresh) {
+      if (a->gramH_acc != nullptr) { CNMF_TRY(cnmf_b200_axpy(a->gramH_acc, a->Ac, (int64_t)a->R * a->Kp * a->Kp, stream)); n += 1; }
+    } else {
+      CNMF_CHECK_ARG(a->xt && a->Hopc && a->Bc, "online_chunk: null pointer (statistics)");
+      CNMF_TRY(launch_round_tf32_2d(a->Hopc, a->Hs, rk, a->c, a->ldp, st));
+      CNMF_TRY(cnmf_b200_dense_gemm_tf32(a->xt, a->ldxt, a->n_genes, a->c, a->Hopc, a->ldp, a->Bc, a->ldw, a->active,
+                                         a->R, a->Kp, 0, stream));
+      n += 2;
+    }
+    if (a->max_iter > 0) { CNMF_TRY(copy_rows(a->Ht, a->ldh, a->Hs, a->ldp, rk, a->c, st)); n += 1; }
+  } else if (phase == CNMF_B200_ONLINE_SPECTRA) {
+    CNMF_CHECK_ARG(a->A && a->Ac && a->Bst && a->Bc && a->Wall && a->Wop && a->gramW && a->iters_w && a->ws_loop &&
+                       a->ws_gram, "online_chunk: null pointer (spectra phase)");
+    CNMF_TRY(cnmf_b200_axpy(a->A, a->Ac, (int64_t)a->R * a->Kp * a->Kp, stream));
+    CNMF_TRY(cnmf_b200_axpy(a->Bst, a->Bc, rk * a->ldw, stream));
+    CNMF_TRY(cnmf_b200_online_loop(a->Bst, a->ldw, a->Wall, a->ldw, a->A, a->active, a->n_genes, a->R, a->Kp, a->l1_W,
+                                   a->l2_W, a->eps, a->w_tol, a->max_iter, a->iters_w, nullptr, a->ws_loop, stream));
+    CNMF_TRY(launch_round_tf32_2d(a->Wop, a->Wall, rk, a->n_genes, a->ldw, st));
+    if (a->Wlo != nullptr) { CNMF_TRY(launch_residual_tf32(a->Wlo, a->Wall, a->Wop, rk, a->n_genes, a->ldw, st)); n += 1; }
+    CNMF_TRY(launch_gram(a->Wall, a->ldw, a->R, a->Kp, a->n_genes, a->gramW, a->ws_gram, st));
+    n += 6;
+  } else {
+    set_error("online_chunk: unknown phase %d", phase);
+    return CNMF_B200_ERR_INVALID;
+  }
+  reset_launch_count();
+  count_launch(n);
   return 0;
 }
 

@@ -163,6 +163,24 @@ class DenseFrobeniusEngine:
             self.normX2, x_sum, self.N_total = float(tot[0]), float(tot[1]), int(round(tot[2]))
         self.x_mean = x_sum / (float(self.N_total) * self.G)
 
+    def _chunked_xt(self, chunk_size):
+        """X^T stored chunk by chunk, [n_chunks, G, ldc] with chunk ci = (rows ci*chunk .. of X)^T: the A operand of the
+        chunk's B = h^T x product.  Taken from the global X^T its 128-row TMA boxes would stride over N floats per row
+        -- 4 MB at a million cells, every box row on its own page.  Built once per chunk size."""
+        cached = getattr(self, "_xtc", None)
+        if cached is not None and cached[0] == int(chunk_size):
+            return cached[1], cached[2]
+        cs = int(chunk_size)
+        n_chunks = max(1, (self.N + cs - 1) // cs)
+        ldc = pad_ld(min(cs, self.N))
+        xtc = torch.zeros((n_chunks, self.G, ldc), device=self.device, dtype=torch.float32)
+        for ci in range(n_chunks):
+            lo = ci * cs
+            c = min(cs, self.N - lo)
+            xtc[ci, :, :c] = self.X[lo:lo + c, :self.G].t()
+        self._xtc = (cs, xtc, ldc)
+        return xtc, ldc
+
     def host_matrix(self) -> np.ndarray:
         return np.asarray(self._x_host.cpu().numpy() if torch.is_tensor(self._x_host) else self._x_host, dtype=np.float64)
 
@@ -280,48 +298,67 @@ class DenseFrobeniusEngine:
         A = torch.zeros((R, Kp, Kp), **f32)
         Ac = torch.zeros((R, Kp, Kp), **f32)
         Wop = torch.zeros((rk, ldw), **f32)
-        Hop = torch.zeros((rk, ldh), **f32)
+        Wlo = torch.zeros((rk, ldw), **f32)        # tf32(W - tf32 W): second GEMM pass of the refresh / objective
+        Hs = torch.zeros((rk, ldp), **f32)         # the chunk's usages, compact (fp32 / tf32 copy)
+        Hopc = torch.zeros((rk, ldp), **f32)
+        cross = torch.zeros(R, device=dev, dtype=torch.float64)
         ws_gram = torch.empty(max(256, int(L.cnmf_b200_gram_workspace_bytes(R, Kp, max(cmax, G)))), device=dev,
                               dtype=torch.uint8)
         Wall, Ht, active = b.Wall, b.Ht, b.active
         n_chunks = _d.allreduce_max_int((N + chunk_size - 1) // chunk_size, dev, grp)
 
-        def refresh_w_caches():
-            check(L.cnmf_b200_round_tf32_2d(ptr(Wop), ptr(Wall), rk, G, ldw, st()), "round_tf32_2d")
-            check(L.cnmf_b200_gram(ptr(Wall), ldw, R, Kp, G, ptr(b.gramW), ptr(ws_gram), st()), "gram")
-
         iters_hw = torch.zeros((2, R), device=dev, dtype=torch.int32)     # inner iterations per replicate: h loops, W loops
         ws_loop = torch.empty(max(256, int(L.cnmf_b200_online_loop_workspace_bytes(R))), device=dev, dtype=torch.uint8)
+        xtc, ldc = self._chunked_xt(chunk_size)      # X^T chunk by chunk: [n_local_chunks, G, ldc]
+        # one library call per chunk phase (cnmf_b200_online_chunk): the dozen kernels of a chunk are enqueued from C,
+        # and the inner loops stop on the device -- nothing in a pass waits for the host
+        ca = _lib.OnlineChunkArgs(
+            ldx=self.ldx, ldxt=ldc, n_genes=G, R=R, Kp=Kp, Wall=ptr(Wall), Wop=ptr(Wop), ldw=ldw, ldh=ldh, Hs=ptr(Hs),
+            Hopc=ptr(Hopc), Pt=ptr(Pt), ldp=ldp, Wlo=ptr(Wlo), cross=ptr(cross), gramH_acc=ptr(b.gramH),
+            gramW=ptr(b.gramW), A=ptr(A), Ac=ptr(Ac), Bst=ptr(Bst), Bc=ptr(Bc), active=ptr(active), l1_H=l1_H,
+            l2_H=l2_H, l1_W=l1_W, l2_W=l2_W, eps=eps, h_tol=h_tol, w_tol=w_tol, max_iter=int(chunk_max_iter),
+            iters_h=ptr(iters_hw[0]), iters_w=ptr(iters_hw[1]), ws_loop=ptr(ws_loop), ws_gram=ptr(ws_gram))
+        x_ptr, ht_ptr, xtc_ptr = ptr(self.X), ptr(Ht), ptr(xtc)
+        xtc_stride = 4 * G * ldc
 
-        def inner(p_ptr, p_ld, s_ptr, s_ld, g_ptr, M, tol_, l1, l2, which):
-            # the whole inner loop in one launch: replicates stop on the device (no host round trip per few iterations)
-            check(L.cnmf_b200_online_loop(p_ptr, p_ld, s_ptr, s_ld, g_ptr, ptr(active), M, R, Kp, l1, l2, eps, tol_,
-                                          int(chunk_max_iter), ptr(iters_hw[which]), None, ptr(ws_loop), st()),
-                  "online_loop")
-            b.launches += 1
+        def chunk_phase(ci, lo, c, phase):
+            ca.x, ca.xt, ca.c = x_ptr + 4 * lo * self.ldx, xtc_ptr + ci * xtc_stride, c
+            ca.Ht = ht_ptr + 4 * lo
+            check(L.cnmf_b200_online_chunk(C.byref(ca), phase, st()), "online_chunk")
+            b.launches += L.cnmf_b200_last_launch_count()
 
-        def h_chunk(lo, c):
-            check(L.cnmf_b200_dense_gemm_tf32(ptr(self.X) + 4 * lo * self.ldx, self.ldx, c, G, ptr(Wop), ldw, ptr(Pt),
-                                              ldp, ptr(active), R, Kp, 0, st()), "gemm x W^T")
-            b.launches += 1
-            inner(ptr(Pt), ldp, ptr(Ht) + 4 * lo, ldh, ptr(b.gramW), c, h_tol, l1_H, l2_H, 0)
-
-        def objective():
-            check(L.cnmf_b200_frob_prepare(C.byref(b.p), st()), "frob_prepare")
-            if grp is None:
-                return b.objective()
+        def refresh_and_objective(iterate: bool):
+            """H on every cell against the current W (``iterate``; else evaluation only) and the objective by the trace
+            identity ||X||^2 - 2 <H, X W^T> + <W W^T, H^T H>, its data-dependent terms gathered chunk by chunk on the
+            way: no separate pass over X (at a million cells the frozen half-step the batch path uses costs 60 ms)."""
+            cross.zero_()
+            b.gramH.zero_()
+            ca.max_iter = int(chunk_max_iter) if iterate else 0
+            for ci in range(n_chunks):
+                lo = ci * chunk_size
+                c = max(0, min(chunk_size, N - lo))
+                if c > 0:
+                    chunk_phase(ci, lo, c, _lib.ONLINE_REFRESH)
+            ca.max_iter = int(chunk_max_iter)
             sums = torch.zeros((R, 3), device=dev, dtype=torch.float64)
-            check(L.cnmf_b200_frob_objective_parts(C.byref(b.p), ptr(sums), st()), "objective_parts")
-            sw = sums[:, 1].clone()
-            _d.allreduce_sum_([sums, b.gramH], grp)
-            sums[:, 1] = sw                       # W is replicated: its sum must not be multiplied by P
+            sums[:, 0] = cross
+            if l1_W != 0.0:
+                sums[:, 1] = Wall[:, :, :G].sum(dim=(1, 2), dtype=torch.float64)
+            if l1_H != 0.0:
+                sums[:, 2] = Ht[:, :, :N].sum(dim=(1, 2), dtype=torch.float64)
+            if grp is not None:
+                sw = sums[:, 1].clone()
+                _d.allreduce_sum_([sums, b.gramH], grp)
+                sums[:, 1] = sw                   # W is replicated: its sum must not be multiplied by P
             check(L.cnmf_b200_frob_objective_combine(self.normX2, ptr(sums), ptr(b.gramW), ptr(b.gramH), R, Kp,
                                                      l1_H, l2_H, l1_W, l2_W, ptr(b.err2), st()), "objective_combine")
             return b.read_loss()
 
         ar_events = []
-        refresh_w_caches()
-        init = objective()
+        ca.max_iter = 0                                   # W's tf32 copy, its residual and Gram; W itself untouched
+        chunk_phase(0, 0, 1, _lib.ONLINE_SPECTRA)
+        ca.max_iter = int(chunk_max_iter)
+        init = refresh_and_objective(False)
         prev, cur = init.copy(), init
         trace = [(0, init.copy())]
         n_pass = np.full(R, max_pass, dtype=np.int64)
@@ -332,15 +369,11 @@ class DenseFrobeniusEngine:
             for ci in range(n_chunks):
                 lo = ci * chunk_size
                 c = max(0, min(chunk_size, N - lo))
-                Ac.zero_()
-                Bc.zero_()
                 if c > 0:
-                    h_chunk(lo, c)
-                    check(L.cnmf_b200_gram(ptr(Ht) + 4 * lo, ldh, R, Kp, c, ptr(Ac), ptr(ws_gram), st()), "gram")
-                    check(L.cnmf_b200_round_tf32_2d(ptr(Hop) + 4 * lo, ptr(Ht) + 4 * lo, rk, c, ldh, st()), "round")
-                    check(L.cnmf_b200_dense_gemm_tf32(ptr(self.Xt) + 4 * lo, self.ldxt, G, c, ptr(Hop) + 4 * lo, ldh,
-                                                      ptr(Bc), ldw, ptr(active), R, Kp, 0, st()), "gemm h^T x")
-                    b.launches += 4
+                    chunk_phase(ci, lo, c, _lib.ONLINE_USAGE)
+                else:                                     # a rank that has run out of cells contributes zeros
+                    Ac.zero_()
+                    Bc.zero_()
                 if profile is not None and grp is not None:
                     ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
                     ev[0].record()
@@ -349,17 +382,10 @@ class DenseFrobeniusEngine:
                     ar_events.append(ev)
                 else:
                     _d.allreduce_sum_([Ac, Bc], grp)      # the only data-path collective
-                check(L.cnmf_b200_axpy(ptr(A), ptr(Ac), A.numel(), st()), "axpy")
-                check(L.cnmf_b200_axpy(ptr(Bst), ptr(Bc), Bst.numel(), st()), "axpy")
-                inner(ptr(Bst), ldw, ptr(Wall), ldw, ptr(A), G, w_tol, l1_W, l2_W, 1)
-                refresh_w_caches()
-                b.launches += 5
-            for ci in range(n_chunks):                    # end of pass: H on every cell against the final W
-                lo = ci * chunk_size
-                c = max(0, min(chunk_size, N - lo))
-                if c > 0:
-                    h_chunk(lo, c)
-            cur = objective()
+                chunk_phase(ci, lo, max(c, 1), _lib.ONLINE_SPECTRA)
+            # end of pass: H on every cell against the final W.  (A frozen replicate is skipped by every kernel: its
+            # objective is the one it was frozen at.)
+            cur = np.where(alive, refresh_and_objective(True), cur)
             trace.append((ps, cur.copy()))
             conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
             if conv.any():

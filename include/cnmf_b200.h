@@ -218,6 +218,38 @@ int cnmf_b200_online_inner(const float* Pt, int64_t ldp, float* state, int64_t l
                            float tol, int32_t n_iters, int32_t* iters, int32_t* n_pending, void* workspace,
                            void* stream);
 
+/* One chunk of an online pass in one call: what nmf-torch's online loop does per chunk of online_chunk_size cells
+ * (inner loop on the chunk's usages against the cached x W^T, sufficient statistics A += h^T h, B += h^T x, inner
+ * loop on W against (A, B); loop and stopping rule: cnmf.py:355-378).  Pointers are device pointers; x / xt / Ht
+ * point at THIS chunk's rows (x: [c x ldx]) or columns (xt: [G x ldxt], Ht: [R*Kp x ldh]). */
+#define CNMF_B200_ONLINE_REFRESH 0   /* P = x W^T (+ x (W - tf32 W)^T), inner loop on h (max_iter may be 0), cross += <h, P>,
+                                        gramH_acc += h^T h: end-of-pass refresh of H and the objective's terms */
+#define CNMF_B200_ONLINE_USAGE 1     /* P = x W^T, inner loop on h, Ac = h^T h, Bc = h^T x                          */
+#define CNMF_B200_ONLINE_SPECTRA 2   /* A += Ac, B += Bc, inner loop on W, Wop = tf32(W), Wlo, gramW = W W^T        */
+typedef struct cnmf_b200_online_chunk_args {
+  const float* x;  int64_t ldx;
+  const float* xt; int64_t ldxt;
+  int64_t c, n_genes;
+  int32_t R, Kp;
+  float* Wall; float* Wop; int64_t ldw;
+  float* Ht;   int64_t ldh;        /* this chunk's columns of the resident usages [R*Kp x ldh] */
+  float* Hs;   float* Hopc;        /* compact scratch copies of the chunk's usages, fp32 / tf32: [R*Kp x ldp] */
+  float* Pt;   int64_t ldp;        /* scratch [R*Kp x ldp], ldp >= c, a multiple of 4 */
+  float* Wlo;                      /* [R*Kp x ldw] tf32(W - tf32 W), or NULL (then P carries tf32 rounding of W) */
+  double* cross;                   /* [R] += <h, x W^T> in the refresh phase, or NULL */
+  float* gramH_acc;                /* [R x Kp x Kp] += h^T h in the refresh phase, or NULL */
+  float* gramW;                    /* [R x Kp x Kp] */
+  float* A;  float* Ac;            /* [R x Kp x Kp] statistics of the pass / of this chunk */
+  float* Bst; float* Bc;           /* [R*Kp x ldw] */
+  const uint8_t* active;           /* [R] or NULL */
+  float l1_H, l2_H, l1_W, l2_W, eps, h_tol, w_tol;
+  int32_t max_iter;
+  int32_t* iters_h; int32_t* iters_w;   /* [R], incremented */
+  void* ws_loop;                   /* cnmf_b200_online_loop_workspace_bytes(R) */
+  void* ws_gram;                   /* cnmf_b200_gram_workspace_bytes(R, Kp, max(c, n_genes)) */
+} cnmf_b200_online_chunk_args;
+int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, void* stream);
+
 /* The same loop run TO CONVERGENCE in one launch, no host round trip: every replicate iterates until rel_r < tol or
  * max_iter, decided on the device (the replicate's CTAs meet at a counter in global memory after every iteration; a
  * cooperative launch keeps them co-resident).  iters[r] += iterations run; max_iters_seen (device, optional) is raised

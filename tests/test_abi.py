@@ -63,16 +63,23 @@ def test_struct_layout_matches_header():
 #include "cnmf_b200.h"
 int main(void){printf("%zu %zu %zu %zu %zu\n", sizeof(cnmf_b200_frob_problem),
   offsetof(cnmf_b200_frob_problem, Wall), offsetof(cnmf_b200_frob_problem, active),
-  offsetof(cnmf_b200_frob_problem, normX2), offsetof(cnmf_b200_frob_problem, workspace_bytes));return 0;}
+  offsetof(cnmf_b200_frob_problem, normX2), offsetof(cnmf_b200_frob_problem, workspace_bytes));
+  printf("%zu %zu %zu %zu\n", sizeof(cnmf_b200_kl_problem), offsetof(cnmf_b200_kl_problem, impl),
+  offsetof(cnmf_b200_kl_problem, sumX), offsetof(cnmf_b200_kl_problem, workspace_bytes));
+  printf("%zu %zu %zu %zu %zu\n", sizeof(cnmf_b200_online_chunk_args), offsetof(cnmf_b200_online_chunk_args, Wall),
+  offsetof(cnmf_b200_online_chunk_args, active), offsetof(cnmf_b200_online_chunk_args, max_iter),
+  offsetof(cnmf_b200_online_chunk_args, ws_gram));return 0;}
 '''
     with tempfile.TemporaryDirectory() as d:
         open(os.path.join(d, "t.c"), "w").write(src)
         subprocess.run(["gcc", "-I", os.path.join(ROOT, "include"), os.path.join(d, "t.c"), "-o",
                         os.path.join(d, "t")], check=True)
         out = subprocess.run([os.path.join(d, "t")], capture_output=True, text=True, check=True).stdout.split()
-    P = _lib.FrobProblem
+    P, Q, O = _lib.FrobProblem, _lib.KlProblem, _lib.OnlineChunkArgs
     assert [int(v) for v in out] == [C.sizeof(P), P.Wall.offset, P.active.offset, P.normX2.offset,
-                                     P.workspace_bytes.offset]
+                                     P.workspace_bytes.offset,
+                                     C.sizeof(Q), Q.impl.offset, Q.sumX.offset, Q.workspace_bytes.offset,
+                                     C.sizeof(O), O.Wall.offset, O.active.offset, O.max_iter.offset, O.ws_gram.offset]
 
 
 def test_missing_library_fails_loudly(monkeypatch, tmp_path):
