@@ -30,6 +30,51 @@ def load_df_from_npz(filename):
         return pd.DataFrame(**f)
 
 
+def _npy_bytes(arr):
+    """The bytes np.savez would store for one member (object arrays pickled, as np.savez does)."""
+    import io
+    buf = io.BytesIO()
+    np.lib.format.write_array(buf, np.asanyarray(arr), allow_pickle=True)
+    return buf.getvalue()
+
+
+def _deflated_member(name, payload, level=1):
+    """(name, crc32, uncompressed size, raw-deflate bytes) of one archive member; zlib releases the GIL."""
+    import zlib
+    co = zlib.compressobj(level, zlib.DEFLATED, -15)
+    return (name.encode(), zlib.crc32(payload) & 0xFFFFFFFF, len(payload), co.compress(payload) + co.flush())
+
+
+def _write_zip(filename, members):
+    """A plain ZIP archive (method 8, no zip64, no data descriptors) from pre-deflated members.  np.load / zipfile read
+    it like the archive np.savez_compressed writes; zipfile's own writer costs ~1 ms of interpreter time per archive
+    (seeks, locks, header rewrites), which for the 600 replicate files of a run was most of factorize's wall time."""
+    import struct
+    out, central, offset = [], [], 0
+    for name, crc, size, comp in members:
+        local = struct.pack("<IHHHHHIIIHH", 0x04034B50, 20, 0, 8, 0, 0x21, crc, len(comp), size, len(name), 0) + name
+        central.append(struct.pack("<IHHHHHHIIIHHHHHII", 0x02014B50, 20, 20, 0, 8, 0, 0x21, crc, len(comp), size,
+                                   len(name), 0, 0, 0, 0, 0, offset) + name)
+        out.append(local)
+        out.append(comp)
+        offset += len(local) + len(comp)
+    cd = b"".join(central)
+    out.append(cd)
+    out.append(struct.pack("<IHHHHIIH", 0x06054B50, 0, 0, len(members), len(members), len(cd), offset, 0))
+    with open(filename, "wb") as f:
+        f.write(b"".join(out))
+
+
+def save_arrays_to_df_npz(filename, data, index, columns_member, level=1):
+    """A ``.df.npz`` file with the members ``save_df_to_npz`` writes (data / index / columns; np.load and the
+    reference's load_df_from_npz read it the same way), without building a DataFrame and without re-pickling and
+    re-compressing the gene names for each of the hundreds of replicate files of a run: ``columns_member`` is
+    ``_deflated_member("columns.npy", _npy_bytes(columns))``, made once by the caller.  Deflate level 1: the payload
+    is float32 noise, higher levels buy ~2 % of size for 3 x the time."""
+    _write_zip(filename, [_deflated_member("data.npy", _npy_bytes(data), level),
+                          _deflated_member("index.npy", _npy_bytes(index), level), columns_member])
+
+
 def save_df_to_text(obj, filename):
     obj.to_csv(filename, sep="\t")
 
@@ -114,7 +159,17 @@ class cNMF:
             pass
 
     def load_norm_counts(self):
-        """-> (X csr, obs_names, var_names); prefers .h5ad (cnmf.py:873) when it can be read."""
+        """-> (X csr, obs_names, var_names); prefers .h5ad (cnmf.py:873) when it can be read.  The arrays of the last
+        read are kept while the file is unchanged (consensus over several K reads it once, not once per K)."""
+        src = self.paths["normalized_counts"] if os.path.exists(self.paths["normalized_counts"]) \
+            else self.paths["normalized_counts_npz"]
+        hit = self._recall(src)
+        if hit is None:
+            hit = self._read_norm_counts()
+            self._remember("norm_counts", src, hit)
+        return hit
+
+    def _read_norm_counts(self):
         if os.path.exists(self.paths["normalized_counts"]):
             try:
                 import anndata as ad
@@ -316,24 +371,58 @@ class cNMF:
         f4 -- when this call holds EVERY replicate of a K (one worker, nothing skipped), that K's merged file as
         ``combine_nmf`` would build it (cnmf.py:895-920: rows in ``iter`` order, labels ``iter%d_topic%d``) straight
         from memory; ``combine`` then finds it up to date instead of re-reading the replicate files."""
-        jobs = [(self.paths["iter_spectra"] % (k, int(p["iter"])),
-                 pd.DataFrame(res[k].W[j], index=np.arange(1, k + 1), columns=var_names))
-                for k, g in groups.items() for j, (_, p) in enumerate(g.iterrows())]
+        cols = _deflated_member("columns.npy", _npy_bytes(np.asarray(var_names, dtype=object)))   # once for all files
+        jobs = [(self.paths["iter_spectra"] % (k, int(it)), res[k].W[j], np.arange(1, k + 1))
+                for k, g in groups.items() for j, it in enumerate(g["iter"].values)]
         merged = []
         if whole_ledger:
             for k, g in groups.items():
                 order = np.argsort(g["iter"].values, kind="stable")
                 its = g["iter"].values[order]
                 data = np.concatenate([res[k].W[j] for j in order], axis=0)
-                index = ["iter%d_topic%d" % (it, t + 1) for it in its for t in range(k)]
-                merged.append((self.paths["merged_spectra"] % k, pd.DataFrame(data, index=index, columns=var_names)))
+                index = np.array(["iter%d_topic%d" % (it, t + 1) for it in its for t in range(k)], dtype=object)
+                merged.append((self.paths["merged_spectra"] % k, data, index))
+                self._remember("merged", self.paths["merged_spectra"] % k,
+                               pd.DataFrame(data, index=index, columns=np.asarray(var_names, dtype=object)), defer=True)
         with _io_pool() as pool:
-            first = [pool.submit(save_df_to_npz, df, fn) for fn, df in jobs]
+            first = [pool.submit(save_arrays_to_df_npz, fn, data, index, cols) for fn, data, index in jobs]
             for f in first:
                 f.result()
             # merged files strictly after their replicate files: combine's up-to-date test compares mtimes
-            for f in [pool.submit(save_df_to_npz, df, fn) for fn, df in merged]:
+            for f in [pool.submit(save_arrays_to_df_npz, fn, data, index, cols) for fn, data, index in merged]:
                 f.result()
+        self._settle_remembered()
+
+    # ---- in-memory copies of files this object has just written or read (keyed by path, size and mtime) ----------
+    def _remember(self, kind, path, value, defer=False):
+        cache = self.__dict__.setdefault("_file_cache", {})
+        cache[path] = [None if defer else self._stamp(path), value]
+
+    def _settle_remembered(self):
+        for path, ent in self.__dict__.get("_file_cache", {}).items():
+            if ent[0] is None:
+                ent[0] = self._stamp(path)
+
+    @staticmethod
+    def _stamp(path):
+        st = os.stat(path)
+        return (st.st_size, st.st_mtime_ns)
+
+    def _recall(self, path):
+        ent = self.__dict__.get("_file_cache", {}).get(path)
+        if ent is not None and ent[0] is not None and os.path.exists(path) and ent[0] == self._stamp(path):
+            return ent[1]
+        return None
+
+    def _load_merged(self, k):
+        """The merged spectra of k: the copy kept from this object's own factorize / combine when the file is still
+        the one it wrote, else read (and inflated) from disk."""
+        fn = self.paths["merged_spectra"] % k
+        hit = self._recall(fn)
+        if hit is None:
+            hit = load_df_from_npz(fn)
+            self._remember("merged", fn, hit)
+        return hit
 
     def _merged_is_current(self, k, subset):
         """The merged file of k exists, has one block of k rows per ledger replicate and is not older than any of
@@ -346,8 +435,7 @@ class cNMF:
             f = self.paths["iter_spectra"] % (p["n_components"], p["iter"])
             if not os.path.exists(f) or os.path.getmtime(f) > t:
                 return False
-        with np.load(fn, allow_pickle=True) as z:
-            return z["data"].shape[0] == k * len(subset)
+        return self._load_merged(k).shape[0] == k * len(subset)
 
     # ---- combine (cnmf.py:599-620, 895-920) -------------------------------------------------------
     def combine(self, components=None, skip_missing_files=False):
@@ -369,7 +457,7 @@ class cNMF:
         subset = run_params[run_params.n_components == k].sort_values("iter")
         if self._merged_is_current(k, subset):
             print("Merged spectra for k=%d are up to date." % k)
-            return load_df_from_npz(self.paths["merged_spectra"] % k)
+            return self._load_merged(k)
         combined, present = [], []
         for _, p in subset.iterrows():
             fn = self.paths["iter_spectra"] % (p["n_components"], p["iter"])
@@ -387,6 +475,7 @@ class cNMF:
         if len(combined) > 0:
             combined = pd.concat(combined, axis=0)
             save_df_to_npz(combined, self.paths["merged_spectra"] % k)
+            self._remember("merged", self.paths["merged_spectra"] % k, combined)
         else:
             print("No spectra found for k=%d" % k)
         return combined
@@ -424,7 +513,7 @@ class cNMF:
         ``torch.rand``; an int seeds one generator they draw from in the same order.  Returns (consensus spectra
         DataFrame, labels Series, local_density DataFrame); plots and the starCAT reference are outside this path."""
         from .consensus import consensus_front_half
-        merged = load_df_from_npz(self.paths["merged_spectra"] % k)
+        merged = self._load_merged(k)
         dt_str = "2" if skip_density_and_return_after_stats else str(density_threshold)
         dt_repl = dt_str.replace(".", "_")                                    # cnmf.py:1049-1052
         n_neighbors = int(local_neighborhood_size * merged.shape[0] / k)      # cnmf.py:1053

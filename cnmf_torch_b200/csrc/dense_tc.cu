@@ -653,7 +653,11 @@ static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out) 
   static const int forced_t = [] { const char* e = getenv("CNMF_B200_TC_T"); return e ? atoi(e) : 0; }();
   static const int forced_cg = [] { const char* e = getenv("CNMF_B200_TC_CG"); return e ? atoi(e) : 0; }();
   for (int cg = 1; cg <= 2; ++cg) {
-    if (cg == 2 && (num_m < 2 || sms < 2 || forced_cg != 2)) continue;  // pairs: opt-in (CNMF_B200_TC_CG=2), measured no faster
+    // CTA pairs (cta_group::2, M = 256 per MMA, each SM stages half of the B tile) are the default where two row tiles
+    // exist: measured 13 % faster on both cfg-2 stacks (H half-step of the Kp=12 stack 98.9 -> 86.1 us, the plain GEMM
+    // 74.7 -> 65.6 us against 72.4 us for the library's tf32 GEMM of the same shape; profiles/NOTES.md, round 2).
+    // CNMF_B200_TC_CG=1 / =2 force one form (dev knob).
+    if (cg == 2 && (num_m < 2 || sms < 2 || forced_cg == 1)) continue;
     if (forced_cg == 2 && cg == 1 && num_m >= 2) continue;
     for (int t = 1; t * Kp <= TC_MAX_BN; ++t) {
       const int BN = t * Kp;
@@ -669,10 +673,10 @@ static bool tc_plan(int64_t M, int64_t Kd, int R, int Kp, int sms, TcPlan* out) 
       const int64_t waves = ceil_div(tiles, sms / cg);
       // clocks per k-block, measured (profiles/NOTES.md): every operand byte crosses the 128 B/clk shared-memory
       // port twice (TMA write + MMA read): 2*(128+BN) clk, over a floor of ~500 clk from the barrier round trip and
-      // the 4 MMA issues.  (Pairs: half the B bytes per SM but the measured gain is ~8 %.)
+      // the 4 MMA issues.  (Pairs: half the B bytes per SM; measured gain 13-14 % per k-block.)
       double kb_clk = 2.0 * (TC_BM + BN) + 40.0;
       if (kb_clk < 500.0 + 0.6 * BN) kb_clk = 500.0 + 0.6 * BN;
-      if (cg == 2) kb_clk *= 0.92;
+      if (cg == 2) kb_clk *= 0.86;
       const double epi = static_cast<double>(t) * (Kp * Kp + 12.0 * Kp) * 1.5 + 1500.0;
       const double cost = waves * (static_cast<double>(num_kb) * kb_clk + 1000.0) + epi + (cg == 2 ? 1500.0 : 0.0);
       if (cost < best) {

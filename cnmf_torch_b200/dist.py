@@ -51,6 +51,13 @@ def allreduce_sum_(tensors, group=None):
     return tensors
 
 
+def allreduce_flat_(t, group=None):
+    """In-place sum over ranks of ONE contiguous tensor (the online loop's [A | B] message)."""
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return t
+
+
 def allreduce_max_int(value: int, device, group=None) -> int:
     if not dist.is_available() or not dist.is_initialized() or dist.get_world_size(group) == 1:
         return int(value)

@@ -294,9 +294,11 @@ class DenseFrobeniusEngine:
         f32 = dict(device=dev, dtype=torch.float32)
         Pt = torch.zeros((rk, ldp), **f32)
         Bst = torch.zeros((rk, ldw), **f32)
-        Bc = torch.zeros((rk, ldw), **f32)
         A = torch.zeros((R, Kp, Kp), **f32)
-        Ac = torch.zeros((R, Kp, Kp), **f32)
+        # the chunk's statistics [Ac | Bc] in ONE buffer: the message of the all-reduce, no packing copies
+        AcBc = torch.zeros(R * Kp * Kp + rk * ldw, **f32)
+        Ac = AcBc[:R * Kp * Kp].view(R, Kp, Kp)
+        Bc = AcBc[R * Kp * Kp:].view(rk, ldw)
         Wop = torch.zeros((rk, ldw), **f32)
         Wlo = torch.zeros((rk, ldw), **f32)        # tf32(W - tf32 W): second GEMM pass of the refresh / objective
         Hs = torch.zeros((rk, ldp), **f32)         # the chunk's usages, compact (fp32 / tf32 copy)
@@ -377,11 +379,11 @@ class DenseFrobeniusEngine:
                 if profile is not None and grp is not None:
                     ev = (torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True))
                     ev[0].record()
-                    _d.allreduce_sum_([Ac, Bc], grp)
+                    _d.allreduce_flat_(AcBc, grp)
                     ev[1].record()
                     ar_events.append(ev)
                 else:
-                    _d.allreduce_sum_([Ac, Bc], grp)      # the only data-path collective
+                    _d.allreduce_flat_(AcBc, grp)         # the only data-path collective
                 chunk_phase(ci, lo, max(c, 1), _lib.ONLINE_SPECTRA)
             # end of pass: H on every cell against the final W.  (A frozen replicate is skipped by every kernel: its
             # objective is the one it was frozen at.)
