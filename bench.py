@@ -40,7 +40,7 @@ REPLICATES = 100
 ITERS_PER_STEP = 10
 ALGO = "hals"
 E2E_ITERS = 100  # iterations per replicate in one end-to-end public-API call
-KL_PROFILE_CSV = "r02_kl_slab_full_raw.csv"
+KL_PROFILE_CSV = "r01_kl_half_step_full_raw.csv"   # the gather kernels are round 1's; same code
 TC_PROFILE_CSV = "r02_tc_half_step_full_raw.csv"   # ncu --set full raw page of the dominant kernel, this round
 METRIC = "nmf_replicate_iterations_per_second"
 UNIT = "replicate-iters/s"
@@ -495,7 +495,8 @@ def run_cfg3(args):
             b.iterate(ITERS_PER_STEP)
 
     # dominant kernel: the H half-step (slab kernel) of the tallest stack, timed alone through one iteration's events
-    big = max(batches, key=lambda b: b.R * b.Kp)
+    big = max(batches, key=lambda b: (b.R, b.Kp))
+    big_kp = big.Kp
     big.iterate(1)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -526,13 +527,14 @@ def run_cfg3(args):
     torch.cuda.synchronize()
     e2e_s = time.perf_counter() - t0
     ms_total, e2e_s, it_ms_max = _max_over_ranks([ms_total, e2e_s, it_ms], dev, world)
+    pipeline = _cfg3_pipeline(xs, rank, world, dev) if args.pipeline else None
     jobs = len(ledger)
     value = jobs * ITERS_PER_STEP * args.steps / (ms_total * 1e-3)
     if rank == 0:
         peaks, src = _peaks()
         nnz = int(xs.nnz)
-        rk = sum(len(v) * k for k, v in by_k.items() if pad2(k) == max(stacks))       # K x replicates of the big stack
-        r_big = sum(len(v) for k, v in by_k.items() if pad2(k) == max(stacks))
+        rk = sum(len(v) * k for k, v in by_k.items() if pad2(k) == big_kp)       # K x replicates of the big stack
+        r_big = sum(len(v) for k, v in by_k.items() if pad2(k) == big_kp)
         # algorithmic bytes of one batched iteration of that stack: X's CSR twice + factors read and written
         abytes = 2 * (8 * nnz + 4 * (x.shape[0] + 1)) + 8 * rk * (x.shape[0] + x.shape[1])
         aflops = 2.0 * 2 * nnz * 2 * rk                 # 2 half-steps x (s and numerator) x K FMAs per entry
@@ -546,9 +548,10 @@ def run_cfg3(args):
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": abytes / (it_ms_max * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
                          "unit": "GB/s", "frac": abytes / (it_ms_max * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                         "traffic": _traffic_from_profile(KL_PROFILE_CSV, "kl_slab_kernel"),
-                         "kernel": f"one batched KL iteration of the Kp={max(stacks)} stack on rank 0 ({r_big} replicates): "
-                                   f"kl_slab_kernel x2 + finish + column sums", "kernel_ms": it_ms_max,
+                         "traffic": _traffic_from_profile(KL_PROFILE_CSV, "kl_half_step_kernel"),
+                         "kernel": f"one batched KL iteration of the Kp={big_kp} stack on rank 0 ({r_big} replicates): "
+                                   f"kl_half_step_kernel x2 (gather family) + finish passes + column sums",
+                         "kernel_ms": it_ms_max,
                          "peak_source": src,
                          "note": "the algorithmic bytes are tiny against the arithmetic: this path is bound by the fp32 FMA "
                                  "pipe (instruction issue), see roofline_fma"},
@@ -558,6 +561,8 @@ def run_cfg3(args):
                                             "measured at 122-124 of 128 lanes/clk/SM: profiles/r02_simt_rate.txt)"},
             "jobs_per_rank": n_mine,
         }
+        if pipeline is not None:
+            line["pipeline_cfg3"] = pipeline
         if not args.no_cpu_baseline and world == 1:
             import torch as _t
             from oracle import nmf_oracle as no
@@ -571,6 +576,58 @@ def run_cfg3(args):
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def _cfg3_pipeline(xs, rank, world, dev):
+    """BASELINE.json's second metric at cfg-3: wall time of factorize (the ledger strided over the ranks, replicate files
+    written) + combine (rank 0) + consensus of every K (the K values dealt over the ranks), tol and iteration limits as
+    `cnmf prepare` writes them.  Max over ranks per stage."""
+    import shutil
+    import tempfile
+    import torch
+    import torch.distributed as dist
+    from cnmf_torch_b200 import cnmf as host
+    box = [tempfile.mkdtemp(prefix="cnmf_b200_cfg3_") if rank == 0 else None]
+    if world > 1:
+        dist.broadcast_object_list(box, 0)
+    obj = host.cNMF(output_dir=box[0], name="cfg3", device=str(dev))
+    try:
+        if rank == 0:
+            obj.prepare_from_matrix(xs, CFG3["ks"], n_iter=CFG3["replicates"], seed=14, beta_loss="kullback-leibler",
+                                    use_gpu=True)
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        obj.factorize(worker_i=rank, total_workers=world)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
+        if world > 1:
+            dist.barrier()
+        t1b = time.perf_counter()
+        mine_k = CFG3["ks"][rank::world]
+        if mine_k:
+            obj.combine(components=mine_k)            # `cnmf combine -k ...`: one K's merged file per call, dealt over the ranks
+        if world > 1:
+            dist.barrier()
+        t2 = time.perf_counter()
+        for k in CFG3["ks"][rank::world]:
+            obj.consensus(k, density_threshold=0.5, local_neighborhood_size=0.30)
+        torch.cuda.synchronize()
+        t3 = time.perf_counter()
+        if world > 1:
+            dist.barrier()
+        t4 = time.perf_counter()
+        st = _max_over_ranks([t1 - t0, t2 - t1b, t3 - t2, t4 - t0], dev, world)
+        return {"factorize_s": st[0], "combine_s": st[1], "consensus_s": st[2], "total_s": st[3],
+                "what": "cNMF mirror: factorize(worker_i=rank, total_workers=N) of the 900-job KL ledger (tol 1e-4, up to 500 "
+                        "iterations, replicate files written), combine and consensus(k, 0.5, 0.30) incl. the usage "
+                        "refit over all cells, K values dealt over the ranks; max over ranks per stage"}
+    finally:
+        if world > 1:
+            dist.barrier()
+        if rank == 0:
+            shutil.rmtree(box[0], ignore_errors=True)
 
 
 def run_cfg5(args):
@@ -628,6 +685,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--config", default="cfg2", choices=["cfg2", "cfg3", "cfg5"])
+    ap.add_argument("--pipeline", action="store_true",
+                    help="[cfg3] also time factorize + combine + consensus through the cNMF mirror, jobs strided over the ranks")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--path", default="auto", choices=["auto", "simt", "tcgen05"])
     ap.add_argument("--no-extras", action="store_true", help="skip the consensus / KL / online side measurements")

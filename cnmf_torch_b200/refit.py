@@ -31,7 +31,10 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
     sparse = hasattr(X, "toarray")
     if sparse:
         X = X.tocsr()      # densified one chunk at a time below (the reference densifies the whole matrix, cnmf.py:329-330;
-                           # TPM over all genes x 100 000 cells would be 8 GB of host memory)
+                           # TPM over all genes x 100 000 cells would be 8 GB of host memory) -- ON THE DEVICE: the CSR
+                           # arrays are uploaded once (a twelfth of the dense bytes at 8 % density) and each chunk is
+                           # scattered into the dense buffer there; numpy's toarray + a pageable H2D of 800 MB per refit
+                           # were most of a consensus call at 100 000 cells
     else:
         X = np.ascontiguousarray(X, dtype=np.float32)
     n, g = X.shape
@@ -68,11 +71,19 @@ def fit_H_online(X, W, H_init=None, chunk_size=5000, chunk_max_iter=200, h_tol=0
     iters = torch.zeros(1, device=dev, dtype=torch.int32)
     ws = torch.empty(max(256, int(L.cnmf_b200_online_loop_workspace_bytes(1))), device=dev, dtype=torch.uint8)
     Hs = torch.zeros((Kp, ldp), device=dev, dtype=torch.float32)   # chunk-local state: 16-byte aligned columns
+    if sparse:
+        indptr = np.asarray(X.indptr, dtype=np.int64)
+        d_col = torch.from_numpy(np.asarray(X.indices, dtype=np.int64)).to(dev)
+        d_val = torch.from_numpy(np.asarray(X.data, dtype=np.float32)).to(dev)
+        d_row = torch.from_numpy(np.repeat(np.arange(n, dtype=np.int64), np.diff(indptr))).to(dev)
     for lo in range(0, n, int(chunk_size)):
         c = min(int(chunk_size), n - lo)
-        xc = X[lo:lo + c]
-        xc = np.ascontiguousarray(xc.toarray(), dtype=np.float32) if sparse else xc
-        xbuf[:c, :g] = torch.from_numpy(xc).to(dev)                                       # chunk upload (cnmf.py:351)
+        if sparse:
+            a, b_ = int(indptr[lo]), int(indptr[lo + c])
+            xbuf.zero_()
+            xbuf.index_put_((d_row[a:b_] - lo, d_col[a:b_]), d_val[a:b_], accumulate=True)   # (duplicates sum, as toarray)
+        else:
+            xbuf[:c, :g] = torch.from_numpy(X[lo:lo + c]).to(dev)                         # chunk upload (cnmf.py:351)
         check(L.cnmf_b200_gemm_nt(ptr(Wd), ldg, Kp, ptr(xbuf), ldg, c, g, ptr(Pt), ldp, st), "gemm x W^T")
         Hs[:, :c] = Ht[:, lo:lo + c]
         # the chunk's inner loop to convergence in one launch (stops on the device, cnmf.py:365-378)
