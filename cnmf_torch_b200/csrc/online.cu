@@ -103,6 +103,12 @@ __global__ void __launch_bounds__(1024) online_flag_kernel(const double* __restr
 // replicate stops, on the device, exactly where `online_flag_kernel` would have stopped it.  Launched
 // cooperatively (all CTAs co-resident: the spin-wait needs it); replicates beyond the number of resident slots are
 // taken in turn by the same CTAs.
+__device__ __forceinline__ float onl_tf32(float v) {   // round to nearest tf32 (cvt.rna), as dense_tc.cu's operand copies
+  uint32_t r;
+  asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+  return __uint_as_float(r);
+}
+
 constexpr int ONP_THREADS = 256;
 constexpr int ONP_MAX_SLABS = 8;
 
@@ -113,7 +119,8 @@ __global__ void __launch_bounds__(ONP_THREADS, REGS > 0 ? 2 : 1) online_inner_pe
     const float* __restrict__ Pt, int64_t ldp, float* __restrict__ state, int64_t lds, const float* __restrict__ gram,
     const uint8_t* __restrict__ active, int64_t M, int R, float l1, float l2, float eps, float tol, int max_iter,
     int nslab, int* __restrict__ iters, unsigned int* __restrict__ arrive, double* __restrict__ slots,
-    unsigned long long* __restrict__ total_iters, double* __restrict__ cross) {
+    unsigned long long* __restrict__ total_iters, double* __restrict__ cross, float* __restrict__ state_op,
+    float* __restrict__ state_lo, int64_t ldo) {
   __shared__ float sgram[KP * KP];
   __shared__ double red[ONP_THREADS / 32][2];
   __shared__ int s_done;
@@ -216,13 +223,33 @@ __global__ void __launch_bounds__(ONP_THREADS, REGS > 0 ? 2 : 1) online_inner_pe
       ++it;
       if (s_done) break;
     }
+    // write-back; on the way the tf32 operand copy of the final state (and, for W, the tf32 residual state - copy that
+    // the refresh's second GEMM pass reads): two elementwise launches per chunk less
     if (REGS > 0) {
 #pragma unroll
       for (int j = 0; j < REGS; ++j) {
         const int64_t m = c0 + threadIdx.x + (int64_t)j * ONP_THREADS;
         if (m < c1) {
 #pragma unroll
-          for (int k = 0; k < KP; ++k) state[(base + k) * lds + m] = sreg[j][k];
+          for (int k = 0; k < KP; ++k) {
+            const float v = sreg[j][k];
+            state[(base + k) * lds + m] = v;
+            if (state_op != nullptr) {
+              const float o = onl_tf32(v);
+              state_op[(base + k) * ldo + m] = o;
+              if (state_lo != nullptr) state_lo[(base + k) * ldo + m] = onl_tf32(v - o);
+            }
+          }
+        }
+      }
+    } else if (state_op != nullptr) {
+      for (int64_t m = c0 + threadIdx.x; m < c1; m += ONP_THREADS) {
+#pragma unroll
+        for (int k = 0; k < KP; ++k) {
+          const float v = state[(base + k) * lds + m];
+          const float o = onl_tf32(v);
+          state_op[(base + k) * ldo + m] = o;
+          if (state_lo != nullptr) state_lo[(base + k) * ldo + m] = onl_tf32(v - o);
         }
       }
     }
@@ -353,20 +380,20 @@ int64_t cnmf_b200_online_loop_workspace_bytes(int32_t R) {
 static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                             const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                             float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
-                            void* workspace, double* cross, void* stream);
+                            void* workspace, double* cross, float* state_op, float* state_lo, int64_t ldo, void* stream);
 
 int cnmf_b200_online_loop(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                           const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                           float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
                           void* workspace, void* stream) {
   return online_loop_impl(Pt, ldp, state, lds, gram, active, M, R, Kp, l1, l2, eps, tol, max_iter, iters, max_iters_seen,
-                          workspace, nullptr, stream);
+                          workspace, nullptr, nullptr, nullptr, 0, stream);
 }
 
 static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                             const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                             float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
-                            void* workspace, double* cross, void* stream) {
+                            void* workspace, double* cross, float* state_op, float* state_lo, int64_t ldo, void* stream) {
   reset_launch_count();
   CNMF_CHECK_ARG(Pt && state && gram && iters && workspace, "online_loop: null pointer");
   CNMF_CHECK_ARG(M > 0 && R > 0 && ldp >= M && lds >= M && max_iter >= 0, "online_loop: bad shape");
@@ -421,7 +448,8 @@ static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t 
   int R_ = R, max_iter_ = max_iter;
   void* args[] = {(void*)&Pt, (void*)&ldp, (void*)&state, (void*)&lds, (void*)&gram, (void*)&active, (void*)&M_, (void*)&R_,
                   (void*)&l1, (void*)&l2, (void*)&eps, (void*)&tol, (void*)&max_iter_, (void*)&nslab, (void*)&iters,
-                  (void*)&arrive, (void*)&slots, (void*)&max_iters_seen, (void*)&cross};
+                  (void*)&arrive, (void*)&slots, (void*)&max_iters_seen, (void*)&cross, (void*)&state_op, (void*)&state_lo,
+                  (void*)&ldo};
   CNMF_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(ONP_THREADS), args, 0, st));
   count_launch();
   return 0;
@@ -467,30 +495,34 @@ int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, 
     }
     CNMF_TRY(online_loop_impl(a->Pt, a->ldp, a->Hs, a->ldp, a->gramW, a->active, a->c, a->R, a->Kp, a->l1_H, a->l2_H,
                               a->eps, a->h_tol, a->max_iter, a->iters_h, nullptr, a->ws_loop,
-                              refresh ? a->cross : nullptr, stream));
+                              refresh ? a->cross : nullptr, refresh ? nullptr : a->Hopc, nullptr, a->ldp, stream));
     CNMF_TRY(launch_gram(a->Hs, a->ldp, a->R, a->Kp, a->c, a->Ac, a->ws_gram, st));
     n += 3;
     if (refresh) {
       if (a->gramH_acc != nullptr) { CNMF_TRY(cnmf_b200_axpy(a->gramH_acc, a->Ac, (int64_t)a->R * a->Kp * a->Kp, stream)); n += 1; }
     } else {
       CNMF_CHECK_ARG(a->xt && a->Hopc && a->Bc, "online_chunk: null pointer (statistics)");
-      CNMF_TRY(launch_round_tf32_2d(a->Hopc, a->Hs, rk, a->c, a->ldp, st));
       CNMF_TRY(cnmf_b200_dense_gemm_tf32(a->xt, a->ldxt, a->n_genes, a->c, a->Hopc, a->ldp, a->Bc, a->ldw, a->active,
                                          a->R, a->Kp, 0, stream));
-      n += 2;
+      n += 1;
     }
     if (a->max_iter > 0) { CNMF_TRY(copy_rows(a->Ht, a->ldh, a->Hs, a->ldp, rk, a->c, st)); n += 1; }
   } else if (phase == CNMF_B200_ONLINE_SPECTRA) {
     CNMF_CHECK_ARG(a->A && a->Ac && a->Bst && a->Bc && a->Wall && a->Wop && a->gramW && a->iters_w && a->ws_loop &&
                        a->ws_gram, "online_chunk: null pointer (spectra phase)");
-    CNMF_TRY(cnmf_b200_axpy(a->A, a->Ac, (int64_t)a->R * a->Kp * a->Kp, stream));
-    CNMF_TRY(cnmf_b200_axpy(a->Bst, a->Bc, rk * a->ldw, stream));
-    CNMF_TRY(cnmf_b200_online_loop(a->Bst, a->ldw, a->Wall, a->ldw, a->A, a->active, a->n_genes, a->R, a->Kp, a->l1_W,
-                                   a->l2_W, a->eps, a->w_tol, a->max_iter, a->iters_w, nullptr, a->ws_loop, stream));
-    CNMF_TRY(launch_round_tf32_2d(a->Wop, a->Wall, rk, a->n_genes, a->ldw, st));
-    if (a->Wlo != nullptr) { CNMF_TRY(launch_residual_tf32(a->Wlo, a->Wall, a->Wop, rk, a->n_genes, a->ldw, st)); n += 1; }
+    const int64_t na = (int64_t)a->R * a->Kp * a->Kp, nb = rk * a->ldw;
+    if (a->Bst == a->A + na && a->Bc == a->Ac + na) {   // [A | B] and [Ac | Bc] each in one buffer: one launch
+      CNMF_TRY(cnmf_b200_axpy(a->A, a->Ac, na + nb, stream));
+      n -= 1;
+    } else {
+      CNMF_TRY(cnmf_b200_axpy(a->A, a->Ac, na, stream));
+      CNMF_TRY(cnmf_b200_axpy(a->Bst, a->Bc, nb, stream));
+    }
+    CNMF_TRY(online_loop_impl(a->Bst, a->ldw, a->Wall, a->ldw, a->A, a->active, a->n_genes, a->R, a->Kp, a->l1_W,
+                              a->l2_W, a->eps, a->w_tol, a->max_iter, a->iters_w, nullptr, a->ws_loop, nullptr, a->Wop,
+                              a->Wlo, a->ldw, stream));
     CNMF_TRY(launch_gram(a->Wall, a->ldw, a->R, a->Kp, a->n_genes, a->gramW, a->ws_gram, st));
-    n += 6;
+    n += 5;
   } else {
     set_error("online_chunk: unknown phase %d", phase);
     return CNMF_B200_ERR_INVALID;

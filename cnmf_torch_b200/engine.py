@@ -293,8 +293,9 @@ class DenseFrobeniusEngine:
         ldp = pad_ld(cmax)
         f32 = dict(device=dev, dtype=torch.float32)
         Pt = torch.zeros((rk, ldp), **f32)
-        Bst = torch.zeros((rk, ldw), **f32)
-        A = torch.zeros((R, Kp, Kp), **f32)
+        ABst = torch.zeros(R * Kp * Kp + rk * ldw, **f32)     # the pass's statistics [A | B], same layout as [Ac | Bc]
+        A = ABst[:R * Kp * Kp].view(R, Kp, Kp)
+        Bst = ABst[R * Kp * Kp:].view(rk, ldw)
         # the chunk's statistics [Ac | Bc] in ONE buffer: the message of the all-reduce, no packing copies
         AcBc = torch.zeros(R * Kp * Kp + rk * ldw, **f32)
         Ac = AcBc[:R * Kp * Kp].view(R, Kp, Kp)
@@ -366,8 +367,7 @@ class DenseFrobeniusEngine:
         n_pass = np.full(R, max_pass, dtype=np.int64)
         alive = np.ones(R, dtype=bool)
         for ps in range(1, max_pass + 1):
-            A.zero_()
-            Bst.zero_()
+            ABst.zero_()
             for ci in range(n_chunks):
                 lo = ci * chunk_size
                 c = max(0, min(chunk_size, N - lo))
