@@ -120,7 +120,7 @@ __global__ void __launch_bounds__(ONP_THREADS, REGS > 0 ? 2 : 1) online_inner_pe
     const uint8_t* __restrict__ active, int64_t M, int R, float l1, float l2, float eps, float tol, int max_iter,
     int nslab, int* __restrict__ iters, unsigned int* __restrict__ arrive, double* __restrict__ slots,
     unsigned long long* __restrict__ total_iters, double* __restrict__ cross, float* __restrict__ state_op,
-    float* __restrict__ state_lo, int64_t ldo) {
+    float* __restrict__ state_lo, float* __restrict__ state_copy, int64_t ldo) {
   __shared__ float sgram[KP * KP];
   __shared__ double red[ONP_THREADS / 32][2];
   __shared__ int s_done;
@@ -234,6 +234,7 @@ __global__ void __launch_bounds__(ONP_THREADS, REGS > 0 ? 2 : 1) online_inner_pe
           for (int k = 0; k < KP; ++k) {
             const float v = sreg[j][k];
             state[(base + k) * lds + m] = v;
+            if (state_copy != nullptr) state_copy[(base + k) * ldo + m] = v;
             if (state_op != nullptr) {
               const float o = onl_tf32(v);
               state_op[(base + k) * ldo + m] = o;
@@ -242,14 +243,17 @@ __global__ void __launch_bounds__(ONP_THREADS, REGS > 0 ? 2 : 1) online_inner_pe
           }
         }
       }
-    } else if (state_op != nullptr) {
+    } else if (state_op != nullptr || state_copy != nullptr) {
       for (int64_t m = c0 + threadIdx.x; m < c1; m += ONP_THREADS) {
 #pragma unroll
         for (int k = 0; k < KP; ++k) {
           const float v = state[(base + k) * lds + m];
-          const float o = onl_tf32(v);
-          state_op[(base + k) * ldo + m] = o;
-          if (state_lo != nullptr) state_lo[(base + k) * ldo + m] = onl_tf32(v - o);
+          if (state_copy != nullptr) state_copy[(base + k) * ldo + m] = v;
+          if (state_op != nullptr) {
+            const float o = onl_tf32(v);
+            state_op[(base + k) * ldo + m] = o;
+            if (state_lo != nullptr) state_lo[(base + k) * ldo + m] = onl_tf32(v - o);
+          }
         }
       }
     }
@@ -380,20 +384,22 @@ int64_t cnmf_b200_online_loop_workspace_bytes(int32_t R) {
 static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                             const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                             float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
-                            void* workspace, double* cross, float* state_op, float* state_lo, int64_t ldo, void* stream);
+                            void* workspace, double* cross, float* state_op, float* state_lo, float* state_copy, int64_t ldo,
+                            void* stream);
 
 int cnmf_b200_online_loop(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                           const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                           float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
                           void* workspace, void* stream) {
   return online_loop_impl(Pt, ldp, state, lds, gram, active, M, R, Kp, l1, l2, eps, tol, max_iter, iters, max_iters_seen,
-                          workspace, nullptr, nullptr, nullptr, 0, stream);
+                          workspace, nullptr, nullptr, nullptr, nullptr, 0, stream);
 }
 
 static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                             const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                             float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
-                            void* workspace, double* cross, float* state_op, float* state_lo, int64_t ldo, void* stream) {
+                            void* workspace, double* cross, float* state_op, float* state_lo, float* state_copy, int64_t ldo,
+                            void* stream) {
   reset_launch_count();
   CNMF_CHECK_ARG(Pt && state && gram && iters && workspace, "online_loop: null pointer");
   CNMF_CHECK_ARG(M > 0 && R > 0 && ldp >= M && lds >= M && max_iter >= 0, "online_loop: bad shape");
@@ -449,16 +455,17 @@ static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t 
   void* args[] = {(void*)&Pt, (void*)&ldp, (void*)&state, (void*)&lds, (void*)&gram, (void*)&active, (void*)&M_, (void*)&R_,
                   (void*)&l1, (void*)&l2, (void*)&eps, (void*)&tol, (void*)&max_iter_, (void*)&nslab, (void*)&iters,
                   (void*)&arrive, (void*)&slots, (void*)&max_iters_seen, (void*)&cross, (void*)&state_op, (void*)&state_lo,
-                  (void*)&ldo};
+                  (void*)&state_copy, (void*)&ldo};
   CNMF_CUDA(cudaLaunchCooperativeKernel(kern, dim3(grid), dim3(ONP_THREADS), args, 0, st));
   count_launch();
   return 0;
 }
 
 /* One chunk of an online pass as ONE call (the kernels are the ones above and the tensor-core GEMM; what this saves
- * is the host: a dozen library calls per chunk from Python cost more than the kernels they enqueue).  The chunk's
- * usages are worked on in a COMPACT scratch copy (Hs, [R*Kp x ldp]): in the resident array a row of the chunk is
- * ldh floats from the next -- 4 MB at a million cells, one page per row for every TMA box and every warp.
+ * is the host: a dozen library calls per chunk from Python cost more than the kernels they enqueue).  The Gram and
+ * the statistics GEMM read COMPACT copies of the chunk's usages (Hs, Hopc: [R*Kp x ldp]) that the inner loop writes
+ * beside the resident rows: in the resident array a row of the chunk is ldh floats from the next -- 4 MB at a
+ * million cells, one page per row for every TMA box.
  *   phase CNMF_B200_ONLINE_USAGE   : P = x W^T, inner loop on the chunk's usages, then the chunk's statistics
  *                                    Ac = h^T h and Bc = h^T x;
  *   phase CNMF_B200_ONLINE_REFRESH : P = x W^T to fp32 accuracy (a second pass on W - tf32(W)), inner loop (max_iter
@@ -466,12 +473,6 @@ static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t 
  *                                    at the end of a pass and, on the way, the data-dependent terms of the objective;
  *   phase CNMF_B200_ONLINE_SPECTRA : A += Ac, B += Bc (after the caller's all-reduce when cells are sharded), inner
  *                                    loop on W against (A, B), then W's tf32 copy, its residual and Gram. */
-static int copy_rows(float* dst, int64_t ldd, const float* src, int64_t lds_, int64_t rows, int64_t cols, cudaStream_t st) {
-  CNMF_CUDA(cudaMemcpy2DAsync(dst, (size_t)ldd * 4, src, (size_t)lds_ * 4, (size_t)cols * 4, (size_t)rows,
-                              cudaMemcpyDeviceToDevice, st));
-  return 0;
-}
-
 int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, void* stream) {
   reset_launch_count();
   CNMF_CHECK_ARG(a != nullptr, "online_chunk: null arguments");
@@ -483,19 +484,20 @@ int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, 
     CNMF_CHECK_ARG(a->c > 0 && a->x && a->Wop && a->Ht && a->Hs && a->Pt && a->gramW && a->iters_h && a->ws_loop &&
                        a->ws_gram && a->Ac, "online_chunk: null pointer (usage phase)");
     CNMF_CHECK_ARG(a->ldp >= a->c && a->ldp % 4 == 0, "online_chunk: ldp too small or not a multiple of 4");
-    CNMF_TRY(copy_rows(a->Hs, a->ldp, a->Ht, a->ldh, rk, a->c, st));
     CNMF_TRY(cnmf_b200_dense_gemm_tf32(a->x, a->ldx, a->c, a->n_genes, a->Wop, a->ldw, a->Pt, a->ldp, a->active, a->R,
                                        a->Kp, 0, stream));
-    n += 2;
+    n += 1;
     const bool refresh = phase == CNMF_B200_ONLINE_REFRESH;
     if (refresh && a->Wlo != nullptr) {
       CNMF_TRY(cnmf_b200_dense_gemm_tf32(a->x, a->ldx, a->c, a->n_genes, a->Wlo, a->ldw, a->Pt, a->ldp, a->active, a->R,
                                          a->Kp, 1, stream));
       n += 1;
     }
-    CNMF_TRY(online_loop_impl(a->Pt, a->ldp, a->Hs, a->ldp, a->gramW, a->active, a->c, a->R, a->Kp, a->l1_H, a->l2_H,
+    // the loop reads the chunk's usages from the resident array once, keeps them in registers, and writes back the
+    // resident rows plus compact copies (fp32 for the Gram, tf32 for the statistics GEMM)
+    CNMF_TRY(online_loop_impl(a->Pt, a->ldp, a->Ht, a->ldh, a->gramW, a->active, a->c, a->R, a->Kp, a->l1_H, a->l2_H,
                               a->eps, a->h_tol, a->max_iter, a->iters_h, nullptr, a->ws_loop,
-                              refresh ? a->cross : nullptr, refresh ? nullptr : a->Hopc, nullptr, a->ldp, stream));
+                              refresh ? a->cross : nullptr, refresh ? nullptr : a->Hopc, nullptr, a->Hs, a->ldp, stream));
     CNMF_TRY(launch_gram(a->Hs, a->ldp, a->R, a->Kp, a->c, a->Ac, a->ws_gram, st));
     n += 3;
     if (refresh) {
@@ -506,7 +508,6 @@ int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, 
                                          a->R, a->Kp, 0, stream));
       n += 1;
     }
-    if (a->max_iter > 0) { CNMF_TRY(copy_rows(a->Ht, a->ldh, a->Hs, a->ldp, rk, a->c, st)); n += 1; }
   } else if (phase == CNMF_B200_ONLINE_SPECTRA) {
     CNMF_CHECK_ARG(a->A && a->Ac && a->Bst && a->Bc && a->Wall && a->Wop && a->gramW && a->iters_w && a->ws_loop &&
                        a->ws_gram, "online_chunk: null pointer (spectra phase)");
@@ -520,7 +521,7 @@ int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, 
     }
     CNMF_TRY(online_loop_impl(a->Bst, a->ldw, a->Wall, a->ldw, a->A, a->active, a->n_genes, a->R, a->Kp, a->l1_W,
                               a->l2_W, a->eps, a->w_tol, a->max_iter, a->iters_w, nullptr, a->ws_loop, nullptr, a->Wop,
-                              a->Wlo, a->ldw, stream));
+                              a->Wlo, nullptr, a->ldw, stream));
     CNMF_TRY(launch_gram(a->Wall, a->ldw, a->R, a->Kp, a->n_genes, a->gramW, a->ws_gram, st));
     n += 5;
   } else {
