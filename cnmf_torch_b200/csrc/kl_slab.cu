@@ -85,6 +85,14 @@ __device__ __forceinline__ void ldg_pred(int& j, float& x, const int* cp, const 
   asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t@p ld.global.nc.b32 %0, [%2];\n\t@p ld.global.nc.f32 %1, [%3];\n\t}"
                : "+r"(j), "+f"(x) : "l"(cp), "l"(xp), "r"((int)ok));
 }
+__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
+  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+__device__ __forceinline__ void sts64(uint32_t addr, uint32_t a, uint32_t b) {
+  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
+}
 __device__ __forceinline__ float fast_rcp(float v) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
@@ -107,6 +115,7 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
   using Cfg = SlabCfg<KP>;
   constexpr int P = Cfg::P, RGP = Cfg::RGP, A = Cfg::A, LANES = Cfg::LANES;
   constexpr int LINE_WORDS = RGP * P;
+  constexpr int CH = (KS_CHUNK / (2 * A)) * (2 * A);   // entries per staged chunk: whole steps
   extern __shared__ __align__(128) unsigned char slab[];
   __shared__ double s_obj[KS_WARPS][2 * RGP];
 
@@ -120,6 +129,7 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
   const int64_t lo = T * blockIdx.x / gridDim.x, hi = T * (blockIdx.x + 1) / gridDim.x;
 
   const uint32_t slab_u32 = static_cast<uint32_t>(__cvta_generic_to_shared(slab));
+  const uint32_t stage_u32 = slab_u32 + (uint32_t)a.block * KS_LINE;   // per-warp (column, value) staging, after the lines
   uint32_t loff[P];   // byte offset of this lane's m-th load inside a line; word index (m + a) mod P of pair rp
   int hoff[P];        // the same word index for the moving factor's row (in 8-byte words)
 #pragma unroll
@@ -170,9 +180,11 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
       }
       __syncthreads();   // the slab is complete
 
-      // Segments of this phase go round the warps (fixed assignment: the next segment is known in advance, so its
-      // table entries, its row of the moving factor and its first entries are fetched while the current one computes;
-      // with 16 warps per SM nothing else hides those latencies).
+      // Segments of this phase go round the warps (fixed assignment, so what comes next is known in advance).  The
+      // (column, value) pairs of a segment are brought into a per-warp staging buffer by cp.async, a chunk of KS_CHUNK
+      // entries ahead of the arithmetic -- asynchronous copies do not occupy scoreboard slots, which the register
+      // prefetch of the first version kept running out of (a load waited for at the first use of the index, with 16
+      // warps per SM to hide it).  Table entries are fetched two segments ahead, the row of the moving factor one.
       auto load_meta = [&](int sgi, int& row, int& beg, int& end) {
         const int v = a.seg_vrow[sgi];
         row = v - b * M;
@@ -185,88 +197,96 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
 #pragma unroll
         for (int m = 0; m < P; ++m) h[m] = pair_on ? __ldg(hp + hoff[m]) : make_uint2(0u, 0u);
       };
-      // entries of this lane: beg + hw*A + a, then every 2A-th.  Idle slots (past the end; lanes beyond LANES) read
-      // line 0 with x = 0.
-      int jq[KS_PREFETCH];
-      float xq[KS_PREFETCH];
-      auto fill_ring = [&](int beg, int end) {
-#pragma unroll
-        for (int t = 0; t < KS_PREFETCH; ++t) {
-          const int idx = beg + hw * A + aslot + t * 2 * A;
-          const bool ok = lane_on && idx < end;
-          jq[t] = ok ? __ldg(a.col_idx + idx) : c0;
-          xq[t] = ok ? __ldg(a.val + idx) : 0.f;
+      const uint32_t stg = stage_u32 + (uint32_t)warp * (2u * KS_CHUNK * 8u);
+      auto issue_chunk = [&](int buf, int cbeg, int cend) {   // entries cbeg.. of the CSR arrays; past cend: (c0, 0)
+        int need = cend - cbeg;
+        need = need > CH ? CH : (need + 2 * A - 1) / (2 * A) * (2 * A);
+        for (int e = lane; e < need; e += 32) {
+          const uint32_t dst = stg + (uint32_t)(buf * KS_CHUNK + e) * 8u;
+          const int idx = cbeg + e;
+          if (idx < cend) {
+            cp_async4(dst, a.col_idx + idx);
+            cp_async4(dst + 4u, a.val + idx);
+          } else {
+            sts64(dst, (uint32_t)c0, 0u);
+          }
         }
+        cp_async_commit();
       };
+      const uint32_t lane_entry = (uint32_t)(hw * A + aslot) * 8u;   // this lane's entry inside a step's 2A entries
 
       int sg = s + warp;
-      int row = 0, beg = 0, end = 0, nrow = 0, nbeg = 0, nend = 0;
-      uint2 hreg[P];
+      int row = 0, beg = 0, end = 0, nrow = 0, nbeg = 0, nend = 0, n2row = 0, n2beg = 0, n2end = 0;
+      uint2 hreg[P], hnext[P];
+      int buf = 0;
       if (sg < sb_end) {
         load_meta(sg, row, beg, end);
         load_h(row, hreg);
-        fill_ring(beg, end);
+        issue_chunk(0, beg, end);
+        if (sg + KS_WARPS < sb_end) load_meta(sg + KS_WARPS, nrow, nbeg, nend);
       }
       while (sg < sb_end) {
         const int nsg = sg + KS_WARPS;
         const bool has_next = nsg < sb_end;
-        if (has_next) load_meta(nsg, nrow, nbeg, nend);
+        if (nsg + KS_WARPS < sb_end) load_meta(nsg + KS_WARPS, n2row, n2beg, n2end);
         float n0[KP], n1[KP];   // n0[2m], n0[2m+1]: numerators of k-pair (m + a) mod P, replicate rep0
 #pragma unroll
         for (int k = 0; k < KP; ++k) { n0[k] = 0.f; n1[k] = 0.f; }
         float acc0 = 0.f, acc1 = 0.f;
 
-        // KS_PREFETCH steps per trip, each with its own fixed ring slot: the slot is consumed, then refilled with the
-        // entry KS_PREFETCH steps ahead (no register shuffling -- a move of a register that is the destination of a
-        // load in flight would wait for that load, which is exactly what the ring is there to avoid)
-        int pidx = beg + hw * A + aslot + KS_PREFETCH * 2 * A;
-        const int end_lane = lane_on ? end : 0;
-        for (int p0 = beg; p0 < end; p0 += KS_PREFETCH * 2 * A) {
+        for (int cb = beg; cb < end; cb += CH) {
+          cp_async_wait_all();
+          __syncwarp();
+          // the next chunk -- of this segment, or the first of the next one (and that segment's row of the factor)
+          if (cb + CH < end) {
+            issue_chunk(buf ^ 1, cb + CH, end);
+          } else if (has_next) {
+            issue_chunk(buf ^ 1, nbeg, nend);
+            load_h(nrow, hnext);
+          }
+          const int cend = cb + CH < end ? cb + CH : end;
+          uint32_t ep = stg + (uint32_t)(buf * KS_CHUNK) * 8u + lane_entry;
+          uint2 jx_next = lds64(ep);   // the step's (column, value) one step ahead of its use: the line address is
+                                       // then ready when the step starts (one shared-memory latency less per step)
+          for (int p0 = cb; p0 < cend; p0 += 2 * A) {
+            const uint2 jx = jx_next;                                     // (column, value bits); idle lanes: unused
+            ep += 2 * A * 8;
+            jx_next = lds64(ep);       // (past the chunk's last step: a stale slot of the staging area, never used)
+            const uint32_t line = sbase + (lane_on ? (jx.x << 7) : ((uint32_t)c0 << 7));   // sbase = slab - c0 * 128
+            const float x = lane_on ? __uint_as_float(jx.y) : 0.f;
+            uint2 w[P];
 #pragma unroll
-          for (int t = 0; t < KS_PREFETCH; ++t) {
-            if (p0 + t * 2 * A < end) {   // (uniform over the warp)
-              const uint32_t line = sbase + ((uint32_t)jq[t] << 7);   // sbase = slab - c0 * 128
-              float x;
-              asm volatile("mov.f32 %0, %1;" : "=f"(x) : "f"(xq[t]));   // frees the ring register for the refill
-              // refill the slot IN PLACE (a predicated load into the ring register itself: a load into a temporary
-              // followed by a move at the end of the step would wait for the load it has just issued)
-              jq[t] = c0;
-              xq[t] = 0.f;
-              ldg_pred(jq[t], xq[t], a.col_idx + pidx, a.val + pidx, pidx < end_lane);
-              pidx += 2 * A;
-              uint2 w[P];
+            for (int m = 0; m < P; ++m) w[m] = lds64(line + loff[m]);
+            // s = eps + h.w: the clamp max(s, eps) of the update rule without its instruction (eps = 1e-16 vanishes
+            // in any s that is not itself degenerate); one dependent chain per replicate, the two interleave
+            float s0 = a.eps, s1 = a.eps;
 #pragma unroll
-              for (int m = 0; m < P; ++m) w[m] = lds64(line + loff[m]);
-              // s = eps + h.w: the clamp max(s, eps) of the update rule without its instruction (eps = 1e-16 vanishes
-              // in any s that is not itself degenerate); one dependent chain per replicate, the two interleave
-              float s0 = a.eps, s1 = a.eps;
+            for (int m = 0; m < P; ++m) {
+              s0 = fhfma_lo(hreg[m].x, w[m].x, s0);
+              s1 = fhfma_lo(hreg[m].y, w[m].y, s1);
+              s0 = fhfma_hi(hreg[m].x, w[m].x, s0);
+              s1 = fhfma_hi(hreg[m].y, w[m].y, s1);
+            }
+            if (MODE == 0) {
+              const uint16_t q0 = f32_to_f16_bits(x * fast_rcp(s0)), q1 = f32_to_f16_bits(x * fast_rcp(s1));
 #pragma unroll
               for (int m = 0; m < P; ++m) {
-                s0 = fhfma_lo(hreg[m].x, w[m].x, s0);
-                s1 = fhfma_lo(hreg[m].y, w[m].y, s1);
-                s0 = fhfma_hi(hreg[m].x, w[m].x, s0);
-                s1 = fhfma_hi(hreg[m].y, w[m].y, s1);
+                n0[2 * m] = fhfma_q_lo(q0, w[m].x, n0[2 * m]);
+                n0[2 * m + 1] = fhfma_q_hi(q0, w[m].x, n0[2 * m + 1]);
+                n1[2 * m] = fhfma_q_lo(q1, w[m].y, n1[2 * m]);
+                n1[2 * m + 1] = fhfma_q_hi(q1, w[m].y, n1[2 * m + 1]);
               }
-              if (MODE == 0) {
-                const uint16_t q0 = f32_to_f16_bits(x * fast_rcp(s0)), q1 = f32_to_f16_bits(x * fast_rcp(s1));
-#pragma unroll
-                for (int m = 0; m < P; ++m) {
-                  n0[2 * m] = fhfma_q_lo(q0, w[m].x, n0[2 * m]);
-                  n0[2 * m + 1] = fhfma_q_hi(q0, w[m].x, n0[2 * m + 1]);
-                  n1[2 * m] = fhfma_q_lo(q1, w[m].y, n1[2 * m]);
-                  n1[2 * m + 1] = fhfma_q_hi(q1, w[m].y, n1[2 * m + 1]);
-                }
-              } else {
-                acc0 = fmaf(x, __log2f(s0), acc0);   // x = 0 on idle lanes
-                acc1 = fmaf(x, __log2f(s1), acc1);
-              }
+            } else {
+              acc0 = fmaf(x, __log2f(s0), acc0);   // x = 0 on idle lanes and past the end
+              acc1 = fmaf(x, __log2f(s1), acc1);
             }
           }
+          buf ^= 1;
         }
-        // the next segment's operands are requested before this one's results are reduced and stored
-        if (has_next) {
-          load_h(nrow, hreg);
-          fill_ring(nbeg, nend);
+        if (beg >= end && has_next) {   // (an empty segment cannot occur: segments are made from stored entries)
+          issue_chunk(buf ^ 1, nbeg, nend);
+          load_h(nrow, hnext);
+          buf ^= 1;
         }
 
         if (MODE == 0) {
@@ -298,7 +318,11 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
           dacc1 += (double)acc1;
         }
         sg = nsg; row = nrow; beg = nbeg; end = nend;
+        nrow = n2row; nbeg = n2beg; nend = n2end;
+#pragma unroll
+        for (int m = 0; m < P; ++m) hreg[m] = hnext[m];
       }
+      cp_async_wait_all();   // nothing may still be writing the staging buffers when the next phase reuses them
       s = sb_end;
     }
 
@@ -470,11 +494,11 @@ int launch_kl_to_half_pairs(const float* src, void* dst, int64_t rows, int R, in
 
 template <int KP, int MODE>
 static int launch_slab_inst(const KlSlabArgs& a, int grid, cudaStream_t st) {
-  const int smem = a.block * KS_LINE;
+  const int smem = a.block * KS_LINE + KS_STAGE_BYTES;
   static unsigned long long attr_mask = 0;
   if (needs_func_attr(&attr_mask))
     CNMF_CUDA(cudaFuncSetAttribute(kl_slab_kernel<KP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   KS_MAX_LINES * KS_LINE));
+                                   KS_MAX_LINES * KS_LINE + KS_STAGE_BYTES));
   kl_slab_kernel<KP, MODE><<<grid, KS_THREADS, smem, st>>>(a);
   CNMF_LAUNCH_CHECK();
   return 0;

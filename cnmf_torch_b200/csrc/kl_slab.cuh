@@ -8,9 +8,10 @@ namespace cnmf {
 constexpr int KS_THREADS = 512;
 constexpr int KS_WARPS = KS_THREADS / 32;
 constexpr int KS_LINE = 128;               // bytes of shared memory per column of the block
-constexpr int KS_MAX_LINES = 1600;         // 200 KB slab
+constexpr int KS_CHUNK = 128;              // entries per staging chunk (per warp, two buffers of (column, value))
+constexpr int KS_STAGE_BYTES = KS_WARPS * 2 * KS_CHUNK * 8 + 256;   // 32 KB (+ the one-step read-ahead past the last buffer)
+constexpr int KS_MAX_LINES = 1400;         // 175 KB slab + 32 KB staging + static: within 227 KB
 constexpr int KS_SEG_LEN = 640;            // entries per segment (64 steps at Kp = 10)
-constexpr int KS_PREFETCH = 4;              // steps of (index, value) loads in flight per lane
 constexpr int KS_SEG_OVERHEAD_STEPS = 2;   // set-up + un-rotation of a segment, in steps, for the static work split
 
 #define KS_DISPATCH_KP(kp, ...)                                                                       \

@@ -311,10 +311,10 @@ typedef struct cnmf_b200_kl_problem {
  * tolerances of the tests):
  *   GATHER -- one thread per (row segment, replicate), lanes = consecutive replicates, the fp16 copy of the fixed
  *             factor gathered from L2 in coalesced runs (also what the standalone cnmf_b200_kl_half_step runs);
- *             the default: faster at the cfg-3 shape (100 000 cells: 7.4 vs 9.4 ms per batched iteration);
+ *             the default: faster at the cfg-3 shape (100 000 cells: 7.4 vs 8.2 ms per batched iteration);
  *   SLAB   -- the fixed factor's fp16 copy of one replicate group and one block of columns is staged in shared
  *             memory (bank-conflict-free line layout) and gathered from there; fp16 x fp16 + fp32 FMAs (FHFMA);
- *             70 x less L2 traffic, faster on small matrices (20 000 cells: 1.74 vs 1.92 ms). */
+ *             70 x less L2 traffic, faster on small matrices (20 000 cells: 1.71 vs 1.92 ms). */
 #define CNMF_B200_KL_IMPL_GATHER 0
 #define CNMF_B200_KL_IMPL_SLAB 1
 
