@@ -271,7 +271,8 @@ def _extras(dev):
                     "replicate_iters_per_s": 100 / dt,
                     "algorithmic_hbm_gb_s": (2 * 8 * eng.nnz + 100 * 8 * 9 * (cells + 2000)) / dt / 1e9,
                     "fp32_fma_tflops_algorithmic": 2.0 * 2 * eng.nnz * 100 * 2 * 9 / dt / 1e12,
-                    "kernels": "gather family (default); includes 1/10 of an objective evaluation"}
+                    "kernels": ("slab" if eng.impl == 1 else "gather") + " family (the engine's choice at this size); "
+                               "includes 1/10 of an objective evaluation"}
         del eng, b, xk
         torch.cuda.empty_cache()
     # cfg-1/2 in the reference's default mode: online MU, chunk 5000, K=9, R=100, 3 passes
