@@ -303,6 +303,12 @@ def _pipeline_wall(dev):
     x = nb_counts(N_CELLS, N_GENES, seed=14)
     tmp = tempfile.mkdtemp(prefix="cnmf_b200_bench_")
     try:
+        # warm-up on a small matrix: module loading, thread pools and pandas' first calls are not the pipeline's time
+        warm = host.cNMF(output_dir=tmp, name="warm", device=str(dev))
+        warm.prepare_from_matrix(x[:300, :200] + 0.01, [3], n_iter=4, seed=1, beta_loss="frobenius", use_gpu=True)
+        warm.factorize(nmf_kwargs_override=dict(mode="batch", algo=ALGO, batch_max_iter=20))
+        warm.combine()
+        warm.consensus(3, density_threshold=2.0)
         obj = host.cNMF(output_dir=tmp, name="cfg2", device=str(dev))
         obj.prepare_from_matrix(x, KS, n_iter=REPLICATES, seed=14, beta_loss="frobenius", use_gpu=True)  # `cnmf prepare --use_gpu`
         torch.cuda.synchronize()

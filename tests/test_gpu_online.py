@@ -150,6 +150,40 @@ def test_online_engine_matches_oracle(problem, K, chunk):
     print(f"[online K={K} chunk={chunk}] worst objective rel err {worst:.2e}; inner iterations {res.inner_iterations}")
 
 
+def test_online_with_l1_and_l2_regularisation_matches_oracle(problem):
+    """alpha_usage / alpha_spectra (cnmf.py:757-761) in online mode: the L1 / L2 terms of both inner loops and of the
+    objective (whose sum(H), sum(W) terms do not come from the refresh kernels)."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    eng = DenseFrobeniusEngine(problem)
+    reg = dict(l1_H=0.02, l2_H=0.1, l1_W=0.01, l2_W=0.3)
+    H0, W0 = eng.make_init(5, [3, 4])
+    kw = dict(tol=0.0, max_pass=3, chunk_size=200, chunk_max_iter=60)
+    res = eng.factorize_online(5, H0=H0, W0=W0, return_H=True, **kw, **reg)
+    for r in range(2):
+        ora = no.nmf_online(problem, H0[r].numpy(), W0[r].numpy(), l1_h=reg["l1_H"], l2_h=reg["l2_H"], l1_w=reg["l1_W"],
+                            l2_w=reg["l2_W"], **kw)
+        for (p_o, obj_o), (p_g, obj_g) in zip(ora["trace"], res.trace):
+            assert p_o == p_g and abs(obj_g[r] - obj_o) / obj_o < 1e-3, (r, p_o, obj_g[r], obj_o)
+        assert _pearson(res.W[r], ora["W"]) >= 0.999 and _pearson(res.H[r], ora["H"]) >= 0.999
+    plain = eng.factorize_online(5, H0=H0, W0=W0, **kw)
+    assert np.all(res.trace[-1][1] != plain.trace[-1][1])
+
+
+def test_online_frozen_replicates_keep_their_objective(problem):
+    """A replicate that converged is skipped by every kernel of later passes: its state, spectra and reported error
+    are those of the pass it was frozen at (run to convergence vs the same replicates run alone)."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    eng = DenseFrobeniusEngine(problem)
+    seeds = [1, 2, 3, 4, 5, 6]
+    res = eng.factorize_online(6, seeds=seeds, tol=2e-3, max_pass=12, chunk_size=100, chunk_max_iter=40)
+    assert len(set(res.n_iter.tolist())) > 1 or res.n_iter.max() < 12      # they do not all run to the cap together
+    for r in (0, 3):
+        one = eng.factorize_online(6, seeds=[seeds[r]], tol=2e-3, max_pass=12, chunk_size=100, chunk_max_iter=40)
+        assert one.n_iter[0] == res.n_iter[r]
+        assert abs(one.err[0] - res.err[r]) / one.err[0] < 1e-5
+        assert _pearson(one.W[0], res.W[r]) >= 0.99999
+
+
 def test_online_convergence_and_run_nmf_default_kwargs(problem):
     """The exact kwargs cNMF writes to its YAML (cnmf.py:757-771) through the run_nmf drop-in."""
     from cnmf_torch_b200.nmf import run_nmf
