@@ -779,9 +779,9 @@ def main():
     Hs, Hop = big.Ht.clone(), big.Ht.clone()
 
     def dominant():
-        _lib.check(lib.cnmf_b200_dense_half_step(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, Hs.data_ptr(),
-                                                 Hop.data_ptr(), p.ldh, p.gramW, None, p.R, p.Kp, p.algo, 0.0, 0.0,
-                                                 p.eps, None, st))
+        _lib.check(lib.cnmf_b200_dense_half_step_k(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, Hs.data_ptr(),
+                                                   Hop.data_ptr(), p.ldh, p.gramW, None, p.rep_k, p.R, p.Kp, p.algo,
+                                                   0.0, 0.0, p.eps, None, st))
     roof = None
     if impl != _lib.IMPL_SIMT:
         for _ in range(5):

@@ -30,7 +30,7 @@ class FrobProblem(C.Structure):
         ("Wall", vp), ("ldw", i64), ("Ht", vp), ("ldh", i64),
         ("gramW", vp), ("gramH", vp), ("active", vp),
         ("l1_H", f32), ("l2_H", f32), ("l1_W", f32), ("l2_W", f32), ("eps", f32), ("pad0", f32),
-        ("normX2", f64), ("err2", vp), ("workspace", vp), ("workspace_bytes", i64),
+        ("normX2", f64), ("err2", vp), ("workspace", vp), ("workspace_bytes", i64), ("rep_k", vp),
     ]
 
 
@@ -81,6 +81,8 @@ SIGNATURES = {
     "cnmf_b200_init_random": (i32, [vp, i32, i32, i32, i64, i64, i64, i64, f32, vp, i64, vp, i64, vp]),
     "cnmf_b200_dense_half_step": (i32, [vp, i64, i64, i64, vp, i64, vp, vp, i64, vp, vp, i32, i32, i32, f32, f32,
                                         f32, vp, vp]),
+    "cnmf_b200_dense_half_step_k": (i32, [vp, i64, i64, i64, vp, i64, vp, vp, i64, vp, vp, vp, i32, i32, i32, f32, f32,
+                                          f32, vp, vp]),
     "cnmf_b200_frob_objective_parts": (i32, [C.POINTER(FrobProblem), vp, vp]),
     "cnmf_b200_frob_objective_combine": (i32, [f64, vp, vp, vp, i32, i32, f32, f32, f32, f32, vp, vp]),
     "cnmf_b200_dense_gemm_tf32": (i32, [vp, i64, i64, i64, vp, i64, vp, i64, vp, i32, i32, i32, vp]),

@@ -97,17 +97,19 @@ __device__ __forceinline__ double warp_sum(double v) {
 // ginv : optional (HALS) KP reciprocals of the regularised diagonal, 1/(G_kk + l2), or a negative value where
 //        G_kk + l2 < eps (component frozen at 0): the tcgen05 epilogue precomputes them once per tile, which
 //        takes the division (~14 instructions per component) out of the per-row instruction stream.
-template <int KP, int ALGO>
+// KE <= KP: only the first KE components exist (a replicate of K = KE stored in a Kp-padded stack); the padded ones are
+// zero and stay untouched -- bit-identical to running all KP, whose extra terms are exact zeros.
+template <int KP, int ALGO, int KE = KP>
 __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
                                            const float* __restrict__ gram, float l1, float l2,
                                            float eps, const float* __restrict__ ginv = nullptr) {
   if (ALGO == CNMF_B200_ALGO_MU) {
     float out[KP];
 #pragma unroll
-    for (int k = 0; k < KP; ++k) {
+    for (int k = 0; k < KE; ++k) {
       float denom = 0.f;
 #pragma unroll
-      for (int j = 0; j < KP; ++j) denom = fmaf(s[j], gram[j * KP + k], denom);
+      for (int j = 0; j < KE; ++j) denom = fmaf(s[j], gram[j * KP + k], denom);
       denom = fmaf(l2, s[k], denom);
       // (p >= 0: a sum of products of non-negative numbers, so the clamp is the identity when l1 == 0; no branch)
       float numer = fmaxf(p[k] - l1, 0.f);
@@ -119,7 +121,7 @@ __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
       out[k] = s[k] * rate;
     }
 #pragma unroll
-    for (int k = 0; k < KP; ++k) s[k] = out[k];
+    for (int k = 0; k < KE; ++k) s[k] = out[k];
   } else {
     // HALS sweep on a running residual r_j = p_j - l1 - (s.G)_j kept up to date after every component:
     // the same arithmetic as recomputing p_k - s.G_:k before step k, but the per-step dependency is one
@@ -127,14 +129,14 @@ __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
     // dead once r is formed.
     float r[KP];
 #pragma unroll
-    for (int j = 0; j < KP; ++j) {
+    for (int j = 0; j < KE; ++j) {
       float t = 0.f;
 #pragma unroll
-      for (int i = 0; i < KP; ++i) t = fmaf(s[i], gram[i * KP + j], t);
+      for (int i = 0; i < KE; ++i) t = fmaf(s[i], gram[i * KP + j], t);
       r[j] = p[j] - t - l1;
     }
 #pragma unroll
-    for (int k = 0; k < KP; ++k) {
+    for (int k = 0; k < KE; ++k) {
       // s + r * (1/g) in every path (the reciprocal correctly rounded): at most ~1 ulp of the quotient away from
       // the s + r / g of the restated coordinate descent, and the same arithmetic on the SIMT and tcgen05 paths
       float inv;
@@ -148,7 +150,7 @@ __device__ __forceinline__ void update_row(const float (&p)[KP], float (&s)[KP],
       const float delta = v - s[k];
       s[k] = v;
 #pragma unroll
-      for (int j = 0; j < KP; ++j)
+      for (int j = 0; j < KE; ++j)
         if (j > k) r[j] = fmaf(-delta, gram[k * KP + j], r[j]);
     }
   }

@@ -23,6 +23,7 @@
 
 #include <atomic>
 #include <mutex>
+#include <type_traits>
 #include <vector>
 
 #include "common.cuh"
@@ -61,6 +62,7 @@ struct TcParams {
   const float* gram;      // [R x KP x KP], or (gram_ntile > 0) the per-tile partials [R x gram_ntile x KP*KP]
   int gram_ntile;
   const uint8_t* active;  // [R] or null
+  const uint8_t* rep_k;   // [R] true K of every replicate (KP-3 .. KP), or null: all KP
   double* partials;       // [num_m_tiles x R x 2]
   int R;
   int t;  // replicates per tile
@@ -268,7 +270,8 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   uint64_t* tempty = tfull + 2;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
   uint8_t* sact = reinterpret_cast<uint8_t*>(tmem_slot + 2);  // [t] active flags of the tile's replicates
-  float* sginv = reinterpret_cast<float*>(sact + 64);         // [t][KP] HALS: 1/(G_kk + l2), < 0 where frozen
+  uint8_t* srepk = sact + 64;                                 // [t] true K of the tile's replicates (<= KP)
+  float* sginv = reinterpret_cast<float*>(srepk + 64);        // [t][KP] HALS: 1/(G_kk + l2), < 0 where frozen
 
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
@@ -436,8 +439,10 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
       }
       // active flags of the tile's replicates: read once here instead of one dependent global load per replicate
       // inside the update loop
-      for (int i = et; i < t; i += ET)
+      for (int i = et; i < t; i += ET) {
         sact[i] = (r0 + i < prm.R && (prm.active == nullptr || prm.active[r0 + i] != 0)) ? 1 : 0;
+        srepk[i] = (prm.rep_k != nullptr && r0 + i < prm.R) ? prm.rep_k[r0 + i] : static_cast<uint8_t>(KP);
+      }
       epi_bar_sync<ET>(last);
       if (ALGO == CNMF_B200_ALGO_HALS) {
         // reciprocals of the regularised diagonal, once per tile (these warps idle here while the main loop runs)
@@ -494,25 +499,37 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
               sp[static_cast<int64_t>(k) * prm.lds] = (ALGO == TC_MODE_ACCUM) ? s[k] + p[k] : p[k];
           }
         } else {
-          if (in) {
-            if (act) {
-              update_row<KP, ALGO>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps,
-                                   ALGO == CNMF_B200_ALGO_HALS ? sginv + rr * KP : nullptr);
+          // The replicate's own K (a stack holds K = KP-3 .. KP padded to KP): the update, the state traffic and the
+          // sums run over KE components only -- the padded ones are zero and stay zero.  One instantiation per KE;
+          // predicated-off instructions would still take issue slots in this issue-bound loop.
+          auto body = [&](auto ke_tag) {
+            constexpr int KE = decltype(ke_tag)::value;
+            if (in) {
+              if (act) {
+                update_row<KP, ALGO, KE>(p, s, sgram + rr * KP * KP, prm.l1, prm.l2, prm.eps,
+                                         ALGO == CNMF_B200_ALGO_HALS ? sginv + rr * KP : nullptr);
 #pragma unroll
-              for (int k = 0; k < KP; ++k) sp[static_cast<int64_t>(k) * prm.lds] = s[k];
-              if (prm.state_op != nullptr) {
-                float* op = prm.state_op + soff;
+                for (int k = 0; k < KE; ++k) sp[static_cast<int64_t>(k) * prm.lds] = s[k];
+                if (prm.state_op != nullptr) {
+                  float* op = prm.state_op + soff;
 #pragma unroll
-                for (int k = 0; k < KP; ++k) op[static_cast<int64_t>(k) * prm.lds] = to_tf32(s[k]);
+                  for (int k = 0; k < KE; ++k) op[static_cast<int64_t>(k) * prm.lds] = to_tf32(s[k]);
+                }
+              }
+              if (want_sums) {
+#pragma unroll
+                for (int k = 0; k < KE; ++k) {
+                  cross = fmaf(s[k], p[k], cross);
+                  ssum += s[k];
+                }
               }
             }
-            if (want_sums) {
-#pragma unroll
-              for (int k = 0; k < KP; ++k) {
-                cross = fmaf(s[k], p[k], cross);
-                ssum += s[k];
-              }
-            }
+          };
+          switch (KP - static_cast<int>(srepk[rr])) {
+            case 1: body(std::integral_constant<int, (KP > 1 ? KP - 1 : KP)>{}); break;
+            case 2: body(std::integral_constant<int, (KP > 2 ? KP - 2 : KP)>{}); break;
+            case 3: body(std::integral_constant<int, (KP > 3 ? KP - 3 : KP)>{}); break;
+            default: body(std::integral_constant<int, KP>{}); break;
           }
           if (want_sums) {
             cross = warp_sum(cross);
@@ -625,7 +642,7 @@ struct TcPlan {
 static size_t tc_smem_bytes(int t, int Kp, int stages, int cg) {
   const size_t stage = TC_A_BYTES + static_cast<size_t>(t) * Kp / cg * TC_BK * 4;
   size_t extra = static_cast<size_t>(t) * Kp * Kp * 4 + 4 * static_cast<size_t>(t) * 2 * 4;
-  extra += (2 * TC_MAX_STAGES + 4) * 8 + 16 + 64;  // barriers, TMEM slot, per-tile active flags (t <= 64)
+  extra += (2 * TC_MAX_STAGES + 4) * 8 + 16 + 128;  // barriers, TMEM slot, per-tile active flags and K (t <= 64)
   extra += static_cast<size_t>(t) * Kp * 4;         // reciprocal diagonals (HALS)
   return stages * stage + extra + 1024;  // +1024: manual alignment of the dynamic base
 }
@@ -788,7 +805,7 @@ static int launch_tc_inst(const CUtensorMap& ma, const CUtensorMap& mb, const Tc
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st);
+                          double* partials, cudaStream_t st, const uint8_t* rep_k = nullptr);
 
 int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                         float* state, float* state_op, int64_t lds, const float* gram, const uint8_t* active, int R,
@@ -801,7 +818,7 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st) {
+                          double* partials, cudaStream_t st, const uint8_t* rep_k) {
   TcPlan plan;
   const int sms = tc_num_sms();
   if (!tc_plan(M, Kd, R, Kp, sms, &plan)) {
@@ -812,7 +829,7 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
   CNMF_TRY(get_tensor_map(A, M, Kd, lda, TC_BM, &ma));
   CNMF_TRY(get_tensor_map(F, static_cast<int64_t>(R) * Kp, Kd, ldf, plan.BN / plan.cg, &mb));
   TcParams prm;
-  prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.gram_ntile = gram_ntile; prm.active = active;
+  prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.gram_ntile = gram_ntile; prm.active = active; prm.rep_k = rep_k;
   prm.partials = partials; prm.R = R; prm.t = plan.t; prm.num_m_tiles = plan.num_m_tiles; prm.num_m_groups = plan.num_m_groups;
   prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
   static const int dbg = [] { const char* e = getenv("CNMF_B200_TC_DEBUG"); return e ? atoi(e) : 0; }();
@@ -857,6 +874,21 @@ int cnmf_b200_dense_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd
   CNMF_CHECK_ARG(lda >= Kd && ldf >= Kd && lds >= M, "dense_half_step: leading dimension too small");
   return launch_tc_half_step(A, lda, M, Kd, F, ldf, state, state_tf32, lds, gram, active, R, Kp, algo, l1, l2, eps,
                              partials, (cudaStream_t)stream);
+}
+
+/* cnmf_b200_dense_half_step for a stack that holds several K padded to one Kp: rep_k[r] (device, [R]) is the true K of
+ * replicate r (Kp-3 .. Kp); the epilogue updates, loads and stores that many components (rows beyond stay zero). */
+int cnmf_b200_dense_half_step_k(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                                float* state, float* state_tf32, int64_t lds, const float* gram,
+                                const uint8_t* active, const uint8_t* rep_k, int32_t R, int32_t Kp, int32_t algo,
+                                float l1, float l2, float eps, double* partials, void* stream) {
+  CNMF_CHECK_ARG(A && F && state && gram, "dense_half_step_k: null pointer");
+  CNMF_CHECK_ARG(M > 0 && Kd > 0 && R > 0, "dense_half_step_k: empty shape");
+  CNMF_CHECK_ARG(lda % 4 == 0 && ldf % 4 == 0 && aligned16(A) && aligned16(F),
+                 "dense_half_step_k: operands need 16-byte aligned rows (ld multiple of 4)");
+  CNMF_CHECK_ARG(lda >= Kd && ldf >= Kd && lds >= M, "dense_half_step_k: leading dimension too small");
+  return launch_tc_half_step_g(A, lda, M, Kd, F, ldf, state, state_tf32, lds, gram, 0, active, R, Kp, algo, l1, l2, eps,
+                               partials, (cudaStream_t)stream, rep_k);
 }
 
 }  // extern "C"

@@ -20,7 +20,7 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st);
+                          double* partials, cudaStream_t st, const uint8_t* rep_k = nullptr);
 int gram_num_tiles(int64_t L, int Kp);
 int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st);
 int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cudaStream_t st);
@@ -205,15 +205,15 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
       // that consumes a Gram sums them in its (otherwise idle) epilogue warps.
       if (it == 0)
         CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh, p->gramW, 0, p->active,
-                                       p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st));
+                                       p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st, p->rep_k));
       else
         CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh,
                                        reinterpret_cast<const float*>(gws2), ntW, p->active, p->R, p->Kp, p->algo,
-                                       p->l1_H, p->l2_H, p->eps, pH, st));
+                                       p->l1_H, p->l2_H, p->eps, pH, st, p->rep_k));
       CNMF_TRY(launch_gram_partial(p->Ht, p->ldh, p->R, p->Kp, N, gws, st));
       CNMF_TRY(launch_tc_half_step_g(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, Wop, p->ldw,
                                      reinterpret_cast<const float*>(gws), ntH, p->active, p->R, p->Kp, p->algo,
-                                     p->l1_W, p->l2_W, p->eps, pW, st));
+                                     p->l1_W, p->l2_W, p->eps, pW, st, p->rep_k));
       CNMF_TRY(launch_gram_partial(p->Wall, p->ldw, p->R, p->Kp, G, gws2, st));
       if (it == n_iters - 1) {  // leave both Grams in their final form (objective, next call, API contract)
         CNMF_TRY(launch_gram_final(gws, N, p->R, p->Kp, p->gramH, st));

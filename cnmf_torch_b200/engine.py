@@ -515,12 +515,16 @@ class FrobBatch:
         self.gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
         self.active = torch.ones(R, device=dev, dtype=torch.uint8)
         self.err2 = torch.zeros(R, device=dev, dtype=torch.float64)
+        # the true K of every replicate of a mixed-K stack: the tensor-core epilogue works on those components only
+        self.rep_k = None
+        if any(k != Kp for k in self.Ks):
+            self.rep_k = torch.from_numpy(np.repeat(np.asarray(self.Ks, dtype=np.uint8), self.Rs)).to(dev)
         self.p = FrobProblem(
             n_cells=eng.N, n_genes=eng.G, X=ptr(eng.X), ldx=eng.ldx, Xt=ptr(eng.Xt), ldxt=eng.ldxt,
             R=R, K=self.K, Kp=Kp, algo=algo_id, impl=eng.impl, Wall=ptr(self.Wall), ldw=ldw,
             Ht=ptr(self.Ht), ldh=ldh, gramW=ptr(self.gramW), gramH=ptr(self.gramH),
             active=ptr(self.active), l1_H=l1_H, l2_H=l2_H, l1_W=l1_W, l2_W=l2_W, eps=eps,
-            normX2=eng.normX2, err2=ptr(self.err2))
+            normX2=eng.normX2, err2=ptr(self.err2), rep_k=ptr(self.rep_k))
         nbytes = check(eng.lib.cnmf_b200_frob_workspace_bytes(C.byref(self.p)), "frob_workspace_bytes")
         self.ws = torch.empty(max(int(nbytes), 256), device=dev, dtype=torch.uint8)
         self.p.workspace, self.p.workspace_bytes = ptr(self.ws), self.ws.numel()

@@ -123,6 +123,13 @@ int cnmf_b200_dense_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd
                               int32_t algo, float l1, float l2, float eps, double* partials,
                               void* stream);
 
+/* The same for a stack of several K padded to one Kp: rep_k[r] (device, [R]) is the true K of replicate r
+ * (Kp-3 <= rep_k[r] <= Kp, the rows beyond are zero and stay zero); the epilogue works on rep_k[r] components only. */
+int cnmf_b200_dense_half_step_k(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
+                                float* state, float* state_tf32, int64_t lds, const float* gram,
+                                const uint8_t* active, const uint8_t* rep_k, int32_t R, int32_t Kp, int32_t algo,
+                                float l1, float l2, float eps, double* partials, void* stream);
+
 typedef struct cnmf_b200_frob_problem {
   int64_t n_cells;   /* N */
   int64_t n_genes;   /* G */
@@ -150,6 +157,9 @@ typedef struct cnmf_b200_frob_problem {
   double* err2;      /* [R] out: 2 * objective = ||X - H W||_F^2 + regularisation (may be NULL) */
   void* workspace;
   int64_t workspace_bytes;
+  const uint8_t* rep_k;  /* [R] device: the true K of every replicate when a stack holds several K padded to one Kp
+                            (Kp-3 <= rep_k[r] <= Kp; rows rep_k[r]..Kp-1 of the replicate are zero); NULL = all K.
+                            The tensor-core epilogue then updates, loads and stores rep_k[r] components only. */
 } cnmf_b200_frob_problem;
 
 /* 'random' init of R replicates of one K, drawn on the device into the stacked layout:

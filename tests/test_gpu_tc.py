@@ -199,3 +199,43 @@ def test_factorize_many_stacks_match_single_k_runs(problem, algo):
         n = len(one.trace)
         assert [it for it, _ in many[k].trace][:n] == [it for it, _ in one.trace]
         np.testing.assert_allclose(many[k].trace[n - 1][1], one.trace[n - 1][1], rtol=1e-6)
+
+
+@pytest.mark.parametrize("algo", ["mu", "hals"])
+def test_exact_k_epilogue_is_bit_identical_to_the_padded_one(algo):
+    """A stack of K = 9..12 padded to Kp = 12: with rep_k the epilogue updates, loads and stores only each replicate's
+    own K components (cnmf_b200_dense_half_step_k); the padded components are exact zeros, so the result must be
+    bit-identical to the run over all Kp components, and the padding rows must still be zero."""
+    from cnmf_torch_b200 import _lib as L
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine, FrobBatch
+    from cnmf_torch_b200.synth import nb_counts
+    lib = L.lib()
+    x = nb_counts(700, 420, k_true=8, seed=14, libsize=900.0)
+    eng = DenseFrobeniusEngine(x)
+    groups = [(k,) + tuple(eng.make_init(k, [10 * k + i for i in range(5)])) for k in (9, 10, 11, 12)]
+    b = FrobBatch(eng, None, None, None, algo, 0.01, 0.02, 0.0, 0.0, 1e-16, groups=groups)
+    assert b.rep_k is not None and b.rep_k.tolist() == [9] * 5 + [10] * 5 + [11] * 5 + [12] * 5
+    p = b.p
+    st = torch.cuda.current_stream().cuda_stream
+    Wop = b.Wall.clone()
+    L.check(lib.cnmf_b200_round_tf32(Wop.data_ptr(), Wop.numel(), st))
+    outs = []
+    for with_k in (False, True):
+        Hs, Hop = b.Ht.clone(), torch.zeros_like(b.Ht)
+        part = torch.zeros(64 * b.R * 2, dtype=torch.float64, device="cuda")
+        if with_k:
+            L.check(lib.cnmf_b200_dense_half_step_k(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, Hs.data_ptr(),
+                                                    Hop.data_ptr(), p.ldh, p.gramW, None, b.rep_k.data_ptr(), p.R, p.Kp,
+                                                    p.algo, 0.01, 0.02, p.eps, part.data_ptr(), st))
+        else:
+            L.check(lib.cnmf_b200_dense_half_step(p.X, p.ldx, p.n_cells, p.n_genes, Wop.data_ptr(), p.ldw, Hs.data_ptr(),
+                                                  Hop.data_ptr(), p.ldh, p.gramW, None, p.R, p.Kp, p.algo, 0.01, 0.02,
+                                                  p.eps, part.data_ptr(), st))
+        torch.cuda.synchronize()
+        outs.append((Hs, Hop, part))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    torch.testing.assert_close(outs[0][2], outs[1][2], rtol=1e-12, atol=0)
+    Hs = outs[1][0].view(b.R, b.Kp, -1)
+    assert not torch.equal(Hs, b.Ht.view(b.R, b.Kp, -1))             # the step really changed the state
+    for r, k in enumerate(b.rep_k.tolist()):
+        assert torch.all(Hs[r, k:] == 0)
