@@ -63,6 +63,8 @@ struct TcParams {
   int gram_ntile;
   const uint8_t* active;  // [R] or null
   const uint8_t* rep_k;   // [R] true K of every replicate (KP-3 .. KP), or null: all KP
+  float* state_lo;        // same layout as state_op: tf32(state - tf32(state)), the part the operand copy drops (may be null)
+  int npass;              // 1, or 2: second pass of the k loop over the operand of tensor map B2
   double* partials;       // [num_m_tiles x R x 2]
   int R;
   int t;  // replicates per tile
@@ -247,7 +249,7 @@ struct TcWork {
 template <int KP, int ALGO, int CG, bool SUMS>
 __global__ void __launch_bounds__(tc_threads(KP), 1)
 tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                    const TcParams prm) {
+                    const __grid_constant__ CUtensorMap tmB2, const TcParams prm) {
   extern __shared__ uint8_t smem_raw[];
   // 1024-byte alignment by pointer arithmetic ON the __shared__ array: a round trip through uintptr_t loses the
   // address space and every later access (the Gram reads of the epilogue) becomes a generic LD.E instead of LDS
@@ -276,6 +278,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmA)) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB)) : "memory");
+    if (prm.npass > 1) asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(&tmB2)) : "memory");
   }
   if (warp == 1 && lane == 0) {
     for (int i = 0; i < stages; ++i) {
@@ -318,7 +321,11 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
     while (work.next(tile)) {
       const int m_group = tile / prm.num_n_tiles, n_tile = tile - m_group * prm.num_n_tiles;
       const int m_tile = m_group * CG + static_cast<int>(cta_rank);
-      for (int kb = 0; kb < num_kb; ++kb) {
+      // npass = 2: the k loop runs twice, the second time over a second fixed-factor operand (the tf32 residual of the
+      // first): the accumulator then holds A (F + F2)^T, the product with the factor to ~2^-22
+      for (int kk = 0; kk < prm.npass * num_kb; ++kk) {
+        const int kb = kk < num_kb ? kk : kk - num_kb;
+        const CUtensorMap* mapB = kk < num_kb ? &tmB : &tmB2;
         mbar_wait(&empty[stage], phase ^ 1u);
         if (elect_one()) {
           uint8_t* sa = smem + static_cast<size_t>(stage) * stage_bytes;
@@ -327,14 +334,14 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
           } else if (CG == 2) {
             if (leader) mbar_expect_tx(&full[stage], 2u * stage_bytes);  // both CTAs' bytes land on the leader
             tma_load_2d_pair(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
-            tma_load_2d_pair(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK,
+            tma_load_2d_pair(sa + TC_A_BYTES, mapB, &full[stage], kb * TC_BK,
                              n_tile * BN + static_cast<int>(cta_rank) * (BN / 2));
           } else if (prm.dbg & 2) {
             mbar_arrive(&full[stage]);
           } else {
             mbar_expect_tx(&full[stage], stage_bytes);
             tma_load_2d(sa, &tmA, &full[stage], kb * TC_BK, m_tile * TC_BM);
-            tma_load_2d(sa + TC_A_BYTES, &tmB, &full[stage], kb * TC_BK, n_tile * BN);
+            tma_load_2d(sa + TC_A_BYTES, mapB, &full[stage], kb * TC_BK, n_tile * BN);
           }
         }
         __syncwarp();
@@ -359,7 +366,7 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
         mbar_wait(&tempty[buf], tphase ^ 1u);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + static_cast<uint32_t>(buf * TC_MAX_BN);
-        for (int kb = 0; kb < num_kb; ++kb) {
+        for (int kb = 0; kb < prm.npass * num_kb; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           if (elect_one()) {
@@ -514,6 +521,11 @@ tc_half_step_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_consta
                   float* op = prm.state_op + soff;
 #pragma unroll
                   for (int k = 0; k < KE; ++k) op[static_cast<int64_t>(k) * prm.lds] = to_tf32(s[k]);
+                  if (prm.state_lo != nullptr) {
+                    float* lo = prm.state_lo + soff;
+#pragma unroll
+                    for (int k = 0; k < KE; ++k) lo[static_cast<int64_t>(k) * prm.lds] = to_tf32(s[k] - to_tf32(s[k]));
+                  }
                 }
               }
               if (want_sums) {
@@ -765,7 +777,7 @@ static int get_tensor_map(const float* ptr, int64_t rows, int64_t cols, int64_t 
 }
 
 template <int KP, int ALGO, int CG, bool SUMS>
-static int launch_tc_inst3(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
+static int launch_tc_inst3(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mb2, const TcParams& prm, const TcPlan& plan,
                            int grid, cudaStream_t st) {
   static unsigned long long configured = 0;  // per-device bit mask (benign race: setting twice is harmless)
   auto kern = tc_half_step_kernel<KP, ALGO, CG, SUMS>;
@@ -783,29 +795,30 @@ static int launch_tc_inst3(const CUtensorMap& ma, const CUtensorMap& mb, const T
   attr[0].val.clusterDim.z = 1;
   cfg.attrs = attr;
   cfg.numAttrs = 1;
-  CNMF_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, prm));
+  CNMF_CUDA(cudaLaunchKernelEx(&cfg, kern, ma, mb, mb2, prm));
   count_launch();
   return 0;
 }
 
 template <int KP, int ALGO, int CG>
-static int launch_tc_inst2(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
+static int launch_tc_inst2(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mb2, const TcParams& prm, const TcPlan& plan,
                            int grid, cudaStream_t st) {
-  if (ALGO < TC_MODE_STORE && prm.partials != nullptr) return launch_tc_inst3<KP, ALGO, CG, true>(ma, mb, prm, plan, grid, st);
-  return launch_tc_inst3<KP, ALGO, CG, false>(ma, mb, prm, plan, grid, st);
+  if (ALGO < TC_MODE_STORE && prm.partials != nullptr) return launch_tc_inst3<KP, ALGO, CG, true>(ma, mb, mb2, prm, plan, grid, st);
+  return launch_tc_inst3<KP, ALGO, CG, false>(ma, mb, mb2, prm, plan, grid, st);
 }
 
 template <int KP, int ALGO>
-static int launch_tc_inst(const CUtensorMap& ma, const CUtensorMap& mb, const TcParams& prm, const TcPlan& plan,
+static int launch_tc_inst(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& mb2, const TcParams& prm, const TcPlan& plan,
                           int grid, cudaStream_t st) {
-  if (plan.cg == 2) return launch_tc_inst2<KP, ALGO, 2>(ma, mb, prm, plan, grid, st);
-  return launch_tc_inst2<KP, ALGO, 1>(ma, mb, prm, plan, grid, st);
+  if (plan.cg == 2) return launch_tc_inst2<KP, ALGO, 2>(ma, mb, mb2, prm, plan, grid, st);
+  return launch_tc_inst2<KP, ALGO, 1>(ma, mb, mb2, prm, plan, grid, st);
 }
 
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st, const uint8_t* rep_k = nullptr);
+                          double* partials, cudaStream_t st, const uint8_t* rep_k = nullptr, const float* F2 = nullptr,
+                          float* state_lo = nullptr);
 
 int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                         float* state, float* state_op, int64_t lds, const float* gram, const uint8_t* active, int R,
@@ -818,7 +831,7 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st, const uint8_t* rep_k) {
+                          double* partials, cudaStream_t st, const uint8_t* rep_k, const float* F2, float* state_lo) {
   TcPlan plan;
   const int sms = tc_num_sms();
   if (!tc_plan(M, Kd, R, Kp, sms, &plan)) {
@@ -828,8 +841,10 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
   CUtensorMap ma, mb;
   CNMF_TRY(get_tensor_map(A, M, Kd, lda, TC_BM, &ma));
   CNMF_TRY(get_tensor_map(F, static_cast<int64_t>(R) * Kp, Kd, ldf, plan.BN / plan.cg, &mb));
+  CUtensorMap mb2 = mb;   // second fixed-factor operand (F2: the tf32 residual of F): the k loop then runs over both
+  if (F2 != nullptr) CNMF_TRY(get_tensor_map(F2, static_cast<int64_t>(R) * Kp, Kd, ldf, plan.BN / plan.cg, &mb2));
   TcParams prm;
-  prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.gram_ntile = gram_ntile; prm.active = active; prm.rep_k = rep_k;
+  prm.M = M; prm.Kd = Kd; prm.state = state; prm.state_op = state_op; prm.lds = lds; prm.gram = gram; prm.gram_ntile = gram_ntile; prm.active = active; prm.rep_k = rep_k; prm.state_lo = state_lo; prm.npass = F2 != nullptr ? 2 : 1;
   prm.partials = partials; prm.R = R; prm.t = plan.t; prm.num_m_tiles = plan.num_m_tiles; prm.num_m_groups = plan.num_m_groups;
   prm.num_n_tiles = plan.num_n_tiles; prm.stages = plan.stages; prm.l1 = l1; prm.l2 = l2; prm.eps = eps;
   static const int dbg = [] { const char* e = getenv("CNMF_B200_TC_DEBUG"); return e ? atoi(e) : 0; }();
@@ -840,13 +855,13 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
   const int64_t slots = sms / plan.cg;
   const int grid = static_cast<int>((tiles < slots ? tiles : slots) * plan.cg);
   if (algo == CNMF_B200_ALGO_MU) {
-    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_MU>(ma, mb, prm, plan, grid, st)));
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_MU>(ma, mb, mb2, prm, plan, grid, st)));
   } else if (algo == CNMF_B200_ALGO_HALS) {
-    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_HALS>(ma, mb, prm, plan, grid, st)));
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, CNMF_B200_ALGO_HALS>(ma, mb, mb2, prm, plan, grid, st)));
   } else if (algo == TC_MODE_STORE) {
-    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, TC_MODE_STORE>(ma, mb, prm, plan, grid, st)));
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, TC_MODE_STORE>(ma, mb, mb2, prm, plan, grid, st)));
   } else if (algo == TC_MODE_ACCUM) {
-    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, TC_MODE_ACCUM>(ma, mb, prm, plan, grid, st)));
+    CNMF_DISPATCH_KP(Kp, return (launch_tc_inst<KP, TC_MODE_ACCUM>(ma, mb, mb2, prm, plan, grid, st)));
   }
   set_error("unknown algo %d", algo);
   return CNMF_B200_ERR_INVALID;

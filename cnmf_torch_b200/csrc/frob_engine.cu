@@ -20,7 +20,8 @@ int launch_tc_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd, cons
 int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
-                          double* partials, cudaStream_t st, const uint8_t* rep_k = nullptr);
+                          double* partials, cudaStream_t st, const uint8_t* rep_k = nullptr, const float* F2 = nullptr,
+                          float* state_lo = nullptr);
 int gram_num_tiles(int64_t L, int Kp);
 int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st);
 int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cudaStream_t st);
@@ -203,17 +204,23 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
     } else {
       // tcgen05 path: 4 launches per iteration.  The Gram kernels leave per-tile partials; the half-step
       // that consumes a Gram sums them in its (otherwise idle) epilogue warps.
+      // On the iteration whose objective is read, the H half-step also leaves Hlo = tf32(H - tf32 H) and the W
+      // half-step runs its k loop over both operand copies: Q = X^T (tf32 H + Hlo) is then X^T H to ~2^-22, so the
+      // cross term <W, Q> of the objective is that of the fp32 factors (a tf32-only Q gives +-2.5e-5 evaluation
+      // noise, enough to trip run_nmf's "prev <= cur" stop early) -- without the separate residual kernel and frozen
+      // pass over X that round 1 spent on it (6 % of a 10-iteration step).
+      float* Hlo = last ? reinterpret_cast<float*>(ws + l.off_hlo) : nullptr;
       if (it == 0)
         CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh, p->gramW, 0, p->active,
-                                       p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st, p->rep_k));
+                                       p->R, p->Kp, p->algo, p->l1_H, p->l2_H, p->eps, pH, st, p->rep_k, nullptr, Hlo));
       else
         CNMF_TRY(launch_tc_half_step_g(p->X, p->ldx, N, G, Wop, p->ldw, p->Ht, Hop, p->ldh,
                                        reinterpret_cast<const float*>(gws2), ntW, p->active, p->R, p->Kp, p->algo,
-                                       p->l1_H, p->l2_H, p->eps, pH, st, p->rep_k));
+                                       p->l1_H, p->l2_H, p->eps, pH, st, p->rep_k, nullptr, Hlo));
       CNMF_TRY(launch_gram_partial(p->Ht, p->ldh, p->R, p->Kp, N, gws, st));
       CNMF_TRY(launch_tc_half_step_g(p->Xt, p->ldxt, G, N, Hop, p->ldh, p->Wall, Wop, p->ldw,
                                      reinterpret_cast<const float*>(gws), ntH, p->active, p->R, p->Kp, p->algo,
-                                     p->l1_W, p->l2_W, p->eps, pW, st, p->rep_k));
+                                     p->l1_W, p->l2_W, p->eps, pW, st, p->rep_k, Hlo, nullptr));
       CNMF_TRY(launch_gram_partial(p->Wall, p->ldw, p->R, p->Kp, G, gws2, st));
       if (it == n_iters - 1) {  // leave both Grams in their final form (objective, next call, API contract)
         CNMF_TRY(launch_gram_final(gws, N, p->R, p->Kp, p->gramH, st));
@@ -222,7 +229,6 @@ int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, voi
     }
   }
   if (p->err2 != nullptr && n_iters > 0) {
-    if (l.impl == CNMF_B200_IMPL_TCGEN05) CNMF_TRY(tc_cross_residual(p, l, st));
     CNMF_TRY(launch_frob_objective(p->normX2, partW, l.nblkW, partH, l.nblkH, p->gramW, p->gramH, p->R,
                                    p->Kp, p->l1_H, p->l2_H, p->l1_W, p->l2_W, p->err2, st));
   }
