@@ -33,6 +33,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "kl_fhfma.cuh"
 #include "kl_slab.cuh"
 #include "kl_tables.cuh"
 
@@ -50,31 +51,6 @@ struct SlabCfg {
 
 __host__ __device__ static inline int ks_rgp(int Kp) { return 16 / (Kp / 2); }
 
-// ---- fp16 x fp16 + fp32 (FHFMA) on packed words ---------------------------------------------------------------
-__device__ __forceinline__ float fhfma_lo(uint32_t a, uint32_t b, float c) {
-  asm("{\n\t.reg .b16 al, ah, bl, bh;\n\tmov.b32 {al, ah}, %1;\n\tmov.b32 {bl, bh}, %2;\n\t"
-      "fma.rn.f32.f16 %0, al, bl, %0;\n\t}" : "+f"(c) : "r"(a), "r"(b));
-  return c;
-}
-__device__ __forceinline__ float fhfma_hi(uint32_t a, uint32_t b, float c) {
-  asm("{\n\t.reg .b16 al, ah, bl, bh;\n\tmov.b32 {al, ah}, %1;\n\tmov.b32 {bl, bh}, %2;\n\t"
-      "fma.rn.f32.f16 %0, ah, bh, %0;\n\t}" : "+f"(c) : "r"(a), "r"(b));
-  return c;
-}
-// q (a .b16 register holding one fp16) x low / high half of w
-__device__ __forceinline__ float fhfma_q_lo(uint16_t q, uint32_t w, float c) {
-  asm("{\n\t.reg .b16 wl, wh;\n\tmov.b32 {wl, wh}, %2;\n\tfma.rn.f32.f16 %0, %1, wl, %0;\n\t}" : "+f"(c) : "h"(q), "r"(w));
-  return c;
-}
-__device__ __forceinline__ float fhfma_q_hi(uint16_t q, uint32_t w, float c) {
-  asm("{\n\t.reg .b16 wl, wh;\n\tmov.b32 {wl, wh}, %2;\n\tfma.rn.f32.f16 %0, %1, wh, %0;\n\t}" : "+f"(c) : "h"(q), "r"(w));
-  return c;
-}
-__device__ __forceinline__ uint16_t f32_to_f16_bits(float v) {
-  uint16_t h;
-  asm("cvt.rn.f16.f32 %0, %1;" : "=h"(h) : "f"(v));   // overflow -> inf (caught when the factor is written)
-  return h;
-}
 __device__ __forceinline__ uint2 lds64(uint32_t addr) {
   uint2 v;
   asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
