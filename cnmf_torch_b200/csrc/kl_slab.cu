@@ -56,23 +56,30 @@ __device__ __forceinline__ uint2 lds64(uint32_t addr) {
   asm volatile("ld.shared.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "r"(addr));
   return v;
 }
-// col/val of one entry into existing registers, only where `ok` (the registers keep their value elsewhere)
-__device__ __forceinline__ void ldg_pred(int& j, float& x, const int* cp, const float* xp, bool ok) {
-  asm volatile("{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t@p ld.global.nc.b32 %0, [%2];\n\t@p ld.global.nc.f32 %1, [%3];\n\t}"
-               : "+r"(j), "+f"(x) : "l"(cp), "l"(xp), "r"((int)ok));
-}
-__device__ __forceinline__ void cp_async4(uint32_t dst, const void* src) {
-  asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(dst), "l"(src) : "memory");
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
-__device__ __forceinline__ void sts64(uint32_t addr, uint32_t a, uint32_t b) {
-  asm volatile("st.shared.v2.u32 [%0], {%1, %2};" ::"r"(addr), "r"(a), "r"(b) : "memory");
-}
 __device__ __forceinline__ float fast_rcp(float v) {
   float r;
   asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(v));
   return r;
+}
+// mbarrier + bulk-copy wrappers (shared::cta addresses)
+__device__ __forceinline__ void ks_bar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void ks_bar_expect(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void ks_bar_wait(uint32_t bar, uint32_t parity) {   // bounded: a protocol bug traps
+  uint32_t ok = 0, spins = 0;
+  while (true) {
+    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (ok) break;
+    if (++spins > (1u << 28)) __trap();
+  }
+}
+__device__ __forceinline__ void ks_bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+               ::"r"(dst), "l"(src), "r"(bytes), "r"(bar) : "memory");
 }
 
 // first index i in [0, n] with a[i] >= key (a non-decreasing, a[n] = total)
@@ -91,9 +98,12 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
   using Cfg = SlabCfg<KP>;
   constexpr int P = Cfg::P, RGP = Cfg::RGP, A = Cfg::A, LANES = Cfg::LANES;
   constexpr int LINE_WORDS = RGP * P;
-  constexpr int CH = (KS_CHUNK / (2 * A)) * (2 * A);   // entries per staged chunk: whole steps
+  constexpr int STEP_BYTES = 2 * A * 8;                      // (column, value) pairs of one warp step
+  constexpr int CHS = KS_CHUNK_BYTES / STEP_BYTES;           // steps per staged chunk
+  static_assert(CHS >= 1 && STEP_BYTES % 16 == 0, "a chunk holds whole steps; bulk copies move multiples of 16 bytes");
   extern __shared__ __align__(128) unsigned char slab[];
   __shared__ double s_obj[KS_WARPS][2 * RGP];
+  __shared__ __align__(8) uint64_t s_bar[KS_WARPS][KS_RING];
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, hw = lane >> 4, li = lane & 15;
   const bool lane_on = li < LANES;
@@ -105,7 +115,15 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
   const int64_t lo = T * blockIdx.x / gridDim.x, hi = T * (blockIdx.x + 1) / gridDim.x;
 
   const uint32_t slab_u32 = static_cast<uint32_t>(__cvta_generic_to_shared(slab));
-  const uint32_t stage_u32 = slab_u32 + (uint32_t)a.block * KS_LINE;   // per-warp (column, value) staging, after the lines
+  // per-warp ring of staging chunks, after the lines
+  const uint32_t stg = slab_u32 + (uint32_t)a.block * KS_LINE + (uint32_t)warp * (KS_RING * KS_CHUNK_BYTES);
+  const uint32_t bar0 = static_cast<uint32_t>(__cvta_generic_to_shared(&s_bar[warp][0]));
+  if (lane < KS_RING) ks_bar_init(bar0 + 8u * lane, 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  __syncthreads();
+  int fill_buf = 0, use_buf = 0;      // ring positions of the next chunk to request / to consume
+  uint32_t use_par = 0;               // parity of the barrier phase the next consumed chunk completes
+
   uint32_t loff[P];   // byte offset of this lane's m-th load inside a line; word index (m + a) mod P of pair rp
   int hoff[P];        // the same word index for the moving factor's row (in 8-byte words)
 #pragma unroll
@@ -117,6 +135,7 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
     loff[m] = lane_on ? (uint32_t)hoff[m] * 8u : (uint32_t)li * 8u;
   }
   const int64_t rkp = (int64_t)a.R * KP;
+  const uint32_t lane_entry = (uint32_t)(hw * A + aslot) * 8u;   // this lane's entry inside a step's 2A entries
 
   int64_t pos = lo;
   while (pos < hi && W > 0) {
@@ -154,80 +173,98 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
         if (slot < npair * P) v = a.F16[((int64_t)(c0 + line) * a.RP + rp0) * P + slot];
         *reinterpret_cast<uint2*>(slab + line * KS_LINE + slot * 8) = v;
       }
+
+      // The phase's segments [s, sb_end) are dealt to the warps as 16 CONTIGUOUS runs of equal weight, so that a
+      // warp's (column, value) pairs -- stored per segment, padded to whole steps, in segment order -- are one
+      // contiguous stream: it comes in as bulk copies of whole chunks (one instruction of one lane per KB, completion
+      // on an mbarrier), KS_RING chunks ahead of the arithmetic, with no regard for segment boundaries.  (The
+      // version before this one staged each segment's entries with 4-byte cp.async copies: ~100 instructions of
+      // address arithmetic per chunk, a third of all instructions issued.)
+      int bound = 0;
+      if (lane <= KS_WARPS) {
+        const int64_t w0 = a.wcum[s], w1 = a.wcum[sb_end];
+        bound = s + ks_lower_bound(a.wcum + s, sb_end - s, w0 + (w1 - w0) * lane / KS_WARPS);
+      }
+      const int ws = __shfl_sync(0xffffffffu, bound, warp), we = __shfl_sync(0xffffffffu, bound, warp + 1);
+      // stream of this warp, in steps of the pair table: a segment's first step is wcum[seg] - overhead * seg
+      int64_t st_pos = 0;
+      int st_left = 0;                 // steps not yet requested
+      if (ws < we) {
+        st_pos = (int64_t)a.wcum[ws] - (int64_t)KS_SEG_OVERHEAD_STEPS * ws;
+        st_left = (int)((int64_t)a.wcum[we] - (int64_t)KS_SEG_OVERHEAD_STEPS * we - st_pos);
+      }
+      auto request_chunk = [&]() {     // the next chunk of the stream into ring slot fill_buf (all lanes call)
+        const int n = st_left < CHS ? st_left : CHS;
+        if (lane == 0) {
+          const uint32_t bar = bar0 + 8u * fill_buf;
+          ks_bar_expect(bar, (uint32_t)n * STEP_BYTES);
+          ks_bulk_load(stg + (uint32_t)fill_buf * KS_CHUNK_BYTES, a.pairs + st_pos * (2 * A), (uint32_t)n * STEP_BYTES, bar);
+        }
+        st_pos += n;
+        st_left -= n;
+        fill_buf = fill_buf + 1 == KS_RING ? 0 : fill_buf + 1;
+      };
+      int use_left = st_left;          // steps not yet consumed
+#pragma unroll 1
+      for (int i = 0; i < KS_RING && st_left > 0; ++i) request_chunk();
       __syncthreads();   // the slab is complete
 
-      // Segments of this phase go round the warps (fixed assignment, so what comes next is known in advance).  The
-      // (column, value) pairs of a segment are brought into a per-warp staging buffer by cp.async, a chunk of KS_CHUNK
-      // entries ahead of the arithmetic -- asynchronous copies do not occupy scoreboard slots, which the register
-      // prefetch of the first version kept running out of (a load waited for at the first use of the index, with 16
-      // warps per SM to hide it).  Table entries are fetched two segments ahead, the row of the moving factor one.
-      auto load_meta = [&](int sgi, int& row, int& beg, int& end) {
-        const int v = a.seg_vrow[sgi];
-        row = v - b * M;
-        beg = a.seg_beg[sgi];
-        const int ve = a.vend[v];
-        end = beg + a.seg_len < ve ? beg + a.seg_len : ve;
-      };
       auto load_h = [&](int row, uint2 (&h)[P]) {   // this row of the moving factor, rotated like the gathered operand
         const uint2* hp = a.S16 + ((int64_t)row * a.RP + rp0) * P;
 #pragma unroll
         for (int m = 0; m < P; ++m) h[m] = pair_on ? __ldg(hp + hoff[m]) : make_uint2(0u, 0u);
       };
-      const uint32_t stg = stage_u32 + (uint32_t)warp * (2u * KS_CHUNK * 8u);
-      auto issue_chunk = [&](int buf, int cbeg, int cend) {   // entries cbeg.. of the CSR arrays; past cend: (c0, 0)
-        int need = cend - cbeg;
-        need = need > CH ? CH : (need + 2 * A - 1) / (2 * A) * (2 * A);
-        for (int e = lane; e < need; e += 32) {
-          const uint32_t dst = stg + (uint32_t)(buf * KS_CHUNK + e) * 8u;
-          const int idx = cbeg + e;
-          if (idx < cend) {
-            cp_async4(dst, a.col_idx + idx);
-            cp_async4(dst + 4u, a.val + idx);
-          } else {
-            sts64(dst, (uint32_t)c0, 0u);
-          }
-        }
-        cp_async_commit();
-      };
-      const uint32_t lane_entry = (uint32_t)(hw * A + aslot) * 8u;   // this lane's entry inside a step's 2A entries
 
-      int sg = s + warp;
-      int row = 0, beg = 0, end = 0, nrow = 0, nbeg = 0, nend = 0, n2row = 0, n2beg = 0, n2end = 0;
+      int sg = ws;
+      int row = 0, steps = 0, nrow = 0, nsteps = 0, wc = 0;
       uint2 hreg[P], hnext[P];
-      int buf = 0;
-      if (sg < sb_end) {
-        load_meta(sg, row, beg, end);
+      if (sg < we) {
+        row = a.seg_vrow[sg] - b * M;
+        wc = a.wcum[sg + 1];
+        steps = wc - a.wcum[sg] - KS_SEG_OVERHEAD_STEPS;
         load_h(row, hreg);
-        issue_chunk(0, beg, end);
-        if (sg + KS_WARPS < sb_end) load_meta(sg + KS_WARPS, nrow, nbeg, nend);
       }
-      while (sg < sb_end) {
-        const int nsg = sg + KS_WARPS;
-        const bool has_next = nsg < sb_end;
-        if (nsg + KS_WARPS < sb_end) load_meta(nsg + KS_WARPS, n2row, n2beg, n2end);
+      int chunk_left = 0;              // steps left in the chunk being consumed
+      bool first_chunk = true;
+      uint32_t ep = 0;
+      uint2 jx_next = make_uint2(0u, 0u);
+      while (sg < we) {
+        const bool has_next = sg + 1 < we;
+        if (has_next) {                // next segment's table entries and row of the factor, a segment ahead
+          nrow = a.seg_vrow[sg + 1] - b * M;
+          const int wc2 = a.wcum[sg + 2];
+          nsteps = wc2 - wc - KS_SEG_OVERHEAD_STEPS;
+          wc = wc2;
+          load_h(nrow, hnext);
+        }
         float n0[KP], n1[KP];   // n0[2m], n0[2m+1]: numerators of k-pair (m + a) mod P, replicate rep0
 #pragma unroll
         for (int k = 0; k < KP; ++k) { n0[k] = 0.f; n1[k] = 0.f; }
         float acc0 = 0.f, acc1 = 0.f;
 
-        for (int cb = beg; cb < end; cb += CH) {
-          cp_async_wait_all();
-          __syncwarp();
-          // the next chunk -- of this segment, or the first of the next one (and that segment's row of the factor)
-          if (cb + CH < end) {
-            issue_chunk(buf ^ 1, cb + CH, end);
-          } else if (has_next) {
-            issue_chunk(buf ^ 1, nbeg, nend);
-            load_h(nrow, hnext);
+        int seg_left = steps;
+        while (seg_left > 0) {
+          if (chunk_left == 0) {
+            if (!first_chunk) {        // the chunk just consumed: every lane has read it, its slot takes the next request
+              __syncwarp();
+              if (st_left > 0) request_chunk();
+            }
+            first_chunk = false;
+            ks_bar_wait(bar0 + 8u * use_buf, use_par);
+            chunk_left = use_left < CHS ? use_left : CHS;
+            use_left -= chunk_left;
+            ep = stg + (uint32_t)use_buf * KS_CHUNK_BYTES + lane_entry;
+            jx_next = lds64(ep);       // the step's (column, value) one step ahead of its use
+            if (++use_buf == KS_RING) { use_buf = 0; use_par ^= 1u; }
           }
-          const int cend = cb + CH < end ? cb + CH : end;
-          uint32_t ep = stg + (uint32_t)(buf * KS_CHUNK) * 8u + lane_entry;
-          uint2 jx_next = lds64(ep);   // the step's (column, value) one step ahead of its use: the line address is
-                                       // then ready when the step starts (one shared-memory latency less per step)
-          for (int p0 = cb; p0 < cend; p0 += 2 * A) {
+          const int n = seg_left < chunk_left ? seg_left : chunk_left;
+          seg_left -= n;
+          chunk_left -= n;
+#pragma unroll 1
+          for (int i = 0; i < n; ++i) {
             const uint2 jx = jx_next;                                     // (column, value bits); idle lanes: unused
-            ep += 2 * A * 8;
-            jx_next = lds64(ep);       // (past the chunk's last step: a stale slot of the staging area, never used)
+            ep += STEP_BYTES;
+            jx_next = lds64(ep);       // (past the chunk's last step: the next slot or the pad, never used)
             const uint32_t line = sbase + (lane_on ? (jx.x << 7) : ((uint32_t)c0 << 7));   // sbase = slab - c0 * 128
             const float x = lane_on ? __uint_as_float(jx.y) : 0.f;
             uint2 w[P];
@@ -253,16 +290,10 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
                 n1[2 * m + 1] = fhfma_q_hi(q1, w[m].y, n1[2 * m + 1]);
               }
             } else {
-              acc0 = fmaf(x, __log2f(s0), acc0);   // x = 0 on idle lanes and past the end
+              acc0 = fmaf(x, __log2f(s0), acc0);   // x = 0 on idle lanes and in the padding of a segment
               acc1 = fmaf(x, __log2f(s1), acc1);
             }
           }
-          buf ^= 1;
-        }
-        if (beg >= end && has_next) {   // (an empty segment cannot occur: segments are made from stored entries)
-          issue_chunk(buf ^ 1, nbeg, nend);
-          load_h(nrow, hnext);
-          buf ^= 1;
         }
 
         if (MODE == 0) {
@@ -293,12 +324,10 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
           dacc0 += (double)acc0;
           dacc1 += (double)acc1;
         }
-        sg = nsg; row = nrow; beg = nbeg; end = nend;
-        nrow = n2row; nbeg = n2beg; nend = n2end;
+        ++sg; row = nrow; steps = nsteps;
 #pragma unroll
         for (int m = 0; m < P; ++m) hreg[m] = hnext[m];
       }
-      cp_async_wait_all();   // nothing may still be writing the staging buffers when the next phase reuses them
       s = sb_end;
     }
 
@@ -320,6 +349,33 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
           a.opart[(int64_t)blockIdx.x * a.R + rep] = t * 0.6931471805599453;   // ln 2; a CTA meets a replicate once
         }
       }
+    }
+  }
+}
+
+// The pair table: segment s owns steps [wcum[s] - overhead * s, ...) of 2A = Kp entries each; its stored entries come
+// first, the rest of its last step is (first column of the block, 0) -- a line that exists, a value that adds nothing.
+__global__ void __launch_bounds__(256) kl_pack_pairs_kernel(const int* __restrict__ vseg_ptr, int64_t V, int64_t M,
+                                                            int block, const int* __restrict__ seg_vrow,
+                                                            const int* __restrict__ seg_beg, const int* __restrict__ vend,
+                                                            int seg_len, int step_entries, int c0steps,
+                                                            const int* __restrict__ col_idx, const float* __restrict__ val,
+                                                            const int* __restrict__ wcum, uint2* __restrict__ pairs) {
+  const int nseg = vseg_ptr[V];
+  const int lane = threadIdx.x & 31;
+  const int nw = gridDim.x * 8;
+  for (int s = blockIdx.x * 8 + (threadIdx.x >> 5); s < nseg; s += nw) {
+    const int v = seg_vrow[s];
+    const int beg = seg_beg[s];
+    int end = vend[v];
+    if (end > beg + seg_len) end = beg + seg_len;
+    const int w0 = wcum[s], w1 = wcum[s + 1];
+    const int n = (w1 - w0 - c0steps) * step_entries;
+    uint2* dst = pairs + ((int64_t)w0 - (int64_t)c0steps * s) * step_entries;
+    const uint32_t padcol = (uint32_t)((v / M) * block);
+    for (int e = lane; e < n; e += 32) {
+      const int idx = beg + e;
+      dst[e] = idx < end ? make_uint2((uint32_t)col_idx[idx], __float_as_uint(val[idx])) : make_uint2(padcol, 0u);
     }
   }
 }
@@ -452,6 +508,17 @@ int ks_seg_len(int Kp) {
 int launch_kl_work_scan(const KlSegs& sg, int64_t V, int Kp, int* wcum, cudaStream_t st) {
   kl_work_scan_kernel<<<1, 1024, 0, st>>>(sg.vseg_ptr, V, sg.seg_vrow, sg.seg_beg, sg.vend, sg.seg_len, 2 * (Kp / 2),
                                           KS_SEG_OVERHEAD_STEPS, wcum);
+  CNMF_LAUNCH_CHECK();
+  return 0;
+}
+
+int64_t ks_pairs_max(int64_t nnz, int64_t nseg_max, int Kp) { return nnz + nseg_max * (2 * (Kp / 2)); }
+
+int launch_kl_pack_pairs(const KlSegs& sg, int64_t V, int64_t M, int block, int Kp, const int* col_idx, const float* val,
+                         const int* wcum, void* pairs, cudaStream_t st) {
+  kl_pack_pairs_kernel<<<148 * 8, 256, 0, st>>>(sg.vseg_ptr, V, M, block > 0 ? block : 1, sg.seg_vrow, sg.seg_beg, sg.vend,
+                                                sg.seg_len, 2 * (Kp / 2), KS_SEG_OVERHEAD_STEPS, col_idx, val, wcum,
+                                                reinterpret_cast<uint2*>(pairs));
   CNMF_LAUNCH_CHECK();
   return 0;
 }

@@ -8,9 +8,10 @@ namespace cnmf {
 constexpr int KS_THREADS = 512;
 constexpr int KS_WARPS = KS_THREADS / 32;
 constexpr int KS_LINE = 128;               // bytes of shared memory per column of the block
-constexpr int KS_CHUNK = 128;              // entries per staging chunk (per warp, two buffers of (column, value))
-constexpr int KS_STAGE_BYTES = KS_WARPS * 2 * KS_CHUNK * 8 + 256;   // 32 KB (+ the one-step read-ahead past the last buffer)
-constexpr int KS_MAX_LINES = 1400;         // 175 KB slab + 32 KB staging + static: within 227 KB
+constexpr int KS_RING = 3;                 // staging chunks in flight per warp
+constexpr int KS_CHUNK_BYTES = 1024;       // one staging chunk: whole warp steps of (column, value) pairs, <= 1 KB
+constexpr int KS_STAGE_BYTES = KS_WARPS * KS_RING * KS_CHUNK_BYTES + 256;   // 48 KB (+ the one-step read-ahead past the last chunk)
+constexpr int KS_MAX_LINES = 1400;         // 175 KB slab + 48 KB staging + static (barriers, objective sums): within 227 KB
 constexpr int KS_SEG_LEN = 640;            // entries per segment (64 steps at Kp = 10)
 constexpr int KS_SEG_OVERHEAD_STEPS = 2;   // set-up + un-rotation of a segment, in steps, for the static work split
 
@@ -38,8 +39,8 @@ constexpr int KS_SEG_OVERHEAD_STEPS = 2;   // set-up + un-rotation of a segment,
   }
 
 struct KlSlabArgs {
-  const int* col_idx;      // CSR entries of the matrix whose rows are walked
-  const float* val;
+  const uint2* pairs;      // (column, value bits) of every segment, padded to whole warp steps, in segment order
+                           // (kl_pack_pairs_kernel): step t of the table is entries [t * Kp, (t + 1) * Kp)
   int M, C;                // rows; columns (= rows of the fixed factor)
   const uint2* F16;        // fixed factor, pair-interleaved fp16 [C][RP][P] x {rep0 pair, rep1 pair}
   const uint2* S16;        // moving factor (the rows being updated), same layout [M][RP][P]
@@ -62,6 +63,9 @@ int ks_seg_len(int Kp);                      // entries per segment: a whole num
 int ks_num_groups(int R, int Kp);
 int ks_sm_count();
 int launch_kl_work_scan(const KlSegs& sg, int64_t V, int Kp, int* wcum, cudaStream_t st);
+int64_t ks_pairs_max(int64_t nnz, int64_t nseg_max, int Kp);   // entries of the padded pair table, upper bound
+int launch_kl_pack_pairs(const KlSegs& sg, int64_t V, int64_t M, int block, int Kp, const int* col_idx, const float* val,
+                         const int* wcum, void* pairs, cudaStream_t st);
 int launch_kl_to_half_pairs(const float* src, void* dst, int64_t rows, int R, int Kp, int* flag, cudaStream_t st);
 int launch_kl_slab(const KlSlabArgs& a, int Kp, int mode, cudaStream_t st);
 int launch_kl_finish_slab(int64_t M, float* state, void* state16, const float* fsum, const uint8_t* active, int R, int Kp,

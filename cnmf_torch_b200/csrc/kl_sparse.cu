@@ -693,6 +693,7 @@ int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, char* w
 struct KlLayout {
   int64_t off_wsum, off_hsum, off_wsum64, off_hsum64, off_wsq64, off_hsq64, off_cpart, off_opart, off_wh, off_hh, off_part, total;
   int64_t off_flag, off_wcumX, off_wcumXt;   // slab path: range flag, static work split of the two matrices
+  int64_t off_pairsX, off_pairsXt;           // slab path: (column, value) pairs per segment, padded to whole steps
   KlSegLayout segX, segXt;  // CSR(X): never column-blocked (gathers W, G rows); CSR(X^T): blocked over cells when H is large
   int nblk_obj;
   bool slab;
@@ -726,6 +727,8 @@ static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
     const int64_t sx = kl_nseg_max(l.segX.V, p->nnz, l.segX.seg), sxt = kl_nseg_max(l.segXt.V, p->nnz, l.segXt.seg);
     l.off_wcumX = off; off += align_up((sx + 1) * 4, 256);
     l.off_wcumXt = off; off += align_up((sxt + 1) * 4, 256);
+    l.off_pairsX = off; off += align_up(ks_pairs_max(p->nnz, sx, p->Kp) * 8, 256);
+    l.off_pairsXt = off; off += align_up(ks_pairs_max(p->nnz, sxt, p->Kp) * 8, 256);
     l.off_part = off; off += align_up((sx > sxt ? sx : sxt) * C * 4, 256);
     l.total = off;
     return l;
@@ -775,8 +778,7 @@ static KlSlabArgs kl_slab_args(const cnmf_b200_kl_problem* p, const KlLayout& l,
   const uint2* H16 = reinterpret_cast<const uint2*>(ws + l.off_hh);
   const KlSegLayout& o = transposed ? l.segXt : l.segX;
   KlSlabArgs a{};
-  a.col_idx = transposed ? p->t_col_idx : p->col_idx;
-  a.val = transposed ? p->t_val : p->val;
+  a.pairs = reinterpret_cast<const uint2*>(ws + (transposed ? l.off_pairsXt : l.off_pairsX));
   a.M = (int)(transposed ? p->n_genes : p->n_cells);
   a.C = (int)(transposed ? p->n_cells : p->n_genes);
   a.F16 = transposed ? H16 : W16;
@@ -805,9 +807,13 @@ static int kl_slab_prepare(const cnmf_b200_kl_problem* p, const KlLayout& l, boo
   CNMF_TRY(launch_kl_to_half_pairs(p->Hr, ws + l.off_hh, p->n_cells, p->R, p->Kp, flag, st));
   CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, sgX, st));
   CNMF_TRY(launch_kl_work_scan(*sgX, l.segX.V, p->Kp, reinterpret_cast<int*>(ws + l.off_wcumX), st));
+  CNMF_TRY(launch_kl_pack_pairs(*sgX, l.segX.V, p->n_cells, l.segX.block, p->Kp, p->col_idx, p->val,
+                                reinterpret_cast<const int*>(ws + l.off_wcumX), ws + l.off_pairsX, st));
   if (both) {
     CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, sgXt, st));
     CNMF_TRY(launch_kl_work_scan(*sgXt, l.segXt.V, p->Kp, reinterpret_cast<int*>(ws + l.off_wcumXt), st));
+    CNMF_TRY(launch_kl_pack_pairs(*sgXt, l.segXt.V, p->n_genes, l.segXt.block, p->Kp, p->t_col_idx, p->t_val,
+                                  reinterpret_cast<const int*>(ws + l.off_wcumXt), ws + l.off_pairsXt, st));
   }
   return 0;
 }
