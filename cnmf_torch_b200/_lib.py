@@ -43,7 +43,7 @@ class KlProblem(C.Structure):
         ("R", i32), ("K", i32), ("Kp", i32), ("impl", i32),
         ("Hr", vp), ("Wt", vp),
         ("active", vp),
-        ("l1_H", f32), ("l2_H", f32), ("l1_W", f32), ("l2_W", f32), ("eps", f32), ("pad0", f32),
+        ("l1_H", f32), ("l2_H", f32), ("l1_W", f32), ("l2_W", f32), ("eps", f32), ("warm", i32),
         ("sumX", f64), ("xlogx", f64), ("err2", vp), ("workspace", vp), ("workspace_bytes", i64),
     ]
 

@@ -124,15 +124,14 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
   int fill_buf = 0, use_buf = 0;      // ring positions of the next chunk to request / to consume
   uint32_t use_par = 0;               // parity of the barrier phase the next consumed chunk completes
 
-  uint32_t loff[P];   // byte offset of this lane's m-th load inside a line; word index (m + a) mod P of pair rp
-  int hoff[P];        // the same word index for the moving factor's row (in 8-byte words)
+  uint32_t loff[P];   // byte offset of this lane's m-th load inside a line (and inside a row of the moving factor's
+                      // copy): word index (m + a) mod P of pair rp
 #pragma unroll
   for (int m = 0; m < P; ++m) {
     int t = m + aslot;
     if (t >= P) t -= P;
-    hoff[m] = rp * P + t;
     // lanes beyond LANES have no work: they read one of the line's unused words (banks nobody else touches)
-    loff[m] = lane_on ? (uint32_t)hoff[m] * 8u : (uint32_t)li * 8u;
+    loff[m] = lane_on ? (uint32_t)(rp * P + t) * 8u : (uint32_t)li * 8u;
   }
   const int64_t rkp = (int64_t)a.R * KP;
   const uint32_t lane_entry = (uint32_t)(hw * A + aslot) * 8u;   // this lane's entry inside a step's 2A entries
@@ -210,9 +209,11 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
       __syncthreads();   // the slab is complete
 
       auto load_h = [&](int row, uint2 (&h)[P]) {   // this row of the moving factor, rotated like the gathered operand
-        const uint2* hp = a.S16 + ((int64_t)row * a.RP + rp0) * P;
+        // (the rotated word offsets are the ones of a slab line: loff[] is live in registers for the main loop)
+        const char* hp = reinterpret_cast<const char*>(a.S16 + ((int64_t)row * a.RP + rp0) * P);
 #pragma unroll
-        for (int m = 0; m < P; ++m) h[m] = pair_on ? __ldg(hp + hoff[m]) : make_uint2(0u, 0u);
+        for (int m = 0; m < P; ++m)
+          h[m] = pair_on ? __ldg(reinterpret_cast<const uint2*>(hp + loff[m])) : make_uint2(0u, 0u);
       };
 
       int sg = ws;

@@ -661,7 +661,7 @@ int64_t kl_seg_layout_explicit(int64_t M, int64_t n_cols, int64_t nnz, int seg, 
 }
 
 int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, char* ws, const KlSegLayout& o, float* part,
-                      KlSegs* out, cudaStream_t st) {
+                      KlSegs* out, cudaStream_t st, bool launch) {
   int* vsp = reinterpret_cast<int*>(ws + o.off_vsp);
   int* rslot = reinterpret_cast<int*>(ws + o.off_rslot);
   int* svrow = reinterpret_cast<int*>(ws + o.off_svrow);
@@ -673,18 +673,22 @@ int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, char* w
   if (o.nb > 1) {
     int* vb = reinterpret_cast<int*>(ws + o.off_vbeg);
     int* ve = reinterpret_cast<int*>(ws + o.off_vend);
-    kl_block_bounds_kernel<<<(unsigned)ceil_div(M * (o.nb + 1), 256), 256, 0, st>>>(row_ptr, col_idx, M, o.nb, o.block,
-                                                                                     vb, ve);
-    CNMF_LAUNCH_CHECK();
+    if (launch) {
+      kl_block_bounds_kernel<<<(unsigned)ceil_div(M * (o.nb + 1), 256), 256, 0, st>>>(row_ptr, col_idx, M, o.nb, o.block,
+                                                                                       vb, ve);
+      CNMF_LAUNCH_CHECK();
+    }
     vbeg = vb; vend = ve;
   }
-  const bool partial = o.nb > 1 || o.all_partial;   // one partial slot per segment, empty virtual rows own none
-  CNMF_CUDA(cudaMemsetAsync(nmulti, 0, 4, st));
-  kl_seg_scan_kernel<<<1, 1024, 0, st>>>(vbeg, vend, o.V, o.seg, partial ? 0 : 1, vsp, partial ? nullptr : rslot);
-  CNMF_LAUNCH_CHECK();
-  kl_seg_fill_kernel<<<(unsigned)ceil_div(o.V, 256), 256, 0, st>>>(vbeg, o.V, o.seg, vsp, svrow, sbeg,
-                                                                   partial ? nullptr : multi, nmulti);
-  CNMF_LAUNCH_CHECK();
+  if (launch) {
+    const bool partial = o.nb > 1 || o.all_partial;   // one partial slot per segment, empty virtual rows own none
+    CNMF_CUDA(cudaMemsetAsync(nmulti, 0, 4, st));
+    kl_seg_scan_kernel<<<1, 1024, 0, st>>>(vbeg, vend, o.V, o.seg, partial ? 0 : 1, vsp, partial ? nullptr : rslot);
+    CNMF_LAUNCH_CHECK();
+    kl_seg_fill_kernel<<<(unsigned)ceil_div(o.V, 256), 256, 0, st>>>(vbeg, o.V, o.seg, vsp, svrow, sbeg,
+                                                                     partial ? nullptr : multi, nmulti);
+    CNMF_LAUNCH_CHECK();
+  }
   out->vseg_ptr = vsp; out->row_slot_ptr = rslot; out->seg_vrow = svrow; out->seg_beg = sbeg; out->vend = vend;
   out->multi_rows = multi; out->n_multi = nmulti; out->part = part; out->seg_len = o.seg; out->nb = o.nb;
   return 0;
@@ -803,6 +807,11 @@ static int kl_slab_prepare(const cnmf_b200_kl_problem* p, const KlLayout& l, boo
   char* ws = reinterpret_cast<char*>(p->workspace);
   int* flag = reinterpret_cast<int*>(ws + l.off_flag);
   float* part = reinterpret_cast<float*>(ws + l.off_part);
+  if (p->warm != 0) {   // tables, pair tables and fp16 copies are what the previous call left: bind only
+    CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, sgX, st, false));
+    CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, sgXt, st, false));
+    return 0;
+  }
   CNMF_TRY(launch_kl_to_half_pairs(p->Wt, ws + l.off_wh, p->n_genes, p->R, p->Kp, flag, st));
   CNMF_TRY(launch_kl_to_half_pairs(p->Hr, ws + l.off_hh, p->n_cells, p->R, p->Kp, flag, st));
   CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, sgX, st));
@@ -905,7 +914,7 @@ int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* s
   if (l.slab) {
     KlSegs sgX{}, sgXt{};
     int* flag = reinterpret_cast<int*>(ws + l.off_flag);
-    CNMF_TRY(kl_slab_prepare(p, l, true, &sgX, &sgXt, st));   // stateless: copies and tables are rebuilt per call
+    CNMF_TRY(kl_slab_prepare(p, l, true, &sgX, &sgXt, st));   // cold: copies and tables rebuilt; warm: bound only
     const KlSlabArgs aX = kl_slab_args(p, l, false, sgX, 0), aXt = kl_slab_args(p, l, true, sgXt, 0);
     for (int it = 0; it < n_iters; ++it) {
       CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, nullptr, cpart, st));
@@ -923,21 +932,23 @@ int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* s
   __half* Wh = reinterpret_cast<__half*>(ws + l.off_wh);
   __half* Hh = reinterpret_cast<__half*>(ws + l.off_hh);
   int* gflag = reinterpret_cast<int*>(ws + l.off_flag);
-  CNMF_TRY(launch_range_check(p->Hr, p->n_cells * C, gflag, st));
-  CNMF_TRY(launch_range_check(p->Wt, p->n_genes * C, gflag, st));
-  CNMF_TRY(launch_to_half(p->Wt, Wh, p->n_genes * C, st));  // Hh is written by the first H half-step
+  const bool cold = p->warm == 0;   // warm: tables and the fp16 copy of W are what the previous iterate call left
+  if (cold) {
+    CNMF_TRY(launch_range_check(p->Hr, p->n_cells * C, gflag, st));
+    CNMF_TRY(launch_range_check(p->Wt, p->n_genes * C, gflag, st));
+    CNMF_TRY(launch_to_half(p->Wt, Wh, p->n_genes * C, st));  // Hh is written by the first H half-step
+  }
   KlSegs sgX{}, sgXt{};
   float* part = reinterpret_cast<float*>(ws + l.off_part);
-  // stateless: the tables are rebuilt per call (a few tiny kernels against >= 1 iteration)
-  CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, &sgX, st));
-  CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, &sgXt, st));
+  CNMF_TRY(kl_build_segments(p->row_ptr, p->col_idx, p->n_cells, ws, l.segX, part, &sgX, st, cold));
+  CNMF_TRY(kl_build_segments(p->t_row_ptr, p->t_col_idx, p->n_genes, ws, l.segXt, part, &sgXt, st, cold));
   const int64_t nsX = kl_nseg_max(l.segX.V, p->nnz, l.segX.seg), nsXt = kl_nseg_max(l.segXt.V, p->nnz, l.segXt.seg);
   const int64_t mmX = kl_multi_max(p->nnz, l.segX.seg), mmXt = kl_multi_max(p->nnz, l.segXt.seg);
   for (int it = 0; it < n_iters; ++it) {
     CNMF_TRY(launch_colsum(p->Wt, p->n_genes, C, wsum, nullptr, cpart, st));
     CNMF_TRY(launch_kl_half(p->row_ptr, p->col_idx, p->val, p->n_cells, Wh, p->Hr, Hh, wsum, p->active, p->R, p->Kp,
                             p->l1_H, p->l2_H, p->eps, st, &sgX, nsX, mmX, kl_rep_group(p->n_genes, p->Kp)));
-    if (it == 0 && p->active != nullptr)  // frozen replicates skip the write: their copy must exist too
+    if (it == 0 && cold && p->active != nullptr)  // frozen replicates skip the write: their copy must exist too
       CNMF_TRY(launch_to_half(p->Hr, Hh, p->n_cells * C, st));
     CNMF_TRY(launch_colsum(p->Hr, p->n_cells, C, hsum, nullptr, cpart, st));
     CNMF_TRY(launch_kl_half(p->t_row_ptr, p->t_col_idx, p->t_val, p->n_genes, Hh, p->Wt, Wh, hsum, p->active, p->R,
@@ -956,7 +967,7 @@ int cnmf_b200_kl_objective(const cnmf_b200_kl_problem* p, void* stream) {
   const KlLayout l = kl_layout(p);
   if (l.slab) {
     KlSegs sgX{}, sgXt{};
-    CNMF_TRY(kl_slab_prepare(p, l, false, &sgX, &sgXt, (cudaStream_t)stream));
+    CNMF_TRY(kl_slab_prepare(p, l, true, &sgX, &sgXt, (cudaStream_t)stream));   // (both tables: the next call may be warm)
     return kl_objective_impl(p, l, (cudaStream_t)stream, &sgX);
   }
   return kl_objective_impl(p, l, (cudaStream_t)stream);

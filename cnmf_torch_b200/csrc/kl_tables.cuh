@@ -31,7 +31,8 @@ static inline int64_t kl_nseg_max(int64_t V, int64_t nnz, int seg) { return V + 
 // explicit segment length / column block (the slab kernels choose them from the shared-memory size)
 int64_t kl_seg_layout_explicit(int64_t M, int64_t n_cols, int64_t nnz, int seg, int block, int64_t off, KlSegLayout* o);
 
+// launch == false: only bind `out` to the tables a previous call left in the workspace (a warm problem)
 int kl_build_segments(const int* row_ptr, const int* col_idx, int64_t M, char* ws, const KlSegLayout& o, float* part,
-                      KlSegs* out, cudaStream_t st);
+                      KlSegs* out, cudaStream_t st, bool launch = true);
 
 }  // namespace cnmf

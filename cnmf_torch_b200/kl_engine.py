@@ -26,9 +26,9 @@ def pad2(k: int) -> int:
 
 class SparseKLEngine:
     def __init__(self, X, device="cuda:0", init_device="cpu", impl=None, normalise=True):
-        """``impl``: "gather" (coalesced L2-gather kernels) or "slab" (shared-memory slab kernels); default (None, or
-        env CNMF_B200_KL_IMPL) by size: slab up to 50 000 cells, where it measured 11-13 % faster (20 000 cells: 1.71 vs
-        1.92 ms per batched iteration), gather beyond (100 000 cells: 7.45 vs 8.23 ms).
+        """``impl``: "slab" (shared-memory slab kernels; the default -- None, or env CNMF_B200_KL_IMPL) or "gather"
+        (coalesced L2-gather kernels).  Per batched iteration at K=9, R=100: 20 000 cells 1.50 vs 1.92 ms, 100 000 cells
+        6.94 vs 7.45 ms; at R=13: 0.35 vs 0.48 and 1.37 vs 1.52 ms.
         ``normalise``: the kernels gather fp16 copies of the factors, so the engine works on X * c^2 with c the power
         of two that brings mean(X * c^2) to about 1 -- KL multiplicative updates are exactly covariant (H, W scale
         by c, a power of two: the same bits), and factor entries then sit in the middle of the fp16 range whatever
@@ -49,7 +49,7 @@ class SparseKLEngine:
         if csr.nnz and float(csr.data.min()) < 0.0:
             raise ValueError("X must be non-negative")   # the kernels rely on stored entries being > 0
         self.N, self.G = csr.shape
-        self.impl = _KL_IMPL[self._impl_arg or ("slab" if self.N <= 50000 else "gather")]
+        self.impl = _KL_IMPL[self._impl_arg or "slab"]
         self.nnz = int(csr.nnz)
         if self.nnz >= 2 ** 31:
             raise ValueError("nnz must fit 32-bit offsets")
@@ -230,6 +230,12 @@ class KlBatch:
     def iterate(self, n):
         check(self.eng.lib.cnmf_b200_kl_iterate(C.byref(self.p), int(n), self.eng._stream()), "kl_iterate")
         self.launches += self.eng.lib.cnmf_b200_last_launch_count()
+        if n > 0:
+            self.p.warm = 1    # the next call reuses the tables and fp16 copies in the workspace (see invalidate)
+
+    def invalidate(self):
+        """Call after writing ``Hr`` / ``Wt`` directly: the next iterate rebuilds the fp16 copies from them."""
+        self.p.warm = 0
 
     def check_range(self):
         """Raise if a factor entry (or, on the slab path, a ratio x / (WH)) left the fp16 range of the gathered

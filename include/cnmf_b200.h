@@ -305,12 +305,18 @@ typedef struct cnmf_b200_kl_problem {
   const int32_t* t_col_idx;
   const float* t_val;
   int32_t R, K, Kp;          /* Kp: K rounded up to an EVEN number here (<= CNMF_B200_MAX_KP); padding columns zero */
-  int32_t impl;              /* CNMF_B200_KL_IMPL_GATHER (0, default) or CNMF_B200_KL_IMPL_SLAB */
+  int32_t impl;              /* CNMF_B200_KL_IMPL_GATHER (0) or CNMF_B200_KL_IMPL_SLAB (1, what the host layer selects) */
   float* Hr;                 /* [N x R*Kp] updated in place */
   float* Wt;                 /* [G x R*Kp] updated in place */
   const uint8_t* active;     /* [R] or NULL */
   float l1_H, l2_H, l1_W, l2_W;
-  float eps, pad0;
+  float eps;
+  int32_t warm;              /* 0: cnmf_b200_kl_iterate rebuilds its tables (row segments, work split, packed entries)
+                                and the fp16 copies of both factors from the fp32 masters -- stateless, the default.
+                                1: the caller promises that the previous call on this problem was a cnmf_b200_kl_iterate
+                                with the same X, R, Kp, impl and workspace, that the workspace was not touched since and
+                                that nobody else wrote Hr / Wt: the tables and copies in the workspace are reused
+                                (0.13 ms per call at 100 000 x 2000 -- 9 % of an iteration at R = 13). */
   double sumX, xlogx;        /* from cnmf_b200_kl_constants */
   double* err2;              /* [R] out: 2 * (generalised KL divergence + L1 and 0.5*l2*||.||^2 terms); may be NULL */
   void* workspace;
@@ -320,11 +326,12 @@ typedef struct cnmf_b200_kl_problem {
 /* The two kernel families behind cnmf_b200_kl_iterate / _objective (same update rule, same results within the
  * tolerances of the tests):
  *   GATHER -- one thread per (row segment, replicate), lanes = consecutive replicates, the fp16 copy of the fixed
- *             factor gathered from L2 in coalesced runs (also what the standalone cnmf_b200_kl_half_step runs);
- *             the default: faster at the cfg-3 shape (100 000 cells: 7.4 vs 8.2 ms per batched iteration);
+ *             factor gathered from L2 in coalesced runs (also what the standalone cnmf_b200_kl_half_step runs):
+ *             7.45 ms per batched iteration at 100 000 x 2000, K = 9, R = 100; 1.92 ms at 20 000 cells;
  *   SLAB   -- the fixed factor's fp16 copy of one replicate group and one block of columns is staged in shared
- *             memory (bank-conflict-free line layout) and gathered from there; fp16 x fp16 + fp32 FMAs (FHFMA);
- *             70 x less L2 traffic, faster on small matrices (20 000 cells: 1.71 vs 1.92 ms). */
+ *             memory (bank-conflict-free line layout) and gathered from there; the (column, value) pairs of X are
+ *             packed per row segment once and streamed by bulk copies; fp16 x fp16 + fp32 FMAs (FHFMA); 70 x less
+ *             L2 traffic: 6.94 ms at 100 000 cells, 1.50 ms at 20 000 (R = 13: 1.37 vs 1.52 and 0.35 vs 0.48). */
 #define CNMF_B200_KL_IMPL_GATHER 0
 #define CNMF_B200_KL_IMPL_SLAB 1
 

@@ -269,3 +269,42 @@ def test_kl_data_scale_and_out_of_range_init_are_handled_not_clamped(problem):
         ora = no.nmf_batch(problem, (H0[r] * mid).numpy(), (W0[r] / mid).numpy(), beta_loss="kullback-leibler", tol=0.0,
                            max_iter=20)
         assert abs(res.trace[-1][1][r] - ora["trace"][-1][1]) / ora["trace"][-1][1] < 1e-3
+
+
+def test_kl_warm_calls_reuse_tables_and_copies(problem):
+    """cnmf_b200_kl_problem.warm (include/cnmf_b200.h): after the first iterate call the batch reuses the segment
+    tables, packed entries and fp16 copies its workspace holds -- 3 + 3 + 2 iterations with an objective in between
+    are bit-identical to 8 iterations of a fresh batch; `invalidate()` makes a caller's write to a factor count."""
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    eng = SparseKLEngine(problem)
+    H0, W0 = eng.make_init(7, [11, 12, 13])
+    a = eng.new_batch(7, H0=H0, W0=W0)
+    assert a.p.warm == 0
+    a.iterate(3)
+    assert a.p.warm == 1
+    a.objective()
+    a.iterate(3)
+    a.set_active(np.array([True, False, True]))
+    a.iterate(2)
+    b = eng.new_batch(7, H0=H0, W0=W0)
+    b.iterate(6)
+    b.invalidate()
+    b.set_active(np.array([True, False, True]))
+    b.iterate(2)
+    Wa, Ha = a.results(True)
+    Wb, Hb = b.results(True)
+    np.testing.assert_array_equal(Wa, Wb)
+    np.testing.assert_array_equal(Ha, Hb)
+    np.testing.assert_array_equal(a.read_loss(), b.read_loss())
+    # a write to the master without invalidate() would be ignored by the fp16 copies; with it, it counts
+    c = eng.new_batch(7, H0=H0, W0=W0)
+    c.iterate(1)
+    c.Hr.mul_(0.5)
+    c.Wt.mul_(2.0)
+    c.invalidate()
+    c.iterate(1)
+    d = eng.new_batch(7, H0=H0, W0=W0)
+    d.iterate(2)
+    Wc, Hc = c.results(True)
+    Wd, Hd = d.results(True)
+    np.testing.assert_allclose(Hc @ Wc, Hd @ Wd, rtol=5e-3, atol=1e-6)   # H/2, 2W: the same product, fp16 rounding aside
