@@ -97,13 +97,12 @@ template <int KP, int MODE>
 __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs a) {
   using Cfg = SlabCfg<KP>;
   constexpr int P = Cfg::P, RGP = Cfg::RGP, A = Cfg::A, LANES = Cfg::LANES;
-  constexpr int LINE_WORDS = RGP * P;
   constexpr int STEP_BYTES = 2 * A * 8;                      // (column, value) pairs of one warp step
   constexpr int CHS = KS_CHUNK_BYTES / STEP_BYTES;           // steps per staged chunk
   static_assert(CHS >= 1 && STEP_BYTES % 16 == 0, "a chunk holds whole steps; bulk copies move multiples of 16 bytes");
   extern __shared__ __align__(128) unsigned char slab[];
   __shared__ double s_obj[KS_WARPS][2 * RGP];
-  __shared__ __align__(8) uint64_t s_bar[KS_WARPS][KS_RING];
+  __shared__ __align__(8) uint64_t s_bar[KS_WARPS][KS_RING + 2];   // staging ring, then the two line buffers of h
 
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, hw = lane >> 4, li = lane & 15;
   const bool lane_on = li < LANES;
@@ -118,7 +117,11 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
   // per-warp ring of staging chunks, after the lines
   const uint32_t stg = slab_u32 + (uint32_t)a.block * KS_LINE + (uint32_t)warp * (KS_RING * KS_CHUNK_BYTES);
   const uint32_t bar0 = static_cast<uint32_t>(__cvta_generic_to_shared(&s_bar[warp][0]));
-  if (lane < KS_RING) ks_bar_init(bar0 + 8u * lane, 1);
+  if (lane < KS_RING + 2) ks_bar_init(bar0 + 8u * lane, 1);
+  const uint32_t hbar0 = bar0 + 8u * KS_RING;
+  const uint32_t hbuf0 = slab_u32 + (uint32_t)a.block * KS_LINE + KS_STAGE_BYTES + (uint32_t)warp * (2 * KS_LINE);
+  int hfill = 0, huse = 0;            // line buffer of the next request / of the next segment
+  uint32_t hpar = 0;                  // bit i: parity of the phase buffer i completes next
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   __syncthreads();
   int fill_buf = 0, use_buf = 0;      // ring positions of the next chunk to request / to consume
@@ -166,11 +169,11 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
       const int nl = (a.C - c0) < a.block ? (a.C - c0) : a.block;
       const uint32_t sbase = slab_u32 - ((uint32_t)c0 << 7);
       __syncthreads();   // every warp is done with the previous slab
-      for (int w = threadIdx.x; w < nl * LINE_WORDS; w += KS_THREADS) {
-        const int line = w / LINE_WORDS, slot = w - line * LINE_WORDS;
-        uint2 v = make_uint2(0u, 0u);
-        if (slot < npair * P) v = a.F16[((int64_t)(c0 + line) * a.RP + rp0) * P + slot];
-        *reinterpret_cast<uint2*>(slab + line * KS_LINE + slot * 8) = v;
+      // lines of this (block, group): 128 bytes each, ngroups lines apart in the copy
+      for (int w = threadIdx.x; w < nl * (KS_LINE / 16); w += KS_THREADS) {
+        const int line = w >> 3, q = w & 7;
+        *reinterpret_cast<uint4*>(slab + line * KS_LINE + q * 16) =
+            __ldg(reinterpret_cast<const uint4*>(a.F16 + ((int64_t)(c0 + line) * a.ngroups + g) * 16) + q);
       }
 
       // The phase's segments [s, sb_end) are dealt to the warps as 16 CONTIGUOUS runs of equal weight, so that a
@@ -208,22 +211,32 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
       for (int i = 0; i < KS_RING && st_left > 0; ++i) request_chunk();
       __syncthreads();   // the slab is complete
 
-      auto load_h = [&](int row, uint2 (&h)[P]) {   // this row of the moving factor, rotated like the gathered operand
-        // (the rotated word offsets are the ones of a slab line: loff[] is live in registers for the main loop)
-        const char* hp = reinterpret_cast<const char*>(a.S16 + ((int64_t)row * a.RP + rp0) * P);
+      // A segment's row of the moving factor is one 128-byte line of its copy: it comes in by a bulk copy, a segment
+      // ahead, into one of two per-warp line buffers; every lane then picks its rotated words out of shared memory.
+      auto request_h = [&](int row) {
+        if (lane == 0) {
+          const uint32_t bar = hbar0 + 8u * hfill;
+          ks_bar_expect(bar, KS_LINE);
+          ks_bulk_load(hbuf0 + (uint32_t)hfill * KS_LINE, a.S16 + ((int64_t)row * a.ngroups + g) * 16, KS_LINE, bar);
+        }
+        hfill ^= 1;
+      };
+      auto take_h = [&](uint2 (&h)[P]) {
+        ks_bar_wait(hbar0 + 8u * huse, (hpar >> huse) & 1u);
+        const uint32_t base = hbuf0 + (uint32_t)huse * KS_LINE;
 #pragma unroll
-        for (int m = 0; m < P; ++m)
-          h[m] = pair_on ? __ldg(reinterpret_cast<const uint2*>(hp + loff[m])) : make_uint2(0u, 0u);
+        for (int m = 0; m < P; ++m) h[m] = lds64(base + loff[m]);
+        hpar ^= 1u << huse;
+        huse ^= 1;
       };
 
       int sg = ws;
-      int row = 0, steps = 0, nrow = 0, nsteps = 0, wc = 0;
-      uint2 hreg[P], hnext[P];
+      int steps = 0, nsteps = 0, wc = 0;
+      uint2 hreg[P];
       if (sg < we) {
-        row = a.seg_vrow[sg] - b * M;
         wc = a.wcum[sg + 1];
         steps = wc - a.wcum[sg] - KS_SEG_OVERHEAD_STEPS;
-        load_h(row, hreg);
+        request_h(a.seg_vrow[sg] - b * M);
       }
       int chunk_left = 0;              // steps left in the chunk being consumed
       bool first_chunk = true;
@@ -231,13 +244,14 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
       uint2 jx_next = make_uint2(0u, 0u);
       while (sg < we) {
         const bool has_next = sg + 1 < we;
+        __syncwarp();                  // every lane has taken its words of the line buffer the next request overwrites
         if (has_next) {                // next segment's table entries and row of the factor, a segment ahead
-          nrow = a.seg_vrow[sg + 1] - b * M;
+          request_h(a.seg_vrow[sg + 1] - b * M);
           const int wc2 = a.wcum[sg + 2];
           nsteps = wc2 - wc - KS_SEG_OVERHEAD_STEPS;
           wc = wc2;
-          load_h(nrow, hnext);
         }
+        take_h(hreg);
         float n0[KP], n1[KP];   // n0[2m], n0[2m+1]: numerators of k-pair (m + a) mod P, replicate rep0
 #pragma unroll
         for (int k = 0; k < KP; ++k) { n0[k] = 0.f; n1[k] = 0.f; }
@@ -325,9 +339,7 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
           dacc0 += (double)acc0;
           dacc1 += (double)acc1;
         }
-        ++sg; row = nrow; steps = nsteps;
-#pragma unroll
-        for (int m = 0; m < P; ++m) hreg[m] = hnext[m];
+        ++sg; steps = nsteps;
       }
       s = sb_end;
     }
@@ -382,12 +394,12 @@ __global__ void __launch_bounds__(256) kl_pack_pairs_kernel(const int* __restric
 }
 
 // All rows: numerators = partials of the row's segments, block by block and segment by segment (fixed order);
-// multiplicative update of the fp32 master; fp16 copy in the pair-interleaved layout [row][RP][P] x {rep0 pair, rep1 pair}.
+// multiplicative update of the fp32 master; fp16 copy in the line layout (see kl_to_half_pairs_kernel).
 template <int KP>
 __global__ void __launch_bounds__(128) kl_finish_slab_kernel(int64_t M, float* __restrict__ state,
                                                              uint32_t* __restrict__ state16,
                                                              const float* __restrict__ fsum,
-                                                             const uint8_t* __restrict__ active, int R, int RP, float l1,
+                                                             const uint8_t* __restrict__ active, int R, int ngroups, float l1,
                                                              float l2, float eps, const int* __restrict__ vseg_ptr, int nb,
                                                              const float* __restrict__ part, int* __restrict__ flag) {
   constexpr int P = KP / 2;
@@ -414,7 +426,9 @@ __global__ void __launch_bounds__(128) kl_finish_slab_kernel(int64_t M, float* _
   }
   float2* sp = reinterpret_cast<float2*>(state + row * rk + (int64_t)r * KP);
   const float2* dp = reinterpret_cast<const float2*>(fsum + (int64_t)r * KP);
-  uint32_t* hp = state16 + ((row * RP + (r >> 1)) * P) * 2 + (r & 1);
+  constexpr int RGP = 16 / P;
+  const int rpair = r >> 1;      // line of (row, group), word (pair in group) * P + m, half r & 1 of the word
+  uint32_t* hp = state16 + ((row * ngroups + rpair / RGP) * 16 + (rpair % RGP) * P) * 2 + (r & 1);
   bool bad = false;
 #pragma unroll
   for (int m = 0; m < P; ++m) {
@@ -433,21 +447,25 @@ __global__ void __launch_bounds__(128) kl_finish_slab_kernel(int64_t M, float* _
   if (bad) atomicOr(flag, 1);
 }
 
-// fp32 master [rows][R*KP] -> pair-interleaved fp16 copy [rows][RP][P] x {rep0 pair, rep1 pair}; padding replicate = 0
+// fp32 master [rows][R*KP] -> fp16 copy in the LINE layout the slab kernel stages and streams: one 128-byte line per
+// (row, replicate group), 16 words of 8 bytes; word p * P + m = {k-pair m of replicate 2 * (g * RGP + p), the same of
+// the next replicate}; words past RGP * P and replicates past R are zero.
 template <int KP>
 __global__ void __launch_bounds__(256) kl_to_half_pairs_kernel(const float* __restrict__ src, uint2* __restrict__ dst,
-                                                               int64_t rows, int R, int RP, int* __restrict__ flag) {
-  constexpr int P = KP / 2;
-  const int64_t total = rows * RP * P;
+                                                               int64_t rows, int R, int ngroups, int* __restrict__ flag) {
+  constexpr int P = KP / 2, RGP = 16 / P;
+  const int64_t total = rows * ngroups * 16;
   bool bad = false;
   for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
-    const int m = (int)(i % P);
-    const int64_t t = i / P;
-    const int rp = (int)(t % RP);
-    const int64_t row = t / RP;
-    const float2 v0 = *reinterpret_cast<const float2*>(src + row * R * KP + (int64_t)(2 * rp) * KP + 2 * m);
-    float2 v1 = make_float2(0.f, 0.f);
-    if (2 * rp + 1 < R) v1 = *reinterpret_cast<const float2*>(src + row * R * KP + (int64_t)(2 * rp + 1) * KP + 2 * m);
+    const int word = (int)(i & 15);
+    const int64_t t = i >> 4;
+    const int g = (int)(t % ngroups);
+    const int64_t row = t / ngroups;
+    const int pl = word / P, m = word - pl * P;
+    const int r0 = 2 * (g * RGP + pl);
+    float2 v0 = make_float2(0.f, 0.f), v1 = make_float2(0.f, 0.f);
+    if (pl < RGP && r0 < R) v0 = *reinterpret_cast<const float2*>(src + row * R * KP + (int64_t)r0 * KP + 2 * m);
+    if (pl < RGP && r0 + 1 < R) v1 = *reinterpret_cast<const float2*>(src + row * R * KP + (int64_t)(r0 + 1) * KP + 2 * m);
     bad |= !(v0.x <= 65504.f) || !(v0.y <= 65504.f) || !(v1.x <= 65504.f) || !(v1.y <= 65504.f);
     const __half2 h0 = __floats2half2_rn(v0.x, v0.y), h1 = __floats2half2_rn(v1.x, v1.y);
     dst[i] = make_uint2(*reinterpret_cast<const uint32_t*>(&h0), *reinterpret_cast<const uint32_t*>(&h1));
@@ -525,24 +543,24 @@ int launch_kl_pack_pairs(const KlSegs& sg, int64_t V, int64_t M, int block, int 
 }
 
 int launch_kl_to_half_pairs(const float* src, void* dst, int64_t rows, int R, int Kp, int* flag, cudaStream_t st) {
-  const int RP = (R + 1) / 2;
-  const int64_t total = rows * RP * (Kp / 2);
+  const int ngroups = ks_num_groups(R, Kp);
+  const int64_t total = rows * ngroups * 16;
   int64_t blocks = ceil_div(total, 256 * 4);
   if (blocks > 148 * 16) blocks = 148 * 16;
   if (blocks < 1) blocks = 1;
   KS_DISPATCH_KP(Kp, (kl_to_half_pairs_kernel<KP><<<(unsigned)blocks, 256, 0, st>>>(src, reinterpret_cast<uint2*>(dst), rows,
-                                                                                    R, RP, flag)));
+                                                                                    R, ngroups, flag)));
   CNMF_LAUNCH_CHECK();
   return 0;
 }
 
 template <int KP, int MODE>
 static int launch_slab_inst(const KlSlabArgs& a, int grid, cudaStream_t st) {
-  const int smem = a.block * KS_LINE + KS_STAGE_BYTES;
+  const int smem = a.block * KS_LINE + KS_STAGE_BYTES + KS_HBUF_BYTES;
   static unsigned long long attr_mask = 0;
   if (needs_func_attr(&attr_mask))
     CNMF_CUDA(cudaFuncSetAttribute(kl_slab_kernel<KP, MODE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                   KS_MAX_LINES * KS_LINE + KS_STAGE_BYTES));
+                                   KS_MAX_LINES * KS_LINE + KS_STAGE_BYTES + KS_HBUF_BYTES));
   kl_slab_kernel<KP, MODE><<<grid, KS_THREADS, smem, st>>>(a);
   CNMF_LAUNCH_CHECK();
   return 0;
@@ -572,11 +590,11 @@ int launch_kl_slab(const KlSlabArgs& a, int Kp, int mode, cudaStream_t st) {
 
 int launch_kl_finish_slab(int64_t M, float* state, void* state16, const float* fsum, const uint8_t* active, int R, int Kp,
                           float l1, float l2, float eps, const KlSegs& sg, int* flag, cudaStream_t st) {
-  const int RP = (R + 1) / 2;
+  const int ngroups = ks_num_groups(R, Kp);
   const int64_t blocks = ceil_div(M * R, 128);
   CNMF_CHECK_ARG(blocks < (1ll << 31), "kl: rows * replicates too large for one launch");
   KS_DISPATCH_KP(Kp, (kl_finish_slab_kernel<KP><<<(unsigned)blocks, 128, 0, st>>>(
-                         M, state, reinterpret_cast<uint32_t*>(state16), fsum, active, R, RP, l1, l2, eps, sg.vseg_ptr,
+                         M, state, reinterpret_cast<uint32_t*>(state16), fsum, active, R, ngroups, l1, l2, eps, sg.vseg_ptr,
                          sg.nb, sg.part, flag)));
   CNMF_LAUNCH_CHECK();
   return 0;

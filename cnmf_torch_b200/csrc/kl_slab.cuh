@@ -11,7 +11,8 @@ constexpr int KS_LINE = 128;               // bytes of shared memory per column 
 constexpr int KS_RING = 3;                 // staging chunks in flight per warp
 constexpr int KS_CHUNK_BYTES = 1024;       // one staging chunk: whole warp steps of (column, value) pairs, <= 1 KB
 constexpr int KS_STAGE_BYTES = KS_WARPS * KS_RING * KS_CHUNK_BYTES + 256;   // 48 KB (+ the one-step read-ahead past the last chunk)
-constexpr int KS_MAX_LINES = 1400;         // 175 KB slab + 48 KB staging + static (barriers, objective sums): within 227 KB
+constexpr int KS_HBUF_BYTES = KS_WARPS * 2 * KS_LINE;   // two line buffers per warp for the moving factor's rows
+constexpr int KS_MAX_LINES = 1360;         // 170 KB slab + 48 KB staging + 4 KB line buffers + static: within 227 KB
 constexpr int KS_SEG_LEN = 640;            // entries per segment (64 steps at Kp = 10)
 constexpr int KS_SEG_OVERHEAD_STEPS = 2;   // set-up + un-rotation of a segment, in steps, for the static work split
 
@@ -42,8 +43,8 @@ struct KlSlabArgs {
   const uint2* pairs;      // (column, value bits) of every segment, padded to whole warp steps, in segment order
                            // (kl_pack_pairs_kernel): step t of the table is entries [t * Kp, (t + 1) * Kp)
   int M, C;                // rows; columns (= rows of the fixed factor)
-  const uint2* F16;        // fixed factor, pair-interleaved fp16 [C][RP][P] x {rep0 pair, rep1 pair}
-  const uint2* S16;        // moving factor (the rows being updated), same layout [M][RP][P]
+  const uint2* F16;        // fixed factor, fp16 line layout [C][ngroups] x 128 bytes (kl_to_half_pairs_kernel)
+  const uint2* S16;        // moving factor (the rows being updated), same layout [M][ngroups] x 128 bytes
   int R, RP, ngroups;      // replicates, replicate pairs, groups of RGP pairs
   const uint8_t* active;   // [R] or NULL
   float eps;

@@ -720,8 +720,8 @@ static KlLayout kl_layout(const cnmf_b200_kl_problem* p) {
   l.off_cpart = off; off += align_up(ceil_div(Lmax, CS_ROWS) * C * 4, 256);
   l.off_flag = off; off += 256;
   if (l.slab) {
-    // fp16 copies in the pair-interleaved layout [rows][RP][Kp/2] x 8 bytes; objective partials [SMs][R]
-    const int64_t C16 = (int64_t)((p->R + 1) / 2) * (p->Kp / 2) * 8;
+    // fp16 copies in the line layout [rows][groups] x 128 bytes; objective partials [SMs][R]
+    const int64_t C16 = (int64_t)ks_num_groups(p->R, p->Kp) * KS_LINE;   // one 128-byte line per (row, replicate group)
     l.nblk_obj = ks_sm_count();
     l.off_opart = off; off += align_up((int64_t)l.nblk_obj * p->R * 8, 256);
     l.off_wh = off; off += align_up(p->n_genes * C16, 256);
