@@ -41,6 +41,7 @@ ITERS_PER_STEP = 10
 ALGO = "hals"
 E2E_ITERS = 100  # iterations per replicate in one end-to-end public-API call
 KL_PROFILE_CSV = "r01_kl_half_step_full_raw.csv"   # the gather kernels are round 1's; same code
+KL_SLAB_PROFILE_CSV = "r02_kl_slab_c_raw.csv"
 TC_PROFILE_CSV = "r02_tc_half_step_full_raw.csv"   # ncu --set full raw page of the dominant kernel, this round
 METRIC = "nmf_replicate_iterations_per_second"
 UNIT = "replicate-iters/s"
@@ -271,7 +272,7 @@ def _extras(dev):
                     "replicate_iters_per_s": 100 / dt,
                     "algorithmic_hbm_gb_s": (2 * 8 * eng.nnz + 100 * 8 * 9 * (cells + 2000)) / dt / 1e9,
                     "fp32_fma_tflops_algorithmic": 2.0 * 2 * eng.nnz * 100 * 2 * 9 / dt / 1e12,
-                    "kernels": ("slab" if eng.impl == 1 else "gather") + " family (the engine's choice at this size); "
+                    "kernels": ("slab" if b.p.impl == 1 else "gather") + " family (the engine's choice for this Kp); "
                                "includes 1/10 of an objective evaluation"}
         del eng, b, xk
         torch.cuda.empty_cache()
@@ -504,6 +505,7 @@ def run_cfg3(args):
     # dominant kernel: the H half-step (slab kernel) of the tallest stack, timed alone through one iteration's events
     big = max(batches, key=lambda b: (b.R, b.Kp))
     big_kp = big.Kp
+    big_slab = big.p.impl == 1
     big.iterate(1)
     torch.cuda.synchronize()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -555,9 +557,11 @@ def run_cfg3(args):
             "gpu_launches": int(launches), "clocks": clocks,
             "roofline": {"bound": "hbm", "achieved": abytes / (it_ms_max * 1e-3) / 1e9, "peak": peaks["hbm_gbs"],
                          "unit": "GB/s", "frac": abytes / (it_ms_max * 1e-3) / 1e9 / peaks["hbm_gbs"],
-                         "traffic": _traffic_from_profile(KL_PROFILE_CSV, "kl_half_step_kernel"),
+                         "traffic": _traffic_from_profile(KL_SLAB_PROFILE_CSV, "kl_slab_kernel") if big_slab
+                         else _traffic_from_profile(KL_PROFILE_CSV, "kl_half_step_kernel"),
                          "kernel": f"one batched KL iteration of the Kp={big_kp} stack on rank 0 ({r_big} replicates): "
-                                   f"kl_half_step_kernel x2 (gather family) + finish passes + column sums",
+                                   + ("kl_slab_kernel x2 (slab family)" if big_slab else "kl_half_step_kernel x2 (gather family)")
+                                   + " + finish passes + column sums; stacks of Kp <= 10 and 14 run the slab family",
                          "kernel_ms": it_ms_max,
                          "peak_source": src,
                          "note": "the algorithmic bytes are tiny against the arithmetic: this path is bound by the fp32 FMA "

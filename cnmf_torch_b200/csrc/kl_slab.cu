@@ -18,8 +18,11 @@
 //   * arithmetic: fma.rn.f32.f16 (SASS FHFMA: fp16 x fp16 + fp32 -> fp32, half selectors in the operand, full
 //     FFMA rate on sm_100a -- profiles/r02_simt_rate.txt) on the packed words as they come out of shared memory:
 //     no unpacking.  s = h.w with both operands fp16 (11-bit significands, like the tf32 operands of the dense
-//     path), the ratio q = x / s rounded to fp16 for the second FMA chain (q is scale-free; an overflow turns into
-//     inf and is caught where the factor is written), accumulation fp32.
+//     path), the ratio q = x / s rounded to fp16 for the second FMA chain, accumulation fp32.  The staged values
+//     are x * 2^-8 (KS_XSCALE; undone exactly where the partials are summed), so that fp16 holds ratios up to
+//     1.6e7 instead of 65504 -- badly fitted entries of a long run do reach 1e5 -- at full precision down to 0.016
+//     (smaller ratios, which weigh nothing in a numerator of ratios near 1, lose bits gradually).  An overflow
+//     beyond that turns into inf and is caught where the factor is written.
 // Rows are cut into segments (kl_tables.cuh) at column-block boundaries and at `seg_len` entries; every segment
 // leaves its Kp numerators per replicate in `part`, and kl_finish_slab_kernel adds a row's segments in order,
 // applies the multiplicative update to the fp32 master and writes the fp16 copy (deterministic, no atomics).
@@ -359,7 +362,8 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
         if (rep < a.R) {
           double t = 0.0;
           for (int w2 = 0; w2 < KS_WARPS; ++w2) t += s_obj[w2][threadIdx.x];
-          a.opart[(int64_t)blockIdx.x * a.R + rep] = t * 0.6931471805599453;   // ln 2; a CTA meets a replicate once
+          // ln 2 and the scale of the staged values (exact); a CTA meets a replicate once
+          a.opart[(int64_t)blockIdx.x * a.R + rep] = t * (0.6931471805599453 / (double)KS_XSCALE);
         }
       }
     }
@@ -388,7 +392,7 @@ __global__ void __launch_bounds__(256) kl_pack_pairs_kernel(const int* __restric
     const uint32_t padcol = (uint32_t)((v / M) * block);
     for (int e = lane; e < n; e += 32) {
       const int idx = beg + e;
-      dst[e] = idx < end ? make_uint2((uint32_t)col_idx[idx], __float_as_uint(val[idx])) : make_uint2(padcol, 0u);
+      dst[e] = idx < end ? make_uint2((uint32_t)col_idx[idx], __float_as_uint(val[idx] * KS_XSCALE)) : make_uint2(padcol, 0u);
     }
   }
 }
@@ -435,8 +439,9 @@ __global__ void __launch_bounds__(128) kl_finish_slab_kernel(int64_t M, float* _
     float2 h = sp[m];
     const float2 den = dp[m];
     const float d0 = fmaf(l2, h.x, den.x), d1 = fmaf(l2, h.y, den.y);
-    const float a0 = l1 > 0.f ? fmaxf(num[2 * m] - l1, 0.f) : num[2 * m];
-    const float a1 = l1 > 0.f ? fmaxf(num[2 * m + 1] - l1, 0.f) : num[2 * m + 1];
+    const float u0 = num[2 * m] * (1.f / KS_XSCALE), u1 = num[2 * m + 1] * (1.f / KS_XSCALE);   // exact: a power of two
+    const float a0 = l1 > 0.f ? fmaxf(u0 - l1, 0.f) : u0;
+    const float a1 = l1 > 0.f ? fmaxf(u1 - l1, 0.f) : u1;
     h.x *= d0 < eps ? 0.f : __fdiv_rn(a0, d0);
     h.y *= d1 < eps ? 0.f : __fdiv_rn(a1, d1);
     sp[m] = h;

@@ -14,6 +14,7 @@ constexpr int KS_STAGE_BYTES = KS_WARPS * KS_RING * KS_CHUNK_BYTES + 256;   // 4
 constexpr int KS_HBUF_BYTES = KS_WARPS * 2 * KS_LINE;   // two line buffers per warp for the moving factor's rows
 constexpr int KS_MAX_LINES = 1360;         // 170 KB slab + 48 KB staging + 4 KB line buffers + static: within 227 KB
 constexpr int KS_SEG_LEN = 640;            // entries per segment (64 steps at Kp = 10)
+constexpr float KS_XSCALE = 1.f / 256.f;   // the staged values of X are scaled by this (see kl_slab.cu: range of the fp16 ratio)
 constexpr int KS_SEG_OVERHEAD_STEPS = 2;   // set-up + un-rotation of a segment, in steps, for the static work split
 
 #define KS_DISPATCH_KP(kp, ...)                                                                       \

@@ -18,6 +18,15 @@ from .engine import EPS_DEFAULT, BatchResult, SeedInit, draw_init
 _KL_IMPL = {"slab": _lib.KL_IMPL_SLAB, "gather": _lib.KL_IMPL_GATHER}
 
 
+def kl_impl_for(Kp: int) -> int:
+    """The faster kernel family for a stack of padded K = Kp, measured at 100 000 x 2000 cells (ms per batched
+    iteration, R = 200 / R = 26; profiles/NOTES.md): Kp=6 slab 8.6 / 1.45 vs gather 9.8 / 1.70; 8: 9.6 / 1.67 vs
+    11.4 / 1.92; 10: 13.5 / 2.16 vs 13.6 / 2.40; 12: 19.0 / 2.83 vs 15.6 / 2.68; 14: 19.1 / 2.85 vs 19.0 / 3.34.
+    A slab line holds floor(16 / (Kp/2)) replicate pairs: at Kp = 12 only 12 of a half-warp's 16 lanes have work and a
+    group is 4 replicates; from Kp = 16 on the slab kernels' accumulators no longer fit the register file."""
+    return _lib.KL_IMPL_SLAB if (Kp <= 10 or Kp == 14) else _lib.KL_IMPL_GATHER
+
+
 def pad2(k: int) -> int:
     """The KL kernels take any even Kp: every padded component is a gathered value and two FMAs per stored entry."""
     m = 4 if os.environ.get("CNMF_B200_KL_PAD4") else 2      # (dev knob: the multiple-of-4 padding of the dense path)
@@ -26,9 +35,8 @@ def pad2(k: int) -> int:
 
 class SparseKLEngine:
     def __init__(self, X, device="cuda:0", init_device="cpu", impl=None, normalise=True):
-        """``impl``: "slab" (shared-memory slab kernels; the default -- None, or env CNMF_B200_KL_IMPL) or "gather"
-        (coalesced L2-gather kernels).  Per batched iteration at K=9, R=100: 20 000 cells 1.50 vs 1.92 ms, 100 000 cells
-        6.94 vs 7.45 ms; at R=13: 0.35 vs 0.48 and 1.37 vs 1.52 ms.
+        """``impl``: "slab" (shared-memory slab kernels) or "gather" (coalesced L2-gather kernels); default (None, or
+        env CNMF_B200_KL_IMPL): per stack, by its padded K -- see ``kl_impl_for``.
         ``normalise``: the kernels gather fp16 copies of the factors, so the engine works on X * c^2 with c the power
         of two that brings mean(X * c^2) to about 1 -- KL multiplicative updates are exactly covariant (H, W scale
         by c, a power of two: the same bits), and factor entries then sit in the middle of the fp16 range whatever
@@ -49,7 +57,7 @@ class SparseKLEngine:
         if csr.nnz and float(csr.data.min()) < 0.0:
             raise ValueError("X must be non-negative")   # the kernels rely on stored entries being > 0
         self.N, self.G = csr.shape
-        self.impl = _KL_IMPL[self._impl_arg or "slab"]
+        self.impl = _KL_IMPL[self._impl_arg] if self._impl_arg else None      # None: per stack (kl_impl_for)
         self.nnz = int(csr.nnz)
         if self.nnz >= 2 ** 31:
             raise ValueError("nnz must fit 32-bit offsets")
@@ -211,7 +219,7 @@ class KlBatch:
         self.p = KlProblem(
             n_cells=eng.N, n_genes=eng.G, nnz=eng.nnz, row_ptr=ptr(eng.row_ptr), col_idx=ptr(eng.col_idx),
             val=ptr(eng.val), t_row_ptr=ptr(eng.t_row_ptr), t_col_idx=ptr(eng.t_col_idx), t_val=ptr(eng.t_val),
-            R=R, K=self.K, Kp=Kp, impl=eng.impl, Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active),
+            R=R, K=self.K, Kp=Kp, impl=eng.impl if eng.impl is not None else kl_impl_for(Kp), Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active),
             # an L1 strength is compared with a numerator, which scales like the factors; an L2 strength multiplies a
             # factor entry against a denominator that scales the same way
             l1_H=l1_H * eng.c, l2_H=l2_H, l1_W=l1_W * eng.c, l2_W=l2_W, eps=eps, sumX=eng.sumX, xlogx=eng.xlogx,

@@ -308,3 +308,26 @@ def test_kl_warm_calls_reuse_tables_and_copies(problem):
     Wc, Hc = c.results(True)
     Wd, Hd = d.results(True)
     np.testing.assert_allclose(Hc @ Wc, Hd @ Wd, rtol=5e-3, atol=1e-6)   # H/2, 2W: the same product, fp16 rounding aside
+
+
+def test_kl_large_ratios_are_held(problem):
+    """Entries fitted four to five orders of magnitude too low (x / (WH) up to ~1e6: beyond fp16's 65504): the slab
+    kernels stage x * 2^-8 so that the fp16 ratio holds up to 1.6e7 (kl_slab.cu), the gather kernels keep the ratio
+    in fp32 -- one iteration from such a start still matches the oracle and raises no range flag."""
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    eng = SparseKLEngine(problem)
+    H0, W0 = eng.make_init(6, [21, 22])
+    H0 = (H0 * 0.01).contiguous()
+    W0 = (W0 * 0.01).contiguous()
+    b = eng.new_batch(6, H0=H0, W0=W0)
+    b.iterate(1)
+    b.check_range()
+    W, H = b.results(True)
+    xt = torch.from_numpy(problem)
+    ratio_max = float((xt / (H0[0] @ W0[0])).max())
+    assert ratio_max > 2e5          # the case is what it claims to be
+    for r in range(2):
+        h = no.mu_kl_H(xt, H0[r], W0[r], 0.0, 0.0, 1e-16)
+        w = no.mu_kl_W(xt, h, W0[r], 0.0, 0.0, 1e-16)
+        np.testing.assert_allclose(H[r], h.numpy(), rtol=3e-3, atol=1e-6)
+        np.testing.assert_allclose(W[r], w.numpy(), rtol=3e-3, atol=1e-6)

@@ -177,3 +177,14 @@ def test_prepare_from_matrix_writes_the_reference_default_kwargs(tmp_path):
                       n_jobs=-1, use_gpu=False)
     with pytest.raises(NotImplementedError, match="zero"):
         obj.prepare_from_matrix(np.ones((4, 3), dtype=np.float32), [2], n_iter=2, beta_loss="itakura-saito")
+
+
+def test_kl_kernel_family_by_padded_k():
+    """SparseKLEngine picks the kernel family per stack (kl_engine.kl_impl_for): slab where its line layout fills the
+    half-warp (Kp <= 10, 14), gather elsewhere; an explicit impl or CNMF_B200_KL_IMPL overrides."""
+    from cnmf_torch_b200 import _lib
+    from cnmf_torch_b200.kl_engine import kl_impl_for, pad2
+    assert [kl_impl_for(pad2(k)) for k in (5, 6, 7, 8, 9, 10)] == [_lib.KL_IMPL_SLAB] * 6
+    assert kl_impl_for(pad2(11)) == kl_impl_for(12) == _lib.KL_IMPL_GATHER
+    assert kl_impl_for(pad2(13)) == _lib.KL_IMPL_SLAB
+    assert all(kl_impl_for(kp) == _lib.KL_IMPL_GATHER for kp in range(16, 34, 2))
