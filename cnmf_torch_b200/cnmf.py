@@ -76,7 +76,31 @@ def save_arrays_to_df_npz(filename, data, index, columns_member, level=1):
 
 
 def save_df_to_text(obj, filename):
-    obj.to_csv(filename, sep="\t")
+    """``obj.to_csv(filename, sep="\\t")`` (cnmf.py:44-45), byte for byte.  A plain float frame (the usage table of a
+    consensus call is cells x k: 100 000 rows at cfg-3) goes through the library's ``cnmf_b200_write_tsv``: the same
+    digits pandas writes (numpy's shortest round-trip repr), formatted by a few host threads -- pandas spent 0.6-1.2 s
+    per such table, most of a consensus call at that size.  Anything else goes to pandas."""
+    vals = obj.values if isinstance(obj, pd.DataFrame) else None
+    plain = (vals is not None and vals.ndim == 2 and vals.dtype in (np.float32, np.float64)
+             and not isinstance(obj.index, pd.MultiIndex) and not isinstance(obj.columns, pd.MultiIndex)
+             and vals.shape[0] >= 1000)
+    if plain:
+        idx = [str(v) for v in obj.index.tolist()]
+        head = [str(obj.index.name or "")] + [str(v) for v in obj.columns.tolist()]
+        special = ("\t", '"', "\n", "\r")
+        plain = not any(c in v for v in idx + head for c in special)
+    if not plain:
+        obj.to_csv(filename, sep="\t")
+        return
+    from ._lib import check, lib
+    vals = np.ascontiguousarray(vals)
+    enc = [v.encode() for v in idx]
+    off = np.zeros(len(enc) + 1, dtype=np.int64)
+    np.cumsum([len(v) for v in enc], out=off[1:])
+    header = ("\t".join(head) + "\n").encode()
+    check(lib().cnmf_b200_write_tsv(os.fspath(filename).encode(), header, len(header), b"".join(enc),
+                                    off.ctypes.data, vals.ctypes.data, int(vals.dtype == np.float64), vals.shape[0],
+                                    vals.shape[1], vals.shape[1], 0), "write_tsv")
 
 
 def _io_pool():

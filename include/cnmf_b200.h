@@ -433,6 +433,18 @@ int cnmf_b200_ols_xty(const int64_t* col_ptr, const int32_t* row_idx, const floa
 /* Number of kernel launches the last cnmf_b200_frob_iterate on this thread enqueued. */
 int64_t cnmf_b200_last_launch_count(void);
 
+/* ------------------------------------------------------------------------------------------
+ * Host-side helper of the on-disk path (no device work): a float table as tab-separated text, byte for byte what
+ * save_df_to_text writes (DataFrame.to_csv(sep="\t"), /root/reference/src/cnmf/cnmf.py:44-45): numpy's shortest
+ * round-trip repr of every value (positional for 1e-4 <= |x| < 1e16 -- 1e6 for float --, else scientific; NaN -> empty field), rows
+ * formatted by up to 16 host threads.  header: the first line incl. its '\n' (index name, tab, column labels);
+ * index_blob / index_off[n + 1]: the row labels, concatenated; data: [n x k] row-major with leading dimension ld,
+ * float (is_f64 = 0) or double (1).  threads <= 0: hardware concurrency.
+ * ---------------------------------------------------------------------------------------- */
+int cnmf_b200_write_tsv(const char* path, const char* header, int64_t header_len, const char* index_blob,
+                        const int64_t* index_off, const void* data, int32_t is_f64, int64_t n, int64_t k, int64_t ld,
+                        int32_t threads);
+
 #ifdef __cplusplus
 }
 #endif

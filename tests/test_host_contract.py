@@ -188,3 +188,32 @@ def test_kl_kernel_family_by_padded_k():
     assert kl_impl_for(pad2(11)) == kl_impl_for(12) == _lib.KL_IMPL_GATHER
     assert kl_impl_for(pad2(13)) == _lib.KL_IMPL_SLAB
     assert all(kl_impl_for(kp) == _lib.KL_IMPL_GATHER for kp in range(16, 34, 2))
+
+
+@pytest.mark.parametrize("dtype", [np.float32, np.float64])
+def test_text_tables_are_byte_identical_to_pandas(tmp_path, dtype):
+    """save_df_to_text (reference cnmf.py:44-45) through the library's host-side writer cnmf_b200_write_tsv: the
+    bytes pandas' to_csv(sep='\\t') writes -- ordinary values, the notation cut-overs, signed zeros, NaN / inf,
+    subnormals and 180 000 random bit patterns; a frame the fast path does not take (small, or labels that need
+    quoting) still goes through pandas."""
+    import pandas as pd
+    from cnmf_torch_b200.cnmf import save_df_to_text
+    rng = np.random.default_rng(5)
+    n = 30000
+    a = rng.random((n, 9)).astype(dtype)
+    edge = [1e-7, 3.5e10, 0.0, np.nan, 1e-45 if dtype == np.float32 else 5e-324, -2.5, 1e16, 123456789.0, 1e-4,
+            9.9999e-5, 1e15, 9.999999e15, -0.0, np.inf, -np.inf, 1.0, 100.0, 999999.0, 1e6, 1234567.0, 16777216.0,
+            0.00012345, 1e-5, 65504.0, 3.4e38, 1.17549435e-38]
+    a[:len(edge), 0] = np.array(edge, dtype=dtype)
+    bits = rng.integers(0, 2 ** 32 if dtype == np.float32 else 2 ** 63, size=(20000, 9), dtype=np.uint64)
+    a[5000:25000] = bits.astype(np.uint32).view(np.float32) if dtype == np.float32 else bits.view(np.float64)
+    for name in (None, "cell"):
+        df = pd.DataFrame(a, index=["cell_%d" % i for i in range(n)], columns=np.arange(1, 10))
+        df.index.name = name
+        save_df_to_text(df, tmp_path / "fast.txt")
+        df.to_csv(tmp_path / "pandas.txt", sep="\t")
+        assert (tmp_path / "fast.txt").read_bytes() == (tmp_path / "pandas.txt").read_bytes()
+    odd = pd.DataFrame(a[:1500], index=['c"%d' % i for i in range(1500)], columns=list("abcdefghi"))
+    save_df_to_text(odd, tmp_path / "odd.txt")
+    odd.to_csv(tmp_path / "odd_pandas.txt", sep="\t")
+    assert (tmp_path / "odd.txt").read_bytes() == (tmp_path / "odd_pandas.txt").read_bytes()
