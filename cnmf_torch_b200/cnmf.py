@@ -633,7 +633,8 @@ class cNMF:
 
 def _load_results(self, K, density_threshold, n_top_genes=100, norm_usage=True):
     """cnmf.py:1335-1385: (usage cells x K, spectra_scores genes x K, spectra_tpm genes x K, top_genes n_top x K) read
-    back from the text files ``consensus`` wrote for (K, density_threshold)."""
+    back from the text files ``consensus`` wrote for (K, density_threshold).  (Outside SURVEY section 8 -- a reader
+    of this path's own output files, kept as it was in round 1 and not developed further.)"""
     dt = str(density_threshold).replace(".", "_")
     spectra_scores = pd.read_csv(self.paths["gene_spectra_score__txt"] % (K, dt), sep="\t", index_col=0).T
     spectra_tpm = pd.read_csv(self.paths["gene_spectra_tpm__txt"] % (K, dt), sep="\t", index_col=0).T

@@ -4,6 +4,8 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <nvtx3/nvToolsExt.h>   // header-only; a no-op unless a profiler injects itself
+
 #include "../../include/cnmf_b200.h"
 
 namespace cnmf {
@@ -41,6 +43,18 @@ void reset_launch_count();
     }                                                                                      \
     cnmf::count_launch();                                                                  \
   } while (0)
+
+// Named range on the calling host thread for the profilers' timelines (Nsight Systems / Compute --nvtx): every
+// entry point of the library opens one, the engines one per stage (half-step, Gram, objective, chunk phase ...).
+struct NvtxRange {
+  explicit NvtxRange(const char* name) { nvtxRangePushA(name); }
+  ~NvtxRange() { nvtxRangePop(); }
+  NvtxRange(const NvtxRange&) = delete;
+  NvtxRange& operator=(const NvtxRange&) = delete;
+};
+#define CNMF_NVTX_CAT2(a, b) a##b
+#define CNMF_NVTX_CAT(a, b) CNMF_NVTX_CAT2(a, b)
+#define CNMF_NVTX(name) cnmf::NvtxRange CNMF_NVTX_CAT(_nvtx_, __LINE__)(name)
 
 #define CNMF_TRY(call)          \
   do {                          \

@@ -706,6 +706,7 @@ extern "C" {
 
 int cnmf_b200_pairwise_dist(const float* X, int64_t ld, int32_t M, int32_t G, float* D, int64_t ldd, double* sqnorm,
                             void* stream) {
+  CNMF_NVTX("cnmf_b200_pairwise_dist");
   CNMF_CHECK_ARG(X && D && sqnorm, "pairwise_dist: null pointer");
   CNMF_CHECK_ARG(M > 0 && G > 0 && ld >= G && ldd >= M, "pairwise_dist: bad shape");
   cudaStream_t st = (cudaStream_t)stream;
@@ -719,6 +720,7 @@ int cnmf_b200_pairwise_dist(const float* X, int64_t ld, int32_t M, int32_t G, fl
 
 int cnmf_b200_topk_density(const float* D, int64_t ldd, int32_t M, int32_t n_neighbors, float* density, int32_t* nbr,
                            void* stream) {
+  CNMF_NVTX("cnmf_b200_topk_density");
   CNMF_CHECK_ARG(D && density, "topk_density: null pointer");
   CNMF_CHECK_ARG(M > 0 && ldd >= M, "topk_density: bad shape");
   CNMF_CHECK_ARG(n_neighbors >= 1 && n_neighbors + 1 <= M, "topk_density: n_neighbors=%d needs 1 <= n and n+1 <= rows=%d",
@@ -737,6 +739,7 @@ int cnmf_b200_topk_density(const float* D, int64_t ldd, int32_t M, int32_t n_nei
 }
 
 int cnmf_b200_col_center(float* X, int64_t ld, int32_t M, int32_t G, float* mean, void* stream) {
+  CNMF_NVTX("cnmf_b200_col_center");
   CNMF_CHECK_ARG(X && mean && M > 0 && G > 0 && ld >= G, "col_center: bad argument");
   cudaStream_t st = (cudaStream_t)stream;
   col_mean_seq_kernel<<<(unsigned)ceil_div(G, 64), 64, 0, st>>>(X, ld, M, G, mean);
@@ -752,6 +755,7 @@ int64_t cnmf_b200_kmeans_workspace_bytes(int32_t n_init, int32_t k, int32_t G) {
 
 int cnmf_b200_kmeans_assign(const float* X, int64_t ld, int32_t M, int32_t G, const float* centers, int32_t n_init,
                             int32_t k, const uint8_t* active, int32_t* labels, int32_t* n_changed, void* stream) {
+  CNMF_NVTX("cnmf_b200_kmeans_assign");
   CNMF_CHECK_ARG(X && centers && labels && n_changed, "kmeans_assign: null pointer");
   CNMF_CHECK_ARG(M > 0 && G > 0 && n_init > 0 && k >= 1 && k <= KA_C, "kmeans_assign: need 1 <= k <= %d (k=%d)", KA_C, k);
   dim3 grid((unsigned)ceil_div(M, KA_S), n_init);
@@ -763,6 +767,7 @@ int cnmf_b200_kmeans_assign(const float* X, int64_t ld, int32_t M, int32_t G, co
 int cnmf_b200_kmeans_update(const float* X, int64_t ld, int32_t M, int32_t G, const int32_t* labels, int32_t n_init,
                             int32_t k, const uint8_t* active, const float* centers_old, float* centers_new,
                             float* center_shift, int32_t* counts, void* workspace, void* stream) {
+  CNMF_NVTX("cnmf_b200_kmeans_update");
   CNMF_CHECK_ARG(X && labels && centers_old && centers_new && center_shift && counts && workspace,
                  "kmeans_update: null pointer");
   CNMF_CHECK_ARG(M > 0 && G > 0 && n_init > 0 && k >= 1 && k <= KA_C, "kmeans_update: need 1 <= k <= %d", KA_C);
@@ -782,6 +787,7 @@ int64_t cnmf_b200_kmeans_inertia_blocks(int32_t M) { return ceil_div(M, 8); }
 
 int cnmf_b200_kmeans_inertia(const float* X, int64_t ld, int32_t M, int32_t G, const float* centers, int32_t n_init,
                              int32_t k, const int32_t* labels, double* partials, void* stream) {
+  CNMF_NVTX("cnmf_b200_kmeans_inertia");
   CNMF_CHECK_ARG(X && centers && labels && partials, "kmeans_inertia: null pointer");
   dim3 grid((unsigned)ceil_div(M, 8), n_init);
   kmeans_inertia_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(X, ld, M, G, centers, k, labels, partials);
@@ -791,6 +797,7 @@ int cnmf_b200_kmeans_inertia(const float* X, int64_t ld, int32_t M, int32_t G, c
 
 int cnmf_b200_cluster_median(const float* X, int64_t ld, int32_t G, const int32_t* order, const int32_t* offsets,
                              int32_t k, int32_t max_members, float* median, float* normalized, void* stream) {
+  CNMF_NVTX("cnmf_b200_cluster_median");
   CNMF_CHECK_ARG(X && order && offsets && median, "cluster_median: null pointer");
   CNMF_CHECK_ARG(k >= 1 && G > 0 && max_members >= 1, "cluster_median: bad shape");
   const size_t smem = (size_t)max_members * (MD_G + 1) * 4;
@@ -812,6 +819,7 @@ int cnmf_b200_cluster_median(const float* X, int64_t ld, int32_t G, const int32_
 }
 
 int cnmf_b200_l2_normalize(const float* S, int64_t lds, int32_t M, int32_t G, float* out, int64_t ldo, void* stream) {
+  CNMF_NVTX("cnmf_b200_l2_normalize");
   CNMF_CHECK_ARG(S && out && M > 0 && G > 0 && lds >= G && ldo >= G, "l2_normalize: bad argument");
   l2_normalize_kernel<<<(unsigned)ceil_div(M, 128), 128, 0, (cudaStream_t)stream>>>(S, lds, M, G, out, ldo);
   CNMF_LAUNCH_CHECK();
@@ -839,6 +847,7 @@ int64_t cnmf_b200_kmeanspp_workspace_bytes(int32_t M, int32_t n_init, int32_t n_
 int cnmf_b200_kmeanspp(const float* Xc, int64_t ld, int32_t M, int32_t G, int32_t n_init, int32_t k, int32_t n_trials,
                        const int32_t* first_idx, const double* rnd, int32_t* chosen, float* centers, void* workspace,
                        void* stream) {
+  CNMF_NVTX("cnmf_b200_kmeanspp");
   CNMF_CHECK_ARG(Xc && first_idx && chosen && centers && workspace && (rnd || k == 1), "kmeanspp: null pointer");
   CNMF_CHECK_ARG(M > 0 && G > 0 && k >= 1 && k <= M && ld >= G, "kmeanspp: bad shape");
   CNMF_CHECK_ARG(n_trials >= 1 && n_trials <= 8 && n_init >= 1 && n_init * n_trials <= KPP_NC,
@@ -877,6 +886,7 @@ int cnmf_b200_kmeanspp(const float* Xc, int64_t ld, int32_t M, int32_t G, int32_
 
 int cnmf_b200_silhouette(const float* D, int64_t ldd, int32_t M, const int32_t* labels, const int32_t* counts, int32_t k,
                          float* sil, void* stream) {
+  CNMF_NVTX("cnmf_b200_silhouette");
   CNMF_CHECK_ARG(D && labels && counts && sil, "silhouette: null pointer");
   CNMF_CHECK_ARG(M > 0 && ldd >= M && k >= 1 && k <= KA_C, "silhouette: need 1 <= k <= %d", KA_C);
   silhouette_kernel<<<M, SIL_THREADS, 0, (cudaStream_t)stream>>>(D, ldd, M, labels, counts, k, sil);
@@ -886,6 +896,7 @@ int cnmf_b200_silhouette(const float* D, int64_t ldd, int32_t M, const int32_t* 
 
 int cnmf_b200_ols_xty(const int64_t* col_ptr, const int32_t* row_idx, const float* val, int32_t n_targets, const float* X,
                       int32_t K, double* xty, double* ysum, double* ysq, void* stream) {
+  CNMF_NVTX("cnmf_b200_ols_xty");
   CNMF_CHECK_ARG(col_ptr && row_idx && val && X && xty && ysum && ysq, "ols_xty: null pointer");
   CNMF_CHECK_ARG(n_targets > 0 && K >= 1 && K <= 32, "ols_xty: need 1 <= K <= 32 predictors");
   ols_xty_kernel<<<(unsigned)ceil_div(n_targets, 8), 256, 0, (cudaStream_t)stream>>>(col_ptr, row_idx, val, n_targets, X, K,

@@ -434,6 +434,7 @@ __global__ void __launch_bounds__(32) objective_combine_kernel(double normX2, co
 int gram_num_tiles(int64_t L, int Kp) { return Kp <= 12 ? (int)ceil_div(L, GW_SPLIT) : (int)gram_tiles(L); }
 
 int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, void* ws, cudaStream_t st) {
+  CNMF_NVTX("frob: Gram partials");
   float* partial = reinterpret_cast<float*>(ws);
   if (Kp <= 12) {
     const int ns = (int)ceil_div(L, GW_SPLIT);
@@ -480,6 +481,7 @@ int launch_gram_final(const void* ws, int64_t L, int R, int Kp, float* gram, cud
 
 int launch_gram(const float* F, int64_t ld, int R, int Kp, int64_t L, float* gram, void* ws,
                 cudaStream_t st) {
+  CNMF_NVTX("frob: Gram");
   CNMF_TRY(launch_gram_partial(F, ld, R, Kp, L, ws, st));
   return launch_gram_final(ws, L, R, Kp, gram, st);
 }
@@ -554,6 +556,7 @@ int64_t cnmf_b200_sumsq_workspace_bytes(void) { return SUMSQ_BLOCKS * (int64_t)s
 
 int cnmf_b200_sumsq(const float* x, int64_t rows, int64_t cols, int64_t ld, double* out,
                     void* workspace, void* stream) {
+  CNMF_NVTX("cnmf_b200_sumsq");
   CNMF_CHECK_ARG(x && out && workspace, "sumsq: null pointer");
   CNMF_CHECK_ARG(rows >= 0 && cols >= 0 && ld >= cols, "sumsq: bad shape %lld x %lld ld %lld",
                  (long long)rows, (long long)cols, (long long)ld);
@@ -581,6 +584,7 @@ int64_t cnmf_b200_gram_workspace_bytes(int32_t R, int32_t Kp, int64_t L) {
 
 int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
                    void* workspace, void* stream) {
+  CNMF_NVTX("cnmf_b200_gram");
   CNMF_CHECK_ARG(F && gram && workspace, "gram: null pointer");
   CNMF_CHECK_ARG(R > 0 && L > 0 && ld >= L, "gram: bad shape R=%d L=%lld ld=%lld", R, (long long)L,
                  (long long)ld);
@@ -590,6 +594,7 @@ int cnmf_b200_gram(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L,
 
 int cnmf_b200_gemm_nt(const float* A, int64_t lda, int64_t M, const float* B, int64_t ldb, int64_t N,
                       int64_t Kd, float* C, int64_t ldc, void* stream) {
+  CNMF_NVTX("cnmf_b200_gemm_nt");
   CNMF_CHECK_ARG(A && B && C, "gemm_nt: null pointer");
   CNMF_CHECK_ARG(M > 0 && N > 0 && Kd > 0, "gemm_nt: empty shape");
   CNMF_CHECK_ARG(lda % 4 == 0 && ldb % 4 == 0 && ldc % 4 == 0 && aligned16(A) && aligned16(B) &&
@@ -656,6 +661,7 @@ int64_t cnmf_b200_gram_static_max_floats(void) { return GRAM_STATIC_FLOATS; }
  *     threads on the same device) race on it.  Keep them on one stream or serialise them. */
 int cnmf_b200_gram_static(const float* F, int64_t ld, int32_t R, int32_t Kp, int64_t L, float* gram,
                           void* stream) {
+  CNMF_NVTX("cnmf_b200_gram_static");
   CNMF_CHECK_ARG(F && gram, "gram_static: null pointer");
   CNMF_CHECK_ARG(R > 0 && L > 0 && ld >= L, "gram_static: bad shape R=%d L=%lld ld=%lld", R, (long long)L,
                  (long long)ld);
@@ -677,6 +683,7 @@ int64_t cnmf_b200_row_update_blocks(int64_t M) { return ceil_div(M, RU_THREADS);
 int cnmf_b200_row_update(const float* Pt, int64_t ldp, float* state, int64_t lds, const float* gram,
                          const uint8_t* active, int64_t M, int32_t R, int32_t Kp, int32_t algo, float l1,
                          float l2, float eps, double* partials, void* stream) {
+  CNMF_NVTX("cnmf_b200_row_update");
   CNMF_CHECK_ARG(Pt && state && gram && partials, "row_update: null pointer");
   CNMF_CHECK_ARG(M > 0 && R > 0 && ldp >= M && lds >= M, "row_update: bad shape");
   return launch_row_update(Pt, ldp, state, lds, gram, active, M, R, Kp, algo, l1, l2, eps, partials,

@@ -832,6 +832,7 @@ int launch_tc_half_step_g(const float* A, int64_t lda, int64_t M, int64_t Kd, co
                           float* state, float* state_op, int64_t lds, const float* gram, int gram_ntile,
                           const uint8_t* active, int R, int Kp, int algo, float l1, float l2, float eps,
                           double* partials, cudaStream_t st, const uint8_t* rep_k, const float* F2, float* state_lo) {
+  CNMF_NVTX("frob: tcgen05 half-step (GEMM + fused MU/HALS update)");
   TcPlan plan;
   const int sms = tc_num_sms();
   if (!tc_plan(M, Kd, R, Kp, sms, &plan)) {
@@ -874,6 +875,7 @@ using namespace cnmf;
 extern "C" {
 
 int cnmf_b200_round_tf32(float* x, int64_t n, void* stream) {
+  CNMF_NVTX("cnmf_b200_round_tf32");
   CNMF_CHECK_ARG(x != nullptr && n >= 0, "round_tf32: bad argument");
   return launch_round_tf32(x, x, n, (cudaStream_t)stream);
 }
@@ -882,6 +884,7 @@ int cnmf_b200_dense_half_step(const float* A, int64_t lda, int64_t M, int64_t Kd
                               float* state, float* state_tf32, int64_t lds, const float* gram,
                               const uint8_t* active, int32_t R, int32_t Kp, int32_t algo, float l1, float l2,
                               float eps, double* partials, void* stream) {
+  CNMF_NVTX("cnmf_b200_dense_half_step");
   CNMF_CHECK_ARG(A && F && state && gram, "dense_half_step: null pointer");
   CNMF_CHECK_ARG(M > 0 && Kd > 0 && R > 0, "dense_half_step: empty shape");
   CNMF_CHECK_ARG(lda % 4 == 0 && ldf % 4 == 0 && aligned16(A) && aligned16(F),
@@ -897,6 +900,7 @@ int cnmf_b200_dense_half_step_k(const float* A, int64_t lda, int64_t M, int64_t 
                                 float* state, float* state_tf32, int64_t lds, const float* gram,
                                 const uint8_t* active, const uint8_t* rep_k, int32_t R, int32_t Kp, int32_t algo,
                                 float l1, float l2, float eps, double* partials, void* stream) {
+  CNMF_NVTX("cnmf_b200_dense_half_step_k");
   CNMF_CHECK_ARG(A && F && state && gram, "dense_half_step_k: null pointer");
   CNMF_CHECK_ARG(M > 0 && Kd > 0 && R > 0, "dense_half_step_k: empty shape");
   CNMF_CHECK_ARG(lda % 4 == 0 && ldf % 4 == 0 && aligned16(A) && aligned16(F),

@@ -142,6 +142,7 @@ int64_t cnmf_b200_frob_workspace_bytes(const cnmf_b200_frob_problem* p) {
 }
 
 int cnmf_b200_frob_prepare(const cnmf_b200_frob_problem* p, void* stream) {
+  CNMF_NVTX("cnmf_b200_frob_prepare");
   CNMF_TRY(check_problem(p));
   CNMF_TRY(check_pointers(p));
   FrobLayout l = frob_layout(p);
@@ -161,6 +162,7 @@ int cnmf_b200_frob_prepare(const cnmf_b200_frob_problem* p, void* stream) {
 }
 
 int cnmf_b200_frob_iterate(const cnmf_b200_frob_problem* p, int32_t n_iters, void* stream) {
+  CNMF_NVTX("cnmf_b200_frob_iterate");
   reset_launch_count();
   CNMF_TRY(check_problem(p));
   CNMF_TRY(check_pointers(p));
@@ -290,6 +292,7 @@ static int frob_objective_common(const cnmf_b200_frob_problem* p, FrobLayout* l)
 }
 
 int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
+  CNMF_NVTX("cnmf_b200_frob_objective");
   reset_launch_count();
   FrobLayout l;
   CNMF_TRY(frob_objective_common(p, &l));
@@ -307,6 +310,7 @@ int cnmf_b200_frob_objective(const cnmf_b200_frob_problem* p, void* stream) {
  * gramH = local H^T H, gramW = W W^T.  The caller all-reduces sums[:, 0], sums[:, 2] and gramH across
  * ranks (W is replicated) and then calls cnmf_b200_frob_objective_combine. */
 int cnmf_b200_frob_objective_parts(const cnmf_b200_frob_problem* p, double* sums, void* stream) {
+  CNMF_NVTX("cnmf_b200_frob_objective_parts");
   reset_launch_count();
   FrobLayout l;
   CNMF_TRY(frob_objective_common(p, &l));
@@ -321,6 +325,7 @@ int cnmf_b200_frob_objective_parts(const cnmf_b200_frob_problem* p, double* sums
 int cnmf_b200_frob_objective_combine(double normX2, const double* sums, const float* gramW, const float* gramH,
                                      int32_t R, int32_t Kp, float l1_H, float l2_H, float l1_W, float l2_W,
                                      double* err2, void* stream) {
+  CNMF_NVTX("cnmf_b200_frob_objective_combine");
   CNMF_CHECK_ARG(sums && gramW && gramH && err2 && R > 0 && Kp > 0, "frob_objective_combine: bad argument");
   return launch_objective_combine(normX2, sums, gramW, gramH, R, Kp, l1_H, l2_H, l1_W, l2_W, err2,
                                   (cudaStream_t)stream);

@@ -76,6 +76,7 @@ using namespace cnmf;
 extern "C" int cnmf_b200_init_random(const int64_t* seeds, int32_t R, int32_t K, int32_t Kp, int64_t n_total,
                                      int64_t n_local, int64_t row_offset, int64_t n_genes, float avg, float* Ht,
                                      int64_t ldh, float* Wall, int64_t ldw, void* stream) {
+  CNMF_NVTX("cnmf_b200_init_random");
   CNMF_CHECK_ARG(seeds && Ht && Wall, "init_random: null pointer");
   CNMF_CHECK_ARG(R > 0 && K > 0 && Kp >= K && n_total > 0 && n_local > 0 && n_genes > 0 && row_offset >= 0 &&
                      row_offset + n_local <= n_total && ldh >= n_local && ldw >= n_genes,

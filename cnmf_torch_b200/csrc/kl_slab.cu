@@ -540,6 +540,7 @@ int64_t ks_pairs_max(int64_t nnz, int64_t nseg_max, int Kp) { return nnz + nseg_
 
 int launch_kl_pack_pairs(const KlSegs& sg, int64_t V, int64_t M, int block, int Kp, const int* col_idx, const float* val,
                          const int* wcum, void* pairs, cudaStream_t st) {
+  CNMF_NVTX("kl: pack (column, value) pairs");
   kl_pack_pairs_kernel<<<148 * 8, 256, 0, st>>>(sg.vseg_ptr, V, M, block > 0 ? block : 1, sg.seg_vrow, sg.seg_beg, sg.vend,
                                                 sg.seg_len, 2 * (Kp / 2), KS_SEG_OVERHEAD_STEPS, col_idx, val, wcum,
                                                 reinterpret_cast<uint2*>(pairs));
@@ -584,6 +585,7 @@ static int ks_grid() {
 }
 
 int launch_kl_slab(const KlSlabArgs& a, int Kp, int mode, cudaStream_t st) {
+  CNMF_NVTX("kl: slab half-step / objective pass");
   const int grid = a.grid > 0 ? a.grid : ks_grid();
   if (mode == 0) {
     KS_DISPATCH_KP(Kp, return (launch_slab_inst<KP, 0>(a, grid, st)));
@@ -595,6 +597,7 @@ int launch_kl_slab(const KlSlabArgs& a, int Kp, int mode, cudaStream_t st) {
 
 int launch_kl_finish_slab(int64_t M, float* state, void* state16, const float* fsum, const uint8_t* active, int R, int Kp,
                           float l1, float l2, float eps, const KlSegs& sg, int* flag, cudaStream_t st) {
+  CNMF_NVTX("kl: finish rows (sum partials, update, fp16 line)");
   const int ngroups = ks_num_groups(R, Kp);
   const int64_t blocks = ceil_div(M * R, 128);
   CNMF_CHECK_ARG(blocks < (1ll << 31), "kl: rows * replicates too large for one launch");

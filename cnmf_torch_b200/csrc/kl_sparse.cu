@@ -516,6 +516,7 @@ __global__ void __launch_bounds__(1024) kl_constants_kernel(const float* __restr
 
 static int launch_colsum(const float* A, int64_t L, int64_t C, float* out, double* out64, float* partial,
                          cudaStream_t st, bool squares = false) {
+  CNMF_NVTX("kl: column sums");
   const int nslab = (int)ceil_div(L, CS_ROWS);
   dim3 grid((unsigned)ceil_div(C, 128), nslab);
   if (squares) colsum_partial_kernel<true><<<grid, 128, 0, st>>>(A, L, C, partial);
@@ -558,6 +559,7 @@ static int launch_kl_half(const int* rp, const int* ci, const float* v, int64_t 
                           __half* state_h, const float* fsum, const uint8_t* active, int R, int Kp, float l1, float l2,
                           float eps, cudaStream_t st, const KlSegs* sg = nullptr, int64_t nseg_max = 0,
                           int64_t multi_max = 0, int gr = 0) {
+  CNMF_NVTX("kl: gather half-step");
   if (gr >= R) gr = 0;
   const int64_t Rpad = gr > 0 ? ceil_div(R, gr) * gr : R;   // group-major numbering: the last group is padded
   const int64_t blocks = ceil_div((sg ? nseg_max : M) * Rpad, KL_THREADS);
@@ -872,6 +874,7 @@ using namespace cnmf;
 extern "C" {
 
 int cnmf_b200_kl_constants(const float* val, int64_t nnz, double* out2, void* stream) {
+  CNMF_NVTX("cnmf_b200_kl_constants");
   CNMF_CHECK_ARG(val && out2 && nnz >= 0, "kl_constants: bad argument");
   kl_constants_kernel<<<1, 1024, 0, (cudaStream_t)stream>>>(val, nnz, out2);
   CNMF_LAUNCH_CHECK();
@@ -884,6 +887,7 @@ int64_t cnmf_b200_kl_workspace_bytes(const cnmf_b200_kl_problem* p) {
 }
 
 int cnmf_b200_to_half(const float* src, void* dst, int64_t n, void* stream) {
+  CNMF_NVTX("cnmf_b200_to_half");
   CNMF_CHECK_ARG(src && dst && n >= 0, "to_half: bad argument");
   return launch_to_half(src, reinterpret_cast<__half*>(dst), n, (cudaStream_t)stream);
 }
@@ -891,6 +895,7 @@ int cnmf_b200_to_half(const float* src, void* dst, int64_t n, void* stream) {
 int cnmf_b200_kl_half_step(const int32_t* row_ptr, const int32_t* col_idx, const float* val, int64_t M,
                            const void* F_half, float* state, void* state_half, const float* fsum,
                            const uint8_t* active, int32_t R, int32_t Kp, float l1, float l2, float eps, void* stream) {
+  CNMF_NVTX("cnmf_b200_kl_half_step");
   CNMF_CHECK_ARG(row_ptr && col_idx && val && F_half && state && fsum, "kl_half_step: null pointer");
   CNMF_CHECK_ARG(M > 0 && R > 0, "kl_half_step: empty shape");
   CNMF_CHECK_ARG((reinterpret_cast<uintptr_t>(F_half) & 7u) == 0 && aligned16(state) && aligned16(fsum),
@@ -900,6 +905,7 @@ int cnmf_b200_kl_half_step(const int32_t* row_ptr, const int32_t* col_idx, const
 }
 
 int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* stream) {
+  CNMF_NVTX("cnmf_b200_kl_iterate");
   reset_launch_count();
   CNMF_TRY(kl_check(p, true));
   CNMF_CHECK_ARG(n_iters >= 0, "kl: n_iters < 0");
@@ -961,6 +967,7 @@ int cnmf_b200_kl_iterate(const cnmf_b200_kl_problem* p, int32_t n_iters, void* s
 }
 
 int cnmf_b200_kl_objective(const cnmf_b200_kl_problem* p, void* stream) {
+  CNMF_NVTX("cnmf_b200_kl_objective");
   reset_launch_count();
   CNMF_TRY(kl_check(p, true));
   CNMF_CHECK_ARG(p->err2 != nullptr, "kl_objective: err2 is NULL");
@@ -974,6 +981,7 @@ int cnmf_b200_kl_objective(const cnmf_b200_kl_problem* p, void* stream) {
 }
 
 int cnmf_b200_kl_range_flag(const cnmf_b200_kl_problem* p, int32_t* flag_host, void* stream) {
+  CNMF_NVTX("cnmf_b200_kl_range_flag");
   CNMF_TRY(kl_check(p, true));
   CNMF_CHECK_ARG(flag_host != nullptr, "kl_range_flag: null output");
   const KlLayout l = kl_layout(p);
@@ -984,6 +992,7 @@ int cnmf_b200_kl_range_flag(const cnmf_b200_kl_problem* p, int32_t* flag_host, v
 }
 
 int cnmf_b200_kl_range_flag_clear(const cnmf_b200_kl_problem* p, void* stream) {
+  CNMF_NVTX("cnmf_b200_kl_range_flag_clear");
   CNMF_TRY(kl_check(p, true));
   const KlLayout l = kl_layout(p);
   CNMF_CUDA(cudaMemsetAsync(reinterpret_cast<char*>(p->workspace) + l.off_flag, 0, 4, (cudaStream_t)stream));

@@ -323,6 +323,7 @@ extern "C" {
 int cnmf_b200_dense_gemm_tf32(const float* A, int64_t lda, int64_t M, int64_t Kd, const float* F, int64_t ldf,
                               float* out, int64_t ldo, const uint8_t* active, int32_t R, int32_t Kp, int32_t accumulate,
                               void* stream) {
+  CNMF_NVTX("cnmf_b200_dense_gemm_tf32");
   CNMF_CHECK_ARG(A && F && out, "dense_gemm_tf32: null pointer");
   CNMF_CHECK_ARG(M > 0 && Kd > 0 && R > 0, "dense_gemm_tf32: empty shape");
   CNMF_CHECK_ARG(lda % 4 == 0 && ldf % 4 == 0 && aligned16(A) && aligned16(F),
@@ -334,11 +335,13 @@ int cnmf_b200_dense_gemm_tf32(const float* A, int64_t lda, int64_t M, int64_t Kd
 }
 
 int cnmf_b200_round_tf32_2d(float* dst, const float* src, int64_t rows, int64_t cols, int64_t ld, void* stream) {
+  CNMF_NVTX("cnmf_b200_round_tf32_2d");
   CNMF_CHECK_ARG(dst && src && rows >= 0 && cols >= 0 && ld >= cols, "round_tf32_2d: bad argument");
   return launch_round_tf32_2d(dst, src, rows, cols, ld, (cudaStream_t)stream);
 }
 
 int cnmf_b200_axpy(float* y, const float* x, int64_t n, void* stream) {
+  CNMF_NVTX("cnmf_b200_axpy");
   CNMF_CHECK_ARG(y && x && n >= 0, "axpy: bad argument");
   if (n == 0) return 0;
   int64_t blocks = ceil_div(n, 256 * 4);
@@ -356,6 +359,7 @@ int cnmf_b200_online_inner(const float* Pt, int64_t ldp, float* state, int64_t l
                            const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                            float tol, int32_t n_iters, int32_t* iters, int32_t* n_pending, void* workspace,
                            void* stream) {
+  CNMF_NVTX("cnmf_b200_online_inner");
   reset_launch_count();
   CNMF_CHECK_ARG(Pt && state && gram && done && iters && n_pending && workspace, "online_inner: null pointer");
   CNMF_CHECK_ARG(M > 0 && R > 0 && ldp >= M && lds >= M && n_iters >= 0, "online_inner: bad shape");
@@ -391,6 +395,7 @@ int cnmf_b200_online_loop(const float* Pt, int64_t ldp, float* state, int64_t ld
                           const uint8_t* active, int64_t M, int32_t R, int32_t Kp, float l1, float l2, float eps,
                           float tol, int32_t max_iter, int32_t* iters, unsigned long long* max_iters_seen,
                           void* workspace, void* stream) {
+  CNMF_NVTX("cnmf_b200_online_loop");
   return online_loop_impl(Pt, ldp, state, lds, gram, active, M, R, Kp, l1, l2, eps, tol, max_iter, iters, max_iters_seen,
                           workspace, nullptr, nullptr, nullptr, nullptr, 0, stream);
 }
@@ -474,6 +479,7 @@ static int online_loop_impl(const float* Pt, int64_t ldp, float* state, int64_t 
  *   phase CNMF_B200_ONLINE_SPECTRA : A += Ac, B += Bc (after the caller's all-reduce when cells are sharded), inner
  *                                    loop on W against (A, B), then W's tf32 copy, its residual and Gram. */
 int cnmf_b200_online_chunk(const cnmf_b200_online_chunk_args* a, int32_t phase, void* stream) {
+  CNMF_NVTX("cnmf_b200_online_chunk");
   reset_launch_count();
   CNMF_CHECK_ARG(a != nullptr, "online_chunk: null arguments");
   CNMF_CHECK_ARG(a->R > 0 && a->Kp > 0 && a->n_genes > 0, "online_chunk: empty shape");

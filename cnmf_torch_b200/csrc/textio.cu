@@ -107,6 +107,7 @@ static int write_tsv(const char* path, const char* header, int64_t header_len, c
 extern "C" int cnmf_b200_write_tsv(const char* path, const char* header, int64_t header_len, const char* index_blob,
                                    const int64_t* index_off, const void* data, int32_t is_f64, int64_t n, int64_t k,
                                    int64_t ld, int32_t threads) {
+  CNMF_NVTX("cnmf_b200_write_tsv");
   using namespace cnmf;
   CNMF_CHECK_ARG(path && header && index_blob && index_off && data, "write_tsv: null pointer");
   CNMF_CHECK_ARG(n >= 0 && k >= 0 && ld >= k && header_len >= 0, "write_tsv: bad shape");
