@@ -288,7 +288,8 @@ class DenseFrobeniusEngine:
         R, Kp, N, G = b.R, b.Kp, self.N, self.G
         rk = R * Kp
         ldw, ldh = b.p.ldw, b.p.ldh
-        st = FrobBatch._stream
+        _stream_now = FrobBatch._stream()     # one lookup per call (a torch.cuda.current_stream() costs ~14 us; a small run
+        st = lambda: _stream_now              # made 18 of them): the call runs on the stream current at entry
         cmax = max(1, min(chunk_size, N))
         ldp = pad_ld(cmax)
         f32 = dict(device=dev, dtype=torch.float32)
