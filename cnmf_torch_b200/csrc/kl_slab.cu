@@ -155,7 +155,8 @@ __global__ void __launch_bounds__(KS_THREADS, 1) kl_slab_kernel(const KlSlabArgs
     const int npair = (a.RP - rp0) < RGP ? (a.RP - rp0) : RGP;
     const bool pair_on = lane_on && rp < npair;
     const int rep0 = 2 * (rp0 + rp), rep1 = rep0 + 1;
-    bool group_active = a.active == nullptr;
+    // (the objective pass, MODE 1, covers frozen replicates too: their value is reported with every check)
+    bool group_active = a.active == nullptr || MODE == 1;
     if (!group_active)
       for (int r = 2 * rp0; r < 2 * (rp0 + npair) && r < a.R; ++r) group_active |= a.active[r] != 0;
     if (!group_active || s_begin >= s_end) continue;

@@ -111,17 +111,17 @@ class SparseKLEngine:
         return KlBatch(self, K, H0, W0, l1_H, l2_H, l1_W, l2_W, eps)
 
     def factorize(self, K, seeds=None, H0=None, W0=None, algo="mu", tol=1e-4, max_iter=500, l1_H=0.0, l2_H=0.0,
-                  l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False) -> BatchResult:
+                  l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False, compact=0.8) -> BatchResult:
         """Batch-mode KL MU of R replicates; same stopping rule as the Frobenius engine."""
         if algo != "mu":
             raise NotImplementedError("only multiplicative updates exist for beta_loss='kullback-leibler'")
         b = self.new_batch(K, seeds, H0, W0, l1_H, l2_H, l1_W, l2_W, eps)
-        r = _run_kl_batch(b, tol, max_iter, check_every)
+        r = _run_kl_batch(b, tol, max_iter, check_every, compact)
         W, H = b.results(return_H)
         return BatchResult(W=W, H=H, launches=int(b.launches), **r)
 
     def factorize_many(self, ks, seeds_by_k, algo="mu", tol=1e-4, max_iter=500, l1_H=0.0, l2_H=0.0, l1_W=0.0,
-                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False):
+                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False, compact=0.8):
         """Several K in one call (the shape of a cNMF run: K = 5..13 x 100 replicates).  K values that round up to
         the same even Kp are stacked into ONE batch (K = 9, 10 -> Kp 10): the kernels only see Kp, a taller stack
         fills the replicate groups of the slab kernel better (13 replicates of one K on one of 8 GPUs are 2 groups
@@ -136,7 +136,7 @@ class SparseKLEngine:
         for group in stacks.values():
             groups = [(k,) + tuple(self._init_for(k, seeds_by_k[k])) for k in group]
             b = KlBatch(self, None, None, None, l1_H, l2_H, l1_W, l2_W, eps, groups=groups)
-            r = _run_kl_batch(b, tol, max_iter, check_every)
+            r = _run_kl_batch(b, tol, max_iter, check_every, compact)
             for k, sl, W, H in b.results_by_group(return_H):
                 out[k] = BatchResult(W=W, H=H, err=r["err"][sl], n_iter=r["n_iter"][sl],
                                      trace=[(it, v[sl]) for it, v in r["trace"]], launches=int(b.launches))
@@ -144,29 +144,48 @@ class SparseKLEngine:
         return out
 
 
-def _run_kl_batch(b: "KlBatch", tol, max_iter, check_every):
+def _run_kl_batch(b: "KlBatch", tol, max_iter, check_every, compact=0.8):
     """run_nmf's batch loop on a resident KL batch: objective every ``check_every`` iterations, replicates with
-    prev <= cur or |prev - cur| / init < tol are frozen."""
+    prev <= cur or |prev - cur| / init < tol are frozen.
+
+    Frozen replicates still occupy lanes (a slab group of 6 is skipped only when all of them are frozen; a gather warp
+    covers 32 consecutive replicates), and the replicates of a stack converge at very different iteration counts, so
+    once no more than ``compact`` of the working batch is alive the live replicates are copied into a smaller batch
+    (``KlBatch.subset``) and the loop continues there; their state is copied back at the end (or at the next
+    compaction).  Replicates are independent and every reduction is per replicate in a fixed order, so the results
+    are bit-identical to the uncompacted run (``tests/test_gpu_kl.py::test_kl_compaction_is_bit_identical``).
+    ``compact=0`` turns it off."""
     R = b.R
     init = b.objective()
-    prev, cur = init.copy(), init
+    prev, cur = init.copy(), init.copy()
     trace = [(0, init.copy())]
     n_iter = np.full(R, max_iter, dtype=np.int64)
     alive = np.ones(R, dtype=bool)
+    wb, widx = b, np.arange(R)          # the working batch and its replicates' positions in b
     it = 0
     while it < max_iter and alive.any():
         step = min(check_every, max_iter - it)
-        b.iterate(step)
+        wb.iterate(step)
         it += step
-        cur = b.read_loss()
+        cur[widx] = wb.read_loss()
         trace.append((it, cur.copy()))
         if it % check_every == 0:
             conv = alive & ((prev <= cur) | (np.abs((prev - cur) / init) < tol))
             if conv.any():
                 n_iter[conv] = it
                 alive &= ~conv
-                b.set_active(alive)
+                wb.set_active(alive[widx])
             prev = np.where(alive, cur, prev)
+            n_alive = int(alive.sum())
+            if compact > 0 and 0 < n_alive <= compact * wb.R and wb.R - n_alive >= 6 and it < max_iter:
+                if wb is not b:
+                    b.absorb(wb, widx)
+                else:
+                    b.release_workspace()
+                widx = np.flatnonzero(alive)
+                wb = b.subset(widx)
+    if wb is not b:
+        b.absorb(wb, widx)
     return dict(err=np.sqrt(np.maximum(2.0 * cur, 0.0)), n_iter=n_iter, trace=trace)
 
 
@@ -214,6 +233,14 @@ class KlBatch:
         if eng.c != 1.0:               # the engine's units: X * c^2 = (cH)(cW); a power of two, exact
             self.Hr.mul_(eng.c)
             self.Wt.mul_(eng.c)
+        self._regs = (l1_H, l2_H, l1_W, l2_W, eps)
+        self._setup_problem()
+
+    def _setup_problem(self):
+        """Masks, outputs, the C-ABI problem struct and its workspace for the factors this batch holds."""
+        eng, R, Kp = self.eng, self.R, self.Kp
+        dev = eng.device
+        l1_H, l2_H, l1_W, l2_W, eps = self._regs
         self.active = torch.ones(R, device=dev, dtype=torch.uint8)
         self.err2 = torch.zeros(R, device=dev, dtype=torch.float64)
         self.p = KlProblem(
@@ -229,6 +256,31 @@ class KlBatch:
         self.p.workspace, self.p.workspace_bytes = ptr(self.ws), self.ws.numel()
         check(eng.lib.cnmf_b200_kl_range_flag_clear(C.byref(self.p), eng._stream()), "kl_range_flag_clear")
         self.launches = 0
+
+    def subset(self, idx) -> "KlBatch":
+        """A new batch holding copies of the replicates ``idx`` of this one (current state, same strengths): what
+        ``_run_kl_batch`` continues on once enough replicates of a stack are frozen.  ``absorb`` copies them back."""
+        sub = object.__new__(KlBatch)
+        sub.eng, sub.Ks, sub.Rs, sub.K, sub.Kp, sub.R = self.eng, None, None, self.K, self.Kp, len(idx)
+        ii = torch.as_tensor(np.asarray(idx), device=self.eng.device, dtype=torch.long)
+        sub.Hr = self.Hr.index_select(1, ii)
+        sub.Wt = self.Wt.index_select(1, ii)
+        sub._regs = self._regs
+        sub._setup_problem()
+        return sub
+
+    def absorb(self, sub: "KlBatch", idx):
+        """Replicates ``idx`` of this batch take the state of ``sub`` (made by ``subset(idx)``)."""
+        ii = torch.as_tensor(np.asarray(idx), device=self.eng.device, dtype=torch.long)
+        self.Hr.index_copy_(1, ii, sub.Hr)
+        self.Wt.index_copy_(1, ii, sub.Wt)
+        self.launches += sub.launches
+        self.invalidate()
+
+    def release_workspace(self):
+        """Give the workspace back (a stack whose live replicates moved to a subset keeps only its factors)."""
+        self.ws = None
+        self.p.workspace, self.p.workspace_bytes = None, 0
 
     def objective(self):
         check(self.eng.lib.cnmf_b200_kl_objective(C.byref(self.p), self.eng._stream()), "kl_objective")

@@ -331,3 +331,23 @@ def test_kl_large_ratios_are_held(problem):
         w = no.mu_kl_W(xt, h, W0[r], 0.0, 0.0, 1e-16)
         np.testing.assert_allclose(H[r], h.numpy(), rtol=3e-3, atol=1e-6)
         np.testing.assert_allclose(W[r], w.numpy(), rtol=3e-3, atol=1e-6)
+
+
+def test_kl_compaction_is_bit_identical(problem):
+    """Once most replicates of a stack are frozen the live ones continue in a smaller batch (kl_engine._run_kl_batch);
+    replicates are independent, so spectra, usages, objectives and iteration counts equal the uncompacted run's bit
+    for bit -- on a mixed-K stack whose replicates stop at different checks."""
+    from cnmf_torch_b200.kl_engine import SparseKLEngine
+    eng = SparseKLEngine(problem)
+    seeds = {5: list(range(100, 114)), 6: list(range(200, 213))}
+    kw = dict(tol=2e-4, max_iter=300, return_H=True)
+    a = eng.factorize_many([5, 6], seeds, compact=0.8, **kw)
+    b = eng.factorize_many([5, 6], seeds, compact=0.0, **kw)
+    stops = set()
+    for k in (5, 6):
+        np.testing.assert_array_equal(a[k].n_iter, b[k].n_iter)
+        np.testing.assert_array_equal(a[k].W, b[k].W)
+        np.testing.assert_array_equal(a[k].H, b[k].H)
+        np.testing.assert_array_equal(a[k].err, b[k].err)
+        stops |= set(a[k].n_iter.tolist())
+    assert len(stops) >= 3           # replicates did stop at different checks, so the compaction was exercised
