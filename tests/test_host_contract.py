@@ -217,3 +217,20 @@ def test_text_tables_are_byte_identical_to_pandas(tmp_path, dtype):
     save_df_to_text(odd, tmp_path / "odd.txt")
     odd.to_csv(tmp_path / "odd_pandas.txt", sep="\t")
     assert (tmp_path / "odd.txt").read_bytes() == (tmp_path / "odd_pandas.txt").read_bytes()
+
+
+def test_large_frames_round_trip_through_the_fast_npz_writer(tmp_path):
+    """save_df_to_npz (reference cnmf.py:32-34) takes the zip writer of the replicate files for a large frame; the
+    reference's loader (np.load + DataFrame(**f), cnmf.py:37-41) reads it back unchanged, suffix rule included."""
+    import pandas as pd
+    from cnmf_torch_b200.cnmf import load_df_from_npz, save_df_to_npz
+    rng = np.random.default_rng(3)
+    df = pd.DataFrame(rng.random((30000, 7)).astype(np.float32), index=["cell_%d" % i for i in range(30000)],
+                      columns=np.arange(1, 8))
+    save_df_to_npz(df, str(tmp_path / "usages.df.npz"))
+    save_df_to_npz(df, str(tmp_path / "nosuffix"))
+    for name in ("usages.df.npz", "nosuffix.npz"):
+        back = load_df_from_npz(tmp_path / name)
+        pd.testing.assert_frame_equal(back, df, check_names=False)
+        with np.load(tmp_path / name, allow_pickle=True) as f:
+            assert list(f.keys()) == ["data", "index", "columns"]
