@@ -55,8 +55,24 @@ def _npy_bytes(arr):
 def _deflated_member(name, payload, level=1):
     """(name, crc32, uncompressed size, raw-deflate bytes) of one archive member; zlib releases the GIL."""
     import zlib
-    co = zlib.compressobj(level, zlib.DEFLATED, -15)
-    return (name.encode(), zlib.crc32(payload) & 0xFFFFFFFF, len(payload), co.compress(payload) + co.flush())
+    if len(payload) <= (1 << 20):
+        co = zlib.compressobj(level, zlib.DEFLATED, -15)
+        return (name.encode(), zlib.crc32(payload) & 0xFFFFFFFF, len(payload), co.compress(payload) + co.flush())
+    # a large member (the usage table of 100 000 cells): pieces deflated independently on host threads and joined into
+    # ONE valid raw-deflate stream -- every piece but the last ends on a byte boundary with an empty stored block
+    # (Z_SYNC_FLUSH), the last one carries the final-block bit (what pigz does)
+    from concurrent.futures import ThreadPoolExecutor
+    view = memoryview(payload)
+    step = 1 << 19
+    pieces = [view[i:i + step] for i in range(0, len(payload), step)]
+
+    def one(args):
+        i, piece = args
+        co = zlib.compressobj(level, zlib.DEFLATED, -15)
+        return co.compress(piece) + co.flush(zlib.Z_FINISH if i == len(pieces) - 1 else zlib.Z_SYNC_FLUSH)
+    with ThreadPoolExecutor(max_workers=min(8, len(pieces))) as pool:
+        comp = b"".join(pool.map(one, enumerate(pieces)))
+    return (name.encode(), zlib.crc32(payload) & 0xFFFFFFFF, len(payload), comp)
 
 
 def _write_zip(filename, members):
