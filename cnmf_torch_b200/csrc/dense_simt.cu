@@ -156,7 +156,7 @@ struct WarpHalving<N, 0> {
 
 template <int KP, int GW_THREADS>
 __global__ void __launch_bounds__(GW_THREADS) gram_warp_kernel(const float* __restrict__ F, int64_t ld, int64_t L,
-                                                               float* __restrict__ partial, int nsplit) {
+                                                               float* __restrict__ partial, int nsplit, int vec) {
   constexpr int NT = KP * (KP + 1) / 2;
   __shared__ float red[GW_THREADS / 32][NT];
   const int r = blockIdx.y, split = blockIdx.x;
@@ -167,19 +167,29 @@ __global__ void __launch_bounds__(GW_THREADS) gram_warp_kernel(const float* __re
   float acc[NT];
 #pragma unroll
   for (int i = 0; i < NT; ++i) acc[i] = 0.f;
-  for (int64_t l0 = l_begin + warp * 32; l0 < l_end; l0 += (GW_THREADS / 32) * 32 * 2) {
-    float f0[KP], f1[KP];
-    const int64_t c0 = l0 + lane, c1 = l0 + (GW_THREADS / 32) * 32 + lane;
+  // A lane takes four consecutive columns per step (one 16-byte load per row: 12 loads keep 6 KB per warp in flight;
+  // the scalar form with two columns per lane kept 3 KB and ran at 2.7 TB/s, latency-bound).  vec = 0 (ld not a
+  // multiple of 4 or F not 16-byte aligned: only a caller of the public entry point can do that): scalar loads.
+  for (int64_t l0 = l_begin + warp * 128; l0 < l_end; l0 += (GW_THREADS / 32) * 128) {
+    const int64_t c = l0 + lane * 4;
+    float4 f[KP];
+    if (vec && c + 3 < l_end) {
 #pragma unroll
-    for (int a = 0; a < KP; ++a) {
-      f0[a] = c0 < l_end ? Fr[(int64_t)a * ld + c0] : 0.f;
-      f1[a] = c1 < l_end ? Fr[(int64_t)a * ld + c1] : 0.f;
+      for (int a = 0; a < KP; ++a) f[a] = *reinterpret_cast<const float4*>(Fr + (int64_t)a * ld + c);
+    } else {
+#pragma unroll
+      for (int a = 0; a < KP; ++a) {
+        const float* q = Fr + (int64_t)a * ld + c;
+        f[a] = make_float4(c < l_end ? q[0] : 0.f, c + 1 < l_end ? q[1] : 0.f, c + 2 < l_end ? q[2] : 0.f,
+                           c + 3 < l_end ? q[3] : 0.f);
+      }
     }
     int t = 0;
 #pragma unroll
     for (int a = 0; a < KP; ++a)
 #pragma unroll
-      for (int b = a; b < KP; ++b, ++t) acc[t] = fmaf(f1[a], f1[b], fmaf(f0[a], f0[b], acc[t]));
+      for (int b = a; b < KP; ++b, ++t)
+        acc[t] = fmaf(f[a].w, f[b].w, fmaf(f[a].z, f[b].z, fmaf(f[a].y, f[b].y, fmaf(f[a].x, f[b].x, acc[t]))));
   }
   WarpHalving<NT, 16>::run(acc, lane, 0, NT, [&](int i, float v) { red[warp][i] = v; });
   __syncthreads();
@@ -443,18 +453,19 @@ int launch_gram_partial(const float* F, int64_t ld, int R, int Kp, int64_t L, vo
     // empty wave starts, and 128-thread CTAs (four per SM, twice the columns per warp) finish sooner
     // (R=400, Kp=12: 18.5 -> 14.4 us; R=200, Kp=8: 10.1 us with 256 threads, 11.4 with 128).
     const bool narrow = static_cast<int64_t>(ns) * R > 296;
+    const int vec = (ld % 4 == 0 && aligned16(F)) ? 1 : 0;
     switch (Kp) {
       case 4:
-        if (narrow) gram_warp_kernel<4, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
-        else gram_warp_kernel<4, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
+        if (narrow) gram_warp_kernel<4, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns, vec);
+        else gram_warp_kernel<4, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns, vec);
         break;
       case 8:
-        if (narrow) gram_warp_kernel<8, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
-        else gram_warp_kernel<8, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
+        if (narrow) gram_warp_kernel<8, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns, vec);
+        else gram_warp_kernel<8, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns, vec);
         break;
       case 12:
-        if (narrow) gram_warp_kernel<12, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns);
-        else gram_warp_kernel<12, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns);
+        if (narrow) gram_warp_kernel<12, 128><<<grid, 128, 0, st>>>(F, ld, L, partial, ns, vec);
+        else gram_warp_kernel<12, 256><<<grid, 256, 0, st>>>(F, ld, L, partial, ns, vec);
         break;
       default:
         set_error("gram: Kp=%d unsupported (multiples of 4 up to %d)", Kp, CNMF_B200_MAX_KP);
