@@ -41,7 +41,7 @@ ITERS_PER_STEP = 10
 ALGO = "hals"
 E2E_ITERS = 100  # iterations per replicate in one end-to-end public-API call
 KL_PROFILE_CSV = "r01_kl_half_step_full_raw.csv"   # the gather kernels are round 1's; same code
-KL_SLAB_PROFILE_CSV = "r02_kl_slab_c_raw.csv"
+KL_SLAB_PROFILE_CSV = "r02_kl_slab_d_raw.csv"
 TC_PROFILE_CSV = "r02_tc_half_step_full_raw.csv"   # ncu --set full raw page of the dominant kernel, this round
 METRIC = "nmf_replicate_iterations_per_second"
 UNIT = "replicate-iters/s"
