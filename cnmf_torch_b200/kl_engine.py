@@ -18,13 +18,17 @@ from .engine import EPS_DEFAULT, BatchResult, SeedInit, draw_init
 _KL_IMPL = {"slab": _lib.KL_IMPL_SLAB, "gather": _lib.KL_IMPL_GATHER}
 
 
-def kl_impl_for(Kp: int) -> int:
-    """The faster kernel family for a stack of padded K = Kp, measured at 100 000 x 2000 cells (ms per batched
-    iteration, R = 200 / R = 26; profiles/NOTES.md): Kp=6 slab 8.6 / 1.45 vs gather 9.8 / 1.70; 8: 9.6 / 1.67 vs
+def kl_impl_for(Kp: int, R: int = 1 << 30) -> int:
+    """The faster kernel family for a stack of R replicates of padded K = Kp, measured at 100 000 x 2000 cells (ms per
+    batched iteration, R = 200 / R = 26; profiles/NOTES.md): Kp=6 slab 8.6 / 1.45 vs gather 9.8 / 1.70; 8: 9.6 / 1.67 vs
     11.4 / 1.92; 10: 13.5 / 2.16 vs 13.6 / 2.40; 12: 19.0 / 2.83 vs 15.6 / 2.68; 14: 19.1 / 2.85 vs 19.0 / 3.34.
     A slab line holds floor(16 / (Kp/2)) replicate pairs: at Kp = 12 only 12 of a half-warp's 16 lanes have work and a
-    group is 4 replicates; from Kp = 16 on the slab kernels' accumulators no longer fit the register file."""
-    return _lib.KL_IMPL_SLAB if (Kp <= 10 or Kp == 14) else _lib.KL_IMPL_GATHER
+    group is 4 replicates, so the gather family wins there -- except for the few replicates left of a stack near the
+    end of a run, which fill a gather warp (32 consecutive replicates) badly: R = 4 / 8 / 12 slab 0.56 / 0.95 / 1.34 vs
+    gather 0.79 / 1.03 / 1.38 ms.  From Kp = 16 on the slab kernels' accumulators no longer fit the register file."""
+    if Kp <= 10 or Kp == 14 or (Kp == 12 and R <= 12):
+        return _lib.KL_IMPL_SLAB
+    return _lib.KL_IMPL_GATHER
 
 
 def pad2(k: int) -> int:
@@ -246,7 +250,7 @@ class KlBatch:
         self.p = KlProblem(
             n_cells=eng.N, n_genes=eng.G, nnz=eng.nnz, row_ptr=ptr(eng.row_ptr), col_idx=ptr(eng.col_idx),
             val=ptr(eng.val), t_row_ptr=ptr(eng.t_row_ptr), t_col_idx=ptr(eng.t_col_idx), t_val=ptr(eng.t_val),
-            R=R, K=self.K, Kp=Kp, impl=eng.impl if eng.impl is not None else kl_impl_for(Kp), Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active),
+            R=R, K=self.K, Kp=Kp, impl=eng.impl if eng.impl is not None else kl_impl_for(Kp, R), Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active),
             # an L1 strength is compared with a numerator, which scales like the factors; an L2 strength multiplies a
             # factor entry against a denominator that scales the same way
             l1_H=l1_H * eng.c, l2_H=l2_H, l1_W=l1_W * eng.c, l2_W=l2_W, eps=eps, sumX=eng.sumX, xlogx=eng.xlogx,
