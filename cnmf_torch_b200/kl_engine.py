@@ -240,7 +240,7 @@ class KlBatch:
         self._regs = (l1_H, l2_H, l1_W, l2_W, eps)
         self._setup_problem()
 
-    def _setup_problem(self):
+    def _setup_problem(self, impl=None):
         """Masks, outputs, the C-ABI problem struct and its workspace for the factors this batch holds."""
         eng, R, Kp = self.eng, self.R, self.Kp
         dev = eng.device
@@ -250,7 +250,8 @@ class KlBatch:
         self.p = KlProblem(
             n_cells=eng.N, n_genes=eng.G, nnz=eng.nnz, row_ptr=ptr(eng.row_ptr), col_idx=ptr(eng.col_idx),
             val=ptr(eng.val), t_row_ptr=ptr(eng.t_row_ptr), t_col_idx=ptr(eng.t_col_idx), t_val=ptr(eng.t_val),
-            R=R, K=self.K, Kp=Kp, impl=eng.impl if eng.impl is not None else kl_impl_for(Kp, R), Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active),
+            R=R, K=self.K, Kp=Kp, impl=impl if impl is not None else (eng.impl if eng.impl is not None else kl_impl_for(Kp, R)),
+            Hr=ptr(self.Hr), Wt=ptr(self.Wt), active=ptr(self.active),
             # an L1 strength is compared with a numerator, which scales like the factors; an L2 strength multiplies a
             # factor entry against a denominator that scales the same way
             l1_H=l1_H * eng.c, l2_H=l2_H, l1_W=l1_W * eng.c, l2_W=l2_W, eps=eps, sumX=eng.sumX, xlogx=eng.xlogx,
@@ -270,7 +271,7 @@ class KlBatch:
         sub.Hr = self.Hr.index_select(1, ii)
         sub.Wt = self.Wt.index_select(1, ii)
         sub._regs = self._regs
-        sub._setup_problem()
+        sub._setup_problem(impl=self.p.impl)   # same kernel family: a replicate's bits do not depend on its neighbours
         return sub
 
     def absorb(self, sub: "KlBatch", idx):
