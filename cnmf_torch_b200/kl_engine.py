@@ -23,9 +23,9 @@ def kl_impl_for(Kp: int, R: int = 1 << 30) -> int:
     batched iteration, R = 200 / R = 26; profiles/NOTES.md): Kp=6 slab 8.6 / 1.45 vs gather 9.8 / 1.70; 8: 9.6 / 1.67 vs
     11.4 / 1.92; 10: 13.5 / 2.16 vs 13.6 / 2.40; 12: 19.0 / 2.83 vs 15.6 / 2.68; 14: 19.1 / 2.85 vs 19.0 / 3.34.
     A slab line holds floor(16 / (Kp/2)) replicate pairs: at Kp = 12 only 12 of a half-warp's 16 lanes have work and a
-    group is 4 replicates, so the gather family wins there -- except for the few replicates left of a stack near the
-    end of a run, which fill a gather warp (32 consecutive replicates) badly: R = 4 / 8 / 12 slab 0.56 / 0.95 / 1.34 vs
-    gather 0.79 / 1.03 / 1.38 ms.  From Kp = 16 on the slab kernels' accumulators no longer fit the register file."""
+    group is 4 replicates, so the gather family wins there -- except for a stack of a few replicates (a widely sharded
+    ledger), which fills a gather warp (32 consecutive replicates) badly: R = 4 / 8 / 12 slab 0.56 / 0.95 / 1.34 vs
+    gather 0.79 / 1.03 / 1.38 ms.  (A batch compacted during a run keeps the family it started with.)  From Kp = 16 on the slab kernels' accumulators no longer fit the register file."""
     if Kp <= 10 or Kp == 14 or (Kp == 12 and R <= 12):
         return _lib.KL_IMPL_SLAB
     return _lib.KL_IMPL_GATHER

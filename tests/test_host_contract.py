@@ -187,7 +187,7 @@ def test_kl_kernel_family_by_padded_k():
     assert [kl_impl_for(pad2(k)) for k in (5, 6, 7, 8, 9, 10)] == [_lib.KL_IMPL_SLAB] * 6
     assert kl_impl_for(pad2(11)) == kl_impl_for(12) == _lib.KL_IMPL_GATHER
     assert kl_impl_for(pad2(13)) == _lib.KL_IMPL_SLAB
-    assert kl_impl_for(12, 8) == _lib.KL_IMPL_SLAB and kl_impl_for(12, 13) == _lib.KL_IMPL_GATHER   # a stack's last few
+    assert kl_impl_for(12, 8) == _lib.KL_IMPL_SLAB and kl_impl_for(12, 13) == _lib.KL_IMPL_GATHER   # a short stack
     assert all(kl_impl_for(kp) == _lib.KL_IMPL_GATHER for kp in range(16, 34, 2))
 
 
