@@ -217,15 +217,15 @@ class DenseFrobeniusEngine:
 
     def factorize(self, K: int, seeds=None, H0=None, W0=None, algo="mu", tol=1e-4, max_iter=500,
                   l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT, check_every=10,
-                  return_H=False) -> BatchResult:
+                  return_H=False, compact=0.8) -> BatchResult:
         """Batch-mode Frobenius NMF of R replicates (R = len(seeds) or W0.shape[0]).
         Convergence per replicate as run_nmf: every ``check_every`` iterations,
         stop when prev <= cur or |prev - cur| / init < tol; converged replicates are frozen."""
         b = self.new_batch(K, seeds, H0, W0, algo, l1_H, l2_H, l1_W, l2_W, eps)
-        return run_batches([b], tol, max_iter, check_every, return_H)[0]
+        return run_batches([b], tol, max_iter, check_every, return_H, compact=compact)[0]
 
     def factorize_many(self, ks, seeds_by_k, algo="mu", tol=1e-4, max_iter=500, l1_H=0.0, l2_H=0.0, l1_W=0.0,
-                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False):
+                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False, compact=0.8):
         """Several K at once (the shape of a cNMF run: K = 5..13 x 100 replicates).  The K-batches are
         independent, so their kernels run on separate streams and overlap, their inits are drawn by a
         thread pool while earlier batches are already uploading, and convergence is checked for all of
@@ -244,7 +244,7 @@ class DenseFrobeniusEngine:
                 groups = [(k,) + tuple(futs[k].result()) for k in group]
                 batches.append(FrobBatch(self, None, None, None, algo, l1_H, l2_H, l1_W, l2_W, eps, groups=groups))
         streams = [torch.cuda.Stream(device=self.device) for _ in batches]
-        res = run_batches(batches, tol, max_iter, check_every, return_H, streams)
+        res = run_batches(batches, tol, max_iter, check_every, return_H, streams, compact)
         out = {}
         for b, rb in zip(batches, res):
             for k, sl, W, H in b.results_by_group(return_H):
@@ -417,34 +417,53 @@ class DenseFrobeniusEngine:
         return res
 
 
-def run_batches(batches, tol, max_iter, check_every=10, return_H=False, streams=None):
+def run_batches(batches, tol, max_iter, check_every=10, return_H=False, streams=None, compact=0.8):
     """run_nmf's batch loop for a list of resident batches in lock-step: every ``check_every`` iterations the
     objective of every replicate is read back (R doubles per batch) and replicates with
-    prev <= cur or |prev - cur| / init < tol are frozen (their state stops changing on the device)."""
+    prev <= cur or |prev - cur| / init < tol are frozen (their state stops changing on the device).
+
+    A frozen replicate still rides through the GEMM of its tile, and the replicates of a stack stop at very different
+    checks; once no more than ``compact`` of a working batch is alive (and at least 16 replicates are frozen) the
+    live ones are copied into a smaller batch (``FrobBatch.subset``) and the loop continues there; their factors are
+    copied back at the end.  A replicate's arithmetic depends on its neighbours in the stack only through the tile
+    shape (fp32 summation order, tests/test_gpu_properties.py), so the results are those of the uncompacted run to
+    that rounding (``test_cfg2_compaction_matches_uncompacted_run``).  ``compact=0`` turns it off."""
     st = [dict(init=b.objective()) for b in batches]
     for s, b in zip(st, batches):
-        s.update(prev=s["init"].copy(), cur=s["init"], trace=[(0, s["init"].copy())],
-                 n_iter=np.full(b.R, max_iter, dtype=np.int64), alive=np.ones(b.R, dtype=bool))
+        s.update(prev=s["init"].copy(), cur=s["init"].copy(), trace=[(0, s["init"].copy())],
+                 n_iter=np.full(b.R, max_iter, dtype=np.int64), alive=np.ones(b.R, dtype=bool),
+                 wb=b, widx=np.arange(b.R))      # the working batch and its replicates' positions in b
     it = 0
     while it < max_iter and any(s["alive"].any() for s in st):
         step = min(check_every, max_iter - it)
         live = [i for i, s in enumerate(st) if s["alive"].any()]
-        iterate_concurrently([batches[i] for i in live], step, [streams[i] for i in live] if streams else None)
+        iterate_concurrently([st[i]["wb"] for i in live], step, [streams[i] for i in live] if streams else None)
         it += step
         for i in live:
-            s, b = st[i], batches[i]
-            cur = b.read_loss()
-            s["cur"] = cur
+            s, b, wb = st[i], batches[i], st[i]["wb"]
+            s["cur"][s["widx"]] = wb.read_loss()
+            cur = s["cur"]
             s["trace"].append((it, cur.copy()))
             if it % check_every == 0:
                 conv = s["alive"] & ((s["prev"] <= cur) | (np.abs((s["prev"] - cur) / s["init"]) < tol))
                 if conv.any():
                     s["n_iter"][conv] = it
                     s["alive"] &= ~conv
-                    b.set_active(s["alive"])
+                    wb.set_active(s["alive"][s["widx"]])
                 s["prev"] = np.where(s["alive"], cur, s["prev"])
+                n_alive = int(s["alive"].sum())
+                if compact > 0 and 0 < n_alive <= compact * wb.R and wb.R - n_alive >= 16 and it < max_iter:
+                    if wb is not b:
+                        b.absorb(wb, s["widx"])
+                    else:
+                        b.release_workspace()
+                    s["widx"] = np.flatnonzero(s["alive"])
+                    s["wb"] = b.subset(s["widx"])
     out = []
     for s, b in zip(st, batches):
+        if s["wb"] is not b:
+            b.absorb(s["wb"], s["widx"])
+            s["wb"] = None
         W, H = b.results(return_H) if len(b.Ks) == 1 else (None, None)   # mixed-K stacks: results_by_group
         out.append(BatchResult(W=W, H=H, err=np.sqrt(np.maximum(2.0 * s["cur"], 0.0)), n_iter=s["n_iter"],
                                trace=s["trace"], launches=int(b.launches)))
@@ -512,14 +531,22 @@ class FrobBatch:
             self.Wall = parts[0][0] if len(parts) == 1 else torch.cat([q[0] for q in parts], 0)
             self.Ht = parts[0][1] if len(parts) == 1 else torch.cat([q[1] for q in parts], 0)
             del parts
-        self.gramW = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
-        self.gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
-        self.active = torch.ones(R, device=dev, dtype=torch.uint8)
-        self.err2 = torch.zeros(R, device=dev, dtype=torch.float64)
         # the true K of every replicate of a mixed-K stack: the tensor-core epilogue works on those components only
         self.rep_k = None
         if any(k != Kp for k in self.Ks):
             self.rep_k = torch.from_numpy(np.repeat(np.asarray(self.Ks, dtype=np.uint8), self.Rs)).to(dev)
+        self._regs = (algo_id, l1_H, l2_H, l1_W, l2_W, eps, ldw, ldh)
+        self._setup_problem()
+
+    def _setup_problem(self):
+        """Grams, masks, outputs, the C-ABI problem struct and its workspace for the factors this batch holds."""
+        eng, R, Kp = self.eng, self.R, self.Kp
+        dev = eng.device
+        algo_id, l1_H, l2_H, l1_W, l2_W, eps, ldw, ldh = self._regs
+        self.gramW = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
+        self.gramH = torch.zeros((R, Kp, Kp), device=dev, dtype=torch.float32)
+        self.active = torch.ones(R, device=dev, dtype=torch.uint8)
+        self.err2 = torch.zeros(R, device=dev, dtype=torch.float64)
         self.p = FrobProblem(
             n_cells=eng.N, n_genes=eng.G, X=ptr(eng.X), ldx=eng.ldx, Xt=ptr(eng.Xt), ldxt=eng.ldxt,
             R=R, K=self.K, Kp=Kp, algo=algo_id, impl=eng.impl, Wall=ptr(self.Wall), ldw=ldw,
@@ -531,6 +558,31 @@ class FrobBatch:
         self.p.workspace, self.p.workspace_bytes = ptr(self.ws), self.ws.numel()
         self.launches = 0
         check(eng.lib.cnmf_b200_frob_prepare(C.byref(self.p), self._stream()), "frob_prepare")
+
+    def subset(self, idx) -> "FrobBatch":
+        """A new batch holding copies of the replicates ``idx`` of this one (current state, same settings): what
+        ``run_batches`` continues on once enough replicates of a stack are frozen.  ``absorb`` copies them back."""
+        sub = object.__new__(FrobBatch)
+        sub.eng, sub.Ks, sub.Rs, sub.K, sub.Kp, sub.R = self.eng, None, None, self.K, self.Kp, len(idx)
+        ii = torch.as_tensor(np.asarray(idx), device=self.eng.device, dtype=torch.long)
+        sub.Wall = self.Wall.index_select(0, ii)
+        sub.Ht = self.Ht.index_select(0, ii)
+        sub.rep_k = None if self.rep_k is None else self.rep_k.index_select(0, ii)
+        sub._regs = self._regs
+        sub._setup_problem()
+        return sub
+
+    def absorb(self, sub: "FrobBatch", idx) -> None:
+        """Replicates ``idx`` of this batch take the factors of ``sub`` (made by ``subset(idx)``)."""
+        ii = torch.as_tensor(np.asarray(idx), device=self.eng.device, dtype=torch.long)
+        self.Wall.index_copy_(0, ii, sub.Wall)
+        self.Ht.index_copy_(0, ii, sub.Ht)
+        self.launches += sub.launches
+
+    def release_workspace(self) -> None:
+        """Give the workspace back (a stack whose live replicates moved to a subset keeps only its factors)."""
+        self.ws = None
+        self.p.workspace, self.p.workspace_bytes = None, 0
 
     @staticmethod
     def _stream():

@@ -49,6 +49,24 @@ def test_cfg2_convergence_freezes_replicates(cfg2):
         assert max(vals) - min(vals) <= 1e-9 * abs(last[r])
 
 
+def test_cfg2_compaction_matches_uncompacted_run(cfg2):
+    """run_batches moves the live replicates of a stack into a smaller batch as the others freeze
+    (FrobBatch.subset); the factors come out as in the uncompacted run, up to the summation-order rounding of a
+    different tile shape."""
+    from cnmf_torch_b200.engine import DenseFrobeniusEngine
+    eng = DenseFrobeniusEngine(cfg2)
+    kw = dict(seeds=list(range(1, 65)), algo="hals", tol=1e-3, max_iter=400)
+    a = eng.factorize(7, compact=0.8, **kw)
+    b = eng.factorize(7, compact=0.0, **kw)
+    assert a.n_iter.min() < a.n_iter.max()                       # replicates stopped at different checks
+    assert np.mean(a.n_iter == b.n_iter) >= 0.9                  # (a borderline stop may move by one check)
+    same = a.n_iter == b.n_iter
+    assert np.all(np.abs(a.err[same] - b.err[same]) <= 1e-4 * b.err[same])
+    for r in np.flatnonzero(same):
+        c = np.corrcoef(a.W[r].ravel(), b.W[r].ravel())[0, 1]
+        assert c >= 0.9999, (r, c)
+
+
 def test_kl_large_monotone_and_edge_rows():
     from cnmf_torch_b200.kl_engine import SparseKLEngine
     from cnmf_torch_b200.synth import nb_counts
