@@ -96,6 +96,7 @@ SIGNATURES = {
     "cnmf_b200_online_chunk": (i32, [C.POINTER(OnlineChunkArgs), i32, vp]),
     "cnmf_b200_kl_constants": (i32, [vp, i64, vp, vp]),
     "cnmf_b200_to_half": (i32, [vp, vp, i64, vp]),
+    "cnmf_b200_write_npz_batch": (i32, [i64, vp, vp, vp, vp, vp, vp, vp, C.c_char_p, i64, i64, C.c_uint32, i32, i32]),
     "cnmf_b200_write_tsv": (i32, [C.c_char_p, C.c_char_p, i64, C.c_char_p, vp, vp, i32, i64, i64, i64, i32]),
     "cnmf_b200_kl_half_step": (i32, [vp, vp, vp, i64, vp, vp, vp, vp, vp, i32, i32, f32, f32, f32, vp]),
     "cnmf_b200_kl_workspace_bytes": (i64, [C.POINTER(KlProblem)]),

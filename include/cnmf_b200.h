@@ -434,6 +434,20 @@ int cnmf_b200_ols_xty(const int64_t* col_ptr, const int32_t* row_idx, const floa
 int64_t cnmf_b200_last_launch_count(void);
 
 /* ------------------------------------------------------------------------------------------
+ * Host-side helper of the on-disk path (no device work): n_files `.df.npz` archives as save_df_to_npz writes them
+ * (/root/reference/src/cnmf/cnmf.py:32-34: np.savez_compressed(data=, index=, columns=)), compressed and written by up
+ * to 16 host threads.  File i gets member data.npy = data_hdr[i] (the .npy header of its shape, made by the caller)
+ * followed by data_bytes[i] bytes at data[i]; index.npy = index_npy[i] (a complete .npy image); columns.npy = the
+ * caller's PRE-DEFLATED raw stream (the gene names: identical for every replicate file of a run, compressed once).
+ * Members of 2 GiB or more are refused (no zip64).
+ * ---------------------------------------------------------------------------------------- */
+int cnmf_b200_write_npz_batch(int64_t n_files, const char* const* paths, const void* const* data,
+                              const int64_t* data_bytes, const char* const* data_hdr, const int64_t* data_hdr_len,
+                              const char* const* index_npy, const int64_t* index_npy_len, const char* columns_comp,
+                              int64_t columns_comp_len, int64_t columns_raw_len, uint32_t columns_crc, int32_t level,
+                              int32_t threads);
+
+/* ------------------------------------------------------------------------------------------
  * Host-side helper of the on-disk path (no device work): a float table as tab-separated text, byte for byte what
  * save_df_to_text writes (DataFrame.to_csv(sep="\t"), /root/reference/src/cnmf/cnmf.py:44-45): numpy's shortest
  * round-trip repr of every value (positional for 1e-4 <= |x| < 1e16 -- 1e6 for float --, else scientific; NaN -> empty field), rows

@@ -235,3 +235,22 @@ def test_large_frames_round_trip_through_the_fast_npz_writer(tmp_path):
         pd.testing.assert_frame_equal(back, df, check_names=False)
         with np.load(tmp_path / name, allow_pickle=True) as f:
             assert list(f.keys()) == ["data", "index", "columns"]
+
+
+def test_native_replicate_file_writer_matches_the_python_writer(tmp_path):
+    """cnmf_b200_write_npz_batch (the per-replicate spectra files of factorize, reference cnmf.py:889-892 through
+    save_df_to_npz :32-34): the same bytes as the Python zip writer, and the reference's loader reads them back."""
+    from cnmf_torch_b200 import cnmf as c
+    rng = np.random.default_rng(2)
+    genes = np.array(["gene_%d" % i for i in range(300)], dtype=object)
+    cols = c._deflated_member("columns.npy", c._npy_bytes(genes))
+    W = rng.random((40, 9, 300)).astype(np.float32)
+    jobs = [(str(tmp_path / ("n_%d.df.npz" % j)), np.ascontiguousarray(W[j, :5 + j % 5]), np.arange(1, 6 + j % 5))
+            for j in range(40)]
+    jobs.append((str(tmp_path / "f64.df.npz"), W[0].astype(np.float64), np.arange(1, 10)))     # takes the Python writer
+    c.save_replicate_files(jobs, cols)
+    for fn, d, ix in jobs:
+        df = c.load_df_from_npz(fn)
+        assert np.array_equal(df.values, d) and np.array_equal(df.index.values, ix) and list(df.columns) == list(genes)
+        c.save_arrays_to_df_npz(fn + ".ref.npz", d, ix, cols)
+        assert open(fn, "rb").read() == open(fn + ".ref.npz", "rb").read()
