@@ -154,7 +154,7 @@ def save_df_to_text(obj, filename):
     vals = obj.values if isinstance(obj, pd.DataFrame) else None
     plain = (vals is not None and vals.ndim == 2 and vals.dtype in (np.float32, np.float64)
              and not isinstance(obj.index, pd.MultiIndex) and not isinstance(obj.columns, pd.MultiIndex)
-             and vals.shape[0] >= 1000)
+             and vals.size >= 10000)
     if plain:
         idx = [str(v) for v in obj.index.tolist()]
         head = [str(obj.index.name or "")] + [str(v) for v in obj.columns.tolist()]

@@ -214,6 +214,11 @@ def test_text_tables_are_byte_identical_to_pandas(tmp_path, dtype):
         save_df_to_text(df, tmp_path / "fast.txt")
         df.to_csv(tmp_path / "pandas.txt", sep="\t")
         assert (tmp_path / "fast.txt").read_bytes() == (tmp_path / "pandas.txt").read_bytes()
+    wide = pd.DataFrame(a[:9 * 2000].reshape(9, -1)[:, :2000], index=np.arange(1, 10),
+                        columns=["gene_%d" % i for i in range(2000)])          # a spectra table: few rows, many columns
+    save_df_to_text(wide, tmp_path / "wide.txt")
+    wide.to_csv(tmp_path / "wide_pandas.txt", sep="\t")
+    assert (tmp_path / "wide.txt").read_bytes() == (tmp_path / "wide_pandas.txt").read_bytes()
     odd = pd.DataFrame(a[:1500], index=['c"%d' % i for i in range(1500)], columns=list("abcdefghi"))
     save_df_to_text(odd, tmp_path / "odd.txt")
     odd.to_csv(tmp_path / "odd_pandas.txt", sep="\t")
