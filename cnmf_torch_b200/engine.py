@@ -217,7 +217,7 @@ class DenseFrobeniusEngine:
 
     def factorize(self, K: int, seeds=None, H0=None, W0=None, algo="mu", tol=1e-4, max_iter=500,
                   l1_H=0.0, l2_H=0.0, l1_W=0.0, l2_W=0.0, eps=EPS_DEFAULT, check_every=10,
-                  return_H=False, compact=0.8) -> BatchResult:
+                  return_H=False, compact=0.5) -> BatchResult:
         """Batch-mode Frobenius NMF of R replicates (R = len(seeds) or W0.shape[0]).
         Convergence per replicate as run_nmf: every ``check_every`` iterations,
         stop when prev <= cur or |prev - cur| / init < tol; converged replicates are frozen."""
@@ -225,7 +225,7 @@ class DenseFrobeniusEngine:
         return run_batches([b], tol, max_iter, check_every, return_H, compact=compact)[0]
 
     def factorize_many(self, ks, seeds_by_k, algo="mu", tol=1e-4, max_iter=500, l1_H=0.0, l2_H=0.0, l1_W=0.0,
-                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False, compact=0.8):
+                       l2_W=0.0, eps=EPS_DEFAULT, check_every=10, return_H=False, compact=0.5):
         """Several K at once (the shape of a cNMF run: K = 5..13 x 100 replicates).  The K-batches are
         independent, so their kernels run on separate streams and overlap, their inits are drawn by a
         thread pool while earlier batches are already uploading, and convergence is checked for all of
@@ -417,13 +417,14 @@ class DenseFrobeniusEngine:
         return res
 
 
-def run_batches(batches, tol, max_iter, check_every=10, return_H=False, streams=None, compact=0.8):
+def run_batches(batches, tol, max_iter, check_every=10, return_H=False, streams=None, compact=0.5):
     """run_nmf's batch loop for a list of resident batches in lock-step: every ``check_every`` iterations the
     objective of every replicate is read back (R doubles per batch) and replicates with
     prev <= cur or |prev - cur| / init < tol are frozen (their state stops changing on the device).
 
     A frozen replicate still rides through the GEMM of its tile, and the replicates of a stack stop at very different
-    checks; once no more than ``compact`` of a working batch is alive (and at least 16 replicates are frozen) the
+    checks; once no more than ``compact`` of a working batch is alive (half: a step of this path is a few ms, so a
+    compaction -- new buffers, Grams, tensor maps -- must buy a halved GEMM) and at least 16 replicates are frozen the
     live ones are copied into a smaller batch (``FrobBatch.subset``) and the loop continues there; their factors are
     copied back at the end.  A replicate's arithmetic depends on its neighbours in the stack only through the tile
     shape (fp32 summation order, tests/test_gpu_properties.py), so the results are those of the uncompacted run to
